@@ -1,0 +1,176 @@
+/* pmps.h — C ABI of the B200-native PolyMPS particle hot path (libpmps.so).
+ *
+ * Drop-in boundary: the reference has no plugin/FFI layer; its seam is the set of
+ * engine-class methods  void f(MpsParticleSystem*, MpsParticle*, MpsBucket*)  called once per time step from
+ * mainLoopOfSimulation (reference src/main.cpp:230-468).  Every pmps_* stage call below replaces the body of exactly
+ * one of those methods (cited per function); the C++ shims in polymps_b200/host/ keep the reference class names and
+ * signatures and forward here.  Plain pointers and sizes only: no C++/torch types cross this boundary.
+ *
+ * Conventions
+ *  - every function returns 0 on success, <0 on error (PMPS_E_*); pmps_last_error() gives the message.
+ *    The reference itself is void/exit()/throw (src/MpsBucket.cpp:104, src/MpsInputOutput.cpp:521); the shims map
+ *    a non-zero return to the reference behaviour (message on stderr + exit(10)).
+ *  - host arrays use the reference layout: scalars a[i], vectors a[3*i+k], int32 ids, `bool` flags as 1 byte
+ *    (include/MpsParticle.h:139-241).  The library never frees or reallocates a host pointer.
+ *  - a handle owns all device memory; one host thread per handle (the reference is single-driver too).
+ *  - there is NO CPU fallback: if no CUDA device is usable pmps_create fails with PMPS_E_CUDA.
+ */
+#ifndef PMPS_H_
+#define PMPS_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PMPS_ABI_VERSION 1
+
+enum { PMPS_OK = 0, PMPS_E_ARG = -1, PMPS_E_CUDA = -2, PMPS_E_STATE = -3, PMPS_E_UNSUPPORTED = -4, PMPS_E_OVERFLOW = -5 };
+
+/* POD snapshot of the reference's MpsParticleSystem after setParameters()/MpsBucket::allocateMemory()
+ * (include/MpsParticleSystem.h:133-309, src/MpsParticle.cpp:136-227, src/MpsBucket.cpp:20-67).  Same names. */
+typedef struct PmpsParams {
+	int32_t abi_version;            /* = PMPS_ABI_VERSION */
+	/* options (enums as in include/MpsParticleSystem.h:20-124) */
+	int32_t dim;                    /* 2 or 3 ((int)PSystem->dim) */
+	int32_t wallType;               /* 0 particle walls, 1 polygon walls */
+	int32_t mpsType;                /* 0 E-MPS, 1 WC-MPS, 2 implicit PND, 3 implicit PND+divU */
+	int32_t solverType;             /* 0 CG, 1 BiCGSTAB */
+	int32_t pndType;                /* 0 sum wij, 1 mean, 2 diffusive */
+	int32_t weightType;             /* 0..4 (src/MpsParticle.cpp:57-108) */
+	int32_t gradientType;           /* 0..3 (src/MpsPressure.cpp:1288-1300) */
+	int32_t gradientCorrection;     /* bool */
+	int32_t slipCondition;          /* 0 no-slip, 1 free-slip */
+	int32_t freeSurfType;           /* 0 PND+neigh, 1 PND+NPCD, 2 ARC */
+	int32_t collisionType;          /* 0 PC, 1 DPC */
+	int32_t shiftingType;           /* 0 off, 1 DW*Uij, 2 grad C */
+	int32_t repulsiveForceType;     /* 0 Harada 1 Mitsume 2 Lennard-Jones 3 Monaghan-Kajtar */
+	int32_t fluidType;              /* 0 Newtonian (1 = non-Newtonian: PMPS_E_UNSUPPORTED) */
+	int32_t domainTypeBC;           /* 0 none (1 = periodic: PMPS_E_UNSUPPORTED) */
+	int32_t ghost, fluid, wall, dummyWall;      /* particle type ids */
+	int32_t surface, inner, other;              /* particleBC ids */
+	int32_t numBucketsX, numBucketsY, numBucketsZ;
+	int32_t numOfMeshs;
+	int32_t shiftingJacobi;         /* 1: shifting reads a position snapshot (default, parallel-safe);
+	                                   the reference's 1-thread behaviour is a Gauss-Seidel sweep in index order */
+	int32_t _pad0;
+	/* geometry */
+	double domainMinX, domainMinY, domainMinZ, domainMaxX, domainMaxY, domainMaxZ;   /* AFTER the +-3 lo extension */
+	double bucketSide, invBucketSide;
+	double partDist, timeStep, epsilonZero;
+	double reS, reL, reS2, reL2;
+	/* physics */
+	double gravityX, gravityY, gravityZ;
+	double densityWall, DNS_FL1, DNS_FL2;
+	double soundSpeed, gamma;
+	double relaxPress, alphaCompressibility;
+	double reRepulsiveForce, expectMaxVelocity;
+	double repForceCoefMitsume, repForceCoefLennardJones, repForceCoefMonaghanKajtar;
+	double uniformVelWall[3];
+	/* derived coefficients (src/MpsParticle.cpp:196-222) */
+	double pndSmallZero, pndLargeZero, pndGradientZero, lambdaZero, numNeighZero;
+	double coeffViscMultiphase, coeffPressGrad, coeffPressEMPS, coeffPressWCMPS;
+	double coeffShifting1, coeffShifting2, coeffPPE, coeffPPESource;
+	double distCollisionLimit2, restitutionCollision, lambdaCollision;
+	double betaPnd, betaNeigh, delta2;
+	double velMax;                  /* velMax carried in from the host (0 at start, src/MpsParticle.cpp:212) */
+} PmpsParams;
+
+/* Pointers into the host's MpsParticle arrays (include/MpsParticle.h:139-241); NULL = not transferred. */
+typedef struct PmpsHostArrays {
+	int32_t numParticles;           /* live particles (MpsParticle::numParticles) */
+	int32_t numParticlesZero;       /* allocated length (MpsParticle::numParticlesZero) */
+	int32_t *particleType, *particleBC, *numNeigh, *PTYPE, *nearMeshType, *numNeighWallContribution, *elementID;
+	uint8_t *particleNearWall;      /* C++ bool, 1 byte */
+	double *press, *pndi, *pndki, *pndski, *pndSmall, *npcdDeviation2, *concentration, *velDivergence, *diffusiveTerm;
+	double *pndWallContribution, *distParticleWall2, *deviationDotPolygonNormal, *RHO, *MEU, *pndAuxVar1, *pndAuxVar2;
+	double *pressurePPE, *sourceTerm;                      /* Eigen::VectorXd::data() */
+	double *pos, *vel, *acc, *accStar, *npcdDeviation, *gradConcentration;
+	double *correcMatrixRow1, *correcMatrixRow2, *correcMatrixRow3;
+	double *particleAtWallPos, *mirrorParticlePos, *polygonNormal, *forceWall, *dvelCollision;
+} PmpsHostArrays;
+
+typedef struct PmpsScalars {      /* what displayInfo prints (src/MpsInputOutput.cpp:45-53) + health counters */
+	int32_t numParticles;
+	int32_t solverIter;
+	double velMax, CFLcurrent, solverError;
+	double maxDisplacement;       /* max |x - x(at bucket rebuild)| seen this step; > (bucketSide-reL)/2 means the
+	                                 reference's own stale-bucket search would start missing neighbours */
+	int32_t outOfDomainEvents;    /* particles turned into ghosts so far (src/MpsParticle.cpp:286-396) */
+	int32_t maxBucketCount;       /* fullest bucket at the last rebuild */
+} PmpsScalars;
+
+typedef struct pmps_handle pmps_t;
+
+/* ---- lifetime ---------------------------------------------------------------------------------------------- */
+int pmps_create(const PmpsParams* params, int device, pmps_t** out);
+int pmps_destroy(pmps_t* h);
+const char* pmps_last_error(const pmps_t* h);       /* h may be NULL: last error of a failed pmps_create */
+int pmps_abi_version(void);
+
+/* polygon mesh after the reference's initMesh (src/main.cpp:471-555): vertices/faces/normals as produced by
+ * igl::remove_duplicate_vertices + per_face_normals (src/PolygonMesh.cpp:98-106) and the four 50-entry wall
+ * tables of initWijnNeigh (src/PolygonMesh.cpp:377-527).  Call again for a forced mesh after it moved (:413). */
+int pmps_set_mesh(pmps_t* h, int mesh_id, int nV, const double* V, int nF, const int32_t* F, const double* faceNormals,
+                  int nTable, const double* xDataPND, const double* xDataNeigh, const double* Zij, const int32_t* nNeighWall);
+
+/* ---- transfers --------------------------------------------------------------------------------------------- */
+int pmps_upload(pmps_t* h, const PmpsHostArrays* a);           /* all non-NULL arrays, host (reference) order */
+int pmps_download(pmps_t* h, PmpsHostArrays* a);               /* scatter back to host order; non-NULL arrays only */
+int pmps_get_scalars(pmps_t* h, PmpsScalars* out);
+int pmps_set_velmax(pmps_t* h, double velMax);
+int pmps_set_uniform_vel_wall(pmps_t* h, const double v[3]);
+/* device-resident inputs (bench `value` leg, multi-GPU slabs): same layout as the host arrays, device pointers */
+int pmps_upload_device(pmps_t* h, const PmpsHostArrays* device_arrays);
+
+/* ---- stage calls: one per reference method, in mainLoopOfSimulation order (src/main.cpp:256-456) ----------- */
+int pmps_update_buckets(pmps_t* h);              /* MpsBucket::updateParticlesID            src/MpsBucket.cpp:299-353 */
+int pmps_calc_viscosity(pmps_t* h);              /* MpsViscosity::calcViscosity             src/MpsViscosity.cpp:20-100 */
+int pmps_add_gravity(pmps_t* h);                 /* MpsParticle::addGravity                 src/MpsParticle.cpp:111-130 */
+int pmps_predict(pmps_t* h);                     /* MpsParticleVelPos::predictionVelocityPosition  src/MpsParticleVelPos.cpp:20-50 */
+int pmps_check_out_domain(pmps_t* h);            /* MpsParticle::checkParticleOutDomain     src/MpsParticle.cpp:234-402 */
+int pmps_collisions(pmps_t* h);                  /* MpsParticleCollision::checkParticleCollisions / ...Dynamic...  src/MpsParticleCollision.cpp:22-292 */
+int pmps_wall_closest_point(pmps_t* h);          /* PolygonMesh::closestPointPNDBoundaryAABB (all meshes) + updateParticlesNearPolygonMesh  src/PolygonMesh.cpp:585-795 */
+int pmps_wall_npcd(pmps_t* h);                   /* MpsPndNeigh::calcWallNPCD               src/MpsPndNeigh.cpp:105-195 */
+int pmps_correction_matrix(pmps_t* h);           /* MpsVectorMatrix::correctionMatrix       src/MpsVectorMatrix.cpp:20-93 */
+int pmps_pnd_neigh_npcd(pmps_t* h);              /* MpsPndNeigh::calcPndnNeighNPCD          src/MpsPndNeigh.cpp:199-331 */
+int pmps_pnd_diffusive(pmps_t* h);               /* MpsPndNeigh::calcPndDiffusiveTerm       src/MpsPndNeigh.cpp:334-489 */
+int pmps_wall_pnd_diffusive(pmps_t* h);          /* MpsPndNeigh::calcWall{Slip,NoSlip}PndDiffusiveTerm  src/MpsPndNeigh.cpp:492-744 */
+int pmps_update_pnd(pmps_t* h);                  /* MpsPndNeigh::updatePnd                  src/MpsPndNeigh.cpp:747-774 */
+int pmps_mean_pnd_wall_dummy_surface(pmps_t* h); /* MpsPndNeigh::meanPndParticlesWallDummySurface  src/MpsPndNeigh.cpp:777-852 */
+int pmps_update_bc(pmps_t* h);                   /* MpsBoundaryCondition::updateParticleBC  src/MpsBoundaryCondition.cpp:66-399 */
+int pmps_calc_press(pmps_t* h);                  /* MpsPressure::calcPress (EOS or PPE+Krylov)  src/MpsPressure.cpp:31-57 */
+int pmps_extrapolate_press(pmps_t* h);           /* MpsPressure::extrapolatePressParticlesWallDummy  src/MpsPressure.cpp:792-846 */
+int pmps_press_gradient(pmps_t* h);              /* MpsPressure::calcPressGradient          src/MpsPressure.cpp:1217-1338 */
+int pmps_wall_press_gradient(pmps_t* h);         /* MpsPressure::calcWallPressGradient      src/MpsPressure.cpp:1341-1550 */
+int pmps_wall_viscosity(pmps_t* h);              /* MpsViscosity::calcWall{Slip,NoSlip}Viscosity  src/MpsViscosity.cpp:1527-1910 */
+int pmps_correct(pmps_t* h);                     /* MpsParticleVelPos::correctionVelocityPosition  src/MpsParticleVelPos.cpp:53-97 */
+int pmps_shifting(pmps_t* h);                    /* MpsShifting::calcConcAndConcGradient (+ calcShifting for type 1)  src/MpsShifting.cpp:23-101,432-575 */
+int pmps_wall_shifting(pmps_t* h);               /* MpsShifting::calcWallConcAndConcGradient  src/MpsShifting.cpp:578-691 */
+int pmps_update_wall_dummy_vel(pmps_t* h);       /* MpsParticleVelPos::updateVelocityParticlesWallDummy  src/MpsParticleVelPos.cpp:100-158 */
+/* 0-th step passes (src/main.cpp:157-180) */
+int pmps_initial_pnd(pmps_t* h);                 /* MpsPndNeigh::setInitialPndNumberOfNeighNPCD  src/MpsPndNeigh.cpp:21-101 */
+int pmps_mean_wall_pnd(pmps_t* h);               /* MpsPndNeigh::meanWallPnd                src/MpsPndNeigh.cpp:923-994 */
+int pmps_mean_pnd(pmps_t* h);                    /* MpsPndNeigh::meanPnd                    src/MpsPndNeigh.cpp:855-920 */
+int pmps_mean_neigh_fluid_pnd(pmps_t* h);        /* MpsPndNeigh::meanNeighFluidPnd          src/MpsPndNeigh.cpp:997-1049 */
+
+/* ---- fused fast path ---------------------------------------------------------------------------------------- */
+int pmps_init_step0(pmps_t* h);                  /* the whole 0-th step, src/main.cpp:121-180 (buckets, wall pass, initial PND, BC, pressure) */
+int pmps_step(pmps_t* h, int nsteps);            /* nsteps x the loop body of src/main.cpp:256-460, state stays on device */
+
+/* ---- debug / parity hooks (tests only) ---------------------------------------------------------------------- */
+/* bucket id of every host-order particle as the reference computes it at rebuild time, and the members of every
+ * bucket in list order (= ascending host index): flattened CSR. members may be NULL to query sizes. */
+int pmps_debug_buckets(pmps_t* h, int32_t* bucketOfParticle, int32_t* bucketStart /* nB+1 */, int32_t* members /* N */);
+/* neighbour set of host-order particle i under predicate kind: 0 = P(reL), 1 = P(reS), 2 = M(reS), 3 = M(reL),
+ * 4 = collision; returns count, fills out[0..cap) with host-order ids in traversal order. */
+int pmps_debug_neighbors(pmps_t* h, int i, int kind, int32_t* out, int cap);
+/* per-kernel device time of the last pmps_step (CUDA events on the step stream), name list is static */
+int pmps_profile_enable(pmps_t* h, int on);
+int pmps_profile_get(pmps_t* h, int* n, const char*** names, const float** ms_total, const int** launches);
+int pmps_launch_count(pmps_t* h, long long* launches); /* kernels launched by this handle so far */
+void* pmps_stream(pmps_t* h);                    /* cudaStream_t the stages run on */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PMPS_H_ */

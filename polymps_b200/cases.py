@@ -1,0 +1,195 @@
+"""Deterministic synthetic cases in the reference's own input formats (.json / .grid / .stl).
+
+The reference ships no .grid files (its input/grid/grid.zip is a stripped LFS blob), so every
+run — the reference's and ours — starts from a grid synthesized here: a cubic lattice at ((i+1/2) lo, ...)
+(README.md:65-74 of the reference for the format; parser src/MpsInputOutput.cpp:659-776).  The JSON written by
+`write_case` uses the reference's key names so that the unmodified reference binary reads it.
+
+Generators:
+  dam3d(...)           3D dam break, polygon (STL) tank, the InputDamWC / InputDamINC option sets  
+  dam2d_particle(...)  2D dam break with particle walls (1 wall layer id 2 + 2 dummy layers id 3), the
+                       dam1610_h300_lo0p0050_{WC,INC} option sets
+"""
+from __future__ import annotations
+
+import json
+import math
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from .mesh import box_triangles, write_binary_stl
+
+
+@dataclass
+class Case:
+    name: str
+    options: dict                      # JSON document (reference key names)
+    ptype: np.ndarray                  # (N,) int32 material id
+    pos: np.ndarray                    # (N,3)
+    vel: np.ndarray                    # (N,3)
+    press: np.ndarray                  # (N,)
+    tris: np.ndarray | None = None     # (nF,3,3) rigid mesh triangles (polygon walls)
+    meta: dict = field(default_factory=dict)
+
+    @property
+    def n(self) -> int:
+        return len(self.ptype)
+
+
+def base_options(*, dim, lo, dt, wall_type, mps_type, c0=15.0, re_small=2.1, re_large=2.1, grad_type=3,
+                 grad_corr=False, shifting=2, pnd_type=2, fs_type=1, fs_pnd=0.98, max_vel=4.0, gravity=(0.0, 0.0, -9.81),
+                 dom_min=(0.0, 0.0, 0.0), dom_max=(1.0, 1.0, 1.0), final_time=1.0, solver=0, alpha=1e-6, relax_pnd=0.01,
+                 collision=0, slip=0, rep_type=2, weight_type=0, fs_neigh=0.85) -> dict:
+    """A JSON document with the reference's key names (src/MpsInputOutput.cpp:134-505)."""
+    return {
+        "flags": {"wall_type": wall_type, "fem_MESH": False, "forced_MESH": False,
+                  "output_VTU": {"type": 0, "freeSurfWall": False, "pnd": True, "neigh": False, "deviation": False,
+                                 "concentration": False, "auxiliar": False, "non_newtonian": False},
+                  "output_TXT": {"press": False, "force": False}},
+        "pathNames": {"particle_grid_file": "input/grid/case.grid", "mesh_rigid_file": "input/stl/case.stl",
+                      "mesh_deformable_file": "input/stl/none.stl", "mesh_forced_file": "input/stl/none.stl",
+                      "vtu_output_folder": "output/case", "forceTxt_file": "output/force.txt",
+                      "pressTxt_file": "output/press.txt"},
+        "domain": {"min": dict(zip("xyz", map(float, dom_min))), "max": dict(zip("xyz", map(float, dom_max))),
+                   "boundary": {"type": 0, "limit": 0, "direction": {"x": False, "y": False, "z": False}}},
+        "physical": {"fluid_density": 1000.0, "wall_density": 1000.0, "kinematic_visc": 1e-6, "fluid_type": 0,
+                     "gravity": dict(zip("xyz", map(float, gravity))),
+                     "rheological": {"kinematic_visc_phase_2": 1e-6, "fluid_density_phase_1": 1000.0,
+                                     "fluid_density_phase_2": 1540.0, "sediment_density": 1540.0}},
+        "numerical": {
+            "dimension": dim, "particle_dist": lo, "time_step": dt, "final_time": final_time, "iter_output": 1000000,
+            "CFL_number": 0.2, "weight_type": weight_type, "slip_condition": slip,
+            "effective_radius": {"small": re_small, "large": re_large},
+            "gradient": {"type": grad_type, "correction": grad_corr, "relax_fact": 1.0},
+            "mps_type": mps_type,
+            "explicit_mps": {"equation_state": {"speed_sound": c0, "gamma": 7.0}},
+            "semi_implicit_mps": {"solver_type": solver, "weak_compressibility": {"alpha": alpha},
+                                  "source_term": {"relax_pnd": relax_pnd}},
+            "particle_shifting": {"type": shifting, "DRI": 0.01, "coef_A": 2.0, "mach_number": 0.1, "adj_vel_A": 0.9},
+            "pnd": {"type": pnd_type, "diffusive_coeff": 0.35},
+            "wall_repulsive_force": {"type": rep_type, "re": 0.5, "maxVel": max_vel,
+                                     "coefficient": {"Mitsume": 40000000.0, "Lennard-Jones": 2.0, "Monaghan-Kajtar": 1.0},
+                                     "eps_re": 0.01},
+            "free_surface_threshold": {"type": fs_type, "pnd": fs_pnd, "neigh": fs_neigh, "NPCD": 0.2, "ARC": 45.0,
+                                       "normal": 0.2},
+            "particle_collision": {"type": collision, "ratio": 0.2, "dist_limit_ratio": 0.85, "lambda": 0.2},
+            "particle_type": {"ghost": -1, "fluid": 0, "wall": 2, "dummyWall": 3},
+            "boundary_type": {"free_surface": 1, "inner": 0, "other": -1},
+        },
+    }
+
+
+def dam3d(nx: int, ny: int, nz: int, *, lo: float = 0.01, incompressible: bool = False, tank=None,
+          jitter: float = 0.0, seed: int = 20261104, name: str | None = None, dt: float | None = None,
+          offset=(0.0, 0.0, 0.0), **overrides) -> Case:
+    """3D dam break in an open-top polygon tank (InputDamWC / InputDamINC option sets).
+
+    Fluid column of nx*ny*nz particles on the lattice ((i+1/2)lo, (j+1/2)lo, (m+1/2)lo) (+offset, +optional jitter);
+    tank = (Lx, Ly, Lz), default the Lobovsky proportions scaled to the column: Lx = (1.61/0.6)*nx*lo,
+    Ly = ny*lo, Lz = 2*nz*lo.  c0 = 15*sqrt(H/0.3), dt = 0.375*lo/c0 (the acoustic Courant number of InputDamWC),
+    maxVel = 2*sqrt(g H) — the synthetic-block recipe of SURVEY.md §8d.
+    """
+    H = nz * lo
+    if tank is None:
+        tank = ((1.61 / 0.6) * nx * lo, ny * lo, 2.0 * nz * lo)
+    c0 = 15.0 * math.sqrt(H / 0.3)
+    if dt is None:
+        dt = 0.375 * lo / c0
+    i, j, m = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    # x fastest in memory order (like a grid file written x-inner): order by (m, j, i)
+    order = np.lexsort((i.ravel(), j.ravel(), m.ravel()))
+    pos = np.stack([(i.ravel()[order] + 0.5) * lo + offset[0], (j.ravel()[order] + 0.5) * lo + offset[1],
+                    (m.ravel()[order] + 0.5) * lo + offset[2]], axis=1)
+    if jitter > 0.0:
+        rng = np.random.default_rng(seed)
+        pos = pos + rng.uniform(-jitter * lo, jitter * lo, size=pos.shape)
+    n = len(pos)
+    kw = dict(dim=3, lo=lo, dt=dt, wall_type=1, c0=c0, max_vel=2.0 * math.sqrt(9.81 * H),
+              dom_min=(0.0, 0.0, 0.0), dom_max=(tank[0], tank[1], tank[2]))
+    if incompressible:   # InputDamINC: gradient 0 + correction, shifting off, pnd 0, CG
+        kw.update(mps_type=2, grad_type=0, grad_corr=True, shifting=0, pnd_type=0, dt=overrides.pop("dt_inc", dt * 2.0))
+    else:                # InputDamWC
+        kw.update(mps_type=1, grad_type=3, grad_corr=False, shifting=2, pnd_type=2)
+    kw.update(overrides)
+    opts = base_options(**kw)
+    return Case(name=name or ("dam3d_%s_%dx%dx%d" % ("inc" if incompressible else "wc", nx, ny, nz)), options=opts,
+                ptype=np.zeros(n, dtype=np.int32), pos=np.ascontiguousarray(pos), vel=np.zeros((n, 3)),
+                press=np.zeros(n),
+                tris=box_triangles(*tank).astype(np.float32).astype(np.float64),  # what a binary STL can hold
+                meta={"tank": tank, "H": H, "c0": c0})
+
+
+def dam3d_block(k: int, **kw) -> Case:
+    """The benchmark block of SURVEY.md §8d: fluid column 2k x k x k (k=171 -> 10.0M, 292 -> 49.8M, 464 -> 199.8M)."""
+    return dam3d(2 * k, k, k, **kw)
+
+
+def dam2d_particle(nx: int, nz: int, *, lo: float = 0.005, tank_nx: int | None = None, tank_nz: int | None = None,
+                   incompressible: bool = False, name: str | None = None, **overrides) -> Case:
+    """2D dam break with particle walls (dam1610_h300_lo0p0050_{WC,INC} option sets).
+    The reference's 2D cases live in the x-y plane with gravity along -y (input/dam1610_h300_lo0p0050_WC.json)."""
+    tank_nx = tank_nx or int(round(nx * 1.61 / 0.6))
+    tank_nz = tank_nz or 2 * nz
+    P, T = [], []
+    for jy in range(-3, tank_nz):
+        for ix in range(-3, tank_nx + 3):
+            inside = 0 <= ix < tank_nx and jy >= 0
+            if inside:
+                if ix < nx and jy < nz:
+                    P.append(((ix + 0.5) * lo, (jy + 0.5) * lo, 0.0)); T.append(0)
+                continue
+            layer = max(-ix, ix - tank_nx + 1, -jy)   # 1 = wall layer, 2..3 = dummy layers
+            P.append(((ix + 0.5) * lo, (jy + 0.5) * lo, 0.0)); T.append(2 if layer == 1 else 3)
+    pos = np.array(P); ptype = np.array(T, dtype=np.int32)
+    H = nz * lo
+    c0 = 15.0 * math.sqrt(H / 0.3)
+    dt = 0.375 * lo / c0
+    kw = dict(dim=2, lo=lo, dt=dt, wall_type=0, c0=c0, re_small=2.1, re_large=3.1, gravity=(0.0, -9.81, 0.0),
+              grad_type=0, grad_corr=True, fs_type=0, fs_pnd=0.97, max_vel=2.0 * math.sqrt(9.81 * H),
+              dom_min=(-4 * lo, -4 * lo, 0.0), dom_max=((tank_nx + 4) * lo, (tank_nz + 1) * lo, 0.0))
+    if incompressible:
+        kw.update(mps_type=2, shifting=0, pnd_type=0, dt=dt * 2.0)
+    else:
+        kw.update(mps_type=1, shifting=2, pnd_type=2)
+    kw.update(overrides)
+    n = len(pos)
+    return Case(name=name or ("dam2d_%s_%dx%d" % ("inc" if incompressible else "wc", nx, nz)), options=base_options(**kw),
+                ptype=ptype, pos=pos, vel=np.zeros((n, 3)), press=np.zeros(n), tris=None, meta={"H": H, "c0": c0})
+
+
+# ---------------------------------------------------------------------------------------------- files
+def write_grid(path: str, ptype, pos, vel, press) -> None:
+    """.grid: '0', N, then 'id x y z vx vy vz p pav' rows (reference README.md:65-74).  %.17g round-trips doubles."""
+    with open(path, "w") as fh:
+        fh.write("0\n%d\n" % len(ptype))
+        for t, p, v, pr in zip(ptype, pos, vel, press):
+            fh.write("%d %.17g %.17g %.17g %.17g %.17g %.17g %.17g 0\n" % (t, p[0], p[1], p[2], v[0], v[1], v[2], pr))
+
+
+def read_grid(path: str):
+    with open(path) as fh:
+        toks = fh.read().split()
+    n = int(toks[1])
+    a = np.array(toks[2:2 + 9 * n], dtype=np.float64).reshape(n, 9)
+    return a[:, 0].astype(np.int32), a[:, 1:4].copy(), a[:, 4:7].copy(), a[:, 7].copy()
+
+
+def write_case(case: Case, root: str) -> str:
+    """Lay the case out under `root` the way the reference expects it (cwd/input/<name>.json, hard-coded prefix
+    src/MpsInputOutput.cpp:63,99).  Returns the JSON path."""
+    os.makedirs(os.path.join(root, "input", "grid"), exist_ok=True)
+    os.makedirs(os.path.join(root, "input", "stl"), exist_ok=True)
+    os.makedirs(os.path.join(root, "output"), exist_ok=True)
+    opts = json.loads(json.dumps(case.options))
+    opts["pathNames"]["particle_grid_file"] = "input/grid/%s.grid" % case.name
+    opts["pathNames"]["mesh_rigid_file"] = "input/stl/%s.stl" % case.name
+    opts["pathNames"]["vtu_output_folder"] = "output/%s" % case.name
+    write_grid(os.path.join(root, opts["pathNames"]["particle_grid_file"]), case.ptype, case.pos, case.vel, case.press)
+    if case.tris is not None:
+        write_binary_stl(os.path.join(root, opts["pathNames"]["mesh_rigid_file"]), case.tris)
+    jp = os.path.join(root, "input", case.name + ".json")
+    with open(jp, "w") as fh:
+        json.dump(opts, fh, indent=1)
+    return jp
