@@ -169,6 +169,7 @@ int pmps_profile_enable(pmps_t* h, int on);
 int pmps_profile_get(pmps_t* h, int* n, const char*** names, const float** ms_total, const int** launches);
 int pmps_launch_count(pmps_t* h, long long* launches); /* kernels launched by this handle so far */
 void* pmps_stream(pmps_t* h);                    /* cudaStream_t the stages run on */
+int pmps_synchronize(pmps_t* h);                 /* wait for everything queued on the handle's stream */
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,299 @@
+// pmps_api.cu — the C ABI of include/pmps.h: handle lifetime, host<->device transfers, the elementwise stages and
+// the stage/step drivers.  Neighbour stages are instantiations of the list walker (pmps_device.cuh) over the stage
+// bodies (pmps_bodies.cuh).  There is no CPU fallback anywhere: without a CUDA device pmps_create fails.
+#include "pmps_bodies.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+
+thread_local std::string g_create_error;
+
+int pmps_fail(pmps_handle* h, int code, const char* fmt, ...) {
+	char buf[1024]; va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+	if (h) h->err = buf; else g_create_error = buf;
+	return code;
+}
+
+ProfScope::ProfScope(pmps_handle* h_, const char* name) : h(h_), idx(-1) {
+	if (!h->profile) return;
+	for (size_t k = 0; k < h->profNames.size(); k++) if (h->profNames[k] == name) { idx = (int)k; break; }
+	if (idx < 0) { idx = (int)h->profNames.size(); h->profNames.push_back(name); h->profMs.push_back(0.f); h->profLaunches.push_back(0); }
+	cudaEventRecord(h->evA, h->stream);
+}
+ProfScope::~ProfScope() {
+	if (idx < 0) return;
+	cudaEventRecord(h->evB, h->stream); cudaEventSynchronize(h->evB);
+	float ms = 0.f; cudaEventElapsedTime(&ms, h->evA, h->evB);
+	h->profMs[idx] += ms; h->profLaunches[idx] += 1;
+}
+
+// ================================================================================================ elementwise stages
+// MpsParticle::addGravity, src/MpsParticle.cpp:111-130
+__global__ void k_add_gravity(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	if (pk_type(S.pos[i]) == K.p.ghost) return;
+	const double ax = S.acc.x[i] + K.p.gravityX, ay = S.acc.y[i] + K.p.gravityY, az = S.acc.z[i] + K.p.gravityZ;
+	S.acc.x[i] = ax; S.acc.y[i] = ay; S.acc.z[i] = az;
+	S.accStar.x[i] = ax; S.accStar.y[i] = ay; S.accStar.z[i] = az;
+}
+
+__device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, int i, const double4& p) {
+	const float4 b = S.bpos[i];
+	const float dx = (float)(p.x - K.p.domainMinX) - b.x, dy = (float)(p.y - K.p.domainMinY) - b.y, dz = (float)(p.z - K.p.domainMinZ) - b.z;
+	atomic_max_f(S.maxDisp2, dx * dx + dy * dy + dz * dz);
+}
+
+// MpsParticleVelPos::predictionVelocityPosition, src/MpsParticleVelPos.cpp:20-50
+__global__ void k_predict(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	double4 p = S.pos[i];
+	if (pk_type(p) == K.p.ghost) return;
+	const double dt = K.p.timeStep;
+	if (pk_type(p) == K.p.fluid) {
+		double4 v = S.vel[i];
+		v.x += S.acc.x[i] * dt; v.y += S.acc.y[i] * dt; v.z += S.acc.z[i] * dt;
+		p.x += v.x * dt; p.y += v.y * dt; p.z += v.z * dt;
+		S.vel[i] = v; S.pos[i] = p;
+		track_disp(S, K, i, p);
+	}
+	S.acc.x[i] = 0.0; S.acc.y[i] = 0.0; S.acc.z[i] = 0.0;
+	S.dvelCollision.x[i] = 0.0; S.dvelCollision.y[i] = 0.0; S.dvelCollision.z[i] = 0.0;
+	S.npcdDeviation.x[i] = 0.0; S.npcdDeviation.y[i] = 0.0; S.npcdDeviation.z[i] = 0.0;
+	S.numNeighWallContribution[i] = 0; S.particleNearWall[i] = 0; S.distParticleWall2[i] = K.big;
+	if (K.poly) { S.mirrorParticlePos.x[i] = K.big; S.mirrorParticlePos.y[i] = K.big; S.mirrorParticlePos.z[i] = K.big; }
+}
+
+// second loop of checkParticleCollisions (src/MpsParticleCollision.cpp:108-116): vel += dvel for fluid particles
+__global__ void k_apply_collision(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	if (pk_type(S.pos[i]) != K.p.fluid) return;
+	double4 v = S.vel[i];
+	v.x += S.dvelCollision.x[i]; v.y += S.dvelCollision.y[i]; v.z += S.dvelCollision.z[i];
+	S.vel[i] = v;
+}
+
+// MpsParticleVelPos::correctionVelocityPosition, src/MpsParticleVelPos.cpp:53-97 (velMax: max over fluid of |v|)
+__global__ void k_correct(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	double v2 = 0.0;
+	if (i < S.n) {
+		double4 p = S.pos[i];
+		if (pk_type(p) == K.p.fluid) {
+			const double dt = K.p.timeStep; const double ax = S.acc.x[i], ay = S.acc.y[i], az = S.acc.z[i];
+			double4 v = S.vel[i];
+			v.x += ax * dt; v.y += ay * dt; v.z += az * dt;
+			p.x += ax * dt * dt; p.y += ay * dt * dt; p.z += az * dt * dt;
+			S.vel[i] = v; S.pos[i] = p;
+			S.acc.x[i] = 0.0; S.acc.y[i] = 0.0; S.acc.z[i] = 0.0;
+			v2 = v.x * v.x + v.y * v.y + v.z * v.z;
+			track_disp(S, K, i, p);
+		}
+	}
+	// warp max, then one atomic per warp on the bits (non-negative doubles order like unsigned integers)
+	unsigned long long b = (unsigned long long)__double_as_longlong(v2);
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, b, o); b = t > b ? t : b; }
+	if ((threadIdx.x & 31) == 0 && b > S.velMax2Bits[0]) atomicMax(S.velMax2Bits, b);
+}
+__global__ void k_velmax_begin(const __grid_constant__ DevView S) { S.velMax2Bits[0] = 0ull; }
+__global__ void k_velmax_end(const __grid_constant__ DevView S) { S.velMax2Bits[1] = S.velMax2Bits[0]; }
+
+// MpsPndNeigh::updatePnd, src/MpsPndNeigh.cpp:747-774
+__global__ void k_update_pnd(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	if (pk_type(S.pos[i]) == K.p.ghost) return;
+	S.pndi[i] = S.pndAuxVar1[i]; S.pndAuxVar1[i] = 0.0;
+}
+
+// second loops of meanPndParticlesWallDummySurface (src/MpsPndNeigh.cpp:836-850) and meanPnd (:905-918)
+template <int SEL> __global__ void k_mean_pnd_finish(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const int t = pk_type(S.pos[i]);
+	if (t == K.p.ghost) return;
+	const double a1 = S.pndAuxVar1[i], a2 = S.pndAuxVar2[i];
+	if (SEL == 0) { if (t == K.p.wall || S.particleBC[i] == K.p.surface) S.pndi[i] = a2 < K.p.epsilonZero ? a1 : a1 / a2; }
+	else S.pndi[i] = S.numNeigh[i] < 1 ? a1 : a1 / a2;
+	S.pndAuxVar1[i] = 0.0; S.pndAuxVar2[i] = 0.0;
+}
+__global__ void k_zero_aux(const __grid_constant__ DevView S) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	S.pndAuxVar1[i] = 0.0; S.pndAuxVar2[i] = 0.0;
+}
+
+// MpsBoundaryCondition::updateParticleBC (PND_NEIGH, PND_NPCD), src/MpsBoundaryCondition.cpp:66-203
+__device__ __forceinline__ int classify_bc(const DevView& S, const KParams& K, int i, int type) {
+	if (type == K.p.dummyWall) return K.p.other;
+	const double ps = S.pndSmall[i]; const int nn = S.numNeigh[i];
+	int bc = ps < K.p.betaPnd ? K.p.surface : K.p.inner;
+	if (K.p.freeSurfType == 0) bc = (ps < K.p.betaPnd && nn < K.p.betaNeigh) ? K.p.surface : K.p.inner;
+	else if (K.p.freeSurfType == 1) { if (bc == K.p.surface && nn > 4 && S.npcdDeviation2[i] < K.p.delta2) bc = K.p.inner; }
+	return bc;
+}
+__global__ void k_update_bc(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const int t = pk_type(S.pos[i]);
+	if (t == K.p.ghost) return;
+	S.particleBC[i] = classify_bc(S, K, i, t);
+}
+
+// MpsPressure::calcPressEMPS / calcPressWCMPS, src/MpsPressure.cpp:62-163
+__global__ void k_press_eos(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const double4 pi = S.pos[i];
+	if (pk_type(pi) == K.p.ghost) return;
+	const double mi = pk_ptype(pi) == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2; double p = 0.0;
+	if (S.particleBC[i] == K.p.inner) {
+		if (K.p.mpsType == 0) p = (S.pndi[i] - K.p.pndSmallZero) * K.p.coeffPressEMPS * mi;
+		else p = (mi * K.p.coeffPressWCMPS / K.p.gamma) * (pow(S.pndi[i] / K.p.pndSmallZero, K.p.gamma) - 1);
+	}
+	if (p < 0.0) p = 0.0;
+	S.press[i] = p;
+}
+
+// ================================================================================================ handle lifetime
+template <class T> static int dalloc(pmps_handle* h, T** p, size_t count) {
+	void* q = nullptr;
+	cudaError_t e = cudaMalloc(&q, sizeof(T) * (count ? count : 1));
+	if (e != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "cudaMalloc(%zu bytes) failed: %s", sizeof(T) * count, cudaGetErrorString(e));
+	cudaMemsetAsync(q, 0, sizeof(T) * (count ? count : 1), h->stream);
+	h->allocs.push_back(q); *p = (T*)q; return PMPS_OK;
+}
+
+static int alloc_view(pmps_handle* h, DevView& V, int n0, bool primary) {
+	int rc = 0;
+	rc |= dalloc(h, &V.pos, n0); rc |= dalloc(h, &V.vel, n0); rc |= dalloc(h, &V.hostIdx, n0); rc |= dalloc(h, &V.particleNearWall, n0);
+#define X(n) rc |= dalloc(h, &V.n, n0);
+	PMPS_I32_FIELDS(X)
+	PMPS_F64_FIELDS(X)
+#undef X
+#define X(n) rc |= dalloc(h, &V.n.x, n0); rc |= dalloc(h, &V.n.y, n0); rc |= dalloc(h, &V.n.z, n0);
+	PMPS_V3_FIELDS(X)
+#undef X
+	(void)primary;
+	return rc ? PMPS_E_CUDA : PMPS_OK;
+}
+
+__global__ void k_iota(int32_t* a, int32_t* b, int n) { const int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) { a[i] = i; b[i] = i; } }
+
+extern "C" int pmps_abi_version(void) { return PMPS_ABI_VERSION; }
+
+extern "C" const char* pmps_last_error(const pmps_t* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+// numParticlesZero is taken from the first pmps_upload; pmps_create only validates and binds the device.
+extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
+	if (!params || !out) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: NULL argument");
+	*out = nullptr;
+	if (params->abi_version != PMPS_ABI_VERSION) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: ABI version %d, library is %d", params->abi_version, PMPS_ABI_VERSION);
+	if (params->dim != 2 && params->dim != 3) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: dim must be 2 or 3");
+	if (params->fluidType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: non-Newtonian fluids are not on the device path yet (SURVEY 8f row 1)");
+	if (params->domainTypeBC != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: periodic domain boundaries are not on the device path yet (SURVEY 8f row 4)");
+	if (params->freeSurfType == 2) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: ARC free-surface detection is not on the device path yet (SURVEY 8f row 4)");
+	if (params->collisionType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: DPC collisions are not on the device path yet (SURVEY 8f row 4)");
+	if (params->shiftingType == 1) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: shifting type 1 is not on the device path yet (SURVEY 8f row 4)");
+	if (params->mpsType == 3) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: IMPLICIT_PND_DIVU is not on the device path yet (SURVEY 8f row 4)");
+	if (params->relaxPress < 1.0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: prediction pressure gradient (relax_fact < 1) is not on the device path yet");
+	if (params->numBucketsX < 1 || params->numBucketsY < 1 || params->numBucketsZ < 1 || !(params->bucketSide > 0.0)) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: bucket geometry not set");
+	const long long nB = (long long)params->numBucketsX * params->numBucketsY * params->numBucketsZ;
+	if (nB > 2000000000ll) return pmps_fail(nullptr, PMPS_E_OVERFLOW, "pmps_create: %lld buckets overflow int32", nB);
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { cudaGetLastError(); return pmps_fail(nullptr, PMPS_E_CUDA, "pmps_create: no CUDA device (this library has no CPU path)"); }
+	if (device < 0 || device >= ndev) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: device %d of %d", device, ndev);
+	if (cudaSetDevice(device) != cudaSuccess) return pmps_fail(nullptr, PMPS_E_CUDA, "pmps_create: cudaSetDevice failed");
+	pmps_handle* h = new pmps_handle();
+	h->device = device;
+	if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return pmps_fail(nullptr, PMPS_E_CUDA, "pmps_create: cudaStreamCreate failed"); }
+	cudaEventCreate(&h->evA); cudaEventCreate(&h->evB);
+	KParams& K = h->K; memset(&K, 0, sizeof K);
+	K.p = *params;
+	K.big = 10e8 * params->partDist;
+	K.vol = pow(params->partDist, (double)params->dim);
+	K.velMax = params->velMax;
+	K.poly = params->wallType == 1;
+	memset(&h->V, 0, sizeof(DevView)); memset(&h->A, 0, sizeof(DevView));
+	h->V.nB = (int)nB;
+	*out = h;
+	return PMPS_OK;
+}
+
+static int ensure_capacity(pmps_handle* h, int n0) {
+	if (h->numParticlesZero == n0) return PMPS_OK;
+	if (h->numParticlesZero != 0) return pmps_fail(h, PMPS_E_ARG, "numParticlesZero changed from %d to %d; create a new handle", h->numParticlesZero, n0);
+	if (n0 < 1) return pmps_fail(h, PMPS_E_ARG, "numParticlesZero must be positive");
+	cudaSetDevice(h->device);
+	DevView& S = h->V; KParams& K = h->K; const PmpsParams& P = K.p;
+	int rc = 0;
+	rc |= alloc_view(h, S, n0, true); rc |= alloc_view(h, h->A, n0, false);
+	rc |= dalloc(h, &S.scratch1, n0); rc |= dalloc(h, &S.bpos, n0); rc |= dalloc(h, &S.slotOfHost, n0); rc |= dalloc(h, &S.cellOf, n0);
+	rc |= dalloc(h, &S.cellStart, (size_t)S.nB + 2); rc |= dalloc(h, &h->cellCount, (size_t)S.nB + 2);
+	rc |= dalloc(h, &h->perm, n0); rc |= dalloc(h, &h->arbRank, n0); rc |= dalloc(h, &h->newCell, n0);
+	rc |= dalloc(h, &h->tmpHost, 2 * (size_t)n0);
+	h->nScanBlocks = cdiv((long long)S.nB + 2, 512 * 8) + 1;
+	rc |= dalloc(h, &h->scanBlock, h->nScanBlocks);
+	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 1); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
+	// Verlet list: radius = bucketSide (the reference's own search slack, src/MpsBucket.cpp:23); capacity from the
+	// lattice count with head room (PMPS_LIST_CAP overrides)
+	const double rl = P.bucketSide, lo = P.partDist;
+	const double lat = P.dim == 3 ? 4.18879 * pow(rl / lo, 3.0) : 3.14159 * pow(rl / lo, 2.0);
+	int cap = (int)(lat * 1.6) + 8;
+	if (const char* e = getenv("PMPS_LIST_CAP")) cap = atoi(e);
+	cap = (cap + 3) & ~3; if (cap < 8) cap = 8; if (cap > 4096) cap = 4096;
+	S.listCap = cap;
+	const size_t nWarps = ((size_t)n0 + 31) / 32;
+	rc |= dalloc(h, &S.list, nWarps * 32 * (size_t)cap); rc |= dalloc(h, &S.listCnt, nWarps * 32);
+	h->stageBytes = 64 * (size_t)n0;
+	{ void* q = nullptr; if (cudaMalloc(&q, h->stageBytes) != cudaSuccess) rc |= 1; else { h->allocs.push_back(q); h->stage = q; } }
+	if (cudaMallocHost((void**)&h->h_flags, sizeof(int32_t) * NFLAGS) != cudaSuccess) rc |= 1;
+	if (rc) return pmps_fail(h, PMPS_E_CUDA, "device allocation for %d particles failed: %s", n0, cudaGetErrorString(cudaGetLastError()));
+	S.n = n0; S.n0 = n0; S.pos2 = h->A.pos; S.vel2 = h->A.vel;
+	h->A.n = n0; h->A.n0 = n0;
+	// float margin of the list test: positions are stored relative to domainMin in float
+	const double ext = fmax(fmax(P.domainMaxX - P.domainMinX, P.domainMaxY - P.domainMinY), P.domainMaxZ - P.domainMinZ);
+	const double maxRe = fmax(P.reL, P.reS);
+	const double rlf = rl * (1.0 + 1e-6) + 8.0 * 1.2e-7 * ext;
+	K.rl2 = (float)(rlf * rlf);
+	const double guard = 0.5 * (rl - maxRe) - 8.0 * 1.2e-7 * ext;
+	K.guard2 = (float)(guard > 0 ? guard * guard : 0.0);
+	k_iota<<<cdiv(n0, 256), 256, 0, h->stream>>>(S.hostIdx, S.slotOfHost, n0);
+	{ unsigned long long vb[2]; double v2 = K.velMax * K.velMax; memcpy(&vb[0], &v2, 8); vb[1] = vb[0];
+	  cudaMemcpyAsync(S.velMax2Bits, vb, 16, cudaMemcpyHostToDevice, h->stream); cudaStreamSynchronize(h->stream); }
+	h->numParticlesZero = n0;
+	cudaError_t e = cudaGetLastError();
+	if (e != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "initialisation failed: %s", cudaGetErrorString(e));
+	return PMPS_OK;
+}
+int pmps_ensure_capacity(pmps_handle* h, int n0) { return ensure_capacity(h, n0); }
+
+extern "C" int pmps_destroy(pmps_t* h) {
+	if (!h) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	cudaStreamSynchronize(h->stream);
+	for (auto& r : h->registered) cudaHostUnregister(r.first);
+	for (void* p : h->allocs) cudaFree(p);
+	for (DevMesh& m : h->meshes) { cudaFree(m.V); cudaFree(m.F); cudaFree(m.N); cudaFree(m.bbMin); cudaFree(m.bbMax); cudaFree(m.prim);
+		cudaFree(m.xDataPND); cudaFree(m.xDataNeigh); cudaFree(m.Zij); cudaFree(m.nNeighWall); }
+	if (h->d_meshes) cudaFree(h->d_meshes);
+	if (h->h_flags) cudaFreeHost(h->h_flags);
+	cudaEventDestroy(h->evA); cudaEventDestroy(h->evB);
+	cudaStreamDestroy(h->stream);
+	delete h;
+	return PMPS_OK;
+}
+
+extern "C" int pmps_set_mesh(pmps_t* h, int mesh_id, int nV, const double* V, int nF, const int32_t* F, const double* faceNormals,
+                             int nTable, const double* xDataPND, const double* xDataNeigh, const double* Zij, const int32_t* nNeighWall) {
+	if (!h || !V || !F || !faceNormals || !xDataPND || !xDataNeigh || !Zij || !nNeighWall) return h ? pmps_fail(h, PMPS_E_ARG, "pmps_set_mesh: NULL argument") : PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	cudaStreamSynchronize(h->stream);
+	return pmps_mesh_upload(h, mesh_id, nV, V, nF, F, faceNormals, nTable, xDataPND, xDataNeigh, Zij, nNeighWall);
+}
+
+#include "pmps_stages.inc"

@@ -1,0 +1,74 @@
+// pmps_domain.cu — MpsParticle::checkParticleOutDomain (reference src/MpsParticle.cpp:234-402, non-periodic branch).
+//
+// The reference removes a fluid particle that left [domainMin+bucketSide, domainMax-bucketSide] by copying the LAST
+// live particle over it and turning the last slot into a ghost; the loop is serial and order dependent.  On the
+// device a flag kernel collects the (normally zero) offenders; a one-thread kernel then replays the reference's
+// serial loop over just those host indices in ascending order, re-testing each against the CURRENT content of its
+// slot exactly as the reference's loop does.  No host round trip: the fix kernel returns at once when the count is 0.
+#include "pmps_device.cuh"
+
+__device__ __forceinline__ bool out_of_domain(const KParams& K, const double4& p) {
+	const PmpsParams& P = K.p;
+	const double lx = P.domainMinX + P.bucketSide, ly = P.domainMinY + P.bucketSide, lz = P.domainMinZ + P.bucketSide;
+	const double hx = P.domainMaxX - P.bucketSide, hy = P.domainMaxY - P.bucketSide, hz = P.domainMaxZ - P.bucketSide;
+	return p.x > hx || p.x < lx || p.y > hy || p.y < ly || (P.dim == 3 && (p.z > hz || p.z < lz));
+}
+
+__global__ void k_ood_flag(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const double4 p = S.pos[i];
+	if (pk_type(p) != K.p.fluid || !out_of_domain(K, p)) return;
+	const int k = atomicAdd(&S.flags[FLAG_OOD_COUNT], 1);
+	if (k < PMPS_OOD_CAP) S.oodList[k] = S.hostIdx[i];
+}
+
+__global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	int cnt = S.flags[FLAG_OOD_COUNT];
+	if (cnt == 0) return;
+	S.flags[FLAG_OOD_COUNT] = 0;
+	if (cnt > PMPS_OOD_CAP) { atomicOr(&S.flags[FLAG_GUARD], 4); cnt = PMPS_OOD_CAP; }
+	int32_t* L = S.oodList;
+	for (int a = 1; a < cnt; a++) { const int v = L[a]; int b = a; while (b > 0 && L[b - 1] > v) { L[b] = L[b - 1]; b--; } L[b] = v; }
+	int live = S.flags[FLAG_LIVE];
+	for (int e = 0; e < cnt; e++) {
+		const int hi = L[e];
+		if (!(hi < live)) continue;
+		const int si = S.slotOfHost[hi];
+		const double4 pcur = S.pos[si];
+		if (pk_type(pcur) != K.p.fluid || !out_of_domain(K, pcur)) continue;
+		const int hl = live - 1; const int sl = S.slotOfHost[hl];
+		// slot si <- content of slot sl (host index hi keeps its slot), then slot sl becomes a ghost
+		S.pos[si] = S.pos[sl]; S.vel[si] = S.vel[sl]; S.particleNearWall[si] = S.particleNearWall[sl];
+#define X(n) S.n[si] = S.n[sl];
+		PMPS_I32_FIELDS(X)
+		PMPS_F64_FIELDS(X)
+#undef X
+#define X(n) S.n.x[si] = S.n.x[sl]; S.n.y[si] = S.n.y[sl]; S.n.z[si] = S.n.z[sl];
+		PMPS_V3_FIELDS(X)
+#undef X
+		// the moved particle keeps searching around ITS position: give slot si the candidate list of slot sl
+		S.bpos[si] = S.bpos[sl]; S.listCnt[si] = S.listCnt[sl];
+		{
+			uint32_t* Li = S.list + (size_t)(si >> 5) * 32 * (size_t)S.listCap + (si & 31);
+			const uint32_t* Ll = S.list + (size_t)(sl >> 5) * 32 * (size_t)S.listCap + (sl & 31);
+			for (int k = 0; k < S.listCnt[sl]; k++) Li[(size_t)k * 32] = Ll[(size_t)k * 32];
+		}
+		double4 g; g.x = K.p.domainMaxX - K.p.partDist; g.y = K.p.domainMaxY - K.p.partDist;
+		g.z = K.p.dim == 2 ? 0.0 : K.p.domainMaxZ - K.p.partDist; g.w = pk_make(K.p.ghost, pk_ptype(S.pos[sl]));
+		S.pos[sl] = g; double4 vz = S.vel[sl]; vz.x = vz.y = vz.z = 0.0; S.vel[sl] = vz;
+		S.particleBC[sl] = K.p.other; S.particleNearWall[sl] = 0; S.nearMeshType[sl] = 0; S.distParticleWall2[sl] = K.big;
+		S.press[sl] = 0.0;
+		live--; S.flags[FLAG_OOD_TOTAL] += 1;
+	}
+	S.flags[FLAG_LIVE] = live;
+}
+
+extern "C" int pmps_check_out_domain(pmps_t* h) {
+	if (!h) return PMPS_E_ARG;
+	if (!h->haveList) return pmps_fail(h, PMPS_E_STATE, "pmps_check_out_domain: call pmps_update_buckets first");
+	LAUNCH(h, "domain.flag", k_ood_flag, cdiv(h->V.n, 256), 256, h->V, h->K);
+	LAUNCH(h, "domain.fix", k_ood_fix, 1, 1, h->V, h->K);
+	CUDA_TRY(h, cudaGetLastError());
+	return PMPS_OK;
+}

@@ -1,0 +1,132 @@
+// pmps_internal.h — device-side data model of libpmps.so (the B200-native PolyMPS particle hot path).
+//
+// Layout: all per-particle state lives in HBM in SLOT order = particles sorted by the reference's
+// bucket id (src/MpsBucket.cpp:299-353), ascending host index inside a bucket (= the reference's list order).
+//   pos, vel      : 32-byte records {x,y,z,w}; pos.w carries the bits of {particleType, PTYPE}; one sector per gather
+//   every other field : one 8-byte (or 4/1-byte) plane per component, coalesced own-index access
+//   list          : Verlet candidate list built once per step (warp-interleaved, 32-bit slot ids)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/pmps.h"
+
+// ---- field tables (names = reference MpsParticle members, include/MpsParticle.h:139-241) ----------------------
+#define PMPS_I32_FIELDS(X) X(particleBC) X(numNeigh) X(nearMeshType) X(numNeighWallContribution) X(elementID)
+#define PMPS_F64_FIELDS(X) X(press) X(pndi) X(pndki) X(pndski) X(pndSmall) X(npcdDeviation2) X(concentration) \
+	X(velDivergence) X(diffusiveTerm) X(pndWallContribution) X(distParticleWall2) X(deviationDotPolygonNormal) \
+	X(RHO) X(MEU) X(pndAuxVar1) X(pndAuxVar2) X(pressurePPE) X(sourceTerm)
+#define PMPS_V3_FIELDS(X) X(acc) X(accStar) X(npcdDeviation) X(gradConcentration) X(correcMatrixRow1) \
+	X(correcMatrixRow2) X(correcMatrixRow3) X(particleAtWallPos) X(mirrorParticlePos) X(polygonNormal) X(forceWall) \
+	X(dvelCollision)
+
+struct V3 { double* x; double* y; double* z; };
+
+// Pointers to the CURRENT buffers, passed by value to every kernel.
+struct DevView {
+	double4* pos; double4* vel;          // current
+	double4* pos2; double4* vel2;        // alternate (ping-pong target of integrators / permute)
+	float4* bpos;                        // position at list-build time, float, relative to domainMin (guard + build)
+	int32_t* hostIdx;                    // slot -> host (reference) index
+	int32_t* slotOfHost;                 // host index -> slot
+	int32_t* cellOf;                     // slot -> bucket id at the last rebuild
+	int32_t* cellStart;                  // nB+1, slots of bucket b are [cellStart[b], cellStart[b+1])
+	uint32_t* list; uint16_t* listCnt;   // Verlet candidates (slot ids), warp-interleaved, listCap per particle
+	uint8_t* particleNearWall;
+	double* scratch1;                    // per-slot scratch (Pmin of the gradient passes); not a reference field
+#define X(n) int32_t* n;
+	PMPS_I32_FIELDS(X)
+#undef X
+#define X(n) double* n;
+	PMPS_F64_FIELDS(X)
+#undef X
+#define X(n) V3 n;
+	PMPS_V3_FIELDS(X)
+#undef X
+	int32_t n;                           // slots in use (= live particles at the last rebuild incl. later ghosts)
+	int32_t n0;                          // capacity (numParticlesZero)
+	int32_t listCap;
+	int32_t nB;
+	// device scalars
+	unsigned long long* velMax2Bits;     // max |v|^2 of fluid particles (bits of a non-negative double)
+	float* maxDisp2;                     // max squared displacement since the list build (float, >= 0)
+	int32_t* flags;                      // [0] list overflow, [1] out-of-domain count, [2] guard violated, [3] live count
+	int32_t* oodList;                    // host ids flagged by the out-of-domain test
+};
+
+enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, NFLAGS = 8 };
+#define PMPS_OOD_CAP 65536
+
+// Kernel-side parameters: the ABI params plus derived constants
+struct KParams {
+	PmpsParams p;
+	double big;          // 10e8*partDist, the reference's "infinity" (src/MpsParticleVelPos.cpp:37)
+	double vol;          // partDist^dim
+	double velMax;       // velMax of the previous correction (src/MpsPressure.cpp:1585)
+	float rl2;           // (list radius)^2 incl. float margin
+	float guard2;        // (allowed displacement)^2
+	int32_t poly;        // wallType == polygon
+};
+
+#define MAX_TRI_CONST 64
+struct DevMesh {       // one polygon mesh on the device + libigl-order AABB hierarchy in heap order
+	int nV, nF, nNodes, nTable;
+	double* V; int32_t* F; double* N; double* bbMin; double* bbMax; int32_t* prim;
+	double* xDataPND; double* xDataNeigh; double* Zij; int32_t* nNeighWall;
+};
+
+struct pmps_handle {
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	KParams K;
+	DevView V;
+	std::vector<void*> allocs;           // everything cudaMalloc'd
+	std::vector<DevMesh> meshes; DevMesh* d_meshes = nullptr;
+	// alternate buffers for the permute (same shapes as V's planes)
+	DevView A;
+	int32_t* perm = nullptr;             // new slot -> old slot
+	int32_t* cellCount = nullptr;        // nB+1 (histogram / running scatter offsets)
+	int32_t* arbRank = nullptr; int32_t* tmpHost = nullptr; int32_t* newCell = nullptr;
+	int32_t* scanBlock = nullptr; int nScanBlocks = 0;
+	void* stage = nullptr; size_t stageBytes = 0;    // device staging for upload/download (host order)
+	void* pinned = nullptr; size_t pinnedBytes = 0;
+	int32_t* h_flags = nullptr;          // pinned mirror of V.flags
+	int numParticles = 0, numParticlesZero = 0;
+	bool haveState = false, haveList = false;
+	int solverIter = 0; double solverError = 0.0, velMax = 0.0;
+	long long launches = 0;
+	int oodTotal = 0, maxCell = 0;
+	std::string err;
+	std::vector<std::pair<void*, size_t>> registered;   // host ranges pinned with cudaHostRegister
+	// PPE workspace
+	double *ppe_val = nullptr, *ppe_diag = nullptr, *ppe_r = nullptr, *ppe_p = nullptr, *ppe_z = nullptr, *ppe_t = nullptr, *ppe_dots = nullptr;
+	double *ppe_q = nullptr, *ppe_s = nullptr, *ppe_y = nullptr, *ppe_r0 = nullptr;
+	uint8_t* ppe_mask = nullptr;
+	// profiling
+	bool profile = false;
+	std::vector<std::string> profNames; std::vector<float> profMs; std::vector<int> profLaunches;
+	std::vector<const char*> profNamePtrs;
+	cudaEvent_t evA = nullptr, evB = nullptr;
+};
+
+extern thread_local std::string g_create_error;
+int pmps_fail(pmps_handle* h, int code, const char* fmt, ...);
+#define CUDA_TRY(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return pmps_fail((h), PMPS_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+static inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
+
+// Launch helper: counts launches and (optionally) accumulates per-kernel CUDA-event time on the step stream.
+struct ProfScope {
+	pmps_handle* h; int idx;
+	ProfScope(pmps_handle* h_, const char* name);
+	~ProfScope();
+};
+#define LAUNCH(h, name, kernel, grid, block, ...) do { ProfScope ps_((h), name); kernel<<<(grid), (block), 0, (h)->stream>>>(__VA_ARGS__); (h)->launches++; } while (0)
+
+// implemented in the .cu files
+int pmps_ensure_capacity(pmps_handle* h, int n0);
+int pmps_sort_and_list(pmps_handle* h);
+int pmps_ppe_solve(pmps_handle* h);
+int pmps_mesh_upload(pmps_handle* h, int mesh_id, int nV, const double* V, int nF, const int32_t* F, const double* N,
+                     int nTable, const double* xP, const double* xN, const double* Z, const int32_t* nW);

@@ -1,0 +1,218 @@
+// pmps_sort.cu — G0: bucket ordering + Verlet candidate list (replaces MpsBucket::updateParticlesID,
+// reference src/MpsBucket.cpp:299-353).
+//
+// The reference threads particles onto per-bucket linked lists serially.  Here the particles themselves are put in
+// bucket order by a counting sort (one atomic per particle into the bucket histogram, a device-wide exclusive scan
+// = the cell-start table, a scatter, and an in-bucket rank fix that makes the order canonical: ascending host index
+// inside a bucket, i.e. exactly the reference's list order).  All per-particle state is then gathered into the new
+// order so every later kernel reads its neighbours from nearby addresses.  Finally ONE pass over the 27 (9 in 2D)
+// surrounding buckets builds a candidate list with radius bucketSide = reL(1+CFL) in float; the ~10 neighbour passes
+// of the step walk that list (≈67 candidates) instead of re-walking 27 buckets (≈430 candidates) each.
+#include "pmps_device.cuh"
+#include <cstdio>
+
+// ---- 1. bucket id + histogram --------------------------------------------------------------------------------
+__global__ void k_cell_hist(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int32_t* newCell, int32_t* arbRank, int32_t* cellCount) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n0) return;
+	const double4 p = S.pos[i];
+	int cell = S.nB;   // ghosts are parked behind the last bucket (the reference skips them, src/MpsBucket.cpp:332)
+	if (pk_type(p) != K.p.ghost) {
+		const PmpsParams& P = K.p;
+		int ix, iy, iz = 0;
+		if (P.dim == 2) {   // 2D insertion adds epsilonZero, 3D insertion does not (src/MpsBucket.cpp:312-313 vs :333-335)
+			ix = bucket_coord(p.x, P.domainMinX, P.invBucketSide, P.epsilonZero);
+			iy = bucket_coord(p.y, P.domainMinY, P.invBucketSide, P.epsilonZero);
+		} else {
+			ix = (int)__dmul_rn(__dsub_rn(p.x, P.domainMinX), P.invBucketSide);
+			iy = (int)__dmul_rn(__dsub_rn(p.y, P.domainMinY), P.invBucketSide);
+			iz = (int)__dmul_rn(__dsub_rn(p.z, P.domainMinZ), P.invBucketSide);
+		}
+		if (ix < 0 || ix >= P.numBucketsX || iy < 0 || iy >= P.numBucketsY || iz < 0 || iz >= P.numBucketsZ) {
+			atomicOr(&S.flags[FLAG_GUARD], 2);   // a live particle outside the bucket grid: the reference would corrupt memory here
+			ix = min(max(ix, 0), P.numBucketsX - 1); iy = min(max(iy, 0), P.numBucketsY - 1); iz = min(max(iz, 0), P.numBucketsZ - 1);
+		}
+		cell = iz * (P.numBucketsX * P.numBucketsY) + iy * P.numBucketsX + ix;
+	}
+	newCell[i] = cell;
+	arbRank[i] = atomicAdd(&cellCount[cell], 1);
+}
+
+// ---- 2. exclusive scan of the histogram (3 kernels: per-block scan, scan of block sums, add) ------------------
+#define SCAN_T 512
+#define SCAN_ITEMS 8
+__global__ void __launch_bounds__(SCAN_T) k_scan_block(const int32_t* in, int32_t* out, int32_t* blockSum, int n, int32_t* maxOut) {
+	__shared__ int32_t warpSum[SCAN_T / 32];
+	const int base = (blockIdx.x * SCAN_T + threadIdx.x) * SCAN_ITEMS;
+	int v[SCAN_ITEMS]; int s = 0, mx = 0;
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) { const int idx = base + k; v[k] = idx < n ? in[idx] : 0; if (idx < n - 2) mx = max(mx, v[k]); s += v[k]; }
+	int incl = s;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if ((threadIdx.x & 31) >= o) incl += t; }
+	if ((threadIdx.x & 31) == 31) warpSum[threadIdx.x >> 5] = incl;
+	__syncthreads();
+	if (threadIdx.x < 32) {
+		int w = threadIdx.x < SCAN_T / 32 ? warpSum[threadIdx.x] : 0; int wi = w;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, wi, o); if (threadIdx.x >= o) wi += t; }
+		if (threadIdx.x < SCAN_T / 32) warpSum[threadIdx.x] = wi - w;
+		if (threadIdx.x == SCAN_T / 32 - 1) blockSum[blockIdx.x] = wi;
+	}
+	__syncthreads();
+	int run = incl - s + warpSum[threadIdx.x >> 5];
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) { const int idx = base + k; if (idx < n) out[idx] = run; run += v[k]; }
+	mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 16)); mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+	mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 4)); mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2)); mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+	if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(maxOut, mx);
+}
+__global__ void __launch_bounds__(1024) k_scan_sums(int32_t* blockSum, int nBlocks) {   // one block, serial over chunks of 1024
+	__shared__ int32_t sh[1024]; __shared__ int32_t carry;
+	if (threadIdx.x == 0) carry = 0;
+	__syncthreads();
+	for (int base = 0; base < nBlocks; base += 1024) {
+		const int idx = base + threadIdx.x; const int v = idx < nBlocks ? blockSum[idx] : 0;
+		sh[threadIdx.x] = v; __syncthreads();
+		for (int o = 1; o < 1024; o <<= 1) { int t = threadIdx.x >= o ? sh[threadIdx.x - o] : 0; __syncthreads(); sh[threadIdx.x] += t; __syncthreads(); }
+		if (idx < nBlocks) blockSum[idx] = sh[threadIdx.x] - v + carry;
+		__syncthreads();
+		if (threadIdx.x == 1023) carry += sh[1023];
+		__syncthreads();
+	}
+}
+__global__ void __launch_bounds__(SCAN_T) k_scan_add(int32_t* out, const int32_t* blockSum, int n) {
+	const int base = (blockIdx.x * SCAN_T + threadIdx.x) * SCAN_ITEMS; const int add = blockSum[blockIdx.x];
+	#pragma unroll
+	for (int k = 0; k < SCAN_ITEMS; k++) { const int idx = base + k; if (idx < n) out[idx] += add; }
+}
+
+// ---- 3. scatter into bucket ranges (arbitrary order inside a bucket), 4. canonical rank inside the bucket -----
+__global__ void k_scatter(const __grid_constant__ DevView S, const int32_t* newCell, const int32_t* arbRank, const int32_t* cellStart, int2* tmp) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n0) return;
+	tmp[cellStart[newCell[i]] + arbRank[i]] = make_int2(S.hostIdx[i], i);
+}
+__global__ void k_rank_fix(const __grid_constant__ DevView S, const int32_t* newCell, const int32_t* cellStart, const int2* tmp, int32_t* perm) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= S.n0) return;
+	const int2 me = tmp[t];
+	const int c = newCell[me.y]; const int s0 = cellStart[c], s1 = cellStart[c + 1];
+	int rank = 0;
+	for (int u = s0; u < s1; u++) rank += tmp[u].x < me.x;
+	perm[s0 + rank] = me.y;
+}
+
+// ---- 5. gather every plane into the new order --------------------------------------------------------------------
+#define PERM_MAX 16
+struct PermJob8 { const double* src[PERM_MAX]; double* dst[PERM_MAX]; int n; };
+__global__ void k_permute8(const int32_t* __restrict__ perm, const __grid_constant__ PermJob8 J, int n0) {
+	const int s = blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= n0) return;
+	const int o = perm[s];
+	#pragma unroll 4
+	for (int k = 0; k < J.n; k++) J.dst[k][s] = J.src[k][o];
+}
+struct PermJob4 { const int32_t* src[PERM_MAX]; int32_t* dst[PERM_MAX]; int n; };
+__global__ void k_permute4(const int32_t* __restrict__ perm, const __grid_constant__ PermJob4 J, int n0) {
+	const int s = blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= n0) return;
+	const int o = perm[s];
+	for (int k = 0; k < J.n; k++) J.dst[k][s] = J.src[k][o];
+}
+// packs + bookkeeping: pos, vel, nearWall flag, cellOf, slotOfHost, float build position
+__global__ void k_permute_packs(const int32_t* __restrict__ perm, const __grid_constant__ DevView S, const __grid_constant__ DevView A,
+                                const __grid_constant__ KParams K, const int32_t* newCell) {
+	const int s = blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= S.n0) return;
+	const int o = perm[s];
+	const double4 p = S.pos[o];
+	A.pos[s] = p; A.vel[s] = S.vel[o];
+	A.particleNearWall[s] = S.particleNearWall[o];
+	const int h = S.hostIdx[o];
+	A.hostIdx[s] = h; S.slotOfHost[h] = s;
+	S.cellOf[s] = newCell[o];   // cellOf / bpos are not double-buffered: written at the new slot, read via perm only above
+	S.bpos[s] = make_float4((float)(p.x - K.p.domainMinX), (float)(p.y - K.p.domainMinY), (float)(p.z - K.p.domainMinZ), 0.f);
+}
+
+// ---- 6. Verlet candidate list -----------------------------------------------------------------------------------
+// One thread per slot; candidates are emitted bucket row by bucket row (jz, jy outer; the three x-adjacent buckets of
+// a row are one contiguous slot range), slots ascending = the reference's traversal order restricted to the list.
+__global__ void __launch_bounds__(128) k_build_list(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n0) return;
+	const int c = S.cellOf[i];
+	if (c >= S.nB) { S.listCnt[i] = 0; return; }   // ghost
+	const int nX = K.p.numBucketsX, nY = K.p.numBucketsY, nZ = K.p.numBucketsZ, nXY = nX * nY;
+	const int cz = c / nXY, cy = (c - cz * nXY) / nX, cx = c - cz * nXY - cy * nX;
+	const float4 bi = S.bpos[i];
+	uint32_t* L = S.list + (size_t)(i >> 5) * 32 * (size_t)S.listCap + (i & 31);
+	int cnt = 0; const int cap = S.listCap;
+	const int z0 = K.p.dim == 3 ? max(cz - 1, 0) : 0, z1 = K.p.dim == 3 ? min(cz + 1, nZ - 1) : 0;
+	const int y0 = max(cy - 1, 0), y1 = min(cy + 1, nY - 1), x0 = max(cx - 1, 0), x1 = min(cx + 1, nX - 1);
+	for (int jz = z0; jz <= z1; jz++) for (int jy = y0; jy <= y1; jy++) {
+		const int row = jz * nXY + jy * nX;
+		const int s0 = S.cellStart[row + x0], s1 = S.cellStart[row + x1 + 1];
+		for (int j = s0; j < s1; j++) {
+			const float4 bj = S.bpos[j];
+			const float dx = bj.x - bi.x, dy = bj.y - bi.y, dz = bj.z - bi.z;
+			const float d2 = dx * dx + dy * dy + dz * dz;
+			if (d2 < K.rl2 && j != i) { if (cnt < cap) L[(size_t)cnt * 32] = (uint32_t)j; cnt++; }
+		}
+	}
+	if (cnt > cap) { atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = cap; }
+	S.listCnt[i] = (uint16_t)cnt;
+}
+
+__global__ void k_reset_step_scalars(const __grid_constant__ DevView S) {
+	*S.maxDisp2 = 0.f; S.flags[FLAG_MAXCELL] = 0;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+template <class T> static inline void swp(T& a, T& b) { T t = a; a = b; b = t; }
+
+int pmps_sort_and_list(pmps_handle* h) {
+	DevView& S = h->V; DevView& A = h->A; const KParams& K = h->K;
+	const int n0 = S.n0, nB = S.nB, T = 256;
+	CUDA_TRY(h, cudaMemsetAsync(h->cellCount, 0, sizeof(int32_t) * (size_t)(nB + 2), h->stream));
+	LAUNCH(h, "sort.reset", k_reset_step_scalars, 1, 1, S);
+	LAUNCH(h, "sort.cell_hist", k_cell_hist, cdiv(n0, T), T, S, K, h->newCell, h->arbRank, h->cellCount);
+	const int nScan = nB + 2; const int per = SCAN_T * SCAN_ITEMS; const int nblk = cdiv(nScan, per);
+	LAUNCH(h, "sort.scan_block", k_scan_block, nblk, SCAN_T, h->cellCount, S.cellStart, h->scanBlock, nScan, &S.flags[FLAG_MAXCELL]);
+	LAUNCH(h, "sort.scan_sums", k_scan_sums, 1, 1024, h->scanBlock, nblk);
+	LAUNCH(h, "sort.scan_add", k_scan_add, nblk, SCAN_T, S.cellStart, h->scanBlock, nScan);
+	int2* tmp = (int2*)h->tmpHost;
+	LAUNCH(h, "sort.scatter", k_scatter, cdiv(n0, T), T, S, h->newCell, h->arbRank, S.cellStart, tmp);
+	LAUNCH(h, "sort.rank_fix", k_rank_fix, cdiv(n0, T), T, S, h->newCell, S.cellStart, tmp, h->perm);
+	// gather: packs first (needs the old hostIdx), then the planes in groups
+	LAUNCH(h, "sort.permute_packs", k_permute_packs, cdiv(n0, T), T, h->perm, S, A, K, h->newCell);
+	swp(S.pos, A.pos); swp(S.vel, A.vel); swp(S.particleNearWall, A.particleNearWall); swp(S.hostIdx, A.hostIdx);
+	S.pos2 = A.pos; S.vel2 = A.vel;
+	{
+		std::vector<std::pair<double**, double**>> planes;
+#define X(n) planes.push_back({ &S.n, &A.n });
+		PMPS_F64_FIELDS(X)
+#undef X
+#define X(n) planes.push_back({ &S.n.x, &A.n.x }); planes.push_back({ &S.n.y, &A.n.y }); planes.push_back({ &S.n.z, &A.n.z });
+		PMPS_V3_FIELDS(X)
+#undef X
+		for (size_t b = 0; b < planes.size(); b += PERM_MAX) {
+			PermJob8 J; J.n = (int)std::min<size_t>(PERM_MAX, planes.size() - b);
+			for (int k = 0; k < J.n; k++) { J.src[k] = *planes[b + k].first; J.dst[k] = *planes[b + k].second; }
+			LAUNCH(h, "sort.permute8", k_permute8, cdiv(n0, T), T, h->perm, J, n0);
+			for (int k = 0; k < J.n; k++) swp(*planes[b + k].first, *planes[b + k].second);
+		}
+		PermJob4 J4; J4.n = 0;
+#define X(f) J4.src[J4.n] = S.f; J4.dst[J4.n] = A.f; J4.n++;
+		PMPS_I32_FIELDS(X)
+#undef X
+		LAUNCH(h, "sort.permute4", k_permute4, cdiv(n0, T), T, h->perm, J4, n0);
+#define X(n) swp(S.n, A.n);
+		PMPS_I32_FIELDS(X)
+#undef X
+	}
+	LAUNCH(h, "list.build", k_build_list, cdiv(n0, 128), 128, S, K);
+	CUDA_TRY(h, cudaGetLastError());
+	h->haveList = true;
+	return PMPS_OK;
+}

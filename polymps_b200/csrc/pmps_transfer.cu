@@ -1,0 +1,144 @@
+// pmps_transfer.cu — pmps_upload / pmps_download / pmps_upload_device: the reference's host layout
+// (include/MpsParticle.h:139-241: scalars a[i], vectors a[3*i+k], int32 ids, 1-byte bool) <-> the device layout
+// (slot order, 32-byte pos/vel records, one plane per component).  Host arrays are pinned in place on first use
+// (cudaHostRegister) so the copies run at PCIe rate without an extra host-side staging copy.
+#include "pmps_device.cuh"
+#include <cstring>
+
+__global__ void k_up_f64(const double* __restrict__ src, double* dst, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	dst[slotOfHost[hI]] = src[hI];
+}
+__global__ void k_up_i32(const int32_t* __restrict__ src, int32_t* dst, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	dst[slotOfHost[hI]] = src[hI];
+}
+__global__ void k_up_u8(const uint8_t* __restrict__ src, uint8_t* dst, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	dst[slotOfHost[hI]] = src[hI];
+}
+__global__ void k_up_v3(const double* __restrict__ src, V3 dst, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	const int s = slotOfHost[hI];
+	dst.x[s] = src[3 * (size_t)hI]; dst.y[s] = src[3 * (size_t)hI + 1]; dst.z[s] = src[3 * (size_t)hI + 2];
+}
+// pos/vel records: xyz from an interleaved array, pos.w from particleType / PTYPE (any of the sources may be NULL)
+__global__ void k_up_pack(const double* __restrict__ xyz, const int32_t* __restrict__ type, const int32_t* __restrict__ ptype,
+                          double4* dst, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	const int s = slotOfHost[hI];
+	double4 r = dst[s];
+	if (xyz) { r.x = xyz[3 * (size_t)hI]; r.y = xyz[3 * (size_t)hI + 1]; r.z = xyz[3 * (size_t)hI + 2]; }
+	if (type || ptype) r.w = pk_make(type ? type[hI] : pk_type(r), ptype ? ptype[hI] : pk_ptype(r));
+	dst[s] = r;
+}
+
+__global__ void k_dn_f64(double* dst, const double* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	dst[hI] = src[slotOfHost[hI]];
+}
+__global__ void k_dn_i32(int32_t* dst, const int32_t* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	dst[hI] = src[slotOfHost[hI]];
+}
+__global__ void k_dn_u8(uint8_t* dst, const uint8_t* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	dst[hI] = src[slotOfHost[hI]];
+}
+__global__ void k_dn_v3(double* dst, V3 src, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	const int s = slotOfHost[hI];
+	dst[3 * (size_t)hI] = src.x[s]; dst[3 * (size_t)hI + 1] = src.y[s]; dst[3 * (size_t)hI + 2] = src.z[s];
+}
+__global__ void k_dn_pack(double* xyz, int32_t* type, int32_t* ptype, const double4* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	const double4 r = src[slotOfHost[hI]];
+	if (xyz) { xyz[3 * (size_t)hI] = r.x; xyz[3 * (size_t)hI + 1] = r.y; xyz[3 * (size_t)hI + 2] = r.z; }
+	if (type) type[hI] = pk_type(r);
+	if (ptype) ptype[hI] = pk_ptype(r);
+}
+__global__ void k_set_live(const __grid_constant__ DevView S, int live) { S.flags[FLAG_LIVE] = live; }
+
+static void pin_host(pmps_handle* h, const void* p, size_t bytes) {
+	if (!p || bytes < (1u << 16)) return;
+	for (auto& r : h->registered) if (r.first == p && r.second >= bytes) return;
+	if (cudaHostRegister(const_cast<void*>(p), bytes, cudaHostRegisterDefault) == cudaSuccess) h->registered.push_back({ const_cast<void*>(p), bytes });
+	else cudaGetLastError();   // not fatal (already pinned by the caller, or not registrable): the copy still works
+}
+
+static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) {
+	if (!h || !a) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	{ const int rc = pmps_ensure_capacity(h, a->numParticlesZero); if (rc) return rc; }   // first upload fixes the capacity
+	if (a->numParticles < 0 || a->numParticles > a->numParticlesZero) return pmps_fail(h, PMPS_E_ARG, "pmps_upload: bad numParticles");
+	const int n0 = h->numParticlesZero, T = 256, G = cdiv(n0, T);
+	DevView& S = h->V; char* st = (char*)h->stage; const int32_t* soh = S.slotOfHost;
+	// stage one host array (or pass a device pointer through)
+	auto src = [&](const void* p, size_t bytes, size_t off) -> const void* {
+		if (!p) return nullptr;
+		if (deviceSrc) return p;
+		pin_host(h, p, bytes);
+		cudaMemcpyAsync(st + off, p, bytes, cudaMemcpyHostToDevice, h->stream);
+		return st + off;
+	};
+	if (a->pos || a->particleType || a->PTYPE) {
+		const double* x = (const double*)src(a->pos, 24 * (size_t)n0, 0);
+		const int32_t* t = (const int32_t*)src(a->particleType, 4 * (size_t)n0, 24 * (size_t)n0);
+		const int32_t* pt = (const int32_t*)src(a->PTYPE, 4 * (size_t)n0, 28 * (size_t)n0);
+		LAUNCH(h, "upload", k_up_pack, G, T, x, t, pt, S.pos, soh, n0);
+	}
+	if (a->vel) { const double* x = (const double*)src(a->vel, 24 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_pack, G, T, x, (const int32_t*)nullptr, (const int32_t*)nullptr, S.vel, soh, n0); }
+	if (a->particleNearWall) { const uint8_t* x = (const uint8_t*)src(a->particleNearWall, (size_t)n0, 0); LAUNCH(h, "upload", k_up_u8, G, T, x, S.particleNearWall, soh, n0); }
+#define X(n) if (a->n) { const int32_t* x = (const int32_t*)src(a->n, 4 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_i32, G, T, x, S.n, soh, n0); }
+	PMPS_I32_FIELDS(X)
+#undef X
+#define X(n) if (a->n) { const double* x = (const double*)src(a->n, 8 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_f64, G, T, x, S.n, soh, n0); }
+	PMPS_F64_FIELDS(X)
+#undef X
+#define X(n) if (a->n) { const double* x = (const double*)src(a->n, 24 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_v3, G, T, x, S.n, soh, n0); }
+	PMPS_V3_FIELDS(X)
+#undef X
+	LAUNCH(h, "upload", k_set_live, 1, 1, S, a->numParticles);
+	CUDA_TRY(h, cudaGetLastError());
+	h->numParticles = a->numParticles; h->haveState = true;
+	return PMPS_OK;
+}
+
+extern "C" int pmps_upload(pmps_t* h, const PmpsHostArrays* a) { return upload_impl(h, a, false); }
+extern "C" int pmps_upload_device(pmps_t* h, const PmpsHostArrays* a) { return upload_impl(h, a, true); }
+
+extern "C" int pmps_download(pmps_t* h, PmpsHostArrays* a) {
+	if (!h || !a) return PMPS_E_ARG;
+	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_download: nothing uploaded");
+	if (a->numParticlesZero != h->numParticlesZero) return pmps_fail(h, PMPS_E_ARG, "pmps_download: numParticlesZero mismatch");
+	const int n0 = h->numParticlesZero, T = 256, G = cdiv(n0, T);
+	DevView& S = h->V; const int32_t* soh = S.slotOfHost;
+	// two staging halves so the gather of field k+1 can be queued behind the copy-out of field k
+	char* half[2] = { (char*)h->stage, (char*)h->stage + 32 * (size_t)n0 }; int hb = 0;
+	auto out = [&](void* dstHost, const void* stg, size_t bytes) { pin_host(h, dstHost, bytes); cudaMemcpyAsync(dstHost, stg, bytes, cudaMemcpyDeviceToHost, h->stream); };
+	if (a->pos || a->particleType || a->PTYPE) {
+		char* b = half[hb]; hb ^= 1;
+		double* x = a->pos ? (double*)b : nullptr; int32_t* t = a->particleType ? (int32_t*)(b + 24 * (size_t)n0) : nullptr;
+		int32_t* pt = a->PTYPE ? (int32_t*)(b + 28 * (size_t)n0) : nullptr;
+		LAUNCH(h, "download", k_dn_pack, G, T, x, t, pt, S.pos, soh, n0);
+		if (x) out(a->pos, x, 24 * (size_t)n0);
+		if (t) out(a->particleType, t, 4 * (size_t)n0);
+		if (pt) out(a->PTYPE, pt, 4 * (size_t)n0);
+	}
+	if (a->vel) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_pack, G, T, (double*)b, (int32_t*)nullptr, (int32_t*)nullptr, S.vel, soh, n0); out(a->vel, b, 24 * (size_t)n0); }
+	if (a->particleNearWall) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_u8, G, T, (uint8_t*)b, S.particleNearWall, soh, n0); out(a->particleNearWall, b, (size_t)n0); }
+#define X(n) if (a->n) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_i32, G, T, (int32_t*)b, S.n, soh, n0); out(a->n, b, 4 * (size_t)n0); }
+	PMPS_I32_FIELDS(X)
+#undef X
+#define X(n) if (a->n) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_f64, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 8 * (size_t)n0); }
+	PMPS_F64_FIELDS(X)
+#undef X
+#define X(n) if (a->n) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_v3, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 24 * (size_t)n0); }
+	PMPS_V3_FIELDS(X)
+#undef X
+	CUDA_TRY(h, cudaMemcpyAsync(h->h_flags, S.flags, sizeof(int32_t) * NFLAGS, cudaMemcpyDeviceToHost, h->stream));
+	CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+	h->numParticles = h->h_flags[FLAG_LIVE];
+	a->numParticles = h->numParticles;
+	return PMPS_OK;
+}

@@ -66,7 +66,7 @@ class HostState:
 
     @classmethod
     def from_dump(cls, d: dict) -> "HostState":
-        """From a ref_driver dump (oracle/refrun.load_dump)."""
+        """From a raw array dump of the reference (dict name -> array, see tests/golden/make_golden.py)."""
         n = int(d["numParticles"][1])
         s = cls(n)
         s.numParticles = int(d["numParticles"][0])

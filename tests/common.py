@@ -1,0 +1,102 @@
+"""Shared helpers of the test-suite: golden fixtures, case construction, field comparison."""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(HERE, "golden")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+from polymps_b200.params import ParticleSystem  # noqa: E402
+from polymps_b200.mesh import PolygonMesh  # noqa: E402
+from polymps_b200.state import HostState, ALL_FIELDS, I32, U8  # noqa: E402
+from make_golden import load_golden  # noqa: E402
+
+GOLDEN = ["w3", "w3j", "i3", "w2", "i2"]
+
+# ref_driver stage name -> stage calls (oracle method names == engine method names)
+STAGE_MAP = {
+    "updateParticlesID": ["update_buckets"], "calcViscosity": ["calc_viscosity"], "addGravity": ["add_gravity"],
+    "predictionVelocityPosition": ["predict"], "checkParticleOutDomain1": ["check_out_domain"], "collisions": ["collisions"],
+    "wallClosestPoint": ["wall_closest_point"], "calcWallNPCD": ["wall_npcd"], "correctionMatrix1": ["correction_matrix"],
+    "calcPndnNeighNPCD": ["pnd_neigh_npcd"], "calcPndDiffusiveTerm": ["pnd_diffusive"], "calcWallPndDiffusiveTerm": ["wall_pnd_diffusive"],
+    "updatePnd": ["update_pnd"], "meanPndParticlesWallDummySurface": ["mean_pnd_wall_dummy_surface"], "updateParticleBC": ["update_bc"],
+    "calcPress": ["calc_press"], "extrapolatePress": ["extrapolate_press"], "correctionMatrix2": ["correction_matrix"],
+    "calcPressGradient": ["press_gradient"], "calcWallPressGradient": ["wall_press_gradient"], "calcWallViscosity": ["wall_viscosity"],
+    "correctionVelocityPosition": ["correct"], "checkParticleOutDomain2": ["check_out_domain"],
+    "calcConcAndConcGradient": ["shifting"], "calcWallConcAndConcGradient": ["wall_shifting"],
+    "updateVelocityParticlesWallDummy": ["update_wall_dummy_vel"], "checkParticleOutDomain3": ["check_out_domain"],
+}
+SHIFTING_STAGES = {"calcConcAndConcGradient", "calcWallConcAndConcGradient"}
+# fields the reference dumps do not carry, or that are scratch in one of the implementations
+SKIP_FIELDS = {"dvelCollision"}
+
+
+def golden(name):
+    """-> (order, dumps, meta, ps, meshes) for a committed fixture."""
+    order, dumps, meta = load_golden(os.path.join(HERE, "golden", name + ".npz"))
+    ps = ParticleSystem.from_json(meta["options"]).set_parameters()
+    ps.allocate_buckets(np.asarray(meta["case"]["pos"]).reshape(-1, 3))
+    meshes = []
+    if ps.wallType == 1:
+        meshes = [PolygonMesh.from_triangles(meta["case"]["tris"]).init_wall_tables(int(ps.dim), ps.weightType, ps.partDist, ps.reL, ps.reS)]
+    return order, dumps, meta, ps, meshes
+
+
+def stage_sequence(order, step):
+    """[(stage name, previous dump name, this dump name)] of one dumped step, in execution order."""
+    pre = "s%04d_pre" % step
+    names = [o for o in order if o.startswith("s%04d_" % step) and o[6:8].isdigit()]
+    out = []; prev = pre
+    for n in names:
+        out.append((n[9:], prev, n)); prev = n
+    return out
+
+
+def dumped_steps(order):
+    return sorted({int(o[1:5]) for o in order if o.startswith("s") and o.endswith("_pre")})
+
+
+def state_from(d) -> HostState:
+    return HostState.from_dump(d)
+
+
+def compare_states(got: HostState, want, rtol=0.0, fields=None, skip=(), live_only=True, sign_fields_tol=1e-12):
+    """List of (field, n_bad, max_abs_err, max_rel_err) for every field that differs by more than rtol * max|want|.
+    rtol=0 means bit-identical.  `want` is a HostState or a dump dict."""
+    bad = []
+    n = got.numParticles
+    for f in (fields or ALL_FIELDS):
+        if f in SKIP_FIELDS or f in skip:
+            continue
+        y = want.get(f) if isinstance(want, dict) else getattr(want, f)
+        if y is None:
+            continue
+        x = getattr(got, f)
+        k = x.size // got.numParticlesZero
+        if live_only:
+            x = x[:n * k]; y = np.asarray(y)[:n * k]
+        if np.array_equal(x, y):
+            continue
+        if f in I32 or f in U8:
+            bad.append((f, int(np.count_nonzero(x != y)), float(np.abs(x.astype(np.int64) - y.astype(np.int64)).max()), float("inf")))
+            continue
+        with np.errstate(invalid="ignore"):
+            err = np.abs(x - y)
+        if not np.all(np.isfinite(x) == np.isfinite(y)):
+            bad.append((f, -1, float("nan"), float("nan"))); continue
+        scale = max(float(np.abs(y[np.isfinite(y)]).max()) if y.size else 0.0, 1e-300)
+        e = float(np.nanmax(err)) if err.size else 0.0
+        if e <= rtol * scale:
+            continue
+        bad.append((f, int(np.count_nonzero(err > rtol * scale)), e, e / scale))
+    return bad
+
+
+def neighbor_sets_equal(a, b):
+    return sorted(int(v) for v in a) == sorted(int(v) for v in b)

@@ -1,0 +1,108 @@
+"""Generates the committed golden fixtures by running the UNMODIFIED reference (oracle/_ref/ref_driver, built by
+`make -C oracle ref` from /root/reference) on small synthesized cases, single-threaded, and packing its raw stage-by-stage
+dumps into one compressed .npz per case.  Run in the build container only (needs /root/reference):
+
+    python tests/golden/make_golden.py
+
+Each npz holds  "<dump file stem>/<array name>"  entries (dump files: pre_init, init, s0001_pre, s0001_NN_<stage>, ...),
+plus "case/*" (the synthesized input: ptype, pos, vel, press, tris) and "case/options_json".
+"""
+from __future__ import annotations
+
+import glob
+import json
+import os
+import shutil
+import sys
+import tempfile
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "oracle"))
+from polymps_b200 import cases  # noqa: E402
+import refrun  # noqa: E402
+
+
+def golden_cases():
+    """name -> (Case, steps to dump).  Small on purpose: the whole set must stay around a megabyte."""
+    return {
+        # 3D weakly-compressible, polygon tank (InputDamWC option set); exact lattice => equidistant-wall ties
+        "w3": (cases.dam3d(7, 5, 6, name="w3"), (1, 2)),
+        # same with jittered positions and a few steps of evolution
+        "w3j": (cases.dam3d(6, 5, 6, jitter=0.08, name="w3j"), (3,)),
+        # 3D incompressible (InputDamINC option set): gradient type 0 + correction matrix, PPE + CG
+        "i3": (cases.dam3d(6, 5, 5, incompressible=True, jitter=0.05, name="i3"), (1, 2)),
+        # 2D particle walls (dam1610_h300_lo0p0050_{WC,INC} option sets)
+        "w2": (cases.dam2d_particle(8, 10, tank_nx=18, tank_nz=16, name="w2"), (1, 3)),
+        "i2": (cases.dam2d_particle(8, 10, tank_nx=18, tank_nz=16, incompressible=True, name="i2"), (1, 2)),
+    }
+
+
+def chrono_key(stem):
+    if stem == "mesh":
+        return (-3, 0)
+    if stem == "pre_init":
+        return (-2, 0)
+    if stem == "init":
+        return (-1, 0)
+    if stem == "final":
+        return (10 ** 9, 0)
+    step = int(stem[1:5]); rest = stem[6:]
+    return (step, -1 if rest == "pre" else 10 ** 6 if rest == "end" else int(rest[:2]))
+
+
+def load_golden(path):
+    """-> (ordered list of dump names, {name: full dict of arrays}) with the delta encoding undone."""
+    z = np.load(path)
+    order = bytes(z["order"]).decode().split("\n")
+    by = {}
+    for k in z.files:
+        if "/" in k:
+            stem, arr = k.split("/", 1)
+            by.setdefault(stem, {})[arr] = z[k]
+    dumps = {}; cur = {}
+    for stem in order:
+        cur = dict(cur); cur.update(by.get(stem, {}))
+        dumps[stem] = cur
+    meta = {"params": json.loads(bytes(z["params_json"]).decode()), "options": json.loads(bytes(z["case/options_json"]).decode()),
+            "case": by.get("case", {})}
+    return order, dumps, meta
+
+
+def main():
+    if not refrun.have_ref():
+        sys.exit("oracle/_ref/ref_driver missing: run `make -C oracle ref` (needs /root/reference)")
+    for name, (case, steps) in golden_cases().items():
+        root = tempfile.mkdtemp(prefix="golden_")
+        try:
+            cases.write_case(case, root)
+            dump = os.path.join(root, "dump")
+            refrun.run_reference(root, case.name, max(steps), dump, dump_steps=steps, threads=1)
+            out = {}
+            stems = [os.path.splitext(os.path.basename(fn))[0] for fn in glob.glob(os.path.join(dump, "*.bin"))]
+            stems.sort(key=chrono_key)
+            prev = {}
+            for stem in stems:   # delta encoding: an array is stored only where it differs from the previous dump
+                for k, v in refrun.load_dump(os.path.join(dump, stem + ".bin")).items():
+                    if k in prev and prev[k].shape == v.shape and np.array_equal(prev[k], v, equal_nan=True):
+                        continue
+                    out["%s/%s" % (stem, k)] = v
+                    prev[k] = v
+            out["order"] = np.frombuffer("\n".join(stems).encode(), dtype=np.uint8)
+            with open(os.path.join(dump, "params.json")) as fh:
+                out["params_json"] = np.frombuffer(fh.read().encode(), dtype=np.uint8)
+            out["case/ptype"] = case.ptype; out["case/pos"] = case.pos; out["case/vel"] = case.vel; out["case/press"] = case.press
+            if case.tris is not None:
+                out["case/tris"] = case.tris
+            out["case/options_json"] = np.frombuffer(json.dumps(case.options).encode(), dtype=np.uint8)
+            path = os.path.join(HERE, name + ".npz")
+            np.savez_compressed(path, **out)
+            print("%-4s N=%d  %d arrays  %.0f kB" % (name, case.n, len(out), os.path.getsize(path) / 1e3))
+        finally:
+            shutil.rmtree(root, ignore_errors=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,185 @@
+"""GPU parity tests (run with -m gpu on the B200 box).  Everything goes through the C ABI (libpmps.so via
+polymps_b200.engine); the checker is (a) the committed golden dumps of the unmodified reference and (b) the CPU oracle
+on seeded inputs.  Tolerances: integer / index / flag fields and neighbour SETS bit-exact; floating-point fields
+1e-10 relative to the field's max magnitude (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+from common import (GOLDEN, STAGE_MAP, SHIFTING_STAGES, golden, stage_sequence, dumped_steps, state_from, compare_states,
+                    neighbor_sets_equal)
+from polymps_b200 import cases
+from polymps_b200.params import ParticleSystem
+from polymps_b200.mesh import PolygonMesh
+from polymps_b200.state import HostState
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-10
+# sign of a dot product that is pure rounding noise for symmetric neighbourhoods: compared separately
+NOISY = ("deviationDotPolygonNormal",)
+
+
+def _engine(ps, meshes, n0):
+    from polymps_b200.engine import Engine
+    e = Engine(ps, meshes, device=0, shifting_jacobi=True)
+    e.remember_capacity(n0)
+    return e
+
+
+def _oracle(ps, st, meshes, prev=None, jacobi=True):
+    import pyoracle
+    orc = pyoracle.Oracle(ps, st, meshes, shifting_jacobi=jacobi)
+    if prev is not None:
+        orc.first[:] = prev["firstParticleInBucket"]; orc.last[:] = prev["lastParticleInBucket"]; orc.next[:] = prev["nextParticleInSameBucket"]
+        orc.P.velMax = float(prev["scalars"][0])
+    return orc
+
+
+def _check_noisy_sign(got, want_state):
+    """deviationDotPolygonNormal is sign(npcd . n): must agree wherever the dot product is not rounding noise."""
+    n = got.numParticles
+    d = want_state.npcdDeviation.reshape(-1, 3)[:n]; pn = want_state.polygonNormal.reshape(-1, 3)[:n]
+    dot = (d * pn).sum(axis=1)
+    sure = np.abs(dot) > 1e-12 * max(np.abs(d).max(), 1e-300)
+    assert np.array_equal(got.deviationDotPolygonNormal[:n][sure], want_state.deviationDotPolygonNormal[:n][sure])
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_stage_by_stage_against_reference_dumps(name):
+    order, dumps, meta, ps, meshes = golden(name)
+    n0 = int(dumps["pre_init"]["numParticles"][1])
+    eng = _engine(ps, meshes, n0)
+    checked = 0
+    for step in dumped_steps(order):
+        for stage, prev_name, cur_name in stage_sequence(order, step):
+            prev, cur = dumps[prev_name], dumps[cur_name]
+            st = state_from(prev)
+            eng.upload(st)
+            eng.set_velmax(float(prev["scalars"][0]))
+            eng.update_buckets()
+            if stage != "updateParticlesID":
+                for call in STAGE_MAP[stage]:
+                    getattr(eng, call)()
+            got = state_from(prev)
+            eng.download(got)
+            if stage in SHIFTING_STAGES:   # the reference's sweep is sequential: the checker is the Jacobi oracle
+                want = state_from(prev); orc = _oracle(ps, want, meshes, prev, jacobi=True)
+                for call in STAGE_MAP[stage]:
+                    getattr(orc, call)()
+            else:
+                want = state_from(cur)
+            assert got.numParticles == want.numParticles
+            bad = compare_states(got, want, rtol=RTOL, skip=NOISY)
+            assert not bad, "%s step %d stage %s: %s" % (name, step, stage, bad)
+            _check_noisy_sign(got, want)
+            if stage == "correctionVelocityPosition":
+                assert abs(eng.scalars().velMax - float(cur["scalars"][0])) <= 1e-14 * max(1.0, float(cur["scalars"][0]))
+            checked += 1
+    assert checked >= 20
+    eng.close()
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_bucket_membership_matches_reference_lists(name):
+    """Bucket assignment and in-bucket order are bit-exact: same bucket id per particle, same members per bucket in the
+    reference's list order (ascending index)."""
+    order, dumps, meta, ps, meshes = golden(name)
+    step = dumped_steps(order)[-1]
+    pre = dumps["s%04d_pre" % step]; cur = dumps[stage_sequence(order, step)[0][2]]
+    n0 = int(pre["numParticles"][1])
+    eng = _engine(ps, meshes, n0)
+    eng.upload(state_from(pre)); eng.update_buckets()
+    b, start, members = eng.buckets()
+    first, nxt = cur["firstParticleInBucket"], cur["nextParticleInSameBucket"]
+    for cell in range(ps.numBucketsXYZ):
+        ref = []; j = int(first[cell])
+        while j != -1:
+            ref.append(j); j = int(nxt[j])
+        assert list(members[start[cell]:start[cell + 1]]) == ref, "bucket %d" % cell
+        for j in ref:
+            assert b[j] == cell
+    eng.close()
+
+
+def _seeded_case(kind):
+    if kind == "w3":
+        return cases.dam3d(20, 10, 14, jitter=0.05, name="w3s")
+    if kind == "w3lattice":
+        return cases.dam3d(16, 8, 12, name="w3l")
+    if kind == "w2":
+        return cases.dam2d_particle(30, 40, name="w2s")
+    raise KeyError(kind)
+
+
+def _build(case):
+    ps = ParticleSystem.from_json(case.options).set_parameters()
+    ps.allocate_buckets(case.pos)
+    meshes = []
+    if ps.wallType == 1:
+        meshes = [PolygonMesh.from_triangles(case.tris).init_wall_tables(int(ps.dim), ps.weightType, ps.partDist, ps.reL, ps.reS)]
+    return ps, meshes, HostState.from_case(case, ps)
+
+
+@pytest.mark.parametrize("kind", ["w3", "w3lattice", "w2"])
+def test_whole_steps_against_oracle(kind):
+    """pmps_init_step0 + pmps_step against the oracle's drivers on a seeded case a few thousand particles large."""
+    case = _seeded_case(kind)
+    ps, meshes, st0 = _build(case)
+    want = st0.copy(); orc = _oracle(ps, want, meshes, jacobi=True)
+    orc.init_step0()
+    eng = _engine(ps, meshes, st0.numParticlesZero)
+    eng.upload(st0); eng.init_step0()
+    got = st0.copy(); eng.download(got)
+    bad = compare_states(got, want, rtol=RTOL, skip=NOISY)
+    assert not bad, "step 0: %s" % bad
+    for k in range(1, 4):
+        orc.step(1); eng.step(1)
+        eng.download(got)
+        bad = compare_states(got, want, rtol=RTOL * 10 ** (k - 1), skip=NOISY)
+        assert not bad, "step %d: %s" % (k, bad)
+        s = eng.scalars()
+        assert abs(s.velMax - orc.P.velMax) <= 1e-9 * max(orc.P.velMax, 1e-30)
+        assert s.numParticles == want.numParticles
+    eng.close()
+
+
+@pytest.mark.parametrize("kind", ["w3", "w2"])
+def test_neighbour_sets_bit_exact(kind):
+    """Neighbour sets under every predicate of the reference (P(reL), P(reS), M(reS), M(reL), collision) are identical
+    AS SETS to the oracle's bucket walk, after positions have moved away from the bucket build (mid-step)."""
+    case = _seeded_case(kind)
+    ps, meshes, st0 = _build(case)
+    want = st0.copy(); orc = _oracle(ps, want, meshes, jacobi=True)
+    orc.init_step0(); orc.step(2)
+    # go to the middle of step 3: after prediction + wall pass the mirror positions are live
+    orc.update_buckets(); orc.calc_viscosity(); orc.add_gravity(); orc.predict(); orc.check_out_domain(); orc.collisions()
+    eng = _engine(ps, meshes, st0.numParticlesZero)
+    pre = want.copy()
+    if ps.wallType == 1:
+        orc.wall_closest_point()
+    # device: same bucket build (start-of-step positions), then the same moves
+    eng.upload(st0); eng.init_step0(); eng.step(2)
+    eng.update_buckets(); eng.calc_viscosity(); eng.add_gravity(); eng.predict(); eng.check_out_domain(); eng.collisions()
+    if ps.wallType == 1:
+        eng.wall_closest_point()
+    rng = np.random.default_rng(7)
+    idx = rng.choice(want.numParticles, size=min(400, want.numParticles), replace=False)
+    kinds = (0, 1, 2, 3, 4) if ps.wallType == 1 else (0, 1, 4)
+    for i in idx:
+        for kd in kinds:
+            a = eng.neighbors(int(i), kd); b = orc.neighbors(int(i), kd)
+            assert neighbor_sets_equal(a, b), "particle %d kind %d: %s vs %s" % (i, kd, sorted(a), sorted(b))
+    del pre
+    eng.close()
+
+
+def test_errors_are_loud():
+    from polymps_b200.engine import Engine, PmpsError
+    case = cases.dam3d(6, 5, 6, name="err")
+    ps, meshes, st = _build(case)
+    eng = Engine(ps, meshes)
+    with pytest.raises(PmpsError):
+        eng.calc_viscosity()          # nothing uploaded
+    eng.upload(st)
+    with pytest.raises(PmpsError):
+        eng.calc_viscosity()          # buckets not built
+    eng.close()
