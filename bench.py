@@ -1,0 +1,279 @@
+#!/usr/bin/env python
+"""bench.py — particle-steps/s of the 3D weakly-compressible dam break (BASELINE.json metric) on N B200s.
+
+    python bench.py --gpus N --steps K --warmup W            # our CUDA path (one process per GPU under torchrun for N>1)
+    python bench.py --impl reference --steps K --warmup W    # the reference's own CPU code on the host cores
+
+A "step" is one pass of the per-timestep hot path (reference src/main.cpp:256-456) over the synthetic dam-break block of
+SURVEY.md §8d (InputDamWC option set: 3D, polygon walls, WC-MPS, re 2.1/2.1, gradient type 3, shifting 2, diffusive PND,
+Lennard-Jones wall repulsion, NPCD free surface, PC collisions, no-slip).  One JSON line is printed by rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "particle-steps/sec (3D WC dam break)"
+UNIT = "particle-steps/s"
+# Algorithmic bytes per particle per launch (FP64 SoA, every reference array a kernel must read or write counted once;
+# the candidate list is NOT algorithmic traffic).  DESIGN.md §6 derives each line; SURVEY.md §8d gives the step total.
+ALGO_BYTES = {
+    "viscosity": 116, "collision": 104, "collision.apply": 0, "pnd_neigh_npcd": 160, "pnd_diffusive": 124, "wall_npcd": 0,
+    "wall_pnd_diffusive": 0, "mean_pnd_surface": 72, "press_gradient": 96, "wall_press_gradient": 0, "wall_viscosity": 0,
+    "shift.concentration": 64, "shift.gradient": 113, "shift.wall_gradient": 0, "wall.closest_point": 121, "list.build": 308,
+    "predict": 172, "correct": 148, "add_gravity": 0, "update_pnd": 0, "update_bc": 48, "press_eos": 0,
+}
+STEP_ALGO_BYTES = 1732   # sum over the fused groups G0..G7 + E1..E5 of the 3D WC polygon option set
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", float(d.get("sm_max_mhz", 1965.0))
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.index = index; self.rows = []; self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15); self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def block_case(k, jitter=0.0):
+    from polymps_b200 import cases
+    return cases.dam3d_block(k, jitter=jitter, name="block%d" % k)
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def run_reference_cpu(k, steps, warmup, threads):
+    """Times the reference's own CPU implementation on a bounded sample (block of 2k*k*k particles) of the workload.
+    kind "reference": oracle/_ref/ref_driver = the unmodified reference sources driven through main.cpp's call order;
+    kind "port": the C oracle when the reference binary is not present."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refrun
+    case = block_case(k)
+    n = case.n
+    if refrun.have_ref():
+        from polymps_b200 import cases
+        root = tempfile.mkdtemp(prefix="pmps_ref_")
+        try:
+            cases.write_case(case, root)
+            # ref_driver times its own step loop; run warmup+steps and a warmup-only pass to subtract
+            out = refrun.run_reference(root, case.name, warmup + steps, os.path.join(root, "d"), threads=threads, timing=True)
+            tot = float(out.split("loop_seconds=")[1].split()[0])
+            t_w = 0.0
+            if warmup > 0:
+                out_w = refrun.run_reference(root, case.name, warmup, os.path.join(root, "d"), threads=threads, timing=True)
+                t_w = float(out_w.split("loop_seconds=")[1].split()[0])
+            sec = max(tot - t_w, 1e-9)
+        finally:
+            shutil.rmtree(root, ignore_errors=True)
+        kind = "reference"
+    else:
+        import pyoracle
+        from polymps_b200.params import ParticleSystem
+        from polymps_b200.mesh import PolygonMesh
+        from polymps_b200.state import HostState
+        ps = ParticleSystem.from_json(case.options).set_parameters(); ps.allocate_buckets(case.pos)
+        meshes = [PolygonMesh.from_triangles(case.tris).init_wall_tables(int(ps.dim), ps.weightType, ps.partDist, ps.reL, ps.reS)]
+        st = HostState.from_case(case, ps)
+        orc = pyoracle.Oracle(ps, st, meshes, shifting_jacobi=True, threads=threads)
+        orc.init_step0(); orc.step(warmup)
+        t0 = time.time(); orc.step(steps); sec = time.time() - t0
+        kind = "port"
+    return {"value": n * steps / sec, "unit": UNIT, "cores": threads, "kind": kind,
+            "sample": "%d steps of a %dx%dx%d-particle dam-break block (%d particles), same option set" % (steps, 2 * k, k, k, n)}, sec
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    cb, sec = run_reference_cpu(args.ref_k, args.steps, args.warmup, threads)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": "3D WC dam-break block, InputDamWC option set (CPU sample %d particles)" % (2 * args.ref_k ** 3)},
+            "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+E2E_UP = ["pos", "vel", "press", "pndi", "particleBC", "mirrorParticlePos"]      # state a host-driven step must send
+E2E_DOWN = ["pos", "vel", "press", "pndi", "particleBC", "mirrorParticlePos"]    # ... and read back (reference layout)
+
+
+def field_bytes(st, names):
+    return int(sum(getattr(st, f).nbytes for f in names))
+
+
+def main_gpu(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU path; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    from polymps_b200.engine import make_engine
+
+    case = block_case(args.k)
+    ps, meshes, st, eng = make_engine(case, device=local)
+    n = st.numParticles
+    stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
+    eng.init_step0()
+    eng.step(args.warmup)
+    eng.synchronize(); eng.scalars()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    l0 = eng.launch_count()
+    barrier(); sampler.start()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record(stream); eng.step(args.steps); e1.record(stream)
+    eng.synchronize(); barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    launches = eng.launch_count() - l0
+    sc = eng.scalars()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    cnt = torch.tensor([float(sc.numParticles)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms = float(t.item()); total_particles = float(cnt.item())
+    value = total_particles * args.steps / (ms * 1e-3)
+
+    # per-kernel device time (CUDA events around every launch on the step stream; separate pass: it serialises)
+    eng.profile(True); eng.step(args.profile_steps); prof = eng.profile_get(); eng.profile(False)
+    prof_ms = {nm: t_ms / args.profile_steps for nm, t_ms, _ in prof}
+    step_prof_ms = sum(prof_ms.values())
+    top = max(prof, key=lambda r: r[1])
+    top_name, top_avg_ms = top[0], top[1] / max(top[2], 1)
+    peak, peak_src, _ = measured_peaks()
+    algo = ALGO_BYTES.get(top_name, 0) * sc.numParticles
+    achieved = algo / (top_avg_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": top_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": args.traffic, "peak_source": peak_src, "kernel_ms": top_avg_ms, "kernel_share_of_step": top[1] / args.profile_steps / max(step_prof_ms, 1e-9),
+                "algorithmic_bytes_per_particle": ALGO_BYTES.get(top_name, 0),
+                "step": {"algorithmic_bytes_per_particle_step": STEP_ALGO_BYTES, "achieved_GBps": STEP_ALGO_BYTES * sc.numParticles / (ms / args.steps * 1e-3) / 1e9,
+                         "frac": STEP_ALGO_BYTES * sc.numParticles / (ms / args.steps * 1e-3) / 1e9 / peak},
+                "kernels_ms_per_step": {k: round(v, 4) for k, v in sorted(prof_ms.items(), key=lambda kv: -kv[1])}}
+
+    # end to end through the C ABI with HOST buffers: every step uploads the carried state, steps, and reads it back
+    e2e_steps = max(1, min(args.e2e_steps, args.steps))
+    eng.download(st)   # host copy of the current state (also pins the host arrays)
+    eng.upload(st, E2E_UP); eng.step(1); eng.download(st, E2E_DOWN)   # warm: pinning + first touch
+    barrier()
+    e0.record(stream)
+    for _ in range(e2e_steps):
+        eng.upload(st, E2E_UP); eng.step(1); eng.download(st, E2E_DOWN)
+    e1.record(stream); eng.synchronize(); barrier()
+    ms_e = e0.elapsed_time(e1)
+    te = torch.tensor([ms_e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    sc2 = eng.scalars()
+    e2e = {"value": total_particles * e2e_steps / (float(te.item()) * 1e-3), "unit": UNIT, "steps": e2e_steps,
+           "h2d_bytes_per_step": field_bytes(st, E2E_UP) * world, "d2h_bytes_per_step": field_bytes(st, E2E_DOWN) * world,
+           "api": "pmps_upload + pmps_step(1) + pmps_download per step, host arrays pinned in place"}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "synthetic 3D WC dam-break block %dx%dx%d = %d particles per GPU, STL polygon tank (10 triangles), InputDamWC option set" % (2 * args.k, args.k, args.k, n),
+                       "particles_per_gpu": n, "parallelism": "1 GPU" if world == 1 else "%d independent slabs-to-be (replicas; halo exchange not built yet)" % world,
+                       "l2": "state per GPU (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (n * 1500 / 1e9),
+                       "max_displacement_over_lo": sc2.maxDisplacement / ps.partDist, "max_bucket_count": sc2.maxBucketCount},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cb, _ = run_reference_cpu(args.cpu_k, args.cpu_steps, 1, os.cpu_count() or 1)
+        line["cpu_baseline"] = cb
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--k", type=int, default=171, help="block edge: 2k x k x k particles per GPU (171 -> 10.0M)")
+    ap.add_argument("--ref-k", type=int, default=50, help="block edge of the CPU sample for --impl reference")
+    ap.add_argument("--cpu-k", type=int, default=40, help="block edge of the cpu_baseline sample")
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--profile-steps", type=int, default=2)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--traffic", type=float, default=None, help="dram bytes per launch of the top kernel from an ncu --set full capture (profiles/)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        main_reference(args)
+    else:
+        main_gpu(args)
+
+
+if __name__ == "__main__":
+    main()
