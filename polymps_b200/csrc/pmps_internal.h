@@ -100,9 +100,9 @@ struct pmps_handle {
 	std::string err;
 	std::vector<std::pair<void*, size_t>> registered;   // host ranges pinned with cudaHostRegister
 	// PPE workspace
-	double *ppe_val = nullptr, *ppe_diag = nullptr, *ppe_r = nullptr, *ppe_p = nullptr, *ppe_z = nullptr, *ppe_t = nullptr, *ppe_dots = nullptr;
-	double *ppe_q = nullptr, *ppe_s = nullptr, *ppe_y = nullptr, *ppe_r0 = nullptr;
-	uint8_t* ppe_mask = nullptr;
+	uint32_t* ppe_col = nullptr; uint16_t* ppe_cnt = nullptr;
+	double *ppe_val = nullptr, *ppe_diag = nullptr, *ppe_r = nullptr, *ppe_p = nullptr, *ppe_t = nullptr;
+	double *ppe_partial = nullptr, *ppe_scal = nullptr, *ppe_host = nullptr;
 	// profiling
 	bool profile = false;
 	std::vector<std::string> profNames; std::vector<float> profMs; std::vector<int> profLaunches;

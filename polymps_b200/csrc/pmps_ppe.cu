@@ -1,3 +1,232 @@
-// pmps_ppe.cu — placeholder until the PPE kernels land (next commit)
+// pmps_ppe.cu — K1/K2: pressure Poisson equation of the incompressible scheme.
+// Replaces MpsPressure::solvePressurePoissonPnd + solveConjugateGradient + setZeroOnNegativePressure (reference
+// src/MpsPressure.cpp:169-286, :424-445, :471-476) and the Eigen arithmetic under them (ConjugateGradient.h:27-91,
+// BasicPreconditioners.h:67-91).
+//
+// Assembly: the reference pushes triplets serially and lets Eigen build a column-major matrix; its CG is told
+// Lower|Upper on that storage, so it multiplies by the TRANSPOSE of the assembled matrix (identical unless a polygon
+// wall's one-sided mirror test breaks symmetry).  Here one thread per slot c writes row c of A^T directly as a
+// compacted ELL row (column = slot of particle i, value = A_ic) by evaluating row i's predicate from c's candidate
+// list, plus the diagonal and the right-hand side of its own row.  Everything is in slot order, so x-gathers in the
+// SpMV hit nearby addresses.
+// Solve: Eigen's Jacobi-preconditioned CG recurrence, warm start from pressurePPE, threshold eps^2 |b|^2, maxIt 2N.
+// Dot products are two-stage (per-block partials, then one block) so the iteration is deterministic run to run.
 #include "pmps_device.cuh"
-int pmps_ppe_solve(pmps_handle* h) { return pmps_fail(h, PMPS_E_UNSUPPORTED, "pressure Poisson solve not built yet"); }
+#include <cfloat>
+#include <cmath>
+
+#define PPE_T 128
+#define RED_T 256
+
+struct PpeView {
+	uint32_t* col; double* val; uint16_t* cnt;   // A^T, compacted ELL in the candidate-list layout
+	double* diag; double* r; double* p; double* t;
+	double* partial;   // [3][nBlocks] block partial sums
+	double* scal;      // 0 rhs2, 1 res2, 2 absNew, 3 absOld, 4 pt, 5 alpha, 6 beta, 7 thr
+};
+
+template <bool POLY>
+__global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ DevView S, const __grid_constant__ KParams K, const __grid_constant__ PpeView M) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const double4 pi = S.pos[i]; const int ti = pk_type(pi);
+	if (ti == K.p.ghost) { M.cnt[i] = 0; M.diag[i] = 1.0; S.sourceTerm[i] = 0.0; S.pressurePPE[i] = 0.0; return; }
+	const int bci = S.particleBC[i];
+	const bool rowActive = !(bci == K.p.other || bci == K.p.surface);
+	const bool colOK = bci == K.p.inner && ti != K.p.dummyWall;
+	const double mix = POLY ? S.mirrorParticlePos.x[i] : 0.0, miy = POLY ? S.mirrorParticlePos.y[i] : 0.0, miz = POLY ? S.mirrorParticlePos.z[i] : 0.0;
+	const size_t base = (size_t)(i >> 5) * 32 * (size_t)S.listCap + (i & 31);
+	const uint32_t* L = S.list + base; uint32_t* C = M.col + base; double* V = M.val + base;
+	const int cnt = S.listCnt[i];
+	double sum = 0.0, b = 0.0; int nz = 0;
+	for (int k = 0; k < cnt; k++) {
+		const int j = (int)L[(size_t)k * 32];
+		const double4 pj = S.pos[j];
+		const double rx = pj.x - pi.x, ry = pj.y - pi.y, rz = pj.z - pi.z; const double d2 = sq3_exact(rx, ry, rz);
+		if (!(d2 < K.p.reL2)) continue;
+		const double wL = wgt(sqrt(d2), K.p.reL, K.p.weightType); const double a = wL * K.p.coeffPPE;
+		const int tj = pk_type(pj);
+		// row i (src/MpsPressure.cpp:213-229)
+		bool mine = rowActive;
+		if (POLY && mine) { const double mx = pj.x - mix, my = pj.y - miy, mz = pj.z - miz; mine = d2 < sq3_exact(mx, my, mz); }
+		if (mine) {
+			if (tj == K.p.dummyWall) b -= K.p.coeffPPE * (S.RHO[j] * (rx * K.p.gravityX + ry * K.p.gravityY + rz * K.p.gravityZ) * wL);
+			else sum -= a;
+		}
+		// column i of row j: A_ji exists if row j is active, i is a real neighbour of j, i is not a dummy and BC[i] == inner
+		if (colOK) {
+			const int bcj = S.particleBC[j];
+			bool theirs = !(bcj == K.p.other || bcj == K.p.surface);
+			if (POLY && theirs) {
+				const double ex = pi.x - S.mirrorParticlePos.x[j], ey = pi.y - S.mirrorParticlePos.y[j], ez = pi.z - S.mirrorParticlePos.z[j];
+				theirs = d2 < sq3_exact(ex, ey, ez);
+			}
+			if (theirs) { C[(size_t)nz * 32] = (uint32_t)j; V[(size_t)nz * 32] = a; nz++; }
+		}
+	}
+	M.cnt[i] = (uint16_t)nz;
+	if (rowActive) {
+		const double rho = pk_ptype(pi) == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2;
+		sum -= K.p.alphaCompressibility * rho / (K.p.timeStep * K.p.timeStep);
+		M.diag[i] = sum;
+		b += -K.p.coeffPPESource * rho * (S.pndSmall[i] - K.p.pndSmallZero);
+	} else { M.diag[i] = 1.0; b = 0.0; }
+	S.sourceTerm[i] = b;
+}
+
+// ---- block reduction helpers -------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+	return v;
+}
+template <int T> __device__ __forceinline__ double block_sum(double v, double* sh) {
+	v = warp_sum(v);
+	if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+	__syncthreads();
+	double s = 0.0;
+	if (threadIdx.x < 32) { s = threadIdx.x < T / 32 ? sh[threadIdx.x] : 0.0; s = warp_sum(s); }
+	__syncthreads();
+	return s;   // valid in thread 0
+}
+
+__device__ __forceinline__ double ell_row_dot(const DevView& S, const PpeView& M, int i, const double* __restrict__ x) {
+	const size_t base = (size_t)(i >> 5) * 32 * (size_t)S.listCap + (i & 31);
+	const uint32_t* C = M.col + base; const double* V = M.val + base; const int nz = M.cnt[i];
+	double s = M.diag[i] * x[i];
+	for (int k = 0; k < nz; k++) s += V[(size_t)k * 32] * x[C[(size_t)k * 32]];
+	return s;
+}
+
+// r = b - A^T x0 ; partial sums of |b|^2 and |r|^2
+__global__ void __launch_bounds__(PPE_T) k_ppe_residual0(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks) {
+	__shared__ double sh[PPE_T / 32];
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	double b2 = 0.0, r2 = 0.0;
+	if (i < S.n) {
+		const double b = S.sourceTerm[i]; const double r = b - ell_row_dot(S, M, i, S.pressurePPE);
+		M.r[i] = r; b2 = b * b; r2 = r * r;
+	}
+	const double sb = block_sum<PPE_T>(b2, sh); const double sr = block_sum<PPE_T>(r2, sh);
+	if (threadIdx.x == 0) { M.partial[blockIdx.x] = sb; M.partial[nBlocks + blockIdx.x] = sr; }
+}
+// p = M^-1 r ; partial sums of r.p
+__global__ void __launch_bounds__(PPE_T) k_ppe_init_p(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks) {
+	__shared__ double sh[PPE_T / 32];
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	double v = 0.0;
+	if (i < S.n) { const double d = M.diag[i]; const double r = M.r[i]; const double p = (d != 0.0 ? 1.0 / d : 1.0) * r; M.p[i] = p; v = r * p; }
+	const double s = block_sum<PPE_T>(v, sh);
+	if (threadIdx.x == 0) M.partial[blockIdx.x] = s;
+}
+// t = A^T p ; partial sums of p.t
+__global__ void __launch_bounds__(PPE_T) k_ppe_spmv(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks) {
+	__shared__ double sh[PPE_T / 32];
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	double v = 0.0;
+	if (i < S.n) { const double t = ell_row_dot(S, M, i, M.p); M.t[i] = t; v = M.p[i] * t; }
+	const double s = block_sum<PPE_T>(v, sh);
+	if (threadIdx.x == 0) M.partial[blockIdx.x] = s;
+}
+// x += alpha p ; r -= alpha t ; partial sums of |r|^2 and r.(M^-1 r)
+__global__ void __launch_bounds__(PPE_T) k_ppe_update_xr(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks) {
+	__shared__ double sh[PPE_T / 32];
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	const double alpha = M.scal[5];
+	double r2 = 0.0, rz = 0.0;
+	if (i < S.n) {
+		S.pressurePPE[i] += alpha * M.p[i];
+		const double r = M.r[i] - alpha * M.t[i]; M.r[i] = r;
+		const double d = M.diag[i]; const double z = (d != 0.0 ? 1.0 / d : 1.0) * r;
+		r2 = r * r; rz = r * z;
+	}
+	const double s1 = block_sum<PPE_T>(r2, sh); const double s2 = block_sum<PPE_T>(rz, sh);
+	if (threadIdx.x == 0) { M.partial[blockIdx.x] = s1; M.partial[nBlocks + blockIdx.x] = s2; }
+}
+// p = M^-1 r + beta p
+__global__ void __launch_bounds__(PPE_T) k_ppe_update_p(const __grid_constant__ DevView S, const __grid_constant__ PpeView M) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const double beta = M.scal[6]; const double d = M.diag[i];
+	M.p[i] = (d != 0.0 ? 1.0 / d : 1.0) * M.r[i] + beta * M.p[i];
+}
+// second stage of the dot products + the scalar recurrences of Eigen's CG (ConjugateGradient.h:50-89)
+// mode 0: after residual0 -> rhs2, res2, thr ; 1: after init_p -> absNew ; 2: after spmv -> pt, alpha ; 3: after update_xr -> res2, beta
+__global__ void __launch_bounds__(RED_T) k_ppe_reduce(const __grid_constant__ PpeView M, int nBlocks, int mode, double* hostMirror) {
+	__shared__ double sh[RED_T / 32];
+	double a = 0.0, b = 0.0;
+	for (int k = threadIdx.x; k < nBlocks; k += RED_T) { a += M.partial[k]; if (mode == 0 || mode == 3) b += M.partial[nBlocks + k]; }
+	const double sa = block_sum<RED_T>(a, sh); const double sb = block_sum<RED_T>(b, sh);
+	if (threadIdx.x != 0) return;
+	double* s = M.scal;
+	if (mode == 0) { s[0] = sa; s[1] = sb; double thr = DBL_EPSILON * DBL_EPSILON * sa; if (thr < DBL_MIN) thr = DBL_MIN; s[7] = thr; }
+	else if (mode == 1) { s[2] = sa; }
+	else if (mode == 2) { s[4] = sa; s[5] = s[2] / sa; }
+	else { s[1] = sa; s[3] = s[2]; s[2] = sb; s[6] = sb / s[3]; }
+	hostMirror[0] = s[0]; hostMirror[1] = s[1]; hostMirror[2] = s[7];
+}
+// press = max(pressurePPE, 0)  (setZeroOnNegativePressure acts on press only, src/MpsPressure.cpp:471-476)
+__global__ void k_ppe_finish(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int zeroX) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	if (pk_type(S.pos[i]) == K.p.ghost) return;
+	if (zeroX) S.pressurePPE[i] = 0.0;
+	const double x = S.pressurePPE[i];
+	S.press[i] = x < 0 ? 0.0 : x;
+}
+
+template <class T> static int palloc(pmps_handle* h, T** p, size_t count) {
+	if (*p) return 0;
+	void* q = nullptr;
+	if (cudaMalloc(&q, sizeof(T) * (count ? count : 1)) != cudaSuccess) return 1;
+	cudaMemsetAsync(q, 0, sizeof(T) * (count ? count : 1), h->stream);
+	h->allocs.push_back(q); *p = (T*)q; return 0;
+}
+
+int pmps_ppe_solve(pmps_handle* h) {
+	DevView& S = h->V; const KParams& K = h->K;
+	if (K.p.solverType != 0) return pmps_fail(h, PMPS_E_UNSUPPORTED, "PPE: only the conjugate-gradient solver (solver_type 0) is on the device path");
+	const int n = S.n, nBlocks = cdiv(n, PPE_T);
+	const size_t nWarps = ((size_t)S.n0 + 31) / 32, ell = nWarps * 32 * (size_t)S.listCap;
+	int bad = 0;
+	bad |= palloc(h, &h->ppe_col, ell); bad |= palloc(h, &h->ppe_val, ell); bad |= palloc(h, &h->ppe_cnt, nWarps * 32);
+	bad |= palloc(h, &h->ppe_diag, S.n0); bad |= palloc(h, &h->ppe_r, S.n0); bad |= palloc(h, &h->ppe_p, S.n0); bad |= palloc(h, &h->ppe_t, S.n0);
+	bad |= palloc(h, &h->ppe_partial, 2 * (size_t)cdiv(S.n0, PPE_T) + 2); bad |= palloc(h, &h->ppe_scal, 16);
+	if (!h->ppe_host) { if (cudaMallocHost((void**)&h->ppe_host, 64) != cudaSuccess) bad |= 1; }
+	if (bad) return pmps_fail(h, PMPS_E_CUDA, "PPE workspace allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+	PpeView M; M.col = h->ppe_col; M.val = h->ppe_val; M.cnt = h->ppe_cnt; M.diag = h->ppe_diag; M.r = h->ppe_r; M.p = h->ppe_p; M.t = h->ppe_t;
+	M.partial = h->ppe_partial; M.scal = h->ppe_scal;
+	double* hm = h->ppe_host;
+	if (K.poly) { LAUNCH(h, "ppe.assemble", k_ppe_assemble<true>, nBlocks, PPE_T, S, K, M); }
+	else { LAUNCH(h, "ppe.assemble", k_ppe_assemble<false>, nBlocks, PPE_T, S, K, M); }
+	LAUNCH(h, "ppe.residual0", k_ppe_residual0, nBlocks, PPE_T, S, M, nBlocks);
+	LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 0, hm);
+	CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+	const double rhs2 = hm[0]; double res2 = hm[1]; const double thr = hm[2];
+	int iters = 0; double err = 0.0; int zeroX = 0;
+	if (rhs2 == 0.0) { zeroX = 1; }
+	else {
+		if (res2 >= thr) {
+			LAUNCH(h, "ppe.init_p", k_ppe_init_p, nBlocks, PPE_T, S, M, nBlocks);
+			LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 1, hm);
+			const long long maxIt = 2ll * h->numParticles;
+			while (iters < maxIt) {
+				LAUNCH(h, "ppe.spmv", k_ppe_spmv, nBlocks, PPE_T, S, M, nBlocks);
+				LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 2, hm);
+				LAUNCH(h, "ppe.update_xr", k_ppe_update_xr, nBlocks, PPE_T, S, M, nBlocks);
+				LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 3, hm);
+				CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+				res2 = hm[1];
+				if (res2 < thr || !(res2 == res2)) break;
+				LAUNCH(h, "ppe.update_p", k_ppe_update_p, nBlocks, PPE_T, S, M);
+				iters++;
+			}
+		}
+		err = sqrt(res2 / rhs2);
+	}
+	LAUNCH(h, "ppe.finish", k_ppe_finish, cdiv(n, 256), 256, S, K, zeroX);
+	CUDA_TRY(h, cudaGetLastError());
+	h->solverIter = iters; h->solverError = err;
+	if (!(res2 == res2)) return pmps_fail(h, PMPS_E_STATE, "PPE: the conjugate-gradient residual became NaN after %d iterations", iters);
+	return PMPS_OK;
+}
