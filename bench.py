@@ -31,10 +31,13 @@ UNIT = "particle-steps/s"
 # Algorithmic bytes per particle per launch (FP64 SoA, every reference array a kernel must read or write counted once;
 # the candidate list is NOT algorithmic traffic).  DESIGN.md §6 derives each line; SURVEY.md §8d gives the step total.
 ALGO_BYTES = {
-    "viscosity": 116, "collision": 104, "collision.apply": 0, "pnd_neigh_npcd": 160, "pnd_diffusive": 124, "wall_npcd": 0,
-    "wall_pnd_diffusive": 0, "mean_pnd_surface": 72, "press_gradient": 96, "wall_press_gradient": 0, "wall_viscosity": 0,
-    "shift.concentration": 64, "shift.gradient": 113, "shift.wall_gradient": 0, "wall.closest_point": 121, "list.build": 308,
-    "predict": 172, "correct": 148, "add_gravity": 0, "update_pnd": 0, "update_bc": 48, "press_eos": 0,
+    # fused groups of the whole-step path (names = LAUNCH names in polymps_b200/csrc/pmps_stages.inc)
+    "F1.viscosity+predict": 288, "F2.wall+collision": 225, "F2.collision": 104, "F3.pnd+diffusive+wall": 217, "F3.pnd+diffusive": 217,
+    "F3.pnd+wall": 160, "mean_pnd_surface": 72, "E4.bc+eos": 48, "F5.gradient+wall+correct": 313, "F5.gradient+correct": 313,
+    "shift.concentration": 64, "shift.gradient": 113, "shift.wall_gradient": 0, "list.build": 308,
+    # unfused stage kernels (PMPS_STAGED=1 / stage API)
+    "viscosity": 116, "collision": 104, "pnd_neigh_npcd": 160, "pnd_diffusive": 124, "press_gradient": 96, "wall.closest_point": 121,
+    "predict": 172, "correct": 148, "update_bc": 48,
 }
 STEP_ALGO_BYTES = 1732   # sum over the fused groups G0..G7 + E1..E5 of the 3D WC polygon option set
 

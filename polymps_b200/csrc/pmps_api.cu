@@ -39,31 +39,19 @@ __global__ void k_add_gravity(const __grid_constant__ DevView S, const __grid_co
 	S.accStar.x[i] = ax; S.accStar.y[i] = ay; S.accStar.z[i] = az;
 }
 
-__device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, int i, const double4& p) {
-	const float4 b = S.bpos[i];
-	const float dx = (float)(p.x - K.p.domainMinX) - b.x, dy = (float)(p.y - K.p.domainMinY) - b.y, dz = (float)(p.z - K.p.domainMinZ) - b.z;
-	atomic_max_f(S.maxDisp2, dx * dx + dy * dy + dz * dz);
-}
-
 // MpsParticleVelPos::predictionVelocityPosition, src/MpsParticleVelPos.cpp:20-50
 __global__ void k_predict(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= S.n) return;
 	double4 p = S.pos[i];
 	if (pk_type(p) == K.p.ghost) return;
-	const double dt = K.p.timeStep;
 	if (pk_type(p) == K.p.fluid) {
 		double4 v = S.vel[i];
-		v.x += S.acc.x[i] * dt; v.y += S.acc.y[i] * dt; v.z += S.acc.z[i] * dt;
-		p.x += v.x * dt; p.y += v.y * dt; p.z += v.z * dt;
+		integrate_predict(p, v, S.acc.x[i], S.acc.y[i], S.acc.z[i], K.p.timeStep);
 		S.vel[i] = v; S.pos[i] = p;
 		track_disp(S, K, i, p);
 	}
-	S.acc.x[i] = 0.0; S.acc.y[i] = 0.0; S.acc.z[i] = 0.0;
-	S.dvelCollision.x[i] = 0.0; S.dvelCollision.y[i] = 0.0; S.dvelCollision.z[i] = 0.0;
-	S.npcdDeviation.x[i] = 0.0; S.npcdDeviation.y[i] = 0.0; S.npcdDeviation.z[i] = 0.0;
-	S.numNeighWallContribution[i] = 0; S.particleNearWall[i] = 0; S.distParticleWall2[i] = K.big;
-	if (K.poly) { S.mirrorParticlePos.x[i] = K.big; S.mirrorParticlePos.y[i] = K.big; S.mirrorParticlePos.z[i] = K.big; }
+	predict_resets(S, K, i);
 }
 
 // second loop of checkParticleCollisions (src/MpsParticleCollision.cpp:108-116): vel += dvel for fluid particles
@@ -72,7 +60,7 @@ __global__ void k_apply_collision(const __grid_constant__ DevView S, const __gri
 	if (i >= S.n) return;
 	if (pk_type(S.pos[i]) != K.p.fluid) return;
 	double4 v = S.vel[i];
-	v.x += S.dvelCollision.x[i]; v.y += S.dvelCollision.y[i]; v.z += S.dvelCollision.z[i];
+	v.x = __dadd_rn(v.x, S.dvelCollision.x[i]); v.y = __dadd_rn(v.y, S.dvelCollision.y[i]); v.z = __dadd_rn(v.z, S.dvelCollision.z[i]);
 	S.vel[i] = v;
 }
 
@@ -83,10 +71,8 @@ __global__ void k_correct(const __grid_constant__ DevView S, const __grid_consta
 	if (i < S.n) {
 		double4 p = S.pos[i];
 		if (pk_type(p) == K.p.fluid) {
-			const double dt = K.p.timeStep; const double ax = S.acc.x[i], ay = S.acc.y[i], az = S.acc.z[i];
 			double4 v = S.vel[i];
-			v.x += ax * dt; v.y += ay * dt; v.z += az * dt;
-			p.x += ax * dt * dt; p.y += ay * dt * dt; p.z += az * dt * dt;
+			integrate_correct(p, v, S.acc.x[i], S.acc.y[i], S.acc.z[i], K.p.timeStep);
 			S.vel[i] = v; S.pos[i] = p;
 			S.acc.x[i] = 0.0; S.acc.y[i] = 0.0; S.acc.z[i] = 0.0;
 			v2 = v.x * v.x + v.y * v.y + v.z * v.z;
@@ -159,6 +145,23 @@ __global__ void k_press_eos(const __grid_constant__ DevView S, const __grid_cons
 	S.press[i] = p;
 }
 
+// fused elementwise pair of the whole-step path: updateParticleBC then the equation of state
+__global__ void k_bc_eos(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const double4 pi = S.pos[i]; const int t = pk_type(pi);
+	if (t == K.p.ghost) return;
+	const int bc = classify_bc(S, K, i, t);
+	S.particleBC[i] = bc;
+	const double mi = pk_ptype(pi) == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2; double p = 0.0;
+	if (bc == K.p.inner) {
+		if (K.p.mpsType == 0) p = (S.pndi[i] - K.p.pndSmallZero) * K.p.coeffPressEMPS * mi;
+		else p = (mi * K.p.coeffPressWCMPS / K.p.gamma) * (pow(S.pndi[i] / K.p.pndSmallZero, K.p.gamma) - 1);
+	}
+	if (p < 0.0) p = 0.0;
+	S.press[i] = p;
+}
+
 // ================================================================================================ handle lifetime
 template <class T> static int dalloc(pmps_handle* h, T** p, size_t count) {
 	void* q = nullptr;
@@ -218,6 +221,7 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	K.vol = pow(params->partDist, (double)params->dim);
 	K.velMax = params->velMax;
 	K.poly = params->wallType == 1;
+	K.reMax2 = fmax(params->reS2, params->reL2); K.invReS = 1.0 / params->reS; K.invReL = 1.0 / params->reL;
 	memset(&h->V, 0, sizeof(DevView)); memset(&h->A, 0, sizeof(DevView));
 	h->V.nB = (int)nB;
 	*out = h;

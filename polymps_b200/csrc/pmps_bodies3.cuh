@@ -1,0 +1,255 @@
+// pmps_bodies3.cuh — stage bodies, continued: pressure gradient (+ wall terms, + fused correction tail), shifting,
+// particle-wall extrapolations.
+#pragma once
+
+// ------------------------------------------------------------------------------------------------ pressure gradient
+// phi of src/MpsPressure.cpp:1288-1300 times w / d2; invDD = 1/d2, invNi = 1/n_i
+__device__ __forceinline__ double grad_phi_r(const KParams& K, double w, double Pj, double Pi, double Pmin, double ni, double invNi, double nj, double invDD) {
+	switch (K.p.gradientType) {
+		case 0: return w * ((Pj - Pmin) * invDD);
+		case 1: return w * ((Pj + Pi) * invDD);
+		case 2: return w * ((Pj + Pi - 2.0 * Pmin) * invDD);
+		default: return (ni > K.p.epsilonZero && nj > K.p.epsilonZero) ? w * ((ni * Pj * fast_rcp(nj) + nj * Pi * invNi) * invDD) : w;
+	}
+}
+
+// first pass of calcPressGradient / calcWallPressGradient for gradient types 0 and 2: Pmin over P(reS)
+// (src/MpsPressure.cpp:1237-1262, :1405-1430).  Result parked in a scratch plane that is not a reference field.
+struct BPressMin {
+	struct Ctx { double pmin; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) { c.pmin = S.press[s.i]; return true; }
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_P<POLY>(q, K.p.reS2)) return;
+		const double pj = S.press[q.j]; if (c.pmin > pj) c.pmin = pj;
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.pmin = gmin(c.pmin, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) { S.scratch1[s.i] = c.pmin; }
+};
+
+// MpsPressure::calcPressGradient, src/MpsPressure.cpp:1217-1338
+struct BPressGradient {
+	struct Ctx { double Pi, ni, invNi, Pmin, sx, sy, sz; double c1[3], c2[3], c3[3]; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		c.Pi = S.press[s.i]; c.ni = S.pndi[s.i]; c.invNi = c.ni > K.p.epsilonZero ? 1.0 / c.ni : 0.0;
+		c.Pmin = (K.p.gradientType == 0 || K.p.gradientType == 2) ? S.scratch1[s.i] : c.Pi;
+		if (K.p.gradientCorrection) {
+			c.c1[0] = S.correcMatrixRow1.x[s.i]; c.c1[1] = S.correcMatrixRow1.y[s.i]; c.c1[2] = S.correcMatrixRow1.z[s.i];
+			c.c2[0] = S.correcMatrixRow2.x[s.i]; c.c2[1] = S.correcMatrixRow2.y[s.i]; c.c2[2] = S.correcMatrixRow2.z[s.i];
+			c.c3[0] = S.correcMatrixRow3.x[s.i]; c.c3[1] = S.correcMatrixRow3.y[s.i]; c.c3[2] = S.correcMatrixRow3.z[s.i];
+		}
+		c.sx = c.sy = c.sz = 0.0; return true;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_P<POLY>(q, K.p.reS2)) return;
+		const double w = grad_phi_r(K, wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType), S.press[q.j], c.Pi, c.Pmin, c.ni, c.invNi, S.pndi[q.j], q.rinv * q.rinv);
+		if (!K.p.gradientCorrection) { c.sx += q.rx * w; c.sy += q.ry * w; c.sz += q.rz * w; }
+		else {
+			c.sx += (q.rx * c.c1[0] + q.ry * c.c1[1] + q.rz * c.c1[2]) * w; c.sy += (q.rx * c.c2[0] + q.ry * c.c2[1] + q.rz * c.c2[2]) * w;
+			c.sz += (q.rx * c.c3[0] + q.ry * c.c3[1] + q.rz * c.c3[2]) * w;
+		}
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.sx = gsum(c.sx, m); c.sy = gsum(c.sy, m); c.sz = gsum(c.sz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		const double rho = S.RHO[s.i];
+		S.acc.x[s.i] = K.p.relaxPress * c.sx * K.p.coeffPressGrad / rho;
+		S.acc.y[s.i] = K.p.relaxPress * c.sy * K.p.coeffPressGrad / rho;
+		S.acc.z[s.i] = K.p.relaxPress * c.sz * K.p.coeffPressGrad / rho;
+	}
+};
+
+// wall repulsion, src/MpsPressure.cpp:1554-1611: the scalar that multiplies -n
+__device__ __forceinline__ double repulsion(const KParams& K, double r, double rho, double vmax2) {
+	const double re = K.p.reRepulsiveForce;
+	switch (K.p.repulsiveForceType) {
+		case 0: return rho / (K.p.timeStep * K.p.timeStep) * (re - r);
+		case 1: return K.p.repForceCoefMitsume * wgt(r, re, K.p.weightType);
+		case 2: { const double R1 = (re / r) * (re / r); const double R2 = R1 * R1; return (K.p.repForceCoefLennardJones * vmax2 / r) * (R2 - R1) * rho; }
+		default: { const double W1 = (1.0 + 3.0 * 0.5 * r / (re)); const double W2 = (1.0 - r / (re)) * (1.0 - r / (re)) * (1.0 - r / (re));
+			return (K.p.repForceCoefMonaghanKajtar * vmax2 / (r - 0.0 * K.p.partDist)) * (1.0 / 8.0) * (W1) * (W2)*rho; }
+	}
+}
+
+// MpsPressure::calcWallPressGradient, src/MpsPressure.cpp:1341-1550.  velMax of the previous correction is read
+// from the device scalar so the step needs no host round trip.
+struct BWallPressGradient {
+	typedef void wall_frame_tag;
+	struct Ctx { double Pi, ni, invNi, Pmin, sx, sy, sz; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (!s.nearWallFluid) return false;
+		c.Pi = S.press[s.i]; c.ni = S.pndi[s.i]; c.invNi = c.ni > K.p.epsilonZero ? 1.0 / c.ni : 0.0;
+		c.Pmin = (K.p.gradientType == 0 || K.p.gradientType == 2) ? S.scratch1[s.i] : c.Pi;
+		c.sx = c.sy = c.sz = 0.0; return true;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_M(q, K.p.reS2)) return;
+		const double mi = fast_rsqrt(q.dm2);
+		const double w = grad_phi_r(K, wgt_r(mi, q.dm2, K.p.reS, K.invReS, K.p.weightType), S.press[q.j], c.Pi, c.Pmin, c.ni, c.invNi, S.pndi[q.j], mi * mi);
+		c.sx += q.mx * w; c.sy += q.my * w; c.sz += q.mz * w;
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.sx = gsum(c.sx, m); c.sy = gsum(c.sy, m); c.sz = gsum(c.sz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		const double ex = s.pi.x - s.mix, ey = s.pi.y - s.miy, ez = s.pi.z - s.miz; const double dd = sq3_exact(ex, ey, ez);
+		if (dd < K.p.reS2) {
+			const double w = grad_phi_r(K, wgt(sqrt(dd), K.p.reS, K.p.weightType), c.Pi, c.Pi, c.Pmin, c.ni, c.invNi, c.ni, 1.0 / dd);
+			c.sx += ex * w; c.sy += ey * w; c.sz += ez * w;
+		}
+		WallFrame f; wall_frame_of(f, s, K.p.epsilonZero, false);
+		const double rho = S.RHO[s.i];
+		double fr[3] = { 0.0, 0.0, 0.0 };
+		const double r = f.len;
+		if (r < K.p.reRepulsiveForce && r > K.p.epsilonZero) {
+			const double velMax = sqrt(__longlong_as_double((long long)S.velMax2Bits[1]));
+			const double vcap = velMax < K.p.expectMaxVelocity ? velMax : K.p.expectMaxVelocity;
+			const double qq = repulsion(K, r, rho, vcap * vcap);
+			fr[0] = -qq * f.n[0]; fr[1] = -qq * f.n[1]; fr[2] = -qq * f.n[2];
+		}
+		double* a[3] = { S.acc.x, S.acc.y, S.acc.z }; double* fw[3] = { S.forceWall.x, S.forceWall.y, S.forceWall.z };
+		for (int k = 0; k < 3; k++) {
+			const double g = (K.p.relaxPress * MATVEC(f.R, c.sx, c.sy, c.sz, k) * K.p.coeffPressGrad - fr[k]);
+			a[k][s.i] += g / rho;
+			fw[k][s.i] += -g * K.vol;
+		}
+	}
+};
+
+// fused tail of the gradient pass: correctionVelocityPosition (src/MpsParticleVelPos.cpp:53-97).  Reads the acceleration
+// the bodies in front of it stored, writes the new position / velocity to the alternate buffers, feeds velMax.
+struct BCorrectTail {
+	typedef void copy_pos_tag; typedef void copy_vel_tag;
+	struct Ctx {};
+	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams& K, const Self& s) { return s.type == K.p.fluid; }
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
+	__device__ __forceinline__ static void reduce(Ctx& , unsigned m) {  }
+	__device__ __forceinline__ static void end(Ctx&, const DevView& S, const KParams& K, const Self& s) {
+		const int i = s.i;
+		double4 p = s.pi, v = S.vel[i];
+		integrate_correct(p, v, S.acc.x[i], S.acc.y[i], S.acc.z[i], K.p.timeStep);
+		S.pos2[i] = p; S.vel2[i] = v;
+		S.acc.x[i] = 0.0; S.acc.y[i] = 0.0; S.acc.z[i] = 0.0;
+		track_disp(S, K, i, p);
+		const unsigned long long b = (unsigned long long)__double_as_longlong(v.x * v.x + v.y * v.y + v.z * v.z);
+		if (b > S.velMax2Bits[0]) atomicMax(S.velMax2Bits, b);
+	}
+};
+
+// ------------------------------------------------------------------------------------------------ shifting (type 2)
+// MpsShifting::calcConcAndConcGradient, src/MpsShifting.cpp:432-575 — first loop: concentration
+struct BConcentration {
+	struct Ctx { double c; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) { c.c = 0.0; return true; }
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_P<POLY>(q, K.p.reS2)) return;
+		c.c += wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType);
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.c = gsum(c.c, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		S.concentration[s.i] = (c.c + S.pndWallContribution[s.i]) / K.p.pndSmallZero;
+	}
+};
+
+// second loop: concentration gradient and the shift.  Jacobi semantics: positions are READ from S.pos (the snapshot)
+// and the shifted position is WRITTEN to S.pos2; the reference's in-place update is a race for >1 thread
+// (src/MpsShifting.cpp:478-536).
+struct BGradConcentration {
+	typedef void copy_pos_tag;
+	struct Ctx { double ci, gx, gy, gz; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (s.type != K.p.fluid) return false;
+		c.ci = S.concentration[s.i]; c.gx = c.gy = c.gz = 0.0; return true;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_P<POLY>(q, K.p.reS2)) return;
+		const double f = (c.ci + S.concentration[q.j]) * wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType) * (q.rinv * q.rinv);
+		c.gx += q.rx * f; c.gy += q.ry * f; c.gz += q.rz * f;
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.gx = gsum(c.gx, m); c.gy = gsum(c.gy, m); c.gz = gsum(c.gz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		const double g0 = c.gx * -K.p.coeffPressGrad, g1 = c.gy * -K.p.coeffPressGrad, g2 = c.gz * -K.p.coeffPressGrad;
+		S.gradConcentration.x[s.i] = g0; S.gradConcentration.y[s.i] = g1; S.gradConcentration.z[s.i] = g2;
+		if (S.particleBC[s.i] == K.p.inner) {
+			double4 p = s.pi;
+			p.x = __dsub_rn(p.x, __dmul_rn(K.p.coeffShifting2, g0)); p.y = __dsub_rn(p.y, __dmul_rn(K.p.coeffShifting2, g1)); p.z = __dsub_rn(p.z, __dmul_rn(K.p.coeffShifting2, g2));
+			S.pos2[s.i] = p;
+			track_disp(S, K, s.i, p);
+		}
+	}
+};
+
+// MpsShifting::calcWallConcAndConcGradient, src/MpsShifting.cpp:578-691 (same read-snapshot / write-alternate rule)
+struct BWallGradConcentration {
+	typedef void copy_pos_tag; typedef void wall_frame_tag;
+	struct Ctx { double ci, sx, sy, sz; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (!s.nearWallFluid) return false;
+		c.ci = S.concentration[s.i];
+		c.sx = c.sy = c.sz = 0.0; return true;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_M(q, K.p.reS2)) return;
+		const double mi = fast_rsqrt(q.dm2);
+		const double f = (c.ci + S.concentration[q.j]) * wgt_r(mi, q.dm2, K.p.reS, K.invReS, K.p.weightType) * (mi * mi);
+		c.sx += q.mx * f; c.sy += q.my * f; c.sz += q.mz * f;
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.sx = gsum(c.sx, m); c.sy = gsum(c.sy, m); c.sz = gsum(c.sz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		const double ex = s.pi.x - s.mix, ey = s.pi.y - s.miy, ez = s.pi.z - s.miz; const double dd = sq3_exact(ex, ey, ez);
+		if (dd < K.p.reS2) {
+			const double w = wgt(sqrt(dd), K.p.reS, K.p.weightType);
+			c.sx += (c.ci + c.ci) * ex * w / dd; c.sy += (c.ci + c.ci) * ey * w / dd; c.sz += (c.ci + c.ci) * ez * w / dd;
+		}
+		WallFrame f; wall_frame_of(f, s, K.p.epsilonZero, false);
+		double* g[3] = { S.gradConcentration.x, S.gradConcentration.y, S.gradConcentration.z };
+		double p[3] = { s.pi.x, s.pi.y, s.pi.z };
+		const bool inner = S.particleBC[s.i] == K.p.inner;
+		for (int k = 0; k < 3; k++) {
+			const double gw = -MATVEC(f.R, c.sx, c.sy, c.sz, k) * K.p.coeffPressGrad;
+			g[k][s.i] += gw;
+			if (inner) p[k] = __dsub_rn(p[k], __dmul_rn(K.p.coeffShifting2, gw));
+		}
+		if (inner) {
+			double4 pn = s.pi; pn.x = p[0]; pn.y = p[1]; pn.z = p[2]; S.pos2[s.i] = pn;
+			track_disp(S, K, s.i, pn);
+		}
+	}
+};
+
+// ------------------------------------------------------------------------------------------------ particle walls
+// MpsPressure::extrapolatePressParticlesWallDummy, src/MpsPressure.cpp:792-846.  Only non-fluid i are written and
+// only fluid j are read, so the in-place update has no read/write hazard.
+struct BExtrapolatePress {
+	struct Ctx { double ni, pr; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		c.ni = c.pr = 0.0;
+		return s.type == K.p.dummyWall || (K.p.mpsType == 1 && s.type == K.p.wall);
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!(q.d2 < K.p.reS2 && pk_type(q.pj) == K.p.fluid)) return;
+		const double w = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType); c.ni += w;
+		c.pr += (S.press[q.j] - S.RHO[q.j] * (K.p.gravityX * q.rx + K.p.gravityY * q.ry + K.p.gravityZ * q.rz)) * w;
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.ni = gsum(c.ni, m); c.pr = gsum(c.pr, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (c.pr < 0.0) return;
+		S.press[s.i] = c.ni > 0 ? c.pr / c.ni : c.pr;
+	}
+};
+
+// MpsParticleVelPos::updateVelocityParticlesWallDummy, src/MpsParticleVelPos.cpp:100-158 (dummy i written, fluid j read)
+struct BWallDummyVel {
+	struct Ctx { double ni, ux, uy, uz; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		c.ni = c.ux = c.uy = c.uz = 0.0; return s.type == K.p.dummyWall;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!(q.d2 < K.p.reL2 && pk_type(q.pj) == K.p.fluid)) return;
+		const double w = wgt_r(q.rinv, q.d2, K.p.reL, K.invReL, K.p.weightType); const double4 vj = S.vel[q.j];
+		c.ni += w; c.ux += vj.x * w; c.uy += vj.y * w; c.uz += vj.z * w;
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.ni = gsum(c.ni, m); c.ux = gsum(c.ux, m); c.uy = gsum(c.uy, m); c.uz = gsum(c.uz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		double4 v = S.vel[s.i];
+		if (c.ni > K.p.epsilonZero) { v.x = 2.0 * 0.0 - c.ux / c.ni; v.y = 2.0 * 0.0 - c.uy / c.ni; v.z = 2.0 * 0.0 - c.uz / c.ni; }
+		else { v.x = 2.0 * 0.0 - c.ux; v.y = 2.0 * 0.0 - c.uy; v.z = 2.0 * 0.0 - c.uz; }
+		S.vel[s.i] = v;
+	}
+};

@@ -7,10 +7,10 @@ __global__ void k_debug_neighbors(const __grid_constant__ DevView S, const __gri
 	const int i = S.slotOfHost[hostI];
 	const double4 pi = S.pos[i];
 	const double mix = POLY ? S.mirrorParticlePos.x[i] : 0.0, miy = POLY ? S.mirrorParticlePos.y[i] : 0.0, miz = POLY ? S.mirrorParticlePos.z[i] : 0.0;
-	const uint32_t* L = S.list + (size_t)(i >> 5) * 32 * (size_t)S.listCap + (i & 31);
+	const uint32_t* L = S.list + (size_t)i * (size_t)S.listCap;
 	const int cnt = S.listCnt[i]; int n = 0;
 	for (int k = 0; k < cnt; k++) {
-		Pair q; q.j = (int)L[(size_t)k * 32]; q.pj = S.pos[q.j];
+		Pair q; q.j = (int)L[k]; q.pj = S.pos[q.j];
 		q.rx = q.pj.x - pi.x; q.ry = q.pj.y - pi.y; q.rz = q.pj.z - pi.z; q.d2 = sq3_exact(q.rx, q.ry, q.rz);
 		q.mx = q.pj.x - mix; q.my = q.pj.y - miy; q.mz = q.pj.z - miz; q.dm2 = POLY ? sq3_exact(q.mx, q.my, q.mz) : 0.0;
 		bool hit;

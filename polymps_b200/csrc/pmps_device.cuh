@@ -1,12 +1,17 @@
-// pmps_device.cuh — device helpers shared by every kernel: exact (non-contracted) predicate arithmetic, weight
-// functions, the wall-reflection algebra and the Verlet-list walker that replaces the reference's neighbour-loop
-// idiom (canonical instance reference src/MpsViscosity.cpp:22-78).
+// pmps_device.cuh — device helpers shared by every kernel: exact (non-contracted) predicate arithmetic, fast
+// reciprocal / reciprocal-square-root for the weighted sums, the wall-reflection algebra and the Verlet-list walker
+// that replaces the reference's neighbour-loop idiom (canonical instance src/MpsViscosity.cpp:22-78).
+//
+// Arithmetic policy:
+//   * everything a PREDICATE depends on — squared distances, bucket ids, mirror positions, table look-ups, the
+//     position/velocity integrators — is written with __dmul_rn/__dadd_rn/... in the reference's evaluation order, so
+//     neighbour sets, bucket assignment and integer outputs match the reference bit for bit;
+//   * the weighted SUMS may contract to FMA and use 1-ulp reciprocals instead of IEEE division: their results agree
+//     with the reference to ~1e-15 relative, five orders inside the 1e-10 contract, at a third of the FP64 issue slots.
 #pragma once
 #include "pmps_internal.h"
 
-// ---- exact arithmetic for everything a PREDICATE depends on ---------------------------------------------------
-// The reference is built for baseline x86-64 (no FMA); neighbour sets, bucket ids and table look-ups must match it
-// bit for bit, so these never contract.
+// ---- exact arithmetic -------------------------------------------------------------------------------------------
 __device__ __forceinline__ double sq3_exact(double x, double y, double z) {   // (x*x + y*y) + z*z, src/MpsParticle.cpp:35-45
 	return __dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z));
 }
@@ -16,12 +21,39 @@ __device__ __forceinline__ double dot3_exact(double ax, double ay, double az, do
 __device__ __forceinline__ int bucket_coord(double x, double mn, double inv, double eps) {   // src/MpsBucket.cpp:420-425
 	return (int)__dadd_rn(__dmul_rn(__dsub_rn(x, mn), inv), eps);
 }
+__device__ __forceinline__ double madd_exact(double a, double b, double c) { return __dadd_rn(c, __dmul_rn(a, b)); }   // c + a*b, two roundings
+
+// ---- fast 1-ulp reciprocals (MUFU seed + two Newton steps; no special-case handling: arguments are finite, > 0) ----
+__device__ __forceinline__ double fast_rsqrt(double x) {
+	double y; asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+	const double h = 0.5 * x;
+	double e = fma(-h * y, y, 0.5); y = fma(y, e, y);
+	e = fma(-h * y, y, 0.5); y = fma(y, e, y);
+	return y;
+}
+__device__ __forceinline__ double fast_rcp(double x) {
+	double y; asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+	double e = fma(-x, y, 1.0); y = fma(y, e, y);
+	e = fma(-x, y, 1.0); y = fma(y, e, y);
+	return y;
+}
 
 __device__ __forceinline__ int pk_type(const double4& p) { return (int)(uint32_t)(__double_as_longlong(p.w) & 0xffffffffll); }
 __device__ __forceinline__ int pk_ptype(const double4& p) { return (int)(__double_as_longlong(p.w) >> 32); }
 __device__ __forceinline__ double pk_make(int type, int ptype) { return __longlong_as_double(((long long)ptype << 32) | (long long)(uint32_t)type); }
 
-// weight functions, src/MpsParticle.cpp:57-108
+// weight functions, src/MpsParticle.cpp:57-108, from the reciprocal distance: r = d2 * rinv
+__device__ __forceinline__ double wgt_r(double rinv, double d2, double re, double invRe, int type) {
+	if (type == 0) return re * rinv - 1.0;
+	const double q = d2 * rinv * invRe;   // r / re
+	switch (type) {
+		case 1: return re * rinv + q - 2.0;
+		case 2: return re * rinv - q;
+		case 3: return (1.0 - q) * (1.0 - q) * (1.0 - q);
+		default: return (1.0 - q) * (1.0 - q);
+	}
+}
+// IEEE form (used by the rare self / wall terms and the PPE assembly)
 __device__ __forceinline__ double wgt(double r, double re, int type) {
 	switch (type) {
 		case 1: return re / r + r / re - 2.0;
@@ -32,72 +64,120 @@ __device__ __forceinline__ double wgt(double r, double re, int type) {
 	}
 }
 
-// unit normal particle->wall = half of (x_i - mirror_i), reflection R = I - 2 n n^T (e.g. src/MpsPndNeigh.cpp:114-136)
-struct WallFrame { double n[3]; double R[9]; double len; };
-__device__ __forceinline__ void wall_frame(WallFrame& f, double xi, double yi, double zi, double mx, double my, double mz, double eps, bool squaredTest) {
-	f.n[0] = 0.5 * (xi - mx); f.n[1] = 0.5 * (yi - my); f.n[2] = 0.5 * (zi - mz);
-	const double n2 = f.n[0] * f.n[0] + f.n[1] * f.n[1] + f.n[2] * f.n[2];
-	f.len = sqrt(n2);
-	if ((squaredTest ? n2 : f.len) > eps) { f.n[0] = f.n[0] / f.len; f.n[1] = f.n[1] / f.len; f.n[2] = f.n[2] / f.len; }
-	else { f.n[0] = f.n[1] = f.n[2] = 0.0; }
-	f.R[0] = 1.0 - 2.0 * f.n[0] * f.n[0]; f.R[1] = 0.0 - 2.0 * f.n[0] * f.n[1]; f.R[2] = 0.0 - 2.0 * f.n[0] * f.n[2];
-	f.R[3] = 0.0 - 2.0 * f.n[1] * f.n[0]; f.R[4] = 1.0 - 2.0 * f.n[1] * f.n[1]; f.R[5] = 0.0 - 2.0 * f.n[1] * f.n[2];
-	f.R[6] = 0.0 - 2.0 * f.n[2] * f.n[0]; f.R[7] = 0.0 - 2.0 * f.n[2] * f.n[1]; f.R[8] = 1.0 - 2.0 * f.n[2] * f.n[2];
-}
 #define MATVEC(R, a, b, c, k) ((R)[3 * (k)] * (a) + (R)[3 * (k) + 1] * (b) + (R)[3 * (k) + 2] * (c))
 
+__device__ __forceinline__ void atomic_max_f(float* addr, float v) {   // v >= 0: int order == float order
+	if (v > *addr) atomicMax((int*)addr, __float_as_int(v));
+}
+__device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, int i, const double4& p) {
+	const float4 b = S.bpos[i];
+	const float dx = (float)(p.x - K.p.domainMinX) - b.x, dy = (float)(p.y - K.p.domainMinY) - b.y, dz = (float)(p.z - K.p.domainMinZ) - b.z;
+	atomic_max_f(S.maxDisp2, dx * dx + dy * dy + dz * dz);
+}
+
+// ---- lane groups --------------------------------------------------------------------------------------------------
+#define WG 8   // lanes per particle in the list walker
+__device__ __forceinline__ double gsum(double v, unsigned m) {
+	#pragma unroll
+	for (int o = WG / 2; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
+	return v;
+}
+__device__ __forceinline__ int gsum(int v, unsigned m) {
+	#pragma unroll
+	for (int o = WG / 2; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
+	return v;
+}
+__device__ __forceinline__ double gmin(double v, unsigned m) {
+	#pragma unroll
+	for (int o = WG / 2; o > 0; o >>= 1) { const double t = __shfl_xor_sync(m, v, o); v = t < v ? t : v; }
+	return v;
+}
+// one 32-byte record with a single 256-bit load (LDG.E.256 on sm_100a)
+__device__ __forceinline__ double4 ld256(const double4* p) {
+	double4 r;
+	asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+	return r;
+}
+
+// ---- per-particle prologue shared by the fused bodies --------------------------------------------------------------
+struct Self {
+	int i; bool lead; double4 pi; int type, ptype;   // lead: first lane of the particle's group (does the side effects)
+	double mix, miy, miz;       // mirror position of i
+	// wall frame of a near-wall fluid particle: unit normal n = (x_i - mirror_i)/|.|, reflection R = I - 2 n n^T,
+	// len = |x_i - mirror_i| / 2 (e.g. src/MpsPndNeigh.cpp:114-136); filled only when nearWallFluid
+	bool nearWallFluid;
+	double wn[3], wR[9], wlen, wn2;
+};
+__device__ __forceinline__ void self_wall_frame(Self& s) {
+	const double a = 0.5 * (s.pi.x - s.mix), b = 0.5 * (s.pi.y - s.miy), c = 0.5 * (s.pi.z - s.miz);
+	s.wn2 = a * a + b * b + c * c; s.wlen = sqrt(s.wn2);
+	s.wn[0] = a / s.wlen; s.wn[1] = b / s.wlen; s.wn[2] = c / s.wlen;
+	s.wR[0] = 1.0 - 2.0 * s.wn[0] * s.wn[0]; s.wR[1] = 0.0 - 2.0 * s.wn[0] * s.wn[1]; s.wR[2] = 0.0 - 2.0 * s.wn[0] * s.wn[2];
+	s.wR[3] = 0.0 - 2.0 * s.wn[1] * s.wn[0]; s.wR[4] = 1.0 - 2.0 * s.wn[1] * s.wn[1]; s.wR[5] = 0.0 - 2.0 * s.wn[1] * s.wn[2];
+	s.wR[6] = 0.0 - 2.0 * s.wn[2] * s.wn[0]; s.wR[7] = 0.0 - 2.0 * s.wn[2] * s.wn[1]; s.wR[8] = 1.0 - 2.0 * s.wn[2] * s.wn[2];
+}
+// The reference zeroes the normal when the particle sits on the wall; two variants of the test exist: on |n|
+// (calcWallNPCD, wall gradient, wall shifting) and on |n|^2 (wall viscosity, wall diffusive term).
+struct WallFrame { double n[3]; double R[9]; double len; };
+__device__ __forceinline__ void wall_frame_of(WallFrame& f, const Self& s, double eps, bool squaredTest) {
+	f.len = s.wlen;
+	if ((squaredTest ? s.wn2 : s.wlen) > eps) {
+		for (int k = 0; k < 3; k++) f.n[k] = s.wn[k];
+		for (int k = 0; k < 9; k++) f.R[k] = s.wR[k];
+	} else {
+		f.n[0] = f.n[1] = f.n[2] = 0.0;
+		for (int k = 0; k < 9; k++) f.R[k] = (k % 4 == 0) ? 1.0 : 0.0;
+	}
+}
 // mirror velocity of a near-wall particle (src/MpsViscosity.cpp:1729-1752 no-slip, :1565-1590 free-slip)
 __device__ __forceinline__ void mirror_velocity(const KParams& K, int nearMeshType, const WallFrame& f, const double v[3], double vm[3]) {
 	double vw[3] = { 0.0, 0.0, 0.0 };
 	if (nearMeshType == 2) { vw[0] = K.p.uniformVelWall[0]; vw[1] = K.p.uniformVelWall[1]; vw[2] = K.p.uniformVelWall[2]; }
 	const double dn = f.n[0] * vw[0] + f.n[1] * vw[1] + f.n[2] * vw[2];
 	if (K.p.slipCondition == 0) {
-		double t[3];
-		for (int k = 0; k < 3; k++) t[k] = v[k] - 2.0 * (vw[k] - dn * f.n[k]);
-		vm[0] = (-1.0 * t[0] + 0.0 * t[1] + 0.0 * t[2]); vm[1] = (0.0 * t[0] + -1.0 * t[1] + 0.0 * t[2]); vm[2] = (0.0 * t[0] + 0.0 * t[1] + -1.0 * t[2]);
+		for (int k = 0; k < 3; k++) vm[k] = -(v[k] - 2.0 * (vw[k] - dn * f.n[k]));
 	} else {
 		for (int k = 0; k < 3; k++) vm[k] = MATVEC(f.R, v[0], v[1], v[2], k);
 	}
 }
 
-__device__ __forceinline__ void atomic_max_f(float* addr, float v) {   // v >= 0: int order == float order
-	if (v > *addr) atomicMax((int*)addr, __float_as_int(v));
-}
-
-// ---- the pair geometry handed to every stage body ---------------------------------------------------------------
+// ---- the pair geometry handed to every stage body ------------------------------------------------------------------
 struct Pair {
 	int j; double4 pj;
-	double rx, ry, rz, d2;      // r_ij = x_j - x_i
-	double mx, my, mz, dm2;     // x_j - mirror_i (polygon walls only)
-};
-
-// Per-particle prologue data shared by fused bodies
-struct Self {
-	int i; double4 pi; int type, ptype;
-	double mix, miy, miz;       // mirror position of i
+	double rx, ry, rz, d2;      // r_ij = x_j - x_i ; d2 exact
+	double rinv;                // 1/|r_ij| (1 ulp)
+	double mx, my, mz, dm2;     // x_j - mirror_i (polygon walls only) ; dm2 exact
 };
 
 // predicates: P(re) real neighbour, M(re) mirror neighbourhood
 template <bool POLY> __device__ __forceinline__ bool pred_P(const Pair& q, double re2) { return q.d2 < re2 && (!POLY || q.d2 < q.dm2); }
 __device__ __forceinline__ bool pred_M(const Pair& q, double re2) { return q.d2 < re2 && q.dm2 < re2 && q.d2 < q.dm2; }
 
-// Walk the Verlet candidates of slot i.  Bodies... is a pack of stage bodies fused into one pass; each has
-//   struct Ctx;  static bool begin(Ctx&, S, K, self)  -> false: body inactive for this i
-//   static void pair<POLY>(Ctx&, S, K, self, const Pair&)
-//   static void end(Ctx&, S, K, self)
+// ---- body packs --------------------------------------------------------------------------------------------------
+// A body has  struct Ctx;  static bool begin(Ctx&, S, K, self) (false: inactive for this i);
+// template<bool POLY> static void pair(Ctx&, S, K, self, const Pair&);  static void end(Ctx&, S, K, self).
+// Tags:  copy_pos_tag / copy_vel_tag — the body writes pos2 / vel2 in end() (Jacobi-style update of the ping-pong
+// buffer); the walker mirrors pos -> pos2 / vel -> vel2 first so skipped slots stay valid.
 template <class B, class = void> struct CopiesPos { static constexpr bool value = false; };
 template <class B> struct CopiesPos<B, typename B::copy_pos_tag> { static constexpr bool value = true; };
+template <class B, class = void> struct CopiesVel { static constexpr bool value = false; };
+template <class B> struct CopiesVel<B, typename B::copy_vel_tag> { static constexpr bool value = true; };
+template <class B, class = void> struct NeedsWall { static constexpr bool value = false; };
+template <class B> struct NeedsWall<B, typename B::wall_frame_tag> { static constexpr bool value = true; };
 
 template <class... Bodies> struct Fused;
 template <> struct Fused<> {
-	static constexpr bool kCopyPos = false;
+	static constexpr bool kCopyPos = false, kCopyVel = false, kWall = false;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams&, const Self&) { return false; }
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
+	__device__ __forceinline__ static void reduce(Ctx&, unsigned) {}
 	__device__ __forceinline__ static void end(Ctx&, const DevView&, const KParams&, const Self&) {}
 };
 template <class B, class... Rest> struct Fused<B, Rest...> {
 	static constexpr bool kCopyPos = CopiesPos<B>::value || Fused<Rest...>::kCopyPos;
+	static constexpr bool kCopyVel = CopiesVel<B>::value || Fused<Rest...>::kCopyVel;
+	static constexpr bool kWall = NeedsWall<B>::value || Fused<Rest...>::kWall;
 	struct Ctx { typename B::Ctx c; bool on; typename Fused<Rest...>::Ctx r; };
 	__device__ __forceinline__ static bool begin(Ctx& x, const DevView& S, const KParams& K, const Self& s) {
 		x.on = B::begin(x.c, S, K, s);
@@ -108,33 +188,53 @@ template <class B, class... Rest> struct Fused<B, Rest...> {
 		if (x.on) B::template pair<POLY>(x.c, S, K, s, q);
 		Fused<Rest...>::template pair<POLY>(x.r, S, K, s, q);
 	}
+	__device__ __forceinline__ static void reduce(Ctx& x, unsigned m) {
+		if (x.on) B::reduce(x.c, m);   // x.on is uniform over the lanes of a group
+		Fused<Rest...>::reduce(x.r, m);
+	}
 	__device__ __forceinline__ static void end(Ctx& x, const DevView& S, const KParams& K, const Self& s) {
 		if (x.on) B::end(x.c, S, K, s);
 		Fused<Rest...>::end(x.r, S, K, s);
 	}
 };
 
+// Walk the Verlet candidates of slot i with a GROUP of WG lanes: lane g takes candidates g, g+WG, ... of the (row-major)
+// list, so the lanes of a group gather ADJACENT slots — a handful of cache lines per load instruction instead of one
+// line per lane — and the partial sums are combined with warp shuffles before end() runs on the group's first lane.
+// Candidates farther than the largest cut-off are dropped before any body sees them (every predicate of the reference
+// implies d2 < max(reS,reL)^2); the mirror distance and the reciprocal distance are computed only for the survivors.
 template <bool POLY, class F>
 __global__ void __launch_bounds__(128) k_walk(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
-	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	const int i = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) / WG);
+	const int gl = threadIdx.x & (WG - 1);
 	if (i >= S.n) return;
-	Self s; s.i = i; s.pi = S.pos[i]; s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
-	if (F::kCopyPos) S.pos2[i] = s.pi;   // Jacobi position update: bodies overwrite pos2[i] in end()
+	const unsigned gmask = (WG == 32 ? 0xffffffffu : ((1u << WG) - 1u)) << ((threadIdx.x & 31) & ~(WG - 1));
+	Self s; s.i = i; s.lead = gl == 0; s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
+	if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
+	if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
 	if (s.type == K.p.ghost) return;
+	s.nearWallFluid = false;
 	if (POLY) { s.mix = S.mirrorParticlePos.x[i]; s.miy = S.mirrorParticlePos.y[i]; s.miz = S.mirrorParticlePos.z[i]; }
 	else { s.mix = s.miy = s.miz = 0.0; }
+	if (POLY && F::kWall) {
+		s.nearWallFluid = s.type == K.p.fluid && S.particleNearWall[i];
+		if (s.nearWallFluid) self_wall_frame(s);
+	}
 	typename F::Ctx ctx;
 	if (!F::begin(ctx, S, K, s)) return;
-	const uint32_t* L = S.list + (size_t)(i >> 5) * 32 * (size_t)S.listCap + (i & 31);
+	const uint32_t* L = S.list + (size_t)i * (size_t)S.listCap;
 	const int cnt = S.listCnt[i];
-	for (int k = 0; k < cnt; k++) {
-		Pair q; q.j = (int)L[(size_t)k * 32];
-		q.pj = S.pos[q.j];
+	for (int k = gl; k < cnt; k += WG) {
+		Pair q; q.j = (int)L[k];
+		q.pj = ld256(S.pos + q.j);
 		q.rx = q.pj.x - s.pi.x; q.ry = q.pj.y - s.pi.y; q.rz = q.pj.z - s.pi.z;
 		q.d2 = sq3_exact(q.rx, q.ry, q.rz);
+		if (!(q.d2 < K.reMax2)) continue;
 		if (POLY) { q.mx = q.pj.x - s.mix; q.my = q.pj.y - s.miy; q.mz = q.pj.z - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
 		else { q.mx = q.my = q.mz = 0.0; q.dm2 = 0.0; }
+		q.rinv = fast_rsqrt(q.d2);
 		F::template pair<POLY>(ctx, S, K, s, q);
 	}
-	F::end(ctx, S, K, s);
+	F::reduce(ctx, gmask);
+	if (s.lead) F::end(ctx, S, K, s);
 }

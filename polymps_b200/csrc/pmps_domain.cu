@@ -50,9 +50,9 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 		// the moved particle keeps searching around ITS position: give slot si the candidate list of slot sl
 		S.bpos[si] = S.bpos[sl]; S.listCnt[si] = S.listCnt[sl];
 		{
-			uint32_t* Li = S.list + (size_t)(si >> 5) * 32 * (size_t)S.listCap + (si & 31);
-			const uint32_t* Ll = S.list + (size_t)(sl >> 5) * 32 * (size_t)S.listCap + (sl & 31);
-			for (int k = 0; k < S.listCnt[sl]; k++) Li[(size_t)k * 32] = Ll[(size_t)k * 32];
+			uint32_t* Li = S.list + (size_t)si * (size_t)S.listCap;
+			const uint32_t* Ll = S.list + (size_t)sl * (size_t)S.listCap;
+			for (int k = 0; k < S.listCnt[sl]; k++) Li[k] = Ll[k];
 		}
 		double4 g; g.x = K.p.domainMaxX - K.p.partDist; g.y = K.p.domainMaxY - K.p.partDist;
 		g.z = K.p.dim == 2 ? 0.0 : K.p.domainMaxZ - K.p.partDist; g.w = pk_make(K.p.ghost, pk_ptype(S.pos[sl]));

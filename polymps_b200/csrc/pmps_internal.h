@@ -53,6 +53,7 @@ struct DevView {
 	float* maxDisp2;                     // max squared displacement since the list build (float, >= 0)
 	int32_t* flags;                      // [0] list overflow, [1] out-of-domain count, [2] guard violated, [3] live count
 	int32_t* oodList;                    // host ids flagged by the out-of-domain test
+	const struct DevMesh* meshes; int32_t nMeshes;   // polygon meshes (device array), set by pmps_set_mesh
 };
 
 enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, NFLAGS = 8 };
@@ -67,6 +68,8 @@ struct KParams {
 	float rl2;           // (list radius)^2 incl. float margin
 	float guard2;        // (allowed displacement)^2
 	int32_t poly;        // wallType == polygon
+	double reMax2;       // max(reS, reL)^2: no predicate of the reference reaches farther
+	double invReS, invReL;
 };
 
 #define MAX_TRI_CONST 64

@@ -36,11 +36,11 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ 
 	const bool colOK = bci == K.p.inner && ti != K.p.dummyWall;
 	const double mix = POLY ? S.mirrorParticlePos.x[i] : 0.0, miy = POLY ? S.mirrorParticlePos.y[i] : 0.0, miz = POLY ? S.mirrorParticlePos.z[i] : 0.0;
 	const size_t base = (size_t)(i >> 5) * 32 * (size_t)S.listCap + (i & 31);
-	const uint32_t* L = S.list + base; uint32_t* C = M.col + base; double* V = M.val + base;
+	const uint32_t* L = S.list + (size_t)i * (size_t)S.listCap; uint32_t* C = M.col + base; double* V = M.val + base;
 	const int cnt = S.listCnt[i];
 	double sum = 0.0, b = 0.0; int nz = 0;
 	for (int k = 0; k < cnt; k++) {
-		const int j = (int)L[(size_t)k * 32];
+		const int j = (int)L[k];
 		const double4 pj = S.pos[j];
 		const double rx = pj.x - pi.x, ry = pj.y - pi.y, rz = pj.z - pi.z; const double d2 = sq3_exact(rx, ry, rz);
 		if (!(d2 < K.p.reL2)) continue;

@@ -136,32 +136,43 @@ __global__ void k_permute_packs(const int32_t* __restrict__ perm, const __grid_c
 }
 
 // ---- 6. Verlet candidate list -----------------------------------------------------------------------------------
-// One thread per slot; candidates are emitted bucket row by bucket row (jz, jy outer; the three x-adjacent buckets of
-// a row are one contiguous slot range), slots ascending = the reference's traversal order restricted to the list.
+// One WARP per slot: the lanes test 32 consecutive slots of a bucket row at a time (coalesced float4 loads) and the
+// survivors are compacted in order with a ballot, so candidates are emitted bucket row by bucket row (jz, jy outer;
+// the three x-adjacent buckets of a row are one contiguous slot range), slots ascending = the reference's traversal
+// order restricted to the list.  Row-major list: candidate k of slot i at list[i*cap + k].
 __global__ void __launch_bounds__(128) k_build_list(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
-	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	const int i = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+	const int lane = threadIdx.x & 31;
 	if (i >= S.n0) return;
 	const int c = S.cellOf[i];
-	if (c >= S.nB) { S.listCnt[i] = 0; return; }   // ghost
+	if (c >= S.nB) { if (lane == 0) S.listCnt[i] = 0; return; }   // ghost
 	const int nX = K.p.numBucketsX, nY = K.p.numBucketsY, nZ = K.p.numBucketsZ, nXY = nX * nY;
 	const int cz = c / nXY, cy = (c - cz * nXY) / nX, cx = c - cz * nXY - cy * nX;
 	const float4 bi = S.bpos[i];
-	uint32_t* L = S.list + (size_t)(i >> 5) * 32 * (size_t)S.listCap + (i & 31);
+	uint32_t* L = S.list + (size_t)i * (size_t)S.listCap;
 	int cnt = 0; const int cap = S.listCap;
 	const int z0 = K.p.dim == 3 ? max(cz - 1, 0) : 0, z1 = K.p.dim == 3 ? min(cz + 1, nZ - 1) : 0;
 	const int y0 = max(cy - 1, 0), y1 = min(cy + 1, nY - 1), x0 = max(cx - 1, 0), x1 = min(cx + 1, nX - 1);
+	const unsigned below = (1u << lane) - 1u;
 	for (int jz = z0; jz <= z1; jz++) for (int jy = y0; jy <= y1; jy++) {
 		const int row = jz * nXY + jy * nX;
 		const int s0 = S.cellStart[row + x0], s1 = S.cellStart[row + x1 + 1];
-		for (int j = s0; j < s1; j++) {
-			const float4 bj = S.bpos[j];
-			const float dx = bj.x - bi.x, dy = bj.y - bi.y, dz = bj.z - bi.z;
-			const float d2 = dx * dx + dy * dy + dz * dz;
-			if (d2 < K.rl2 && j != i) { if (cnt < cap) L[(size_t)cnt * 32] = (uint32_t)j; cnt++; }
+		for (int base = s0; base < s1; base += 32) {
+			const int j = base + lane; bool hit = false;
+			if (j < s1) {
+				const float4 bj = S.bpos[j];
+				const float dx = bj.x - bi.x, dy = bj.y - bi.y, dz = bj.z - bi.z;
+				hit = dx * dx + dy * dy + dz * dz < K.rl2 && j != i;
+			}
+			const unsigned b = __ballot_sync(0xffffffffu, hit);
+			if (hit) { const int at = cnt + __popc(b & below); if (at < cap) L[at] = (uint32_t)j; }
+			cnt += __popc(b);
 		}
 	}
-	if (cnt > cap) { atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = cap; }
-	S.listCnt[i] = (uint16_t)cnt;
+	if (lane == 0) {
+		if (cnt > cap) { atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = cap; }
+		S.listCnt[i] = (uint16_t)cnt;
+	}
 }
 
 __global__ void k_reset_step_scalars(const __grid_constant__ DevView S) {
@@ -211,7 +222,7 @@ int pmps_sort_and_list(pmps_handle* h) {
 		PMPS_I32_FIELDS(X)
 #undef X
 	}
-	LAUNCH(h, "list.build", k_build_list, cdiv(n0, 128), 128, S, K);
+	LAUNCH(h, "list.build", k_build_list, cdiv((long long)n0 * 32, 128), 128, S, K);
 	CUDA_TRY(h, cudaGetLastError());
 	h->haveList = true;
 	return PMPS_OK;

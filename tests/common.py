@@ -66,10 +66,20 @@ def state_from(d) -> HostState:
     return HostState.from_dump(d)
 
 
-def compare_states(got: HostState, want, rtol=0.0, fields=None, skip=(), live_only=True, sign_fields_tol=1e-12):
-    """List of (field, n_bad, max_abs_err, max_rel_err) for every field that differs by more than rtol * max|want|.
-    rtol=0 means bit-identical.  `want` is a HostState or a dump dict."""
+def natural_scales(ps):
+    """Magnitudes below which a field is rounding noise of the formula that produces it (used as the floor of the
+    relative comparison).  The weakly-compressible equation of state is stiff: p = rho c0^2/gamma ((n/n0)^gamma - 1), so a
+    1e-16 relative change of n moves p by rho c0^2 * 1e-16 however small p itself is; accelerations inherit it through
+    grad p / rho ~ p / (rho lo)."""
+    p0 = ps.DNS_FL1 * ps.soundSpeed ** 2 / ps.gamma
+    return {"press": p0, "pressurePPE": p0, "acc": p0 / (ps.DNS_FL1 * ps.partDist), "accStar": p0 / (ps.DNS_FL1 * ps.partDist)}
+
+
+def compare_states(got: HostState, want, rtol=0.0, fields=None, skip=(), live_only=True, scales=None):
+    """List of (field, n_bad, max_abs_err, max_rel_err) for every field that differs by more than
+    rtol * max(max|want|, scales[field]).  rtol=0 means bit-identical.  `want` is a HostState or a dump dict."""
     bad = []
+    scales = scales or {}
     n = got.numParticles
     for f in (fields or ALL_FIELDS):
         if f in SKIP_FIELDS or f in skip:
@@ -90,7 +100,7 @@ def compare_states(got: HostState, want, rtol=0.0, fields=None, skip=(), live_on
             err = np.abs(x - y)
         if not np.all(np.isfinite(x) == np.isfinite(y)):
             bad.append((f, -1, float("nan"), float("nan"))); continue
-        scale = max(float(np.abs(y[np.isfinite(y)]).max()) if y.size else 0.0, 1e-300)
+        scale = max(float(np.abs(y[np.isfinite(y)]).max()) if y.size else 0.0, float(scales.get(f, 0.0)), 1e-300)
         e = float(np.nanmax(err)) if err.size else 0.0
         if e <= rtol * scale:
             continue

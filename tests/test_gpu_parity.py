@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from common import (GOLDEN, STAGE_MAP, SHIFTING_STAGES, golden, stage_sequence, dumped_steps, state_from, compare_states,
-                    neighbor_sets_equal)
+                    neighbor_sets_equal, natural_scales)
 from polymps_b200 import cases
 from polymps_b200.params import ParticleSystem
 from polymps_b200.mesh import PolygonMesh
@@ -68,7 +68,7 @@ def test_stage_by_stage_against_reference_dumps(name):
             else:
                 want = state_from(cur)
             assert got.numParticles == want.numParticles
-            bad = compare_states(got, want, rtol=RTOL, skip=NOISY)
+            bad = compare_states(got, want, rtol=RTOL, skip=NOISY, scales=natural_scales(ps))
             assert not bad, "%s step %d stage %s: %s" % (name, step, stage, bad)
             _check_noisy_sign(got, want)
             if stage == "correctionVelocityPosition":
@@ -133,12 +133,12 @@ def test_whole_steps_against_oracle(kind):
     eng = _engine(ps, meshes, st0.numParticlesZero)
     eng.upload(st0); eng.init_step0()
     got = st0.copy(); eng.download(got)
-    bad = compare_states(got, want, rtol=RTOL, skip=NOISY)
+    bad = compare_states(got, want, rtol=RTOL, skip=NOISY, scales=natural_scales(ps))
     assert not bad, "step 0: %s" % bad
     for k in range(1, 4):
         orc.step(1); eng.step(1)
         eng.download(got)
-        bad = compare_states(got, want, rtol=RTOL * 10 ** (k - 1), skip=NOISY)
+        bad = compare_states(got, want, rtol=RTOL * 10 ** (k - 1), skip=NOISY, scales=natural_scales(ps))
         assert not bad, "step %d: %s" % (k, bad)
         s = eng.scalars()
         assert abs(s.velMax - orc.P.velMax) <= 1e-9 * max(orc.P.velMax, 1e-30)
