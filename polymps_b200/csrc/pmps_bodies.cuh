@@ -54,7 +54,7 @@ __device__ __forceinline__ void predict_resets(const DevView& S, const KParams& 
 // acceleration BViscosity::end just stored, writes the NEW position/velocity to the alternate buffers (neighbours are
 // still reading the old ones in this launch).
 struct BPredictTail {
-	typedef void copy_pos_tag; typedef void copy_vel_tag;
+	typedef void copy_pos_tag; typedef void copy_vel_tag; typedef void no_pair_tag;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams&, const Self&) { return true; }
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
@@ -143,7 +143,7 @@ struct BCollision {
 };
 // fused tail: second loop of checkParticleCollisions (:108-116), vel2 = vel + dvel (neighbours still read vel)
 struct BCollisionTail {
-	typedef void copy_vel_tag;
+	typedef void copy_vel_tag; typedef void no_pair_tag;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams& K, const Self& s) { return s.type == K.p.fluid; }
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}

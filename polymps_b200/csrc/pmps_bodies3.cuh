@@ -115,7 +115,7 @@ struct BWallPressGradient {
 // fused tail of the gradient pass: correctionVelocityPosition (src/MpsParticleVelPos.cpp:53-97).  Reads the acceleration
 // the bodies in front of it stored, writes the new position / velocity to the alternate buffers, feeds velMax.
 struct BCorrectTail {
-	typedef void copy_pos_tag; typedef void copy_vel_tag;
+	typedef void copy_pos_tag; typedef void copy_vel_tag; typedef void no_pair_tag;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams& K, const Self& s) { return s.type == K.p.fluid; }
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}

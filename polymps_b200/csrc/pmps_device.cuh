@@ -95,7 +95,7 @@ __device__ __forceinline__ double gmin(double v, unsigned m) {
 // one 32-byte record with a single 256-bit load (LDG.E.256 on sm_100a)
 __device__ __forceinline__ double4 ld256(const double4* p) {
 	double4 r;
-	asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+	asm("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
 	return r;
 }
 
@@ -162,6 +162,8 @@ template <class B, class = void> struct CopiesPos { static constexpr bool value 
 template <class B> struct CopiesPos<B, typename B::copy_pos_tag> { static constexpr bool value = true; };
 template <class B, class = void> struct CopiesVel { static constexpr bool value = false; };
 template <class B> struct CopiesVel<B, typename B::copy_vel_tag> { static constexpr bool value = true; };
+template <class B, class = void> struct NoPairs { static constexpr bool value = false; };
+template <class B> struct NoPairs<B, typename B::no_pair_tag> { static constexpr bool value = true; };   // tail bodies: begin/end only
 template <class B, class = void> struct NeedsWall { static constexpr bool value = false; };
 template <class B> struct NeedsWall<B, typename B::wall_frame_tag> { static constexpr bool value = true; };
 
@@ -170,6 +172,7 @@ template <> struct Fused<> {
 	static constexpr bool kCopyPos = false, kCopyVel = false, kWall = false;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams&, const Self&) { return false; }
+	__device__ __forceinline__ static bool need_pairs(const Ctx&) { return false; }
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
 	__device__ __forceinline__ static void reduce(Ctx&, unsigned) {}
 	__device__ __forceinline__ static void end(Ctx&, const DevView&, const KParams&, const Self&) {}
@@ -184,8 +187,9 @@ template <class B, class... Rest> struct Fused<B, Rest...> {
 		const bool o = Fused<Rest...>::begin(x.r, S, K, s);
 		return x.on || o;
 	}
+	__device__ __forceinline__ static bool need_pairs(const Ctx& x) { return (x.on && !NoPairs<B>::value) || Fused<Rest...>::need_pairs(x.r); }
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& x, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
-		if (x.on) B::template pair<POLY>(x.c, S, K, s, q);
+		if (!NoPairs<B>::value) { if (x.on) B::template pair<POLY>(x.c, S, K, s, q); }
 		Fused<Rest...>::template pair<POLY>(x.r, S, K, s, q);
 	}
 	__device__ __forceinline__ static void reduce(Ctx& x, unsigned m) {
@@ -203,6 +207,18 @@ template <class B, class... Rest> struct Fused<B, Rest...> {
 // line per lane — and the partial sums are combined with warp shuffles before end() runs on the group's first lane.
 // Candidates farther than the largest cut-off are dropped before any body sees them (every predicate of the reference
 // implies d2 < max(reS,reL)^2); the mirror distance and the reciprocal distance are computed only for the survivors.
+template <bool POLY, class F>
+__device__ __forceinline__ void walk_one(typename F::Ctx& ctx, const DevView& S, const KParams& K, const Self& s, int j, const double4& pj) {
+	Pair q; q.j = j; q.pj = pj;
+	q.rx = pj.x - s.pi.x; q.ry = pj.y - s.pi.y; q.rz = pj.z - s.pi.z;
+	q.d2 = sq3_exact(q.rx, q.ry, q.rz);
+	if (!(q.d2 < K.reMax2)) return;
+	if (POLY) { q.mx = pj.x - s.mix; q.my = pj.y - s.miy; q.mz = pj.z - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
+	else { q.mx = q.my = q.mz = 0.0; q.dm2 = 0.0; }
+	q.rinv = fast_rsqrt(q.d2);
+	F::template pair<POLY>(ctx, S, K, s, q);
+}
+
 template <bool POLY, class F>
 __global__ void __launch_bounds__(128) k_walk(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
 	const int i = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) / WG);
@@ -222,18 +238,18 @@ __global__ void __launch_bounds__(128) k_walk(const __grid_constant__ DevView S,
 	}
 	typename F::Ctx ctx;
 	if (!F::begin(ctx, S, K, s)) return;
-	const uint32_t* L = S.list + (size_t)i * (size_t)S.listCap;
-	const int cnt = S.listCnt[i];
-	for (int k = gl; k < cnt; k += WG) {
-		Pair q; q.j = (int)L[k];
-		q.pj = ld256(S.pos + q.j);
-		q.rx = q.pj.x - s.pi.x; q.ry = q.pj.y - s.pi.y; q.rz = q.pj.z - s.pi.z;
-		q.d2 = sq3_exact(q.rx, q.ry, q.rz);
-		if (!(q.d2 < K.reMax2)) continue;
-		if (POLY) { q.mx = q.pj.x - s.mix; q.my = q.pj.y - s.miy; q.mz = q.pj.z - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
-		else { q.mx = q.my = q.mz = 0.0; q.dm2 = 0.0; }
-		q.rinv = fast_rsqrt(q.d2);
-		F::template pair<POLY>(ctx, S, K, s, q);
+	if (F::need_pairs(ctx)) {
+		const uint32_t* L = S.list + (size_t)i * (size_t)S.listCap;
+		const int cnt = S.listCnt[i];
+		// two candidates per lane and trip: both list entries, then both position records, are requested before either is
+		// used, which doubles the loads in flight per warp (the walks are latency-bound: profiles/r01_ncu_walk_v3.txt)
+		for (int k = gl; k < cnt; k += 2 * WG) {
+			const bool two = k + WG < cnt;
+			const int j0 = (int)L[k]; const int j1 = two ? (int)L[k + WG] : j0;
+			const double4 p0 = ld256(S.pos + j0); const double4 p1 = ld256(S.pos + j1);
+			walk_one<POLY, F>(ctx, S, K, s, j0, p0);
+			if (two) walk_one<POLY, F>(ctx, S, K, s, j1, p1);
+		}
 	}
 	F::reduce(ctx, gmask);
 	if (s.lead) F::end(ctx, S, K, s);
