@@ -2,6 +2,7 @@
 // the stage/step drivers.  Neighbour stages are instantiations of the list walker (pmps_device.cuh) over the stage
 // bodies (pmps_bodies.cuh).  There is no CPU fallback anywhere: without a CUDA device pmps_create fails.
 #include "pmps_bodies.cuh"
+#include "pmps_tile.cuh"
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -242,6 +243,13 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	rc |= dalloc(h, &h->tmpHost, 2 * (size_t)n0);
 	h->nScanBlocks = cdiv((long long)S.nB + 2, 512 * 8) + 1;
 	rc |= dalloc(h, &h->scanBlock, h->nScanBlocks);
+	{	// tiles of the tile walker: TILE_CX consecutive buckets of one bucket row
+		const long long nXB = (P.numBucketsX + TILE_CX - 1) / TILE_CX;
+		const long long nt = nXB * P.numBucketsY * P.numBucketsZ;
+		h->nTilesAll = (int)nt;
+		rc |= dalloc(h, &S.tileList, (size_t)(nt < n0 ? nt : n0) + 1); rc |= dalloc(h, &S.nTiles, 1);
+		int sm = 148; cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device); h->smCount = sm;
+	}
 	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 1); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
 	// Verlet list: radius = bucketSide (the reference's own search slack, src/MpsBucket.cpp:23); capacity from the
 	// lattice count with head room (PMPS_LIST_CAP overrides)

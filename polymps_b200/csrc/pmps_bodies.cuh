@@ -22,7 +22,7 @@ struct BViscosity {
 		double nu = (c.mu + muj) > K.p.epsilonZero ? 2.0 * c.mu * muj * fast_rcp(c.mu + muj) : 0.0;
 		if (pk_type(q.pj) == K.p.wall) nu = 2.0 * c.mu;
 		const double f = w * nu * c.invRho;
-		const double4 vj = ld256(S.vel + q.j);
+		const double4 vj = S.vel[q.j];
 		c.sx += (vj.x - c.vx) * f; c.sy += (vj.y - c.vy) * f; c.sz += (vj.z - c.vz) * f;
 	}
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.sx = gsum(c.sx, m); c.sy = gsum(c.sy, m); c.sz = gsum(c.sz, m); }
@@ -91,7 +91,7 @@ struct BWallViscosity {
 		const double muj = S.MEU[q.j];
 		double nu = (c.mu + muj) > K.p.epsilonZero ? 2.0 * c.mu * muj * fast_rcp(c.mu + muj) : 0.0;
 		const double f = w * nu * c.invRhoDiv;
-		const double4 vj = ld256(S.vel + q.j);
+		const double4 vj = S.vel[q.j];
 		c.sx += (vj.x - c.vm[0]) * f; c.sy += (vj.y - c.vm[1]) * f; c.sz += (vj.z - c.vm[2]) * f;
 	}
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.sx = gsum(c.sx, m); c.sy = gsum(c.sy, m); c.sz = gsum(c.sz, m); }
@@ -126,7 +126,7 @@ struct BCollision {
 	}
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.distCollisionLimit2)) return;
-		const double4 vj = ld256(S.vel + q.j);
+		const double4 vj = S.vel[q.j];
 		double f = (c.vx - vj.x) * q.rx + (c.vy - vj.y) * q.ry + (c.vz - vj.z) * q.rz;
 		if (f > 0.0) {
 			const bool jf = pk_type(q.pj) == K.p.fluid;

@@ -108,7 +108,7 @@ struct BPndDiffusive {
 			c.Di += c.kDi * (S.press[q.j] - c.Pi - pgh) * wL;
 		}
 		if (q.d2 < K.p.reS2) {
-			const double4 vj = ld256(S.vel + q.j);
+			const double4 vj = S.vel[q.j];
 			const double ux = vj.x - c.vx, uy = vj.y - c.vy, uz = vj.z - c.vz;
 			const double wS = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType) * (q.rinv * q.rinv);   // w / d2
 			if (!K.p.gradientCorrection) c.div += S.pndi[q.j] * (ux * q.rx + uy * q.ry + uz * q.rz) * wS;   // * (dim/n0S)/ni in end()
@@ -149,7 +149,7 @@ struct BWallPndDiffusive {
 	}
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_M(q, K.p.reS2)) return;
-		const double4 vj = ld256(S.vel + q.j);
+		const double4 vj = S.vel[q.j];
 		c.div += term(c, K, s, vj.x, vj.y, vj.z, q.mx, q.my, q.mz, S.pndi[q.j], q.dm2);
 	}
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.div = gsum(c.div, m); }

@@ -26,6 +26,7 @@ extern "C" int pmps_debug_neighbors(pmps_t* h, int i, int kind, int32_t* out, in
 	if (!h || !out || cap < 0) return PMPS_E_ARG;
 	cudaSetDevice(h->device);
 	if (!h->haveList) return pmps_fail(h, PMPS_E_STATE, "pmps_debug_neighbors: call pmps_update_buckets first");
+	{ const int rc = pmps_ensure_list(h); if (rc) return rc; }
 	if (i < 0 || i >= h->numParticlesZero) return pmps_fail(h, PMPS_E_ARG, "pmps_debug_neighbors: index out of range");
 	int32_t* d = (int32_t*)h->stage; int32_t* dcount = d + cap;
 	if ((size_t)(cap + 1) * 4 > h->stageBytes) return pmps_fail(h, PMPS_E_ARG, "pmps_debug_neighbors: cap too large");

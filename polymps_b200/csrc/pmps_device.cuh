@@ -77,19 +77,20 @@ __device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, i
 
 // ---- lane groups --------------------------------------------------------------------------------------------------
 #define WG 8   // lanes per particle in the list walker
+#ifndef WALK_MIN_BLOCKS
+#define WALK_MIN_BLOCKS 8   // resident 128-thread blocks per SM the walker is compiled for (64 registers per thread)
+#endif
+// reductions over the lanes named in m: an aligned power-of-two group (8 in the list walker, 1..8 in the tile walker)
 __device__ __forceinline__ double gsum(double v, unsigned m) {
-	#pragma unroll
-	for (int o = WG / 2; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
+	for (int o = __popc(m) >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
 	return v;
 }
 __device__ __forceinline__ int gsum(int v, unsigned m) {
-	#pragma unroll
-	for (int o = WG / 2; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
+	for (int o = __popc(m) >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
 	return v;
 }
 __device__ __forceinline__ double gmin(double v, unsigned m) {
-	#pragma unroll
-	for (int o = WG / 2; o > 0; o >>= 1) { const double t = __shfl_xor_sync(m, v, o); v = t < v ? t : v; }
+	for (int o = __popc(m) >> 1; o > 0; o >>= 1) { const double t = __shfl_xor_sync(m, v, o); v = t < v ? t : v; }
 	return v;
 }
 // one 32-byte record with a single 256-bit load (LDG.E.256 on sm_100a)
@@ -220,7 +221,7 @@ __device__ __forceinline__ void walk_one(typename F::Ctx& ctx, const DevView& S,
 }
 
 template <bool POLY, class F>
-__global__ void __launch_bounds__(128) k_walk(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+__global__ void __launch_bounds__(128, WALK_MIN_BLOCKS) k_walk(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
 	const int i = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) / WG);
 	const int gl = threadIdx.x & (WG - 1);
 	if (i >= S.n) return;

@@ -48,8 +48,9 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 		PMPS_V3_FIELDS(X)
 #undef X
 		// the moved particle keeps searching around ITS position: give slot si the candidate list of slot sl
-		S.bpos[si] = S.bpos[sl]; S.listCnt[si] = S.listCnt[sl];
-		{
+		S.bpos[si] = S.bpos[sl];
+		if (S.listValid) {
+			S.listCnt[si] = S.listCnt[sl];
 			uint32_t* Li = S.list + (size_t)si * (size_t)S.listCap;
 			const uint32_t* Ll = S.list + (size_t)sl * (size_t)S.listCap;
 			for (int k = 0; k < S.listCnt[sl]; k++) Li[k] = Ll[k];

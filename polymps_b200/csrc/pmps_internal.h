@@ -54,6 +54,8 @@ struct DevView {
 	int32_t* flags;                      // [0] list overflow, [1] out-of-domain count, [2] guard violated, [3] live count
 	int32_t* oodList;                    // host ids flagged by the out-of-domain test
 	const struct DevMesh* meshes; int32_t nMeshes;   // polygon meshes (device array), set by pmps_set_mesh
+	int32_t listValid;                   // the Verlet list of the current bucket order has been built
+	int32_t* tileList; int32_t* nTiles;  // non-empty tiles (TILE_CX consecutive buckets of one row) of the last rebuild; count on device
 };
 
 enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, NFLAGS = 8 };
@@ -96,7 +98,8 @@ struct pmps_handle {
 	void* pinned = nullptr; size_t pinnedBytes = 0;
 	int32_t* h_flags = nullptr;          // pinned mirror of V.flags
 	int numParticles = 0, numParticlesZero = 0;
-	bool haveState = false, haveList = false;
+	bool haveState = false, haveList = false, listBuilt = false;   // haveList: bucket order valid; listBuilt: Verlet list valid
+	int nTilesAll = 0, smCount = 148;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;
 	long long launches = 0;
 	int oodTotal = 0, maxCell = 0;
@@ -130,6 +133,7 @@ struct ProfScope {
 // implemented in the .cu files
 int pmps_ensure_capacity(pmps_handle* h, int n0);
 int pmps_sort_and_list(pmps_handle* h);
+int pmps_ensure_list(pmps_handle* h);
 int pmps_ppe_solve(pmps_handle* h);
 int pmps_mesh_upload(pmps_handle* h, int mesh_id, int nV, const double* V, int nF, const int32_t* F, const double* N,
                      int nTable, const double* xP, const double* xN, const double* Z, const int32_t* nW);

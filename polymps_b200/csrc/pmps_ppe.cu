@@ -186,6 +186,7 @@ template <class T> static int palloc(pmps_handle* h, T** p, size_t count) {
 int pmps_ppe_solve(pmps_handle* h) {
 	DevView& S = h->V; const KParams& K = h->K;
 	if (K.p.solverType != 0) return pmps_fail(h, PMPS_E_UNSUPPORTED, "PPE: only the conjugate-gradient solver (solver_type 0) is on the device path");
+	{ const int rc = pmps_ensure_list(h); if (rc) return rc; }   // the assembly walks the Verlet candidate list
 	const int n = S.n, nBlocks = cdiv(n, PPE_T);
 	const size_t nWarps = ((size_t)S.n0 + 31) / 32, ell = nWarps * 32 * (size_t)S.listCap;
 	int bad = 0;

@@ -222,8 +222,17 @@ int pmps_sort_and_list(pmps_handle* h) {
 		PMPS_I32_FIELDS(X)
 #undef X
 	}
-	LAUNCH(h, "list.build", k_build_list, cdiv((long long)n0 * 32, 128), 128, S, K);
 	CUDA_TRY(h, cudaGetLastError());
-	h->haveList = true;
+	h->haveList = true;      // bucket order valid
+	h->listBuilt = false;    // the Verlet list is built on demand (stage API, PPE assembly, debug hooks)
+	S.listValid = 0;
+	return PMPS_OK;
+}
+
+int pmps_ensure_list(pmps_handle* h) {
+	if (h->listBuilt) return PMPS_OK;
+	LAUNCH(h, "list.build", k_build_list, cdiv((long long)h->V.n0 * 32, 128), 128, h->V, h->K);
+	CUDA_TRY(h, cudaGetLastError());
+	h->listBuilt = true; h->V.listValid = 1;
 	return PMPS_OK;
 }
