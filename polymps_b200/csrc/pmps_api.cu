@@ -1,8 +1,8 @@
 // pmps_api.cu — the C ABI of include/pmps.h: handle lifetime, host<->device transfers, the elementwise stages and
-// the stage/step drivers.  Neighbour stages are instantiations of the list walker (pmps_device.cuh) over the stage
+// the stage/step drivers.  Neighbour stages are instantiations of the tile-Verlet walker (pmps_tv.cuh) over the stage
 // bodies (pmps_bodies.cuh).  There is no CPU fallback anywhere: without a CUDA device pmps_create fails.
 #include "pmps_bodies.cuh"
-#include "pmps_tile.cuh"
+#include "pmps_tv.cuh"
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -225,6 +225,14 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	K.reMax2 = fmax(params->reS2, params->reL2); K.invReS = 1.0 / params->reS; K.invReL = 1.0 / params->reL;
 	memset(&h->V, 0, sizeof(DevView)); memset(&h->A, 0, sizeof(DevView));
 	h->V.nB = (int)nB;
+	// tiles of the tile-Verlet walker (pmps_tv.cuh): 2x2x2 buckets in 3D (halo 4x4x4), 4x4 in 2D (halo 6x6)
+	K.TX = params->dim == 3 ? 2 : 4; K.TY = K.TX; K.TZ = params->dim == 3 ? 2 : 1;
+	if (const char* e = getenv("PMPS_TILE")) { int a = 0, b = 0, c = 0; if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && b > 0 && c > 0 && (a + 2) * (b + 2) * (c + 2) <= TV_HMAX) { K.TX = a; K.TY = b; K.TZ = params->dim == 3 ? c : 1; } }
+	K.TV = K.TX * K.TY * K.TZ;
+	K.nTX = (params->numBucketsX + K.TX - 1) / K.TX; K.nTY = (params->numBucketsY + K.TY - 1) / K.TY; K.nTZ = (params->numBucketsZ + K.TZ - 1) / K.TZ;
+	const long long nC = (long long)K.nTX * K.nTY * K.nTZ * K.TV;
+	if (nC > 2000000000ll) { delete h; return pmps_fail(nullptr, PMPS_E_OVERFLOW, "pmps_create: %lld cells overflow int32", nC); }
+	h->V.nC = (int)nC; h->nTilesAll = K.nTX * K.nTY * K.nTZ;
 	*out = h;
 	return PMPS_OK;
 }
@@ -238,16 +246,14 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	int rc = 0;
 	rc |= alloc_view(h, S, n0, true); rc |= alloc_view(h, h->A, n0, false);
 	rc |= dalloc(h, &S.scratch1, n0); rc |= dalloc(h, &S.bpos, n0); rc |= dalloc(h, &S.slotOfHost, n0); rc |= dalloc(h, &S.cellOf, n0);
-	rc |= dalloc(h, &S.cellStart, (size_t)S.nB + 2); rc |= dalloc(h, &h->cellCount, (size_t)S.nB + 2);
+	rc |= dalloc(h, &S.cellStart, (size_t)S.nC + 2); rc |= dalloc(h, &h->cellCount, (size_t)S.nC + 2);
 	rc |= dalloc(h, &h->perm, n0); rc |= dalloc(h, &h->arbRank, n0); rc |= dalloc(h, &h->newCell, n0);
 	rc |= dalloc(h, &h->tmpHost, 2 * (size_t)n0);
-	h->nScanBlocks = cdiv((long long)S.nB + 2, 512 * 8) + 1;
+	h->nScanBlocks = cdiv((long long)S.nC + 2, 512 * 8) + 1;
 	rc |= dalloc(h, &h->scanBlock, h->nScanBlocks);
-	{	// tiles of the tile walker: TILE_CX consecutive buckets of one bucket row
-		const long long nXB = (P.numBucketsX + TILE_CX - 1) / TILE_CX;
-		const long long nt = nXB * P.numBucketsY * P.numBucketsZ;
-		h->nTilesAll = (int)nt;
-		rc |= dalloc(h, &S.tileList, (size_t)(nt < n0 ? nt : n0) + 1); rc |= dalloc(h, &S.nTiles, 1);
+	{	// work items of the tile-Verlet walker: at most one per non-empty cell
+		const size_t items = (size_t)(S.nC < n0 ? S.nC : n0) + 1;
+		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
 		int sm = 148; cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device); h->smCount = sm;
 	}
 	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 1); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
@@ -258,9 +264,14 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	int cap = (int)(lat * 1.6) + 8;
 	if (const char* e = getenv("PMPS_LIST_CAP")) cap = atoi(e);
 	cap = (cap + 3) & ~3; if (cap < 8) cap = 8; if (cap > 4096) cap = 4096;
-	S.listCap = cap;
-	const size_t nWarps = ((size_t)n0 + 31) / 32;
-	rc |= dalloc(h, &S.list, nWarps * 32 * (size_t)cap); rc |= dalloc(h, &S.listCnt, nWarps * 32);
+	S.listCap = cap;   // the global-slot list itself is allocated on first use (pmps_ensure_list)
+	// tile-local list: whole chunks of 64 entries; staging capacity from the shared-memory budget of the fattest pass
+	S.tlCap = ((cap + TV_CHUNK - 1) / TV_CHUNK) * TV_CHUNK; if (S.tlCap > 255 * TV_CHUNK) S.tlCap = 255 * TV_CHUNK;
+	rc |= dalloc(h, &S.tlist, (size_t)n0 * (size_t)S.tlCap); rc |= dalloc(h, &S.tlistChunks, n0);
+	K.tvMaxM = (int)((TV_SMEM_BUDGET - (size_t)TV_NG * S.tlCap * 2) / TV_REC_MAX);
+	if (K.tvMaxM > 65534) K.tvMaxM = 65534;
+	if (const char* e = getenv("PMPS_TILE_MAXM")) { const int v = atoi(e); if (v > 0 && v < K.tvMaxM) K.tvMaxM = v; }   // tests: force the split path
+	if (K.tvMaxM < 64) return pmps_fail(h, PMPS_E_UNSUPPORTED, "candidate lists of %d entries leave no room for the staged halo", S.tlCap);
 	h->stageBytes = 64 * (size_t)n0;
 	{ void* q = nullptr; if (cudaMalloc(&q, h->stageBytes) != cudaSuccess) rc |= 1; else { h->allocs.push_back(q); h->stage = q; } }
 	if (cudaMallocHost((void**)&h->h_flags, sizeof(int32_t) * NFLAGS) != cudaSuccess) rc |= 1;
@@ -274,6 +285,8 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	K.rl2 = (float)(rlf * rlf);
 	const double guard = 0.5 * (rl - maxRe) - 8.0 * 1.2e-7 * ext;
 	K.guard2 = (float)(guard > 0 ? guard * guard : 0.0);
+	// |x_j - mirror_i| >= 2 dist(i, wall) - displacement - |x_j - x_i| > re whenever dist > re + displacement/2: margin = the full guard
+	{ const double far = maxRe * (1.0 + 1e-6) + (guard > 0 ? guard : 0.0) + 1e-6 * lo; K.mirrorFar2 = far * far; }
 	k_iota<<<cdiv(n0, 256), 256, 0, h->stream>>>(S.hostIdx, S.slotOfHost, n0);
 	{ unsigned long long vb[2]; double v2 = K.velMax * K.velMax; memcpy(&vb[0], &v2, 8); vb[1] = vb[0];
 	  cudaMemcpyAsync(S.velMax2Bits, vb, 16, cudaMemcpyHostToDevice, h->stream); cudaStreamSynchronize(h->stream); }

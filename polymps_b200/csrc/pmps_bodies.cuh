@@ -15,15 +15,15 @@ struct BViscosity {
 		const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z; c.mu = S.MEU[s.i]; c.invRho = 1.0 / S.RHO[s.i];
 		c.sx = c.sy = c.sz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reL2)) return;
 		const double w = wgt_r(q.rinv, q.d2, K.p.reL, K.invReL, K.p.weightType);
 		const double muj = S.MEU[q.j];
 		double nu = (c.mu + muj) > K.p.epsilonZero ? 2.0 * c.mu * muj * fast_rcp(c.mu + muj) : 0.0;
-		if (pk_type(q.pj) == K.p.wall) nu = 2.0 * c.mu;
+		if (q.tj == K.p.wall) nu = 2.0 * c.mu;
 		const double f = w * nu * c.invRho;
-		const double4 vj = S.vel[q.j];
-		c.sx += (vj.x - c.vx) * f; c.sy += (vj.y - c.vy) * f; c.sz += (vj.z - c.vz) * f;
+		const double vjx = S.vx[q.j], vjy = S.vy[q.j], vjz = S.vz[q.j];
+		c.sx += (vjx - c.vx) * f; c.sy += (vjy - c.vy) * f; c.sz += (vjz - c.vz) * f;
 	}
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.sx = gsum(c.sx, m); c.sy = gsum(c.sy, m); c.sz = gsum(c.sz, m); }
 	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
@@ -57,7 +57,7 @@ struct BPredictTail {
 	typedef void copy_pos_tag; typedef void copy_vel_tag; typedef void no_pair_tag;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams&, const Self&) { return true; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const Nb&, const KParams&, const Self&, const Pair&) {}
 	__device__ __forceinline__ static void reduce(Ctx& , unsigned m) {  }
 	__device__ __forceinline__ static void end(Ctx&, const DevView& S, const KParams& K, const Self& s) {
 		const int i = s.i;
@@ -85,14 +85,14 @@ struct BWallViscosity {
 		c.invRhoDiv = 1.0 / (s.ptype == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2);
 		c.sx = c.sy = c.sz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_M(q, K.p.reL2)) return;
 		const double w = wgt_r(fast_rsqrt(q.dm2), q.dm2, K.p.reL, K.invReL, K.p.weightType);
 		const double muj = S.MEU[q.j];
 		double nu = (c.mu + muj) > K.p.epsilonZero ? 2.0 * c.mu * muj * fast_rcp(c.mu + muj) : 0.0;
 		const double f = w * nu * c.invRhoDiv;
-		const double4 vj = S.vel[q.j];
-		c.sx += (vj.x - c.vm[0]) * f; c.sy += (vj.y - c.vm[1]) * f; c.sz += (vj.z - c.vm[2]) * f;
+		const double vjx = S.vx[q.j], vjy = S.vy[q.j], vjz = S.vz[q.j];
+		c.sx += (vjx - c.vm[0]) * f; c.sy += (vjy - c.vm[1]) * f; c.sz += (vjz - c.vm[2]) * f;
 	}
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.sx = gsum(c.sx, m); c.sy = gsum(c.sy, m); c.sz = gsum(c.sz, m); }
 	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
@@ -124,13 +124,13 @@ struct BCollision {
 		const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z;
 		c.mi = s.ptype == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2; c.dx = c.dy = c.dz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.distCollisionLimit2)) return;
-		const double4 vj = S.vel[q.j];
-		double f = (c.vx - vj.x) * q.rx + (c.vy - vj.y) * q.ry + (c.vz - vj.z) * q.rz;
+		const double vjx = S.vx[q.j], vjy = S.vy[q.j], vjz = S.vz[q.j];
+		double f = (c.vx - vjx) * q.rx + (c.vy - vjy) * q.ry + (c.vz - vjz) * q.rz;
 		if (f > 0.0) {
-			const bool jf = pk_type(q.pj) == K.p.fluid;
-			const double mj = jf ? (pk_ptype(q.pj) == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2) : K.p.densityWall;
+			const bool jf = q.tj == K.p.fluid;
+			const double mj = jf ? (q.ptj == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2) : K.p.densityWall;
 			f *= K.p.restitutionCollision * mj / (c.mi + mj) / q.d2;
 			if (jf) { c.dx -= q.rx * f; c.dy -= q.ry * f; c.dz -= q.rz * f; }
 			else { c.dx -= 2.0 * q.rx * f; c.dy -= 2.0 * q.ry * f; c.dz -= 2.0 * q.rz * f; }
@@ -146,7 +146,7 @@ struct BCollisionTail {
 	typedef void copy_vel_tag; typedef void no_pair_tag;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams& K, const Self& s) { return s.type == K.p.fluid; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const Nb&, const KParams&, const Self&, const Pair&) {}
 	__device__ __forceinline__ static void reduce(Ctx& , unsigned m) {  }
 	__device__ __forceinline__ static void end(Ctx&, const DevView& S, const KParams& K, const Self& s) {
 		double4 v = S.vel[s.i];
@@ -160,7 +160,7 @@ struct BCollisionTail {
 struct BWallClosestHead {
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView& S, const KParams& K, const Self& s) { if (s.lead) wall_closest_of(S, K, s.i, s.pi); return false; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const Nb&, const KParams&, const Self&, const Pair&) {}
 	__device__ __forceinline__ static void reduce(Ctx& , unsigned m) {  }
 	__device__ __forceinline__ static void end(Ctx&, const DevView&, const KParams&, const Self&) {}
 };

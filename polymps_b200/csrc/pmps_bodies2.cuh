@@ -10,7 +10,7 @@ struct BWallNpcd {
 		if (!s.nearWallFluid) return false;
 		c.sx = c.sy = c.sz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_M(q, K.p.reS2)) return;
 		const double w = wgt_r(fast_rsqrt(q.dm2), q.dm2, K.p.reS, K.invReS, K.p.weightType);
 		c.sx += q.mx * w; c.sy += q.my * w; c.sz += q.mz * w;
@@ -41,7 +41,7 @@ struct BPndNeighNpcd {
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		c.ni = c.wsum = 0.0; c.cnt = 0; c.dx = c.dy = c.dz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reL2)) return;
 		c.cnt += 1;
 		if (q.d2 < K.p.reS2) {
@@ -65,7 +65,7 @@ struct BInitialPnd {
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		c.acc = 0.0; c.wsum = 0.0; c.cnt = 0; c.dx = c.dy = c.dz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reL2)) return;
 		c.cnt += 1;
 		if (q.d2 < K.p.reS2) {
@@ -99,17 +99,17 @@ struct BPndDiffusive {
 		}
 		c.Di = c.div = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reL2)) return;
-		if (s.type == K.p.fluid && pk_type(q.pj) == K.p.fluid) {
+		if (s.type == K.p.fluid && q.tj == K.p.fluid) {
 			const double wL = wgt_r(q.rinv, q.d2, K.p.reL, K.invReL, K.p.weightType);
 			const double rhoj = S.RHO[q.j];
 			const double pgh = -2.0 * (c.rho * rhoj * fast_rcp(c.rho + rhoj)) * (K.p.gravityX * q.rx + K.p.gravityY * q.ry + K.p.gravityZ * q.rz);
 			c.Di += c.kDi * (S.press[q.j] - c.Pi - pgh) * wL;
 		}
 		if (q.d2 < K.p.reS2) {
-			const double4 vj = S.vel[q.j];
-			const double ux = vj.x - c.vx, uy = vj.y - c.vy, uz = vj.z - c.vz;
+			const double vjx = S.vx[q.j], vjy = S.vy[q.j], vjz = S.vz[q.j];
+			const double ux = vjx - c.vx, uy = vjy - c.vy, uz = vjz - c.vz;
 			const double wS = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType) * (q.rinv * q.rinv);   // w / d2
 			if (!K.p.gradientCorrection) c.div += S.pndi[q.j] * (ux * q.rx + uy * q.ry + uz * q.rz) * wS;   // * (dim/n0S)/ni in end()
 			else {
@@ -147,10 +147,10 @@ struct BWallPndDiffusive {
 		if (K.p.slipCondition == 1) { ux = vjx - c.vm[0]; uy = vjy - c.vm[1]; uz = vjz - c.vm[2]; qx = mx; qy = my; qz = mz; }
 		return ((double)K.p.dim / K.p.pndSmallZero) * (pndj / c.ni) * (ux * qx + uy * qy + uz * qz) * wS / dd;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_M(q, K.p.reS2)) return;
-		const double4 vj = S.vel[q.j];
-		c.div += term(c, K, s, vj.x, vj.y, vj.z, q.mx, q.my, q.mz, S.pndi[q.j], q.dm2);
+		const double vjx = S.vx[q.j], vjy = S.vy[q.j], vjz = S.vz[q.j];
+		c.div += term(c, K, s, vjx, vjy, vjz, q.mx, q.my, q.mz, S.pndi[q.j], q.dm2);
 	}
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.div = gsum(c.div, m); }
 	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
@@ -172,7 +172,7 @@ template <int SEL> struct BMeanPnd {
 		}
 		return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reS2)) return;
 		const double w = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType); c.up += S.pndi[q.j] * w; c.dn += w;
 	}
@@ -190,7 +190,7 @@ struct BMeanWallPnd {
 		c.up = c.dn = 0.0; S.pndAuxVar1[s.i] = 0.0; S.pndAuxVar2[s.i] = 0.0;
 		return S.particleNearWall[s.i] != 0;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_M(q, K.p.reS2)) return;
 		const double w = wgt(sqrt(q.dm2), K.p.reS, K.p.weightType); c.up += S.pndi[q.j] * w; c.dn += w;
 	}
@@ -206,8 +206,8 @@ struct BMeanWallPnd {
 struct BMeanNeighFluidPnd {
 	struct Ctx { double up, dn; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) { c.up = c.dn = 0.0; return true; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
-		if (!(pred_P<POLY>(q, K.p.reS2) && pk_type(q.pj) == K.p.fluid)) return;
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!(pred_P<POLY>(q, K.p.reS2) && q.tj == K.p.fluid)) return;
 		const double w = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType); c.up += S.pndki[q.j] * w; c.dn += w;
 	}
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.up = gsum(c.up, m); c.dn = gsum(c.dn, m); }
@@ -240,7 +240,7 @@ __device__ __forceinline__ void invert3(double M[9], int dim, double eps) {   //
 struct BCorrectionMatrix {
 	struct Ctx { double M[9]; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) { for (int k = 0; k < 9; k++) c.M[k] = 0.0; return true; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reS2)) return;
 		const double w = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType) * (q.rinv * q.rinv); const double r[3] = { q.rx, q.ry, q.rz };
 		for (int a = 0; a < 3; a++) for (int b = 0; b < 3; b++) c.M[3 * a + b] += w * r[a] * r[b];

@@ -18,7 +18,7 @@ __device__ __forceinline__ double grad_phi_r(const KParams& K, double w, double 
 struct BPressMin {
 	struct Ctx { double pmin; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) { c.pmin = S.press[s.i]; return true; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reS2)) return;
 		const double pj = S.press[q.j]; if (c.pmin > pj) c.pmin = pj;
 	}
@@ -39,7 +39,7 @@ struct BPressGradient {
 		}
 		c.sx = c.sy = c.sz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reS2)) return;
 		const double w = grad_phi_r(K, wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType), S.press[q.j], c.Pi, c.Pmin, c.ni, c.invNi, S.pndi[q.j], q.rinv * q.rinv);
 		if (!K.p.gradientCorrection) { c.sx += q.rx * w; c.sy += q.ry * w; c.sz += q.rz * w; }
@@ -80,7 +80,7 @@ struct BWallPressGradient {
 		c.Pmin = (K.p.gradientType == 0 || K.p.gradientType == 2) ? S.scratch1[s.i] : c.Pi;
 		c.sx = c.sy = c.sz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_M(q, K.p.reS2)) return;
 		const double mi = fast_rsqrt(q.dm2);
 		const double w = grad_phi_r(K, wgt_r(mi, q.dm2, K.p.reS, K.invReS, K.p.weightType), S.press[q.j], c.Pi, c.Pmin, c.ni, c.invNi, S.pndi[q.j], mi * mi);
@@ -118,7 +118,7 @@ struct BCorrectTail {
 	typedef void copy_pos_tag; typedef void copy_vel_tag; typedef void no_pair_tag;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams& K, const Self& s) { return s.type == K.p.fluid; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const Nb&, const KParams&, const Self&, const Pair&) {}
 	__device__ __forceinline__ static void reduce(Ctx& , unsigned m) {  }
 	__device__ __forceinline__ static void end(Ctx&, const DevView& S, const KParams& K, const Self& s) {
 		const int i = s.i;
@@ -137,7 +137,7 @@ struct BCorrectTail {
 struct BConcentration {
 	struct Ctx { double c; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) { c.c = 0.0; return true; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reS2)) return;
 		c.c += wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType);
 	}
@@ -157,7 +157,7 @@ struct BGradConcentration {
 		if (s.type != K.p.fluid) return false;
 		c.ci = S.concentration[s.i]; c.gx = c.gy = c.gz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reS2)) return;
 		const double f = (c.ci + S.concentration[q.j]) * wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType) * (q.rinv * q.rinv);
 		c.gx += q.rx * f; c.gy += q.ry * f; c.gz += q.rz * f;
@@ -184,7 +184,7 @@ struct BWallGradConcentration {
 		c.ci = S.concentration[s.i];
 		c.sx = c.sy = c.sz = 0.0; return true;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_M(q, K.p.reS2)) return;
 		const double mi = fast_rsqrt(q.dm2);
 		const double f = (c.ci + S.concentration[q.j]) * wgt_r(mi, q.dm2, K.p.reS, K.invReS, K.p.weightType) * (mi * mi);
@@ -222,8 +222,8 @@ struct BExtrapolatePress {
 		c.ni = c.pr = 0.0;
 		return s.type == K.p.dummyWall || (K.p.mpsType == 1 && s.type == K.p.wall);
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
-		if (!(q.d2 < K.p.reS2 && pk_type(q.pj) == K.p.fluid)) return;
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!(q.d2 < K.p.reS2 && q.tj == K.p.fluid)) return;
 		const double w = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType); c.ni += w;
 		c.pr += (S.press[q.j] - S.RHO[q.j] * (K.p.gravityX * q.rx + K.p.gravityY * q.ry + K.p.gravityZ * q.rz)) * w;
 	}
@@ -240,10 +240,10 @@ struct BWallDummyVel {
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		c.ni = c.ux = c.uy = c.uz = 0.0; return s.type == K.p.dummyWall;
 	}
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
-		if (!(q.d2 < K.p.reL2 && pk_type(q.pj) == K.p.fluid)) return;
-		const double w = wgt_r(q.rinv, q.d2, K.p.reL, K.invReL, K.p.weightType); const double4 vj = S.vel[q.j];
-		c.ni += w; c.ux += vj.x * w; c.uy += vj.y * w; c.uz += vj.z * w;
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!(q.d2 < K.p.reL2 && q.tj == K.p.fluid)) return;
+		const double w = wgt_r(q.rinv, q.d2, K.p.reL, K.invReL, K.p.weightType); const double vjx = S.vx[q.j], vjy = S.vy[q.j], vjz = S.vz[q.j];
+		c.ni += w; c.ux += vjx * w; c.uy += vjy * w; c.uz += vjz * w;
 	}
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.ni = gsum(c.ni, m); c.ux = gsum(c.ux, m); c.uy = gsum(c.uy, m); c.uz = gsum(c.uz, m); }
 	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {

@@ -102,7 +102,7 @@ __device__ __forceinline__ double4 ld256(const double4* p) {
 
 // ---- per-particle prologue shared by the fused bodies --------------------------------------------------------------
 struct Self {
-	int i; bool lead; double4 pi; int type, ptype;   // lead: first lane of the particle's group (does the side effects)
+	int i; bool lead; double4 pi; int type, ptype; bool hasMirror;   // hasMirror: the polygon-wall pass gave i a mirror particle   // lead: first lane of the particle's group (does the side effects)
 	double mix, miy, miz;       // mirror position of i
 	// wall frame of a near-wall fluid particle: unit normal n = (x_i - mirror_i)/|.|, reflection R = I - 2 n n^T,
 	// len = |x_i - mirror_i| / 2 (e.g. src/MpsPndNeigh.cpp:114-136); filled only when nearWallFluid
@@ -144,15 +144,35 @@ __device__ __forceinline__ void mirror_velocity(const KParams& K, int nearMeshTy
 
 // ---- the pair geometry handed to every stage body ------------------------------------------------------------------
 struct Pair {
-	int j; double4 pj;
+	int j;                      // index of the neighbour in the arrays of the Nb view the body receives
+	int tj, ptj;                // particleType / PTYPE of the neighbour
 	double rx, ry, rz, d2;      // r_ij = x_j - x_i ; d2 exact
 	double rinv;                // 1/|r_ij| (1 ulp)
-	double mx, my, mz, dm2;     // x_j - mirror_i (polygon walls only) ; dm2 exact
+	double mx, my, mz, dm2;     // x_j - mirror_i (polygon walls, i near a wall; otherwise dm2 = +inf) ; dm2 exact
+};
+// Neighbour-side fields as pair() sees them: planes indexed by Pair::j.  The tile walker points them at the shared-memory
+// copies of the staged halo (pmps_tv.cuh); a plane a body does not declare in NbFields is null.
+struct Nb {
+	const double *vx, *vy, *vz, *press, *pndi, *RHO, *MEU, *concentration, *pndki;
 };
 
 // predicates: P(re) real neighbour, M(re) mirror neighbourhood
 template <bool POLY> __device__ __forceinline__ bool pred_P(const Pair& q, double re2) { return q.d2 < re2 && (!POLY || q.d2 < q.dm2); }
 __device__ __forceinline__ bool pred_M(const Pair& q, double re2) { return q.d2 < re2 && q.dm2 < re2 && q.d2 < q.dm2; }
+
+// tile-major cell index of bucket (ix, iy, iz): tiles of TX x TY x TZ buckets, x fastest inside a tile and between tiles
+__host__ __device__ __forceinline__ int cell_index(const KParams& K, int ix, int iy, int iz) {
+	const int tx = ix / K.TX, ty = iy / K.TY, tz = iz / K.TZ;
+	const int lx = ix - tx * K.TX, ly = iy - ty * K.TY, lz = iz - tz * K.TZ;
+	return ((tz * K.nTY + ty) * K.nTX + tx) * K.TV + (lz * K.TY + ly) * K.TX + lx;
+}
+// inverse: bucket coordinates of a cell (may lie outside the bucket grid for the padding cells of border tiles)
+__host__ __device__ __forceinline__ void cell_coords(const KParams& K, int c, int& ix, int& iy, int& iz) {
+	const int t = c / K.TV, l = c - t * K.TV;
+	const int tz = t / (K.nTX * K.nTY), ty = (t - tz * K.nTX * K.nTY) / K.nTX, tx = t - (tz * K.nTY + ty) * K.nTX;
+	const int lz = l / (K.TX * K.TY), ly = (l - lz * K.TX * K.TY) / K.TX, lx = l - (lz * K.TY + ly) * K.TX;
+	ix = tx * K.TX + lx; iy = ty * K.TY + ly; iz = tz * K.TZ + lz;
+}
 
 // ---- body packs --------------------------------------------------------------------------------------------------
 // A body has  struct Ctx;  static bool begin(Ctx&, S, K, self) (false: inactive for this i);
@@ -174,7 +194,7 @@ template <> struct Fused<> {
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams&, const Self&) { return false; }
 	__device__ __forceinline__ static bool need_pairs(const Ctx&) { return false; }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const DevView&, const KParams&, const Self&, const Pair&) {}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const Nb&, const KParams&, const Self&, const Pair&) {}
 	__device__ __forceinline__ static void reduce(Ctx&, unsigned) {}
 	__device__ __forceinline__ static void end(Ctx&, const DevView&, const KParams&, const Self&) {}
 };
@@ -189,7 +209,7 @@ template <class B, class... Rest> struct Fused<B, Rest...> {
 		return x.on || o;
 	}
 	__device__ __forceinline__ static bool need_pairs(const Ctx& x) { return (x.on && !NoPairs<B>::value) || Fused<Rest...>::need_pairs(x.r); }
-	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& x, const DevView& S, const KParams& K, const Self& s, const Pair& q) {
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& x, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!NoPairs<B>::value) { if (x.on) B::template pair<POLY>(x.c, S, K, s, q); }
 		Fused<Rest...>::template pair<POLY>(x.r, S, K, s, q);
 	}
@@ -203,55 +223,3 @@ template <class B, class... Rest> struct Fused<B, Rest...> {
 	}
 };
 
-// Walk the Verlet candidates of slot i with a GROUP of WG lanes: lane g takes candidates g, g+WG, ... of the (row-major)
-// list, so the lanes of a group gather ADJACENT slots — a handful of cache lines per load instruction instead of one
-// line per lane — and the partial sums are combined with warp shuffles before end() runs on the group's first lane.
-// Candidates farther than the largest cut-off are dropped before any body sees them (every predicate of the reference
-// implies d2 < max(reS,reL)^2); the mirror distance and the reciprocal distance are computed only for the survivors.
-template <bool POLY, class F>
-__device__ __forceinline__ void walk_one(typename F::Ctx& ctx, const DevView& S, const KParams& K, const Self& s, int j, const double4& pj) {
-	Pair q; q.j = j; q.pj = pj;
-	q.rx = pj.x - s.pi.x; q.ry = pj.y - s.pi.y; q.rz = pj.z - s.pi.z;
-	q.d2 = sq3_exact(q.rx, q.ry, q.rz);
-	if (!(q.d2 < K.reMax2)) return;
-	if (POLY) { q.mx = pj.x - s.mix; q.my = pj.y - s.miy; q.mz = pj.z - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
-	else { q.mx = q.my = q.mz = 0.0; q.dm2 = 0.0; }
-	q.rinv = fast_rsqrt(q.d2);
-	F::template pair<POLY>(ctx, S, K, s, q);
-}
-
-template <bool POLY, class F>
-__global__ void __launch_bounds__(128, WALK_MIN_BLOCKS) k_walk(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
-	const int i = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) / WG);
-	const int gl = threadIdx.x & (WG - 1);
-	if (i >= S.n) return;
-	const unsigned gmask = (WG == 32 ? 0xffffffffu : ((1u << WG) - 1u)) << ((threadIdx.x & 31) & ~(WG - 1));
-	Self s; s.i = i; s.lead = gl == 0; s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
-	if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
-	if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
-	if (s.type == K.p.ghost) return;
-	s.nearWallFluid = false;
-	if (POLY) { s.mix = S.mirrorParticlePos.x[i]; s.miy = S.mirrorParticlePos.y[i]; s.miz = S.mirrorParticlePos.z[i]; }
-	else { s.mix = s.miy = s.miz = 0.0; }
-	if (POLY && F::kWall) {
-		s.nearWallFluid = s.type == K.p.fluid && S.particleNearWall[i];
-		if (s.nearWallFluid) self_wall_frame(s);
-	}
-	typename F::Ctx ctx;
-	if (!F::begin(ctx, S, K, s)) return;
-	if (F::need_pairs(ctx)) {
-		const uint32_t* L = S.list + (size_t)i * (size_t)S.listCap;
-		const int cnt = S.listCnt[i];
-		// two candidates per lane and trip: both list entries, then both position records, are requested before either is
-		// used, which doubles the loads in flight per warp (the walks are latency-bound: profiles/r01_ncu_walk_v3.txt)
-		for (int k = gl; k < cnt; k += 2 * WG) {
-			const bool two = k + WG < cnt;
-			const int j0 = (int)L[k]; const int j1 = two ? (int)L[k + WG] : j0;
-			const double4 p0 = ld256(S.pos + j0); const double4 p1 = ld256(S.pos + j1);
-			walk_one<POLY, F>(ctx, S, K, s, j0, p0);
-			if (two) walk_one<POLY, F>(ctx, S, K, s, j1, p1);
-		}
-	}
-	F::reduce(ctx, gmask);
-	if (s.lead) F::end(ctx, S, K, s);
-}

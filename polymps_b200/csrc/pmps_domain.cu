@@ -1,7 +1,7 @@
 // pmps_domain.cu — MpsParticle::checkParticleOutDomain (reference src/MpsParticle.cpp:234-402, non-periodic branch).
 //
 // The reference removes a fluid particle that left [domainMin+bucketSide, domainMax-bucketSide] by copying the LAST
-// live particle over it and turning the last slot into a ghost; the loop is serial and order dependent.  On the
+// live particle over it and turning the last array element into a ghost; the loop is serial and order dependent.  On the
 // device a flag kernel collects the (normally zero) offenders; a one-thread kernel then replays the reference's
 // serial loop over just those host indices in ascending order, re-testing each against the CURRENT content of its
 // slot exactly as the reference's loop does.  No host round trip: the fix kernel returns at once when the count is 0.
@@ -38,28 +38,27 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 		const double4 pcur = S.pos[si];
 		if (pk_type(pcur) != K.p.fluid || !out_of_domain(K, pcur)) continue;
 		const int hl = live - 1; const int sl = S.slotOfHost[hl];
-		// slot si <- content of slot sl (host index hi keeps its slot), then slot sl becomes a ghost
-		S.pos[si] = S.pos[sl]; S.vel[si] = S.vel[sl]; S.particleNearWall[si] = S.particleNearWall[sl];
+		// The reference copies particle hl over particle hi and turns hl into a ghost.  In slot space the DATA stays where
+		// it is (slot sl keeps searching around its own position with its own candidate list); the host LABELS are swapped:
+		// slot sl now answers to host index hi, slot si — which receives a copy of sl's fields, as array element hl keeps
+		// them in the reference — becomes the ghost hl.
+		if (sl != si) {
+			S.pos[si] = S.pos[sl]; S.vel[si] = S.vel[sl]; S.particleNearWall[si] = S.particleNearWall[sl];
 #define X(n) S.n[si] = S.n[sl];
-		PMPS_I32_FIELDS(X)
-		PMPS_F64_FIELDS(X)
+			PMPS_I32_FIELDS(X)
+			PMPS_F64_FIELDS(X)
 #undef X
 #define X(n) S.n.x[si] = S.n.x[sl]; S.n.y[si] = S.n.y[sl]; S.n.z[si] = S.n.z[sl];
-		PMPS_V3_FIELDS(X)
+			PMPS_V3_FIELDS(X)
 #undef X
-		// the moved particle keeps searching around ITS position: give slot si the candidate list of slot sl
-		S.bpos[si] = S.bpos[sl];
-		if (S.listValid) {
-			S.listCnt[si] = S.listCnt[sl];
-			uint32_t* Li = S.list + (size_t)si * (size_t)S.listCap;
-			const uint32_t* Ll = S.list + (size_t)sl * (size_t)S.listCap;
-			for (int k = 0; k < S.listCnt[sl]; k++) Li[k] = Ll[k];
+			S.hostIdx[sl] = hi; S.slotOfHost[hi] = sl; S.hostIdx[si] = hl; S.slotOfHost[hl] = si;
 		}
+		const int sg = si;   // the slot that becomes the ghost
 		double4 g; g.x = K.p.domainMaxX - K.p.partDist; g.y = K.p.domainMaxY - K.p.partDist;
-		g.z = K.p.dim == 2 ? 0.0 : K.p.domainMaxZ - K.p.partDist; g.w = pk_make(K.p.ghost, pk_ptype(S.pos[sl]));
-		S.pos[sl] = g; double4 vz = S.vel[sl]; vz.x = vz.y = vz.z = 0.0; S.vel[sl] = vz;
-		S.particleBC[sl] = K.p.other; S.particleNearWall[sl] = 0; S.nearMeshType[sl] = 0; S.distParticleWall2[sl] = K.big;
-		S.press[sl] = 0.0;
+		g.z = K.p.dim == 2 ? 0.0 : K.p.domainMaxZ - K.p.partDist; g.w = pk_make(K.p.ghost, pk_ptype(S.pos[sg]));
+		S.pos[sg] = g; double4 vz = S.vel[sg]; vz.x = vz.y = vz.z = 0.0; S.vel[sg] = vz;
+		S.particleBC[sg] = K.p.other; S.particleNearWall[sg] = 0; S.nearMeshType[sg] = 0; S.distParticleWall2[sg] = K.big;
+		S.press[sg] = 0.0;
 		live--; S.flags[FLAG_OOD_TOTAL] += 1;
 	}
 	S.flags[FLAG_LIVE] = live;

@@ -4,7 +4,8 @@
 // bucket id (src/MpsBucket.cpp:299-353), ascending host index inside a bucket (= the reference's list order).
 //   pos, vel      : 32-byte records {x,y,z,w}; pos.w carries the bits of {particleType, PTYPE}; one sector per gather
 //   every other field : one 8-byte (or 4/1-byte) plane per component, coalesced own-index access
-//   list          : Verlet candidate list built once per step (warp-interleaved, 32-bit slot ids)
+//   tlist         : per-step Verlet candidates as 16-bit indices into the staged halo of the particle's tile
+//                   (pmps_tv.cuh); list: the same candidates as global slot ids, built on demand (PPE, debug hooks)
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -31,8 +32,9 @@ struct DevView {
 	int32_t* hostIdx;                    // slot -> host (reference) index
 	int32_t* slotOfHost;                 // host index -> slot
 	int32_t* cellOf;                     // slot -> bucket id at the last rebuild
-	int32_t* cellStart;                  // nB+1, slots of bucket b are [cellStart[b], cellStart[b+1])
-	uint32_t* list; uint16_t* listCnt;   // Verlet candidates (slot ids), warp-interleaved, listCap per particle
+	int32_t* cellStart;                  // nC+2, slots of cell c (tile-major bucket index, cell_index()) are [cellStart[c], cellStart[c+1]); cell nC = ghosts
+	uint32_t* list; uint16_t* listCnt;   // Verlet candidates (slot ids), row-major, listCap per particle; built on demand
+	uint16_t* tlist; uint8_t* tlistChunks;   // tile-local candidates: tlCap entries per slot in chunks of 64 (interleaved by 8), chunks used
 	uint8_t* particleNearWall;
 	double* scratch1;                    // per-slot scratch (Pmin of the gradient passes); not a reference field
 #define X(n) int32_t* n;
@@ -47,7 +49,9 @@ struct DevView {
 	int32_t n;                           // slots in use (= live particles at the last rebuild incl. later ghosts)
 	int32_t n0;                          // capacity (numParticlesZero)
 	int32_t listCap;
-	int32_t nB;
+	int32_t nB;                          // reference buckets (numBucketsX*Y*Z)
+	int32_t nC;                          // cells of the tile-major index (>= nB: tiles are padded to full size)
+	int32_t tlCap;                       // entries per slot in tlist (multiple of 64)
 	// device scalars
 	unsigned long long* velMax2Bits;     // max |v|^2 of fluid particles (bits of a non-negative double)
 	float* maxDisp2;                     // max squared displacement since the list build (float, >= 0)
@@ -55,11 +59,15 @@ struct DevView {
 	int32_t* oodList;                    // host ids flagged by the out-of-domain test
 	const struct DevMesh* meshes; int32_t nMeshes;   // polygon meshes (device array), set by pmps_set_mesh
 	int32_t listValid;                   // the Verlet list of the current bucket order has been built
-	int32_t* tileList; int32_t* nTiles;  // non-empty tiles (TILE_CX consecutive buckets of one row) of the last rebuild; count on device
+	int32_t* tileList; int32_t* nTiles;  // work items of the last rebuild: tile id (whole tile) or ~cell (one bucket of a tile whose halo
+	                                     // does not fit the staging area); count on device
+	int32_t* tileCursor;                 // work-stealing cursors, one per walk launch of a step
+	uint8_t* tileWall;                   // per tile: some particle of the tile is near a polygon wall (set by the wall pass)
 };
 
-enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, NFLAGS = 8 };
+enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, NFLAGS = 8 };
 #define PMPS_OOD_CAP 65536
+#define PMPS_CURSORS 64   // work-stealing cursors per step (one per tile-walker launch)
 
 // Kernel-side parameters: the ABI params plus derived constants
 struct KParams {
@@ -70,7 +78,11 @@ struct KParams {
 	float rl2;           // (list radius)^2 incl. float margin
 	float guard2;        // (allowed displacement)^2
 	int32_t poly;        // wallType == polygon
+	int32_t TX, TY, TZ, TV;       // buckets per tile along x, y, z and their product
+	int32_t nTX, nTY, nTZ;        // tiles per axis
+	int32_t tvMaxM;               // staged records a tile may need (smallest capacity over the passes): larger tiles are split
 	double reMax2;       // max(reS, reL)^2: no predicate of the reference reaches farther
+	double mirrorFar2;   // a particle farther than this from every wall (distParticleWall2) cannot fail d2 < dm2 nor pass M(re): its mirror is skipped
 	double invReS, invReL;
 };
 
@@ -99,7 +111,8 @@ struct pmps_handle {
 	int32_t* h_flags = nullptr;          // pinned mirror of V.flags
 	int numParticles = 0, numParticlesZero = 0;
 	bool haveState = false, haveList = false, listBuilt = false;   // haveList: bucket order valid; listBuilt: Verlet list valid
-	int nTilesAll = 0, smCount = 148;
+	int nTilesAll = 0, smCount = 148, walkSeq = 0; bool tileWallValid = false;
+	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;
 	long long launches = 0;
 	int oodTotal = 0, maxCell = 0;
@@ -134,6 +147,7 @@ struct ProfScope {
 int pmps_ensure_capacity(pmps_handle* h, int n0);
 int pmps_sort_and_list(pmps_handle* h);
 int pmps_ensure_list(pmps_handle* h);
+int pmps_tv_prepare(pmps_handle* h);
 int pmps_ppe_solve(pmps_handle* h);
 int pmps_mesh_upload(pmps_handle* h, int mesh_id, int nV, const double* V, int nF, const int32_t* F, const double* N,
                      int nTable, const double* xP, const double* xN, const double* Z, const int32_t* nW);

@@ -8,7 +8,7 @@
 // order so every later kernel reads its neighbours from nearby addresses.  Finally ONE pass over the 27 (9 in 2D)
 // surrounding buckets builds a candidate list with radius bucketSide = reL(1+CFL) in float; the ~10 neighbour passes
 // of the step walk that list (≈67 candidates) instead of re-walking 27 buckets (≈430 candidates) each.
-#include "pmps_device.cuh"
+#include "pmps_tv.cuh"
 #include <cstdio>
 
 // ---- 1. bucket id + histogram --------------------------------------------------------------------------------
@@ -16,7 +16,7 @@ __global__ void k_cell_hist(const __grid_constant__ DevView S, const __grid_cons
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= S.n0) return;
 	const double4 p = S.pos[i];
-	int cell = S.nB;   // ghosts are parked behind the last bucket (the reference skips them, src/MpsBucket.cpp:332)
+	int cell = S.nC;   // ghosts are parked behind the last cell (the reference skips them, src/MpsBucket.cpp:332)
 	if (pk_type(p) != K.p.ghost) {
 		const PmpsParams& P = K.p;
 		int ix, iy, iz = 0;
@@ -32,7 +32,7 @@ __global__ void k_cell_hist(const __grid_constant__ DevView S, const __grid_cons
 			atomicOr(&S.flags[FLAG_GUARD], 2);   // a live particle outside the bucket grid: the reference would corrupt memory here
 			ix = min(max(ix, 0), P.numBucketsX - 1); iy = min(max(iy, 0), P.numBucketsY - 1); iz = min(max(iz, 0), P.numBucketsZ - 1);
 		}
-		cell = iz * (P.numBucketsX * P.numBucketsY) + iy * P.numBucketsX + ix;
+		cell = cell_index(K, ix, iy, iz);   // tile-major: the particles of a tile end up in consecutive slots
 	}
 	newCell[i] = cell;
 	arbRank[i] = atomicAdd(&cellCount[cell], 1);
@@ -136,27 +136,26 @@ __global__ void k_permute_packs(const int32_t* __restrict__ perm, const __grid_c
 }
 
 // ---- 6. Verlet candidate list -----------------------------------------------------------------------------------
-// One WARP per slot: the lanes test 32 consecutive slots of a bucket row at a time (coalesced float4 loads) and the
-// survivors are compacted in order with a ballot, so candidates are emitted bucket row by bucket row (jz, jy outer;
-// the three x-adjacent buckets of a row are one contiguous slot range), slots ascending = the reference's traversal
-// order restricted to the list.  Row-major list: candidate k of slot i at list[i*cap + k].
+// Global-slot form of the candidate list, built ON DEMAND for the consumers that are not tile passes (PPE assembly,
+// debug hooks).  One WARP per slot: the lanes test 32 slots of a bucket at a time and the survivors are compacted in
+// order with a ballot; buckets in the reference's order (jz, jy, jx).  Row-major: candidate k of slot i at list[i*cap + k].
 __global__ void __launch_bounds__(128) k_build_list(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
 	const int i = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
 	const int lane = threadIdx.x & 31;
 	if (i >= S.n0) return;
 	const int c = S.cellOf[i];
-	if (c >= S.nB) { if (lane == 0) S.listCnt[i] = 0; return; }   // ghost
-	const int nX = K.p.numBucketsX, nY = K.p.numBucketsY, nZ = K.p.numBucketsZ, nXY = nX * nY;
-	const int cz = c / nXY, cy = (c - cz * nXY) / nX, cx = c - cz * nXY - cy * nX;
+	if (c >= S.nC) { if (lane == 0) S.listCnt[i] = 0; return; }   // ghost
+	const int nX = K.p.numBucketsX, nY = K.p.numBucketsY, nZ = K.p.numBucketsZ;
+	int cx, cy, cz; cell_coords(K, c, cx, cy, cz);
 	const float4 bi = S.bpos[i];
 	uint32_t* L = S.list + (size_t)i * (size_t)S.listCap;
 	int cnt = 0; const int cap = S.listCap;
 	const int z0 = K.p.dim == 3 ? max(cz - 1, 0) : 0, z1 = K.p.dim == 3 ? min(cz + 1, nZ - 1) : 0;
 	const int y0 = max(cy - 1, 0), y1 = min(cy + 1, nY - 1), x0 = max(cx - 1, 0), x1 = min(cx + 1, nX - 1);
 	const unsigned below = (1u << lane) - 1u;
-	for (int jz = z0; jz <= z1; jz++) for (int jy = y0; jy <= y1; jy++) {
-		const int row = jz * nXY + jy * nX;
-		const int s0 = S.cellStart[row + x0], s1 = S.cellStart[row + x1 + 1];
+	for (int jz = z0; jz <= z1; jz++) for (int jy = y0; jy <= y1; jy++) for (int jx = x0; jx <= x1; jx++) {
+		const int cj = cell_index(K, jx, jy, jz);
+		const int s0 = S.cellStart[cj], s1 = S.cellStart[cj + 1];
 		for (int base = s0; base < s1; base += 32) {
 			const int j = base + lane; bool hit = false;
 			if (j < s1) {
@@ -184,8 +183,8 @@ template <class T> static inline void swp(T& a, T& b) { T t = a; a = b; b = t; }
 
 int pmps_sort_and_list(pmps_handle* h) {
 	DevView& S = h->V; DevView& A = h->A; const KParams& K = h->K;
-	const int n0 = S.n0, nB = S.nB, T = 256;
-	CUDA_TRY(h, cudaMemsetAsync(h->cellCount, 0, sizeof(int32_t) * (size_t)(nB + 2), h->stream));
+	const int n0 = S.n0, nB = S.nC, T = 256;
+	CUDA_TRY(h, cudaMemsetAsync(h->cellCount, 0, sizeof(int32_t) * (size_t)(nB + 2), h->stream));   // nB here = cells of the tile-major index
 	LAUNCH(h, "sort.reset", k_reset_step_scalars, 1, 1, S);
 	LAUNCH(h, "sort.cell_hist", k_cell_hist, cdiv(n0, T), T, S, K, h->newCell, h->arbRank, h->cellCount);
 	const int nScan = nB + 2; const int per = SCAN_T * SCAN_ITEMS; const int nblk = cdiv(nScan, per);
@@ -231,8 +230,33 @@ int pmps_sort_and_list(pmps_handle* h) {
 
 int pmps_ensure_list(pmps_handle* h) {
 	if (h->listBuilt) return PMPS_OK;
-	LAUNCH(h, "list.build", k_build_list, cdiv((long long)h->V.n0 * 32, 128), 128, h->V, h->K);
+	DevView& S = h->V;
+	if (!S.list) {   // allocated on first use: only the PPE assembly and the debug hooks read global slot ids
+		const size_t nWarps = ((size_t)S.n0 + 31) / 32, cnt = nWarps * 32 * (size_t)S.listCap;
+		void* a = nullptr; void* b = nullptr;
+		if (cudaMalloc(&a, cnt * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&b, nWarps * 32 * sizeof(uint16_t)) != cudaSuccess)
+			return pmps_fail(h, PMPS_E_CUDA, "candidate list allocation (%zu bytes) failed: %s", cnt * 4, cudaGetErrorString(cudaGetLastError()));
+		h->allocs.push_back(a); h->allocs.push_back(b);
+		S.list = (uint32_t*)a; S.listCnt = (uint16_t*)b;
+	}
+	LAUNCH(h, "list.build", k_build_list, cdiv((long long)S.n0 * 32, 128), 128, h->V, h->K);
 	CUDA_TRY(h, cudaGetLastError());
-	h->listBuilt = true; h->V.listValid = 1;
+	h->listBuilt = true; S.listValid = 1;
+	return PMPS_OK;
+}
+
+// work items + tile-local Verlet list of the new bucket order (every neighbour pass of the step walks it)
+int pmps_tv_prepare(pmps_handle* h) {
+	DevView& S = h->V;
+	CUDA_TRY(h, cudaMemsetAsync(S.nTiles, 0, sizeof(int32_t), h->stream));
+	CUDA_TRY(h, cudaMemsetAsync(S.tileCursor, 0, sizeof(int32_t) * PMPS_CURSORS, h->stream));
+	CUDA_TRY(h, cudaMemsetAsync(S.tileWall, 0, (size_t)h->nTilesAll, h->stream));
+	h->walkSeq = 0; h->tileWallValid = false;
+	LAUNCH(h, "sort.tile_items", k_tv_items, cdiv(h->nTilesAll, 128), 128, S, h->K, h->nTilesAll);
+	const int maxM = h->K.tvMaxM;
+	const size_t smem = 16 * (size_t)maxM + (size_t)TV_NG * S.tlCap * 2;
+	CUDA_TRY(h, cudaFuncSetAttribute(k_tv_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	{ ProfScope ps_(h, "list.tile_build"); k_tv_build<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, maxM, h->walkSeq++); h->launches++; }
+	CUDA_TRY(h, cudaGetLastError());
 	return PMPS_OK;
 }

@@ -101,6 +101,7 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 	LAUNCH(h, "upload", k_set_live, 1, 1, S, a->numParticles);
 	CUDA_TRY(h, cudaGetLastError());
 	h->numParticles = a->numParticles; h->haveState = true;
+	if (a->particleNearWall) h->tileWallValid = false;
 	return PMPS_OK;
 }
 

@@ -1,0 +1,357 @@
+// pmps_tv.cuh — the tile-Verlet walker: every neighbour loop of the reference as one kernel family.
+//
+// Buckets are grouped in TILES of TX x TY x TZ buckets; the sort puts the particles of a tile in consecutive slots
+// (cell_index()).  A thread block takes one tile and copies what its particles can possibly need — the particles of the
+// (TX+2)(TY+2)(TZ+2) surrounding buckets, the HALO — into shared memory with coalesced, independent loads: a float
+// position relative to the tile origin (+ the type word), the exact FP64 position, and the neighbour fields the fused
+// bodies declare (NbFields).  Candidates come from a per-step Verlet list (k_tv_build) whose entries are 16-bit
+// indices INTO THAT STAGED HALO, so the inner loop never touches global memory:
+//   scan  : 8 lanes per particle; lane g tests candidates g, g+8, ... with the float positions (the threshold carries
+//           the float error) and the survivors of the 8 lanes are compacted into the particle's queue with a ballot;
+//   pairs : the lanes drain the queue round-robin: exact FP64 distance, the reference's predicates, the stage bodies;
+//   end   : partial sums are combined with shuffles, the first lane runs the body epilogues.
+// Consecutive candidates of a list are (nearly) consecutive staged records, so the 8 lanes of a particle read one
+// 128-byte stretch of shared memory per scan step: no bank conflicts to speak of.
+//
+// The list is valid while no particle has moved farther than (listRadius - re)/2 since the build (tracked, checked in
+// pmps_get_scalars); listRadius = bucketSide is the reference's own search slack (src/MpsBucket.cpp:23).
+#pragma once
+#include "pmps_bodies.cuh"
+
+#define TV_T 256                 // threads per block
+#define TV_G 8                   // lanes per particle
+#define TV_NG (TV_T / TV_G)      // particles per round
+#define TV_HMAX 160              // halo buckets a work item may have
+#define TV_CHUNK 64              // list entries per chunk: lane g holds entries g, g+8, ..., g+56 of the chunk in one uint4
+#define TV_SMEM_BUDGET (110 * 1024)   // dynamic shared memory per block: two blocks per SM
+
+enum { NF_VEL = 1, NF_PRESS = 2, NF_PNDI = 4, NF_RHO = 8, NF_MEU = 16, NF_CONC = 32, NF_PNDKI = 64 };
+// neighbour fields each body reads in pair() (positions and the type word are always staged)
+template <class B> struct NbFields { static constexpr unsigned value = 0; };
+template <> struct NbFields<BViscosity> { static constexpr unsigned value = NF_VEL | NF_MEU; };
+template <> struct NbFields<BWallViscosity> { static constexpr unsigned value = NF_VEL | NF_MEU; };
+template <> struct NbFields<BCollision> { static constexpr unsigned value = NF_VEL; };
+template <> struct NbFields<BPndDiffusive> { static constexpr unsigned value = NF_VEL | NF_PRESS | NF_PNDI | NF_RHO; };
+template <> struct NbFields<BWallPndDiffusive> { static constexpr unsigned value = NF_VEL | NF_PNDI; };
+template <> struct NbFields<BMeanPnd<0>> { static constexpr unsigned value = NF_PNDI; };
+template <> struct NbFields<BMeanPnd<1>> { static constexpr unsigned value = NF_PNDI; };
+template <> struct NbFields<BMeanWallPnd> { static constexpr unsigned value = NF_PNDI; };
+template <> struct NbFields<BMeanNeighFluidPnd> { static constexpr unsigned value = NF_PNDKI; };
+template <> struct NbFields<BPressMin> { static constexpr unsigned value = NF_PRESS; };
+template <> struct NbFields<BPressGradient> { static constexpr unsigned value = NF_PRESS | NF_PNDI; };
+template <> struct NbFields<BWallPressGradient> { static constexpr unsigned value = NF_PRESS | NF_PNDI; };
+template <> struct NbFields<BGradConcentration> { static constexpr unsigned value = NF_CONC; };
+template <> struct NbFields<BWallGradConcentration> { static constexpr unsigned value = NF_CONC; };
+template <> struct NbFields<BExtrapolatePress> { static constexpr unsigned value = NF_PRESS | NF_RHO; };
+template <> struct NbFields<BWallDummyVel> { static constexpr unsigned value = NF_VEL; };
+template <class... B> struct PackFields { static constexpr unsigned value = 0; };
+template <class B, class... R> struct PackFields<B, R...> { static constexpr unsigned value = NbFields<B>::value | PackFields<R...>::value; };
+// bodies that act only on particles near a polygon wall: their launches skip tiles without any (tileWall)
+template <class B, class = void> struct WallOnly { static constexpr bool value = false; };
+template <class B> struct WallOnly<B, typename B::wall_frame_tag> { static constexpr bool value = true; };
+template <class... B> struct PackWallOnly { static constexpr bool value = true; };
+template <class B, class... R> struct PackWallOnly<B, R...> { static constexpr bool value = (WallOnly<B>::value || NoPairs<B>::value) && PackWallOnly<R...>::value; };
+// (tail bodies — NoPairs — still run for every particle of a skipped tile: see the light path of k_tv)
+
+__host__ __device__ constexpr int popc8(unsigned f) { int n = 0; for (int k = 0; k < 8; k++) n += (f >> k) & 1; return n; }
+__host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes per halo record
+	return 16 + 24 + ((f & NF_VEL) ? 24 : 0) + 8 * popc8(f & ~(unsigned)NF_VEL);
+}
+#define TV_REC_MAX (16 + 24 + 24 + 8 * 3)   // the fattest pack of the step paths: F3 (vel, press, pndi, RHO)
+
+// ---- work item -> boxes ----------------------------------------------------------------------------------------
+struct TvBox {
+	int ox, oy, oz;        // bucket coordinates of the first own bucket
+	int HX, HY, HZ, HV;    // halo box extents in buckets (own extent + 2; HZ = 1 in 2D) and their product
+	int c0, c1;            // own cells [c0, c1)
+};
+__device__ __forceinline__ TvBox tv_box(const KParams& K, int item) {
+	TvBox b; const bool three = K.p.dim == 3;
+	int ex, ey, ez;
+	if (item >= 0) {
+		const int tz = item / (K.nTX * K.nTY), ty = (item - tz * K.nTX * K.nTY) / K.nTX, tx = item - (tz * K.nTY + ty) * K.nTX;
+		b.ox = tx * K.TX; b.oy = ty * K.TY; b.oz = tz * K.TZ; ex = K.TX; ey = K.TY; ez = K.TZ; b.c0 = item * K.TV; b.c1 = b.c0 + K.TV;
+	} else {
+		const int c = ~item; cell_coords(K, c, b.ox, b.oy, b.oz); ex = ey = ez = 1; b.c0 = c; b.c1 = c + 1;
+	}
+	b.HX = ex + 2; b.HY = ey + 2; b.HZ = three ? ez + 2 : 1; b.HV = b.HX * b.HY * b.HZ;
+	return b;
+}
+// cell of halo bucket hb of the box, or -1 outside the bucket grid
+__device__ __forceinline__ int tv_halo_cell(const KParams& K, const TvBox& b, int hb) {
+	const int hz = hb / (b.HX * b.HY), hy = (hb - hz * b.HX * b.HY) / b.HX, hx = hb - (hz * b.HY + hy) * b.HX;
+	const int ix = b.ox - 1 + hx, iy = b.oy - 1 + hy, iz = K.p.dim == 3 ? b.oz - 1 + hz : 0;
+	if (ix < 0 || ix >= K.p.numBucketsX || iy < 0 || iy >= K.p.numBucketsY || iz < 0 || iz >= K.p.numBucketsZ) return -1;
+	return cell_index(K, ix, iy, iz);
+}
+// halo table in shared memory: hBase[hb] first slot, hOff[hb] first staged index (hOff[HV] = staged records)
+__device__ __forceinline__ void tv_halo_table(const DevView& S, const KParams& K, const TvBox& b, int* hBase, int* hOff) {
+	const int tid = threadIdx.x;
+	if (tid < b.HV) {
+		const int c = tv_halo_cell(K, b, tid);
+		int s0 = 0, n = 0;
+		if (c >= 0) { s0 = S.cellStart[c]; n = S.cellStart[c + 1] - s0; }
+		hBase[tid] = s0; hOff[tid + 1] = n;
+	}
+	__syncthreads();
+	if (tid < 32) {   // exclusive scan of <= TV_HMAX counts by one warp: 5 consecutive entries per lane
+		constexpr int PER = (TV_HMAX + 31) / 32;
+		int v[PER]; int sum = 0;
+		#pragma unroll
+		for (int k = 0; k < PER; k++) { const int e = tid * PER + k; v[k] = e < b.HV ? hOff[e + 1] : 0; sum += v[k]; }
+		int incl = sum;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (tid >= o) incl += t; }
+		int run = incl - sum;
+		__syncwarp();
+		#pragma unroll
+		for (int k = 0; k < PER; k++) { const int e = tid * PER + k; if (e < b.HV) hOff[e] = run; run += v[k]; if (e == b.HV - 1) hOff[b.HV] = run; }
+	}
+	__syncthreads();
+}
+__device__ __forceinline__ float tv_type_word(const double4& p) { return __int_as_float((pk_type(p) & 0xffff) | (pk_ptype(p) << 16)); }
+
+// ---- work items of the current bucket order ---------------------------------------------------------------------
+// One thread per tile: a tile whose halo fits the staging area is one item; otherwise each of its non-empty buckets is.
+static __global__ void k_tv_items(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int nTilesAll) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= nTilesAll) return;
+	if (S.cellStart[(t + 1) * K.TV] == S.cellStart[t * K.TV]) return;
+	const TvBox b = tv_box(K, t);
+	int M = 0;
+	for (int hb = 0; hb < b.HV; hb++) { const int c = tv_halo_cell(K, b, hb); if (c >= 0) M += S.cellStart[c + 1] - S.cellStart[c]; }
+	if (M + 1 <= K.tvMaxM) { S.tileList[atomicAdd(S.nTiles, 1)] = t; return; }
+	for (int c = b.c0; c < b.c1; c++) if (S.cellStart[c + 1] > S.cellStart[c]) S.tileList[atomicAdd(S.nTiles, 1)] = ~c;
+}
+static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int copyPos, int copyVel) {
+	const int i = S.cellStart[S.nC] + blockIdx.x * blockDim.x + threadIdx.x;   // ghosts are parked behind the last cell
+	if (i >= S.n0) return;
+	if (copyPos) S.pos2[i] = S.pos[i];
+	if (copyVel) S.vel2[i] = S.vel[i];
+}
+
+// ---- Verlet list in tile-local indices ---------------------------------------------------------------------------
+// Same tiling as the walker.  Float positions (relative to the tile origin) of the halo are staged; the 8 lanes of a
+// particle sweep the 27 (9 in 2D) buckets around the particle's own bucket — nine (three) contiguous stretches of the
+// staged halo — and append the records within the list radius, in staged order, to the particle's list.  Entry number
+// e of a list lives at  chunk (e / 64), position (e % 8) * 8 + (e % 64) / 8  so that lane g of the walker gets entries
+// g, g+8, ... with one 128-bit load.  The unused tail of the last chunk points at the far-away dummy record (index M).
+static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+	extern __shared__ __align__(16) unsigned char smemRaw[];
+	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
+	float4* fpos = (float4*)smemRaw;
+	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)maxM) + (size_t)(threadIdx.x / TV_G) * S.tlCap;
+	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
+	const unsigned gmask = 0xffu << ((tid & 31) & ~(TV_G - 1));
+	const unsigned below = ((1u << g) - 1u) << ((tid & 31) & ~(TV_G - 1));
+	const bool three = K.p.dim == 3;
+	const int nItems = *S.nTiles;
+	for (;;) {
+		__syncthreads();
+		if (tid == 0) sItem = atomicAdd(&S.tileCursor[cursorIdx], 1);
+		__syncthreads();
+		const int tt = sItem;
+		if (tt >= nItems) break;
+		const TvBox b = tv_box(K, S.tileList[tt]);
+		tv_halo_table(S, K, b, hBase, hOff);
+		const int M = hOff[b.HV];
+		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
+		if (M + 1 > maxM) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
+			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1);
+			for (int p = tid; p < P; p += TV_T) S.tlistChunks[own0 + p] = 0;
+			continue;
+		}
+		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
+		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
+		for (int hb = tid / 16; hb < b.HV; hb += TV_T / 16) {
+			const int s0 = hBase[hb], n = hOff[hb + 1] - hOff[hb], off = hOff[hb];
+			for (int r = tid % 16; r < n; r += 16) {
+				const double4 pj = ld256(S.pos + s0 + r);
+				fpos[off + r] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), 0.f);
+			}
+		}
+		__syncthreads();
+		for (int p0 = 0; p0 < P; p0 += TV_NG) {
+			const int p = p0 + grp;
+			if (p < P) {   // uniform over the lanes of a group
+				const int i = own0 + p;
+				const int ci = S.cellOf[i];
+				int cnt = 0;
+				if (ci < S.nC) {
+					int ix, iy, iz; cell_coords(K, ci, ix, iy, iz);
+					const int hx = ix - b.ox + 1, hy = iy - b.oy + 1, hz = three ? iz - b.oz + 1 : 0;
+					const int self = hOff[(hz * b.HY + hy) * b.HX + hx] + (i - hBase[(hz * b.HY + hy) * b.HX + hx]);
+					const float4 fi = fpos[self];
+					for (int dz = three ? -1 : 0; dz <= (three ? 1 : 0); dz++) for (int dy = -1; dy <= 1; dy++) {
+						const int hb0 = ((hz + dz) * b.HY + hy + dy) * b.HX + hx - 1;
+						const int r0 = hOff[hb0], r1 = hOff[hb0 + 3];
+						for (int base = r0; base < r1; base += TV_G) {
+							const int m = base + g; bool hit = false;
+							if (m < r1) {
+								const float4 f = fpos[m];
+								const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
+								hit = dx * dx + dy2 * dy2 + dz2 * dz2 < K.rl2 && m != self;
+							}
+							const unsigned bal = __ballot_sync(gmask, hit);
+							if (hit) {
+								const int e = cnt + __popc(bal & below);
+								if (e < S.tlCap) glist[(e & ~(TV_CHUNK - 1)) + (e & 7) * 8 + ((e & (TV_CHUNK - 1)) >> 3)] = (uint16_t)m;
+							}
+							cnt += __popc(bal & gmask);
+						}
+					}
+				}
+				if (cnt > S.tlCap) { if (g == 0) atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = S.tlCap; }
+				const int nch = (cnt + TV_CHUNK - 1) / TV_CHUNK;
+				for (int e = cnt + g; e < nch * TV_CHUNK; e += TV_G) glist[(e & ~(TV_CHUNK - 1)) + (e & 7) * 8 + ((e & (TV_CHUNK - 1)) >> 3)] = (uint16_t)M;
+				__syncwarp(gmask);
+				uint4* dst = (uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap);
+				for (int ch = 0; ch < nch; ch++) dst[ch * 8 + g] = ((const uint4*)glist)[ch * 8 + g];
+				if (g == 0) S.tlistChunks[i] = (uint8_t)nch;
+				__syncwarp(gmask);
+			}
+		}
+	}
+}
+
+// ---- the walker ---------------------------------------------------------------------------------------------------
+struct TvStage {   // shared-memory planes of the staged halo
+	float4* fpos; double *px, *py, *pz; Nb nb;
+};
+template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp, int maxM) {
+	TvStage t; const size_t m = (size_t)maxM;
+	t.fpos = (float4*)sp; sp += 16 * m;
+	t.px = (double*)sp; sp += 8 * m; t.py = (double*)sp; sp += 8 * m; t.pz = (double*)sp; sp += 8 * m;
+	double *vx = nullptr, *vy = nullptr, *vz = nullptr, *pr = nullptr, *pn = nullptr, *rh = nullptr, *mu = nullptr, *cc = nullptr, *pk = nullptr;
+	if (FIELDS & NF_VEL) { vx = (double*)sp; sp += 8 * m; vy = (double*)sp; sp += 8 * m; vz = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_PRESS) { pr = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_PNDI) { pn = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_RHO) { rh = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_MEU) { mu = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_CONC) { cc = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_PNDKI) { pk = (double*)sp; sp += 8 * m; }
+	t.nb.vx = vx; t.nb.vy = vy; t.nb.vz = vz; t.nb.press = pr; t.nb.pndi = pn; t.nb.RHO = rh; t.nb.MEU = mu; t.nb.concentration = cc; t.nb.pndki = pk;
+	return t;
+}
+
+// exact pair geometry of staged record m for particle s, then the bodies
+template <bool POLY, class F>
+__device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m) {
+	Pair q; q.j = m;
+	q.rx = T.px[m] - s.pi.x; q.ry = T.py[m] - s.pi.y; q.rz = T.pz[m] - s.pi.z;
+	q.d2 = sq3_exact(q.rx, q.ry, q.rz);
+	if (!(q.d2 < K.reMax2)) return;
+	const int tw = __float_as_int(T.fpos[m].w);
+	q.tj = (int)(short)(tw & 0xffff); q.ptj = tw >> 16;
+	if (POLY && s.hasMirror) { q.mx = T.px[m] - s.mix; q.my = T.py[m] - s.miy; q.mz = T.pz[m] - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
+	else { q.mx = q.my = q.mz = 0.0; q.dm2 = __longlong_as_double(0x7ff0000000000000ll); }   // no mirror: the reference's is at "infinity" (10e8 lo)
+	q.rinv = fast_rsqrt(q.d2);
+	F::template pair<POLY>(ctx, T.nb, K, s, q);
+}
+
+template <bool POLY, unsigned FIELDS, bool WALLONLY, class F>
+__global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+	extern __shared__ __align__(16) unsigned char smemRaw[];
+	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
+	const TvStage T = tv_carve<FIELDS>(smemRaw, maxM);
+	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
+	uint16_t* gq = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + (size_t)grp * S.tlCap;   // this particle's queue
+	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
+	const unsigned gmask = 0xffu << gshift, below = ((1u << g) - 1u) << gshift;
+	const bool three = K.p.dim == 3;
+	const int nItems = *S.nTiles;
+	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
+	for (;;) {
+		__syncthreads();   // the previous item is done with the tables and the staged data
+		if (tid == 0) sItem = atomicAdd(&S.tileCursor[cursorIdx], 1);
+		__syncthreads();
+		const int tt = sItem;
+		if (tt >= nItems) break;
+		const int item = S.tileList[tt];
+		const TvBox b = tv_box(K, item);
+		if (WALLONLY) {   // no particle of this tile is near a wall: the pair bodies are idle, only the tails run (one lane per particle)
+			if (!S.tileWall[b.c0 / K.TV]) {
+				const int o0 = S.cellStart[b.c0], Pn = S.cellStart[b.c1] - o0;
+				for (int p = tid; p < Pn; p += TV_T) {
+					const int i = o0 + p;
+					Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+					s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
+					if (F::kCopyPos) S.pos2[i] = s.pi;
+					if (F::kCopyVel) S.vel2[i] = S.vel[i];
+					if (s.type == K.p.ghost) continue;
+					typename F::Ctx ctx;
+					if (F::begin(ctx, S, K, s)) F::end(ctx, S, K, s);
+				}
+				continue;   // uniform over the block
+			}
+		}
+		tv_halo_table(S, K, b, hBase, hOff);
+		const int M = hOff[b.HV];
+		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
+		if (M + 1 > maxM) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
+		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
+		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
+		// ---- stage the halo: half a warp per bucket ----
+		for (int hb = tid / 16; hb < b.HV; hb += TV_T / 16) {
+			const int s0 = hBase[hb], n = hOff[hb + 1] - hOff[hb], off = hOff[hb];
+			for (int r = tid % 16; r < n; r += 16) {
+				const int j = s0 + r, m = off + r;
+				const double4 pj = ld256(S.pos + j);
+				T.fpos[m] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), tv_type_word(pj));
+				T.px[m] = pj.x; T.py[m] = pj.y; T.pz[m] = pj.z;
+				if (FIELDS & NF_VEL) { const double4 vj = ld256(S.vel + j); ((double*)T.nb.vx)[m] = vj.x; ((double*)T.nb.vy)[m] = vj.y; ((double*)T.nb.vz)[m] = vj.z; }
+				if (FIELDS & NF_PRESS) ((double*)T.nb.press)[m] = S.press[j];
+				if (FIELDS & NF_PNDI) ((double*)T.nb.pndi)[m] = S.pndi[j];
+				if (FIELDS & NF_RHO) ((double*)T.nb.RHO)[m] = S.RHO[j];
+				if (FIELDS & NF_MEU) ((double*)T.nb.MEU)[m] = S.MEU[j];
+				if (FIELDS & NF_CONC) ((double*)T.nb.concentration)[m] = S.concentration[j];
+				if (FIELDS & NF_PNDKI) ((double*)T.nb.pndki)[m] = S.pndki[j];
+			}
+		}
+		if (tid == 0) T.fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the record list padding points at
+		__syncthreads();
+		// ---- rounds of TV_NG particles ----
+		for (int p0 = 0; p0 < P; p0 += TV_NG) {
+			const int p = p0 + grp;
+			if (p >= P) continue;   // uniform over the lanes of a group; nothing below synchronises wider than the group
+			const int i = own0 + p;
+			Self s; s.i = i; s.lead = g == 0; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+			s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
+			if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
+			if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
+			if (s.type == K.p.ghost) continue;
+			if (POLY) {
+				s.mix = S.mirrorParticlePos.x[i]; s.miy = S.mirrorParticlePos.y[i]; s.miz = S.mirrorParticlePos.z[i];
+				s.hasMirror = S.distParticleWall2[i] < K.mirrorFar2;
+			}
+			if (POLY && F::kWall) { s.nearWallFluid = s.type == K.p.fluid && S.particleNearWall[i]; if (s.nearWallFluid) self_wall_frame(s); }
+			typename F::Ctx ctx;
+			if (!F::begin(ctx, S, K, s)) continue;
+			if (F::need_pairs(ctx)) {
+				const float fx = (float)(s.pi.x - ox), fy = (float)(s.pi.y - oy), fz = (float)(s.pi.z - oz);
+				const int nch = S.tlistChunks[i];
+				const uint4* L = (const uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap) + g;
+				int qn = 0;
+				for (int ch = 0; ch < nch; ch++) {
+					const uint4 e = __ldg(L + ch * 8);
+					const unsigned w[4] = { e.x, e.y, e.z, e.w };
+					#pragma unroll
+					for (int u = 0; u < 8; u++) {
+						const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
+						const float4 f = T.fpos[m];
+						const float dx = f.x - fx, dy = f.y - fy, dz = f.z - fz;
+						const bool hit = dx * dx + dy * dy + dz * dz < rfilt2;
+						const unsigned bal = __ballot_sync(gmask, hit);
+						if (hit) gq[qn + __popc(bal & below)] = (uint16_t)m;
+						qn += __popc(bal);
+					}
+				}
+				__syncwarp(gmask);
+				for (int t = g; t < qn; t += TV_G) tv_pair<POLY, F>(ctx, T, K, s, gq[t]);
+				__syncwarp(gmask);
+			}
+			F::reduce(ctx, gmask);
+			if (s.lead) F::end(ctx, S, K, s);
+		}
+	}
+}

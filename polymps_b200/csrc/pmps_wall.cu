@@ -91,6 +91,7 @@ __global__ void __launch_bounds__(128) k_wall_closest(const __grid_constant__ De
 	const double4 pi = S.pos[i];
 	if (pk_type(pi) == K.p.ghost) return;
 	wall_closest_of(S, K, i, pi);
+	if (S.particleNearWall[i] && S.cellOf[i] < S.nC) S.tileWall[S.cellOf[i] / K.TV] = 1;   // wall-only passes skip the other tiles
 }
 
 extern "C" int pmps_wall_closest_point(pmps_t* h) {
@@ -98,7 +99,9 @@ extern "C" int pmps_wall_closest_point(pmps_t* h) {
 	cudaSetDevice(h->device);
 	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_wall_closest_point: no particle state uploaded");
 	if ((int)h->meshes.size() < h->K.p.numOfMeshs || h->K.p.numOfMeshs < 1) return pmps_fail(h, PMPS_E_STATE, "pmps_wall_closest_point: %d meshes expected, %d set", h->K.p.numOfMeshs, (int)h->meshes.size());
+	if (h->haveList) CUDA_TRY(h, cudaMemsetAsync(h->V.tileWall, 0, (size_t)h->nTilesAll, h->stream));
 	LAUNCH(h, "wall.closest_point", k_wall_closest, cdiv(h->V.n, 128), 128, h->V, h->K);
+	h->tileWallValid = h->haveList;
 	CUDA_TRY(h, cudaGetLastError());
 	return PMPS_OK;
 }
