@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(TV_T) k_debug_neighbors(const __grid_constant_
 	const uint16_t* L = S.tlist + (size_t)i * (size_t)S.tlCap;
 	int n = 0;
 	for (int e = 0; e < S.tlistChunks[i] * TV_CHUNK; e++) {
-		const int m = L[(e & ~(TV_CHUNK - 1)) + (e & 7) * 8 + ((e & (TV_CHUNK - 1)) >> 3)];
+		const int m = L[tv_list_pos(e)];
 		if (m >= M) continue;   // padding
 		int hb = 0; while (hOff[hb + 1] <= m) hb++;
 		const int j = hBase[hb] + (m - hOff[hb]);

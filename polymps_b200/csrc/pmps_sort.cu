@@ -254,7 +254,7 @@ int pmps_tv_prepare(pmps_handle* h) {
 	h->walkSeq = 0; h->tileWallValid = false;
 	LAUNCH(h, "sort.tile_items", k_tv_items, cdiv(h->nTilesAll, 128), 128, S, h->K, h->nTilesAll);
 	const int maxM = h->K.tvMaxM;
-	const size_t smem = 16 * (size_t)maxM + (size_t)TV_NG * S.tlCap * 2;
+	const size_t smem = 16 * (size_t)maxM + (size_t)(TV_T / TV_BG) * S.tlCap * 2;
 	CUDA_TRY(h, cudaFuncSetAttribute(k_tv_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 	{ ProfScope ps_(h, "list.tile_build"); k_tv_build<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, maxM, h->walkSeq++); h->launches++; }
 	CUDA_TRY(h, cudaGetLastError());

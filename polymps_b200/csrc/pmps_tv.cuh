@@ -6,12 +6,14 @@
 // position relative to the tile origin (+ the type word), the exact FP64 position, and the neighbour fields the fused
 // bodies declare (NbFields).  Candidates come from a per-step Verlet list (k_tv_build) whose entries are 16-bit
 // indices INTO THAT STAGED HALO, so the inner loop never touches global memory:
-//   scan  : 8 lanes per particle; lane g tests candidates g, g+8, ... with the float positions (the threshold carries
-//           the float error) and the survivors of the 8 lanes are compacted into the particle's queue with a ballot;
+//   scan  : TV_G lanes per particle; lane g tests candidates g, g+TV_G, ... of a 64-entry chunk with the float positions
+//           (the threshold carries the float error) and the survivors of the lanes are compacted into the particle's
+//           queue with a full-warp ballot (control flow is kept warp-uniform so the ballots need no partial masks:
+//           ncu showed partial-mask votes costing a quarter of all issued instructions);
 //   pairs : the lanes drain the queue round-robin: exact FP64 distance, the reference's predicates, the stage bodies;
 //   end   : partial sums are combined with shuffles, the first lane runs the body epilogues.
-// Consecutive candidates of a list are (nearly) consecutive staged records, so the 8 lanes of a particle read one
-// 128-byte stretch of shared memory per scan step: no bank conflicts to speak of.
+// Consecutive candidates of a list are (nearly) consecutive staged records, so the lanes of a particle read one
+// contiguous stretch of shared memory per scan step.
 //
 // The list is valid while no particle has moved farther than (listRadius - re)/2 since the build (tracked, checked in
 // pmps_get_scalars); listRadius = bucketSide is the reference's own search slack (src/MpsBucket.cpp:23).
@@ -19,11 +21,20 @@
 #include "pmps_bodies.cuh"
 
 #define TV_T 256                 // threads per block
-#define TV_G 8                   // lanes per particle
+#ifndef TV_G
+#define TV_G 4                   // lanes per particle in the walker
+#endif
 #define TV_NG (TV_T / TV_G)      // particles per round
+#define TV_BG 8                  // lanes per particle in the list build
 #define TV_HMAX 160              // halo buckets a work item may have
-#define TV_CHUNK 64              // list entries per chunk: lane g holds entries g, g+8, ..., g+56 of the chunk in one uint4
-#define TV_SMEM_BUDGET (110 * 1024)   // dynamic shared memory per block: two blocks per SM
+#define TV_CHUNK 64              // list entries per chunk: walker lane g holds entries g, g+TV_G, ... of the chunk, contiguously
+#define TV_PER (TV_CHUNK / TV_G) // entries per lane and chunk
+#define TV_MAXOWN 1024           // particles a work item may own (ownMap)
+#define TV_SMEM_BUDGET (111 * 1024)   // dynamic shared memory per block: two blocks per SM
+// fixed dynamic shared memory of the walker besides the staged records: the queues (one chunk per particle) + ownMap
+#define TV_FIXED_BYTES (TV_NG * TV_CHUNK * 2 + TV_MAXOWN * 2)
+// position of list entry e inside the particle's list: chunk-major, then lane-major
+__host__ __device__ __forceinline__ int tv_list_pos(int e) { const int w = e & (TV_CHUNK - 1); return (e & ~(TV_CHUNK - 1)) + (w % TV_G) * TV_PER + w / TV_G; }
 
 enum { NF_VEL = 1, NF_PRESS = 2, NF_PNDI = 4, NF_RHO = 8, NF_MEU = 16, NF_CONC = 32, NF_PNDKI = 64 };
 // neighbour fields each body reads in pair() (positions and the type word are always staged)
@@ -130,20 +141,22 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 	if (copyVel) S.vel2[i] = S.vel[i];
 }
 
+
 // ---- Verlet list in tile-local indices ---------------------------------------------------------------------------
-// Same tiling as the walker.  Float positions (relative to the tile origin) of the halo are staged; the 8 lanes of a
+// Same tiling as the walker.  Float positions (relative to the tile origin) of the halo are staged; TV_BG lanes per
 // particle sweep the 27 (9 in 2D) buckets around the particle's own bucket — nine (three) contiguous stretches of the
-// staged halo — and append the records within the list radius, in staged order, to the particle's list.  Entry number
-// e of a list lives at  chunk (e / 64), position (e % 8) * 8 + (e % 64) / 8  so that lane g of the walker gets entries
-// g, g+8, ... with one 128-bit load.  The unused tail of the last chunk points at the far-away dummy record (index M).
+// staged halo — and append the records within the list radius, in staged order, to the particle's list (tv_list_pos()).
+// The unused tail of the last chunk points at the far-away dummy record (index M).  Control flow is warp-uniform
+// (trip counts are the maximum over the warp) so the ballots run with the full mask.
 static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
+	constexpr int NGB = TV_T / TV_BG;   // particles per round
 	float4* fpos = (float4*)smemRaw;
-	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)maxM) + (size_t)(threadIdx.x / TV_G) * S.tlCap;
-	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
-	const unsigned gmask = 0xffu << ((tid & 31) & ~(TV_G - 1));
-	const unsigned below = ((1u << g) - 1u) << ((tid & 31) & ~(TV_G - 1));
+	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)maxM) + (size_t)(threadIdx.x / TV_BG) * S.tlCap;
+	const int tid = threadIdx.x, grp = tid / TV_BG, g = tid % TV_BG;
+	const unsigned gshift = (tid & 31) & ~(TV_BG - 1);
+	const unsigned gbits = (1u << TV_BG) - 1u, lower = (1u << g) - 1u;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
 	for (;;) {
@@ -156,8 +169,8 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 		tv_halo_table(S, K, b, hBase, hOff);
 		const int M = hOff[b.HV];
 		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
-		if (M + 1 > maxM) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
-			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1);
+		if (M + 1 > maxM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
+			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1 > maxM ? M + 1 : P);
 			for (int p = tid; p < P; p += TV_T) S.tlistChunks[own0 + p] = 0;
 			continue;
 		}
@@ -171,45 +184,49 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 			}
 		}
 		__syncthreads();
-		for (int p0 = 0; p0 < P; p0 += TV_NG) {
+		for (int p0 = 0; p0 < P; p0 += NGB) {   // uniform over the block
 			const int p = p0 + grp;
-			if (p < P) {   // uniform over the lanes of a group
-				const int i = own0 + p;
-				const int ci = S.cellOf[i];
-				int cnt = 0;
-				if (ci < S.nC) {
-					int ix, iy, iz; cell_coords(K, ci, ix, iy, iz);
-					const int hx = ix - b.ox + 1, hy = iy - b.oy + 1, hz = three ? iz - b.oz + 1 : 0;
-					const int self = hOff[(hz * b.HY + hy) * b.HX + hx] + (i - hBase[(hz * b.HY + hy) * b.HX + hx]);
-					const float4 fi = fpos[self];
-					for (int dz = three ? -1 : 0; dz <= (three ? 1 : 0); dz++) for (int dy = -1; dy <= 1; dy++) {
-						const int hb0 = ((hz + dz) * b.HY + hy + dy) * b.HX + hx - 1;
-						const int r0 = hOff[hb0], r1 = hOff[hb0 + 3];
-						for (int base = r0; base < r1; base += TV_G) {
-							const int m = base + g; bool hit = false;
-							if (m < r1) {
-								const float4 f = fpos[m];
-								const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
-								hit = dx * dx + dy2 * dy2 + dz2 * dz2 < K.rl2 && m != self;
-							}
-							const unsigned bal = __ballot_sync(gmask, hit);
-							if (hit) {
-								const int e = cnt + __popc(bal & below);
-								if (e < S.tlCap) glist[(e & ~(TV_CHUNK - 1)) + (e & 7) * 8 + ((e & (TV_CHUNK - 1)) >> 3)] = (uint16_t)m;
-							}
-							cnt += __popc(bal & gmask);
-						}
+			const bool act = p < P;
+			const int i = own0 + (act ? p : 0);
+			int hx = 1, hy = 1, hz = three ? 1 : 0, self = 0;
+			float4 fi = make_float4(0.f, 0.f, 0.f, 0.f);
+			if (act) {
+				int ix, iy, iz; cell_coords(K, S.cellOf[i], ix, iy, iz);
+				hx = ix - b.ox + 1; hy = iy - b.oy + 1; hz = three ? iz - b.oz + 1 : 0;
+				const int hbs = (hz * b.HY + hy) * b.HX + hx;
+				self = hOff[hbs] + (i - hBase[hbs]);
+				fi = fpos[self];
+			}
+			int cnt = 0;
+			for (int dz = three ? -1 : 0; dz <= (three ? 1 : 0); dz++) for (int dy = -1; dy <= 1; dy++) {
+				const int hb0 = ((hz + dz) * b.HY + hy + dy) * b.HX + hx - 1;
+				const int r0 = hOff[hb0], r1 = act ? hOff[hb0 + 3] : r0;
+				const int trips = __reduce_max_sync(0xffffffffu, (r1 - r0 + TV_BG - 1) / TV_BG);
+				for (int k = 0; k < trips; k++) {
+					const int m = r0 + k * TV_BG + g; bool hit = false;
+					if (m < r1) {
+						const float4 f = fpos[m];
+						const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
+						hit = dx * dx + dy2 * dy2 + dz2 * dz2 < K.rl2 && m != self;
 					}
+					const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
+					if (hit) { const int e = cnt + __popc(gb & lower); if (e < S.tlCap) glist[tv_list_pos(e)] = (uint16_t)m; }
+					cnt += __popc(gb);
 				}
+			}
+			if (act) {
 				if (cnt > S.tlCap) { if (g == 0) atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = S.tlCap; }
 				const int nch = (cnt + TV_CHUNK - 1) / TV_CHUNK;
-				for (int e = cnt + g; e < nch * TV_CHUNK; e += TV_G) glist[(e & ~(TV_CHUNK - 1)) + (e & 7) * 8 + ((e & (TV_CHUNK - 1)) >> 3)] = (uint16_t)M;
-				__syncwarp(gmask);
-				uint4* dst = (uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap);
-				for (int ch = 0; ch < nch; ch++) dst[ch * 8 + g] = ((const uint4*)glist)[ch * 8 + g];
-				if (g == 0) S.tlistChunks[i] = (uint8_t)nch;
-				__syncwarp(gmask);
+				for (int e = cnt + g; e < nch * TV_CHUNK; e += TV_BG) glist[tv_list_pos(e)] = (uint16_t)M;
 			}
+			__syncwarp();
+			if (act) {
+				const int nch = (cnt + TV_CHUNK - 1) / TV_CHUNK;
+				uint4* dst = (uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap);
+				for (int q = g; q < nch * (TV_CHUNK / 8); q += TV_BG) dst[q] = ((const uint4*)glist)[q];
+				if (g == 0) S.tlistChunks[i] = (uint8_t)nch;
+			}
+			__syncwarp();
 		}
 	}
 }
@@ -238,16 +255,18 @@ template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned 
 template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m) {
 	Pair q; q.j = m;
-	q.rx = T.px[m] - s.pi.x; q.ry = T.py[m] - s.pi.y; q.rz = T.pz[m] - s.pi.z;
+	const double xj = T.px[m], yj = T.py[m], zj = T.pz[m];
+	q.rx = xj - s.pi.x; q.ry = yj - s.pi.y; q.rz = zj - s.pi.z;
 	q.d2 = sq3_exact(q.rx, q.ry, q.rz);
 	if (!(q.d2 < K.reMax2)) return;
 	const int tw = __float_as_int(T.fpos[m].w);
 	q.tj = (int)(short)(tw & 0xffff); q.ptj = tw >> 16;
-	if (POLY && s.hasMirror) { q.mx = T.px[m] - s.mix; q.my = T.py[m] - s.miy; q.mz = T.pz[m] - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
-	else { q.mx = q.my = q.mz = 0.0; q.dm2 = __longlong_as_double(0x7ff0000000000000ll); }   // no mirror: the reference's is at "infinity" (10e8 lo)
+	if (POLY && s.hasMirror) { q.mx = xj - s.mix; q.my = yj - s.miy; q.mz = zj - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
+	else { q.mx = q.my = q.mz = 0.0; q.dm2 = __longlong_as_double(0x7ff0000000000000ll); }   // no mirror in reach: d2 < dm2 holds, M(re) fails (pmps_internal.h, mirrorFar2)
 	q.rinv = fast_rsqrt(q.d2);
 	F::template pair<POLY>(ctx, T.nb, K, s, q);
 }
+__device__ __forceinline__ void tv_prefetch(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
 template <bool POLY, unsigned FIELDS, bool WALLONLY, class F>
 __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
@@ -255,9 +274,10 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
 	const TvStage T = tv_carve<FIELDS>(smemRaw, maxM);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
-	uint16_t* gq = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + (size_t)grp * S.tlCap;   // this particle's queue
+	uint16_t* gq = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + grp * TV_CHUNK;   // this particle's queue: one chunk
+	uint16_t* ownMap = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + TV_NG * TV_CHUNK;   // own particle -> staged index
 	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
-	const unsigned gmask = 0xffu << gshift, below = ((1u << g) - 1u) << gshift;
+	const unsigned gbits = (1u << TV_G) - 1u, lower = (1u << g) - 1u, gmask = gbits << gshift;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
 	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
@@ -288,17 +308,19 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 		tv_halo_table(S, K, b, hBase, hOff);
 		const int M = hOff[b.HV];
 		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
-		if (M + 1 > maxM) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
+		if (M + 1 > maxM || P > TV_MAXOWN) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
 		// ---- stage the halo: half a warp per bucket ----
 		for (int hb = tid / 16; hb < b.HV; hb += TV_T / 16) {
 			const int s0 = hBase[hb], n = hOff[hb + 1] - hOff[hb], off = hOff[hb];
+			const bool own = s0 >= own0 && s0 < own0 + P;
 			for (int r = tid % 16; r < n; r += 16) {
 				const int j = s0 + r, m = off + r;
 				const double4 pj = ld256(S.pos + j);
 				T.fpos[m] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), tv_type_word(pj));
 				T.px[m] = pj.x; T.py[m] = pj.y; T.pz[m] = pj.z;
+				if (own) ownMap[j - own0] = (uint16_t)m;
 				if (FIELDS & NF_VEL) { const double4 vj = ld256(S.vel + j); ((double*)T.nb.vx)[m] = vj.x; ((double*)T.nb.vy)[m] = vj.y; ((double*)T.nb.vz)[m] = vj.z; }
 				if (FIELDS & NF_PRESS) ((double*)T.nb.press)[m] = S.press[j];
 				if (FIELDS & NF_PNDI) ((double*)T.nb.pndi)[m] = S.pndi[j];
@@ -309,49 +331,75 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 			}
 		}
 		if (tid == 0) T.fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the record list padding points at
+		// first round's lists on their way while the staging loads land
+		if (grp < P) { const char* L0 = (const char*)(S.tlist + (size_t)(own0 + grp) * (size_t)S.tlCap); tv_prefetch(L0 + g * (2 * TV_PER)); }
 		__syncthreads();
-		// ---- rounds of TV_NG particles ----
+		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask ballots) ----
 		for (int p0 = 0; p0 < P; p0 += TV_NG) {
 			const int p = p0 + grp;
-			if (p >= P) continue;   // uniform over the lanes of a group; nothing below synchronises wider than the group
-			const int i = own0 + p;
+			bool act = p < P;
+			const int i = own0 + (act ? p : 0);
+			if (p + TV_NG < P) {   // next round's list and flags on their way to L1
+				const char* Ln = (const char*)(S.tlist + (size_t)(i + TV_NG) * (size_t)S.tlCap);
+				tv_prefetch(Ln + g * (2 * TV_PER)); tv_prefetch(Ln + TV_CHUNK * 2 + g * (2 * TV_PER));
+			}
 			Self s; s.i = i; s.lead = g == 0; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
-			s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
-			if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
-			if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
-			if (s.type == K.p.ghost) continue;
-			if (POLY) {
-				s.mix = S.mirrorParticlePos.x[i]; s.miy = S.mirrorParticlePos.y[i]; s.miz = S.mirrorParticlePos.z[i];
-				s.hasMirror = S.distParticleWall2[i] < K.mirrorFar2;
+			s.type = K.p.ghost; s.ptype = 0;
+			int nch = 0;
+			if (act) {
+				nch = S.tlistChunks[i];
+				const int ms = ownMap[p];
+				const int tw = __float_as_int(T.fpos[ms].w);
+				s.type = (int)(short)(tw & 0xffff); s.ptype = tw >> 16;
+				s.pi.x = T.px[ms]; s.pi.y = T.py[ms]; s.pi.z = T.pz[ms]; s.pi.w = pk_make(s.type, s.ptype);
+				if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
+				if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
+				act = s.type != K.p.ghost;
 			}
-			if (POLY && F::kWall) { s.nearWallFluid = s.type == K.p.fluid && S.particleNearWall[i]; if (s.nearWallFluid) self_wall_frame(s); }
 			typename F::Ctx ctx;
-			if (!F::begin(ctx, S, K, s)) continue;
-			if (F::need_pairs(ctx)) {
-				const float fx = (float)(s.pi.x - ox), fy = (float)(s.pi.y - oy), fz = (float)(s.pi.z - oz);
-				const int nch = S.tlistChunks[i];
-				const uint4* L = (const uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap) + g;
-				int qn = 0;
-				for (int ch = 0; ch < nch; ch++) {
-					const uint4 e = __ldg(L + ch * 8);
-					const unsigned w[4] = { e.x, e.y, e.z, e.w };
-					#pragma unroll
-					for (int u = 0; u < 8; u++) {
-						const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
-						const float4 f = T.fpos[m];
-						const float dx = f.x - fx, dy = f.y - fy, dz = f.z - fz;
-						const bool hit = dx * dx + dy * dy + dz * dz < rfilt2;
-						const unsigned bal = __ballot_sync(gmask, hit);
-						if (hit) gq[qn + __popc(bal & below)] = (uint16_t)m;
-						qn += __popc(bal);
-					}
+			bool pairs = false;
+			if (act) {
+				if (POLY) {
+					s.hasMirror = S.distParticleWall2[i] < K.mirrorFar2;
+					if (s.hasMirror) { s.mix = S.mirrorParticlePos.x[i]; s.miy = S.mirrorParticlePos.y[i]; s.miz = S.mirrorParticlePos.z[i]; }
+					else { s.mix = s.miy = s.miz = K.big; }
 				}
-				__syncwarp(gmask);
-				for (int t = g; t < qn; t += TV_G) tv_pair<POLY, F>(ctx, T, K, s, gq[t]);
-				__syncwarp(gmask);
+				if (POLY && F::kWall) { s.nearWallFluid = s.type == K.p.fluid && S.particleNearWall[i]; if (s.nearWallFluid) self_wall_frame(s); }
+				act = F::begin(ctx, S, K, s);
+				pairs = act && F::need_pairs(ctx);
 			}
-			F::reduce(ctx, gmask);
-			if (s.lead) F::end(ctx, S, K, s);
+			if (!pairs) nch = 0;
+			const float fx = pairs ? (float)(s.pi.x - ox) : 0.f, fy = pairs ? (float)(s.pi.y - oy) : 0.f, fz = pairs ? (float)(s.pi.z - oz) : 0.f;
+			const uint4* L = (const uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);
+			const int nchW = __reduce_max_sync(0xffffffffu, nch);
+			for (int ch = 0; ch < nchW; ch++) {
+				unsigned w[TV_PER / 2];
+				if (ch < nch) {
+					#pragma unroll
+					for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(L + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
+				} else {
+					#pragma unroll
+					for (int v = 0; v < TV_PER / 2; v++) w[v] = (unsigned)M * 0x10001u;
+				}
+				int qn = 0;
+				#pragma unroll
+				for (int u = 0; u < TV_PER; u++) {
+					const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
+					const float4 f = T.fpos[m];
+					const float dx = f.x - fx, dy = f.y - fy, dz = f.z - fz;
+					const bool hit = dx * dx + dy * dy + dz * dz < rfilt2;
+					const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
+					if (hit) gq[qn + __popc(gb & lower)] = (uint16_t)m;
+					qn += __popc(gb);
+				}
+				__syncwarp();
+				for (int t = g; t < qn; t += TV_G) tv_pair<POLY, F>(ctx, T, K, s, gq[t]);
+				__syncwarp();
+			}
+			if (act) {
+				F::reduce(ctx, gmask);
+				if (s.lead) F::end(ctx, S, K, s);
+			}
 		}
 	}
 }
