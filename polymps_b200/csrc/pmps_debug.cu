@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(TV_T) k_debug_neighbors(const __grid_constant_
 	const double mix = POLY ? S.mirrorParticlePos.x[i] : 0.0, miy = POLY ? S.mirrorParticlePos.y[i] : 0.0, miz = POLY ? S.mirrorParticlePos.z[i] : 0.0;
 	const uint16_t* L = S.tlist + (size_t)i * (size_t)S.tlCap;
 	int n = 0;
-	for (int e = 0; e < S.tlistChunks[i] * TV_CHUNK; e++) {
+	for (int e = 0; e < S.tlistCnt[i]; e++) {
 		const int m = L[tv_list_pos(e)];
 		if (m >= M) continue;   // padding
 		int hb = 0; while (hOff[hb + 1] <= m) hb++;

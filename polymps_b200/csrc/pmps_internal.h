@@ -34,7 +34,8 @@ struct DevView {
 	int32_t* cellOf;                     // slot -> bucket id at the last rebuild
 	int32_t* cellStart;                  // nC+2, slots of cell c (tile-major bucket index, cell_index()) are [cellStart[c], cellStart[c+1]); cell nC = ghosts
 	uint32_t* list; uint16_t* listCnt;   // Verlet candidates (slot ids), row-major, listCap per particle; built on demand
-	uint16_t* tlist; uint8_t* tlistChunks;   // tile-local candidates: tlCap entries per slot in chunks of 64 (interleaved by 8), chunks used
+	uint16_t* tlist; uint16_t* tlistCnt;   // tile-local Verlet candidates: tlCap entries per slot in chunks of 64 (tv_list_pos), entries used
+	uint16_t* hlist; uint16_t* hcnt;       // hit list: the candidates within reach at the positions of the current epoch (same layout)
 	uint8_t* particleNearWall;
 	double* scratch1;                    // per-slot scratch (Pmin of the gradient passes); not a reference field
 #define X(n) int32_t* n;
@@ -112,6 +113,7 @@ struct pmps_handle {
 	int numParticles = 0, numParticlesZero = 0;
 	bool haveState = false, haveList = false, listBuilt = false;   // haveList: bucket order valid; listBuilt: Verlet list valid
 	int nTilesAll = 0, smCount = 148, walkSeq = 0; bool tileWallValid = false;
+	bool hitValid = false;               // hlist matches the current positions (set by the list build / k_tv_hits, cleared when positions change)
 	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;
 	long long launches = 0;
@@ -148,6 +150,7 @@ int pmps_ensure_capacity(pmps_handle* h, int n0);
 int pmps_sort_and_list(pmps_handle* h);
 int pmps_ensure_list(pmps_handle* h);
 int pmps_tv_prepare(pmps_handle* h);
+int pmps_tv_hits(pmps_handle* h);
 int pmps_ppe_solve(pmps_handle* h);
 int pmps_mesh_upload(pmps_handle* h, int mesh_id, int nV, const double* V, int nF, const int32_t* F, const double* N,
                      int nTable, const double* xP, const double* xN, const double* Z, const int32_t* nW);

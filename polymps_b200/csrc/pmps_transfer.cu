@@ -102,6 +102,7 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 	CUDA_TRY(h, cudaGetLastError());
 	h->numParticles = a->numParticles; h->haveState = true;
 	if (a->particleNearWall) h->tileWallValid = false;
+	if (a->pos) h->hitValid = false;
 	return PMPS_OK;
 }
 

@@ -32,7 +32,7 @@
 #define TV_MAXOWN 1024           // particles a work item may own (ownMap)
 #define TV_SMEM_BUDGET (111 * 1024)   // dynamic shared memory per block: two blocks per SM
 // fixed dynamic shared memory of the walker besides the staged records: the queues (one chunk per particle) + ownMap
-#define TV_FIXED_BYTES (TV_NG * TV_CHUNK * 2 + TV_MAXOWN * 2)
+#define TV_FIXED_BYTES(follow) (((follow) ? 0 : TV_NG * TV_CHUNK * 2) + TV_MAXOWN * 2)
 // position of list entry e inside the particle's list: chunk-major, then lane-major
 __host__ __device__ __forceinline__ int tv_list_pos(int e) { const int w = e & (TV_CHUNK - 1); return (e & ~(TV_CHUNK - 1)) + (w % TV_G) * TV_PER + w / TV_G; }
 
@@ -154,6 +154,8 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 	constexpr int NGB = TV_T / TV_BG;   // particles per round
 	float4* fpos = (float4*)smemRaw;
 	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)maxM) + (size_t)(threadIdx.x / TV_BG) * S.tlCap;
+	uint16_t* hl = glist + (size_t)NGB * S.tlCap;   // hit list of the build positions (epoch of the first passes of the step)
+	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
 	const int tid = threadIdx.x, grp = tid / TV_BG, g = tid % TV_BG;
 	const unsigned gshift = (tid & 31) & ~(TV_BG - 1);
 	const unsigned gbits = (1u << TV_BG) - 1u, lower = (1u << g) - 1u;
@@ -171,7 +173,7 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
 		if (M + 1 > maxM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
 			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1 > maxM ? M + 1 : P);
-			for (int p = tid; p < P; p += TV_T) S.tlistChunks[own0 + p] = 0;
+			for (int p = tid; p < P; p += TV_T) { S.tlistCnt[own0 + p] = 0; S.hcnt[own0 + p] = 0; }
 			continue;
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
@@ -197,21 +199,25 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 				self = hOff[hbs] + (i - hBase[hbs]);
 				fi = fpos[self];
 			}
-			int cnt = 0;
+			int cnt = 0, cntH = 0;
 			for (int dz = three ? -1 : 0; dz <= (three ? 1 : 0); dz++) for (int dy = -1; dy <= 1; dy++) {
 				const int hb0 = ((hz + dz) * b.HY + hy + dy) * b.HX + hx - 1;
 				const int r0 = hOff[hb0], r1 = act ? hOff[hb0 + 3] : r0;
 				const int trips = __reduce_max_sync(0xffffffffu, (r1 - r0 + TV_BG - 1) / TV_BG);
 				for (int k = 0; k < trips; k++) {
-					const int m = r0 + k * TV_BG + g; bool hit = false;
+					const int m = r0 + k * TV_BG + g; bool hit = false, hitH = false;
 					if (m < r1) {
 						const float4 f = fpos[m];
 						const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
-						hit = dx * dx + dy2 * dy2 + dz2 * dz2 < K.rl2 && m != self;
+						const float d2 = dx * dx + dy2 * dy2 + dz2 * dz2;
+						hit = d2 < K.rl2 && m != self; hitH = hit && d2 < rfilt2;
 					}
 					const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
 					if (hit) { const int e = cnt + __popc(gb & lower); if (e < S.tlCap) glist[tv_list_pos(e)] = (uint16_t)m; }
 					cnt += __popc(gb);
+					const unsigned gh = (__ballot_sync(0xffffffffu, hitH) >> gshift) & gbits;
+					if (hitH) { const int e = cntH + __popc(gh & lower); if (e < S.tlCap) hl[tv_list_pos(e)] = (uint16_t)m; }
+					cntH += __popc(gh);
 				}
 			}
 			if (act) {
@@ -224,7 +230,10 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 				const int nch = (cnt + TV_CHUNK - 1) / TV_CHUNK;
 				uint4* dst = (uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap);
 				for (int q = g; q < nch * (TV_CHUNK / 8); q += TV_BG) dst[q] = ((const uint4*)glist)[q];
-				if (g == 0) S.tlistChunks[i] = (uint8_t)nch;
+				if (cntH > S.tlCap) cntH = S.tlCap;
+				uint4* dstH = (uint4*)(S.hlist + (size_t)i * (size_t)S.tlCap);
+				for (int q = g; q < (cntH + TV_CHUNK - 1) / TV_CHUNK * (TV_CHUNK / 8); q += TV_BG) dstH[q] = ((const uint4*)hl)[q];
+				if (g == 0) { S.tlistCnt[i] = (uint16_t)cnt; S.hcnt[i] = (uint16_t)cntH; }
 			}
 			__syncwarp();
 		}
@@ -268,14 +277,17 @@ __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, 
 }
 __device__ __forceinline__ void tv_prefetch(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
-template <bool POLY, unsigned FIELDS, bool WALLONLY, class F>
+// FOLLOW: the candidates are the particle's HIT list (k_tv_hits / k_tv_build: the Verlet candidates within reach at the
+// positions of the current epoch), every lane just takes its share — no scan, no queue, no votes.  Otherwise the Verlet
+// list itself is scanned with the float positions and the survivors are queued (used when no hit list is valid).
+template <bool POLY, unsigned FIELDS, bool WALLONLY, bool FOLLOW, class F>
 __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
 	const TvStage T = tv_carve<FIELDS>(smemRaw, maxM);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
 	uint16_t* gq = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + grp * TV_CHUNK;   // this particle's queue: one chunk
-	uint16_t* ownMap = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + TV_NG * TV_CHUNK;   // own particle -> staged index
+	uint16_t* ownMap = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + (FOLLOW ? 0 : TV_NG * TV_CHUNK);   // own particle -> staged index
 	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
 	const unsigned gbits = (1u << TV_G) - 1u, lower = (1u << g) - 1u, gmask = gbits << gshift;
 	const bool three = K.p.dim == 3;
@@ -332,7 +344,8 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 		}
 		if (tid == 0) T.fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the record list padding points at
 		// first round's lists on their way while the staging loads land
-		if (grp < P) { const char* L0 = (const char*)(S.tlist + (size_t)(own0 + grp) * (size_t)S.tlCap); tv_prefetch(L0 + g * (2 * TV_PER)); }
+		const uint16_t* const LIST = FOLLOW ? S.hlist : S.tlist;
+		if (grp < P) { const char* L0 = (const char*)(LIST + (size_t)(own0 + grp) * (size_t)S.tlCap); tv_prefetch(L0 + g * (2 * TV_PER)); }
 		__syncthreads();
 		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask ballots) ----
 		for (int p0 = 0; p0 < P; p0 += TV_NG) {
@@ -340,14 +353,14 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 			bool act = p < P;
 			const int i = own0 + (act ? p : 0);
 			if (p + TV_NG < P) {   // next round's list and flags on their way to L1
-				const char* Ln = (const char*)(S.tlist + (size_t)(i + TV_NG) * (size_t)S.tlCap);
-				tv_prefetch(Ln + g * (2 * TV_PER)); tv_prefetch(Ln + TV_CHUNK * 2 + g * (2 * TV_PER));
+				const char* Ln = (const char*)(LIST + (size_t)(i + TV_NG) * (size_t)S.tlCap);
+				tv_prefetch(Ln + g * (2 * TV_PER)); if (!FOLLOW) tv_prefetch(Ln + TV_CHUNK * 2 + g * (2 * TV_PER));
 			}
 			Self s; s.i = i; s.lead = g == 0; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
 			s.type = K.p.ghost; s.ptype = 0;
-			int nch = 0;
+			int cntE = 0;
 			if (act) {
-				nch = S.tlistChunks[i];
+				cntE = FOLLOW ? S.hcnt[i] : S.tlistCnt[i];
 				const int ms = ownMap[p];
 				const int tw = __float_as_int(T.fpos[ms].w);
 				s.type = (int)(short)(tw & 0xffff); s.ptype = tw >> 16;
@@ -368,38 +381,141 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 				act = F::begin(ctx, S, K, s);
 				pairs = act && F::need_pairs(ctx);
 			}
-			if (!pairs) nch = 0;
-			const float fx = pairs ? (float)(s.pi.x - ox) : 0.f, fy = pairs ? (float)(s.pi.y - oy) : 0.f, fz = pairs ? (float)(s.pi.z - oz) : 0.f;
+			if (!pairs) cntE = 0;
+			const uint4* L = (const uint4*)(LIST + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);
+			if (FOLLOW) {
+				for (int ch = 0; ch * TV_CHUNK < cntE; ch++) {
+					unsigned w[TV_PER / 2];
+					#pragma unroll
+					for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(L + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
+					const int rem = cntE - ch * TV_CHUNK - g;   // entries u * TV_G + g of this chunk exist for u * TV_G < rem
+					#pragma unroll
+					for (int u = 0; u < TV_PER; u++) {
+						if (u * TV_G < rem) tv_pair<POLY, F>(ctx, T, K, s, (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu));
+					}
+				}
+			} else {
+				const float fx = pairs ? (float)(s.pi.x - ox) : 0.f, fy = pairs ? (float)(s.pi.y - oy) : 0.f, fz = pairs ? (float)(s.pi.z - oz) : 0.f;
+				const int nchW = __reduce_max_sync(0xffffffffu, (cntE + TV_CHUNK - 1) / TV_CHUNK);
+				for (int ch = 0; ch < nchW; ch++) {
+					unsigned w[TV_PER / 2];
+					const int rem = cntE - ch * TV_CHUNK;
+					if (rem > 0) {
+						#pragma unroll
+						for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(L + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
+					} else {
+						#pragma unroll
+						for (int v = 0; v < TV_PER / 2; v++) w[v] = (unsigned)M * 0x10001u;
+					}
+					const int tripsW = (min(__reduce_max_sync(0xffffffffu, rem), TV_CHUNK) + TV_G - 1) / TV_G;   // the tail of a chunk is padding
+					int qn = 0;
+					#pragma unroll
+					for (int u = 0; u < TV_PER; u++) {
+						if (u < tripsW) {   // uniform over the warp
+							const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
+							const float4 f = T.fpos[m];
+							const float dx = f.x - fx, dy = f.y - fy, dz = f.z - fz;
+							const bool hit = dx * dx + dy * dy + dz * dz < rfilt2;
+							const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
+							if (hit) gq[qn + __popc(gb & lower)] = (uint16_t)m;
+							qn += __popc(gb);
+						}
+					}
+					__syncwarp();
+					for (int t = g; t < qn; t += TV_G) tv_pair<POLY, F>(ctx, T, K, s, gq[t]);
+					__syncwarp();
+				}
+			}
+			if (act) {
+				F::reduce(ctx, gmask);
+				if (s.lead) F::end(ctx, S, K, s);
+			}
+		}
+	}
+}
+
+// ---- hit list of a new position epoch ------------------------------------------------------------------------------
+// After the positions changed (prediction, correction) the Verlet candidates are filtered ONCE with the float positions
+// of the new epoch; every neighbour pass until the next change then follows the hit list (k_tv, FOLLOW).  Stages only the
+// float positions (16 bytes per halo record); same warp-uniform scan as the walker's scanning mode.
+static __global__ void __launch_bounds__(TV_T) k_tv_hits(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+	extern __shared__ __align__(16) unsigned char smemRaw[];
+	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
+	float4* fpos = (float4*)smemRaw;
+	uint16_t* ownMap = (uint16_t*)(smemRaw + 16 * (size_t)maxM);
+	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
+	uint16_t* hl = ownMap + TV_MAXOWN + (size_t)grp * S.tlCap;
+	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
+	const unsigned gbits = (1u << TV_G) - 1u, lower = (1u << g) - 1u;
+	const bool three = K.p.dim == 3;
+	const int nItems = *S.nTiles;
+	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
+	for (;;) {
+		__syncthreads();
+		if (tid == 0) sItem = atomicAdd(&S.tileCursor[cursorIdx], 1);
+		__syncthreads();
+		const int tt = sItem;
+		if (tt >= nItems) break;
+		const TvBox b = tv_box(K, S.tileList[tt]);
+		tv_halo_table(S, K, b, hBase, hOff);
+		const int M = hOff[b.HV];
+		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
+		if (M + 1 > maxM || P > TV_MAXOWN) continue;   // reported by k_tv_build
+		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
+		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
+		for (int hb = tid / 16; hb < b.HV; hb += TV_T / 16) {
+			const int s0 = hBase[hb], n = hOff[hb + 1] - hOff[hb], off = hOff[hb];
+			const bool own = s0 >= own0 && s0 < own0 + P;
+			for (int r = tid % 16; r < n; r += 16) {
+				const double4 pj = ld256(S.pos + s0 + r);
+				fpos[off + r] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), 0.f);
+				if (own) ownMap[s0 + r - own0] = (uint16_t)(off + r);
+			}
+		}
+		if (tid == 0) fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);
+		__syncthreads();
+		for (int p0 = 0; p0 < P; p0 += TV_NG) {
+			const int p = p0 + grp;
+			const bool act = p < P;
+			const int i = own0 + (act ? p : 0);
+			int cntE = 0; float4 fi = make_float4(0.f, 0.f, 0.f, 0.f);
+			if (act) { cntE = S.tlistCnt[i]; fi = fpos[ownMap[p]]; }
 			const uint4* L = (const uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);
-			const int nchW = __reduce_max_sync(0xffffffffu, nch);
+			const int nchW = __reduce_max_sync(0xffffffffu, (cntE + TV_CHUNK - 1) / TV_CHUNK);
+			int cntH = 0;
 			for (int ch = 0; ch < nchW; ch++) {
 				unsigned w[TV_PER / 2];
-				if (ch < nch) {
+				const int rem = cntE - ch * TV_CHUNK;
+				if (rem > 0) {
 					#pragma unroll
 					for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(L + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
 				} else {
 					#pragma unroll
 					for (int v = 0; v < TV_PER / 2; v++) w[v] = (unsigned)M * 0x10001u;
 				}
-				int qn = 0;
+				const int tripsW = (min(__reduce_max_sync(0xffffffffu, rem), TV_CHUNK) + TV_G - 1) / TV_G;
 				#pragma unroll
 				for (int u = 0; u < TV_PER; u++) {
-					const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
-					const float4 f = T.fpos[m];
-					const float dx = f.x - fx, dy = f.y - fy, dz = f.z - fz;
-					const bool hit = dx * dx + dy * dy + dz * dz < rfilt2;
-					const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
-					if (hit) gq[qn + __popc(gb & lower)] = (uint16_t)m;
-					qn += __popc(gb);
+					if (u < tripsW) {
+						const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
+						const float4 f = fpos[m];
+						const float dx = f.x - fi.x, dy = f.y - fi.y, dz = f.z - fi.z;
+						const bool hit = dx * dx + dy * dy + dz * dz < rfilt2;
+						const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
+						if (hit) hl[tv_list_pos(cntH + __popc(gb & lower))] = (uint16_t)m;
+						cntH += __popc(gb);
+					}
 				}
-				__syncwarp();
-				for (int t = g; t < qn; t += TV_G) tv_pair<POLY, F>(ctx, T, K, s, gq[t]);
-				__syncwarp();
 			}
+			__syncwarp();
 			if (act) {
-				F::reduce(ctx, gmask);
-				if (s.lead) F::end(ctx, S, K, s);
+				uint4* dstH = (uint4*)(S.hlist + (size_t)i * (size_t)S.tlCap);
+				const int nq = (cntH + TV_CHUNK - 1) / TV_CHUNK * (TV_CHUNK / 8);
+				#pragma unroll
+				for (int v = 0; v < TV_PER / 8; v++) for (int c = 0; c * (TV_CHUNK / 8) < nq; c++) dstH[c * (TV_CHUNK / 8) + g * (TV_PER / 8) + v] = ((const uint4*)hl)[c * (TV_CHUNK / 8) + g * (TV_PER / 8) + v];
+				if (g == 0) S.hcnt[i] = (uint16_t)cntH;
 			}
+			__syncwarp();
 		}
 	}
 }
