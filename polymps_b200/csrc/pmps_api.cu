@@ -229,6 +229,8 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	K.TX = params->dim == 3 ? 2 : 4; K.TY = K.TX; K.TZ = params->dim == 3 ? 2 : 1;
 	if (const char* e = getenv("PMPS_TILE")) { int a = 0, b = 0, c = 0; if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && b > 0 && c > 0 && (a + 2) * (b + 2) * (c + 2) <= TV_HMAX) { K.TX = a; K.TY = b; K.TZ = params->dim == 3 ? c : 1; } }
 	K.TV = K.TX * K.TY * K.TZ;
+	K.HVt = (K.TX + 2) * (K.TY + 2) * (params->dim == 3 ? K.TZ + 2 : 1); if (K.HVt < 27) K.HVt = 27;
+	K.tabStride = (2 * K.HVt + 3 + 3) & ~3;
 	K.nTX = (params->numBucketsX + K.TX - 1) / K.TX; K.nTY = (params->numBucketsY + K.TY - 1) / K.TY; K.nTZ = (params->numBucketsZ + K.TZ - 1) / K.TZ;
 	const long long nC = (long long)K.nTX * K.nTY * K.nTZ * K.TV;
 	if (nC > 2000000000ll) { delete h; return pmps_fail(nullptr, PMPS_E_OVERFLOW, "pmps_create: %lld cells overflow int32", nC); }
@@ -253,7 +255,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	rc |= dalloc(h, &h->scanBlock, h->nScanBlocks);
 	{	// work items of the tile-Verlet walker: at most one per non-empty cell
 		const size_t items = (size_t)(S.nC < n0 ? S.nC : n0) + 1;
-		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
+		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.itemTab, items * (size_t)K.tabStride); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
 		int sm = 148; cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device); h->smCount = sm;
 	}
 	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 1); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);

@@ -62,6 +62,7 @@ struct DevView {
 	int32_t listValid;                   // the Verlet list of the current bucket order has been built
 	int32_t* tileList; int32_t* nTiles;  // work items of the last rebuild: tile id (whole tile) or ~cell (one bucket of a tile whose halo
 	                                     // does not fit the staging area); count on device
+	int32_t* itemTab;                    // per work item: precomputed halo table (K.tabStride ints, pmps_tv.cuh)
 	int32_t* tileCursor;                 // work-stealing cursors, one per walk launch of a step
 	uint8_t* tileWall;                   // per tile: some particle of the tile is near a polygon wall (set by the wall pass)
 };
@@ -81,6 +82,7 @@ struct KParams {
 	int32_t poly;        // wallType == polygon
 	int32_t TX, TY, TZ, TV;       // buckets per tile along x, y, z and their product
 	int32_t nTX, nTY, nTZ;        // tiles per axis
+	int32_t HVt, tabStride;       // halo buckets of a whole tile; ints per item table
 	int32_t tvMaxM;               // staged records a tile may need (smallest capacity over the passes): larger tiles are split
 	double reMax2;       // max(reS, reL)^2: no predicate of the reference reaches farther
 	double mirrorFar2;   // a particle farther than this from every wall (distParticleWall2) cannot fail d2 < dm2 nor pass M(re): its mirror is skipped
@@ -113,6 +115,7 @@ struct pmps_handle {
 	int numParticles = 0, numParticlesZero = 0;
 	bool haveState = false, haveList = false, listBuilt = false;   // haveList: bucket order valid; listBuilt: Verlet list valid
 	int nTilesAll = 0, smCount = 148, walkSeq = 0; bool tileWallValid = false;
+	double dispNow = 0.0, dispInc = 0.0, dispIncPrev = 0.0; int stepsSinceBuild = 0; bool needRebuild = true;   // displacement since the list build (step_begin's rebuild decision)
 	bool hitValid = false;               // hlist matches the current positions (set by the list build / k_tv_hits, cleared when positions change)
 	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;

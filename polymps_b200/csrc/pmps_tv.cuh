@@ -69,6 +69,13 @@ __host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes p
 	return 16 + 24 + ((f & NF_VEL) ? 24 : 0) + 8 * popc8(f & ~(unsigned)NF_VEL);
 }
 #define TV_REC_MAX (16 + 24 + 24 + 8 * 3)   // the fattest pack of the step paths: F3 (vel, press, pndi, RHO)
+#ifndef TV_LIGHT_REC
+#define TV_LIGHT_REC 0            // packs staging at most this many bytes per record would run three blocks per SM (measured: 85 registers spill, slower)
+#endif
+#define TV_BLOCKS(f) (tv_rec_bytes(f) <= TV_LIGHT_REC ? 3 : 2)
+#ifndef TV_ILP2
+#define TV_ILP2 0                 // 1: follow passes take two list entries per trip (interleaved geometry chains); measured: no gain
+#endif
 
 // ---- work item -> boxes ----------------------------------------------------------------------------------------
 struct TvBox {
@@ -124,6 +131,22 @@ __device__ __forceinline__ float tv_type_word(const double4& p) { return __int_a
 
 // ---- work items of the current bucket order ---------------------------------------------------------------------
 // One thread per tile: a tile whose halo fits the staging area is one item; otherwise each of its non-empty buckets is.
+// Every item gets its halo table precomputed (K.tabStride ints: hOff[0..HVt], hBase[0..HVt), own0, P — HVt = halo
+// buckets of a whole tile) so the passes read it with one coalesced load instead of chasing cellStart.
+#define TV_TABMAX (2 * TV_HMAX + 4)
+__device__ __forceinline__ void tv_write_table(const DevView& S, const KParams& K, const TvBox& b, int slot) {
+	int* tab = S.itemTab + (size_t)slot * K.tabStride;
+	int run = 0;
+	for (int hb = 0; hb < b.HV; hb++) {
+		const int c = tv_halo_cell(K, b, hb);
+		int s0 = 0, n = 0;
+		if (c >= 0) { s0 = S.cellStart[c]; n = S.cellStart[c + 1] - s0; }
+		tab[hb] = run; tab[K.HVt + 1 + hb] = s0; run += n;
+	}
+	tab[b.HV] = run;
+	const int own0 = S.cellStart[b.c0];
+	tab[2 * K.HVt + 1] = own0; tab[2 * K.HVt + 2] = S.cellStart[b.c1] - own0;
+}
 static __global__ void k_tv_items(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int nTilesAll) {
 	const int t = blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= nTilesAll) return;
@@ -131,8 +154,27 @@ static __global__ void k_tv_items(const __grid_constant__ DevView S, const __gri
 	const TvBox b = tv_box(K, t);
 	int M = 0;
 	for (int hb = 0; hb < b.HV; hb++) { const int c = tv_halo_cell(K, b, hb); if (c >= 0) M += S.cellStart[c + 1] - S.cellStart[c]; }
-	if (M + 1 <= K.tvMaxM) { S.tileList[atomicAdd(S.nTiles, 1)] = t; return; }
-	for (int c = b.c0; c < b.c1; c++) if (S.cellStart[c + 1] > S.cellStart[c]) S.tileList[atomicAdd(S.nTiles, 1)] = ~c;
+	if (M + 1 <= K.tvMaxM) { const int slot = atomicAdd(S.nTiles, 1); S.tileList[slot] = t; tv_write_table(S, K, b, slot); return; }
+	for (int c = b.c0; c < b.c1; c++) if (S.cellStart[c + 1] > S.cellStart[c]) {
+		const int slot = atomicAdd(S.nTiles, 1); S.tileList[slot] = ~c; tv_write_table(S, K, tv_box(K, ~c), slot);
+	}
+}
+// item scheduling shared by the tile kernels: a work-stealing cursor whose NEXT value is requested at the start of an
+// item, so the atomic's latency is hidden behind the item's work
+__device__ __forceinline__ int tv_first_item(const DevView& S, int cursorIdx, int* sItem) {
+	if (threadIdx.x == 0) *sItem = atomicAdd(&S.tileCursor[cursorIdx], 1);
+	__syncthreads();
+	return *sItem;
+}
+__device__ __forceinline__ int tv_advance(int nxt, int* sItem) {
+	__syncthreads();   // the item is done with the tables and the staged data
+	if (threadIdx.x == 0) *sItem = nxt;
+	__syncthreads();
+	return *sItem;
+}
+__device__ __forceinline__ void tv_load_table(const DevView& S, const KParams& K, int tt, int* sTab) {
+	for (int k = threadIdx.x; k < K.tabStride; k += TV_T) sTab[k] = S.itemTab[(size_t)tt * K.tabStride + k];
+	__syncthreads();
 }
 static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int copyPos, int copyVel) {
 	const int i = S.cellStart[S.nC] + blockIdx.x * blockDim.x + threadIdx.x;   // ghosts are parked behind the last cell
@@ -142,17 +184,104 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 }
 
 
+// ---- shared-memory image of the halo ------------------------------------------------------------------------------
+struct TvStage {   // shared-memory planes of the staged halo
+	float4* fpos; double *px, *py, *pz; Nb nb;
+};
+template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp, int maxM) {
+	TvStage t; const size_t m = (size_t)maxM;
+	t.fpos = (float4*)sp; sp += 16 * m;
+	t.px = (double*)sp; sp += 8 * m; t.py = (double*)sp; sp += 8 * m; t.pz = (double*)sp; sp += 8 * m;
+	double *vx = nullptr, *vy = nullptr, *vz = nullptr, *pr = nullptr, *pn = nullptr, *rh = nullptr, *mu = nullptr, *cc = nullptr, *pk = nullptr;
+	if (FIELDS & NF_VEL) { vx = (double*)sp; sp += 8 * m; vy = (double*)sp; sp += 8 * m; vz = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_PRESS) { pr = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_PNDI) { pn = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_RHO) { rh = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_MEU) { mu = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_CONC) { cc = (double*)sp; sp += 8 * m; }
+	if (FIELDS & NF_PNDKI) { pk = (double*)sp; sp += 8 * m; }
+	t.nb.vx = vx; t.nb.vy = vy; t.nb.vz = vz; t.nb.press = pr; t.nb.pndi = pn; t.nb.RHO = rh; t.nb.MEU = mu; t.nb.concentration = cc; t.nb.pndki = pk;
+	return t;
+}
+
+
+// ---- staging the halo ------------------------------------------------------------------------------------------------
+// One warp per halo bucket.  Neighbour fields are copied with cp.async (global -> shared, no registers, no waiting until
+// the end); positions go through registers four buckets at a time, every load of a batch issued before the first store,
+// so a tile pays a few memory round trips instead of one per bucket (ncu: the staging loads were 20-30 % of all stall
+// samples when issued one bucket at a time).
+template <bool PLANES, unsigned FIELDS>
+__device__ __forceinline__ void tv_stage_one(const DevView& S, const TvStage& T, int j, int m, const double4& pj, double ox, double oy, double oz) {
+	T.fpos[m] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), tv_type_word(pj));
+	if (PLANES) { T.px[m] = pj.x; T.py[m] = pj.y; T.pz[m] = pj.z; }
+}
+__device__ __forceinline__ void tv_cp8(const double* dstShared, const double* srcGlobal) {   // 8-byte asynchronous global -> shared copy
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"((unsigned)__cvta_generic_to_shared(dstShared)), "l"(srcGlobal));
+}
+template <bool PLANES, unsigned FIELDS>
+__device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, const int* hOff, const int* hBase, int HV, int own0, int P,
+                                         double ox, double oy, double oz, uint16_t* ownMap) {
+	constexpr int NB = 4;   // buckets per thread whose position loads are in flight together
+	constexpr int NW = TV_T / 32;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	// neighbour fields: asynchronous copies straight into the planes (cp.async: no registers, nothing waits until the end)
+	if (FIELDS) {
+		for (int hb = warp; hb < HV; hb += NW) {
+			const int off = hOff[hb], n = hOff[hb + 1] - off, s0 = hBase[hb];
+			for (int r = lane; r < n; r += 32) {
+				const int j = s0 + r, m = off + r;
+				if (FIELDS & NF_VEL) { const double* v = (const double*)(S.vel + j); tv_cp8(T.nb.vx + m, v); tv_cp8(T.nb.vy + m, v + 1); tv_cp8(T.nb.vz + m, v + 2); }
+				if (FIELDS & NF_PRESS) tv_cp8(T.nb.press + m, S.press + j);
+				if (FIELDS & NF_PNDI) tv_cp8(T.nb.pndi + m, S.pndi + j);
+				if (FIELDS & NF_RHO) tv_cp8(T.nb.RHO + m, S.RHO + j);
+				if (FIELDS & NF_MEU) tv_cp8(T.nb.MEU + m, S.MEU + j);
+				if (FIELDS & NF_CONC) tv_cp8(T.nb.concentration + m, S.concentration + j);
+				if (FIELDS & NF_PNDKI) tv_cp8(T.nb.pndki + m, S.pndki + j);
+			}
+		}
+	}
+	// positions go through registers (float copy relative to the tile origin, type word, planes)
+	for (int hb0 = warp; hb0 < HV; hb0 += NW * NB) {
+		double4 p[NB]; int j[NB], m[NB]; bool ok[NB];
+		#pragma unroll
+		for (int b = 0; b < NB; b++) {
+			const int hb = hb0 + b * NW;
+			ok[b] = false; j[b] = 0; m[b] = 0;
+			if (hb < HV) { const int off = hOff[hb]; ok[b] = lane < hOff[hb + 1] - off; j[b] = hBase[hb] + lane; m[b] = off + lane; }
+			if (ok[b]) p[b] = ld256(S.pos + j[b]);
+		}
+		#pragma unroll
+		for (int b = 0; b < NB; b++) {
+			if (!ok[b]) continue;
+			tv_stage_one<PLANES, FIELDS>(S, T, j[b], m[b], p[b], ox, oy, oz);
+			if (ownMap && j[b] >= own0 && j[b] < own0 + P) ownMap[j[b] - own0] = (uint16_t)m[b];
+		}
+		#pragma unroll
+		for (int b = 0; b < NB; b++) {   // buckets with more than 32 particles (far above the lattice density)
+			const int hb = hb0 + b * NW;
+			if (hb >= HV) continue;
+			const int off = hOff[hb], n = hOff[hb + 1] - off, s0 = hBase[hb];
+			for (int r = lane + 32; r < n; r += 32) {
+				tv_stage_one<PLANES, FIELDS>(S, T, s0 + r, off + r, ld256(S.pos + s0 + r), ox, oy, oz);
+				if (ownMap && s0 + r >= own0 && s0 + r < own0 + P) ownMap[s0 + r - own0] = (uint16_t)(off + r);
+			}
+		}
+	}
+	if (FIELDS) asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
 // ---- Verlet list in tile-local indices ---------------------------------------------------------------------------
 // Same tiling as the walker.  Float positions (relative to the tile origin) of the halo are staged; TV_BG lanes per
 // particle sweep the 27 (9 in 2D) buckets around the particle's own bucket — nine (three) contiguous stretches of the
 // staged halo — and append the records within the list radius, in staged order, to the particle's list (tv_list_pos()).
 // The unused tail of the last chunk points at the far-away dummy record (index M).  Control flow is warp-uniform
 // (trip counts are the maximum over the warp) so the ballots run with the full mask.
-static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
-	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
+	__shared__ int sTab[TV_TABMAX], sItem;
 	constexpr int NGB = TV_T / TV_BG;   // particles per round
-	float4* fpos = (float4*)smemRaw;
+	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
+	float4* const fpos = T.fpos;
 	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)maxM) + (size_t)(threadIdx.x / TV_BG) * S.tlCap;
 	uint16_t* hl = glist + (size_t)NGB * S.tlCap;   // hit list of the build positions (epoch of the first passes of the step)
 	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
@@ -161,16 +290,12 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 	const unsigned gbits = (1u << TV_BG) - 1u, lower = (1u << g) - 1u;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
-	for (;;) {
-		__syncthreads();
-		if (tid == 0) sItem = atomicAdd(&S.tileCursor[cursorIdx], 1);
-		__syncthreads();
-		const int tt = sItem;
-		if (tt >= nItems) break;
+	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
+	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
+		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const TvBox b = tv_box(K, S.tileList[tt]);
-		tv_halo_table(S, K, b, hBase, hOff);
-		const int M = hOff[b.HV];
-		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
+		tv_load_table(S, K, tt, sTab);
+		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > maxM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
 			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1 > maxM ? M + 1 : P);
 			for (int p = tid; p < P; p += TV_T) { S.tlistCnt[own0 + p] = 0; S.hcnt[own0 + p] = 0; }
@@ -178,13 +303,7 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		for (int hb = tid / 16; hb < b.HV; hb += TV_T / 16) {
-			const int s0 = hBase[hb], n = hOff[hb + 1] - hOff[hb], off = hOff[hb];
-			for (int r = tid % 16; r < n; r += 16) {
-				const double4 pj = ld256(S.pos + s0 + r);
-				fpos[off + r] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), 0.f);
-			}
-		}
+		tv_stage<false, 0>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, nullptr);
 		__syncthreads();
 		for (int p0 = 0; p0 < P; p0 += NGB) {   // uniform over the block
 			const int p = p0 + grp;
@@ -241,25 +360,6 @@ static __global__ void __launch_bounds__(TV_T) k_tv_build(const __grid_constant_
 }
 
 // ---- the walker ---------------------------------------------------------------------------------------------------
-struct TvStage {   // shared-memory planes of the staged halo
-	float4* fpos; double *px, *py, *pz; Nb nb;
-};
-template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp, int maxM) {
-	TvStage t; const size_t m = (size_t)maxM;
-	t.fpos = (float4*)sp; sp += 16 * m;
-	t.px = (double*)sp; sp += 8 * m; t.py = (double*)sp; sp += 8 * m; t.pz = (double*)sp; sp += 8 * m;
-	double *vx = nullptr, *vy = nullptr, *vz = nullptr, *pr = nullptr, *pn = nullptr, *rh = nullptr, *mu = nullptr, *cc = nullptr, *pk = nullptr;
-	if (FIELDS & NF_VEL) { vx = (double*)sp; sp += 8 * m; vy = (double*)sp; sp += 8 * m; vz = (double*)sp; sp += 8 * m; }
-	if (FIELDS & NF_PRESS) { pr = (double*)sp; sp += 8 * m; }
-	if (FIELDS & NF_PNDI) { pn = (double*)sp; sp += 8 * m; }
-	if (FIELDS & NF_RHO) { rh = (double*)sp; sp += 8 * m; }
-	if (FIELDS & NF_MEU) { mu = (double*)sp; sp += 8 * m; }
-	if (FIELDS & NF_CONC) { cc = (double*)sp; sp += 8 * m; }
-	if (FIELDS & NF_PNDKI) { pk = (double*)sp; sp += 8 * m; }
-	t.nb.vx = vx; t.nb.vy = vy; t.nb.vz = vz; t.nb.press = pr; t.nb.pndi = pn; t.nb.RHO = rh; t.nb.MEU = mu; t.nb.concentration = cc; t.nb.pndki = pk;
-	return t;
-}
-
 // exact pair geometry of staged record m for particle s, then the bodies
 template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m) {
@@ -275,15 +375,37 @@ __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, 
 	q.rinv = fast_rsqrt(q.d2);
 	F::template pair<POLY>(ctx, T.nb, K, s, q);
 }
+// two staged records at once: the two geometry chains (shared-memory loads, exact distance, reciprocal square root) are
+// independent and interleave, which is what hides the FP64 latencies with only four warps per scheduler
+template <bool POLY, class F>
+__device__ __forceinline__ void tv_pair2(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m0, int m1) {
+	Pair a, b; a.j = m0; b.j = m1;
+	const double xa = T.px[m0], ya = T.py[m0], za = T.pz[m0], xb = T.px[m1], yb = T.py[m1], zb = T.pz[m1];
+	const int wa = __float_as_int(T.fpos[m0].w), wb = __float_as_int(T.fpos[m1].w);
+	a.rx = xa - s.pi.x; a.ry = ya - s.pi.y; a.rz = za - s.pi.z; b.rx = xb - s.pi.x; b.ry = yb - s.pi.y; b.rz = zb - s.pi.z;
+	a.d2 = sq3_exact(a.rx, a.ry, a.rz); b.d2 = sq3_exact(b.rx, b.ry, b.rz);
+	const bool ha = a.d2 < K.reMax2, hb = b.d2 < K.reMax2;
+	if (!(ha || hb)) return;
+	a.tj = (int)(short)(wa & 0xffff); a.ptj = wa >> 16; b.tj = (int)(short)(wb & 0xffff); b.ptj = wb >> 16;
+	if (POLY && s.hasMirror) {
+		a.mx = xa - s.mix; a.my = ya - s.miy; a.mz = za - s.miz; a.dm2 = sq3_exact(a.mx, a.my, a.mz);
+		b.mx = xb - s.mix; b.my = yb - s.miy; b.mz = zb - s.miz; b.dm2 = sq3_exact(b.mx, b.my, b.mz);
+	} else {
+		a.mx = a.my = a.mz = b.mx = b.my = b.mz = 0.0; a.dm2 = b.dm2 = __longlong_as_double(0x7ff0000000000000ll);
+	}
+	a.rinv = fast_rsqrt(a.d2); b.rinv = fast_rsqrt(b.d2);
+	if (ha) F::template pair<POLY>(ctx, T.nb, K, s, a);
+	if (hb) F::template pair<POLY>(ctx, T.nb, K, s, b);
+}
 __device__ __forceinline__ void tv_prefetch(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
 // FOLLOW: the candidates are the particle's HIT list (k_tv_hits / k_tv_build: the Verlet candidates within reach at the
 // positions of the current epoch), every lane just takes its share — no scan, no queue, no votes.  Otherwise the Verlet
 // list itself is scanned with the float positions and the survivors are queued (used when no hit list is valid).
 template <bool POLY, unsigned FIELDS, bool WALLONLY, bool FOLLOW, class F>
-__global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+__global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
-	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
+	__shared__ int sTab[TV_TABMAX], sItem;
 	const TvStage T = tv_carve<FIELDS>(smemRaw, maxM);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
 	uint16_t* gq = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + grp * TV_CHUNK;   // this particle's queue: one chunk
@@ -293,12 +415,9 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
 	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
-	for (;;) {
-		__syncthreads();   // the previous item is done with the tables and the staged data
-		if (tid == 0) sItem = atomicAdd(&S.tileCursor[cursorIdx], 1);
-		__syncthreads();
-		const int tt = sItem;
-		if (tt >= nItems) break;
+	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
+	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
+		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const int item = S.tileList[tt];
 		const TvBox b = tv_box(K, item);
 		if (WALLONLY) {   // no particle of this tile is near a wall: the pair bodies are idle, only the tails run (one lane per particle)
@@ -317,35 +436,16 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 				continue;   // uniform over the block
 			}
 		}
-		tv_halo_table(S, K, b, hBase, hOff);
-		const int M = hOff[b.HV];
-		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
+		tv_load_table(S, K, tt, sTab);
+		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > maxM || P > TV_MAXOWN) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		// ---- stage the halo: half a warp per bucket ----
-		for (int hb = tid / 16; hb < b.HV; hb += TV_T / 16) {
-			const int s0 = hBase[hb], n = hOff[hb + 1] - hOff[hb], off = hOff[hb];
-			const bool own = s0 >= own0 && s0 < own0 + P;
-			for (int r = tid % 16; r < n; r += 16) {
-				const int j = s0 + r, m = off + r;
-				const double4 pj = ld256(S.pos + j);
-				T.fpos[m] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), tv_type_word(pj));
-				T.px[m] = pj.x; T.py[m] = pj.y; T.pz[m] = pj.z;
-				if (own) ownMap[j - own0] = (uint16_t)m;
-				if (FIELDS & NF_VEL) { const double4 vj = ld256(S.vel + j); ((double*)T.nb.vx)[m] = vj.x; ((double*)T.nb.vy)[m] = vj.y; ((double*)T.nb.vz)[m] = vj.z; }
-				if (FIELDS & NF_PRESS) ((double*)T.nb.press)[m] = S.press[j];
-				if (FIELDS & NF_PNDI) ((double*)T.nb.pndi)[m] = S.pndi[j];
-				if (FIELDS & NF_RHO) ((double*)T.nb.RHO)[m] = S.RHO[j];
-				if (FIELDS & NF_MEU) ((double*)T.nb.MEU)[m] = S.MEU[j];
-				if (FIELDS & NF_CONC) ((double*)T.nb.concentration)[m] = S.concentration[j];
-				if (FIELDS & NF_PNDKI) ((double*)T.nb.pndki)[m] = S.pndki[j];
-			}
-		}
-		if (tid == 0) T.fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the record list padding points at
 		// first round's lists on their way while the staging loads land
 		const uint16_t* const LIST = FOLLOW ? S.hlist : S.tlist;
 		if (grp < P) { const char* L0 = (const char*)(LIST + (size_t)(own0 + grp) * (size_t)S.tlCap); tv_prefetch(L0 + g * (2 * TV_PER)); }
+		tv_stage<true, FIELDS>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, ownMap);
+		if (tid == 0) { T.fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f); T.px[M] = T.py[M] = T.pz[M] = 1e30; }   // the record list padding points at
 		__syncthreads();
 		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask ballots) ----
 		for (int p0 = 0; p0 < P; p0 += TV_NG) {
@@ -389,10 +489,17 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 					#pragma unroll
 					for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(L + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
 					const int rem = cntE - ch * TV_CHUNK - g;   // entries u * TV_G + g of this chunk exist for u * TV_G < rem
+#if TV_ILP2
+					#pragma unroll
+					for (int u = 0; u < TV_PER; u += 2) {   // two entries per trip (one 32-bit word of the list); a missing one points at the dummy record
+						if (u * TV_G < rem) tv_pair2<POLY, F>(ctx, T, K, s, (int)(w[u >> 1] & 0xffffu), (u + 1) * TV_G < rem ? (int)(w[u >> 1] >> 16) : M);
+					}
+#else
 					#pragma unroll
 					for (int u = 0; u < TV_PER; u++) {
 						if (u * TV_G < rem) tv_pair<POLY, F>(ctx, T, K, s, (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu));
 					}
+#endif
 				}
 			} else {
 				const float fx = pairs ? (float)(s.pi.x - ox) : 0.f, fy = pairs ? (float)(s.pi.y - oy) : 0.f, fz = pairs ? (float)(s.pi.z - oz) : 0.f;
@@ -438,10 +545,11 @@ __global__ void __launch_bounds__(TV_T, 2) k_tv(const __grid_constant__ DevView 
 // After the positions changed (prediction, correction) the Verlet candidates are filtered ONCE with the float positions
 // of the new epoch; every neighbour pass until the next change then follows the hit list (k_tv, FOLLOW).  Stages only the
 // float positions (16 bytes per halo record); same warp-uniform scan as the walker's scanning mode.
-static __global__ void __launch_bounds__(TV_T) k_tv_hits(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
-	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
-	float4* fpos = (float4*)smemRaw;
+	__shared__ int sTab[TV_TABMAX], sItem;
+	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
+	float4* const fpos = T.fpos;
 	uint16_t* ownMap = (uint16_t*)(smemRaw + 16 * (size_t)maxM);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
 	uint16_t* hl = ownMap + TV_MAXOWN + (size_t)grp * S.tlCap;
@@ -450,28 +558,16 @@ static __global__ void __launch_bounds__(TV_T) k_tv_hits(const __grid_constant__
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
 	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
-	for (;;) {
-		__syncthreads();
-		if (tid == 0) sItem = atomicAdd(&S.tileCursor[cursorIdx], 1);
-		__syncthreads();
-		const int tt = sItem;
-		if (tt >= nItems) break;
+	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
+	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
+		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const TvBox b = tv_box(K, S.tileList[tt]);
-		tv_halo_table(S, K, b, hBase, hOff);
-		const int M = hOff[b.HV];
-		const int own0 = S.cellStart[b.c0], P = S.cellStart[b.c1] - own0;
+		tv_load_table(S, K, tt, sTab);
+		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > maxM || P > TV_MAXOWN) continue;   // reported by k_tv_build
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		for (int hb = tid / 16; hb < b.HV; hb += TV_T / 16) {
-			const int s0 = hBase[hb], n = hOff[hb + 1] - hOff[hb], off = hOff[hb];
-			const bool own = s0 >= own0 && s0 < own0 + P;
-			for (int r = tid % 16; r < n; r += 16) {
-				const double4 pj = ld256(S.pos + s0 + r);
-				fpos[off + r] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), 0.f);
-				if (own) ownMap[s0 + r - own0] = (uint16_t)(off + r);
-			}
-		}
+		tv_stage<false, 0>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, ownMap);
 		if (tid == 0) fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);
 		__syncthreads();
 		for (int p0 = 0; p0 < P; p0 += TV_NG) {

@@ -17,7 +17,7 @@ from .params import ParticleSystem, PmpsParams, to_c_params
 from .state import HostState, PmpsHostArrays, PmpsScalars
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpmps.so")
+LIB_PATH = os.environ.get("PMPS_LIB", os.path.join(HERE, "libpmps.so"))   # PMPS_LIB: an experimental build of the same library (A/B timing)
 
 STAGES = ["update_buckets", "calc_viscosity", "add_gravity", "predict", "check_out_domain", "collisions", "wall_closest_point",
           "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive", "wall_pnd_diffusive", "update_pnd",

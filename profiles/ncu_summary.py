@@ -2,7 +2,7 @@
 """Summarise an .ncu-rep (read here, no GPU needed): per-kernel headline metrics, stall mix and — for one kernel —
 instruction / stall-sample shares per SOURCE LINE (joins ncu's SASS page with nvdisasm's line table of libpmps.so).
 
-    python profiles/ncu_summary.py gpurun_out/prof.ncu-rep [--lines <substring of the mangled kernel name>] [--top N]
+    python profiles/ncu_summary.py gpurun_out/prof.ncu-rep [--lines <substring of the mangled kernel name> [--ncu-name <substring of the demangled name>]] [--top N]
 """
 import collections
 import csv
@@ -45,7 +45,7 @@ def raw(rep):
         print("  stall mix: " + ", ".join("%s %.0f%%" % (k[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")], 100 * v / tot) for v, k in sorted(st, reverse=True)[:8]))
 
 
-def lines(rep, pat, top):
+def lines(rep, pat, top, ncupat):
     tmp = tempfile.mkdtemp()
     subprocess.run(["cuobjdump", "-xelf", "all", os.path.join(ROOT, "polymps_b200", "libpmps.so")], cwd=tmp, capture_output=True)
     seq = None
@@ -79,7 +79,7 @@ def lines(rep, pat, top):
         if curb is not None:
             curb["rows"].append(r)
     for b in blocks:
-        if pat not in b["name"]:
+        if ncupat not in b["name"]:
             continue
         hdr, data = b["rows"][0], b["rows"][1:]
         ie, isamp = hdr.index("Instructions Executed"), hdr.index("Warp Stall Sampling (All Samples)")
@@ -99,6 +99,7 @@ if __name__ == "__main__":
     rep = sys.argv[1]
     if "--lines" in sys.argv:
         top = int(sys.argv[sys.argv.index("--top") + 1]) if "--top" in sys.argv else 30
-        lines(rep, sys.argv[sys.argv.index("--lines") + 1], top)
+        pat = sys.argv[sys.argv.index("--lines") + 1]
+        lines(rep, pat, top, sys.argv[sys.argv.index("--ncu-name") + 1] if "--ncu-name" in sys.argv else pat)
     else:
         raw(rep)
