@@ -271,7 +271,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	S.tlCap = ((cap + TV_CHUNK - 1) / TV_CHUNK) * TV_CHUNK; if (S.tlCap > 255 * TV_CHUNK) S.tlCap = 255 * TV_CHUNK;
 	rc |= dalloc(h, &S.tlist, (size_t)n0 * (size_t)S.tlCap); rc |= dalloc(h, &S.tlistCnt, n0);
 	rc |= dalloc(h, &S.hlist, (size_t)n0 * (size_t)S.tlCap); rc |= dalloc(h, &S.hcnt, n0);
-	K.tvMaxM = (int)((TV_SMEM_BUDGET - (size_t)TV_FIXED_BYTES(true)) / TV_REC_MAX);   // follow passes; a scanning pass of the fattest pack gets one block per SM
+	K.tvMaxM = TV_MAXM;   // follow passes; a scanning pass of the fattest pack gets one block per SM
 	if (K.tvMaxM > 65534) K.tvMaxM = 65534;
 	if (const char* e = getenv("PMPS_TILE_MAXM")) { const int v = atoi(e); if (v > 0 && v < K.tvMaxM) K.tvMaxM = v; }   // tests: force the split path
 	if (K.tvMaxM < 64) return pmps_fail(h, PMPS_E_UNSUPPORTED, "candidate lists of %d entries leave no room for the staged halo", S.tlCap);

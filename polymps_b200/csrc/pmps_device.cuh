@@ -76,21 +76,26 @@ __device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, i
 }
 
 // ---- lane groups --------------------------------------------------------------------------------------------------
-#define WG 8   // lanes per particle in the list walker
-#ifndef WALK_MIN_BLOCKS
-#define WALK_MIN_BLOCKS 8   // resident 128-thread blocks per SM the walker is compiled for (64 registers per thread)
+#ifndef TV_G
+#define TV_G 4   // lanes per particle in the tile walker (pmps_tv.cuh)
 #endif
-// reductions over the lanes named in m: an aligned power-of-two group (8 in the list walker, 1..8 in the tile walker)
-__device__ __forceinline__ double gsum(double v, unsigned m) {
-	for (int o = __popc(m) >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
+// Reductions over the TV_G lanes of a particle (an aligned group of a warp).  They are called by ALL 32 lanes of the warp
+// in uniform control flow, so the shuffles run with the full mask (partial masks cost a WARPSYNC/vote sequence per
+// shuffle: ncu showed them at 10 % of the issued instructions of a pass).  The mask argument is kept for the bodies'
+// signatures and ignored.
+__device__ __forceinline__ double gsum(double v, unsigned) {
+	#pragma unroll
+	for (int o = TV_G >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
 	return v;
 }
-__device__ __forceinline__ int gsum(int v, unsigned m) {
-	for (int o = __popc(m) >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
+__device__ __forceinline__ int gsum(int v, unsigned) {
+	#pragma unroll
+	for (int o = TV_G >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
 	return v;
 }
-__device__ __forceinline__ double gmin(double v, unsigned m) {
-	for (int o = __popc(m) >> 1; o > 0; o >>= 1) { const double t = __shfl_xor_sync(m, v, o); v = t < v ? t : v; }
+__device__ __forceinline__ double gmin(double v, unsigned) {
+	#pragma unroll
+	for (int o = TV_G >> 1; o > 0; o >>= 1) { const double t = __shfl_xor_sync(0xffffffffu, v, o); v = t < v ? t : v; }
 	return v;
 }
 // one 32-byte record with a single 256-bit load (LDG.E.256 on sm_100a)
@@ -214,7 +219,7 @@ template <class B, class... Rest> struct Fused<B, Rest...> {
 		Fused<Rest...>::template pair<POLY>(x.r, S, K, s, q);
 	}
 	__device__ __forceinline__ static void reduce(Ctx& x, unsigned m) {
-		if (x.on) B::reduce(x.c, m);   // x.on is uniform over the lanes of a group
+		B::reduce(x.c, m);   // every lane of the warp takes part (full-mask shuffles); the sums of an idle body are never read
 		Fused<Rest...>::reduce(x.r, m);
 	}
 	__device__ __forceinline__ static void end(Ctx& x, const DevView& S, const KParams& K, const Self& s) {

@@ -253,10 +253,9 @@ int pmps_tv_prepare(pmps_handle* h) {
 	CUDA_TRY(h, cudaMemsetAsync(S.tileWall, 0, (size_t)h->nTilesAll, h->stream));
 	h->walkSeq = 0; h->tileWallValid = false;
 	LAUNCH(h, "sort.tile_items", k_tv_items, cdiv(h->nTilesAll, 128), 128, S, h->K, h->nTilesAll);
-	const int maxM = h->K.tvMaxM;
-	const size_t smem = 16 * (size_t)maxM + 2 * (size_t)(TV_T / TV_BG) * S.tlCap * 2;   // float positions + the two lists under construction
+	const size_t smem = 16 * (size_t)TV_MAXM + 2 * (size_t)(TV_T / TV_BG) * S.tlCap * 2;   // float positions + the two lists under construction
 	CUDA_TRY(h, cudaFuncSetAttribute(k_tv_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	{ ProfScope ps_(h, "list.tile_build"); k_tv_build<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, maxM, h->walkSeq++); h->launches++; }
+	{ ProfScope ps_(h, "list.tile_build"); k_tv_build<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, h->walkSeq++); h->launches++; }
 	CUDA_TRY(h, cudaGetLastError());
 	h->hitValid = true;   // the build emits the hit list of the build positions too
 	return PMPS_OK;
@@ -266,10 +265,9 @@ int pmps_tv_prepare(pmps_handle* h) {
 int pmps_tv_hits(pmps_handle* h) {
 	DevView& S = h->V;
 	if (h->walkSeq >= PMPS_CURSORS) return pmps_fail(h, PMPS_E_STATE, "more than %d tile passes since the last pmps_update_buckets", PMPS_CURSORS - 1);
-	const int maxM = h->K.tvMaxM;
-	const size_t smem = 16 * (size_t)maxM + 2 * (size_t)TV_MAXOWN + (size_t)TV_NG * S.tlCap * 2;
+	const size_t smem = 16 * (size_t)TV_MAXM + 2 * (size_t)TV_MAXOWN + (size_t)TV_NG * S.tlCap * 2;
 	CUDA_TRY(h, cudaFuncSetAttribute(k_tv_hits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	{ ProfScope ps_(h, "list.hits"); k_tv_hits<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, maxM, h->walkSeq++); h->launches++; }
+	{ ProfScope ps_(h, "list.hits"); k_tv_hits<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, h->walkSeq++); h->launches++; }
 	CUDA_TRY(h, cudaGetLastError());
 	h->hitValid = true;
 	return PMPS_OK;

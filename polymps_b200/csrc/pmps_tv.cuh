@@ -21,9 +21,7 @@
 #include "pmps_bodies.cuh"
 
 #define TV_T 256                 // threads per block
-#ifndef TV_G
-#define TV_G 4                   // lanes per particle in the walker
-#endif
+// TV_G (lanes per particle in the walker) is defined in pmps_device.cuh next to the group reductions
 #define TV_NG (TV_T / TV_G)      // particles per round
 #define TV_BG 8                  // lanes per particle in the list build
 #define TV_HMAX 160              // halo buckets a work item may have
@@ -73,6 +71,9 @@ __host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes p
 #define TV_LIGHT_REC 0            // packs staging at most this many bytes per record would run three blocks per SM (measured: 85 registers spill, slower)
 #endif
 #define TV_BLOCKS(f) (tv_rec_bytes(f) <= TV_LIGHT_REC ? 3 : 2)
+// staged records per work item: a compile-time constant, so every plane of the shared-memory image sits at a constant
+// offset (no registers spent on plane pointers).  Sized for two blocks per SM of the fattest pack in follow mode.
+#define TV_MAXM ((TV_SMEM_BUDGET - TV_FIXED_BYTES(true)) / TV_REC_MAX)
 #ifndef TV_ILP2
 #define TV_ILP2 0                 // 1: follow passes take two list entries per trip (interleaved geometry chains); measured: no gain
 #endif
@@ -188,8 +189,8 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 struct TvStage {   // shared-memory planes of the staged halo
 	float4* fpos; double *px, *py, *pz; Nb nb;
 };
-template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp, int maxM) {
-	TvStage t; const size_t m = (size_t)maxM;
+template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp) {
+	TvStage t; constexpr size_t m = TV_MAXM;
 	t.fpos = (float4*)sp; sp += 16 * m;
 	t.px = (double*)sp; sp += 8 * m; t.py = (double*)sp; sp += 8 * m; t.pz = (double*)sp; sp += 8 * m;
 	double *vx = nullptr, *vy = nullptr, *vz = nullptr, *pr = nullptr, *pn = nullptr, *rh = nullptr, *mu = nullptr, *cc = nullptr, *pk = nullptr;
@@ -276,13 +277,13 @@ __device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, con
 // staged halo — and append the records within the list radius, in staged order, to the particle's list (tv_list_pos()).
 // The unused tail of the last chunk points at the far-away dummy record (index M).  Control flow is warp-uniform
 // (trip counts are the maximum over the warp) so the ballots run with the full mask.
-static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
 	constexpr int NGB = TV_T / TV_BG;   // particles per round
 	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
 	float4* const fpos = T.fpos;
-	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)maxM) + (size_t)(threadIdx.x / TV_BG) * S.tlCap;
+	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM) + (size_t)(threadIdx.x / TV_BG) * S.tlCap;
 	uint16_t* hl = glist + (size_t)NGB * S.tlCap;   // hit list of the build positions (epoch of the first passes of the step)
 	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
 	const int tid = threadIdx.x, grp = tid / TV_BG, g = tid % TV_BG;
@@ -296,8 +297,8 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 		const TvBox b = tv_box(K, S.tileList[tt]);
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
-		if (M + 1 > maxM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
-			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1 > maxM ? M + 1 : P);
+		if (M + 1 > TV_MAXM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
+			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1 > TV_MAXM ? M + 1 : P);
 			for (int p = tid; p < P; p += TV_T) { S.tlistCnt[own0 + p] = 0; S.hcnt[own0 + p] = 0; }
 			continue;
 		}
@@ -403,13 +404,13 @@ __device__ __forceinline__ void tv_prefetch(const void* p) { asm volatile("prefe
 // positions of the current epoch), every lane just takes its share — no scan, no queue, no votes.  Otherwise the Verlet
 // list itself is scanned with the float positions and the survivors are queued (used when no hit list is valid).
 template <bool POLY, unsigned FIELDS, bool WALLONLY, bool FOLLOW, class F>
-__global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+__global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
-	const TvStage T = tv_carve<FIELDS>(smemRaw, maxM);
+	const TvStage T = tv_carve<FIELDS>(smemRaw);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
-	uint16_t* gq = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + grp * TV_CHUNK;   // this particle's queue: one chunk
-	uint16_t* ownMap = (uint16_t*)(smemRaw + (size_t)maxM * tv_rec_bytes(FIELDS)) + (FOLLOW ? 0 : TV_NG * TV_CHUNK);   // own particle -> staged index
+	uint16_t* gq = (uint16_t*)(smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS)) + grp * TV_CHUNK;   // this particle's queue: one chunk
+	uint16_t* ownMap = (uint16_t*)(smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS)) + (FOLLOW ? 0 : TV_NG * TV_CHUNK);   // own particle -> staged index
 	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
 	const unsigned gbits = (1u << TV_G) - 1u, lower = (1u << g) - 1u, gmask = gbits << gshift;
 	const bool three = K.p.dim == 3;
@@ -438,7 +439,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		}
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
-		if (M + 1 > maxM || P > TV_MAXOWN) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
+		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
 		// first round's lists on their way while the staging loads land
@@ -469,7 +470,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 				if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
 				act = s.type != K.p.ghost;
 			}
-			typename F::Ctx ctx;
+			typename F::Ctx ctx = {};   // idle lanes still take part in the (full-mask) reductions
 			bool pairs = false;
 			if (act) {
 				if (POLY) {
@@ -533,10 +534,8 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 					__syncwarp();
 				}
 			}
-			if (act) {
-				F::reduce(ctx, gmask);
-				if (s.lead) F::end(ctx, S, K, s);
-			}
+			F::reduce(ctx, gmask);   // all lanes, uniform
+			if (act && s.lead) F::end(ctx, S, K, s);
 		}
 	}
 }
@@ -545,12 +544,12 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 // After the positions changed (prediction, correction) the Verlet candidates are filtered ONCE with the float positions
 // of the new epoch; every neighbour pass until the next change then follows the hit list (k_tv, FOLLOW).  Stages only the
 // float positions (16 bytes per halo record); same warp-uniform scan as the walker's scanning mode.
-static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int maxM, int cursorIdx) {
+static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
 	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
 	float4* const fpos = T.fpos;
-	uint16_t* ownMap = (uint16_t*)(smemRaw + 16 * (size_t)maxM);
+	uint16_t* ownMap = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
 	uint16_t* hl = ownMap + TV_MAXOWN + (size_t)grp * S.tlCap;
 	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
@@ -564,7 +563,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 		const TvBox b = tv_box(K, S.tileList[tt]);
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
-		if (M + 1 > maxM || P > TV_MAXOWN) continue;   // reported by k_tv_build
+		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_tv_build
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
 		tv_stage<false, 0>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, ownMap);
