@@ -163,6 +163,7 @@ struct BWallPndDiffusive {
 // sum_j pndi_j w / sum_j w over P(reS): first half of MpsPndNeigh::meanPndParticlesWallDummySurface (src/MpsPndNeigh.cpp:777-852)
 // and of meanPnd (:855-920).  SEL 0: wall or surface particles, overwrite; SEL 1: every particle, accumulate (meanPnd)
 template <int SEL> struct BMeanPnd {
+	typedef void sparse_tag;
 	struct Ctx { double up, dn; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		c.up = c.dn = 0.0;

@@ -170,7 +170,7 @@ struct BGradConcentration {
 			double4 p = s.pi;
 			p.x = __dsub_rn(p.x, __dmul_rn(K.p.coeffShifting2, g0)); p.y = __dsub_rn(p.y, __dmul_rn(K.p.coeffShifting2, g1)); p.z = __dsub_rn(p.z, __dmul_rn(K.p.coeffShifting2, g2));
 			S.pos2[s.i] = p;
-			track_disp(S, K, s.i, p);
+			track_disp(S, K, s.i, p); track_shift(S, p.x - s.pi.x, p.y - s.pi.y, p.z - s.pi.z);
 		}
 	}
 };
@@ -208,7 +208,7 @@ struct BWallGradConcentration {
 		}
 		if (inner) {
 			double4 pn = s.pi; pn.x = p[0]; pn.y = p[1]; pn.z = p[2]; S.pos2[s.i] = pn;
-			track_disp(S, K, s.i, pn);
+			track_disp(S, K, s.i, pn); track_shift(S, pn.x - s.pi.x, pn.y - s.pi.y, pn.z - s.pi.z);
 		}
 	}
 };
@@ -217,6 +217,7 @@ struct BWallGradConcentration {
 // MpsPressure::extrapolatePressParticlesWallDummy, src/MpsPressure.cpp:792-846.  Only non-fluid i are written and
 // only fluid j are read, so the in-place update has no read/write hazard.
 struct BExtrapolatePress {
+	typedef void sparse_tag;
 	struct Ctx { double ni, pr; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		c.ni = c.pr = 0.0;
@@ -236,6 +237,7 @@ struct BExtrapolatePress {
 
 // MpsParticleVelPos::updateVelocityParticlesWallDummy, src/MpsParticleVelPos.cpp:100-158 (dummy i written, fluid j read)
 struct BWallDummyVel {
+	typedef void sparse_tag;
 	struct Ctx { double ni, ux, uy, uz; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		c.ni = c.ux = c.uy = c.uz = 0.0; return s.type == K.p.dummyWall;

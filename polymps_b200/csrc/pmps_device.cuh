@@ -75,6 +75,10 @@ __device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, i
 	atomic_max_f(S.maxDisp2, dx * dx + dy * dy + dz * dz);
 }
 
+__device__ __forceinline__ void track_shift(const DevView& S, double dx, double dy, double dz) {   // size of a shifting move (hit-list validity)
+	const float a = (float)dx, b = (float)dy, c = (float)dz; atomic_max_f(S.maxDisp2 + 1, (a * a + b * b + c * c) * 1.0001f);
+}
+
 // ---- lane groups --------------------------------------------------------------------------------------------------
 #ifndef TV_G
 #define TV_G 4   // lanes per particle in the tile walker (pmps_tv.cuh)

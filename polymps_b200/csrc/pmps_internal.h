@@ -55,7 +55,7 @@ struct DevView {
 	int32_t tlCap;                       // entries per slot in tlist (multiple of 64)
 	// device scalars
 	unsigned long long* velMax2Bits;     // max |v|^2 of fluid particles (bits of a non-negative double)
-	float* maxDisp2;                     // max squared displacement since the list build (float, >= 0)
+	float* maxDisp2;                     // [0] max squared displacement since the list build, [1] max squared shift of the shifting passes of the step (float, >= 0)
 	int32_t* flags;                      // [0] list overflow, [1] out-of-domain count, [2] guard violated, [3] live count
 	int32_t* oodList;                    // host ids flagged by the out-of-domain test
 	const struct DevMesh* meshes; int32_t nMeshes;   // polygon meshes (device array), set by pmps_set_mesh
@@ -79,6 +79,8 @@ struct KParams {
 	double velMax;       // velMax of the previous correction (src/MpsPressure.cpp:1585)
 	float rl2;           // (list radius)^2 incl. float margin
 	float guard2;        // (allowed displacement)^2
+	float hitR2;         // (reach of the hit lists)^2 = (max(reS, reL) + 2 hitDelta)^2 with the float margin
+	double hitDelta;     // a hit list stays valid while no particle moved farther than this since it was made (covers the shifting)
 	int32_t poly;        // wallType == polygon
 	int32_t TX, TY, TZ, TV;       // buckets per tile along x, y, z and their product
 	int32_t nTX, nTY, nTZ;        // tiles per axis
@@ -116,6 +118,8 @@ struct pmps_handle {
 	bool haveState = false, haveList = false, listBuilt = false;   // haveList: bucket order valid; listBuilt: Verlet list valid
 	int nTilesAll = 0, smCount = 148, walkSeq = 0; bool tileWallValid = false;
 	double dispNow = 0.0, dispInc = 0.0, dispIncPrev = 0.0; int stepsSinceBuild = 0; bool needRebuild = true;   // displacement since the list build (step_begin's rebuild decision)
+	double lastShift = 0.0;              // largest shift of the last step's shifting passes
+	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
 	bool hitValid = false;               // hlist matches the current positions (set by the list build / k_tv_hits, cleared when positions change)
 	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;

@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(128) k_build_list(const __grid_constant__ DevV
 }
 
 __global__ void k_reset_step_scalars(const __grid_constant__ DevView S) {
-	*S.maxDisp2 = 0.f; S.flags[FLAG_MAXCELL] = 0;
+	S.maxDisp2[0] = 0.f; S.flags[FLAG_MAXCELL] = 0;
 }
 
 // -------------------------------------------------------------------------------------------------------------------

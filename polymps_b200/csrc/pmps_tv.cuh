@@ -61,6 +61,12 @@ template <class B> struct WallOnly<B, typename B::wall_frame_tag> { static const
 template <class... B> struct PackWallOnly { static constexpr bool value = true; };
 template <class B, class... R> struct PackWallOnly<B, R...> { static constexpr bool value = (WallOnly<B>::value || NoPairs<B>::value) && PackWallOnly<R...>::value; };
 // (tail bodies — NoPairs — still run for every particle of a skipped tile: see the light path of k_tv)
+// bodies that act on a sparse subset of the particles (free surface, wall/dummy particles): their launches first ask
+// begin() of every particle of the tile, one lane per particle, and skip the staging when nobody wants pairs
+template <class B, class = void> struct Sparse { static constexpr bool value = false; };
+template <class B> struct Sparse<B, typename B::sparse_tag> { static constexpr bool value = true; };
+template <class... B> struct PackSparse { static constexpr bool value = true; };
+template <class B, class... R> struct PackSparse<B, R...> { static constexpr bool value = (Sparse<B>::value || NoPairs<B>::value) && PackSparse<R...>::value; };
 
 __host__ __device__ constexpr int popc8(unsigned f) { int n = 0; for (int k = 0; k < 8; k++) n += (f >> k) & 1; return n; }
 __host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes per halo record
@@ -285,7 +291,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 	float4* const fpos = T.fpos;
 	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM) + (size_t)(threadIdx.x / TV_BG) * S.tlCap;
 	uint16_t* hl = glist + (size_t)NGB * S.tlCap;   // hit list of the build positions (epoch of the first passes of the step)
-	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
+	const float rfilt2 = K.hitR2;
 	const int tid = threadIdx.x, grp = tid / TV_BG, g = tid % TV_BG;
 	const unsigned gshift = (tid & 31) & ~(TV_BG - 1);
 	const unsigned gbits = (1u << TV_BG) - 1u, lower = (1u << g) - 1u;
@@ -403,7 +409,7 @@ __device__ __forceinline__ void tv_prefetch(const void* p) { asm volatile("prefe
 // FOLLOW: the candidates are the particle's HIT list (k_tv_hits / k_tv_build: the Verlet candidates within reach at the
 // positions of the current epoch), every lane just takes its share — no scan, no queue, no votes.  Otherwise the Verlet
 // list itself is scanned with the float positions and the survivors are queued (used when no hit list is valid).
-template <bool POLY, unsigned FIELDS, bool WALLONLY, bool FOLLOW, class F>
+template <bool POLY, unsigned FIELDS, bool WALLONLY, bool SPARSE, bool FOLLOW, class F>
 __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
@@ -415,7 +421,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 	const unsigned gbits = (1u << TV_G) - 1u, lower = (1u << g) - 1u, gmask = gbits << gshift;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
-	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
+	const float rfilt2 = K.hitR2;
 	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
 	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
@@ -440,6 +446,30 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
+		if (SPARSE) {   // does any particle of the tile want pairs?  (begin() of these bodies is idempotent)
+			bool want = false;
+			for (int p = tid; p < P; p += TV_T) {
+				const int i = own0 + p;
+				Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+				s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
+				if (s.type == K.p.ghost) continue;
+				typename F::Ctx ctx = {};
+				if (F::begin(ctx, S, K, s) && F::need_pairs(ctx)) want = true;
+			}
+			if (!__syncthreads_or(want)) {
+				for (int p = tid; p < P; p += TV_T) {   // nobody: the tails still run, one lane per particle
+					const int i = own0 + p;
+					Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+					s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
+					if (F::kCopyPos) S.pos2[i] = s.pi;
+					if (F::kCopyVel) S.vel2[i] = S.vel[i];
+					if (s.type == K.p.ghost) continue;
+					typename F::Ctx ctx = {};
+					if (F::begin(ctx, S, K, s)) F::end(ctx, S, K, s);
+				}
+				continue;   // uniform over the block
+			}
+		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
 		// first round's lists on their way while the staging loads land
@@ -556,7 +586,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 	const unsigned gbits = (1u << TV_G) - 1u, lower = (1u << g) - 1u;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
-	const float rfilt2 = (float)(K.reMax2 * (1.0 + 2e-5));
+	const float rfilt2 = K.hitR2;
 	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
 	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);

@@ -2,7 +2,7 @@
 """Summarise an .ncu-rep (read here, no GPU needed): per-kernel headline metrics, stall mix and — for one kernel —
 instruction / stall-sample shares per SOURCE LINE (joins ncu's SASS page with nvdisasm's line table of libpmps.so).
 
-    python profiles/ncu_summary.py gpurun_out/prof.ncu-rep [--lines <substring of the mangled kernel name> [--ncu-name <substring of the demangled name>]] [--top N]
+    python profiles/ncu_summary.py gpurun_out/prof.ncu-rep [--lines <substring of the mangled kernel name> [--ncu-name <substring of the demangled name>]] [--top N] [--lib <the libpmps.so the capture ran>]
 """
 import collections
 import csv
@@ -47,7 +47,7 @@ def raw(rep):
 
 def lines(rep, pat, top, ncupat):
     tmp = tempfile.mkdtemp()
-    subprocess.run(["cuobjdump", "-xelf", "all", os.path.join(ROOT, "polymps_b200", "libpmps.so")], cwd=tmp, capture_output=True)
+    subprocess.run(["cuobjdump", "-xelf", "all", (sys.argv[sys.argv.index("--lib") + 1] if "--lib" in sys.argv else os.path.join(ROOT, "polymps_b200", "libpmps.so"))], cwd=tmp, capture_output=True)
     seq = None
     for cub in glob.glob(os.path.join(tmp, "*.cubin")):
         txt = subprocess.run(["nvdisasm", "-g", "-c", cub], capture_output=True, text=True).stdout
