@@ -35,6 +35,7 @@ ALGO_BYTES = {
     "F1.viscosity+predict": 288, "F2.wall+collision": 225, "F2.collision": 104, "F3.pnd+diffusive+wall": 217, "F3.pnd+diffusive": 217,
     "F3.pnd+wall": 160, "mean_pnd_surface": 72, "E4.bc+eos": 48, "F5.gradient+wall+correct": 313, "F5.gradient+correct": 313,
     "shift.concentration": 64, "shift.gradient": 113, "shift.wall_gradient": 0, "list.build": 308,
+    "F5.gradient": 165, "W5.wall+correct": 148,
     # unfused stage kernels (PMPS_STAGED=1 / stage API)
     "viscosity": 116, "collision": 104, "pnd_neigh_npcd": 160, "pnd_diffusive": 124, "press_gradient": 96, "wall.closest_point": 121,
     "predict": 172, "correct": 148, "update_bc": 48,
@@ -210,7 +211,10 @@ def main_gpu(args):
     eng.profile(True); eng.step(args.profile_steps); prof = eng.profile_get(); eng.profile(False)
     prof_ms = {nm: t_ms / args.profile_steps for nm, t_ms, _ in prof}
     step_prof_ms = sum(prof_ms.values())
-    top = max(prof, key=lambda r: r[1])
+    # dominant kernel = the neighbour-pass (or sort/elementwise) launch group with the largest device time among those that carry
+    # algorithmic traffic; the candidate filters (list.hits / list.tile_build) move no reference array: they are overhead
+    # of this design and count only in the step-level figure below
+    top = max([r for r in prof if ALGO_BYTES.get(r[0], 0) > 0] or prof, key=lambda r: r[1])
     top_name, top_avg_ms = top[0], top[1] / max(top[2], 1)
     peak, peak_src, _ = measured_peaks()
     algo = ALGO_BYTES.get(top_name, 0) * sc.numParticles
@@ -220,7 +224,8 @@ def main_gpu(args):
                 "algorithmic_bytes_per_particle": ALGO_BYTES.get(top_name, 0),
                 "step": {"algorithmic_bytes_per_particle_step": STEP_ALGO_BYTES, "achieved_GBps": STEP_ALGO_BYTES * sc.numParticles / (ms / args.steps * 1e-3) / 1e9,
                          "frac": STEP_ALGO_BYTES * sc.numParticles / (ms / args.steps * 1e-3) / 1e9 / peak},
-                "kernels_ms_per_step": {k: round(v, 4) for k, v in sorted(prof_ms.items(), key=lambda kv: -kv[1])}}
+                "kernels_ms_per_step": {k: round(v, 4) for k, v in sorted(prof_ms.items(), key=lambda kv: -kv[1])},
+                "kernels_frac_of_hbm_peak": {k: round(ALGO_BYTES[k] * sc.numParticles / (t_ms / max(c, 1) * 1e-3) / 1e9 / peak, 4) for k, t_ms, c in prof if ALGO_BYTES.get(k, 0) > 0 and t_ms > 0}}
 
     # end to end through the C ABI with HOST buffers: every step uploads the carried state, steps, and reads it back
     e2e_steps = max(1, min(args.e2e_steps, args.steps))

@@ -121,6 +121,7 @@ int pmps_set_velmax(pmps_t* h, double velMax);
 int pmps_set_uniform_vel_wall(pmps_t* h, const double v[3]);
 /* device-resident inputs (bench `value` leg, multi-GPU slabs): same layout as the host arrays, device pointers */
 int pmps_upload_device(pmps_t* h, const PmpsHostArrays* device_arrays);
+int pmps_download_device(pmps_t* h, PmpsHostArrays* device_arrays);   /* gather to host order into device arrays */
 
 /* ---- stage calls: one per reference method, in mainLoopOfSimulation order (src/main.cpp:256-456) ----------- */
 int pmps_update_buckets(pmps_t* h);              /* MpsBucket::updateParticlesID            src/MpsBucket.cpp:299-353 */
@@ -156,6 +157,26 @@ int pmps_mean_neigh_fluid_pnd(pmps_t* h);        /* MpsPndNeigh::meanNeighFluidP
 /* ---- fused fast path ---------------------------------------------------------------------------------------- */
 int pmps_init_step0(pmps_t* h);                  /* the whole 0-th step, src/main.cpp:121-180 (buckets, wall pass, initial PND, BC, pressure) */
 int pmps_step(pmps_t* h, int nsteps);            /* nsteps x the loop body of src/main.cpp:256-460, state stays on device */
+
+/* ---- slab decomposition over the GPUs of one box ----------------------------------------------
+ * The reference is a single-process OpenMP code (no domain decomposition to mirror); these calls are what a
+ * distributed host (polymps_b200/slab.py: one process per GPU, NCCL send/recv between neighbouring slabs) needs on
+ * top of the calls above.  A rank uploads a particle table whose host indices [0, nOwned) are the particles inside its
+ * slab and [nOwned, numParticles) are halo copies of the neighbours' particles within bucketSide of its cuts, then runs
+ * the fused step phase by phase: after each phase it refreshes the halo copies of the fields that phase produced.
+ * velMax (src/MpsParticleVelPos.cpp:91), the displacement since the bucket rebuild and the out-of-domain test
+ * (src/MpsParticle.cpp:234-402) count owned particles only; pmps_slab_collect / pmps_slab_apply let the caller
+ * reduce them over the ranks so that every rank takes the same rebuild decision and uses the same velMax. */
+enum { PMPS_HF_POS = 1, PMPS_HF_VEL = 2, PMPS_HF_PRESS = 4, PMPS_HF_PNDI = 8, PMPS_HF_CONC = 16, PMPS_HF_PNDKI = 32 };
+int pmps_halo_planes(unsigned fields);           /* doubles per particle of a packed buffer (pos carries {x,y,z,type bits}) */
+int pmps_slab_begin(pmps_t* h, int nOwned);      /* after each (re-)upload of the rank's particle table */
+int pmps_halo_pack(pmps_t* h, unsigned fields, const int32_t* d_hostIndex, int n, double* d_out);   /* device pointers; plane-major */
+int pmps_halo_unpack(pmps_t* h, unsigned fields, int firstHostIndex, int n, const double* d_in);    /* onto host indices [first, first+n) */
+int pmps_step_phases(void);                      /* number of phases of the fused step */
+int pmps_step_phase(pmps_t* h, int phase, unsigned* haloFieldsAfter);   /* one phase of the loop body of src/main.cpp:256-460 */
+int pmps_slab_collect(pmps_t* h, double* d_out3);        /* device: {max displacement^2 since rebuild, max shift^2, velMax^2} of this rank */
+int pmps_slab_apply(pmps_t* h, const double* d_in3);     /* the same three after the MAX all-reduce: ends the step */
+int pmps_slab_wants_rebuild(pmps_t* h);                  /* 1: re-partition (migrate + new halo) and re-upload before the next step */
 
 /* ---- debug / parity hooks (tests only) ---------------------------------------------------------------------- */
 /* bucket id of every host-order particle as the reference computes it at rebuild time, and the members of every

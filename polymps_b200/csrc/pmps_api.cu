@@ -76,7 +76,7 @@ __global__ void k_correct(const __grid_constant__ DevView S, const __grid_consta
 			integrate_correct(p, v, S.acc.x[i], S.acc.y[i], S.acc.z[i], K.p.timeStep);
 			S.vel[i] = v; S.pos[i] = p;
 			S.acc.x[i] = 0.0; S.acc.y[i] = 0.0; S.acc.z[i] = 0.0;
-			v2 = v.x * v.x + v.y * v.y + v.z * v.z;
+			if (owned_slot(S, i)) v2 = v.x * v.x + v.y * v.y + v.z * v.z;
 			track_disp(S, K, i, p);
 		}
 	}
@@ -279,7 +279,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	{ void* q = nullptr; if (cudaMalloc(&q, h->stageBytes) != cudaSuccess) rc |= 1; else { h->allocs.push_back(q); h->stage = q; } }
 	if (cudaMallocHost((void**)&h->h_flags, sizeof(int32_t) * NFLAGS) != cudaSuccess) rc |= 1;
 	if (rc) return pmps_fail(h, PMPS_E_CUDA, "device allocation for %d particles failed: %s", n0, cudaGetErrorString(cudaGetLastError()));
-	S.n = n0; S.n0 = n0; S.pos2 = h->A.pos; S.vel2 = h->A.vel;
+	S.n = n0; S.n0 = n0; S.nOwn = 0x7fffffff; S.pos2 = h->A.pos; S.vel2 = h->A.vel;
 	h->A.n = n0; h->A.n0 = n0;
 	// float margin of the list test: positions are stored relative to domainMin in float
 	const double ext = fmax(fmax(P.domainMaxX - P.domainMinX, P.domainMaxY - P.domainMinY), P.domainMaxZ - P.domainMinZ);

@@ -128,7 +128,7 @@ struct BCorrectTail {
 		S.acc.x[i] = 0.0; S.acc.y[i] = 0.0; S.acc.z[i] = 0.0;
 		track_disp(S, K, i, p);
 		const unsigned long long b = (unsigned long long)__double_as_longlong(v.x * v.x + v.y * v.y + v.z * v.z);
-		if (b > S.velMax2Bits[0]) atomicMax(S.velMax2Bits, b);
+		if (b > S.velMax2Bits[0] && owned_slot(S, i)) atomicMax(S.velMax2Bits, b);
 	}
 };
 
@@ -170,7 +170,7 @@ struct BGradConcentration {
 			double4 p = s.pi;
 			p.x = __dsub_rn(p.x, __dmul_rn(K.p.coeffShifting2, g0)); p.y = __dsub_rn(p.y, __dmul_rn(K.p.coeffShifting2, g1)); p.z = __dsub_rn(p.z, __dmul_rn(K.p.coeffShifting2, g2));
 			S.pos2[s.i] = p;
-			track_disp(S, K, s.i, p); track_shift(S, p.x - s.pi.x, p.y - s.pi.y, p.z - s.pi.z);
+			track_disp(S, K, s.i, p); track_shift(S, s.i, p.x - s.pi.x, p.y - s.pi.y, p.z - s.pi.z);
 		}
 	}
 };
@@ -208,7 +208,7 @@ struct BWallGradConcentration {
 		}
 		if (inner) {
 			double4 pn = s.pi; pn.x = p[0]; pn.y = p[1]; pn.z = p[2]; S.pos2[s.i] = pn;
-			track_disp(S, K, s.i, pn); track_shift(S, pn.x - s.pi.x, pn.y - s.pi.y, pn.z - s.pi.z);
+			track_disp(S, K, s.i, pn); track_shift(S, s.i, pn.x - s.pi.x, pn.y - s.pi.y, pn.z - s.pi.z);
 		}
 	}
 };

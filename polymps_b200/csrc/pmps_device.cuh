@@ -69,13 +69,17 @@ __device__ __forceinline__ double wgt(double r, double re, int type) {
 __device__ __forceinline__ void atomic_max_f(float* addr, float v) {   // v >= 0: int order == float order
 	if (v > *addr) atomicMax((int*)addr, __float_as_int(v));
 }
+// slab decomposition: is slot i a particle this rank owns (not a halo copy)?  Always true on a single GPU.
+__device__ __forceinline__ bool owned_slot(const DevView& S, int i) { return S.nOwn == 0x7fffffff || S.hostIdx[i] < S.nOwn; }
 __device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, int i, const double4& p) {
+	if (!owned_slot(S, i)) return;
 	const float4 b = S.bpos[i];
 	const float dx = (float)(p.x - K.p.domainMinX) - b.x, dy = (float)(p.y - K.p.domainMinY) - b.y, dz = (float)(p.z - K.p.domainMinZ) - b.z;
 	atomic_max_f(S.maxDisp2, dx * dx + dy * dy + dz * dz);
 }
 
-__device__ __forceinline__ void track_shift(const DevView& S, double dx, double dy, double dz) {   // size of a shifting move (hit-list validity)
+__device__ __forceinline__ void track_shift(const DevView& S, int i, double dx, double dy, double dz) {   // size of a shifting move (hit-list validity)
+	if (!owned_slot(S, i)) return;
 	const float a = (float)dx, b = (float)dy, c = (float)dz; atomic_max_f(S.maxDisp2 + 1, (a * a + b * b + c * c) * 1.0001f);
 }
 

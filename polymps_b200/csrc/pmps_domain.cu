@@ -18,7 +18,7 @@ __global__ void k_ood_flag(const __grid_constant__ DevView S, const __grid_const
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= S.n) return;
 	const double4 p = S.pos[i];
-	if (pk_type(p) != K.p.fluid || !out_of_domain(K, p)) return;
+	if (pk_type(p) != K.p.fluid || !out_of_domain(K, p) || !owned_slot(S, i)) return;
 	const int k = atomicAdd(&S.flags[FLAG_OOD_COUNT], 1);
 	if (k < PMPS_OOD_CAP) S.oodList[k] = S.hostIdx[i];
 }

@@ -49,6 +49,9 @@ struct DevView {
 #undef X
 	int32_t n;                           // slots in use (= live particles at the last rebuild incl. later ghosts)
 	int32_t n0;                          // capacity (numParticlesZero)
+	int32_t nOwn;                        // slab decomposition (pmps_slab.cu): host indices >= nOwn are HALO COPIES of particles another
+	                                     // rank owns; they take part in every neighbour sum but not in velMax / displacement / out-of-domain
+	                                     // bookkeeping (their owner does that).  INT32_MAX on a single GPU.
 	int32_t listCap;
 	int32_t nB;                          // reference buckets (numBucketsX*Y*Z)
 	int32_t nC;                          // cells of the tile-major index (>= nB: tiles are padded to full size)
@@ -119,6 +122,7 @@ struct pmps_handle {
 	int nTilesAll = 0, smCount = 148, walkSeq = 0; bool tileWallValid = false;
 	double dispNow = 0.0, dispInc = 0.0, dispIncPrev = 0.0; int stepsSinceBuild = 0; bool needRebuild = true;   // displacement since the list build (step_begin's rebuild decision)
 	double lastShift = 0.0;              // largest shift of the last step's shifting passes
+	bool slab = false;                   // slab mode: rebuilds and the step-end scalars are decided by the caller from GLOBAL maxima (pmps_slab.cu)
 	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
 	bool hitValid = false;               // hlist matches the current positions (set by the list build / k_tv_hits, cleared when positions change)
 	size_t listAllocated = 0;
@@ -159,5 +163,6 @@ int pmps_ensure_list(pmps_handle* h);
 int pmps_tv_prepare(pmps_handle* h);
 int pmps_tv_hits(pmps_handle* h);
 int pmps_ppe_solve(pmps_handle* h);
+int pmps_step_end_apply(pmps_handle* h, double disp2, double shift2);   // pmps_stages.inc: the host half of step_end
 int pmps_mesh_upload(pmps_handle* h, int mesh_id, int nV, const double* V, int nF, const int32_t* F, const double* N,
                      int nTable, const double* xP, const double* xN, const double* Z, const int32_t* nW);

@@ -109,33 +109,37 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 extern "C" int pmps_upload(pmps_t* h, const PmpsHostArrays* a) { return upload_impl(h, a, false); }
 extern "C" int pmps_upload_device(pmps_t* h, const PmpsHostArrays* a) { return upload_impl(h, a, true); }
 
-extern "C" int pmps_download(pmps_t* h, PmpsHostArrays* a) {
+static int download_impl(pmps_handle* h, PmpsHostArrays* a, bool deviceDst) {
 	if (!h || !a) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
 	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_download: nothing uploaded");
 	if (a->numParticlesZero != h->numParticlesZero) return pmps_fail(h, PMPS_E_ARG, "pmps_download: numParticlesZero mismatch");
 	const int n0 = h->numParticlesZero, T = 256, G = cdiv(n0, T);
 	DevView& S = h->V; const int32_t* soh = S.slotOfHost;
 	// two staging halves so the gather of field k+1 can be queued behind the copy-out of field k
 	char* half[2] = { (char*)h->stage, (char*)h->stage + 32 * (size_t)n0 }; int hb = 0;
-	auto out = [&](void* dstHost, const void* stg, size_t bytes) { pin_host(h, dstHost, bytes); cudaMemcpyAsync(dstHost, stg, bytes, cudaMemcpyDeviceToHost, h->stream); };
+	auto out = [&](void* dstHost, const void* stg, size_t bytes) { if (deviceDst) return; pin_host(h, dstHost, bytes); cudaMemcpyAsync(dstHost, stg, bytes, cudaMemcpyDeviceToHost, h->stream); };
+	// device destinations (pmps_download_device): the gather kernels write straight into the caller's arrays
+#define STG(dst) (deviceDst ? (char*)(dst) : half[(hb ^= 1) ^ 1])
 	if (a->pos || a->particleType || a->PTYPE) {
 		char* b = half[hb]; hb ^= 1;
 		double* x = a->pos ? (double*)b : nullptr; int32_t* t = a->particleType ? (int32_t*)(b + 24 * (size_t)n0) : nullptr;
 		int32_t* pt = a->PTYPE ? (int32_t*)(b + 28 * (size_t)n0) : nullptr;
+		if (deviceDst) { x = a->pos; t = a->particleType; pt = a->PTYPE; }
 		LAUNCH(h, "download", k_dn_pack, G, T, x, t, pt, S.pos, soh, n0);
 		if (x) out(a->pos, x, 24 * (size_t)n0);
 		if (t) out(a->particleType, t, 4 * (size_t)n0);
 		if (pt) out(a->PTYPE, pt, 4 * (size_t)n0);
 	}
-	if (a->vel) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_pack, G, T, (double*)b, (int32_t*)nullptr, (int32_t*)nullptr, S.vel, soh, n0); out(a->vel, b, 24 * (size_t)n0); }
-	if (a->particleNearWall) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_u8, G, T, (uint8_t*)b, S.particleNearWall, soh, n0); out(a->particleNearWall, b, (size_t)n0); }
-#define X(n) if (a->n) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_i32, G, T, (int32_t*)b, S.n, soh, n0); out(a->n, b, 4 * (size_t)n0); }
+	if (a->vel) { char* b = STG(a->vel); LAUNCH(h, "download", k_dn_pack, G, T, (double*)b, (int32_t*)nullptr, (int32_t*)nullptr, S.vel, soh, n0); out(a->vel, b, 24 * (size_t)n0); }
+	if (a->particleNearWall) { char* b = STG(a->particleNearWall); LAUNCH(h, "download", k_dn_u8, G, T, (uint8_t*)b, S.particleNearWall, soh, n0); out(a->particleNearWall, b, (size_t)n0); }
+#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_i32, G, T, (int32_t*)b, S.n, soh, n0); out(a->n, b, 4 * (size_t)n0); }
 	PMPS_I32_FIELDS(X)
 #undef X
-#define X(n) if (a->n) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_f64, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 8 * (size_t)n0); }
+#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_f64, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 8 * (size_t)n0); }
 	PMPS_F64_FIELDS(X)
 #undef X
-#define X(n) if (a->n) { char* b = half[hb]; hb ^= 1; LAUNCH(h, "download", k_dn_v3, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 24 * (size_t)n0); }
+#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_v3, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 24 * (size_t)n0); }
 	PMPS_V3_FIELDS(X)
 #undef X
 	CUDA_TRY(h, cudaMemcpyAsync(h->h_flags, S.flags, sizeof(int32_t) * NFLAGS, cudaMemcpyDeviceToHost, h->stream));
@@ -143,4 +147,7 @@ extern "C" int pmps_download(pmps_t* h, PmpsHostArrays* a) {
 	h->numParticles = h->h_flags[FLAG_LIVE];
 	a->numParticles = h->numParticles;
 	return PMPS_OK;
+#undef STG
 }
+extern "C" int pmps_download(pmps_t* h, PmpsHostArrays* a) { return download_impl(h, a, false); }
+extern "C" int pmps_download_device(pmps_t* h, PmpsHostArrays* a) { return download_impl(h, a, true); }
