@@ -126,6 +126,31 @@ def dam3d_block(k: int, **kw) -> Case:
     return dam3d(2 * k, k, k, **kw)
 
 
+def dam3d_block_columns(k: int, i0: int, i1: int, *, lo: float = 0.01):
+    """Lattice columns i0 <= i < i1 (along x) of the benchmark block dam3d_block(k), without building the whole block:
+    (ptype, pos, vel, press, gid) with gid = the particle's index in dam3d_block(k)'s order (x fastest, then y, then z).
+    A slab rank generates only its own part of a 50M / 200M-particle block this way (polymps_b200/slab.py)."""
+    nx, ny, nz = 2 * k, k, k
+    i0 = max(0, int(i0)); i1 = min(nx, int(i1)); ni = max(0, i1 - i0)
+    m, j, i = np.meshgrid(np.arange(nz, dtype=np.int64), np.arange(ny, dtype=np.int64), np.arange(i0, i0 + ni, dtype=np.int64), indexing="ij")
+    i = i.ravel(); j = j.ravel(); m = m.ravel()
+    pos = np.stack([(i + 0.5) * lo, (j + 0.5) * lo, (m + 0.5) * lo], axis=1)
+    n = len(pos)
+    return {"ptype": np.zeros(n, dtype=np.int32), "pos": np.ascontiguousarray(pos), "vel": np.zeros((n, 3)), "press": np.zeros(n),
+            "gid": (m * ny + j) * nx + i}
+
+
+def dam3d_block_options(k: int, *, lo: float = 0.01) -> Case:
+    """dam3d_block(k) without particles: options, tank mesh and meta only."""
+    c = dam3d(1, 1, 1, lo=lo)   # a one-particle case just for the key set
+    nx, ny, nz = 2 * k, k, k
+    H = nz * lo; tank = ((1.61 / 0.6) * nx * lo, ny * lo, 2.0 * nz * lo); c0 = 15.0 * math.sqrt(H / 0.3)
+    kw = dict(dim=3, lo=lo, dt=0.375 * lo / c0, wall_type=1, c0=c0, max_vel=2.0 * math.sqrt(9.81 * H), dom_min=(0.0, 0.0, 0.0),
+              dom_max=tank, mps_type=1, grad_type=3, grad_corr=False, shifting=2, pnd_type=2)
+    return Case(name="block%d" % k, options=base_options(**kw), ptype=np.zeros(0, dtype=np.int32), pos=np.zeros((0, 3)), vel=np.zeros((0, 3)),
+                press=np.zeros(0), tris=box_triangles(*tank).astype(np.float32).astype(np.float64), meta={"tank": tank, "H": H, "c0": c0})
+
+
 def dam2d_particle(nx: int, nz: int, *, lo: float = 0.005, tank_nx: int | None = None, tank_nz: int | None = None,
                    incompressible: bool = False, name: str | None = None, **overrides) -> Case:
     """2D dam break with particle walls (dam1610_h300_lo0p0050_{WC,INC} option sets).

@@ -1,0 +1,20 @@
+"""Slab decomposition on the device: two ranks sharing cuda:0 (gloo, host-staged messages) against the single-GPU engine.
+The multi-GPU NCCL run of the same script is `gpurun --gpus 2 -- python -m torch.distributed.run ... tests/slab_parity.py`."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3])
+def test_slab_run_matches_single_engine(world):
+    port = 29700 + (os.getpid() % 1000) + world
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(HERE, "slab_parity.py"), "--backend", "gloo", "--one-gpu", "--steps", "40"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    sys.stdout.write(r.stdout[-4000:]); sys.stderr.write(r.stderr[-4000:])
+    assert r.returncode == 0 and "SLAB PARITY OK" in r.stdout
