@@ -165,6 +165,127 @@ def field_bytes(st, names):
     return int(sum(getattr(st, f).nbytes for f in names))
 
 
+def roofline_from_profile(prof, profile_steps, n_particles, ms_step, traffic):
+    """prof = [(launch name, total ms, launches)] of `profile_steps` profiled steps of ONE rank holding n_particles."""
+    prof_ms = {nm: t_ms / profile_steps for nm, t_ms, _ in prof}
+    step_prof_ms = sum(prof_ms.values())
+    # dominant kernel = the neighbour-pass (or sort/elementwise) launch group with the largest device time among those that carry
+    # algorithmic traffic; the candidate filters (list.hits / list.tile_build) move no reference array: they are overhead
+    # of this design and count only in the step-level figure below
+    top = max([r for r in prof if ALGO_BYTES.get(r[0], 0) > 0] or prof, key=lambda r: r[1])
+    top_name, top_avg_ms = top[0], top[1] / max(top[2], 1)
+    peak, peak_src, _ = measured_peaks()
+    algo = ALGO_BYTES.get(top_name, 0) * n_particles
+    achieved = algo / (top_avg_ms * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": top_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": traffic, "peak_source": peak_src, "kernel_ms": top_avg_ms, "kernel_share_of_step": top[1] / profile_steps / max(step_prof_ms, 1e-9),
+            "algorithmic_bytes_per_particle": ALGO_BYTES.get(top_name, 0),
+            "step": {"algorithmic_bytes_per_particle_step": STEP_ALGO_BYTES, "achieved_GBps": STEP_ALGO_BYTES * n_particles / (ms_step * 1e-3) / 1e9,
+                     "frac": STEP_ALGO_BYTES * n_particles / (ms_step * 1e-3) / 1e9 / peak},
+            "kernels_ms_per_step": {k: round(v, 4) for k, v in sorted(prof_ms.items(), key=lambda kv: -kv[1])},
+            "kernels_frac_of_hbm_peak": {k: round(ALGO_BYTES[k] * n_particles / (t_ms / max(c, 1) * 1e-3) / 1e9 / peak, 4) for k, t_ms, c in prof if ALGO_BYTES.get(k, 0) > 0 and t_ms > 0}}
+
+
+def main_gpu_slab(args, rank, world, local):
+    """N > 1: ONE dam-break block of N x (the single-GPU particle count), cut into x-slabs, one rank per GPU (polymps_b200/slab.py):
+    halo refresh after every phase of the step and migration at bucket rebuilds over NCCL send/recv, three scalars all-reduced per step."""
+    import torch
+    import torch.distributed as dist
+    from polymps_b200 import cases
+    from polymps_b200.mesh import PolygonMesh
+    from polymps_b200.params import ParticleSystem
+    from polymps_b200.slab import SlabEngine, choose_cuts, TABLE_FIELDS, field_width, field_dtype
+
+    kN = int(round(args.k * world ** (1.0 / 3.0)))
+    case = cases.dam3d_block_options(kN)
+    ps = ParticleSystem.from_json(case.options).set_parameters(); ps.allocate_buckets(None)
+    meshes = [PolygonMesh.from_triangles(case.tris).init_wall_tables(int(ps.dim), ps.weightType, ps.partDist, ps.reL, ps.reS)]
+    nx, ny, nz = 2 * kN, kN, kN; lo = ps.partDist
+    xi = (np.arange(nx) + 0.5) * lo
+    col = ((xi - ps.domainMinX) * ps.invBucketSide).astype(np.int64)
+    cuts = choose_cuts(np.bincount(col, minlength=ps.numBucketsX) * (ny * nz), world)
+    cuts_x = [ps.domainMinX + c * ps.bucketSide for c in cuts]
+    mine = np.nonzero((xi >= cuts_x[rank]) & (xi < cuts_x[rank + 1]))[0]
+    loc = cases.dam3d_block_columns(kN, int(mine[0]), int(mine[-1]) + 1, lo=lo)
+    halo_est = int(2 * 3.6 * ny * nz)
+    se = SlabEngine(ps, meshes, loc, cuts_x, rank, world, device=local, capacity=len(loc["ptype"]) + 2 * halo_est + 200000)
+    del loc
+    eng = se.eng; stream = se.stream
+    se.init_step0(); se.step(args.warmup); eng.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    l0 = eng.launch_count(); st0 = dict(se.dom.stats)
+    barrier(); sampler.start()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record(stream); se.step(args.steps); e1.record(stream)
+    eng.synchronize(); barrier()
+    clocks = sampler.stop()
+    ms_local = e0.elapsed_time(e1)
+    launches = eng.launch_count() - l0
+    st1 = dict(se.dom.stats)
+    n_own = se.n_own
+    t = torch.tensor([ms_local], dtype=torch.float64, device="cuda"); cnt = torch.tensor([float(n_own)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms = float(t.item()); total = float(cnt.item())
+    value = total * args.steps / (ms * 1e-3)
+    sc = eng.scalars()
+
+    eng.profile(True); se.step(args.profile_steps); prof = eng.profile_get(); eng.profile(False)
+    roofline = roofline_from_profile(prof, args.profile_steps, se.dom.n_live, ms / args.steps, args.traffic)
+    roofline["note"] = "rank 0's kernels; a rank's launches run over its owned particles + halo copies (%d + %d)" % (se.n_own, se.dom.n_live - se.n_own)
+
+    # end to end with HOST buffers: every step sends the carried state of the rank's table from pinned host memory, steps, reads it back
+    e2e_fields = [f for f in E2E_UP]
+    host = {f: torch.empty((se.backend.n0, 3) if field_width(f) == 3 else (se.backend.n0,), dtype=field_dtype(f)).pin_memory() for f in e2e_fields}
+    e2e_steps = max(1, min(args.e2e_steps, args.steps))
+
+    def roundtrip(first):
+        with torch.cuda.stream(stream):
+            if first:
+                T = se.backend.download_table(e2e_fields)
+                for f in e2e_fields:
+                    host[f].copy_(T[f], non_blocking=True)
+                eng.synchronize()
+            T = {f: host[f].to(se.dev, non_blocking=True) for f in e2e_fields}
+            se.backend.upload_table(T, se.dom.n_live, se.dom.n_own)
+        se.step(1)
+        with torch.cuda.stream(stream):
+            T = se.backend.download_table(e2e_fields)
+            for f in e2e_fields:
+                host[f].copy_(T[f], non_blocking=True)
+            eng.synchronize()
+    roundtrip(True)
+    barrier(); e0.record(stream)
+    for _ in range(e2e_steps):
+        roundtrip(False)
+    e1.record(stream); eng.synchronize(); barrier()
+    te = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda"); dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    nb = torch.tensor([float(sum(host[f].numel() * host[f].element_size() for f in e2e_fields))], dtype=torch.float64, device="cuda"); dist.all_reduce(nb)
+    e2e = {"value": total * e2e_steps / (float(te.item()) * 1e-3), "unit": UNIT, "steps": e2e_steps, "h2d_bytes_per_step": int(nb.item()), "d2h_bytes_per_step": int(nb.item()),
+           "api": "per rank and step: pinned host table -> pmps_upload_device, the phased step with halo refreshes (re-partition included: new positions force the bucket rebuild), pmps_download_device -> pinned host"}
+    per_rank = [None] * world
+    dist.all_gather_object(per_rank, {"owned": n_own, "halo": se.dom.n_live - n_own, "ms_per_step": ms_local / args.steps,
+                                      "repartitions": st1["repartitions"] - st0["repartitions"], "migrants_out": st1["migrants_out"] - st0["migrants_out"],
+                                      "halo_refresh_MB_per_step": (st1["refresh_bytes"] - st0["refresh_bytes"]) / args.steps / 1e6})
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "synthetic 3D WC dam-break block %dx%dx%d = %d particles over %d GPUs (%.2fM per GPU), STL polygon tank (10 triangles), InputDamWC option set" % (nx, ny, nz, int(total), world, total / world / 1e6),
+                       "particles_total": int(total), "parallelism": "%d x-slabs cut on bucket columns, one rank per GPU; halo refresh after every phase + migration at rebuilds over NCCL send/recv; 3 scalars MAX-all-reduced per step" % world,
+                       "l2": "state per GPU (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (se.dom.n_live * 1500 / 1e9),
+                       "ranks": per_rank, "max_displacement_over_lo": sc.maxDisplacement / ps.partDist},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    torch.cuda.synchronize()
+    host.clear(); del roundtrip   # pinned buffers were used on the engine's stream: release them before the stream goes away
+    import gc; gc.collect()
+    se.close()
+    dist.destroy_process_group()
+
+
 def main_gpu(args):
     import torch
     import torch.distributed as dist
@@ -174,6 +295,8 @@ def main_gpu(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the product has no CPU path; use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    if world > 1:
+        return main_gpu_slab(args, rank, world, local)
     from polymps_b200.engine import make_engine
 
     case = block_case(args.k)
@@ -209,23 +332,7 @@ def main_gpu(args):
 
     # per-kernel device time (CUDA events around every launch on the step stream; separate pass: it serialises)
     eng.profile(True); eng.step(args.profile_steps); prof = eng.profile_get(); eng.profile(False)
-    prof_ms = {nm: t_ms / args.profile_steps for nm, t_ms, _ in prof}
-    step_prof_ms = sum(prof_ms.values())
-    # dominant kernel = the neighbour-pass (or sort/elementwise) launch group with the largest device time among those that carry
-    # algorithmic traffic; the candidate filters (list.hits / list.tile_build) move no reference array: they are overhead
-    # of this design and count only in the step-level figure below
-    top = max([r for r in prof if ALGO_BYTES.get(r[0], 0) > 0] or prof, key=lambda r: r[1])
-    top_name, top_avg_ms = top[0], top[1] / max(top[2], 1)
-    peak, peak_src, _ = measured_peaks()
-    algo = ALGO_BYTES.get(top_name, 0) * sc.numParticles
-    achieved = algo / (top_avg_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": top_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": args.traffic, "peak_source": peak_src, "kernel_ms": top_avg_ms, "kernel_share_of_step": top[1] / args.profile_steps / max(step_prof_ms, 1e-9),
-                "algorithmic_bytes_per_particle": ALGO_BYTES.get(top_name, 0),
-                "step": {"algorithmic_bytes_per_particle_step": STEP_ALGO_BYTES, "achieved_GBps": STEP_ALGO_BYTES * sc.numParticles / (ms / args.steps * 1e-3) / 1e9,
-                         "frac": STEP_ALGO_BYTES * sc.numParticles / (ms / args.steps * 1e-3) / 1e9 / peak},
-                "kernels_ms_per_step": {k: round(v, 4) for k, v in sorted(prof_ms.items(), key=lambda kv: -kv[1])},
-                "kernels_frac_of_hbm_peak": {k: round(ALGO_BYTES[k] * sc.numParticles / (t_ms / max(c, 1) * 1e-3) / 1e9 / peak, 4) for k, t_ms, c in prof if ALGO_BYTES.get(k, 0) > 0 and t_ms > 0}}
+    roofline = roofline_from_profile(prof, args.profile_steps, sc.numParticles, ms / args.steps, args.traffic)
 
     # end to end through the C ABI with HOST buffers: every step uploads the carried state, steps, and reads it back
     e2e_steps = max(1, min(args.e2e_steps, args.steps))
@@ -248,7 +355,7 @@ def main_gpu(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "synthetic 3D WC dam-break block %dx%dx%d = %d particles per GPU, STL polygon tank (10 triangles), InputDamWC option set" % (2 * args.k, args.k, args.k, n),
-                       "particles_per_gpu": n, "parallelism": "1 GPU" if world == 1 else "%d independent slabs-to-be (replicas; halo exchange not built yet)" % world,
+                       "particles_per_gpu": n, "parallelism": "1 GPU",
                        "l2": "state per GPU (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (n * 1500 / 1e9),
                        "max_displacement_over_lo": sc2.maxDisplacement / ps.partDist, "max_bucket_count": sc2.maxBucketCount},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline}

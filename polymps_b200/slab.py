@@ -143,7 +143,7 @@ class SlabDomain:
             hs = {k: v.cpu() for k, v in send.items()}; hr = {k: torch.empty_like(v, device="cpu") for k, v in recv.items()}
             self._exchange_raw(hs, hr)
             for k, v in recv.items():
-                if v.numel() > 0:
+                if v.numel() > 0 and self._peer(k) is not None:
                     v.copy_(hr[k])
             return
         self._exchange_raw(send, recv)
@@ -407,4 +407,9 @@ class SlabEngine:
         return self.eng.scalars()
 
     def close(self):
+        """Drops every tensor that lives on the engine's stream BEFORE the handle (and with it the stream) is destroyed."""
+        import gc
+        torch.cuda.synchronize(self.dev)
+        self.dom._buf.clear(); self.dom.gid = None; self.dom.send_idx = {}; self.scal = None
+        gc.collect(); torch.cuda.empty_cache()
         self.eng.close()
