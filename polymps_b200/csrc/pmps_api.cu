@@ -47,7 +47,7 @@ __global__ void k_predict(const __grid_constant__ DevView S, const __grid_consta
 	double4 p = S.pos[i];
 	if (pk_type(p) == K.p.ghost) return;
 	if (pk_type(p) == K.p.fluid) {
-		double4 v = S.vel[i];
+		double4 v = S.vel[i]; const double4 o = p;
 		integrate_predict(p, v, S.acc.x[i], S.acc.y[i], S.acc.z[i], K.p.timeStep);
 		S.vel[i] = v; S.pos[i] = p;
 		track_disp(S, K, i, p);
@@ -72,7 +72,7 @@ __global__ void k_correct(const __grid_constant__ DevView S, const __grid_consta
 	if (i < S.n) {
 		double4 p = S.pos[i];
 		if (pk_type(p) == K.p.fluid) {
-			double4 v = S.vel[i];
+			double4 v = S.vel[i]; const double4 o = p;
 			integrate_correct(p, v, S.acc.x[i], S.acc.y[i], S.acc.z[i], K.p.timeStep);
 			S.vel[i] = v; S.pos[i] = p;
 			S.acc.x[i] = 0.0; S.acc.y[i] = 0.0; S.acc.z[i] = 0.0;
@@ -247,7 +247,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	DevView& S = h->V; KParams& K = h->K; const PmpsParams& P = K.p;
 	int rc = 0;
 	rc |= alloc_view(h, S, n0, true); rc |= alloc_view(h, h->A, n0, false);
-	rc |= dalloc(h, &S.scratch1, n0); rc |= dalloc(h, &S.bpos, n0); rc |= dalloc(h, &S.slotOfHost, n0); rc |= dalloc(h, &S.cellOf, n0);
+	rc |= dalloc(h, &S.scratch1, n0); rc |= dalloc(h, &S.bpos, n0); rc |= dalloc(h, &S.hpos, n0); rc |= dalloc(h, &S.slotOfHost, n0); rc |= dalloc(h, &S.cellOf, n0);
 	rc |= dalloc(h, &S.cellStart, (size_t)S.nC + 2); rc |= dalloc(h, &h->cellCount, (size_t)S.nC + 2);
 	rc |= dalloc(h, &h->perm, n0); rc |= dalloc(h, &h->arbRank, n0); rc |= dalloc(h, &h->newCell, n0);
 	rc |= dalloc(h, &h->tmpHost, 2 * (size_t)n0);
@@ -258,7 +258,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.itemTab, items * (size_t)K.tabStride); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
 		int sm = 148; cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device); h->smCount = sm;
 	}
-	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 2); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
+	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 2); rc |= dalloc(h, &S.hitMove, 4); rc |= dalloc(h, &S.hitFlag, 2); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
 	// Verlet list: radius = bucketSide (the reference's own search slack, src/MpsBucket.cpp:23); capacity from the
 	// lattice count with head room (PMPS_LIST_CAP overrides)
 	const double rl = P.bucketSide, lo = P.partDist;
@@ -288,7 +288,11 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	K.rl2 = (float)(rlf * rlf);
 	const double guard = 0.5 * (rl - maxRe) - 8.0 * 1.2e-7 * ext;
 	K.guard2 = (float)(guard > 0 ? guard * guard : 0.0);
-	K.hitDelta = 0.01 * lo;
+	// reach of the hit lists beyond the cut-offs: a hit list stays valid until somebody may have moved hitDelta since it was made
+	// (k_hits_decide); a larger reach means fewer rebuilds and more rejected candidates per pass, (re + 2 delta)^3
+	K.hitDelta = 0.05 * lo;
+	if (const char* e = getenv("PMPS_HIT_DELTA")) { const double v = atof(e); if (v > 0.0 && v < 0.2) K.hitDelta = v * lo; }
+	if (maxRe + 2.0 * K.hitDelta > rl - 1e-3 * lo) K.hitDelta = fmax(0.5 * (rl - 1e-3 * lo - maxRe), 0.0);   // never beyond the Verlet radius
 	{ const double r = (maxRe + 2.0 * K.hitDelta) * (1.0 + 1e-5); K.hitR2 = (float)(r * r); }
 	// |x_j - mirror_i| >= 2 dist(i, wall) - displacement - |x_j - x_i| > re whenever dist > re + displacement/2: margin = the full guard
 	{ const double far = maxRe * (1.0 + 1e-6) + (guard > 0 ? guard : 0.0) + 1e-6 * lo; K.mirrorFar2 = far * far; }

@@ -62,6 +62,7 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 		live--; S.flags[FLAG_OOD_TOTAL] += 1;
 	}
 	S.flags[FLAG_LIVE] = live;
+	S.hitMove[0] = 1e30f;   // a slot changed its content: the hit lists are rebuilt at the next check
 }
 
 extern "C" int pmps_check_out_domain(pmps_t* h) {

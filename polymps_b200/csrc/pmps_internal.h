@@ -29,6 +29,7 @@ struct DevView {
 	double4* pos; double4* vel;          // current
 	double4* pos2; double4* vel2;        // alternate (ping-pong target of integrators / permute)
 	float4* bpos;                        // position at list-build time, float, relative to domainMin (guard + build)
+	float4* hpos;                        // position when the hit list was made, same format (hit-list validity, k_hits_decide)
 	int32_t* hostIdx;                    // slot -> host (reference) index
 	int32_t* slotOfHost;                 // host index -> slot
 	int32_t* cellOf;                     // slot -> bucket id at the last rebuild
@@ -59,6 +60,9 @@ struct DevView {
 	// device scalars
 	unsigned long long* velMax2Bits;     // max |v|^2 of fluid particles (bits of a non-negative double)
 	float* maxDisp2;                     // [0] max squared displacement since the list build, [1] max squared shift of the shifting passes of the step (float, >= 0)
+	float* hitMove;                      // hit-list validity (pmps_tv.cuh): [0] largest squared displacement of ANY slot (halo copies included)
+	                                     // from its position when the hit list was made (running maximum, reset by a rebuild)
+	int32_t* hitFlag;                    // [0] 1: k_tv_hits must rebuild the hit list now (set by k_hits_decide), [1] rebuilds so far
 	int32_t* flags;                      // [0] list overflow, [1] out-of-domain count, [2] guard violated, [3] live count
 	int32_t* oodList;                    // host ids flagged by the out-of-domain test
 	const struct DevMesh* meshes; int32_t nMeshes;   // polygon meshes (device array), set by pmps_set_mesh
@@ -124,6 +128,7 @@ struct pmps_handle {
 	double lastShift = 0.0;              // largest shift of the last step's shifting passes
 	bool slab = false;                   // slab mode: rebuilds and the step-end scalars are decided by the caller from GLOBAL maxima (pmps_slab.cu)
 	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
+	bool hitForce = false;               // positions were replaced from outside (upload): the next check rebuilds the hit list
 	bool hitValid = false;               // hlist matches the current positions (set by the list build / k_tv_hits, cleared when positions change)
 	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;

@@ -27,12 +27,17 @@ __global__ void k_halo_pack(const __grid_constant__ DevView S, unsigned f, const
 	if (f & PMPS_HF_CONC) { o[0] = S.concentration[s]; o += st; }
 	if (f & PMPS_HF_PNDKI) { o[0] = S.pndki[s]; o += st; }
 }
-__global__ void k_halo_unpack(const __grid_constant__ DevView S, unsigned f, int first, int n, const double* __restrict__ in) {
+__global__ void k_halo_unpack(const __grid_constant__ DevView S, const __grid_constant__ KParams K, unsigned f, int first, int n, const double* __restrict__ in) {
 	const int t = blockIdx.x * blockDim.x + threadIdx.x;
 	if (t >= n) return;
 	const int s = S.slotOfHost[first + t];
 	const double* o = in + t; const size_t st = (size_t)n;
-	if (f & PMPS_HF_POS) { double4 p; p.x = o[0]; p.y = o[st]; p.z = o[2 * st]; p.w = o[3 * st]; S.pos[s] = p; o += 4 * st; }
+	if (f & PMPS_HF_POS) {
+		double4 p; p.x = o[0]; p.y = o[st]; p.z = o[2 * st]; p.w = o[3 * st];
+		S.pos[s] = p; o += 4 * st;
+		track_hit_disp(S, K, s, p);   // the copy's TRUE position: does the hit list still cover it?
+
+	}
 	if (f & PMPS_HF_VEL) { double4 v = S.vel[s]; v.x = o[0]; v.y = o[st]; v.z = o[2 * st]; S.vel[s] = v; o += 3 * st; }
 	if (f & PMPS_HF_PRESS) { S.press[s] = o[0]; o += st; }
 	if (f & PMPS_HF_PNDI) { S.pndi[s] = o[0]; o += st; }
@@ -65,9 +70,9 @@ extern "C" int pmps_halo_unpack(pmps_t* h, unsigned fields, int firstHostIndex, 
 	if (firstHostIndex < h->V.nOwn && n > 0) return pmps_fail(h, PMPS_E_ARG, "pmps_halo_unpack: host index %d is an owned particle (nOwned %d)", firstHostIndex, h->V.nOwn);
 	if (n == 0 || fields == 0) return PMPS_OK;
 	cudaSetDevice(h->device);
-	LAUNCH(h, "halo.unpack", k_halo_unpack, cdiv(n, 256), 256, h->V, fields, firstHostIndex, n, d_in);
+	LAUNCH(h, "halo.unpack", k_halo_unpack, cdiv(n, 256), 256, h->V, h->K, fields, firstHostIndex, n, d_in);
 	CUDA_TRY(h, cudaGetLastError());
-	if (fields & PMPS_HF_POS) h->hitValid = false;
+	if (fields & PMPS_HF_POS) h->hitValid = false;   // checked (and rebuilt if needed) before the next full pass
 	return PMPS_OK;
 }
 

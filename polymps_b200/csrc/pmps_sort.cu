@@ -257,13 +257,25 @@ int pmps_tv_prepare(pmps_handle* h) {
 	CUDA_TRY(h, cudaFuncSetAttribute(k_tv_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 	{ ProfScope ps_(h, "list.tile_build"); k_tv_build<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, h->walkSeq++); h->launches++; }
 	CUDA_TRY(h, cudaGetLastError());
-	h->hitValid = true;   // the build emits the hit list of the build positions too
+	CUDA_TRY(h, cudaMemsetAsync(S.hitMove, 0, 4 * sizeof(float), h->stream));   // the build emits the hit list of the build positions too
+	h->hitValid = true; h->hitForce = false;
 	return PMPS_OK;
 }
 
-// hit list of the current positions (after the prediction / correction moved the particles)
+// Is the hit list still good for the positions of the new epoch?  It reaches hitDelta beyond every cut-off on both sides, so it
+// is while nobody has moved farther than hitDelta from where it was when the list was made (hpos; track_hit_disp keeps the
+// running maximum over all slots).  One thread.
+__global__ void k_hits_decide(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int force) {
+	const float lim = (float)K.hitDelta * 0.98f;   // float positions relative to domainMin: a few 1e-7 of the domain extent of slack
+	if (force || S.hitMove[0] > lim * lim) { S.hitFlag[0] = 1; S.hitFlag[1] += 1; S.hitMove[0] = 0.f; }
+	else S.hitFlag[0] = 0;
+}
+// hit list for the current positions (after the prediction / correction / shifting moved the particles): re-made only when
+// k_hits_decide says the old one may miss a pair (k_tv_hits returns at once otherwise)
 int pmps_tv_hits(pmps_handle* h) {
 	DevView& S = h->V;
+	LAUNCH(h, "list.hits_decide", k_hits_decide, 1, 1, S, h->K, h->hitForce ? 1 : 0);
+	h->hitForce = false;
 	if (h->walkSeq >= PMPS_CURSORS) return pmps_fail(h, PMPS_E_STATE, "more than %d tile passes since the last pmps_update_buckets", PMPS_CURSORS - 1);
 	const size_t smem = 16 * (size_t)TV_MAXM + 2 * (size_t)TV_MAXOWN + (size_t)TV_NG * S.tlCap * 2;
 	CUDA_TRY(h, cudaFuncSetAttribute(k_tv_hits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -102,7 +102,7 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 	CUDA_TRY(h, cudaGetLastError());
 	h->numParticles = a->numParticles; h->haveState = true;
 	if (a->particleNearWall) h->tileWallValid = false;
-	if (a->pos) { h->hitValid = false; h->needRebuild = true; }   // new positions: the next fused step re-sorts and rebuilds the lists
+	if (a->pos) { h->hitValid = false; h->hitForce = true; h->needRebuild = true; }   // new positions: the next fused step re-sorts and rebuilds the lists
 	return PMPS_OK;
 }
 

@@ -359,7 +359,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 				if (cntH > S.tlCap) cntH = S.tlCap;
 				uint4* dstH = (uint4*)(S.hlist + (size_t)i * (size_t)S.tlCap);
 				for (int q = g; q < (cntH + TV_CHUNK - 1) / TV_CHUNK * (TV_CHUNK / 8); q += TV_BG) dstH[q] = ((const uint4*)hl)[q];
-				if (g == 0) { S.tlistCnt[i] = (uint16_t)cnt; S.hcnt[i] = (uint16_t)cntH; }
+				if (g == 0) { S.tlistCnt[i] = (uint16_t)cnt; S.hcnt[i] = (uint16_t)cntH; S.hpos[i] = S.bpos[i]; }
 			}
 			__syncwarp();
 		}
@@ -575,6 +575,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 // of the new epoch; every neighbour pass until the next change then follows the hit list (k_tv, FOLLOW).  Stages only the
 // float positions (16 bytes per halo record); same warp-uniform scan as the walker's scanning mode.
 static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
+	if (!S.hitFlag[0]) return;   // k_hits_decide: the hit list still covers the current positions
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
 	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
@@ -638,7 +639,10 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 				const int nq = (cntH + TV_CHUNK - 1) / TV_CHUNK * (TV_CHUNK / 8);
 				#pragma unroll
 				for (int v = 0; v < TV_PER / 8; v++) for (int c = 0; c * (TV_CHUNK / 8) < nq; c++) dstH[c * (TV_CHUNK / 8) + g * (TV_PER / 8) + v] = ((const uint4*)hl)[c * (TV_CHUNK / 8) + g * (TV_PER / 8) + v];
-				if (g == 0) S.hcnt[i] = (uint16_t)cntH;
+				if (g == 0) {
+					S.hcnt[i] = (uint16_t)cntH;
+					S.hpos[i] = make_float4(fi.x + (float)(ox - K.p.domainMinX), fi.y + (float)(oy - K.p.domainMinY), fi.z + (float)(oz - (three ? K.p.domainMinZ : 0.0)), 0.f);
+				}
 			}
 			__syncwarp();
 		}
