@@ -151,7 +151,8 @@ def main_reference(args):
     cb, sec = run_reference_cpu(args.ref_k, args.steps, args.warmup, threads)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": {"workload": "3D WC dam-break block, InputDamWC option set (CPU sample %d particles)" % (2 * args.ref_k ** 3)},
+            "data": "synthetic", "config": {"workload": "synthetic 3D WC dam-break block %dx%dx%d = %d particles per GPU, STL polygon tank (10 triangles), InputDamWC option set" % (2 * args.k, args.k, args.k, 2 * args.k ** 3),
+                                            "cpu_sample": "each step runs a %d-particle block of the same recipe (CPU throughput is size-insensitive, SURVEY 8d)" % (2 * args.ref_k ** 3)},
             "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
@@ -372,8 +373,8 @@ def main_gpu(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=40, help="timed steps (40: several bucket rebuilds / re-partitions fall inside the timed region)")
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--k", type=int, default=171, help="block edge: 2k x k x k particles per GPU (171 -> 10.0M)")
     ap.add_argument("--ref-k", type=int, default=50, help="block edge of the CPU sample for --impl reference")
