@@ -20,7 +20,9 @@
 #pragma once
 #include "pmps_bodies.cuh"
 
+#ifndef TV_T
 #define TV_T 256                 // threads per block
+#endif
 // TV_G (lanes per particle in the walker) is defined in pmps_device.cuh next to the group reductions
 #define TV_NG (TV_T / TV_G)      // particles per round
 #define TV_BG 8                  // lanes per particle in the list build
