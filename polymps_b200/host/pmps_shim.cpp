@@ -1,0 +1,197 @@
+// pmps_shim.cpp — the reference-side binding of libpmps: the per-timestep methods of the reference's engine classes
+// (called from the UNMODIFIED src/main.cpp:98-456) re-implemented as forwards to the C ABI (include/pmps.h).
+//
+// Built only where the reference tree is present (polymps_b200/host/Makefile): this file is compiled against the reference's
+// own headers and linked IN FRONT OF the unmodified reference objects with -Wl,--allow-multiple-definition, so the linker
+// takes these definitions for the hot-path methods and the reference's for everything else (input parsing, setParameters,
+// bucket geometry, STL reading, wall tables, VTU output).  Nothing of the reference is copied or edited.
+//
+// State policy: the particle arrays live on the device between calls.  The host arrays of MpsParticle are refreshed
+//   * before every output iteration (writeOutputFiles reads them, src/main.cpp:234-236): pmps_download of every field;
+//   * every step: numParticles, velMax, CFLcurrent (displayInfo, src/MpsInputOutput.cpp:37-55).
+// Error behaviour: the reference's methods are void and exit(10) on fatal conditions (src/MpsBucket.cpp:104): same here.
+#include <limits>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include "MpsParticleSystem.h"
+#include "MpsParticle.h"
+#include "MpsBucket.h"
+#include "MpsPndNeigh.h"
+#include "MpsViscosity.h"
+#include "MpsPressure.h"
+#include "MpsParticleCollision.h"
+#include "MpsShifting.h"
+#include "MpsVectorMatrix.h"
+#include "MpsParticleVelPos.h"
+#include "MpsBoundaryCondition.h"
+#include "PolygonMesh.h"
+#include "pmps.h"
+
+namespace {
+pmps_t* g_h = nullptr;
+MpsParticleSystem* g_S = nullptr;
+MpsParticle* g_P = nullptr;
+int g_oodCalls = 0;            // checkParticleOutDomain is called three times per step (src/main.cpp:283,411,441)
+bool g_meshSet[3] = { false, false, false };
+
+void die(const char* where, int rc) {
+	fprintf(stderr, "libpmps: %s failed (%d): %s\n", where, rc, pmps_last_error(g_h));
+	exit(10);
+}
+#define CALL(fn) do { const int rc_ = (fn); if (rc_ < 0) die(#fn, rc_); } while (0)
+
+PmpsHostArrays host_arrays(MpsParticle* P) {
+	PmpsHostArrays a; memset(&a, 0, sizeof a);
+	a.numParticles = P->numParticles; a.numParticlesZero = P->numParticlesZero;
+#define F(n) a.n = P->n;
+	F(particleType) F(particleBC) F(numNeigh) F(PTYPE) F(nearMeshType) F(numNeighWallContribution) F(elementID)
+	F(press) F(pndi) F(pndki) F(pndski) F(pndSmall) F(npcdDeviation2) F(concentration) F(velDivergence) F(diffusiveTerm)
+	F(pndWallContribution) F(distParticleWall2) F(deviationDotPolygonNormal) F(RHO) F(MEU) F(pndAuxVar1) F(pndAuxVar2)
+	F(pos) F(vel) F(acc) F(accStar) F(npcdDeviation) F(gradConcentration) F(correcMatrixRow1) F(correcMatrixRow2) F(correcMatrixRow3)
+	F(particleAtWallPos) F(mirrorParticlePos) F(polygonNormal) F(forceWall) F(dvelCollision)
+#undef F
+	a.particleNearWall = reinterpret_cast<uint8_t*>(P->particleNearWall);   // C++ bool, one byte
+	if (P->pressurePPE.size() == P->numParticlesZero) { a.pressurePPE = P->pressurePPE.data(); a.sourceTerm = P->sourceTerm.data(); }
+	return a;
+}
+
+// POD snapshot of MpsParticleSystem after setParameters() / MpsBucket::allocateMemory() — same member names on both sides
+PmpsParams params_of(MpsParticleSystem* S) {
+	PmpsParams p; memset(&p, 0, sizeof p);
+	p.abi_version = PMPS_ABI_VERSION;
+	p.shiftingJacobi = 1;   // parallel-safe shifting: the reference's own loop is a race for more than one thread
+#define C(n) p.n = (decltype(p.n))S->n;
+	C(dim) C(wallType) C(mpsType) C(solverType) C(pndType) C(weightType) C(gradientType) C(gradientCorrection)
+	C(slipCondition) C(freeSurfType) C(collisionType) C(shiftingType) C(repulsiveForceType) C(fluidType) C(domainTypeBC)
+	C(ghost) C(fluid) C(wall) C(dummyWall) C(surface) C(inner) C(other) C(numBucketsX) C(numBucketsY) C(numBucketsZ)
+	C(numOfMeshs) C(domainMinX) C(domainMinY) C(domainMinZ) C(domainMaxX) C(domainMaxY) C(domainMaxZ) C(bucketSide)
+	C(invBucketSide) C(partDist) C(timeStep) C(epsilonZero) C(reS) C(reL) C(reS2) C(reL2) C(gravityX) C(gravityY)
+	C(gravityZ) C(densityWall) C(DNS_FL1) C(DNS_FL2) C(soundSpeed) C(gamma) C(relaxPress) C(alphaCompressibility)
+	C(reRepulsiveForce) C(expectMaxVelocity) C(repForceCoefMitsume) C(repForceCoefLennardJones)
+	C(repForceCoefMonaghanKajtar) C(pndSmallZero) C(pndLargeZero) C(pndGradientZero) C(lambdaZero) C(numNeighZero)
+	C(coeffViscMultiphase) C(coeffPressGrad) C(coeffPressEMPS) C(coeffPressWCMPS) C(coeffShifting1) C(coeffShifting2)
+	C(coeffPPE) C(coeffPPESource) C(distCollisionLimit2) C(restitutionCollision) C(lambdaCollision) C(betaPnd)
+	C(betaNeigh) C(delta2) C(velMax)
+#undef C
+	for (int k = 0; k < 3; k++) p.uniformVelWall[k] = S->uniformVelWall[k];
+	return p;
+}
+
+// first hot-path call: create the handle from the (by now complete) parameter set and send the particle arrays
+pmps_t* handle(MpsParticleSystem* S, MpsParticle* P) {
+	if (g_h) return g_h;
+	g_S = S; g_P = P;
+	const PmpsParams p = params_of(S);
+	int dev = 0; if (const char* e = getenv("PMPS_DEVICE")) dev = atoi(e);
+	const int rc = pmps_create(&p, dev, &g_h);
+	if (rc < 0) { fprintf(stderr, "libpmps: pmps_create failed (%d): %s\n", rc, pmps_last_error(nullptr)); exit(10); }
+	const PmpsHostArrays a = host_arrays(P);
+	CALL(pmps_upload(g_h, &a));
+	return g_h;
+}
+pmps_t* handle() {
+	if (!g_h) { fprintf(stderr, "libpmps: a mesh / particle method was called before MpsBucket::updateParticlesID\n"); exit(10); }
+	return g_h;
+}
+void pull_scalars() {   // what displayInfo and the host loop read
+	PmpsScalars s; CALL(pmps_get_scalars(g_h, &s));
+	g_P->numParticles = s.numParticles; g_S->velMax = s.velMax; g_S->CFLcurrent = s.CFLcurrent;
+}
+void pull_arrays() {    // before writeOutputFiles
+	PmpsHostArrays a = host_arrays(g_P);
+	CALL(pmps_download(g_h, &a));
+	g_P->numParticles = a.numParticles;
+}
+// the iteration about to start writes output (src/main.cpp:234): numOfIterations is incremented right after the call we are in
+bool output_next(int inc) { return g_S->iterOutput > 0 && (g_S->numOfIterations + inc) % g_S->iterOutput == 0; }
+
+// row-major copies of an Eigen mesh (column-major) for pmps_set_mesh; the wall tables are private members, passed in by the caller
+void send_mesh(int me, const Eigen::MatrixXd& NV, const Eigen::MatrixXi& NF, const Eigen::MatrixXd& NN, const std::vector<double>& xP,
+               const std::vector<double>& xN, const std::vector<double>& Z, const std::vector<int>& nNW) {
+	const int nV = (int)NV.rows(), nF = (int)NF.rows();
+	std::vector<double> V(3 * (size_t)nV), N(3 * (size_t)nF); std::vector<int32_t> F(3 * (size_t)nF);
+	for (int i = 0; i < nV; i++) for (int k = 0; k < 3; k++) V[3 * i + k] = NV(i, k);
+	for (int i = 0; i < nF; i++) for (int k = 0; k < 3; k++) { F[3 * i + k] = NF(i, k); N[3 * i + k] = NN(i, k); }
+	std::vector<int32_t> nw(nNW.begin(), nNW.end());
+	CALL(pmps_set_mesh(handle(), me, nV, V.data(), nF, F.data(), N.data(), (int)xP.size(), xP.data(), xN.data(), Z.data(), nw.data()));
+	g_meshSet[me] = true;
+}
+}   // namespace
+
+#define H(S, P) handle((S), (P))
+// ---- MpsBucket (src/MpsBucket.cpp:299-353) -------------------------------------------------------------------------
+void MpsBucket::updateParticlesID(MpsParticleSystem *PSystem, MpsParticle *Particles) { CALL(pmps_update_buckets(H(PSystem, Particles))); }
+
+// ---- MpsParticle (src/MpsParticle.cpp:111-130, 234-402) --------------------------------------------------------------
+void MpsParticle::addGravity(MpsParticleSystem *PSystem, MpsParticle *Particles) { CALL(pmps_add_gravity(H(PSystem, Particles))); }
+void MpsParticle::checkParticleOutDomain(MpsParticleSystem *PSystem) {
+	CALL(pmps_check_out_domain(H(PSystem, this)));
+	// calls per time step: after the prediction, after the correction, at the end (src/main.cpp:283,411,441); the call in main()
+	// before the loop is number 0.  The last one of a step is where the host's view is refreshed.
+	if (g_oodCalls > 0 && g_oodCalls % 3 == 0) { pull_scalars(); if (output_next(1)) pull_arrays(); }
+	g_oodCalls++;
+}
+
+// ---- MpsViscosity (src/MpsViscosity.cpp:20-100, 1527-1910) -----------------------------------------------------------
+void MpsViscosity::calcViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_calc_viscosity(H(PSystem, Particles))); }
+void MpsViscosity::calcWallSlipViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_viscosity(H(PSystem, Particles))); }
+void MpsViscosity::calcWallNoSlipViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_viscosity(H(PSystem, Particles))); }
+
+// ---- MpsParticleVelPos (src/MpsParticleVelPos.cpp:20-158) ------------------------------------------------------------
+void MpsParticleVelPos::predictionVelocityPosition(MpsParticleSystem *PSystem, MpsParticle *Particles) { CALL(pmps_predict(H(PSystem, Particles))); }
+void MpsParticleVelPos::correctionVelocityPosition(MpsParticleSystem *PSystem, MpsParticle *Particles) { CALL(pmps_correct(H(PSystem, Particles))); }
+void MpsParticleVelPos::updateVelocityParticlesWallDummy(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_update_wall_dummy_vel(H(PSystem, Particles))); }
+
+// ---- MpsParticleCollision (src/MpsParticleCollision.cpp:22-119) ------------------------------------------------------
+void MpsParticleCollision::checkParticleCollisions(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_collisions(H(PSystem, Particles))); }
+
+// ---- MpsPndNeigh (src/MpsPndNeigh.cpp:21-1049) ------------------------------------------------------------------------
+void MpsPndNeigh::setInitialPndNumberOfNeighNPCD(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_initial_pnd(H(PSystem, Particles))); }
+void MpsPndNeigh::calcWallNPCD(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_npcd(H(PSystem, Particles))); }
+void MpsPndNeigh::calcPndnNeighNPCD(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_pnd_neigh_npcd(H(PSystem, Particles))); }
+void MpsPndNeigh::calcPndDiffusiveTerm(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_pnd_diffusive(H(PSystem, Particles))); }
+void MpsPndNeigh::calcWallSlipPndDiffusiveTerm(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_pnd_diffusive(H(PSystem, Particles))); }
+void MpsPndNeigh::calcWallNoSlipPndDiffusiveTerm(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_pnd_diffusive(H(PSystem, Particles))); }
+void MpsPndNeigh::updatePnd(MpsParticle *Particles) { CALL(pmps_update_pnd(handle())); }
+void MpsPndNeigh::meanPndParticlesWallDummySurface(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_mean_pnd_wall_dummy_surface(H(PSystem, Particles))); }
+void MpsPndNeigh::meanPnd(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_mean_pnd(H(PSystem, Particles))); }
+void MpsPndNeigh::meanWallPnd(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_mean_wall_pnd(H(PSystem, Particles))); }
+void MpsPndNeigh::meanNeighFluidPnd(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_mean_neigh_fluid_pnd(H(PSystem, Particles))); }
+
+// ---- MpsBoundaryCondition (src/MpsBoundaryCondition.cpp:66-399) --------------------------------------------------------
+void MpsBoundaryCondition::updateParticleBC(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_update_bc(H(PSystem, Particles))); }
+
+// ---- MpsVectorMatrix (src/MpsVectorMatrix.cpp:20-93) ---------------------------------------------------------------------
+void MpsVectorMatrix::correctionMatrix(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_correction_matrix(H(PSystem, Particles))); }
+
+// ---- MpsPressure (src/MpsPressure.cpp:31-57, 792-846, 1217-1611) -----------------------------------------------------------
+void MpsPressure::calcPress(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) {
+	CALL(pmps_calc_press(H(PSystem, Particles)));
+	if (PSystem->mpsType == calcPressType::IMPLICIT_PND || PSystem->mpsType == calcPressType::IMPLICIT_PND_DIVU) {
+		PmpsScalars s; CALL(pmps_get_scalars(g_h, &s)); solverIter = s.solverIter; solverError = s.solverError;
+	}
+	if (g_oodCalls == 1) { pull_scalars(); pull_arrays(); }   // end of the 0-th step (src/main.cpp:176): iteration 0 writes output
+}
+void MpsPressure::extrapolatePressParticlesWallDummy(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_extrapolate_press(H(PSystem, Particles))); }
+void MpsPressure::calcPressGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_press_gradient(H(PSystem, Particles))); }
+void MpsPressure::calcWallPressGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_press_gradient(H(PSystem, Particles))); }
+
+// ---- MpsShifting (src/MpsShifting.cpp:432-691) -------------------------------------------------------------------------------
+void MpsShifting::calcConcAndConcGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_shifting(H(PSystem, Particles))); }
+void MpsShifting::calcWallConcAndConcGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_shifting(H(PSystem, Particles))); }
+
+// ---- PolygonMesh (src/PolygonMesh.cpp:585-795) ---------------------------------------------------------------------------------
+// main.cpp calls closestPointPNDBoundaryAABB once per mesh and then updateParticlesNearPolygonMesh on mesh 0 (src/main.cpp:293-305,
+// 529-545); pmps_wall_closest_point does all of it in one pass, so the per-mesh call only makes sure the device has the mesh (again
+// every step for the forced mesh, whose vertices the host moves: src/main.cpp:405) and the last call of the group runs the pass.
+void PolygonMesh::closestPointPNDBoundaryAABB(double reS2, double reL2, int nP, int wijType, int *Typ, int fld, int msh_id, int sta_id,
+	int fem_id, int frw_id, const double *Pos, double *wallPos, double *mirrorPos, double *riw2, int *elementID, int *meshID, double *NormalWall) {
+	if (msh_id < 0 || msh_id > 2) { fprintf(stderr, "libpmps: mesh id %d\n", msh_id); exit(10); }
+	if (!g_meshSet[msh_id] || msh_id == frw_id) send_mesh(msh_id, NV, NF, NNormals, xDataPND, xDataNeigh, Zij, nNeighWall);
+}
+void PolygonMesh::updateParticlesNearPolygonMesh(double reS2, double reL2, int nP, int wijType, int *Typ, int fld, const double *riw2,
+	double *niw, int *numNeighw, std::vector<int>& meshParticlesNeighbors, bool *Nw) {
+	CALL(pmps_wall_closest_point(handle()));
+}
