@@ -167,7 +167,8 @@ int pmps_step(pmps_t* h, int nsteps);            /* nsteps x the loop body of sr
  * velMax (src/MpsParticleVelPos.cpp:91), the displacement since the bucket rebuild and the out-of-domain test
  * (src/MpsParticle.cpp:234-402) count owned particles only; pmps_slab_collect / pmps_slab_apply let the caller
  * reduce them over the ranks so that every rank takes the same rebuild decision and uses the same velMax. */
-enum { PMPS_HF_POS = 1, PMPS_HF_VEL = 2, PMPS_HF_PRESS = 4, PMPS_HF_PNDI = 8, PMPS_HF_CONC = 16, PMPS_HF_PNDKI = 32 };
+enum { PMPS_HF_POS = 1, PMPS_HF_VEL = 2, PMPS_HF_PRESS = 4, PMPS_HF_PNDI = 8, PMPS_HF_CONC = 16, PMPS_HF_PNDKI = 32,
+       PMPS_HF_BC = 64, PMPS_HF_PPE_X = 128 /* pressurePPE: the CG iterate / warm start */, PMPS_HF_PPE_P = 256 /* the CG search direction */ };
 int pmps_halo_planes(unsigned fields);           /* doubles per particle of a packed buffer (pos carries {x,y,z,type bits}) */
 int pmps_slab_begin(pmps_t* h, int nOwned);      /* after each (re-)upload of the rank's particle table */
 int pmps_halo_pack(pmps_t* h, unsigned fields, const int32_t* d_hostIndex, int n, double* d_out);   /* device pointers; plane-major */
@@ -176,7 +177,14 @@ int pmps_step_phases(void);                      /* number of phases of the fuse
 int pmps_step_phase(pmps_t* h, int phase, unsigned* haloFieldsAfter);   /* one phase of the loop body of src/main.cpp:256-460 */
 int pmps_slab_collect(pmps_t* h, double* d_out3);        /* device: {max displacement^2 since rebuild, max shift^2, velMax^2} of this rank */
 int pmps_slab_apply(pmps_t* h, const double* d_in3);     /* the same three after the MAX all-reduce: ends the step */
-int pmps_slab_wants_rebuild(pmps_t* h);                  /* 1: re-partition (migrate + new halo) and re-upload before the next step */
+int pmps_slab_wants_rebuild(pmps_t* h);
+/* Incompressible scheme on slabs: the conjugate-gradient solve (src/MpsPressure.cpp:424-445; Eigen ConjugateGradient.h:27-91) sums
+ * its dot products over OWNED rows and calls back into the host at the two points where ranks must talk: `sum(user, n)` must
+ * SUM-all-reduce, in place, the first n doubles of the device workspace given here; `refresh(user, fields)` must refresh the halo
+ * copies of `fields` (PMPS_HF_PPE_P before every matrix-vector product).  Both run on pmps_stream(h). */
+typedef void (*pmps_sum_fn)(void* user, int n);
+typedef void (*pmps_refresh_fn)(void* user, unsigned fields);
+int pmps_slab_set_hooks(pmps_t* h, double* d_workspace8, pmps_sum_fn sum, pmps_refresh_fn refresh, void* user);                  /* 1: re-partition (migrate + new halo) and re-upload before the next step */
 
 /* ---- debug / parity hooks (tests only) ---------------------------------------------------------------------- */
 /* bucket id of every host-order particle as the reference computes it at rebuild time, and the members of every

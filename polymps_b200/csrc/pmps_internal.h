@@ -38,6 +38,7 @@ struct DevView {
 	uint16_t* tlist; uint16_t* tlistCnt;   // tile-local Verlet candidates: tlCap entries per slot in chunks of 64 (tv_list_pos), entries used
 	uint16_t* hlist; uint16_t* hcnt;       // hit list: the candidates within reach at the positions of the current epoch (same layout)
 	uint8_t* particleNearWall;
+	double* ppeP;                        // CG search direction (pmps_ppe.cu), here so that the halo pack / unpack kernels reach it
 	double* scratch1;                    // per-slot scratch (Pmin of the gradient passes); not a reference field
 #define X(n) int32_t* n;
 	PMPS_I32_FIELDS(X)
@@ -126,6 +127,7 @@ struct pmps_handle {
 	int nTilesAll = 0, smCount = 148, walkSeq = 0; bool tileWallValid = false;
 	double dispNow = 0.0, dispInc = 0.0, dispIncPrev = 0.0; int stepsSinceBuild = 0; bool needRebuild = true;   // displacement since the list build (step_begin's rebuild decision)
 	double lastShift = 0.0;              // largest shift of the last step's shifting passes
+	double* slabWork = nullptr; pmps_sum_fn slabSum = nullptr; pmps_refresh_fn slabRefresh = nullptr; void* slabUser = nullptr;   // pmps_slab_set_hooks
 	bool slab = false;                   // slab mode: rebuilds and the step-end scalars are decided by the caller from GLOBAL maxima (pmps_slab.cu)
 	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
 	bool hitForce = false;               // positions were replaced from outside (upload): the next check rebuilds the hit list

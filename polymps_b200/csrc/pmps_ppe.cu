@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_residual0(const __grid_constant__
 	double b2 = 0.0, r2 = 0.0;
 	if (i < S.n) {
 		const double b = S.sourceTerm[i]; const double r = b - ell_row_dot(S, M, i, S.pressurePPE);
-		M.r[i] = r; b2 = b * b; r2 = r * r;
+		M.r[i] = r; if (owned_slot(S, i)) { b2 = b * b; r2 = r * r; }
 	}
 	const double sb = block_sum<PPE_T>(b2, sh); const double sr = block_sum<PPE_T>(r2, sh);
 	if (threadIdx.x == 0) { M.partial[blockIdx.x] = sb; M.partial[nBlocks + blockIdx.x] = sr; }
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_init_p(const __grid_constant__ De
 	__shared__ double sh[PPE_T / 32];
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	double v = 0.0;
-	if (i < S.n) { const double d = M.diag[i]; const double r = M.r[i]; const double p = (d != 0.0 ? 1.0 / d : 1.0) * r; M.p[i] = p; v = r * p; }
+	if (i < S.n) { const double d = M.diag[i]; const double r = M.r[i]; const double p = (d != 0.0 ? 1.0 / d : 1.0) * r; M.p[i] = p; if (owned_slot(S, i)) v = r * p; }
 	const double s = block_sum<PPE_T>(v, sh);
 	if (threadIdx.x == 0) M.partial[blockIdx.x] = s;
 }
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_spmv(const __grid_constant__ DevV
 	__shared__ double sh[PPE_T / 32];
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	double v = 0.0;
-	if (i < S.n) { const double t = ell_row_dot(S, M, i, M.p); M.t[i] = t; v = M.p[i] * t; }
+	if (i < S.n) { const double t = ell_row_dot(S, M, i, M.p); M.t[i] = t; if (owned_slot(S, i)) v = M.p[i] * t; }
 	const double s = block_sum<PPE_T>(v, sh);
 	if (threadIdx.x == 0) M.partial[blockIdx.x] = s;
 }
@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_update_xr(const __grid_constant__
 		S.pressurePPE[i] += alpha * M.p[i];
 		const double r = M.r[i] - alpha * M.t[i]; M.r[i] = r;
 		const double d = M.diag[i]; const double z = (d != 0.0 ? 1.0 / d : 1.0) * r;
-		r2 = r * r; rz = r * z;
+		if (owned_slot(S, i)) { r2 = r * r; rz = r * z; }
 	}
 	const double s1 = block_sum<PPE_T>(r2, sh); const double s2 = block_sum<PPE_T>(rz, sh);
 	if (threadIdx.x == 0) { M.partial[blockIdx.x] = s1; M.partial[nBlocks + blockIdx.x] = s2; }
@@ -150,14 +150,18 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_update_p(const __grid_constant__ 
 	const double beta = M.scal[6]; const double d = M.diag[i];
 	M.p[i] = (d != 0.0 ? 1.0 / d : 1.0) * M.r[i] + beta * M.p[i];
 }
-// second stage of the dot products + the scalar recurrences of Eigen's CG (ConjugateGradient.h:50-89)
-// mode 0: after residual0 -> rhs2, res2, thr ; 1: after init_p -> absNew ; 2: after spmv -> pt, alpha ; 3: after update_xr -> res2, beta
-__global__ void __launch_bounds__(RED_T) k_ppe_reduce(const __grid_constant__ PpeView M, int nBlocks, int mode, double* hostMirror) {
+// second stage of the dot products: block partials -> sums[0..1] (device; on a slab rank the host then SUM-all-reduces them in place)
+// mode 0: after residual0 (|b|^2, |r|^2) ; 1: after init_p (r.z) ; 2: after spmv (p.t) ; 3: after update_xr (|r|^2, r.z)
+__global__ void __launch_bounds__(RED_T) k_ppe_reduce(const __grid_constant__ PpeView M, int nBlocks, int mode, double* sums) {
 	__shared__ double sh[RED_T / 32];
 	double a = 0.0, b = 0.0;
 	for (int k = threadIdx.x; k < nBlocks; k += RED_T) { a += M.partial[k]; if (mode == 0 || mode == 3) b += M.partial[nBlocks + k]; }
 	const double sa = block_sum<RED_T>(a, sh); const double sb = block_sum<RED_T>(b, sh);
-	if (threadIdx.x != 0) return;
+	if (threadIdx.x == 0) { sums[0] = sa; sums[1] = sb; }
+}
+// the scalar recurrences of Eigen's CG (ConjugateGradient.h:50-89) from the (global) sums
+__global__ void k_ppe_recur(const __grid_constant__ PpeView M, int mode, const double* sums, double* hostMirror) {
+	const double sa = sums[0], sb = sums[1];
 	double* s = M.scal;
 	if (mode == 0) { s[0] = sa; s[1] = sb; double thr = DBL_EPSILON * DBL_EPSILON * sa; if (thr < DBL_MIN) thr = DBL_MIN; s[7] = thr; }
 	else if (mode == 1) { s[2] = sa; }
@@ -198,10 +202,17 @@ int pmps_ppe_solve(pmps_handle* h) {
 	PpeView M; M.col = h->ppe_col; M.val = h->ppe_val; M.cnt = h->ppe_cnt; M.diag = h->ppe_diag; M.r = h->ppe_r; M.p = h->ppe_p; M.t = h->ppe_t;
 	M.partial = h->ppe_partial; M.scal = h->ppe_scal;
 	double* hm = h->ppe_host;
+	S.ppeP = h->ppe_p;
+	const bool slab = h->slab && h->slabSum;
+	double* sums = slab ? h->slabWork : M.scal + 8;
+	// one dot-product stage: partials -> sums, (slab: SUM over the ranks,) scalar recurrence
+#define REDUCE(mode, nvals) do { LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, (mode), sums); \
+		if (slab) h->slabSum(h->slabUser, (nvals)); \
+		LAUNCH(h, "ppe.recur", k_ppe_recur, 1, 1, M, (mode), sums, hm); } while (0)
 	if (K.poly) { LAUNCH(h, "ppe.assemble", k_ppe_assemble<true>, nBlocks, PPE_T, S, K, M); }
 	else { LAUNCH(h, "ppe.assemble", k_ppe_assemble<false>, nBlocks, PPE_T, S, K, M); }
 	LAUNCH(h, "ppe.residual0", k_ppe_residual0, nBlocks, PPE_T, S, M, nBlocks);
-	LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 0, hm);
+	REDUCE(0, 2);
 	CUDA_TRY(h, cudaStreamSynchronize(h->stream));
 	const double rhs2 = hm[0]; double res2 = hm[1]; const double thr = hm[2];
 	int iters = 0; double err = 0.0; int zeroX = 0;
@@ -209,13 +220,14 @@ int pmps_ppe_solve(pmps_handle* h) {
 	else {
 		if (res2 >= thr) {
 			LAUNCH(h, "ppe.init_p", k_ppe_init_p, nBlocks, PPE_T, S, M, nBlocks);
-			LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 1, hm);
+			REDUCE(1, 1);
 			const long long maxIt = 2ll * h->numParticles;
 			while (iters < maxIt) {
+				if (slab) h->slabRefresh(h->slabUser, PMPS_HF_PPE_P);   // the halo copies' p before the matrix-vector product
 				LAUNCH(h, "ppe.spmv", k_ppe_spmv, nBlocks, PPE_T, S, M, nBlocks);
-				LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 2, hm);
+				REDUCE(2, 1);
 				LAUNCH(h, "ppe.update_xr", k_ppe_update_xr, nBlocks, PPE_T, S, M, nBlocks);
-				LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 3, hm);
+				REDUCE(3, 2);
 				CUDA_TRY(h, cudaStreamSynchronize(h->stream));
 				res2 = hm[1];
 				if (res2 < thr || !(res2 == res2)) break;
@@ -225,6 +237,7 @@ int pmps_ppe_solve(pmps_handle* h) {
 		}
 		err = sqrt(res2 / rhs2);
 	}
+#undef REDUCE
 	LAUNCH(h, "ppe.finish", k_ppe_finish, cdiv(n, 256), 256, S, K, zeroX);
 	CUDA_TRY(h, cudaGetLastError());
 	h->solverIter = iters; h->solverError = err;

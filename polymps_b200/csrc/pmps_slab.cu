@@ -11,7 +11,7 @@
 
 static __host__ __device__ inline int halo_planes(unsigned f) {
 	return ((f & PMPS_HF_POS) ? 4 : 0) + ((f & PMPS_HF_VEL) ? 3 : 0) + ((f & PMPS_HF_PRESS) ? 1 : 0) + ((f & PMPS_HF_PNDI) ? 1 : 0)
-	     + ((f & PMPS_HF_CONC) ? 1 : 0) + ((f & PMPS_HF_PNDKI) ? 1 : 0);
+	     + ((f & PMPS_HF_CONC) ? 1 : 0) + ((f & PMPS_HF_PNDKI) ? 1 : 0) + ((f & PMPS_HF_BC) ? 1 : 0) + ((f & PMPS_HF_PPE_X) ? 1 : 0) + ((f & PMPS_HF_PPE_P) ? 1 : 0);
 }
 extern "C" int pmps_halo_planes(unsigned fields) { return halo_planes(fields); }
 
@@ -26,6 +26,9 @@ __global__ void k_halo_pack(const __grid_constant__ DevView S, unsigned f, const
 	if (f & PMPS_HF_PNDI) { o[0] = S.pndi[s]; o += st; }
 	if (f & PMPS_HF_CONC) { o[0] = S.concentration[s]; o += st; }
 	if (f & PMPS_HF_PNDKI) { o[0] = S.pndki[s]; o += st; }
+	if (f & PMPS_HF_BC) { o[0] = (double)S.particleBC[s]; o += st; }
+	if (f & PMPS_HF_PPE_X) { o[0] = S.pressurePPE[s]; o += st; }
+	if (f & PMPS_HF_PPE_P) { o[0] = S.ppeP[s]; o += st; }
 }
 __global__ void k_halo_unpack(const __grid_constant__ DevView S, const __grid_constant__ KParams K, unsigned f, int first, int n, const double* __restrict__ in) {
 	const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -43,6 +46,9 @@ __global__ void k_halo_unpack(const __grid_constant__ DevView S, const __grid_co
 	if (f & PMPS_HF_PNDI) { S.pndi[s] = o[0]; o += st; }
 	if (f & PMPS_HF_CONC) { S.concentration[s] = o[0]; o += st; }
 	if (f & PMPS_HF_PNDKI) { S.pndki[s] = o[0]; o += st; }
+	if (f & PMPS_HF_BC) { S.particleBC[s] = (int)o[0]; o += st; }
+	if (f & PMPS_HF_PPE_X) { S.pressurePPE[s] = o[0]; o += st; }
+	if (f & PMPS_HF_PPE_P) { S.ppeP[s] = o[0]; o += st; }
 }
 
 extern "C" int pmps_slab_begin(pmps_t* h, int nOwned) {
@@ -50,14 +56,20 @@ extern "C" int pmps_slab_begin(pmps_t* h, int nOwned) {
 	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_slab_begin: upload the particle table first");
 	if (nOwned < 0 || nOwned > h->numParticles) return pmps_fail(h, PMPS_E_ARG, "pmps_slab_begin: %d owned of %d particles", nOwned, h->numParticles);
 	const PmpsParams& P = h->K.p;
-	if (P.mpsType != 0 && P.mpsType != 1) return pmps_fail(h, PMPS_E_UNSUPPORTED, "slab mode runs the explicit / weakly-compressible schemes; the pressure Poisson solve is not sharded yet");
+	if ((P.mpsType == 2 || P.mpsType == 3) && !h->slabSum) return pmps_fail(h, PMPS_E_STATE, "pmps_slab_begin: the incompressible scheme needs pmps_slab_set_hooks first (all-reduce / halo refresh inside the Poisson solve)");
 	h->V.nOwn = nOwned; h->slab = true;
+	return PMPS_OK;
+}
+extern "C" int pmps_slab_set_hooks(pmps_t* h, double* d_workspace8, pmps_sum_fn sum, pmps_refresh_fn refresh, void* user) {
+	if (!h || !d_workspace8 || !sum || !refresh) return PMPS_E_ARG;
+	h->slabWork = d_workspace8; h->slabSum = sum; h->slabRefresh = refresh; h->slabUser = user;
 	return PMPS_OK;
 }
 extern "C" int pmps_halo_pack(pmps_t* h, unsigned fields, const int32_t* d_hostIndex, int n, double* d_out) {
 	if (!h || n < 0 || (n > 0 && (!d_hostIndex || !d_out))) return PMPS_E_ARG;
 	if (!h->haveList) return pmps_fail(h, PMPS_E_STATE, "pmps_halo_pack: no bucket order yet");
 	if (n == 0 || fields == 0) return PMPS_OK;
+	if ((fields & PMPS_HF_PPE_P) && !h->V.ppeP) return pmps_fail(h, PMPS_E_STATE, "pmps_halo_pack: no Poisson solve in progress");
 	cudaSetDevice(h->device);
 	LAUNCH(h, "halo.pack", k_halo_pack, cdiv(n, 256), 256, h->V, fields, d_hostIndex, n, d_out);
 	CUDA_TRY(h, cudaGetLastError());

@@ -35,18 +35,18 @@ import torch.distributed as dist
 
 from .state import F64, I32, U8, VEC, PmpsHostArrays
 
-HF_POS, HF_VEL, HF_PRESS, HF_PNDI, HF_CONC, HF_PNDKI = 1, 2, 4, 8, 16, 32
-HF_ALL = 63
+HF_POS, HF_VEL, HF_PRESS, HF_PNDI, HF_CONC, HF_PNDKI, HF_BC, HF_PPE_X, HF_PPE_P = 1, 2, 4, 8, 16, 32, 64, 128, 256
+MAX_PLANES = 14
 
 
 def halo_planes(mask: int) -> int:
-    return (4 if mask & HF_POS else 0) + (3 if mask & HF_VEL else 0) + sum(1 for b in (HF_PRESS, HF_PNDI, HF_CONC, HF_PNDKI) if mask & b)
+    return (4 if mask & HF_POS else 0) + (3 if mask & HF_VEL else 0) + sum(1 for b in (HF_PRESS, HF_PNDI, HF_CONC, HF_PNDKI, HF_BC, HF_PPE_X, HF_PPE_P) if mask & b)
 
 
 # State that lives from one step into the next (everything else is recomputed inside a step before it is read): what a
 # migrating particle takes along and what a new halo copy is created with.
 TABLE_FIELDS = ["particleType", "PTYPE", "particleBC", "numNeigh", "nearMeshType", "numNeighWallContribution", "particleNearWall",
-                "press", "pndi", "pndki", "pndski", "pndSmall", "RHO", "MEU", "distParticleWall2", "pndWallContribution", "concentration",
+                "press", "pndi", "pndki", "pndski", "pndSmall", "RHO", "MEU", "distParticleWall2", "pndWallContribution", "concentration", "pressurePPE",
                 "pos", "vel", "acc", "mirrorParticlePos", "particleAtWallPos", "polygonNormal"]
 
 
@@ -243,7 +243,7 @@ class SlabDomain:
             if self._peer(side) is None:
                 continue
             ns, nr = int(self.send_idx[side].numel()), self.halo_n[side]
-            sb = self._buffer("s" + side, 11 * ns)[:P * ns]; rb = self._buffer("r" + side, 11 * nr)[:P * nr]
+            sb = self._buffer("s" + side, MAX_PLANES * ns)[:P * ns]; rb = self._buffer("r" + side, MAX_PLANES * nr)[:P * nr]
             if ns:
                 b.halo_pack(mask, self.send_idx[side], sb)
             send[side] = sb; recv[side] = rb
@@ -260,6 +260,14 @@ class SlabDomain:
             t = torch.empty(max(n, 1), dtype=torch.float64, device=self.b.device); self._buf[key] = t
         return t
 
+    def all_sum(self, t: torch.Tensor) -> torch.Tensor:
+        if self.world > 1:
+            if self.stage_host and t.device.type == "cuda":
+                c = t.cpu(); dist.all_reduce(c, op=dist.ReduceOp.SUM, group=self.group); t.copy_(c)
+            else:
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return t
+
     def all_max(self, t: torch.Tensor) -> torch.Tensor:
         if self.world > 1:
             if self.stage_host and t.device.type == "cuda":
@@ -270,6 +278,10 @@ class SlabDomain:
 
 
 # ------------------------------------------------------------------------------------------------ libpmps binding
+SUM_FN = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_int)
+REFRESH_FN = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_uint)
+
+
 class EngineBackend(TableBackend):
     """The rank's table lives in a libpmps handle; transfers are device-to-device on the engine's stream."""
 
@@ -284,6 +296,7 @@ class EngineBackend(TableBackend):
         L.pmps_slab_collect.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.pmps_slab_apply.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.pmps_slab_wants_rebuild.argtypes = [ctypes.c_void_p]
+        L.pmps_slab_set_hooks.argtypes = [ctypes.c_void_p, ctypes.c_void_p, SUM_FN, REFRESH_FN, ctypes.c_void_p]
         ps = eng.ps
         self._ghost_pos = [ps.domainMaxX - ps.partDist, ps.domainMaxY - ps.partDist, 0.0 if int(ps.dim) == 2 else ps.domainMaxZ - ps.partDist]
         self._ghost = {"particleType": float(ps.ghost), "particleBC": float(ps.other), "distParticleWall2": 10e8 * ps.partDist}
@@ -340,6 +353,15 @@ class SlabEngine:
         self.dom = SlabDomain(self.backend, rank, world, cuts_x[rank], cuts_x[rank + 1], ps.bucketSide * (1.0 + 1e-9), group=group)
         self.scal = torch.zeros(3, dtype=torch.float64, device=self.dev)
         self.nph = int(self.eng.lib.pmps_step_phases())
+        # the Poisson solve of the incompressible scheme calls back for its all-reduces and the halo refresh of the search direction
+        self.work = torch.zeros(8, dtype=torch.float64, device=self.dev)
+        def _sum(user, n):
+            self.dom.all_sum(self.work[:n])
+
+        def _refresh(user, fields):
+            self.dom.refresh(int(fields))
+        self._sum_cb = SUM_FN(_sum); self._refresh_cb = REFRESH_FN(_refresh)
+        self.eng._chk(self.eng.lib.pmps_slab_set_hooks(self.eng.h, self.work.data_ptr(), self._sum_cb, self._refresh_cb, None))
         with torch.cuda.stream(self.stream):
             T = {}
             for f in TABLE_FIELDS:
@@ -373,7 +395,7 @@ class SlabEngine:
             self._stage("initial_pnd", m)
             if poly:
                 self._stage("mean_wall_pnd", m)
-            self._stage("mean_pnd", m); self._stage("mean_neigh_fluid_pnd", m); self._stage("update_bc"); self._stage("calc_press", m)
+            self._stage("mean_pnd", m); self._stage("mean_neigh_fluid_pnd", m); self._stage("update_bc", HF_BC); self._stage("calc_press", m | HF_PPE_X)
 
     def step(self, n: int = 1):
         L = self.eng.lib; h = self.eng.h
@@ -410,6 +432,6 @@ class SlabEngine:
         """Drops every tensor that lives on the engine's stream BEFORE the handle (and with it the stream) is destroyed."""
         import gc
         torch.cuda.synchronize(self.dev)
-        self.dom._buf.clear(); self.dom.gid = None; self.dom.send_idx = {}; self.scal = None
+        self.dom._buf.clear(); self.dom.gid = None; self.dom.send_idx = {}; self.scal = None; self.work = None
         gc.collect(); torch.cuda.empty_cache()
         self.eng.close()

@@ -27,7 +27,7 @@ from polymps_b200.mesh import PolygonMesh  # noqa: E402
 from polymps_b200.params import ParticleSystem  # noqa: E402
 from polymps_b200.slab import SlabEngine, choose_cuts  # noqa: E402
 
-FIELDS = ["pos", "vel", "press", "pndi", "particleBC", "numNeigh", "pndSmall", "concentration", "particleType"]
+FIELDS = ["pos", "vel", "press", "pndi", "particleBC", "numNeigh", "pndSmall", "concentration", "particleType", "pressurePPE"]
 
 
 def main():
@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--nx", type=int, default=40); ap.add_argument("--ny", type=int, default=10); ap.add_argument("--nz", type=int, default=14)
     ap.add_argument("--drift", type=float, default=1.5)
     ap.add_argument("--rtol", type=float, default=1e-9)
+    ap.add_argument("--inc", action="store_true", help="incompressible scheme: PPE assembly + CG sharded over the slabs")
     a = ap.parse_args()
     rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); local = 0 if a.one_gpu else int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -45,7 +46,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     else:
         dist.init_process_group("gloo")
-    case = cases.dam3d(a.nx, a.ny, a.nz, jitter=0.05, name="slabparity")
+    case = cases.dam3d(a.nx, a.ny, a.nz, jitter=0.05, name="slabparity", incompressible=a.inc)
     case.vel[:, 0] = a.drift
     ps = ParticleSystem.from_json(case.options).set_parameters(); ps.allocate_buckets(case.pos)
     meshes = [PolygonMesh.from_triangles(case.tris).init_wall_tables(int(ps.dim), ps.weightType, ps.partDist, ps.reL, ps.reS)]
@@ -58,7 +59,7 @@ def main():
     se.init_step0(); se.step(a.steps)
     got = se.download_owned(FIELDS)
     sc = se.scalars()
-    stats = dict(se.dom.stats); stats.update(n_own=se.n_own, velMax=sc.velMax, launches=se.eng.launch_count())
+    stats = dict(se.dom.stats); stats.update(n_own=se.n_own, velMax=sc.velMax, launches=se.eng.launch_count(), solverIter=sc.solverIter)
     allgot = [None] * world; allstats = [None] * world
     dist.all_gather_object(allgot, got); dist.all_gather_object(allstats, stats)
     ok = True
@@ -79,6 +80,9 @@ def main():
                 err = float(np.abs(v - w).max()) / scale
                 print("  %-16s max |diff| / max |ref| = %.3e" % (f, err)); ok &= err <= a.rtol
         dv = abs(allstats[0]["velMax"] - s1.velMax) / max(s1.velMax, 1e-300)
+        if a.inc:
+            print("  CG iterations of the last step: slabs %d, single engine %d" % (allstats[0]["solverIter"], s1.solverIter))
+            ok &= abs(allstats[0]["solverIter"] - s1.solverIter) <= 3 and s1.solverIter > 3
         print("  velMax %.12g vs %.12g (rel %.2e); migrants %d, repartitions %d" % (allstats[0]["velMax"], s1.velMax, dv, sum(s["migrants_out"] for s in allstats), allstats[0]["repartitions"]))
         ok &= dv <= a.rtol
         if world > 1:
