@@ -7,6 +7,8 @@
 // after every phase of the step (pmps_step_phase) the caller packs the fields that phase produced for the particles its
 // neighbours hold copies of (pmps_halo_pack), exchanges the buffers (NCCL send/recv, polymps_b200/slab.py) and unpacks
 // what it received onto its own copies (pmps_halo_unpack).  Buffers are plane-major: plane p of particle t at [p*n + t].
+// The Poisson solve of the incompressible scheme (pmps_ppe.cu) reaches the host through pmps_slab_set_hooks for its all-reduces
+// and the refresh of the search direction.
 #include "pmps_device.cuh"
 
 static __host__ __device__ inline int halo_planes(unsigned f) {

@@ -18,8 +18,10 @@ bucket grid (src/MpsBucket.cpp:20-67), so bucket ids stay globally consistent:
 * velMax (src/MpsParticleVelPos.cpp:91), the displacement since the rebuild and the largest shift are MAX-all-reduced
   once per step (three doubles, in place in device memory).
 
-There is no data-path collective besides those: the path shards (`"scaling": "weak"` in bench.py).  The incompressible
-scheme's PPE solve is not sharded yet (`pmps_slab_begin` refuses it).
+There is no data-path collective besides those in the explicit / weakly-compressible schemes: the path shards (`"scaling":
+"weak"` in bench.py).  The incompressible scheme adds the exchanges of its Krylov solve: the conjugate-gradient dot products
+are SUM-all-reduced and the halo copies of the search direction refreshed before every matrix-vector product; libpmps calls
+back for both (`pmps_slab_set_hooks`).
 
 `SlabDomain` holds the partition / exchange logic over an abstract particle-table backend, so the CPU tests run the very
 same code over gloo with a host backend (tests/test_slab_host.py); `SlabEngine` binds it to libpmps.
