@@ -36,6 +36,8 @@ ALGO_BYTES = {
     "F3.pnd+wall": 160, "mean_pnd_surface": 72, "E4.bc+eos": 48, "F5.gradient+wall+correct": 313, "F5.gradient+correct": 313,
     "shift.concentration": 64, "shift.gradient": 113, "shift.wall_gradient": 0, "list.build": 308,
     "F5.gradient": 165, "W5.wall+correct": 148,
+    # incompressible scheme (--scheme inc; SURVEY.md 8d "Same, INC"): ELL row of A^T 40 x 12 B + count/diag + x, y
+    "ppe.spmv": 500, "ppe.assemble": 580, "ppe.update_xr": 56, "ppe.update_p": 32, "ppe.residual0": 516,
     # unfused stage kernels (PMPS_STAGED=1 / stage API)
     "viscosity": 116, "collision": 104, "pnd_neigh_npcd": 160, "pnd_diffusive": 124, "press_gradient": 96, "wall.closest_point": 121,
     "predict": 172, "correct": 148, "update_bc": 48,
@@ -97,9 +99,9 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def block_case(k, jitter=0.0):
+def block_case(k, jitter=0.0, inc=False):
     from polymps_b200 import cases
-    return cases.dam3d_block(k, jitter=jitter, name="block%d" % k)
+    return cases.dam3d_block(k, jitter=jitter, name="block%d" % k, incompressible=inc)
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm
@@ -300,7 +302,7 @@ def main_gpu(args):
         return main_gpu_slab(args, rank, world, local)
     from polymps_b200.engine import make_engine
 
-    case = block_case(args.k)
+    case = block_case(args.k, inc=args.scheme == "inc")
     ps, meshes, st, eng = make_engine(case, device=local)
     n = st.numParticles
     stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
@@ -353,9 +355,10 @@ def main_gpu(args):
            "h2d_bytes_per_step": field_bytes(st, E2E_UP) * world, "d2h_bytes_per_step": field_bytes(st, E2E_DOWN) * world,
            "api": "pmps_upload + pmps_step(1) + pmps_download per step, host arrays pinned in place"}
 
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+    line = {"metric": METRIC if args.scheme == "wc" else "particle-steps/sec (3D INC dam break: PPE assembly + Jacobi-CG)", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "synthetic 3D WC dam-break block %dx%dx%d = %d particles per GPU, STL polygon tank (10 triangles), InputDamWC option set" % (2 * args.k, args.k, args.k, n),
+            "config": {"workload": "synthetic 3D %s dam-break block %dx%dx%d = %d particles per GPU, STL polygon tank (10 triangles), %s option set" % (args.scheme.upper(), 2 * args.k, args.k, args.k, n, "InputDamWC" if args.scheme == "wc" else "InputDamINC"),
+                       "cg_iterations_last_step": sc2.solverIter if args.scheme == "inc" else None,
                        "particles_per_gpu": n, "parallelism": "1 GPU",
                        "l2": "state per GPU (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (n * 1500 / 1e9),
                        "max_displacement_over_lo": sc2.maxDisplacement / ps.partDist, "max_bucket_count": sc2.maxBucketCount},
@@ -376,6 +379,7 @@ def main():
     ap.add_argument("--steps", type=int, default=40, help="timed steps (40: several bucket rebuilds / re-partitions fall inside the timed region)")
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scheme", default="wc", choices=["wc", "inc"], help="wc = the BASELINE.json metric (default); inc = the incompressible configuration (#3), single GPU, reported under profiles/")
     ap.add_argument("--k", type=int, default=171, help="block edge: 2k x k x k particles per GPU (171 -> 10.0M)")
     ap.add_argument("--ref-k", type=int, default=50, help="block edge of the CPU sample for --impl reference")
     ap.add_argument("--cpu-k", type=int, default=40, help="block edge of the cpu_baseline sample")
