@@ -255,7 +255,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	rc |= dalloc(h, &h->scanBlock, h->nScanBlocks);
 	{	// work items of the tile-Verlet walker: at most one per non-empty cell
 		const size_t items = (size_t)(S.nC < n0 ? S.nC : n0) + 1;
-		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.itemTab, items * (size_t)K.tabStride); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
+		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.itemMinD2, items); rc |= dalloc(h, &S.itemTab, items * (size_t)K.tabStride); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
 		int sm = 148; cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device); h->smCount = sm;
 	}
 	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 2); rc |= dalloc(h, &S.hitMove, 4); rc |= dalloc(h, &S.hitFlag, 2); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
@@ -294,6 +294,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	if (const char* e = getenv("PMPS_HIT_DELTA")) { const double v = atof(e); if (v > 0.0 && v < 0.2) K.hitDelta = v * lo; }
 	if (maxRe + 2.0 * K.hitDelta > rl - 1e-3 * lo) K.hitDelta = fmax(0.5 * (rl - 1e-3 * lo - maxRe), 0.0);   // never beyond the Verlet radius
 	{ const double r = (maxRe + 2.0 * K.hitDelta) * (1.0 + 1e-5); K.hitR2 = (float)(r * r); }
+	{ const double r = (sqrt(P.distCollisionLimit2) + 2.0 * K.hitDelta) * (1.0 + 1e-5) + 8.0 * 1.2e-7 * 4.0 * rl; K.closeR2 = (float)(r * r); }
 	// |x_j - mirror_i| >= 2 dist(i, wall) - displacement - |x_j - x_i| > re whenever dist > re + displacement/2: margin = the full guard
 	{ const double far = maxRe * (1.0 + 1e-6) + (guard > 0 ? guard : 0.0) + 1e-6 * lo; K.mirrorFar2 = far * far; }
 	k_iota<<<cdiv(n0, 256), 256, 0, h->stream>>>(S.hostIdx, S.slotOfHost, n0);

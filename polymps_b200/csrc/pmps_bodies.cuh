@@ -118,6 +118,7 @@ struct BWallViscosity {
 // ------------------------------------------------------------------------------------------------ collisions (PC)
 // MpsParticleCollision::checkParticleCollisions, src/MpsParticleCollision.cpp:22-119 (first loop: dvel)
 struct BCollision {
+	typedef void close_pairs_tag;
 	struct Ctx { double vx, vy, vz, mi, dx, dy, dz; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		if (s.type != K.p.fluid) return false;

@@ -206,12 +206,16 @@ template <class B, class = void> struct CopiesVel { static constexpr bool value 
 template <class B> struct CopiesVel<B, typename B::copy_vel_tag> { static constexpr bool value = true; };
 template <class B, class = void> struct NoPairs { static constexpr bool value = false; };
 template <class B> struct NoPairs<B, typename B::no_pair_tag> { static constexpr bool value = true; };   // tail bodies: begin/end only
+// close_pairs_tag: the body's pair term needs d < distCollisionLimit only; its launch skips the work items whose closest pair (tracked
+// when the hit list was made, k_tv_hits / k_tv_build) cannot have come that close since
+template <class B, class = void> struct ClosePairs { static constexpr bool value = false; };
+template <class B> struct ClosePairs<B, typename B::close_pairs_tag> { static constexpr bool value = true; };
 template <class B, class = void> struct NeedsWall { static constexpr bool value = false; };
 template <class B> struct NeedsWall<B, typename B::wall_frame_tag> { static constexpr bool value = true; };
 
 template <class... Bodies> struct Fused;
 template <> struct Fused<> {
-	static constexpr bool kCopyPos = false, kCopyVel = false, kWall = false;
+	static constexpr bool kCopyPos = false, kCopyVel = false, kWall = false, kCloseOnly = true;
 	struct Ctx {};
 	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams&, const Self&) { return false; }
 	__device__ __forceinline__ static bool need_pairs(const Ctx&) { return false; }
@@ -223,6 +227,7 @@ template <class B, class... Rest> struct Fused<B, Rest...> {
 	static constexpr bool kCopyPos = CopiesPos<B>::value || Fused<Rest...>::kCopyPos;
 	static constexpr bool kCopyVel = CopiesVel<B>::value || Fused<Rest...>::kCopyVel;
 	static constexpr bool kWall = NeedsWall<B>::value || Fused<Rest...>::kWall;
+	static constexpr bool kCloseOnly = (ClosePairs<B>::value || NoPairs<B>::value) && Fused<Rest...>::kCloseOnly;   // every pair term is a close-pair term
 	struct Ctx { typename B::Ctx c; bool on; typename Fused<Rest...>::Ctx r; };
 	__device__ __forceinline__ static bool begin(Ctx& x, const DevView& S, const KParams& K, const Self& s) {
 		x.on = B::begin(x.c, S, K, s);

@@ -70,6 +70,7 @@ struct DevView {
 	int32_t listValid;                   // the Verlet list of the current bucket order has been built
 	int32_t* tileList; int32_t* nTiles;  // work items of the last rebuild: tile id (whole tile) or ~cell (one bucket of a tile whose halo
 	                                     // does not fit the staging area); count on device
+	float* itemMinD2;                    // per work item: smallest squared pair distance (float positions) when the hit list was made
 	int32_t* itemTab;                    // per work item: precomputed halo table (K.tabStride ints, pmps_tv.cuh)
 	int32_t* tileCursor;                 // work-stealing cursors, one per walk launch of a step
 	uint8_t* tileWall;                   // per tile: some particle of the tile is near a polygon wall (set by the wall pass)
@@ -87,6 +88,7 @@ struct KParams {
 	double velMax;       // velMax of the previous correction (src/MpsPressure.cpp:1585)
 	float rl2;           // (list radius)^2 incl. float margin
 	float guard2;        // (allowed displacement)^2
+	float closeR2;       // (sqrt(distCollisionLimit2) + 2 hitDelta)^2 with the float margin: work items whose closest pair was farther skip the collision walk
 	float hitR2;         // (reach of the hit lists)^2 = (max(reS, reL) + 2 hitDelta)^2 with the float margin
 	double hitDelta;     // a hit list stays valid while no particle moved farther than this since it was made (covers the shifting)
 	int32_t poly;        // wallType == polygon

@@ -288,6 +288,7 @@ __device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, con
 static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
+	__shared__ unsigned sMinBits;   // smallest squared pair distance of the item (bits of a positive float)
 	constexpr int NGB = TV_T / TV_BG;   // particles per round
 	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
 	float4* const fpos = T.fpos;
@@ -303,6 +304,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const TvBox b = tv_box(K, S.tileList[tt]);
+		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; }
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
@@ -327,7 +329,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 				self = hOff[hbs] + (i - hBase[hbs]);
 				fi = fpos[self];
 			}
-			int cnt = 0, cntH = 0;
+			int cnt = 0, cntH = 0; float dmin = __int_as_float(0x7f800000);
 			for (int dz = three ? -1 : 0; dz <= (three ? 1 : 0); dz++) for (int dy = -1; dy <= 1; dy++) {
 				const int hb0 = ((hz + dz) * b.HY + hy + dy) * b.HX + hx - 1;
 				const int r0 = hOff[hb0], r1 = act ? hOff[hb0 + 3] : r0;
@@ -339,6 +341,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 						const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
 						const float d2 = dx * dx + dy2 * dy2 + dz2 * dz2;
 						hit = d2 < K.rl2 && m != self; hitH = hit && d2 < rfilt2;
+						if (m != self) dmin = fminf(dmin, d2);
 					}
 					const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
 					if (hit) { const int e = cnt + __popc(gb & lower); if (e < S.tlCap) glist[tv_list_pos(e)] = (uint16_t)m; }
@@ -363,8 +366,11 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 				for (int q = g; q < (cntH + TV_CHUNK - 1) / TV_CHUNK * (TV_CHUNK / 8); q += TV_BG) dstH[q] = ((const uint4*)hl)[q];
 				if (g == 0) { S.tlistCnt[i] = (uint16_t)cnt; S.hcnt[i] = (uint16_t)cntH; S.hpos[i] = S.bpos[i]; }
 			}
+			{ const unsigned mb = __reduce_min_sync(0xffffffffu, __float_as_uint(dmin)); if ((tid & 31) == 0) atomicMin(&sMinBits, mb); }
 			__syncwarp();
 		}
+		__syncthreads();
+		if (tid == 0) S.itemMinD2[tt] = __uint_as_float(sMinBits);
 	}
 }
 
@@ -429,8 +435,9 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const int item = S.tileList[tt];
 		const TvBox b = tv_box(K, item);
-		if (WALLONLY) {   // no particle of this tile is near a wall: the pair bodies are idle, only the tails run (one lane per particle)
-			if (!S.tileWall[b.c0 / K.TV]) {
+		if (WALLONLY || (FOLLOW && F::kCloseOnly)) {   // no particle of this tile is near a wall / no pair of this item is close enough for the
+			// close-pair terms: the pair bodies are idle, only the tails run (one lane per particle)
+			if (WALLONLY ? !S.tileWall[b.c0 / K.TV] : S.itemMinD2[tt] >= K.closeR2) {
 				const int o0 = S.cellStart[b.c0], Pn = S.cellStart[b.c1] - o0;
 				for (int p = tid; p < Pn; p += TV_T) {
 					const int i = o0 + p;
@@ -580,6 +587,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 	if (!S.hitFlag[0]) return;   // k_hits_decide: the hit list still covers the current positions
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
+	__shared__ unsigned sMinBits;
 	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
 	float4* const fpos = T.fpos;
 	uint16_t* ownMap = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM);
@@ -594,6 +602,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const TvBox b = tv_box(K, S.tileList[tt]);
+		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; }
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_tv_build
@@ -610,7 +619,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 			if (act) { cntE = S.tlistCnt[i]; fi = fpos[ownMap[p]]; }
 			const uint4* L = (const uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);
 			const int nchW = __reduce_max_sync(0xffffffffu, (cntE + TV_CHUNK - 1) / TV_CHUNK);
-			int cntH = 0;
+			int cntH = 0; float dmin = __int_as_float(0x7f800000);
 			for (int ch = 0; ch < nchW; ch++) {
 				unsigned w[TV_PER / 2];
 				const int rem = cntE - ch * TV_CHUNK;
@@ -628,7 +637,9 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 						const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
 						const float4 f = fpos[m];
 						const float dx = f.x - fi.x, dy = f.y - fi.y, dz = f.z - fi.z;
-						const bool hit = dx * dx + dy * dy + dz * dz < rfilt2;
+						const float d2 = dx * dx + dy * dy + dz * dz;
+						const bool hit = d2 < rfilt2;
+						if (act) dmin = fminf(dmin, d2);
 						const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
 						if (hit) hl[tv_list_pos(cntH + __popc(gb & lower))] = (uint16_t)m;
 						cntH += __popc(gb);
@@ -646,7 +657,10 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 					S.hpos[i] = make_float4(fi.x + (float)(ox - K.p.domainMinX), fi.y + (float)(oy - K.p.domainMinY), fi.z + (float)(oz - (three ? K.p.domainMinZ : 0.0)), 0.f);
 				}
 			}
+			{ const unsigned mb = __reduce_min_sync(0xffffffffu, __float_as_uint(dmin)); if ((tid & 31) == 0) atomicMin(&sMinBits, mb); }
 			__syncwarp();
 		}
+		__syncthreads();
+		if (tid == 0) S.itemMinD2[tt] = __uint_as_float(sMinBits);
 	}
 }
