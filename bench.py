@@ -42,6 +42,10 @@ ALGO_BYTES = {
     "viscosity": 116, "collision": 104, "pnd_neigh_npcd": 160, "pnd_diffusive": 124, "press_gradient": 96, "wall.closest_point": 121,
     "predict": 172, "correct": 148, "update_bc": 48,
 }
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the round-1 `ncu --set full` captures at k = 171 (10.0 M particles),
+# profiles/r01_ncu_full_summaries.txt; used for roofline.traffic when the run has that size and --traffic is not given
+NCU_TRAFFIC_K171 = {"F3.pnd+diffusive": 5.613739e9 + 0.754892e9, "F1.viscosity+predict": 4.492037e9 + 1.947121e9,
+                    "F5.gradient": 3.306431e9 + 0.238906e9, "shift.concentration": 2.573800e9 + 0.082468e9}
 STEP_ALGO_BYTES = 1732   # sum over the fused groups G0..G7 + E1..E5 of the 3D WC polygon option set
 
 
@@ -180,6 +184,8 @@ def roofline_from_profile(prof, profile_steps, n_particles, ms_step, traffic):
     peak, peak_src, _ = measured_peaks()
     algo = ALGO_BYTES.get(top_name, 0) * n_particles
     achieved = algo / (top_avg_ms * 1e-3) / 1e9
+    if traffic is None and abs(n_particles - 10000422) < 800000:
+        traffic = NCU_TRAFFIC_K171.get(top_name)
     return {"bound": "hbm", "kernel": top_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": traffic, "peak_source": peak_src, "kernel_ms": top_avg_ms, "kernel_share_of_step": top[1] / profile_steps / max(step_prof_ms, 1e-9),
             "algorithmic_bytes_per_particle": ALGO_BYTES.get(top_name, 0),

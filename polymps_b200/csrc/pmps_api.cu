@@ -290,7 +290,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	K.guard2 = (float)(guard > 0 ? guard * guard : 0.0);
 	// reach of the hit lists beyond the cut-offs: a hit list stays valid until somebody may have moved hitDelta since it was made
 	// (k_hits_decide); a larger reach means fewer rebuilds and more rejected candidates per pass, (re + 2 delta)^3
-	K.hitDelta = 0.05 * lo;
+	K.hitDelta = 0.06 * lo;
 	if (const char* e = getenv("PMPS_HIT_DELTA")) { const double v = atof(e); if (v > 0.0 && v < 0.2) K.hitDelta = v * lo; }
 	if (maxRe + 2.0 * K.hitDelta > rl - 1e-3 * lo) K.hitDelta = fmax(0.5 * (rl - 1e-3 * lo - maxRe), 0.0);   // never beyond the Verlet radius
 	{ const double r = (maxRe + 2.0 * K.hitDelta) * (1.0 + 1e-5); K.hitR2 = (float)(r * r); }

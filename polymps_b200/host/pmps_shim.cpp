@@ -190,6 +190,7 @@ void PolygonMesh::closestPointPNDBoundaryAABB(double reS2, double reL2, int nP, 
 	int fem_id, int frw_id, const double *Pos, double *wallPos, double *mirrorPos, double *riw2, int *elementID, int *meshID, double *NormalWall) {
 	if (msh_id < 0 || msh_id > 2) { fprintf(stderr, "libpmps: mesh id %d\n", msh_id); exit(10); }
 	if (!g_meshSet[msh_id] || msh_id == frw_id) send_mesh(msh_id, NV, NF, NNormals, xDataPND, xDataNeigh, Zij, nNeighWall);
+	if (msh_id == 0 && g_S) CALL(pmps_set_uniform_vel_wall(handle(), g_S->uniformVelWall));   // set by updateForcedPolygonMesh (src/main.cpp:405)
 }
 void PolygonMesh::updateParticlesNearPolygonMesh(double reS2, double reL2, int nP, int wijType, int *Typ, int fld, const double *riw2,
 	double *niw, int *numNeighw, std::vector<int>& meshParticlesNeighbors, bool *Nw) {
