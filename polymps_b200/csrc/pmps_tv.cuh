@@ -304,7 +304,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const TvBox b = tv_box(K, S.tileList[tt]);
-		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; }
+		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; S.tileClose[b.c0 / K.TV] = 1; }
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
@@ -370,8 +370,36 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 			__syncwarp();
 		}
 		__syncthreads();
-		if (tid == 0) S.itemMinD2[tt] = __uint_as_float(sMinBits);
+		if (tid == 0) { const float md = __uint_as_float(sMinBits); S.itemMinD2[tt] = md; if (S.tileList[tt] >= 0) S.tileClose[b.c0 / K.TV] = md < K.closeR2 ? 1 : 0; }
 	}
+}
+
+// ---- passes that act on few tiles ----------------------------------------------------------------------------------
+// Wall-only packs touch the tiles with a particle near a polygon wall, close-pair packs (collisions) the tiles that held a
+// close pair when the hit list was made.  For the other tiles only the TAILS of the pack run (integrators, buffer copies):
+// k_tails does that with one thread per particle, fully coalesced, and k_tv leaves those work items at once.
+static __global__ void k_item_flags(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int tt = blockIdx.x * blockDim.x + threadIdx.x;
+	if (tt >= *S.nTiles) return;
+	const int item = S.tileList[tt]; const int tile = item >= 0 ? item : (~item) / K.TV;
+	if (S.tileWall[tile]) S.actList[atomicAdd(&S.actCount[0], 1)] = tt;
+	if (S.tileClose[tile]) S.actList[S.actCap + atomicAdd(&S.actCount[1], 1)] = tt;
+}
+template <bool WALLONLY, class F>
+static __global__ void __launch_bounds__(256) k_tails(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const int c = S.cellOf[i];
+	if (c >= S.nC) return;   // parked ghost slots: k_copy_ghost_tail
+	const int tile = c / K.TV;
+	if (WALLONLY ? S.tileWall[tile] != 0 : S.tileClose[tile] != 0) return;   // k_tv does this tile
+	Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+	s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
+	if (F::kCopyPos) S.pos2[i] = s.pi;
+	if (F::kCopyVel) S.vel2[i] = S.vel[i];
+	if (s.type == K.p.ghost) return;
+	typename F::Ctx ctx;
+	if (F::begin(ctx, S, K, s)) F::end(ctx, S, K, s);
 }
 
 // ---- the walker ---------------------------------------------------------------------------------------------------
@@ -431,27 +459,15 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 	const int nItems = *S.nTiles;
 	const float rfilt2 = K.hitR2;
 	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
-	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
+	// wall-only / close-pair packs visit only the work items k_item_flags listed for them (the tails of the other tiles: k_tails)
+	constexpr bool LISTED = WALLONLY || F::kCloseOnly;
+	const int nVisit = LISTED ? S.actCount[WALLONLY ? 0 : 1] : nItems;
+	const int32_t* visit = S.actList + (WALLONLY ? 0 : S.actCap);
+	for (int it = tv_first_item(S, cursorIdx, &sItem), nxt = 0; it < nVisit; it = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
+		const int tt = LISTED ? visit[it] : it;
 		const int item = S.tileList[tt];
 		const TvBox b = tv_box(K, item);
-		if (WALLONLY || (FOLLOW && F::kCloseOnly)) {   // no particle of this tile is near a wall / no pair of this item is close enough for the
-			// close-pair terms: the pair bodies are idle, only the tails run (one lane per particle)
-			if (WALLONLY ? !S.tileWall[b.c0 / K.TV] : S.itemMinD2[tt] >= K.closeR2) {
-				const int o0 = S.cellStart[b.c0], Pn = S.cellStart[b.c1] - o0;
-				for (int p = tid; p < Pn; p += TV_T) {
-					const int i = o0 + p;
-					Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
-					s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
-					if (F::kCopyPos) S.pos2[i] = s.pi;
-					if (F::kCopyVel) S.vel2[i] = S.vel[i];
-					if (s.type == K.p.ghost) continue;
-					typename F::Ctx ctx;
-					if (F::begin(ctx, S, K, s)) F::end(ctx, S, K, s);
-				}
-				continue;   // uniform over the block
-			}
-		}
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
@@ -602,7 +618,7 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const TvBox b = tv_box(K, S.tileList[tt]);
-		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; }
+		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; S.tileClose[b.c0 / K.TV] = 1; }
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_tv_build
@@ -661,6 +677,6 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constan
 			__syncwarp();
 		}
 		__syncthreads();
-		if (tid == 0) S.itemMinD2[tt] = __uint_as_float(sMinBits);
+		if (tid == 0) { const float md = __uint_as_float(sMinBits); S.itemMinD2[tt] = md; if (S.tileList[tt] >= 0) S.tileClose[b.c0 / K.TV] = md < K.closeR2 ? 1 : 0; }
 	}
 }
