@@ -255,7 +255,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	rc |= dalloc(h, &h->scanBlock, h->nScanBlocks);
 	{	// work items of the tile-Verlet walker: at most one per non-empty cell
 		const size_t items = (size_t)(S.nC < n0 ? S.nC : n0) + 1;
-		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.itemMinD2, items); rc |= dalloc(h, &S.actList, 2 * items); rc |= dalloc(h, &S.actCount, 2); S.actCap = (int32_t)items; rc |= dalloc(h, &S.tileClose, (size_t)h->nTilesAll + 1); rc |= dalloc(h, &S.itemTab, items * (size_t)K.tabStride); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
+		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.itemMinD2, items); rc |= dalloc(h, &S.actList, 3 * items); rc |= dalloc(h, &S.actCount, 4); rc |= dalloc(h, &S.tileSparse, (size_t)h->nTilesAll + 1); S.actCap = (int32_t)items; rc |= dalloc(h, &S.tileClose, (size_t)h->nTilesAll + 1); rc |= dalloc(h, &S.itemTab, items * (size_t)K.tabStride); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
 		int sm = 148; cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device); h->smCount = sm;
 	}
 	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 2); rc |= dalloc(h, &S.hitMove, 4); rc |= dalloc(h, &S.hitFlag, 2); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);

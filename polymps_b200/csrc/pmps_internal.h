@@ -71,7 +71,8 @@ struct DevView {
 	int32_t* tileList; int32_t* nTiles;  // work items of the last rebuild: tile id (whole tile) or ~cell (one bucket of a tile whose halo
 	                                     // does not fit the staging area); count on device
 	uint8_t* tileClose;                  // per tile: some pair of the tile was closer than closeR when the hit list was made (split tiles: always 1)
-	int32_t* actList; int32_t* actCount; // work items a wall-only ([0, cap)) / close-pair ([cap, 2 cap)) pass has to visit, compacted before the pass (k_item_flags); counts [2]
+	uint8_t* tileSparse;                 // per tile: some particle of it wants pairs in the sparse pack about to run (k_sparse_mark)
+	int32_t* actList; int32_t* actCount; // work items a wall-only ([0, cap)) / close-pair ([cap, 2 cap)) / sparse ([2 cap, 3 cap)) pass has to visit, compacted before the pass (k_item_flags); counts [3]
 	int32_t actCap;
 	float* itemMinD2;                    // per work item: smallest squared pair distance (float positions) when the hit list was made
 	int32_t* itemTab;                    // per work item: precomputed halo table (K.tabStride ints, pmps_tv.cuh)

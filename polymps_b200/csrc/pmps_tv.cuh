@@ -384,21 +384,35 @@ static __global__ void k_item_flags(const __grid_constant__ DevView S, const __g
 	const int item = S.tileList[tt]; const int tile = item >= 0 ? item : (~item) / K.TV;
 	if (S.tileWall[tile]) S.actList[atomicAdd(&S.actCount[0], 1)] = tt;
 	if (S.tileClose[tile]) S.actList[S.actCap + atomicAdd(&S.actCount[1], 1)] = tt;
+	if (S.tileSparse[tile]) S.actList[2 * S.actCap + atomicAdd(&S.actCount[2], 1)] = tt;
 }
-template <bool WALLONLY, class F>
+// sparse packs (free-surface / wall-particle means): which tiles hold a particle that wants pairs?  begin() of these bodies is idempotent.
+template <class F>
+static __global__ void __launch_bounds__(256) k_sparse_mark(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const int c = S.cellOf[i];
+	if (c >= S.nC) return;
+	Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+	s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
+	if (s.type == K.p.ghost) return;
+	typename F::Ctx ctx = {};
+	if (F::begin(ctx, S, K, s) && F::need_pairs(ctx)) S.tileSparse[c / K.TV] = 1;
+}
+template <int KIND, class F>   // KIND 0 wall-only, 1 close-pair, 2 sparse
 static __global__ void __launch_bounds__(256) k_tails(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= S.n) return;
 	const int c = S.cellOf[i];
 	if (c >= S.nC) return;   // parked ghost slots: k_copy_ghost_tail
 	const int tile = c / K.TV;
-	if (WALLONLY ? S.tileWall[tile] != 0 : S.tileClose[tile] != 0) return;   // k_tv does this tile
+	if ((KIND == 0 ? S.tileWall[tile] : KIND == 1 ? S.tileClose[tile] : S.tileSparse[tile]) != 0) return;   // k_tv does this tile
 	Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
 	s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
 	if (F::kCopyPos) S.pos2[i] = s.pi;
 	if (F::kCopyVel) S.vel2[i] = S.vel[i];
 	if (s.type == K.p.ghost) return;
-	typename F::Ctx ctx;
+	typename F::Ctx ctx = {};
 	if (F::begin(ctx, S, K, s)) F::end(ctx, S, K, s);
 }
 
@@ -460,9 +474,10 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 	const float rfilt2 = K.hitR2;
 	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
 	// wall-only / close-pair packs visit only the work items k_item_flags listed for them (the tails of the other tiles: k_tails)
-	constexpr bool LISTED = WALLONLY || F::kCloseOnly;
-	const int nVisit = LISTED ? S.actCount[WALLONLY ? 0 : 1] : nItems;
-	const int32_t* visit = S.actList + (WALLONLY ? 0 : S.actCap);
+	constexpr bool LISTED = WALLONLY || F::kCloseOnly || SPARSE;
+	constexpr int KIND = WALLONLY ? 0 : SPARSE ? 2 : 1;
+	const int nVisit = LISTED ? S.actCount[KIND] : nItems;
+	const int32_t* visit = S.actList + KIND * S.actCap;
 	for (int it = tv_first_item(S, cursorIdx, &sItem), nxt = 0; it < nVisit; it = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const int tt = LISTED ? visit[it] : it;
