@@ -37,6 +37,17 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 		const int si = S.slotOfHost[hi];
 		const double4 pcur = S.pos[si];
 		if (pk_type(pcur) != K.p.fluid || !out_of_domain(K, pcur)) continue;
+		if (S.nOwn != 0x7fffffff) {
+			// slab rank (pmps_slab.cu): the last live row of the table is a halo copy, not a particle to move into the hole.  The
+			// particle becomes a ghost IN PLACE; the row is reclaimed at the next re-partition (the owner drops ghosts there), the
+			// neighbours' copies turn into ghosts with the next position refresh (the type travels with the position).
+			double4 g; g.x = K.p.domainMaxX - K.p.partDist; g.y = K.p.domainMaxY - K.p.partDist;
+			g.z = K.p.dim == 2 ? 0.0 : K.p.domainMaxZ - K.p.partDist; g.w = pk_make(K.p.ghost, pk_ptype(pcur));
+			S.pos[si] = g; double4 vz = S.vel[si]; vz.x = vz.y = vz.z = 0.0; S.vel[si] = vz;
+			S.particleBC[si] = K.p.other; S.particleNearWall[si] = 0; S.nearMeshType[si] = 0; S.distParticleWall2[si] = K.big; S.press[si] = 0.0;
+			S.flags[FLAG_OOD_TOTAL] += 1;
+			continue;
+		}
 		const int hl = live - 1; const int sl = S.slotOfHost[hl];
 		// The reference copies particle hl over particle hi and turns hl into a ghost.  In slot space the DATA stays where
 		// it is (slot sl keeps searching around its own position with its own candidate list); the host LABELS are swapped:

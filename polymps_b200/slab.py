@@ -175,9 +175,10 @@ class SlabDomain:
         nO = self.n_own
         x = T["pos"][:nO, 0]
         false = torch.zeros(nO, dtype=torch.bool, device=dev)
-        goL = (x < self.xlo) if self.left is not None else false
-        goR = (x >= self.xhi) if self.right is not None else false
-        stay = ~(goL | goR)
+        alive = T["particleType"][:nO] != int(b.ghost_fill("particleType")) if "particleType" in T else ~false   # removed by the out-of-domain test: dropped here
+        goL = alive & (x < self.xlo) if self.left is not None else false
+        goR = alive & (x >= self.xhi) if self.right is not None else false
+        stay = alive & ~(goL | goR)
         nearL = stay & (x < self.xlo + self.W) if self.left is not None else false
         nearR = stay & (x >= self.xhi - self.W) if self.right is not None else false
         idx = {k: torch.nonzero(m, as_tuple=False).flatten() for k, m in (("stay", stay), ("goL", goL), ("goR", goR), ("nearL", nearL), ("nearR", nearR))}

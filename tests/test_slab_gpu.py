@@ -10,11 +10,13 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world,scheme", [(2, "wc"), (3, "wc"), (2, "inc")])
+@pytest.mark.parametrize("world,scheme", [(2, "wc"), (3, "wc"), (2, "inc"), (2, "splash")])
 def test_slab_run_matches_single_engine(world, scheme):
-    port = 29700 + (os.getpid() % 1000) + world + (7 if scheme == "inc" else 0)
+    port = 29700 + (os.getpid() % 1000) + world + {"wc": 0, "inc": 7, "splash": 13}[scheme]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(HERE, "slab_parity.py"), "--backend", "gloo", "--one-gpu", "--steps", "40"]
+    if scheme == "splash":   # particles leave through the open top: out-of-domain removal on slab ranks
+        cmd += ["--splash", "4.0", "--drift", "0.5"]
     if scheme == "inc":   # PPE assembly + CG sharded over the slabs (all-reduced dot products, halo refresh of p per iteration)
         cmd += ["--inc", "--steps", "20"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
