@@ -217,7 +217,7 @@ def main_gpu_slab(args, rank, world, local):
     mine = np.nonzero((xi >= cuts_x[rank]) & (xi < cuts_x[rank + 1]))[0]
     loc = cases.dam3d_block_columns(kN, int(mine[0]), int(mine[-1]) + 1, lo=lo)
     halo_est = int(2 * 3.6 * ny * nz)
-    se = SlabEngine(ps, meshes, loc, cuts_x, rank, world, device=local, capacity=len(loc["ptype"]) + 2 * halo_est + 200000)
+    se = SlabEngine(ps, meshes, loc, cuts_x, rank, world, device=local, capacity=len(loc["ptype"]) + 6 * halo_est + 200000, cuts=cuts)
     del loc
     eng = se.eng; stream = se.stream
     se.init_step0(); se.step(args.warmup); eng.synchronize()

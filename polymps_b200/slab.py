@@ -114,9 +114,13 @@ class SlabDomain:
     """Partition state of one rank + the two exchanges (re-partition at rebuilds, field refresh between phases)."""
 
     def __init__(self, backend: TableBackend, rank: int, world: int, xlo: float, xhi: float, halo_width: float, group=None,
-                 fields=TABLE_FIELDS):
+                 fields=TABLE_FIELDS, grid=None):
+        """grid = (domainMinX, bucketSide, numBucketsX, cuts) enables RE-BALANCING: at every re-partition the cuts (bucket-column
+        indices, identical on all ranks) move by at most ONE column towards the balanced partition of the current particle count
+        per column — one column = one halo width, so every particle still only ever moves to a neighbouring rank."""
         self.b = backend; self.rank = rank; self.world = world; self.group = group
         self.xlo = float(xlo); self.xhi = float(xhi); self.W = float(halo_width)
+        self.grid = grid; self.cuts = list(grid[3]) if grid else None; self.min_cols = 3
         if world > 1 and self.xhi - self.xlo <= 2.0 * self.W:
             raise ValueError("slab [%g, %g) is not wider than two halos of %g" % (xlo, xhi, halo_width))
         self.fields = list(fields)
@@ -175,6 +179,8 @@ class SlabDomain:
         nO = self.n_own
         x = T["pos"][:nO, 0]
         false = torch.zeros(nO, dtype=torch.bool, device=dev)
+        if self.grid is not None and self.world > 1:
+            self._rebalance(x if "particleType" not in T else x[T["particleType"][:nO] != int(b.ghost_fill("particleType"))])
         alive = T["particleType"][:nO] != int(b.ghost_fill("particleType")) if "particleType" in T else ~false   # removed by the out-of-domain test: dropped here
         goL = alive & (x < self.xlo) if self.left is not None else false
         goR = alive & (x >= self.xhi) if self.right is not None else false
@@ -235,6 +241,24 @@ class SlabDomain:
         self.n_own = new_own; self.n_live = n_live
         b.upload_table(newT, n_live, new_own)
         self.stats["repartitions"] += 1; self.stats["migrants_out"] += len(idx["goL"]) + len(idx["goR"]); self.stats["halo"] = nHL + nHR
+
+    def _rebalance(self, x_alive: torch.Tensor) -> None:
+        x0, side, ncol, _ = self.grid
+        col = ((x_alive - x0) / side).to(torch.int64).clamp_(0, ncol - 1)
+        hist = torch.bincount(col, minlength=ncol).to(torch.float64)
+        self.all_sum(hist)
+        target = choose_cuts(hist.cpu().numpy().astype(np.int64), self.world, self.min_cols)
+        new = list(self.cuts)
+        for r in range(1, self.world):
+            new[r] += (target[r] > new[r]) - (target[r] < new[r])
+        for r in range(1, self.world):
+            new[r] = max(new[r], new[r - 1] + self.min_cols)
+        for r in range(self.world - 1, 0, -1):
+            new[r] = min(new[r], new[r + 1] - self.min_cols)
+        if new != self.cuts:
+            self.stats["cut_moves"] = self.stats.get("cut_moves", 0) + sum(1 for a, c in zip(new, self.cuts) if a != c)
+        self.cuts = new
+        self.xlo = x0 + new[self.rank] * side; self.xhi = x0 + new[self.rank + 1] * side
 
     # -- per-phase refresh of the halo copies
     def refresh(self, mask: int) -> None:
@@ -344,7 +368,8 @@ class SlabEngine:
     farther than one slab from where they belong; the first re-partition moves strays and builds the halos."""
 
     def __init__(self, ps, meshes, local: dict, cuts_x: Sequence[float], rank: int, world: int, device: int = 0, group=None,
-                 capacity: Optional[int] = None, shifting_jacobi: bool = True):
+                 capacity: Optional[int] = None, shifting_jacobi: bool = True, cuts: Optional[Sequence[int]] = None):
+        """cuts = the bucket-column indices behind cuts_x: given, the slabs re-balance themselves as the particles move."""
         from .engine import Engine
         self.ps = ps; self.rank = rank; self.world = world
         self.dev = torch.device("cuda", device)
@@ -353,7 +378,8 @@ class SlabEngine:
         n = len(local["ptype"])
         n0 = int(capacity) if capacity else int(n * 1.25) + 200000
         self.backend = EngineBackend(self.eng, n0, self.dev)
-        self.dom = SlabDomain(self.backend, rank, world, cuts_x[rank], cuts_x[rank + 1], ps.bucketSide * (1.0 + 1e-9), group=group)
+        grid = (ps.domainMinX, ps.bucketSide, ps.numBucketsX, list(cuts)) if cuts is not None else None
+        self.dom = SlabDomain(self.backend, rank, world, cuts_x[rank], cuts_x[rank + 1], ps.bucketSide * (1.0 + 1e-9), group=group, grid=grid)
         self.scal = torch.zeros(3, dtype=torch.float64, device=self.dev)
         self.nph = int(self.eng.lib.pmps_step_phases())
         # the Poisson solve of the incompressible scheme calls back for its all-reduces and the halo refresh of the search direction

@@ -67,11 +67,11 @@ def main():
     cuts_x = [ps.domainMinX + c * ps.bucketSide for c in cuts]
     mine = np.nonzero((case.pos[:, 0] >= cuts_x[rank]) & (case.pos[:, 0] < cuts_x[rank + 1]))[0]
     loc = {"ptype": case.ptype[mine], "pos": case.pos[mine], "vel": case.vel[mine], "press": case.press[mine], "gid": mine.astype(np.int64)}
-    se = SlabEngine(ps, meshes, loc, cuts_x, rank, world, device=local, capacity=case.n + 1000)
+    se = SlabEngine(ps, meshes, loc, cuts_x, rank, world, device=local, capacity=case.n + 1000, cuts=cuts)
     se.init_step0(); se.step(a.steps)
     got = se.download_owned(FIELDS)
     sc = se.scalars()
-    stats = dict(se.dom.stats); stats.update(n_own=se.n_own, velMax=sc.velMax, launches=se.eng.launch_count(), solverIter=sc.solverIter)
+    stats = dict(se.dom.stats); stats.update(cuts=list(se.dom.cuts), n_own=se.n_own, velMax=sc.velMax, launches=se.eng.launch_count(), solverIter=sc.solverIter)
     allgot = [None] * world; allstats = [None] * world
     dist.all_gather_object(allgot, got); dist.all_gather_object(allstats, stats)
     ok = True
@@ -112,7 +112,7 @@ def main():
         if a.inc:
             print("  CG iterations of the last step: slabs %d, single engine %d" % (allstats[0]["solverIter"], s1.solverIter))
             ok &= abs(allstats[0]["solverIter"] - s1.solverIter) <= 3 and s1.solverIter > 3
-        print("  velMax %.12g vs %.12g (rel %.2e); migrants %d, repartitions %d" % (allstats[0]["velMax"], s1.velMax, dv, sum(s["migrants_out"] for s in allstats), allstats[0]["repartitions"]))
+        print("  velMax %.12g vs %.12g (rel %.2e); migrants %d, repartitions %d, cuts %s -> %s (%d moves), owned %s" % (allstats[0]["velMax"], s1.velMax, dv, sum(s["migrants_out"] for s in allstats), allstats[0]["repartitions"], list(cuts), allstats[0]["cuts"], allstats[0].get("cut_moves", 0), [s["n_own"] for s in allstats]))
         ok &= dv <= a.rtol
         if world > 1:
             ok &= sum(s["migrants_out"] for s in allstats) > 0 and allstats[0]["repartitions"] > 2

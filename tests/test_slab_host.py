@@ -82,7 +82,7 @@ def _gather(obj, world):
     return out
 
 
-def _worker(rank, world, port, n_total, seed, rounds):
+def _worker(rank, world, port, n_total, seed, rounds, rebalance=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -98,9 +98,14 @@ def _worker(rank, world, port, n_total, seed, rounds):
         be.T["pos"][:n] = torch.from_numpy(pos[mine]); be.T["particleType"][:] = -1; be.T["particleType"][:n] = 0
         be.T["press"][:n] = torch.from_numpy(mine.astype(np.float64)) * 10.0
         be.n_live = be.n_own = n
-        dom = SlabDomain(be, rank, world, cuts[rank], cuts[rank + 1], W, fields=FIELDS)
+        grid = (0.0, W, int(round(L / W)), [int(round(c / W)) for c in cuts]) if rebalance else None
+        dom = SlabDomain(be, rank, world, cuts[rank], cuts[rank + 1], W, fields=FIELDS, grid=grid)
+        if rebalance:
+            vel_bias = 12.0   # everybody drifts to the right: the cuts must follow
         dom.repartition(gid=torch.from_numpy(mine.astype(np.int64)), n_own=n)
         vel = rng.normal(0.0, 1.0, size=(n_total, 3)) * np.array([0.6, 0.05, 0.05])   # global velocity field by gid
+        if rebalance:
+            vel[:, 0] = np.abs(vel[:, 0]) * 0.2 + vel_bias * (pos[:, 0] < 0.5 * L)   # the left half streams right
         for rd in range(rounds):
             # ---- invariants of the partition
             own_g = dom.gid[:dom.n_own].numpy(); own_x = be.T["pos"][:dom.n_own, 0].numpy()
@@ -115,7 +120,7 @@ def _worker(rank, world, port, n_total, seed, rounds):
                 f0, nh = dom.halo_first[side], dom.halo_n[side]
                 hg = set(dom.gid[f0:f0 + nh].numpy().tolist())
                 ng, nx = allown[nb]
-                cut = cuts[rank] if side == "L" else cuts[rank + 1]
+                cut = dom.xlo if side == "L" else dom.xhi
                 near = set(ng[np.abs(nx - cut) < W * 0.999].tolist())
                 assert near <= hg, "round %d rank %d side %s: %d of the neighbour's near particles have no halo copy" % (rd, rank, side, len(near - hg))
                 assert hg <= set(ng.tolist()), "halo copy of a particle the neighbour does not own"
@@ -124,7 +129,7 @@ def _worker(rank, world, port, n_total, seed, rounds):
             g_own = dom.gid[:dom.n_own].double()
             be.T["press"][:dom.n_own] = g_own * 10.0 + rd; be.T["pndi"][:dom.n_own] = g_own * 0.5 - rd
             be.T["concentration"][:dom.n_own] = g_own + 0.25 * rd; be.T["pndki"][:dom.n_own] = -g_own
-            be.T["vel"][:dom.n_own] = torch.from_numpy(vel[dom.gid[:dom.n_own].numpy()]) * (1 + rd)
+            be.T["vel"][:dom.n_own] = torch.from_numpy(vel[dom.gid[:dom.n_own].numpy()]) * ((1 + rd) if not rebalance else 1.0)
             be.T["pos"][:dom.n_own] += 0.02 * be.T["vel"][:dom.n_own]
             for f in ("press", "pndi", "concentration", "pndki"):
                 be.T[f][dom.n_own:dom.n_live] = -777.0
@@ -144,6 +149,13 @@ def _worker(rank, world, port, n_total, seed, rounds):
             # ---- next rebuild: particles have moved (some across the cuts)
             dom.repartition()
         assert dom.stats["repartitions"] == rounds + 1
+        if rebalance:
+            moved = torch.tensor([float(dom.stats.get("cut_moves", 0))]); dist.all_reduce(moved)
+            assert moved.item() > 0, "the cuts never moved"
+            own_x = be.T["pos"][:dom.n_own, 0]
+            lo_ok = rank == 0 or float(own_x.min()) >= dom.xlo          # the end slabs keep whatever lies beyond the domain
+            hi_ok = rank == world - 1 or float(own_x.max()) < dom.xhi
+            assert dom.n_own == 0 or (lo_ok and hi_ok), "an owned particle lies outside the slab"
         tot = torch.tensor([float(dom.stats["migrants_out"])]); dist.all_reduce(tot)
         assert tot.item() > 0, "the test moved nobody across a cut"
         m = dom.all_max(torch.tensor([float(rank)])); assert m.item() == world - 1
@@ -155,6 +167,13 @@ def _worker(rank, world, port, n_total, seed, rounds):
 def test_slab_partition_over_gloo(world):
     port = 29500 + (os.getpid() % 2000) + world
     mp.spawn(_worker, args=(world, port, 6000, 7 + world, 4), nprocs=world, join=True)
+
+
+def test_slab_rebalancing_over_gloo():
+    """The left half of the particles streams to the right: the cuts move (one bucket column per re-partition) and every
+    invariant of the partition keeps holding."""
+    port = 29500 + (os.getpid() % 2000) + 11
+    mp.spawn(_worker, args=(3, port, 6000, 5, 8, True), nprocs=3, join=True)
 
 
 def test_choose_cuts_balances_and_respects_width():
