@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define PMPS_ABI_VERSION 1
+#define PMPS_ABI_VERSION 2
 
 enum { PMPS_OK = 0, PMPS_E_ARG = -1, PMPS_E_CUDA = -2, PMPS_E_STATE = -3, PMPS_E_UNSUPPORTED = -4, PMPS_E_OVERFLOW = -5 };
 
@@ -44,7 +44,7 @@ typedef struct PmpsParams {
 	int32_t collisionType;          /* 0 PC, 1 DPC */
 	int32_t shiftingType;           /* 0 off, 1 DW*Uij, 2 grad C */
 	int32_t repulsiveForceType;     /* 0 Harada 1 Mitsume 2 Lennard-Jones 3 Monaghan-Kajtar */
-	int32_t fluidType;              /* 0 Newtonian (1 = non-Newtonian: PMPS_E_UNSUPPORTED) */
+	int32_t fluidType;              /* 0 Newtonian, 1 non-Newtonian (two-phase granular rheology; particle walls only so far) */
 	int32_t domainTypeBC;           /* 0 none (1 = periodic: PMPS_E_UNSUPPORTED) */
 	int32_t ghost, fluid, wall, dummyWall;      /* particle type ids */
 	int32_t surface, inner, other;              /* particleBC ids */
@@ -53,6 +53,7 @@ typedef struct PmpsParams {
 	int32_t shiftingJacobi;         /* 1: shifting reads a position snapshot (default, parallel-safe);
 	                                   the reference's 1-thread behaviour is a Gauss-Seidel sweep in index order */
 	int32_t _pad0;
+	int32_t fractionMethod;         /* PSystem->Fraction_method: 1 neighbour count, 2 weighted (src/MpsViscosity.cpp:106,145) */
 	/* geometry */
 	double domainMinX, domainMinY, domainMinZ, domainMaxX, domainMaxY, domainMaxZ;   /* AFTER the +-3 lo extension */
 	double bucketSide, invBucketSide;
@@ -73,6 +74,9 @@ typedef struct PmpsParams {
 	double distCollisionLimit2, restitutionCollision, lambdaCollision;
 	double betaPnd, betaNeigh, delta2;
 	double velMax;                  /* velMax carried in from the host (0 at start, src/MpsParticle.cpp:212) */
+	/* non-Newtonian rheology (fluidType 1), names as in include/MpsParticleSystem.h; src/MpsInputOutput.cpp:250-316 */
+	double KNM_VS1, KNM_VS2, DNS_SDT, PHI_1, PHI_2, cohes, MEU0, DG, I0, mm, Cd, VF_min, VF_max;
+	double timeCurrent;             /* time at pmps_create; the fused step advances its own copy by timeStep (src/main.cpp:463) */
 } PmpsParams;
 
 /* Pointers into the host's MpsParticle arrays (include/MpsParticle.h:139-241); NULL = not transferred. */
@@ -87,6 +91,8 @@ typedef struct PmpsHostArrays {
 	double *pos, *vel, *acc, *accStar, *npcdDeviation, *gradConcentration;
 	double *correcMatrixRow1, *correcMatrixRow2, *correcMatrixRow3;
 	double *particleAtWallPos, *mirrorParticlePos, *polygonNormal, *forceWall, *dvelCollision;
+	/* non-Newtonian fields (allocated by the reference only when fluidType == 1, src/MpsInputOutput.cpp:729-744) */
+	double *Cv, *II, *MEU_Y, *Inertia, *p_rheo_new, *p_smooth, *VF, *S11, *S12, *S13, *S22, *S23, *S33;
 } PmpsHostArrays;
 
 typedef struct PmpsScalars {      /* what displayInfo prints (src/MpsInputOutput.cpp:45-53) + health counters */
@@ -97,6 +103,7 @@ typedef struct PmpsScalars {      /* what displayInfo prints (src/MpsInputOutput
 	                                 reference's own stale-bucket search would start missing neighbours */
 	int32_t outOfDomainEvents;    /* particles turned into ghosts so far (src/MpsParticle.cpp:286-396) */
 	int32_t maxBucketCount;       /* fullest bucket at the last rebuild */
+	double CFLvisc;               /* fluidType 1: timeStep*max(MEU)/(rho_mix lo^2), src/MpsViscosity.cpp:690 */
 } PmpsScalars;
 
 typedef struct pmps_handle pmps_t;
@@ -125,6 +132,9 @@ int pmps_download_device(pmps_t* h, PmpsHostArrays* device_arrays);   /* gather 
 
 /* ---- stage calls: one per reference method, in mainLoopOfSimulation order (src/main.cpp:256-456) ----------- */
 int pmps_update_buckets(pmps_t* h);              /* MpsBucket::updateParticlesID            src/MpsBucket.cpp:299-353 */
+int pmps_calc_volume_fraction(pmps_t* h);        /* MpsViscosity::calcVolumeFraction        src/MpsViscosity.cpp:104-190 (fluidType 1) */
+int pmps_calc_viscosity_interaction(pmps_t* h);  /* MpsViscosity::calcViscosityInteractionVal src/MpsViscosity.cpp:194-700 (fluidType 1) */
+int pmps_set_time(pmps_t* h, double timeCurrent);/* PSystem->timeCurrent as the rheology reads it (3D branch, src/MpsViscosity.cpp:529) */
 int pmps_calc_viscosity(pmps_t* h);              /* MpsViscosity::calcViscosity             src/MpsViscosity.cpp:20-100 */
 int pmps_add_gravity(pmps_t* h);                 /* MpsParticle::addGravity                 src/MpsParticle.cpp:111-130 */
 int pmps_predict(pmps_t* h);                     /* MpsParticleVelPos::predictionVelocityPosition  src/MpsParticleVelPos.cpp:20-50 */

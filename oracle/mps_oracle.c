@@ -173,6 +173,10 @@ int oracle_check_out_domain(const PmpsParams* P, PmpsHostArrays* A) {
 			MV3(acc); MV3(accStar); MV3(pos); MV3(vel); MV3(npcdDeviation); MV3(gradConcentration); MV3(correcMatrixRow1);
 			MV3(correcMatrixRow2); MV3(correcMatrixRow3); MV3(dvelCollision); MV3(particleAtWallPos); MV3(mirrorParticlePos);
 			MV3(polygonNormal); MV3(forceWall);
+			if (P->fluidType == 1) {   /* src/MpsParticle.cpp:322-337 */
+				MV1(Cv); MV1(II); MV1(MEU_Y); MV1(Inertia); MV1(p_rheo_new); MV1(p_smooth); MV1(VF);
+				MV1(S12); MV1(S13); MV1(S23); MV1(S11); MV1(S22); MV1(S33);
+			}
 			A->particleType[last] = P->ghost; A->particleBC[last] = P->other; A->particleNearWall[last] = 0;
 			A->nearMeshType[last] = 0; A->distParticleWall2[last] = 10e8 * P->partDist;
 			for (int k = 0; k < 3; k++) A->vel[3 * (size_t)last + k] = 0.0;
@@ -982,9 +986,137 @@ void oracle_init_step0(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMes
 	pressure_stage(P, A, B, NULL, NULL);
 }
 
+/* ------------------------------------------------------------------------------------------------ non-Newtonian rheology */
+void oracle_calc_volume_fraction(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {   /* src/MpsViscosity.cpp:104-190 */
+	PARFOR
+	for (int i = 0; i < A->numParticles; i++) {
+		if (A->particleType[i] != P->fluid) continue;
+		const double* xi = A->pos + 3 * (size_t)i; double sum1 = 0.0, sum2 = 0.0;
+		NEIGH_LOOP(P, A, B, xi, xi, {
+			if (d2 < P->reS2) {
+				if (j != i && A->particleType[j] == P->fluid) {
+					double w = 1.0;
+					if (P->fractionMethod != 1) { const double dst = sqrt(d2); w = wgt(dst, P->reS, P->weightType); }
+					sum1 += w;
+					if (A->PTYPE[j] >= 2) sum2 += w;
+				}
+			}
+		});
+		A->Cv[i] = sum1 < P->epsilonZero ? 0.0 : sum2 / sum1;
+	}
+}
+
+/* src/MpsViscosity.cpp:194-700.  The column maps are filled in index order (one thread), as the reference does with OMP_NUM_THREADS=1;
+ * returns CFLvisc (:690). */
+double oracle_calc_viscosity_interaction(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	const double gravityMod = sqrt(P->gravityX * P->gravityX + P->gravityY * P->gravityY + P->gravityZ * P->gravityZ);
+	const double Xmin = P->domainMinX, Xmax = P->domainMaxX, Ymin = P->domainMinY;
+	double Ymax = Ymin, Zmin = 0.0;
+	if (P->dim == 3) { Ymax = P->domainMaxY; Zmin = P->domainMinZ; }
+	const double aaL0 = 2.0 * P->partDist;
+	const int kx_max = (int)((Xmax - Xmin) / aaL0) + 1, ky_max = (int)((Ymax - Ymin) / aaL0) + 1;
+	const int stride = ky_max + 1; const size_t cells = (size_t)(kx_max + 1) * stride;
+	double* BL = (double*)malloc(sizeof(double) * cells); double* WL = (double*)malloc(sizeof(double) * cells); double* PS = (double*)malloc(sizeof(double) * cells);
+	for (size_t c = 0; c < cells; c++) { BL[c] = P->dim == 2 ? Ymin : Zmin; WL[c] = BL[c]; PS[c] = 0.0; }
+	for (int i = 0; i < A->numParticles; i++) {   /* :273-301 */
+		if (A->particleType[i] != P->fluid) continue;
+		const double* x = A->pos + 3 * (size_t)i;
+		const int kx = (int)((x[0] - Xmin) / aaL0) + 1;
+		const int ky = P->dim == 2 ? 1 : (int)((x[1] - Ymin) / aaL0) + 1;
+		const double h = P->dim == 2 ? x[1] : x[2]; const size_t c = (size_t)kx * stride + ky;
+		if (h > BL[c] && A->Cv[i] > 0.5) { BL[c] = h; PS[c] = A->press[i]; }
+		if (h > WL[c] && A->PTYPE[i] == 1) WL[c] = h;
+	}
+	PARFOR
+	for (int i = 0; i < A->numParticles; i++) {   /* strain rate, :304-437 */
+		if (A->particleType[i] != P->fluid) continue;
+		double sum1 = 0.0, sum2 = 0.0, sum3 = 0.0, sum4 = 0.0, sum5 = 0.0, sum6 = 0.0, sum7 = 0.0, sum8 = 0.0, sum9 = 0.0, sum10 = 0.0, sumWs = 0.0;
+		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i; const double* vi = A->vel + 3 * (size_t)i;
+		double MC[9];
+		for (int k = 0; k < 3; k++) { MC[k] = A->correcMatrixRow1[3 * (size_t)i + k]; MC[3 + k] = A->correcMatrixRow2[3 * (size_t)i + k]; MC[6 + k] = A->correcMatrixRow3[3 * (size_t)i + k]; }
+		NEIGH_LOOP(P, A, B, xi, mi, {
+			if (PRED_P(P, P->reS2)) {
+				if (j != i) {
+					const double dst = sqrt(d2); const double wS = wgt(dst, P->reS, P->weightType);
+					const double ux = A->vel[3 * (size_t)j] - vi[0], uy = A->vel[3 * (size_t)j + 1] - vi[1], uz = A->vel[3 * (size_t)j + 2] - vi[2];
+					const double inv = 1.0 / d2;
+					double r0 = rx, r1 = ry, r2 = rz;
+					if (P->gradientCorrection) {
+						r0 = (rx * MC[0] + ry * MC[1] + rz * MC[2]); r1 = (rx * MC[3] + ry * MC[4] + rz * MC[5]); r2 = (rx * MC[6] + ry * MC[7] + rz * MC[8]);
+					}
+					sum1 += ux * r0 * wS * inv; sum2 += ux * r1 * wS * inv; sum3 += ux * r2 * wS * inv;
+					sum4 += uy * r0 * wS * inv; sum5 += uy * r1 * wS * inv; sum6 += uy * r2 * wS * inv;
+					sum7 += uz * r0 * wS * inv; sum8 += uz * r1 * wS * inv; sum9 += uz * r2 * wS * inv;
+					sum10 += A->press[j] * wS; sumWs += wS;
+				}
+			}
+		});
+		const double a = -P->coeffPressGrad;
+		const double Uxx = a * sum1, Uxy = a * sum2, Uxz = a * sum3, Uyx = a * sum4, Uyy = a * sum5, Uyz = a * sum6, Uzx = a * sum7, Uzy = a * sum8, Uzz = a * sum9;
+		if (sumWs > P->epsilonZero) A->p_smooth[i] = sum10 / sumWs; else A->p_smooth[i] = A->press[i];
+		if (A->p_smooth[i] < P->epsilonZero) A->p_smooth[i] = 0.0;
+		A->S11[i] = 0.5 * (Uxx + Uxx); A->S12[i] = 0.5 * (Uxy + Uyx); A->S13[i] = 0.5 * (Uxz + Uzx);
+		A->S22[i] = 0.5 * (Uyy + Uyy); A->S23[i] = 0.5 * (Uyz + Uzy); A->S33[i] = 0.5 * (Uzz + Uzz);
+		A->II[i] = 0.5 * (A->S11[i] * A->S11[i] + 2.0 * A->S12[i] * A->S12[i] + 2.0 * A->S13[i] * A->S13[i] + A->S22[i] * A->S22[i] + 2.0 * A->S23[i] * A->S23[i] + A->S33[i] * A->S33[i]);
+		if (A->II[i] < P->epsilonZero || A->II[i] * 0 != 0) A->II[i] = 0.0;
+	}
+	double mi_max = 0.0;
+	for (int i = 0; i < A->numParticles; i++) {   /* :463-640 */
+		if (A->particleType[i] != P->fluid) continue;
+		const double* x = A->pos + 3 * (size_t)i; const double* v = A->vel + 3 * (size_t)i;
+		const double vel2i = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+		if (A->PTYPE[i] == 1) A->MEU[i] = P->KNM_VS1 * P->DNS_FL1;
+		else if (A->PTYPE[i] == 2) {
+			double phi = (A->Cv[i] - 0.25) * P->PHI_1 / (1.0 - 0.25), phi2 = (A->Cv[i] - 0.25) * P->PHI_2 / (1.0 - 0.25);
+			if (A->Cv[i] <= 0.25) { phi = P->epsilonZero; phi2 = P->epsilonZero; }
+			A->p_rheo_new[i] = A->p_smooth[i];
+			const int kx = (int)((x[0] - Xmin) / aaL0) + 1; int ky; double normal_stress; size_t c;
+			if (P->dim == 2) {
+				ky = 1; c = (size_t)kx * stride + ky;
+				normal_stress = (BL[c] - x[1] + P->partDist * 0.5) * (P->DNS_FL2 - P->DNS_FL1) * gravityMod - vel2i * (P->DNS_FL2 - P->DNS_FL1) * 0.5;
+				if (WL[c] < BL[c]) normal_stress = A->p_smooth[i];
+				else normal_stress = A->p_smooth[i] - PS[c];
+			} else {
+				ky = (int)((x[1] - Ymin) / aaL0) + 1; c = (size_t)kx * stride + ky;
+				normal_stress = (BL[c] - x[2] + P->partDist * 0.5) * (P->DNS_FL2 - P->DNS_FL1) * gravityMod - vel2i * (P->DNS_FL2 - P->DNS_FL1) * 0.5;
+				if (A->p_smooth[i] - (WL[c] - x[2]) * P->DNS_FL1 * gravityMod < P->epsilonZero) A->p_smooth[i] = (WL[c] - x[2]) * P->DNS_FL1 * gravityMod;
+				if (P->timeCurrent <= 1.0) normal_stress = (1.0 - P->timeCurrent) * (A->p_smooth[i] - (WL[c] - x[2]) * P->DNS_FL1 * gravityMod) + P->timeCurrent * normal_stress;
+			}
+			if (normal_stress < 1.0 || A->Cv[i] < 0.5) normal_stress = 1.0;
+			A->p_rheo_new[i] = normal_stress;
+			const double modE = sqrt(A->II[i]);
+			if (WL[c] < BL[c]) A->Inertia[i] = modE * P->DG / sqrt(normal_stress / P->DNS_SDT);
+			else A->Inertia[i] = modE * P->DG / sqrt(normal_stress / (P->DNS_FL1 * P->Cd));
+			A->VF[i] = P->VF_max - (P->VF_max - P->VF_min) * A->Inertia[i];
+			if (A->VF[i] < P->VF_min) A->VF[i] = P->VF_min;
+			A->RHO[i] = P->DNS_SDT * A->VF[i] + (1.0 - A->VF[i]) * P->DNS_FL1;
+			phi *= (A->VF[i] / P->VF_max);
+			const double alpha_1 = 2.0 * sqrt(3.0) * sin(phi) / (3.0 - sin(phi)), beta_1 = 2.0 * sqrt(3.0) * cos(phi) / (3.0 - sin(phi));
+			double yield_stress = P->cohes * beta_1 + normal_stress * alpha_1;
+			if (yield_stress < P->epsilonZero) yield_stress = 0.0;
+			A->MEU_Y[i] = yield_stress / (2.0 * sqrt(modE * modE + P->epsilonZero));
+			double meu_0;
+			if (WL[c] < BL[c]) meu_0 = 0.5 * (tan(phi2) - tan(phi)) * normal_stress * P->DG / (P->I0 * sqrt(normal_stress / P->DNS_FL2) + modE * P->DG) * modE / (sqrt(modE * modE + P->epsilonZero));
+			else meu_0 = 0.5 * (tan(phi2) - tan(phi)) * normal_stress * P->DG / (P->I0 * sqrt(normal_stress / (P->DNS_FL1 * P->Cd)) + modE * P->DG) * modE / (sqrt(modE * modE + P->epsilonZero));
+			if (modE <= P->epsilonZero || (meu_0 * 0) != 0) meu_0 = P->MEU0;
+			const double visc_max = (meu_0 + yield_stress * P->mm * 0.5);
+			A->MEU[i] = A->MEU_Y[i] + meu_0;
+			if (A->II[i] <= P->epsilonZero) A->MEU[i] = visc_max;
+			if (A->MEU[i] > mi_max) mi_max = A->MEU[i];
+		}
+		if (A->PTYPE[i] >= 2) {
+			if (A->Cv[i] > 0.5) A->RHO[i] = P->DNS_FL2;
+			else A->RHO[i] = A->Cv[i] * P->DNS_FL2 + (1.0 - A->Cv[i]) * P->DNS_FL1;
+		}
+	}
+	free(BL); free(WL); free(PS);
+	return P->timeStep * mi_max / ((P->DNS_SDT * P->VF_max + (1.0 - P->VF_max) * P->DNS_FL1) * P->partDist * P->partDist);
+}
+
 void oracle_step(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMesh* meshes, int* solverIter, double* solverErr) {
 	const int poly = P->wallType == 1;   /* order: src/main.cpp:256-456 */
 	oracle_update_buckets(P, A, B);
+	if (P->fluidType == 1) { oracle_calc_volume_fraction(P, A, B); oracle_calc_viscosity_interaction(P, A, B); }   /* src/main.cpp:259-262 */
 	oracle_calc_viscosity(P, A, B);
 	oracle_add_gravity(P, A);
 	oracle_predict(P, A);
@@ -1007,10 +1139,13 @@ void oracle_step(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMesh* mes
 	if (!poly) oracle_extrapolate_press(P, A, B);
 	if (P->gradientCorrection) oracle_correction_matrix(P, A, B);
 	oracle_press_gradient(P, A, B);
-	if (poly) { oracle_wall_press_gradient(P, A, B, P->velMax); oracle_wall_viscosity(P, A, B); }
+	if (poly) oracle_wall_press_gradient(P, A, B, P->velMax);
+	if (P->fluidType == 1) { oracle_calc_volume_fraction(P, A, B); oracle_calc_viscosity_interaction(P, A, B); }   /* src/main.cpp:387-390 (particle walls) */
+	if (poly) oracle_wall_viscosity(P, A, B);
 	P->velMax = oracle_correct(P, A);
 	oracle_check_out_domain(P, A);
 	if (P->shiftingType == 2) { oracle_shifting(P, A, B); if (poly) oracle_wall_shifting(P, A, B); }
 	if (!poly) oracle_update_wall_dummy_vel(P, A, B);
 	oracle_check_out_domain(P, A);
+	P->timeCurrent += P->timeStep;   /* src/main.cpp:460 */
 }

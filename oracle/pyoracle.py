@@ -48,7 +48,7 @@ def _ip(a):
 class Oracle:
     """One simulation on the CPU oracle: params (ParticleSystem), HostState, buckets, meshes."""
 
-    STAGES_PAB = ["calc_viscosity", "collisions", "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive",
+    STAGES_PAB = ["calc_volume_fraction", "calc_viscosity", "collisions", "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive",
                   "wall_pnd_diffusive", "mean_pnd_wall_dummy_surface", "extrapolate_press", "press_gradient", "wall_viscosity",
                   "shifting", "wall_shifting", "update_wall_dummy_vel", "initial_pnd", "mean_wall_pnd", "mean_pnd",
                   "mean_neigh_fluid_pnd"]
@@ -58,6 +58,7 @@ class Oracle:
         self.lib = ctypes.CDLL(build())
         L = self.lib
         L.oracle_correct.restype = ctypes.c_double
+        L.oracle_calc_viscosity_interaction.restype = ctypes.c_double
         L.oracle_wall_press_gradient.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double]
         L.oracle_set_threads(int(threads))
         self.ps = ps
@@ -105,6 +106,9 @@ class Oracle:
                 getattr(self.lib, "oracle_" + name)(ctypes.byref(self.P), self._A()); self._sync()
             return f
         raise AttributeError(name)
+
+    def calc_viscosity_interaction(self):
+        self.CFLvisc = float(self.lib.oracle_calc_viscosity_interaction(ctypes.byref(self.P), self._A(), ctypes.byref(self.B))); self._sync()
 
     def update_buckets(self):
         self.lib.oracle_update_buckets(ctypes.byref(self.P), self._A(), ctypes.byref(self.B))

@@ -73,7 +73,7 @@ static void dump_params(const Sim& s, const std::string& path) {
 	PD(domainMinX); PD(domainMinY); PD(domainMinZ); PD(domainMaxX); PD(domainMaxY); PD(domainMaxZ);
 	PI(domainTypeBC); PI(numBC); PI(limitTypeBC); PI(periodicDirectionX); PI(periodicDirectionY); PI(periodicDirectionZ);
 	PD(densityFluid); PD(densityWall); PD(KNM_VS1); PI(fluidType); PD(gravityX); PD(gravityY); PD(gravityZ);
-	PD(KNM_VS2); PD(DNS_FL1); PD(DNS_FL2); PD(DNS_SDT);
+	PD(KNM_VS2); PD(DNS_FL1); PD(DNS_FL2); PD(DNS_SDT); PD(PHI_1); PD(PHI_2); PD(cohes); PD(MEU0); PD(DG); PD(I0); PD(mm); PD(Cd); PD(VF_min); PD(VF_max); PI(Fraction_method);
 	PD(dim); PD(partDist); PD(timeStep); PD(timeSimulation); PI(iterOutput); PD(cflNumber); PI(weightType); PI(slipCondition);
 	PD(reS); PD(reL); PI(gradientType); PI(gradientCorrection); PD(relaxPress); PI(mpsType); PD(soundSpeed); PD(gamma);
 	PI(solverType); PD(alphaCompressibility); PD(relaxPND); PD(shiftingType); PD(dri); PD(coefA); PD(machNumber);
@@ -143,6 +143,12 @@ static void dump_state(const Sim& s, const std::string& path) {
 	if (s.ps->mpsType == calcPressType::IMPLICIT_PND || s.ps->mpsType == calcPressType::IMPLICIT_PND_DIVU) {
 		D.d("pressurePPE", p->pressurePPE.data(), n); D.d("sourceTerm", p->sourceTerm.data(), n);
 		double it[2] = { (double)s.pr->getSolverIter(), s.pr->getSolverError() }; D.d("solver", it, 2);
+	}
+	if (s.ps->fluidType == viscType::NON_NEWTONIAN) {
+		D.d("Cv", p->Cv, n); D.d("II", p->II, n); D.d("MEU_Y", p->MEU_Y, n); D.d("Inertia", p->Inertia, n); D.d("p_rheo_new", p->p_rheo_new, n);
+		D.d("p_smooth", p->p_smooth, n); D.d("VF", p->VF, n); D.d("S11", p->S11, n); D.d("S12", p->S12, n); D.d("S13", p->S13, n);
+		D.d("S22", p->S22, n); D.d("S23", p->S23, n); D.d("S33", p->S33, n);
+		double cv[1] = { s.ps->CFLvisc }; D.d("CFLvisc", cv, 1);
 	}
 	D.i("firstParticleInBucket", p->firstParticleInBucket, s.ps->numBucketsXYZ);
 	D.i("lastParticleInBucket", p->lastParticleInBucket, s.ps->numBucketsXYZ);

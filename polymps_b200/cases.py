@@ -41,7 +41,7 @@ class Case:
 def base_options(*, dim, lo, dt, wall_type, mps_type, c0=15.0, re_small=2.1, re_large=2.1, grad_type=3,
                  grad_corr=False, shifting=2, pnd_type=2, fs_type=1, fs_pnd=0.98, max_vel=4.0, gravity=(0.0, 0.0, -9.81),
                  dom_min=(0.0, 0.0, 0.0), dom_max=(1.0, 1.0, 1.0), final_time=1.0, solver=0, alpha=1e-6, relax_pnd=0.01,
-                 collision=0, slip=0, rep_type=2, weight_type=0, fs_neigh=0.85) -> dict:
+                 collision=0, slip=0, rep_type=2, weight_type=0, fs_neigh=0.85, fluid_type=0, rheo=None) -> dict:
     """A JSON document with the reference's key names (src/MpsInputOutput.cpp:134-505)."""
     return {
         "flags": {"wall_type": wall_type, "fem_MESH": False, "forced_MESH": False,
@@ -54,10 +54,10 @@ def base_options(*, dim, lo, dt, wall_type, mps_type, c0=15.0, re_small=2.1, re_
                       "pressTxt_file": "output/press.txt"},
         "domain": {"min": dict(zip("xyz", map(float, dom_min))), "max": dict(zip("xyz", map(float, dom_max))),
                    "boundary": {"type": 0, "limit": 0, "direction": {"x": False, "y": False, "z": False}}},
-        "physical": {"fluid_density": 1000.0, "wall_density": 1000.0, "kinematic_visc": 1e-6, "fluid_type": 0,
+        "physical": {"fluid_density": 1000.0, "wall_density": 1000.0, "kinematic_visc": 1e-6, "fluid_type": fluid_type,
                      "gravity": dict(zip("xyz", map(float, gravity))),
-                     "rheological": {"kinematic_visc_phase_2": 1e-6, "fluid_density_phase_1": 1000.0,
-                                     "fluid_density_phase_2": 1540.0, "sediment_density": 1540.0}},
+                     "rheological": dict({"kinematic_visc_phase_2": 1e-6, "fluid_density_phase_1": 1000.0,
+                                          "fluid_density_phase_2": 1540.0, "sediment_density": 1540.0}, **(rheo or {}))},
         "numerical": {
             "dimension": dim, "particle_dist": lo, "time_step": dt, "final_time": final_time, "iter_output": 1000000,
             "CFL_number": 0.2, "weight_type": weight_type, "slip_condition": slip,
@@ -182,6 +182,46 @@ def dam2d_particle(nx: int, nz: int, *, lo: float = 0.005, tank_nx: int | None =
     n = len(pos)
     return Case(name=name or ("dam2d_%s_%dx%d" % ("inc" if incompressible else "wc", nx, nz)), options=base_options(**kw),
                 ptype=ptype, pos=pos, vel=np.zeros((n, 3)), press=np.zeros(n), tris=None, meta={"H": H, "c0": c0})
+
+
+# rheological block of input/2D_dam_fraccarollo_lo02p50e-03_WC.json (BASELINE.json configs[0])
+FRACCAROLLO_RHEO = {"power_law_index": 1.2, "consistency_index": 0.03, "phi": {"lower": 0.4, "wall": 0.4, "bed": 0.4, "second": 0.611},
+                    "cohes_coeff": 0.0, "fraction_method": 2, "grain_size": 0.0035, "I0": 0.75, "mm": 300.0, "stress_calc_method": 1,
+                    "viscosity": {"iter_num": 1, "error": 0.0, "average": 0.0}, "drag_coeff": 0.47, "volume_fraction": {"min": 0.25, "max": 0.69}}
+
+
+def dam2d_erosion(nx: int, nz: int, bed: int, *, lo: float = 0.0025, tank_nx: int | None = None, tank_nz: int | None = None,
+                  jitter: float = 0.0, seed: int = 20261104, name: str | None = None, **overrides) -> Case:
+    """Erosional dam break over a mobile bed (Fraccarollo & Capart 2002; option set of input/2D_dam_fraccarollo_lo02p50e-03_WC.json:
+    2D, particle walls, WC-MPS, NON-NEWTONIAN two-phase rheology).  A sediment bed of `bed` layers (grid id 1: the reader turns
+    it into fluid particles of phase 2, src/MpsInputOutput.cpp:839-847) covers the tank floor; a water column of nx x nz
+    particles stands on its left end."""
+    tank_nx = tank_nx or int(round(nx * 2.5))
+    tank_nz = tank_nz or (bed + 2 * nz)
+    rng = np.random.default_rng(seed)
+    P, T = [], []
+    for jy in range(-3, tank_nz):
+        for ix in range(-3, tank_nx + 3):
+            inside = 0 <= ix < tank_nx and jy >= 0
+            x = ((ix + 0.5) * lo, (jy + 0.5) * lo, 0.0)
+            if inside:
+                t = 1 if jy < bed else (0 if (ix < nx and jy < bed + nz) else None)
+                if t is not None:
+                    if jitter > 0.0:
+                        d = rng.uniform(-jitter * lo, jitter * lo, size=2); x = (x[0] + d[0], x[1] + d[1], 0.0)
+                    P.append(x); T.append(t)
+                continue
+            layer = max(-ix, ix - tank_nx + 1, -jy)
+            P.append(x); T.append(2 if layer == 1 else 3)
+    pos = np.array(P); ptype = np.array(T, dtype=np.int32)
+    H = nz * lo
+    kw = dict(dim=2, lo=lo, dt=0.02 * lo, wall_type=0, mps_type=1, c0=20.0, re_small=2.1, re_large=3.1, gravity=(0.0, -9.81, 0.0),
+              grad_type=3, grad_corr=False, fs_type=0, fs_pnd=0.97, max_vel=4.0, shifting=2, pnd_type=2, fluid_type=1,
+              rheo=FRACCAROLLO_RHEO, dom_min=(-4 * lo, -4 * lo, 0.0), dom_max=((tank_nx + 4) * lo, (tank_nz + 1) * lo, 0.0))
+    kw.update(overrides)
+    n = len(pos)
+    return Case(name=name or "dam2d_erosion_%dx%d_%d" % (nx, nz, bed), options=base_options(**kw), ptype=ptype, pos=pos,
+                vel=np.zeros((n, 3)), press=np.zeros(n), tris=None, meta={"H": H})
 
 
 # ---------------------------------------------------------------------------------------------- files

@@ -179,6 +179,9 @@ static int alloc_view(pmps_handle* h, DevView& V, int n0, bool primary) {
 	PMPS_I32_FIELDS(X)
 	PMPS_F64_FIELDS(X)
 #undef X
+#define X(n) rc |= dalloc(h, &V.n, h->K.p.fluidType == 1 ? n0 : 1);
+	PMPS_RHEO_FIELDS(X)
+#undef X
 #define X(n) rc |= dalloc(h, &V.n.x, n0); rc |= dalloc(h, &V.n.y, n0); rc |= dalloc(h, &V.n.z, n0);
 	PMPS_V3_FIELDS(X)
 #undef X
@@ -198,7 +201,9 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	*out = nullptr;
 	if (params->abi_version != PMPS_ABI_VERSION) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: ABI version %d, library is %d", params->abi_version, PMPS_ABI_VERSION);
 	if (params->dim != 2 && params->dim != 3) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: dim must be 2 or 3");
-	if (params->fluidType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: non-Newtonian fluids are not on the device path yet (SURVEY 8f row 1)");
+	if (params->fluidType != 0 && params->fluidType != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: fluidType %d", params->fluidType);
+	if (params->fluidType == 1 && params->wallType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: the non-Newtonian rheology is on the device path for particle walls only (the polygon-wall variants, src/MpsViscosity.cpp:703-1526, are not: SURVEY 8f row 1)");
+	if (params->fluidType == 1 && params->fractionMethod != 1 && params->fractionMethod != 2) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: fractionMethod %d", params->fractionMethod);
 	if (params->domainTypeBC != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: periodic domain boundaries are not on the device path yet (SURVEY 8f row 4)");
 	if (params->freeSurfType == 2) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: ARC free-surface detection is not on the device path yet (SURVEY 8f row 4)");
 	if (params->collisionType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: DPC collisions are not on the device path yet (SURVEY 8f row 4)");
@@ -257,6 +262,13 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 		const size_t items = (size_t)(S.nC < n0 ? S.nC : n0) + 1;
 		rc |= dalloc(h, &S.tileList, items); rc |= dalloc(h, &S.itemMinD2, items); rc |= dalloc(h, &S.actList, 3 * items); rc |= dalloc(h, &S.actCount, 4); rc |= dalloc(h, &S.tileSparse, (size_t)h->nTilesAll + 1); S.actCap = (int32_t)items; rc |= dalloc(h, &S.tileClose, (size_t)h->nTilesAll + 1); rc |= dalloc(h, &S.itemTab, items * (size_t)K.tabStride); rc |= dalloc(h, &S.nTiles, 1); rc |= dalloc(h, &S.tileCursor, PMPS_CURSORS); rc |= dalloc(h, &S.tileWall, (size_t)h->nTilesAll + 1);
 		int sm = 148; cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device); h->smCount = sm;
+	}
+	{	// column maps of the rheology (src/MpsViscosity.cpp:236-238)
+		const double aa = 2.0 * K.p.partDist;
+		K.rheoKx = (int)((K.p.domainMaxX - K.p.domainMinX) / aa) + 1;
+		K.rheoKy = K.p.dim == 3 ? (int)((K.p.domainMaxY - K.p.domainMinY) / aa) + 1 : 1;
+		const size_t nc = K.p.fluidType == 1 ? (size_t)(K.rheoKx + 1) * (K.rheoKy + 1) : 1;
+		rc |= dalloc(h, &S.rheoBL, nc); rc |= dalloc(h, &S.rheoWL, nc); rc |= dalloc(h, &S.rheoIdx, nc); rc |= dalloc(h, &S.meuMaxBits, 1);
 	}
 	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 2); rc |= dalloc(h, &S.hitMove, 4); rc |= dalloc(h, &S.hitFlag, 2); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
 	// Verlet list: radius = bucketSide (the reference's own search slack, src/MpsBucket.cpp:23); capacity from the

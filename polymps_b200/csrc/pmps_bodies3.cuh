@@ -255,3 +255,4 @@ struct BWallDummyVel {
 		S.vel[s.i] = v;
 	}
 };
+#include "pmps_rheo.cuh"

@@ -59,6 +59,11 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 			PMPS_I32_FIELDS(X)
 			PMPS_F64_FIELDS(X)
 #undef X
+			if (K.p.fluidType == 1) {   // src/MpsParticle.cpp:322-337
+#define X(n) S.n[si] = S.n[sl];
+				PMPS_RHEO_FIELDS(X)
+#undef X
+			}
 #define X(n) S.n.x[si] = S.n.x[sl]; S.n.y[si] = S.n.y[sl]; S.n.z[si] = S.n.z[sl];
 			PMPS_V3_FIELDS(X)
 #undef X

@@ -18,6 +18,9 @@
 #define PMPS_F64_FIELDS(X) X(press) X(pndi) X(pndki) X(pndski) X(pndSmall) X(npcdDeviation2) X(concentration) \
 	X(velDivergence) X(diffusiveTerm) X(pndWallContribution) X(distParticleWall2) X(deviationDotPolygonNormal) \
 	X(RHO) X(MEU) X(pndAuxVar1) X(pndAuxVar2) X(pressurePPE) X(sourceTerm)
+// non-Newtonian fields (include/MpsParticle.h, allocated by the reference only when fluidType == 1, src/MpsInputOutput.cpp:729-744):
+// full-size planes only on handles created with fluidType 1, one element otherwise
+#define PMPS_RHEO_FIELDS(X) X(Cv) X(II) X(MEU_Y) X(Inertia) X(p_rheo_new) X(p_smooth) X(VF) X(S11) X(S12) X(S13) X(S22) X(S23) X(S33)
 #define PMPS_V3_FIELDS(X) X(acc) X(accStar) X(npcdDeviation) X(gradConcentration) X(correcMatrixRow1) \
 	X(correcMatrixRow2) X(correcMatrixRow3) X(particleAtWallPos) X(mirrorParticlePos) X(polygonNormal) X(forceWall) \
 	X(dvelCollision)
@@ -45,6 +48,7 @@ struct DevView {
 #undef X
 #define X(n) double* n;
 	PMPS_F64_FIELDS(X)
+	PMPS_RHEO_FIELDS(X)
 #undef X
 #define X(n) V3 n;
 	PMPS_V3_FIELDS(X)
@@ -78,6 +82,9 @@ struct DevView {
 	int32_t* itemTab;                    // per work item: precomputed halo table (K.tabStride ints, pmps_tv.cuh)
 	int32_t* tileCursor;                 // work-stealing cursors, one per walk launch of a step
 	uint8_t* tileWall;                   // per tile: some particle of the tile is near a polygon wall (set by the wall pass)
+	// rheology (pmps_rheo.cuh): bed level / water level per column of 2 lo x 2 lo (src/MpsViscosity.cpp:236-311) as order-preserving
+	// 64-bit keys, the host index of the particle that set the bed level (its pressure is PS), max(MEU) of the mixture particles
+	unsigned long long* rheoBL; unsigned long long* rheoWL; int32_t* rheoIdx; unsigned long long* meuMaxBits;
 };
 
 enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, NFLAGS = 8 };
@@ -100,6 +107,7 @@ struct KParams {
 	int32_t nTX, nTY, nTZ;        // tiles per axis
 	int32_t HVt, tabStride;       // halo buckets of a whole tile; ints per item table
 	int32_t tvMaxM;               // staged records a tile may need (smallest capacity over the passes): larger tiles are split
+	int32_t rheoKx, rheoKy;       // columns of the bed / water level maps (kx_max, ky_max of src/MpsViscosity.cpp:237-238)
 	double reMax2;       // max(reS, reL)^2: no predicate of the reference reaches farther
 	double mirrorFar2;   // a particle farther than this from every wall (distParticleWall2) cannot fail d2 < dm2 nor pass M(re): its mirror is skipped
 	double invReS, invReL;
@@ -134,6 +142,7 @@ struct pmps_handle {
 	double dispNow = 0.0, dispInc = 0.0, dispIncPrev = 0.0; int stepsSinceBuild = 0; bool needRebuild = true;   // displacement since the list build (step_begin's rebuild decision)
 	double lastShift = 0.0;              // largest shift of the last step's shifting passes
 	double* slabWork = nullptr; pmps_sum_fn slabSum = nullptr; pmps_refresh_fn slabRefresh = nullptr; void* slabUser = nullptr;   // pmps_slab_set_hooks
+	double meuMax = 0.0;                 // max MEU of the last rheology pass (CFLvisc)
 	bool slab = false;                   // slab mode: rebuilds and the step-end scalars are decided by the caller from GLOBAL maxima (pmps_slab.cu)
 	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
 	bool hitForce = false;               // positions were replaced from outside (upload): the next check rebuilds the hit list

@@ -202,6 +202,7 @@ int pmps_sort_and_list(pmps_handle* h) {
 		std::vector<std::pair<double**, double**>> planes;
 #define X(n) planes.push_back({ &S.n, &A.n });
 		PMPS_F64_FIELDS(X)
+		if (K.p.fluidType == 1) { PMPS_RHEO_FIELDS(X) }
 #undef X
 #define X(n) planes.push_back({ &S.n.x, &A.n.x }); planes.push_back({ &S.n.y, &A.n.y }); planes.push_back({ &S.n.z, &A.n.z });
 		PMPS_V3_FIELDS(X)

@@ -94,6 +94,7 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 #undef X
 #define X(n) if (a->n) { const double* x = (const double*)src(a->n, 8 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_f64, G, T, x, S.n, soh, n0); }
 	PMPS_F64_FIELDS(X)
+	if (h->K.p.fluidType == 1) { PMPS_RHEO_FIELDS(X) }
 #undef X
 #define X(n) if (a->n) { const double* x = (const double*)src(a->n, 24 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_v3, G, T, x, S.n, soh, n0); }
 	PMPS_V3_FIELDS(X)
@@ -138,6 +139,7 @@ static int download_impl(pmps_handle* h, PmpsHostArrays* a, bool deviceDst) {
 #undef X
 #define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_f64, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 8 * (size_t)n0); }
 	PMPS_F64_FIELDS(X)
+	if (h->K.p.fluidType == 1) { PMPS_RHEO_FIELDS(X) }
 #undef X
 #define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_v3, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 24 * (size_t)n0); }
 	PMPS_V3_FIELDS(X)

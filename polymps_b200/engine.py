@@ -19,7 +19,7 @@ from .state import HostState, PmpsHostArrays, PmpsScalars
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PMPS_LIB", os.path.join(HERE, "libpmps.so"))   # PMPS_LIB: an experimental build of the same library (A/B timing)
 
-STAGES = ["update_buckets", "calc_viscosity", "add_gravity", "predict", "check_out_domain", "collisions", "wall_closest_point",
+STAGES = ["update_buckets", "calc_volume_fraction", "calc_viscosity_interaction", "calc_viscosity", "add_gravity", "predict", "check_out_domain", "collisions", "wall_closest_point",
           "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive", "wall_pnd_diffusive", "update_pnd",
           "mean_pnd_wall_dummy_surface", "update_bc", "calc_press", "extrapolate_press", "press_gradient",
           "wall_press_gradient", "wall_viscosity", "correct", "shifting", "wall_shifting", "update_wall_dummy_vel",
@@ -27,7 +27,8 @@ STAGES = ["update_buckets", "calc_viscosity", "add_gravity", "predict", "check_o
 
 # reference method name -> stage call (src/main.cpp:256-456)
 REFERENCE_NAMES = {
-    "updateParticlesID": "update_buckets", "calcViscosity": "calc_viscosity", "addGravity": "add_gravity",
+    "updateParticlesID": "update_buckets", "calcVolumeFraction": "calc_volume_fraction",
+    "calcViscosityInteractionVal": "calc_viscosity_interaction", "calcViscosity": "calc_viscosity", "addGravity": "add_gravity",
     "predictionVelocityPosition": "predict", "checkParticleOutDomain": "check_out_domain",
     "checkParticleCollisions": "collisions", "closestPointPNDBoundaryAABB": "wall_closest_point", "calcWallNPCD": "wall_npcd",
     "correctionMatrix": "correction_matrix", "calcPndnNeighNPCD": "pnd_neigh_npcd", "calcPndDiffusiveTerm": "pnd_diffusive",
@@ -169,6 +170,9 @@ class Engine:
         if check:
             self._chk(rc)
         return s
+
+    def set_time(self, t: float):
+        self._chk(self.lib.pmps_set_time(self.h, ctypes.c_double(float(t))))
 
     def set_velmax(self, v: float):
         self._chk(self.lib.pmps_set_velmax(self.h, float(v)))

@@ -52,6 +52,11 @@ PmpsHostArrays host_arrays(MpsParticle* P) {
 	F(pos) F(vel) F(acc) F(accStar) F(npcdDeviation) F(gradConcentration) F(correcMatrixRow1) F(correcMatrixRow2) F(correcMatrixRow3)
 	F(particleAtWallPos) F(mirrorParticlePos) F(polygonNormal) F(forceWall) F(dvelCollision)
 #undef F
+	if (g_S && g_S->fluidType == viscType::NON_NEWTONIAN) {   // allocated only then (src/MpsInputOutput.cpp:729-744)
+#define F(n) a.n = P->n;
+		F(Cv) F(II) F(MEU_Y) F(Inertia) F(p_rheo_new) F(p_smooth) F(VF) F(S11) F(S12) F(S13) F(S22) F(S23) F(S33)
+#undef F
+	}
 	a.particleNearWall = reinterpret_cast<uint8_t*>(P->particleNearWall);   // C++ bool, one byte
 	if (P->pressurePPE.size() == P->numParticlesZero) { a.pressurePPE = P->pressurePPE.data(); a.sourceTerm = P->sourceTerm.data(); }
 	return a;
@@ -74,7 +79,9 @@ PmpsParams params_of(MpsParticleSystem* S) {
 	C(coeffViscMultiphase) C(coeffPressGrad) C(coeffPressEMPS) C(coeffPressWCMPS) C(coeffShifting1) C(coeffShifting2)
 	C(coeffPPE) C(coeffPPESource) C(distCollisionLimit2) C(restitutionCollision) C(lambdaCollision) C(betaPnd)
 	C(betaNeigh) C(delta2) C(velMax)
+	C(KNM_VS1) C(KNM_VS2) C(DNS_SDT) C(PHI_1) C(PHI_2) C(cohes) C(MEU0) C(DG) C(I0) C(mm) C(Cd) C(VF_min) C(VF_max) C(timeCurrent)
 #undef C
+	p.fractionMethod = S->Fraction_method;
 	for (int k = 0; k < 3; k++) p.uniformVelWall[k] = S->uniformVelWall[k];
 	return p;
 }
@@ -98,6 +105,7 @@ pmps_t* handle() {
 void pull_scalars() {   // what displayInfo and the host loop read
 	PmpsScalars s; CALL(pmps_get_scalars(g_h, &s));
 	g_P->numParticles = s.numParticles; g_S->velMax = s.velMax; g_S->CFLcurrent = s.CFLcurrent;
+	if (g_S->fluidType == viscType::NON_NEWTONIAN) g_S->CFLvisc = s.CFLvisc;
 }
 void pull_arrays() {    // before writeOutputFiles
 	PmpsHostArrays a = host_arrays(g_P);
@@ -136,6 +144,13 @@ void MpsParticle::checkParticleOutDomain(MpsParticleSystem *PSystem) {
 
 // ---- MpsViscosity (src/MpsViscosity.cpp:20-100, 1527-1910) -----------------------------------------------------------
 void MpsViscosity::calcViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_calc_viscosity(H(PSystem, Particles))); }
+// non-Newtonian rheology, particle walls (src/MpsViscosity.cpp:104-190, :194-700); the polygon-wall variants stay on the host side of the
+// boundary and are refused by pmps_create (fluidType 1 with wallType 1)
+void MpsViscosity::calcVolumeFraction(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_calc_volume_fraction(H(PSystem, Particles))); }
+void MpsViscosity::calcViscosityInteractionVal(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) {
+	CALL(pmps_set_time(H(PSystem, Particles), PSystem->timeCurrent));
+	CALL(pmps_calc_viscosity_interaction(H(PSystem, Particles)));
+}
 void MpsViscosity::calcWallSlipViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_viscosity(H(PSystem, Particles))); }
 void MpsViscosity::calcWallNoSlipViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_viscosity(H(PSystem, Particles))); }
 

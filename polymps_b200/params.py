@@ -64,6 +64,18 @@ class ParticleSystem:
     gravityY: float = 0.0
     gravityZ: float = -9.81
     KNM_VS2: float = 0.000001
+    DNS_SDT: float = 1540.0
+    MEU0: float = 0.03
+    PHI_1: float = 0.541
+    PHI_2: float = 0.6
+    cohes: float = 0.0
+    fractionMethod: int = 2
+    DG: float = 0.0035
+    I0: float = 0.75
+    mm: float = 100.0
+    Cd: float = 0.47
+    VF_min: float = 0.25
+    VF_max: float = 0.65
     DNS_FL1: float = 1000.0
     DNS_FL2: float = 1540.0
     dim: float = 3.0
@@ -214,6 +226,16 @@ class ParticleSystem:
         ps.KNM_VS2 = float(g(rh, "kinematic_visc_phase_2", 0.000001))
         ps.DNS_FL1 = float(g(rh, "fluid_density_phase_1", 1000.0))
         ps.DNS_FL2 = float(g(rh, "fluid_density_phase_2", 1540.0))
+        ps.DNS_SDT = float(g(rh, "sediment_density", 1540.0))
+        ps.MEU0 = float(g(rh, "consistency_index", 0.03))
+        phi = rh.get("phi", {})
+        ps.PHI_1 = float(g(phi, "lower", 0.541)); ps.PHI_2 = float(g(phi, "second", 0.6))
+        ps.cohes = float(g(rh, "cohes_coeff", 0.0))
+        ps.fractionMethod = int(g(rh, "fraction_method", 2))
+        ps.DG = float(g(rh, "grain_size", 0.0035)); ps.I0 = float(g(rh, "I0", 0.75)); ps.mm = float(g(rh, "mm", 100.0))
+        ps.Cd = float(g(rh, "drag_coeff", 0.47))
+        vf = rh.get("volume_fraction", {})
+        ps.VF_min = float(g(vf, "min", 0.25)); ps.VF_max = float(g(vf, "max", 0.65))
         nu = je.get("numerical", {})
         ps.dim = float(g(nu, "dimension", 3.0))
         ps.partDist = float(g(nu, "particle_dist", 0.01))
@@ -402,7 +424,7 @@ class PmpsParams(ctypes.Structure):
     _I = ["abi_version", "dim", "wallType", "mpsType", "solverType", "pndType", "weightType", "gradientType",
           "gradientCorrection", "slipCondition", "freeSurfType", "collisionType", "shiftingType", "repulsiveForceType",
           "fluidType", "domainTypeBC", "ghost", "fluid", "wall", "dummyWall", "surface", "inner", "other",
-          "numBucketsX", "numBucketsY", "numBucketsZ", "numOfMeshs", "shiftingJacobi", "_pad0"]
+          "numBucketsX", "numBucketsY", "numBucketsZ", "numOfMeshs", "shiftingJacobi", "_pad0", "fractionMethod"]
     _D = ["domainMinX", "domainMinY", "domainMinZ", "domainMaxX", "domainMaxY", "domainMaxZ", "bucketSide", "invBucketSide",
           "partDist", "timeStep", "epsilonZero", "reS", "reL", "reS2", "reL2", "gravityX", "gravityY", "gravityZ",
           "densityWall", "DNS_FL1", "DNS_FL2", "soundSpeed", "gamma", "relaxPress", "alphaCompressibility",
@@ -412,22 +434,23 @@ class PmpsParams(ctypes.Structure):
            "coeffPressGrad", "coeffPressEMPS", "coeffPressWCMPS", "coeffShifting1", "coeffShifting2", "coeffPPE",
            "coeffPPESource", "distCollisionLimit2", "restitutionCollision", "lambdaCollision", "betaPnd", "betaNeigh",
            "delta2", "velMax"]
+    _D3 = ["KNM_VS1", "KNM_VS2", "DNS_SDT", "PHI_1", "PHI_2", "cohes", "MEU0", "DG", "I0", "mm", "Cd", "VF_min", "VF_max", "timeCurrent"]
     _fields_ = ([(n, ctypes.c_int32) for n in _I] + [(n, ctypes.c_double) for n in _D]
-                + [("uniformVelWall", ctypes.c_double * 3)] + [(n, ctypes.c_double) for n in _D2])
+                + [("uniformVelWall", ctypes.c_double * 3)] + [(n, ctypes.c_double) for n in _D2 + _D3])
 
 
 def to_c_params(ps: ParticleSystem, shifting_jacobi: bool = True) -> PmpsParams:
     c = PmpsParams()
     for n in PmpsParams._I:
         if n == "abi_version":
-            c.abi_version = 1
+            c.abi_version = 2
         elif n == "shiftingJacobi":
             c.shiftingJacobi = 1 if shifting_jacobi else 0
         elif n == "_pad0":
             c._pad0 = 0
         else:
             setattr(c, n, int(getattr(ps, n)))
-    for n in PmpsParams._D + PmpsParams._D2:
+    for n in PmpsParams._D + PmpsParams._D2 + PmpsParams._D3:
         setattr(c, n, float(getattr(ps, n)))
     for k in range(3):
         c.uniformVelWall[k] = float(ps.uniformVelWall[k])

@@ -17,7 +17,9 @@ F64 = ["press", "pndi", "pndki", "pndski", "pndSmall", "npcdDeviation2", "concen
        "pressurePPE", "sourceTerm"]
 VEC = ["pos", "vel", "acc", "accStar", "npcdDeviation", "gradConcentration", "correcMatrixRow1", "correcMatrixRow2",
        "correcMatrixRow3", "particleAtWallPos", "mirrorParticlePos", "polygonNormal", "forceWall", "dvelCollision"]
-ALL_FIELDS = I32 + U8 + F64 + VEC
+# non-Newtonian fields (src/MpsInputOutput.cpp:729-744); transferred only by handles created with fluidType 1
+RHEO = ["Cv", "II", "MEU_Y", "Inertia", "p_rheo_new", "p_smooth", "VF", "S11", "S12", "S13", "S22", "S23", "S33"]
+ALL_FIELDS = I32 + U8 + F64 + VEC + RHEO
 
 
 class PmpsHostArrays(ctypes.Structure):
@@ -25,13 +27,14 @@ class PmpsHostArrays(ctypes.Structure):
                 + [(n, ctypes.POINTER(ctypes.c_int32)) for n in I32]
                 + [(n, ctypes.POINTER(ctypes.c_uint8)) for n in U8]
                 + [(n, ctypes.POINTER(ctypes.c_double)) for n in F64]
-                + [(n, ctypes.POINTER(ctypes.c_double)) for n in VEC])
+                + [(n, ctypes.POINTER(ctypes.c_double)) for n in VEC]
+                + [(n, ctypes.POINTER(ctypes.c_double)) for n in RHEO])
 
 
 class PmpsScalars(ctypes.Structure):
     _fields_ = [("numParticles", ctypes.c_int32), ("solverIter", ctypes.c_int32), ("velMax", ctypes.c_double),
                 ("CFLcurrent", ctypes.c_double), ("solverError", ctypes.c_double), ("maxDisplacement", ctypes.c_double),
-                ("outOfDomainEvents", ctypes.c_int32), ("maxBucketCount", ctypes.c_int32)]
+                ("outOfDomainEvents", ctypes.c_int32), ("maxBucketCount", ctypes.c_int32), ("CFLvisc", ctypes.c_double)]
 
 
 class HostState:
@@ -44,7 +47,7 @@ class HostState:
             setattr(self, f, np.zeros(n, dtype=np.int32))
         for f in U8:
             setattr(self, f, np.zeros(n, dtype=np.uint8))
-        for f in F64:
+        for f in F64 + RHEO:
             setattr(self, f, np.zeros(n, dtype=np.float64))
         for f in VEC:
             setattr(self, f, np.zeros(3 * n, dtype=np.float64))
@@ -57,11 +60,13 @@ class HostState:
         s.vel[:] = np.asarray(case.vel, dtype=np.float64).reshape(-1)
         s.press[:] = case.press
         s.distParticleWall2[:] = 10e8 * ps.partDist
-        if ps.fluidType != 0:
-            raise NotImplementedError("non-Newtonian fluids are out of scope this round (SURVEY §8f row 1)")
         s.RHO[:] = ps.DNS_FL1
         s.PTYPE[:] = 1
         s.MEU[:] = ps.KNM_VS1 * ps.DNS_FL1
+        if ps.fluidType == 1:   # grid id 1 = sediment: fluid particle of phase 2 (src/MpsInputOutput.cpp:839-856)
+            sed = s.particleType == 1
+            s.particleType[sed] = ps.fluid; s.PTYPE[sed] = 2
+            s.RHO[sed] = ps.DNS_FL2; s.MEU[sed] = ps.KNM_VS2 * ps.DNS_FL2
         return s
 
     @classmethod

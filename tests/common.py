@@ -17,11 +17,12 @@ from polymps_b200.mesh import PolygonMesh  # noqa: E402
 from polymps_b200.state import HostState, ALL_FIELDS, I32, U8  # noqa: E402
 from make_golden import load_golden  # noqa: E402
 
-GOLDEN = ["w3", "w3j", "i3", "w2", "i2"]
+GOLDEN = ["w3", "w3j", "i3", "w2", "i2", "n2"]
 
 # ref_driver stage name -> stage calls (oracle method names == engine method names)
 STAGE_MAP = {
-    "updateParticlesID": ["update_buckets"], "calcViscosity": ["calc_viscosity"], "addGravity": ["add_gravity"],
+    "updateParticlesID": ["update_buckets"], "nonNewtonian1": ["calc_volume_fraction", "calc_viscosity_interaction"],
+    "nonNewtonian2": ["calc_volume_fraction", "calc_viscosity_interaction"], "calcViscosity": ["calc_viscosity"], "addGravity": ["add_gravity"],
     "predictionVelocityPosition": ["predict"], "checkParticleOutDomain1": ["check_out_domain"], "collisions": ["collisions"],
     "wallClosestPoint": ["wall_closest_point"], "calcWallNPCD": ["wall_npcd"], "correctionMatrix1": ["correction_matrix"],
     "calcPndnNeighNPCD": ["pnd_neigh_npcd"], "calcPndDiffusiveTerm": ["pnd_diffusive"], "calcWallPndDiffusiveTerm": ["wall_pnd_diffusive"],

@@ -23,14 +23,14 @@ def test_library_exports_every_declared_symbol():
     assert len(syms) >= 45
     missing = [s for s in syms if not hasattr(lib, s)]
     assert not missing, missing
-    assert lib.pmps_abi_version() == 1
+    assert lib.pmps_abi_version() == 2
 
 
 def test_struct_layouts_match_header():
-    # sizes computed from the header: 29 int32 + (30 + 3 + 20) doubles; 2 int32 + 46 pointers
-    assert ctypes.sizeof(PmpsParams) == 29 * 4 + 4 + 53 * 8 or ctypes.sizeof(PmpsParams) == 29 * 4 + 53 * 8 + 4
-    assert ctypes.sizeof(PmpsHostArrays) == 8 + 8 * (7 + 1 + 18 + 14)
-    assert ctypes.sizeof(PmpsScalars) == 48
+    # sizes computed from the header: 30 int32 + (30 + 3 + 20 + 14) doubles; 2 int32 + 53 pointers
+    assert ctypes.sizeof(PmpsParams) == 30 * 4 + 67 * 8
+    assert ctypes.sizeof(PmpsHostArrays) == 8 + 8 * (7 + 1 + 18 + 14 + 13)
+    assert ctypes.sizeof(PmpsScalars) == 56
 
 
 def test_create_fails_loudly_without_gpu_or_with_bad_params():
