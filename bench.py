@@ -206,7 +206,7 @@ def main_gpu_slab(args, rank, world, local):
     from polymps_b200.slab import SlabEngine, choose_cuts, TABLE_FIELDS, field_width, field_dtype
 
     kN = int(round(args.k * world ** (1.0 / 3.0)))
-    case = cases.dam3d_block_options(kN)
+    case = cases.dam3d_block_options(kN, incompressible=args.scheme == "inc")
     ps = ParticleSystem.from_json(case.options).set_parameters(); ps.allocate_buckets(None)
     meshes = [PolygonMesh.from_triangles(case.tris).init_wall_tables(int(ps.dim), ps.weightType, ps.partDist, ps.reL, ps.reS)]
     nx, ny, nz = 2 * kN, kN, kN; lo = ps.partDist
@@ -279,9 +279,11 @@ def main_gpu_slab(args, rank, world, local):
     dist.all_gather_object(per_rank, {"owned": n_own, "halo": se.dom.n_live - n_own, "ms_per_step": ms_local / args.steps,
                                       "repartitions": st1["repartitions"] - st0["repartitions"], "migrants_out": st1["migrants_out"] - st0["migrants_out"],
                                       "halo_refresh_MB_per_step": (st1["refresh_bytes"] - st0["refresh_bytes"]) / args.steps / 1e6})
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+    inc = args.scheme == "inc"
+    line = {"metric": METRIC if not inc else "particle-steps/sec (3D INC dam break: PPE assembly + Jacobi-CG)", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "synthetic 3D WC dam-break block %dx%dx%d = %d particles over %d GPUs (%.2fM per GPU), STL polygon tank (10 triangles), InputDamWC option set" % (nx, ny, nz, int(total), world, total / world / 1e6),
+            "config": {"workload": "synthetic 3D %s dam-break block %dx%dx%d = %d particles over %d GPUs (%.2fM per GPU), STL polygon tank (10 triangles), %s option set" % ("INC" if inc else "WC", nx, ny, nz, int(total), world, total / world / 1e6, "InputDamINC" if inc else "InputDamWC"),
+                       "cg_iterations_last_step": sc.solverIter if inc else None,
                        "particles_total": int(total), "parallelism": "%d x-slabs cut on bucket columns, one rank per GPU; halo refresh after every phase + migration at rebuilds over NCCL send/recv; 3 scalars MAX-all-reduced per step" % world,
                        "l2": "state per GPU (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (se.dom.n_live * 1500 / 1e9),
                        "ranks": per_rank, "max_displacement_over_lo": sc.maxDisplacement / ps.partDist},

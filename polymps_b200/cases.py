@@ -140,13 +140,15 @@ def dam3d_block_columns(k: int, i0: int, i1: int, *, lo: float = 0.01):
             "gid": (m * ny + j) * nx + i}
 
 
-def dam3d_block_options(k: int, *, lo: float = 0.01) -> Case:
+def dam3d_block_options(k: int, *, lo: float = 0.01, incompressible: bool = False) -> Case:
     """dam3d_block(k) without particles: options, tank mesh and meta only."""
     c = dam3d(1, 1, 1, lo=lo)   # a one-particle case just for the key set
     nx, ny, nz = 2 * k, k, k
     H = nz * lo; tank = ((1.61 / 0.6) * nx * lo, ny * lo, 2.0 * nz * lo); c0 = 15.0 * math.sqrt(H / 0.3)
     kw = dict(dim=3, lo=lo, dt=0.375 * lo / c0, wall_type=1, c0=c0, max_vel=2.0 * math.sqrt(9.81 * H), dom_min=(0.0, 0.0, 0.0),
               dom_max=tank, mps_type=1, grad_type=3, grad_corr=False, shifting=2, pnd_type=2)
+    if incompressible:   # InputDamINC, as dam3d(..., incompressible=True)
+        kw.update(mps_type=2, grad_type=0, grad_corr=True, shifting=0, pnd_type=0, dt=2.0 * kw["dt"])
     return Case(name="block%d" % k, options=base_options(**kw), ptype=np.zeros(0, dtype=np.int32), pos=np.zeros((0, 3)), vel=np.zeros((0, 3)),
                 press=np.zeros(0), tris=box_triangles(*tank).astype(np.float32).astype(np.float64), meta={"tank": tank, "H": H, "c0": c0})
 
