@@ -87,7 +87,7 @@ struct DevView {
 	unsigned long long* rheoBL; unsigned long long* rheoWL; int32_t* rheoIdx; unsigned long long* meuMaxBits;
 };
 
-enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, NFLAGS = 8 };
+enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, FLAG_UPLOAD_TYPES = 7, NFLAGS = 8 };
 #define PMPS_OOD_CAP 65536
 #define PMPS_CURSORS 64   // work-stealing cursors per step (one per tile-walker launch)
 

@@ -33,6 +33,20 @@ __global__ void k_up_pack(const double* __restrict__ xyz, const int32_t* __restr
 	dst[s] = r;
 }
 
+// positions replaced from the host while a bucket order and its lists exist: the same bookkeeping as a position update inside a
+// step (displacement from the build / hit-list positions), plus a flag when a type word changes — then the caller rebuilds
+__global__ void k_up_pos_soft(const double* __restrict__ xyz, const int32_t* __restrict__ type, const int32_t* __restrict__ ptype,
+                              const __grid_constant__ DevView S, const __grid_constant__ KParams K, int n0) {
+	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
+	const int s = S.slotOfHost[hI];
+	const double4 old = S.pos[s]; double4 r = old;
+	r.x = xyz[3 * (size_t)hI]; r.y = xyz[3 * (size_t)hI + 1]; r.z = xyz[3 * (size_t)hI + 2];
+	if (type || ptype) r.w = pk_make(type ? type[hI] : pk_type(r), ptype ? ptype[hI] : pk_ptype(r));
+	if (__double_as_longlong(r.w) != __double_as_longlong(old.w)) S.flags[FLAG_UPLOAD_TYPES] = 1;
+	S.pos[s] = r;
+	if (pk_type(r) != K.p.ghost) track_disp(S, K, s, r);
+}
+
 __global__ void k_dn_f64(double* dst, const double* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
 	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
 	dst[hI] = src[slotOfHost[hI]];
@@ -81,11 +95,14 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 		cudaMemcpyAsync(st + off, p, bytes, cudaMemcpyHostToDevice, h->stream);
 		return st + off;
 	};
+	bool soft = false;
 	if (a->pos || a->particleType || a->PTYPE) {
 		const double* x = (const double*)src(a->pos, 24 * (size_t)n0, 0);
 		const int32_t* t = (const int32_t*)src(a->particleType, 4 * (size_t)n0, 24 * (size_t)n0);
 		const int32_t* pt = (const int32_t*)src(a->PTYPE, 4 * (size_t)n0, 28 * (size_t)n0);
-		LAUNCH(h, "upload", k_up_pack, G, T, x, t, pt, S.pos, soh, n0);
+		soft = a->pos && h->haveList && !h->slab && a->numParticles == h->numParticles && !getenv("PMPS_HARD_UPLOAD");
+		if (soft) { cudaMemsetAsync(&S.flags[FLAG_UPLOAD_TYPES], 0, sizeof(int32_t), h->stream); LAUNCH(h, "upload", k_up_pos_soft, G, T, x, t, pt, S, h->K, n0); }
+		else LAUNCH(h, "upload", k_up_pack, G, T, x, t, pt, S.pos, soh, n0);
 	}
 	if (a->vel) { const double* x = (const double*)src(a->vel, 24 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_pack, G, T, x, (const int32_t*)nullptr, (const int32_t*)nullptr, S.vel, soh, n0); }
 	if (a->particleNearWall) { const uint8_t* x = (const uint8_t*)src(a->particleNearWall, (size_t)n0, 0); LAUNCH(h, "upload", k_up_u8, G, T, x, S.particleNearWall, soh, n0); }
@@ -103,7 +120,18 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 	CUDA_TRY(h, cudaGetLastError());
 	h->numParticles = a->numParticles; h->haveState = true;
 	if (a->particleNearWall) h->tileWallValid = false;
-	if (a->pos) { h->hitValid = false; h->hitForce = true; h->needRebuild = true; }   // new positions: the next fused step re-sorts and rebuilds the lists
+	if (a->pos && soft) {
+		// the bucket order and the candidate lists survive an upload that moves nobody beyond their guards (a host-driven loop
+		// that sends back the positions it received): the displacement trackers decide, exactly as inside a step
+		float md = 0.f;
+		CUDA_TRY(h, cudaMemcpyAsync(h->h_flags, S.flags, sizeof(int32_t) * NFLAGS, cudaMemcpyDeviceToHost, h->stream));
+		CUDA_TRY(h, cudaMemcpyAsync(&md, S.maxDisp2, sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+		CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+		h->hitValid = false;
+		if (h->h_flags[FLAG_UPLOAD_TYPES]) soft = false;
+		else h->dispNow = fmax(h->dispNow, sqrt((double)md));
+	}
+	if (a->pos && !soft) { h->hitValid = false; h->hitForce = true; h->needRebuild = true; }   // new positions: the next fused step re-sorts and rebuilds the lists
 	return PMPS_OK;
 }
 

@@ -2,6 +2,8 @@
 polymps_b200.engine); the checker is (a) the committed golden dumps of the unmodified reference and (b) the CPU oracle
 on seeded inputs.  Tolerances: integer / index / flag fields and neighbour SETS bit-exact; floating-point fields
 1e-10 relative to the field's max magnitude (BASELINE.json north_star)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -228,3 +230,39 @@ def test_errors_are_loud():
     with pytest.raises(PmpsError):
         eng.calc_viscosity()          # buckets not built
     eng.close()
+
+
+@pytest.mark.gpu
+def test_host_driven_loop_keeps_lists_and_results():
+    """upload -> step -> download every step (the e2e pattern of bench.py): sending back the positions just received must not
+    force a re-sort (the displacement trackers decide, pmps_transfer.cu), and the run must equal the device-resident run bit for
+    bit (same slot order, same candidate lists => same summation order).  A changed particle type does force the rebuild."""
+    case = cases.dam3d(16, 8, 12, jitter=0.04, name="e2e")
+    ps, meshes, st0 = _build(case)
+    a = _engine(ps, meshes, st0.numParticlesZero); a.upload(st0); a.init_step0(); a.step(8)
+    sa = st0.copy(); a.download(sa)
+    b = _engine(ps, meshes, st0.numParticlesZero); b.upload(st0); b.init_step0()
+    sb = st0.copy(); b.download(sb)
+    l0 = b.launch_count()
+    for _ in range(8):
+        b.upload(sb); b.step(1); b.download(sb)
+    per_step = (b.launch_count() - l0) / 8.0
+    assert np.array_equal(sa.pos, sb.pos) and np.array_equal(sa.vel, sb.vel) and np.array_equal(sa.press, sb.press)
+    # a forced rebuild per step launches the sort + list build (>= 12 kernels) on top of the step and the transfers
+    b2 = _engine(ps, meshes, st0.numParticlesZero); b2.upload(st0); b2.init_step0(); s2 = st0.copy(); b2.download(s2)
+    os.environ["PMPS_HARD_UPLOAD"] = "1"
+    try:
+        l0 = b2.launch_count()
+        for _ in range(8):
+            b2.upload(s2); b2.step(1); b2.download(s2)
+        hard = (b2.launch_count() - l0) / 8.0
+    finally:
+        del os.environ["PMPS_HARD_UPLOAD"]
+    assert per_step < hard - 8, (per_step, hard)
+    assert not compare_states(s2, sa, rtol=1e-9, skip=NOISY, scales=natural_scales(ps))
+    # a particle turned into a ghost on the host: the upload notices the changed type word and the next step rebuilds
+    sb.particleType[5] = ps.ghost
+    b.upload(sb); b.step(1); b.download(sb)
+    assert sb.particleType[5] == ps.ghost and b.scalars().numParticles == sb.numParticles
+    for e in (a, b, b2):
+        e.close()
