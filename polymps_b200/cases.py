@@ -32,6 +32,8 @@ class Case:
     press: np.ndarray                  # (N,)
     tris: np.ndarray | None = None     # (nF,3,3) rigid mesh triangles (polygon walls)
     meta: dict = field(default_factory=dict)
+    deformable_tris: np.ndarray | None = None   # mesh 1 (fem_MESH) and mesh 2 (forced_MESH, moved by the host every step):
+    forced_tris: np.ndarray | None = None       # src/main.cpp:471-493 reads them in this order
 
     @property
     def n(self) -> int:
@@ -186,6 +188,18 @@ def dam2d_particle(nx: int, nz: int, *, lo: float = 0.005, tank_nx: int | None =
                 ptype=ptype, pos=pos, vel=np.zeros((n, 3)), press=np.zeros(n), tris=None, meta={"H": H, "c0": c0})
 
 
+def slosh3d(nx: int, ny: int, nz: int, *, lo: float = 0.0093, name: str | None = None, jitter: float = 0.0, **overrides) -> Case:
+    """Sloshing tank with MOVING polygon walls (option set of input/sloshing_3D_bulian_lo0p00930.json, BASELINE configs[3]):
+    three meshes as in the reference input — rigid and deformable are single far-away triangles, the tank is the FORCED mesh
+    that PolygonMesh::updateForcedPolygonMesh rotates about (0.45, 0) every step (src/PolygonMesh.cpp:174-366)."""
+    tank = (0.9, ny * lo, 2.5 * nz * lo)
+    c = dam3d(nx, ny, nz, lo=lo, tank=tank, jitter=jitter, name=name or "slosh3d", offset=(0.45 - 0.5 * nx * lo, 0.0, 0.0), **overrides)
+    far = np.array([[[0.0, 0.0, -9.0], [0.01, 0.0, -9.0], [0.0, 0.01, -9.0]]])
+    c.forced_tris = c.tris; c.tris = far; c.deformable_tris = far + np.array([0.0, 0.0, -1.0])
+    c.options["flags"].update(fem_MESH=True, forced_MESH=True)
+    return c
+
+
 # rheological block of input/2D_dam_fraccarollo_lo02p50e-03_WC.json (BASELINE.json configs[0])
 FRACCAROLLO_RHEO = {"power_law_index": 1.2, "consistency_index": 0.03, "phi": {"lower": 0.4, "wall": 0.4, "bed": 0.4, "second": 0.611},
                     "cohes_coeff": 0.0, "fraction_method": 2, "grain_size": 0.0035, "I0": 0.75, "mm": 300.0, "stress_calc_method": 1,
@@ -256,6 +270,10 @@ def write_case(case: Case, root: str) -> str:
     write_grid(os.path.join(root, opts["pathNames"]["particle_grid_file"]), case.ptype, case.pos, case.vel, case.press)
     if case.tris is not None:
         write_binary_stl(os.path.join(root, opts["pathNames"]["mesh_rigid_file"]), case.tris)
+    for key, tris in (("mesh_deformable_file", case.deformable_tris), ("mesh_forced_file", case.forced_tris)):
+        if tris is not None:
+            opts["pathNames"][key] = "input/stl/%s_%s.stl" % (case.name, key.split("_")[1])
+            write_binary_stl(os.path.join(root, opts["pathNames"][key]), tris)
     jp = os.path.join(root, "input", case.name + ".json")
     with open(jp, "w") as fh:
         json.dump(opts, fh, indent=1)

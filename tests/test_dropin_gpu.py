@@ -35,7 +35,7 @@ def _run(binary, root, name, threads=1):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kind", ["wc3d", "inc3d", "wc2d", "nn2d"])
+@pytest.mark.parametrize("kind", ["wc3d", "inc3d", "wc2d", "nn2d", "slosh3d"])
 def test_unmodified_main_with_shim_matches_stock_reference(kind):
     if not (os.path.isfile(REF_BIN) and os.path.isfile(GPU_BIN)):
         pytest.skip("drop-in binaries not built (they need the reference tree at build time)")
@@ -43,6 +43,8 @@ def test_unmodified_main_with_shim_matches_stock_reference(kind):
         case = cases.dam3d(14, 7, 10, jitter=0.05, name="dropin", shifting=0)
     elif kind == "inc3d":
         case = cases.dam3d(12, 6, 8, jitter=0.03, incompressible=True, name="dropin")
+    elif kind == "slosh3d":   # BASELINE configs[3]: three meshes, the tank is the forced mesh the host rotates every step
+        case = cases.slosh3d(30, 6, 8, jitter=0.03, name="dropin", shifting=0)
     elif kind == "nn2d":   # BASELINE configs[0]: 2D erosional dam break, non-Newtonian rheology (rheology arrays written to the .vtu)
         case = cases.dam2d_erosion(20, 20, 8, jitter=0.03, name="dropin", shifting=0)
         case.options["flags"]["output_VTU"].update(non_newtonian=True, auxiliar=True)
