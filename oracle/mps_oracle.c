@@ -900,8 +900,55 @@ int oracle_solve_ppe(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, 
 		if (!dd_) t_ += diag[c_] * (v)[c_]; (y)[c_] = t_; } } while (0)
 	double *r = (double*)malloc(sizeof(double) * N), *p = (double*)malloc(sizeof(double) * N), *z = (double*)malloc(sizeof(double) * N), *t = (double*)malloc(sizeof(double) * N);
 	int iters = 0; double err = 0.0;
-	SPMV_T(t, x);
 	double rhs2 = 0.0, res2 = 0.0;
+	if (P->solverType == 1) {
+		/* BiCGSTAB multiplies by A itself (Eigen BiCGSTAB.h:29-107; Jacobi preconditioner, tolerance DBL_EPSILON, maxIt 2N, warm start).
+		 * The triplets are in row order (i ascends in the assembly loop): row-compressed A straight from them. */
+		int* rs = (int*)calloc((size_t)N + 1, sizeof(int));
+		for (int k = 0; k < nnz; k++) rs[ti[k] + 1]++;
+		for (int i = 0; i < N; i++) rs[i + 1] += rs[i];
+#define SPMV_A(y, v) do { for (int r_ = 0; r_ < N; r_++) { double t_ = diag[r_] * (v)[r_]; for (int s_ = rs[r_]; s_ < rs[r_ + 1]; s_++) t_ += tv[s_] * (v)[tj[s_]]; (y)[r_] = t_; } } while (0)
+#define DOT(a, c, out) do { double d_ = 0.0; for (int i_ = 0; i_ < N; i_++) d_ += (a)[i_] * (c)[i_]; (out) = d_; } while (0)
+#define DINV(i) (diag[i] != 0.0 ? 1.0 / diag[i] : 1.0)
+		double *r0 = (double*)malloc(sizeof(double) * N), *v = (double*)calloc(N, sizeof(double)), *sv = (double*)malloc(sizeof(double) * N), *y = (double*)malloc(sizeof(double) * N);
+		for (int i = 0; i < N; i++) p[i] = 0.0;
+		SPMV_A(t, x);
+		for (int i = 0; i < N; i++) { r[i] = b[i] - t[i]; r0[i] = r[i]; }
+		double r0n; DOT(r0, r0, r0n); DOT(b, b, rhs2);
+		if (rhs2 == 0.0) { for (int i = 0; i < N; i++) x[i] = 0.0; iters = 2 * N; err = DBL_EPSILON; }
+		else {
+			double rho = 1.0, alpha = 1.0, w = 1.0; const double tol2 = DBL_EPSILON * DBL_EPSILON * rhs2, eps2 = DBL_EPSILON * DBL_EPSILON;
+			const int maxIt = 2 * N; int restarts = 0;
+			DOT(r, r, res2);
+			while (res2 > tol2 && iters < maxIt) {
+				const double rho_old = rho;
+				DOT(r0, r, rho);
+				if (fabs(rho) < eps2 * r0n) {
+					SPMV_A(t, x);
+					for (int i = 0; i < N; i++) { r[i] = b[i] - t[i]; r0[i] = r[i]; }
+					DOT(r, r, rho); r0n = rho;
+					if (restarts++ == 0) iters = 0;
+				}
+				const double beta = (rho / rho_old) * (alpha / w);
+				for (int i = 0; i < N; i++) { p[i] = r[i] + beta * (p[i] - w * v[i]); y[i] = DINV(i) * p[i]; }
+				SPMV_A(v, y);
+				double r0v; DOT(r0, v, r0v); alpha = rho / r0v;
+				for (int i = 0; i < N; i++) { sv[i] = r[i] - alpha * v[i]; z[i] = DINV(i) * sv[i]; }
+				SPMV_A(t, z);
+				double tt, ts; DOT(t, t, tt); DOT(t, sv, ts);
+				w = tt > 0.0 ? ts / tt : 0.0;
+				for (int i = 0; i < N; i++) { x[i] += alpha * y[i] + w * z[i]; r[i] = sv[i] - w * t[i]; }
+				DOT(r, r, res2);
+				++iters;
+			}
+			err = sqrt(res2 / rhs2);
+		}
+#undef SPMV_A
+#undef DOT
+#undef DINV
+		free(rs); free(r0); free(v); free(sv); free(y);
+	} else {
+	SPMV_T(t, x);
 	for (int i = 0; i < N; i++) { r[i] = b[i] - t[i]; rhs2 += b[i] * b[i]; }
 	if (rhs2 == 0.0) { for (int i = 0; i < N; i++) x[i] = 0.0; iters = 0; err = 0.0; }
 	else {
@@ -926,6 +973,7 @@ int oracle_solve_ppe(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, 
 			}
 		}
 		err = sqrt(res2 / rhs2);
+	}
 	}
 #undef SPMV_T
 	for (int i = 0; i < N; i++) { A->press[i] = x[i]; if (A->press[i] < 0) A->press[i] = 0.0; }

@@ -155,6 +155,7 @@ struct pmps_handle {
 	std::vector<std::pair<void*, size_t>> registered;   // host ranges pinned with cudaHostRegister
 	// PPE workspace
 	uint32_t* ppe_col = nullptr; uint16_t* ppe_cnt = nullptr;
+	double* ppe_bicg[5] = { nullptr, nullptr, nullptr, nullptr, nullptr };   // r0, v, s, y, z of the BiCGSTAB solver
 	double *ppe_val = nullptr, *ppe_diag = nullptr, *ppe_r = nullptr, *ppe_p = nullptr, *ppe_t = nullptr;
 	double *ppe_partial = nullptr, *ppe_scal = nullptr, *ppe_host = nullptr;
 	// profiling

@@ -22,11 +22,12 @@ struct PpeView {
 	uint32_t* col; double* val; uint16_t* cnt;   // A^T, compacted ELL in the candidate-list layout
 	double* diag; double* r; double* p; double* t;
 	double* partial;   // [3][nBlocks] block partial sums
-	double* scal;      // 0 rhs2, 1 res2, 2 absNew, 3 absOld, 4 pt, 5 alpha, 6 beta, 7 thr
+	double* scal;      // 0 rhs2, 1 res2, 2 absNew, 3 absOld, 4 pt, 5 alpha, 6 beta, 7 thr ; BiCGSTAB: 2 rho, 3 rho_old, 5 alpha, 6 beta, 11 w, 12 |r0|^2 (8, 9 hold the reduced sums)
+	double* r0; double* v; double* s; double* y; double* z;   // BiCGSTAB work vectors (r, p, t above are shared with CG)
 };
 
 template <bool POLY>
-__global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ DevView S, const __grid_constant__ KParams K, const __grid_constant__ PpeView M) {
+__global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ DevView S, const __grid_constant__ KParams K, const __grid_constant__ PpeView M, int rowsOfA) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= S.n) return;
 	const double4 pi = S.pos[i]; const int ti = pk_type(pi);
@@ -53,8 +54,12 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ 
 			if (tj == K.p.dummyWall) b -= K.p.coeffPPE * (S.RHO[j] * (rx * K.p.gravityX + ry * K.p.gravityY + rz * K.p.gravityZ) * wL);
 			else sum -= a;
 		}
+		// BiCGSTAB multiplies by A itself (BiCGSTAB.h:81,88): row i of A = the entries row i's own predicate admits (:220-228)
+		if (rowsOfA) {
+			if (mine && tj != K.p.dummyWall && S.particleBC[j] == K.p.inner) { C[(size_t)nz * 32] = (uint32_t)j; V[(size_t)nz * 32] = a; nz++; }
+		}
 		// column i of row j: A_ji exists if row j is active, i is a real neighbour of j, i is not a dummy and BC[i] == inner
-		if (colOK) {
+		else if (colOK) {
 			const int bcj = S.particleBC[j];
 			bool theirs = !(bcj == K.p.other || bcj == K.p.surface);
 			if (POLY && theirs) {
@@ -179,6 +184,82 @@ __global__ void k_ppe_finish(const __grid_constant__ DevView S, const __grid_con
 	S.press[i] = x < 0 ? 0.0 : x;
 }
 
+// ---- BiCGSTAB (Eigen BiCGSTAB.h:29-107 with the Jacobi preconditioner, BasicPreconditioners.h:67-91) ---------------------------
+__device__ __forceinline__ double jacobi(const PpeView& M, int i) { const double d = M.diag[i]; return d != 0.0 ? 1.0 / d : 1.0; }
+// r0 = r ; p = v = 0   (after residual0, and at a restart)
+__global__ void __launch_bounds__(PPE_T) k_bicg_start(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int clearPV) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	M.r0[i] = M.r[i];
+	if (clearPV) { M.p[i] = 0.0; M.v[i] = 0.0; }
+}
+// p = r + beta (p - w v) ; y = M^-1 p
+__global__ void __launch_bounds__(PPE_T) k_bicg_p(const __grid_constant__ DevView S, const __grid_constant__ PpeView M) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const double beta = M.scal[6], w = M.scal[11];
+	const double p = M.r[i] + beta * (M.p[i] - w * M.v[i]);
+	M.p[i] = p; M.y[i] = jacobi(M, i) * p;
+}
+// out = A in ; partial sums: which 0: r0.out   1: |out|^2 and out.s
+__global__ void __launch_bounds__(PPE_T) k_bicg_spmv(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks, int which) {
+	__shared__ double sh[PPE_T / 32];
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	double a = 0.0, b = 0.0;
+	if (i < S.n) {
+		const double o = ell_row_dot(S, M, i, which == 0 ? M.y : M.z);
+		if (which == 0) { M.v[i] = o; if (owned_slot(S, i)) a = M.r0[i] * o; }
+		else { M.t[i] = o; if (owned_slot(S, i)) { a = o * o; b = o * M.s[i]; } }
+	}
+	const double sa = block_sum<PPE_T>(a, sh); const double sb = block_sum<PPE_T>(b, sh);
+	if (threadIdx.x == 0) { M.partial[blockIdx.x] = sa; M.partial[nBlocks + blockIdx.x] = sb; }
+}
+// s = r - alpha v ; z = M^-1 s
+__global__ void __launch_bounds__(PPE_T) k_bicg_s(const __grid_constant__ DevView S, const __grid_constant__ PpeView M) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	const double s = M.r[i] - M.scal[5] * M.v[i];
+	M.s[i] = s; M.z[i] = jacobi(M, i) * s;
+}
+// x += alpha y + w z ; r = s - w t ; partial sums of |r|^2 and r0.r
+__global__ void __launch_bounds__(PPE_T) k_bicg_xr(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks) {
+	__shared__ double sh[PPE_T / 32];
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	double a = 0.0, b = 0.0;
+	if (i < S.n) {
+		const double alpha = M.scal[5], w = M.scal[11];
+		S.pressurePPE[i] += alpha * M.y[i] + w * M.z[i];
+		const double r = M.s[i] - w * M.t[i]; M.r[i] = r;
+		if (owned_slot(S, i)) { a = r * r; b = M.r0[i] * r; }
+	}
+	const double sa = block_sum<PPE_T>(a, sh); const double sb = block_sum<PPE_T>(b, sh);
+	if (threadIdx.x == 0) { M.partial[blockIdx.x] = sa; M.partial[nBlocks + blockIdx.x] = sb; }
+}
+// r = b - A x (restart) ; partial sums of |r|^2
+__global__ void __launch_bounds__(PPE_T) k_bicg_residual(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks) {
+	__shared__ double sh[PPE_T / 32];
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	double a = 0.0;
+	if (i < S.n) { const double r = S.sourceTerm[i] - ell_row_dot(S, M, i, S.pressurePPE); M.r[i] = r; if (owned_slot(S, i)) a = r * r; }
+	const double sa = block_sum<PPE_T>(a, sh); const double sb = block_sum<PPE_T>(0.0, sh);
+	if (threadIdx.x == 0) { M.partial[blockIdx.x] = sa; M.partial[nBlocks + blockIdx.x] = sb; }
+}
+// scalar recurrences.  mode 10: after residual0 (|b|^2, |r|^2): rho = alpha = w = 1, |r0|^2 = |r|^2, then rho <- r0.r = |r|^2 for the
+// first trip; 11: after spmv v (r0.v); 12: after spmv t (|t|^2, t.s); 13: after xr (|r|^2, r0.r); 14: restart (|r|^2)
+__global__ void k_bicg_recur(const __grid_constant__ PpeView M, int mode, const double* sums, double* hostMirror) {
+	const double sa = sums[0], sb = sums[1];
+	double* s = M.scal;
+	if (mode == 10) {
+		s[0] = sa; s[1] = sb; s[12] = sb; s[7] = DBL_EPSILON * DBL_EPSILON * sa;
+		s[3] = 1.0; s[5] = 1.0; s[11] = 1.0; s[2] = sb;               // rho_old = alpha = w = 1 ; rho = r0.r = |r|^2
+		s[6] = (s[2] / s[3]) * (s[5] / s[11]);
+	} else if (mode == 11) { s[5] = s[2] / sa; }
+	else if (mode == 12) { s[11] = sa > 0.0 ? sb / sa : 0.0; }
+	else if (mode == 13) { s[1] = sa; s[3] = s[2]; s[2] = sb; s[6] = (s[2] / s[3]) * (s[5] / s[11]); }
+	else { s[1] = sa; s[12] = sa; s[2] = sa; s[6] = (s[2] / s[3]) * (s[5] / s[11]); }   // restart: r0 = r, rho = |r0|^2 = |r|^2 (rho_old stays)
+	hostMirror[0] = s[0]; hostMirror[1] = s[1]; hostMirror[2] = s[7]; hostMirror[3] = s[2]; hostMirror[4] = s[12];
+}
+
 template <class T> static int palloc(pmps_handle* h, T** p, size_t count) {
 	if (*p) return 0;
 	void* q = nullptr;
@@ -189,7 +270,8 @@ template <class T> static int palloc(pmps_handle* h, T** p, size_t count) {
 
 int pmps_ppe_solve(pmps_handle* h) {
 	DevView& S = h->V; const KParams& K = h->K;
-	if (K.p.solverType != 0) return pmps_fail(h, PMPS_E_UNSUPPORTED, "PPE: only the conjugate-gradient solver (solver_type 0) is on the device path");
+	if (K.p.solverType != 0 && K.p.solverType != 1) return pmps_fail(h, PMPS_E_ARG, "PPE: solver_type %d (0 = CG, 1 = BiCGSTAB)", K.p.solverType);
+	const bool bicg = K.p.solverType == 1;
 	{ const int rc = pmps_ensure_list(h); if (rc) return rc; }   // the assembly walks the Verlet candidate list
 	const int n = S.n, nBlocks = cdiv(n, PPE_T);
 	const size_t nWarps = ((size_t)S.n0 + 31) / 32, ell = nWarps * 32 * (size_t)S.listCap;
@@ -197,10 +279,12 @@ int pmps_ppe_solve(pmps_handle* h) {
 	bad |= palloc(h, &h->ppe_col, ell); bad |= palloc(h, &h->ppe_val, ell); bad |= palloc(h, &h->ppe_cnt, nWarps * 32);
 	bad |= palloc(h, &h->ppe_diag, S.n0); bad |= palloc(h, &h->ppe_r, S.n0); bad |= palloc(h, &h->ppe_p, S.n0); bad |= palloc(h, &h->ppe_t, S.n0);
 	bad |= palloc(h, &h->ppe_partial, 2 * (size_t)cdiv(S.n0, PPE_T) + 2); bad |= palloc(h, &h->ppe_scal, 16);
+	if (bicg) for (int k = 0; k < 5; k++) bad |= palloc(h, &h->ppe_bicg[k], S.n0);
 	if (!h->ppe_host) { if (cudaMallocHost((void**)&h->ppe_host, 64) != cudaSuccess) bad |= 1; }
 	if (bad) return pmps_fail(h, PMPS_E_CUDA, "PPE workspace allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
 	PpeView M; M.col = h->ppe_col; M.val = h->ppe_val; M.cnt = h->ppe_cnt; M.diag = h->ppe_diag; M.r = h->ppe_r; M.p = h->ppe_p; M.t = h->ppe_t;
 	M.partial = h->ppe_partial; M.scal = h->ppe_scal;
+	M.r0 = h->ppe_bicg[0]; M.v = h->ppe_bicg[1]; M.s = h->ppe_bicg[2]; M.y = h->ppe_bicg[3]; M.z = h->ppe_bicg[4];
 	double* hm = h->ppe_host;
 	S.ppeP = h->ppe_p;
 	const bool slab = h->slab && h->slabSum;
@@ -209,14 +293,50 @@ int pmps_ppe_solve(pmps_handle* h) {
 #define REDUCE(mode, nvals) do { LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, (mode), sums); \
 		if (slab) h->slabSum(h->slabUser, (nvals)); \
 		LAUNCH(h, "ppe.recur", k_ppe_recur, 1, 1, M, (mode), sums, hm); } while (0)
-	if (K.poly) { LAUNCH(h, "ppe.assemble", k_ppe_assemble<true>, nBlocks, PPE_T, S, K, M); }
-	else { LAUNCH(h, "ppe.assemble", k_ppe_assemble<false>, nBlocks, PPE_T, S, K, M); }
+	if (K.poly) { LAUNCH(h, "ppe.assemble", k_ppe_assemble<true>, nBlocks, PPE_T, S, K, M, bicg ? 1 : 0); }
+	else { LAUNCH(h, "ppe.assemble", k_ppe_assemble<false>, nBlocks, PPE_T, S, K, M, bicg ? 1 : 0); }
 	LAUNCH(h, "ppe.residual0", k_ppe_residual0, nBlocks, PPE_T, S, M, nBlocks);
-	REDUCE(0, 2);
+	if (!bicg) REDUCE(0, 2);
+	else { LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 0, sums); if (slab) h->slabSum(h->slabUser, 2); LAUNCH(h, "ppe.recur", k_bicg_recur, 1, 1, M, 10, sums, hm); }
 	CUDA_TRY(h, cudaStreamSynchronize(h->stream));
 	const double rhs2 = hm[0]; double res2 = hm[1]; const double thr = hm[2];
 	int iters = 0; double err = 0.0; int zeroX = 0;
-	if (rhs2 == 0.0) { zeroX = 1; }
+	if (rhs2 == 0.0) { zeroX = 1; if (bicg) { iters = 2 * h->numParticles; err = DBL_EPSILON; } }   // Eigen's BiCGSTAB returns before it touches iters / error
+	else if (bicg) {
+		// Eigen BiCGSTAB.h:29-107.  Per trip: p/y update, v = A y (+ r0.v), s/z update, t = A z (+ |t|^2, t.s), x/r update (+ |r|^2, r0.r);
+		// one host read of {|r|^2, rho, |r0|^2} per trip decides about convergence and the restart
+#define BREDUCE(mode, nvals) do { LAUNCH(h, "ppe.reduce", k_ppe_reduce, 1, RED_T, M, nBlocks, 0, sums); \
+		if (slab) h->slabSum(h->slabUser, (nvals)); \
+		LAUNCH(h, "ppe.recur", k_bicg_recur, 1, 1, M, (mode), sums, hm); } while (0)
+		LAUNCH(h, "ppe.bicg_start", k_bicg_start, nBlocks, PPE_T, S, M, 1);
+		const long long maxIt = 2ll * h->numParticles; int restarts = 0;
+		const double eps2 = DBL_EPSILON * DBL_EPSILON;
+		double rho = hm[3], r0n = hm[4];
+		while (res2 > thr && iters < maxIt) {
+			if (fabs(rho) < eps2 * r0n) {   // the residual became orthogonal to r0: restart from the true residual (:67-75)
+				LAUNCH(h, "ppe.bicg_residual", k_bicg_residual, nBlocks, PPE_T, S, M, nBlocks);
+				BREDUCE(14, 1);
+				LAUNCH(h, "ppe.bicg_start", k_bicg_start, nBlocks, PPE_T, S, M, 0);
+				if (restarts++ == 0) iters = 0;
+			}
+			LAUNCH(h, "ppe.bicg_p", k_bicg_p, nBlocks, PPE_T, S, M);
+			if (slab) { S.ppeP = M.y; h->slabRefresh(h->slabUser, PMPS_HF_PPE_P); }
+			LAUNCH(h, "ppe.spmv", k_bicg_spmv, nBlocks, PPE_T, S, M, nBlocks, 0);
+			BREDUCE(11, 1);
+			LAUNCH(h, "ppe.bicg_s", k_bicg_s, nBlocks, PPE_T, S, M);
+			if (slab) { S.ppeP = M.z; h->slabRefresh(h->slabUser, PMPS_HF_PPE_P); }
+			LAUNCH(h, "ppe.spmv", k_bicg_spmv, nBlocks, PPE_T, S, M, nBlocks, 1);
+			BREDUCE(12, 2);
+			LAUNCH(h, "ppe.bicg_xr", k_bicg_xr, nBlocks, PPE_T, S, M, nBlocks);
+			BREDUCE(13, 2);
+			CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+			res2 = hm[1]; rho = hm[3]; r0n = hm[4];
+			iters++;
+			if (!(res2 == res2)) break;
+		}
+#undef BREDUCE
+		err = sqrt(res2 / rhs2);
+	}
 	else {
 		if (res2 >= thr) {
 			LAUNCH(h, "ppe.init_p", k_ppe_init_p, nBlocks, PPE_T, S, M, nBlocks);

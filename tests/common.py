@@ -17,7 +17,7 @@ from polymps_b200.mesh import PolygonMesh  # noqa: E402
 from polymps_b200.state import HostState, ALL_FIELDS, I32, U8  # noqa: E402
 from make_golden import load_golden  # noqa: E402
 
-GOLDEN = ["w3", "w3j", "i3", "w2", "i2", "n2"]
+GOLDEN = ["w3", "w3j", "i3", "w2", "i2", "n2", "b3"]
 
 # ref_driver stage name -> stage calls (oracle method names == engine method names)
 STAGE_MAP = {

@@ -37,6 +37,8 @@ def golden_cases():
         # 2D particle walls (dam1610_h300_lo0p0050_{WC,INC} option sets)
         "w2": (cases.dam2d_particle(8, 10, tank_nx=18, tank_nz=16, name="w2"), (1, 3)),
         "i2": (cases.dam2d_particle(8, 10, tank_nx=18, tank_nz=16, incompressible=True, name="i2"), (1, 2)),
+        # 3D incompressible with the BiCGSTAB solver (solver_type 1)
+        "b3": (cases.dam3d(6, 5, 5, incompressible=True, jitter=0.05, name="b3", solver=1), (1, 2)),
         # 2D erosional dam break, non-Newtonian two-phase rheology (2D_dam_fraccarollo_lo02p50e-03_WC option set, BASELINE configs[0])
         "n2": (cases.dam2d_erosion(8, 8, 4, tank_nx=20, tank_nz=15, jitter=0.05, name="n2"), (1, 2, 6)),
     }

@@ -113,6 +113,8 @@ def _seeded_case(kind):
         return cases.dam3d(16, 8, 12, incompressible=True, jitter=0.03, name="i3s")
     if kind == "i2":
         return cases.dam2d_particle(30, 40, incompressible=True, name="i2s")
+    if kind == "b3":   # incompressible with the BiCGSTAB solver
+        return cases.dam3d(16, 8, 12, incompressible=True, jitter=0.03, name="b3s", solver=1)
     if kind == "n2":   # non-Newtonian erosional dam break (BASELINE configs[0] option set)
         return cases.dam2d_erosion(24, 24, 8, jitter=0.03, name="n2s")
     raise KeyError(kind)
@@ -127,7 +129,7 @@ def _build(case):
     return ps, meshes, HostState.from_case(case, ps)
 
 
-@pytest.mark.parametrize("kind", ["w3", "w3lattice", "w2", "i3", "i2", "n2"])
+@pytest.mark.parametrize("kind", ["w3", "w3lattice", "w2", "i3", "i2", "n2", "b3"])
 def test_whole_steps_against_oracle(kind):
     """pmps_init_step0 + pmps_step against the oracle's drivers on a seeded case a few thousand particles large."""
     case = _seeded_case(kind)
