@@ -17,7 +17,7 @@ from polymps_b200.mesh import PolygonMesh  # noqa: E402
 from polymps_b200.state import HostState, ALL_FIELDS, I32, U8  # noqa: E402
 from make_golden import load_golden  # noqa: E402
 
-GOLDEN = ["w3", "w3j", "i3", "w2", "i2", "n2", "b3"]
+GOLDEN = ["w3", "w3j", "i3", "w2", "i2", "n2", "b3", "e3"]
 
 # ref_driver stage name -> stage calls (oracle method names == engine method names)
 STAGE_MAP = {
@@ -33,6 +33,13 @@ STAGE_MAP = {
     "calcConcAndConcGradient": ["shifting"], "calcWallConcAndConcGradient": ["wall_shifting"],
     "updateVelocityParticlesWallDummy": ["update_wall_dummy_vel"], "checkParticleOutDomain3": ["check_out_domain"],
 }
+# stages whose call list depends on the wall type
+def stage_calls(stage, ps):
+    if stage == "meanPnd":   # pnd type 1: src/main.cpp:345-350
+        return (["mean_wall_pnd"] if ps.wallType == 1 else []) + ["mean_pnd"]
+    return STAGE_MAP[stage]
+
+
 SHIFTING_STAGES = {"calcConcAndConcGradient", "calcWallConcAndConcGradient"}
 # fields the reference dumps do not carry, or that are scratch in one of the implementations
 SKIP_FIELDS = {"dvelCollision"}
@@ -111,3 +118,24 @@ def compare_states(got: HostState, want, rtol=0.0, fields=None, skip=(), live_on
 
 def neighbor_sets_equal(a, b):
     return sorted(int(v) for v in a) == sorted(int(v) for v in b)
+
+
+# Option variants of the same kernel family (weight types, gradient types, slip condition, repulsion models, PND
+# types, free-surface tests).  name -> (builder of a SMALL case for the live reference run, builder of the seeded GPU case)
+def _v3(**kw):
+    from polymps_b200 import cases
+    return (lambda: cases.dam3d(6, 5, 5, jitter=0.05, name="var", **kw), lambda: cases.dam3d(14, 8, 10, jitter=0.04, name="var", **kw))
+
+
+def _v2(**kw):
+    from polymps_b200 import cases
+    return (lambda: cases.dam2d_particle(8, 10, tank_nx=18, tank_nz=16, name="var", **kw), lambda: cases.dam2d_particle(24, 30, name="var", **kw))
+
+
+VARIANTS = {
+    "slip": _v3(slip=1), "grad0": _v3(grad_type=0), "grad1": _v3(grad_type=1), "grad2": _v3(grad_type=2),
+    "gradcorr": _v3(grad_type=3, grad_corr=True), "rep0": _v3(rep_type=0), "rep1": _v3(rep_type=1), "rep3": _v3(rep_type=3),
+    "w1": _v3(weight_type=1), "w2": _v3(weight_type=2), "w3": _v3(weight_type=3), "w4": _v3(weight_type=4),
+    "pnd0": _v3(pnd_type=0), "pnd1": _v3(pnd_type=1), "fs0": _v3(fs_type=0), "noshift": _v3(shifting=0),
+    "2d_grad3": _v2(grad_type=3, grad_corr=False), "2d_w3": _v2(weight_type=3), "2d_fs1": _v2(fs_type=1), "2d_pnd0": _v2(pnd_type=0),
+}

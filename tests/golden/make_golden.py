@@ -37,6 +37,8 @@ def golden_cases():
         # 2D particle walls (dam1610_h300_lo0p0050_{WC,INC} option sets)
         "w2": (cases.dam2d_particle(8, 10, tank_nx=18, tank_nz=16, name="w2"), (1, 3)),
         "i2": (cases.dam2d_particle(8, 10, tank_nx=18, tank_nz=16, incompressible=True, name="i2"), (1, 2)),
+        # 3D explicit MPS (mps_type 0: E-MPS equation of state, src/MpsPressure.cpp:62-108), otherwise the WC option set
+        "e3": (cases.dam3d(6, 5, 5, jitter=0.05, name="e3", mps_type=0), (1, 2)),
         # 3D incompressible with the BiCGSTAB solver (solver_type 1)
         "b3": (cases.dam3d(6, 5, 5, incompressible=True, jitter=0.05, name="b3", solver=1), (1, 2)),
         # 2D erosional dam break, non-Newtonian two-phase rheology (2D_dam_fraccarollo_lo02p50e-03_WC option set, BASELINE configs[0])
@@ -73,6 +75,23 @@ def load_golden(path):
     meta = {"params": json.loads(bytes(z["params_json"]).decode()), "options": json.loads(bytes(z["case/options_json"]).decode()),
             "case": by.get("case", {})}
     return order, dumps, meta
+
+
+def reference_dumps(case, steps):
+    """Runs the unmodified reference on `case` right now (needs oracle/_ref) -> (order, dumps, params) like load_golden."""
+    root = tempfile.mkdtemp(prefix="refdump_")
+    try:
+        cases.write_case(case, root)
+        dump = os.path.join(root, "dump")
+        refrun.run_reference(root, case.name, max(steps), dump, dump_steps=steps, threads=1)
+        stems = [os.path.splitext(os.path.basename(fn))[0] for fn in glob.glob(os.path.join(dump, "*.bin"))]
+        stems.sort(key=chrono_key)
+        dumps = {stem: refrun.load_dump(os.path.join(dump, stem + ".bin")) for stem in stems}
+        with open(os.path.join(dump, "params.json")) as fh:
+            params = json.load(fh)
+        return stems, dumps, params
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
 
 
 def main():

@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 
-from common import (GOLDEN, STAGE_MAP, SHIFTING_STAGES, golden, stage_sequence, dumped_steps, state_from, compare_states,
+from common import (GOLDEN, STAGE_MAP, VARIANTS, SHIFTING_STAGES, golden, stage_sequence, dumped_steps, state_from, compare_states,
                     neighbor_sets_equal, natural_scales)
 from polymps_b200 import cases
 from polymps_b200.params import ParticleSystem
@@ -113,6 +113,8 @@ def _seeded_case(kind):
         return cases.dam3d(16, 8, 12, incompressible=True, jitter=0.03, name="i3s")
     if kind == "i2":
         return cases.dam2d_particle(30, 40, incompressible=True, name="i2s")
+    if kind == "e3":   # explicit MPS equation of state
+        return cases.dam3d(16, 8, 12, jitter=0.04, name="e3s", mps_type=0)
     if kind == "b3":   # incompressible with the BiCGSTAB solver
         return cases.dam3d(16, 8, 12, incompressible=True, jitter=0.03, name="b3s", solver=1)
     if kind == "n2":   # non-Newtonian erosional dam break (BASELINE configs[0] option set)
@@ -129,7 +131,7 @@ def _build(case):
     return ps, meshes, HostState.from_case(case, ps)
 
 
-@pytest.mark.parametrize("kind", ["w3", "w3lattice", "w2", "i3", "i2", "n2", "b3"])
+@pytest.mark.parametrize("kind", ["w3", "w3lattice", "w2", "i3", "i2", "n2", "b3", "e3"])
 def test_whole_steps_against_oracle(kind):
     """pmps_init_step0 + pmps_step against the oracle's drivers on a seeded case a few thousand particles large."""
     case = _seeded_case(kind)
@@ -268,3 +270,26 @@ def test_host_driven_loop_keeps_lists_and_results():
     assert sb.particleType[5] == ps.ghost and b.scalars().numParticles == sb.numParticles
     for e in (a, b, b2):
         e.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(VARIANTS))
+def test_option_variants_against_oracle(name):
+    """Weight / gradient / repulsion / PND / free-surface / slip variants of the kernel family: init_step0 + 3 fused steps against
+    the oracle (pinned bit-exactly to the live reference on the same variants by tests/test_oracle_variants.py)."""
+    case = VARIANTS[name][1]()
+    ps, meshes, st0 = _build(case)
+    want = st0.copy(); orc = _oracle(ps, want, meshes, jacobi=True)
+    orc.init_step0()
+    eng = _engine(ps, meshes, st0.numParticlesZero)
+    eng.upload(st0); eng.init_step0()
+    got = st0.copy(); eng.download(got)
+    bad = compare_states(got, want, rtol=RTOL, skip=NOISY, scales=natural_scales(ps))
+    assert not bad, "step 0: %s" % bad
+    for k in range(1, 4):
+        orc.step(1); eng.step(1)
+        eng.download(got)
+        bad = compare_states(got, want, rtol=RTOL * 10 ** (k - 1), skip=NOISY, scales=natural_scales(ps))
+        assert not bad, "%s step %d: %s" % (name, k, bad)
+        assert abs(eng.scalars().velMax - orc.P.velMax) <= 1e-9 * max(orc.P.velMax, 1e-30)
+    eng.close()
