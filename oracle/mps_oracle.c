@@ -602,7 +602,40 @@ void oracle_wall_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OB
  * with one thread this is a Gauss-Seidel sweep in index order (shiftingJacobi = 0 reproduces it bit for bit); with
  * several threads it is a data race.  shiftingJacobi = 1 reads a snapshot of the positions instead — the only
  * order-independent definition, and the one the CUDA path implements. */
+static inline double del_wgt(double r, double re, int type) {   /* src/MpsParticle.cpp:94-108 */
+	switch (type) {
+		case 1: return -re / (r * r) + 1.0 / re;
+		case 2: return -re / (r * r) - 1.0 / re;
+		case 3: return -3.0 / re * (1.0 - r / re) * (1.0 - r / re);
+		case 4: return -2.0 / re * (1.0 - r / re);
+		default: return -re / (r * r);
+	}
+}
+/* shifting type 1 (velocity adjustment), src/MpsShifting.cpp:23-101.  The reference updates vel in place inside the particle
+ * loop (a Gauss-Seidel sweep with one thread); shiftingJacobi reads a snapshot instead, as for type 2. */
+static void shifting_velocity(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	const int N = A->numParticles; double* snap = NULL; const double* vsrc = A->vel;
+	if (P->shiftingJacobi) { snap = (double*)malloc(sizeof(double) * 3 * (size_t)N); memcpy(snap, A->vel, sizeof(double) * 3 * (size_t)N); vsrc = snap; }
+	for (int i = 0; i < N; i++) {
+		if (A->particleType[i] != P->fluid) continue;
+		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i;
+		const double vx = vsrc[3 * (size_t)i], vy = vsrc[3 * (size_t)i + 1], vz = vsrc[3 * (size_t)i + 2];
+		double dux = 0.0, duy = 0.0, duz = 0.0;
+		NEIGH_LOOP(P, A, B, xi, mi, {
+			if (PRED_P(P, P->reS2) && j != i) {
+				const double dw = del_wgt(sqrt(d2), P->reS, P->weightType);
+				dux += dw * (vsrc[3 * (size_t)j] - vx); duy += dw * (vsrc[3 * (size_t)j + 1] - vy); duz += dw * (vsrc[3 * (size_t)j + 2] - vz);
+			}
+		});
+		if (A->particleBC[i] == P->inner) {
+			A->vel[3 * (size_t)i] -= P->coeffShifting1 * dux; A->vel[3 * (size_t)i + 1] -= P->coeffShifting1 * duy; A->vel[3 * (size_t)i + 2] -= P->coeffShifting1 * duz;
+		}
+	}
+	free(snap);
+}
+
 void oracle_shifting(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	if (P->shiftingType == 1) { shifting_velocity(P, A, B); return; }
 	PARFOR
 	for (int i = 0; i < A->numParticles; i++) {
 		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i;
@@ -1192,6 +1225,7 @@ void oracle_step(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMesh* mes
 	if (poly) oracle_wall_viscosity(P, A, B);
 	P->velMax = oracle_correct(P, A);
 	oracle_check_out_domain(P, A);
+	if (P->shiftingType == 1) oracle_shifting(P, A, B);
 	if (P->shiftingType == 2) { oracle_shifting(P, A, B); if (poly) oracle_wall_shifting(P, A, B); }
 	if (!poly) oracle_update_wall_dummy_vel(P, A, B);
 	oracle_check_out_domain(P, A);

@@ -207,7 +207,6 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	if (params->domainTypeBC != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: periodic domain boundaries are not on the device path yet (SURVEY 8f row 4)");
 	if (params->freeSurfType == 2) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: ARC free-surface detection is not on the device path yet (SURVEY 8f row 4)");
 	if (params->collisionType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: DPC collisions are not on the device path yet (SURVEY 8f row 4)");
-	if (params->shiftingType == 1) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: shifting type 1 is not on the device path yet (SURVEY 8f row 4)");
 	if (params->mpsType == 3) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: IMPLICIT_PND_DIVU is not on the device path yet (SURVEY 8f row 4)");
 	if (params->relaxPress < 1.0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: prediction pressure gradient (relax_fact < 1) is not on the device path yet");
 	if (params->numBucketsX < 1 || params->numBucketsY < 1 || params->numBucketsZ < 1 || !(params->bucketSide > 0.0)) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: bucket geometry not set");

@@ -255,4 +255,35 @@ struct BWallDummyVel {
 		S.vel[s.i] = v;
 	}
 };
+
+// MpsShifting::calcShifting (shifting type 1: velocity adjustment), src/MpsShifting.cpp:23-101 with delWeight of src/MpsParticle.cpp:94-108.
+// Jacobi semantics like the type-2 pass: neighbours' velocities are READ from S.vel, the adjusted velocity is WRITTEN to S.vel2.
+__device__ __forceinline__ double del_wgt(double r, double re, int type) {
+	switch (type) {
+		case 1: return -re / (r * r) + 1.0 / re;
+		case 2: return -re / (r * r) - 1.0 / re;
+		case 3: return -3.0 / re * (1.0 - r / re) * (1.0 - r / re);
+		case 4: return -2.0 / re * (1.0 - r / re);
+		default: return -re / (r * r);
+	}
+}
+struct BShiftVel {
+	typedef void copy_vel_tag;
+	struct Ctx { double vx, vy, vz, dx, dy, dz; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (s.type != K.p.fluid) return false;
+		const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z; c.dx = c.dy = c.dz = 0.0; return true;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_P<POLY>(q, K.p.reS2)) return;
+		const double dw = del_wgt(sqrt(q.d2), K.p.reS, K.p.weightType);
+		c.dx += dw * (S.vx[q.j] - c.vx); c.dy += dw * (S.vy[q.j] - c.vy); c.dz += dw * (S.vz[q.j] - c.vz);
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.dx = gsum(c.dx, m); c.dy = gsum(c.dy, m); c.dz = gsum(c.dz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		double4 v = S.vel[s.i];
+		if (S.particleBC[s.i] == K.p.inner) { v.x -= K.p.coeffShifting1 * c.dx; v.y -= K.p.coeffShifting1 * c.dy; v.z -= K.p.coeffShifting1 * c.dz; }
+		S.vel2[s.i] = v;
+	}
+};
 #include "pmps_rheo.cuh"

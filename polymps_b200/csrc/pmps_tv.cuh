@@ -55,6 +55,7 @@ template <> struct NbFields<BGradConcentration> { static constexpr unsigned valu
 template <> struct NbFields<BWallGradConcentration> { static constexpr unsigned value = NF_CONC; };
 template <> struct NbFields<BExtrapolatePress> { static constexpr unsigned value = NF_PRESS | NF_RHO; };
 template <> struct NbFields<BWallDummyVel> { static constexpr unsigned value = NF_VEL; };
+template <> struct NbFields<BShiftVel> { static constexpr unsigned value = NF_VEL; };
 template <> struct NbFields<BStrainRate> { static constexpr unsigned value = NF_VEL | NF_PRESS; };
 template <class... B> struct PackFields { static constexpr unsigned value = 0; };
 template <class B, class... R> struct PackFields<B, R...> { static constexpr unsigned value = NbFields<B>::value | PackFields<R...>::value; };

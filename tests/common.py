@@ -30,7 +30,7 @@ STAGE_MAP = {
     "calcPress": ["calc_press"], "extrapolatePress": ["extrapolate_press"], "correctionMatrix2": ["correction_matrix"],
     "calcPressGradient": ["press_gradient"], "calcWallPressGradient": ["wall_press_gradient"], "calcWallViscosity": ["wall_viscosity"],
     "correctionVelocityPosition": ["correct"], "checkParticleOutDomain2": ["check_out_domain"],
-    "calcConcAndConcGradient": ["shifting"], "calcWallConcAndConcGradient": ["wall_shifting"],
+    "calcShifting": ["shifting"], "calcConcAndConcGradient": ["shifting"], "calcWallConcAndConcGradient": ["wall_shifting"],
     "updateVelocityParticlesWallDummy": ["update_wall_dummy_vel"], "checkParticleOutDomain3": ["check_out_domain"],
 }
 # stages whose call list depends on the wall type
@@ -40,7 +40,7 @@ def stage_calls(stage, ps):
     return STAGE_MAP[stage]
 
 
-SHIFTING_STAGES = {"calcConcAndConcGradient", "calcWallConcAndConcGradient"}
+SHIFTING_STAGES = {"calcShifting", "calcConcAndConcGradient", "calcWallConcAndConcGradient"}
 # fields the reference dumps do not carry, or that are scratch in one of the implementations
 SKIP_FIELDS = {"dvelCollision"}
 
@@ -136,6 +136,6 @@ VARIANTS = {
     "slip": _v3(slip=1), "grad0": _v3(grad_type=0), "grad1": _v3(grad_type=1), "grad2": _v3(grad_type=2),
     "gradcorr": _v3(grad_type=3, grad_corr=True), "rep0": _v3(rep_type=0), "rep1": _v3(rep_type=1), "rep3": _v3(rep_type=3),
     "w1": _v3(weight_type=1), "w2": _v3(weight_type=2), "w3": _v3(weight_type=3), "w4": _v3(weight_type=4),
-    "pnd0": _v3(pnd_type=0), "pnd1": _v3(pnd_type=1), "fs0": _v3(fs_type=0), "noshift": _v3(shifting=0),
+    "pnd0": _v3(pnd_type=0), "pnd1": _v3(pnd_type=1), "fs0": _v3(fs_type=0), "noshift": _v3(shifting=0), "shift1": _v3(shifting=1), "2d_shift1": _v2(shifting=1),
     "2d_grad3": _v2(grad_type=3, grad_corr=False), "2d_w3": _v2(weight_type=3), "2d_fs1": _v2(fs_type=1), "2d_pnd0": _v2(pnd_type=0),
 }
