@@ -137,6 +137,8 @@ int pmps_calc_viscosity_interaction(pmps_t* h);  /* MpsViscosity::calcViscosityI
 int pmps_set_time(pmps_t* h, double timeCurrent);/* PSystem->timeCurrent as the rheology reads it (3D branch, src/MpsViscosity.cpp:529) */
 int pmps_calc_viscosity(pmps_t* h);              /* MpsViscosity::calcViscosity             src/MpsViscosity.cpp:20-100 */
 int pmps_add_gravity(pmps_t* h);                 /* MpsParticle::addGravity                 src/MpsParticle.cpp:111-130 */
+int pmps_prediction_press_gradient(pmps_t* h);      /* MpsPressure::predictionPressGradient     src/MpsPressure.cpp:932-1028 (relax_fact < 1) */
+int pmps_prediction_wall_press_gradient(pmps_t* h); /* MpsPressure::predictionWallPressGradient src/MpsPressure.cpp:1031-1214 */
 int pmps_predict(pmps_t* h);                     /* MpsParticleVelPos::predictionVelocityPosition  src/MpsParticleVelPos.cpp:20-50 */
 int pmps_check_out_domain(pmps_t* h);            /* MpsParticle::checkParticleOutDomain     src/MpsParticle.cpp:234-402 */
 int pmps_collisions(pmps_t* h);                  /* MpsParticleCollision::checkParticleCollisions / ...Dynamic...  src/MpsParticleCollision.cpp:22-292 */

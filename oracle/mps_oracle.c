@@ -527,7 +527,11 @@ static inline double grad_phi(const PmpsParams* P, double w, double Pj, double P
 	}
 }
 
-void oracle_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+static void press_gradient_impl(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, int prediction);
+void oracle_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) { press_gradient_impl(P, A, B, 0); }
+/* relax_fact < 1 (src/MpsPressure.cpp:932-1028): no correction matrix, acc += (1 - relaxPress) ... */
+void oracle_prediction_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) { press_gradient_impl(P, A, B, 1); }
+static void press_gradient_impl(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, int prediction) {
 	PARFOR
 	for (int i = 0; i < A->numParticles; i++) {
 		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i;
@@ -539,13 +543,19 @@ void oracle_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBucket
 		NEIGH_LOOP(P, A, B, xi, mi, {
 			if (PRED_P(P, P->reS2) && j != i) {
 				const double w = grad_phi(P, wgt(sqrt(d2), P->reS, P->weightType), A->press[j], Pi, Pmin, ni, A->pndi[j], d2);
-				if (!P->gradientCorrection) { sx += rx * w; sy += ry * w; sz += rz * w; }
+				if (prediction || !P->gradientCorrection) { sx += rx * w; sy += ry * w; sz += rz * w; }
 				else {
 					sx += (rx * c1[0] + ry * c1[1] + rz * c1[2]) * w; sy += (rx * c2[0] + ry * c2[1] + rz * c2[2]) * w;
 					sz += (rx * c3[0] + ry * c3[1] + rz * c3[2]) * w;
 				}
 			}
 		});
+		if (prediction) {
+			A->acc[3 * (size_t)i] += (1.0 - P->relaxPress) * sx * P->coeffPressGrad / A->RHO[i];
+			A->acc[3 * (size_t)i + 1] += (1.0 - P->relaxPress) * sy * P->coeffPressGrad / A->RHO[i];
+			A->acc[3 * (size_t)i + 2] += (1.0 - P->relaxPress) * sz * P->coeffPressGrad / A->RHO[i];
+			continue;
+		}
 		A->acc[3 * (size_t)i] = P->relaxPress * sx * P->coeffPressGrad / A->RHO[i];
 		A->acc[3 * (size_t)i + 1] = P->relaxPress * sy * P->coeffPressGrad / A->RHO[i];
 		A->acc[3 * (size_t)i + 2] = P->relaxPress * sz * P->coeffPressGrad / A->RHO[i];
@@ -564,7 +574,10 @@ static inline double repulsion(const PmpsParams* P, double r, double rho, double
 	}
 }
 
-void oracle_wall_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, double velMax) {
+static void wall_press_gradient_impl(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, double velMax, int prediction);
+void oracle_wall_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, double velMax) { wall_press_gradient_impl(P, A, B, velMax, 0); }
+void oracle_prediction_wall_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, double velMax) { wall_press_gradient_impl(P, A, B, velMax, 1); }   /* src/MpsPressure.cpp:1031-1214 */
+static void wall_press_gradient_impl(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, double velMax, int prediction) {
 	const double vol = pow(P->partDist, (double)P->dim);
 	const double vcap = velMax < P->expectMaxVelocity ? velMax : P->expectMaxVelocity; const double vmax2 = vcap * vcap;
 	PARFOR
@@ -590,9 +603,9 @@ void oracle_wall_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OB
 		double f[3] = { 0.0, 0.0, 0.0 };
 		if (r < P->reRepulsiveForce && r > P->epsilonZero) { const double q = repulsion(P, r, A->RHO[i], vmax2); f[0] = -q * n[0]; f[1] = -q * n[1]; f[2] = -q * n[2]; }
 		for (int k = 0; k < 3; k++) {
-			const double g = (P->relaxPress * MATVEC(R, sx, sy, sz, k) * P->coeffPressGrad - f[k]);
+			const double g = ((prediction ? 1.0 - P->relaxPress : P->relaxPress) * MATVEC(R, sx, sy, sz, k) * P->coeffPressGrad - f[k]);
 			A->acc[3 * (size_t)i + k] += g / A->RHO[i];
-			A->forceWall[3 * (size_t)i + k] += -g * vol;
+			if (!prediction) A->forceWall[3 * (size_t)i + k] += -g * vol;
 		}
 	}
 }
@@ -1200,6 +1213,7 @@ void oracle_step(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMesh* mes
 	if (P->fluidType == 1) { oracle_calc_volume_fraction(P, A, B); oracle_calc_viscosity_interaction(P, A, B); }   /* src/main.cpp:259-262 */
 	oracle_calc_viscosity(P, A, B);
 	oracle_add_gravity(P, A);
+	if (P->relaxPress < 1.0) { oracle_prediction_press_gradient(P, A, B); if (poly) oracle_prediction_wall_press_gradient(P, A, B, P->velMax); }   /* src/main.cpp:268-276 */
 	oracle_predict(P, A);
 	oracle_check_out_domain(P, A);
 	oracle_collisions(P, A, B);

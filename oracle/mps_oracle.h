@@ -56,6 +56,8 @@ int  oracle_solve_ppe(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B,
 void oracle_extrapolate_press(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);  /* src/MpsPressure.cpp:792-846 */
 void oracle_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);     /* src/MpsPressure.cpp:1217-1338 */
 void oracle_wall_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, double velMax); /* src/MpsPressure.cpp:1341-1611 */
+void oracle_prediction_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);          /* src/MpsPressure.cpp:932-1028 */
+void oracle_prediction_wall_press_gradient(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, double velMax); /* src/MpsPressure.cpp:1031-1214 */
 void oracle_wall_viscosity(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);     /* src/MpsViscosity.cpp:1527-1910 */
 double oracle_correct(const PmpsParams* P, PmpsHostArrays* A);                             /* src/MpsParticleVelPos.cpp:53-97, returns velMax */
 void oracle_shifting(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);           /* src/MpsShifting.cpp:432-575 */

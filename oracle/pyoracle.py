@@ -48,7 +48,7 @@ def _ip(a):
 class Oracle:
     """One simulation on the CPU oracle: params (ParticleSystem), HostState, buckets, meshes."""
 
-    STAGES_PAB = ["calc_volume_fraction", "calc_viscosity", "collisions", "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive",
+    STAGES_PAB = ["prediction_press_gradient", "calc_volume_fraction", "calc_viscosity", "collisions", "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive",
                   "wall_pnd_diffusive", "mean_pnd_wall_dummy_surface", "extrapolate_press", "press_gradient", "wall_viscosity",
                   "shifting", "wall_shifting", "update_wall_dummy_vel", "initial_pnd", "mean_wall_pnd", "mean_pnd",
                   "mean_neigh_fluid_pnd"]
@@ -60,6 +60,7 @@ class Oracle:
         L.oracle_correct.restype = ctypes.c_double
         L.oracle_calc_viscosity_interaction.restype = ctypes.c_double
         L.oracle_wall_press_gradient.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double]
+        L.oracle_prediction_wall_press_gradient.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_double]
         L.oracle_set_threads(int(threads))
         self.ps = ps
         self.P = to_c_params(ps, shifting_jacobi)
@@ -118,6 +119,9 @@ class Oracle:
 
     def wall_closest_point(self):
         self.lib.oracle_wall_closest_point(ctypes.byref(self.P), self._A(), self.meshes); self._sync()
+
+    def prediction_wall_press_gradient(self):
+        self.lib.oracle_prediction_wall_press_gradient(ctypes.byref(self.P), self._A(), ctypes.byref(self.B), ctypes.c_double(self.P.velMax)); self._sync()
 
     def wall_press_gradient(self):
         self.lib.oracle_wall_press_gradient(ctypes.byref(self.P), self._A(), ctypes.byref(self.B), ctypes.c_double(self.P.velMax))

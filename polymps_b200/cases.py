@@ -43,7 +43,7 @@ class Case:
 def base_options(*, dim, lo, dt, wall_type, mps_type, c0=15.0, re_small=2.1, re_large=2.1, grad_type=3,
                  grad_corr=False, shifting=2, pnd_type=2, fs_type=1, fs_pnd=0.98, max_vel=4.0, gravity=(0.0, 0.0, -9.81),
                  dom_min=(0.0, 0.0, 0.0), dom_max=(1.0, 1.0, 1.0), final_time=1.0, solver=0, alpha=1e-6, relax_pnd=0.01,
-                 collision=0, slip=0, rep_type=2, weight_type=0, fs_neigh=0.85, fluid_type=0, rheo=None) -> dict:
+                 collision=0, slip=0, rep_type=2, weight_type=0, fs_neigh=0.85, fluid_type=0, rheo=None, relax=1.0) -> dict:
     """A JSON document with the reference's key names (src/MpsInputOutput.cpp:134-505)."""
     return {
         "flags": {"wall_type": wall_type, "fem_MESH": False, "forced_MESH": False,
@@ -64,7 +64,7 @@ def base_options(*, dim, lo, dt, wall_type, mps_type, c0=15.0, re_small=2.1, re_
             "dimension": dim, "particle_dist": lo, "time_step": dt, "final_time": final_time, "iter_output": 1000000,
             "CFL_number": 0.2, "weight_type": weight_type, "slip_condition": slip,
             "effective_radius": {"small": re_small, "large": re_large},
-            "gradient": {"type": grad_type, "correction": grad_corr, "relax_fact": 1.0},
+            "gradient": {"type": grad_type, "correction": grad_corr, "relax_fact": relax},
             "mps_type": mps_type,
             "explicit_mps": {"equation_state": {"speed_sound": c0, "gamma": 7.0}},
             "semi_implicit_mps": {"solver_type": solver, "weak_compressibility": {"alpha": alpha},

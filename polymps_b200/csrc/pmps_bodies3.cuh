@@ -27,12 +27,14 @@ struct BPressMin {
 };
 
 // MpsPressure::calcPressGradient, src/MpsPressure.cpp:1217-1338
-struct BPressGradient {
+// PRED = true: MpsPressure::predictionPressGradient (src/MpsPressure.cpp:932-1028, relax_fact < 1): the same sum without the correction
+// matrix, added to the acceleration with the factor (1 - relaxPress) instead of overwriting it with relaxPress
+template <bool PRED> struct BPressGradientT {
 	struct Ctx { double Pi, ni, invNi, Pmin, sx, sy, sz; double c1[3], c2[3], c3[3]; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		c.Pi = S.press[s.i]; c.ni = S.pndi[s.i]; c.invNi = c.ni > K.p.epsilonZero ? 1.0 / c.ni : 0.0;
 		c.Pmin = (K.p.gradientType == 0 || K.p.gradientType == 2) ? S.scratch1[s.i] : c.Pi;
-		if (K.p.gradientCorrection) {
+		if (!PRED && K.p.gradientCorrection) {
 			c.c1[0] = S.correcMatrixRow1.x[s.i]; c.c1[1] = S.correcMatrixRow1.y[s.i]; c.c1[2] = S.correcMatrixRow1.z[s.i];
 			c.c2[0] = S.correcMatrixRow2.x[s.i]; c.c2[1] = S.correcMatrixRow2.y[s.i]; c.c2[2] = S.correcMatrixRow2.z[s.i];
 			c.c3[0] = S.correcMatrixRow3.x[s.i]; c.c3[1] = S.correcMatrixRow3.y[s.i]; c.c3[2] = S.correcMatrixRow3.z[s.i];
@@ -42,7 +44,7 @@ struct BPressGradient {
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reS2)) return;
 		const double w = grad_phi_r(K, wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType), S.press[q.j], c.Pi, c.Pmin, c.ni, c.invNi, S.pndi[q.j], q.rinv * q.rinv);
-		if (!K.p.gradientCorrection) { c.sx += q.rx * w; c.sy += q.ry * w; c.sz += q.rz * w; }
+		if (PRED || !K.p.gradientCorrection) { c.sx += q.rx * w; c.sy += q.ry * w; c.sz += q.rz * w; }
 		else {
 			c.sx += (q.rx * c.c1[0] + q.ry * c.c1[1] + q.rz * c.c1[2]) * w; c.sy += (q.rx * c.c2[0] + q.ry * c.c2[1] + q.rz * c.c2[2]) * w;
 			c.sz += (q.rx * c.c3[0] + q.ry * c.c3[1] + q.rz * c.c3[2]) * w;
@@ -51,11 +53,19 @@ struct BPressGradient {
 	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.sx = gsum(c.sx, m); c.sy = gsum(c.sy, m); c.sz = gsum(c.sz, m); }
 	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		const double rho = S.RHO[s.i];
+		if (PRED) {
+			S.acc.x[s.i] += (1.0 - K.p.relaxPress) * c.sx * K.p.coeffPressGrad / rho;
+			S.acc.y[s.i] += (1.0 - K.p.relaxPress) * c.sy * K.p.coeffPressGrad / rho;
+			S.acc.z[s.i] += (1.0 - K.p.relaxPress) * c.sz * K.p.coeffPressGrad / rho;
+			return;
+		}
 		S.acc.x[s.i] = K.p.relaxPress * c.sx * K.p.coeffPressGrad / rho;
 		S.acc.y[s.i] = K.p.relaxPress * c.sy * K.p.coeffPressGrad / rho;
 		S.acc.z[s.i] = K.p.relaxPress * c.sz * K.p.coeffPressGrad / rho;
 	}
 };
+typedef BPressGradientT<false> BPressGradient;
+typedef BPressGradientT<true> BPredPressGradient;
 
 // wall repulsion, src/MpsPressure.cpp:1554-1611: the scalar that multiplies -n
 __device__ __forceinline__ double repulsion(const KParams& K, double r, double rho, double vmax2) {
@@ -71,7 +81,8 @@ __device__ __forceinline__ double repulsion(const KParams& K, double r, double r
 
 // MpsPressure::calcWallPressGradient, src/MpsPressure.cpp:1341-1550.  velMax of the previous correction is read
 // from the device scalar so the step needs no host round trip.
-struct BWallPressGradient {
+// PRED = true: predictionWallPressGradient (src/MpsPressure.cpp:1031-1214): factor (1 - relaxPress), no forceWall
+template <bool PRED> struct BWallPressGradientT {
 	typedef void wall_frame_tag;
 	struct Ctx { double Pi, ni, invNi, Pmin, sx, sy, sz; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
@@ -105,12 +116,14 @@ struct BWallPressGradient {
 		}
 		double* a[3] = { S.acc.x, S.acc.y, S.acc.z }; double* fw[3] = { S.forceWall.x, S.forceWall.y, S.forceWall.z };
 		for (int k = 0; k < 3; k++) {
-			const double g = (K.p.relaxPress * MATVEC(f.R, c.sx, c.sy, c.sz, k) * K.p.coeffPressGrad - fr[k]);
+			const double g = ((PRED ? 1.0 - K.p.relaxPress : K.p.relaxPress) * MATVEC(f.R, c.sx, c.sy, c.sz, k) * K.p.coeffPressGrad - fr[k]);
 			a[k][s.i] += g / rho;
-			fw[k][s.i] += -g * K.vol;
+			if (!PRED) fw[k][s.i] += -g * K.vol;
 		}
 	}
 };
+typedef BWallPressGradientT<false> BWallPressGradient;
+typedef BWallPressGradientT<true> BPredWallPressGradient;
 
 // fused tail of the gradient pass: correctionVelocityPosition (src/MpsParticleVelPos.cpp:53-97).  Reads the acceleration
 // the bodies in front of it stored, writes the new position / velocity to the alternate buffers, feeds velMax.

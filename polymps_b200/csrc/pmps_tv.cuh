@@ -51,6 +51,8 @@ template <> struct NbFields<BMeanNeighFluidPnd> { static constexpr unsigned valu
 template <> struct NbFields<BPressMin> { static constexpr unsigned value = NF_PRESS; };
 template <> struct NbFields<BPressGradient> { static constexpr unsigned value = NF_PRESS | NF_PNDI; };
 template <> struct NbFields<BWallPressGradient> { static constexpr unsigned value = NF_PRESS | NF_PNDI; };
+template <> struct NbFields<BPredPressGradient> { static constexpr unsigned value = NF_PRESS | NF_PNDI; };
+template <> struct NbFields<BPredWallPressGradient> { static constexpr unsigned value = NF_PRESS | NF_PNDI; };
 template <> struct NbFields<BGradConcentration> { static constexpr unsigned value = NF_CONC; };
 template <> struct NbFields<BWallGradConcentration> { static constexpr unsigned value = NF_CONC; };
 template <> struct NbFields<BExtrapolatePress> { static constexpr unsigned value = NF_PRESS | NF_RHO; };

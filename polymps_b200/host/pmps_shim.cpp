@@ -190,6 +190,8 @@ void MpsPressure::calcPress(MpsParticleSystem *PSystem, MpsParticle *Particles, 
 	if (g_oodCalls == 1) { pull_scalars(); pull_arrays(); }   // end of the 0-th step (src/main.cpp:176): iteration 0 writes output
 }
 void MpsPressure::extrapolatePressParticlesWallDummy(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_extrapolate_press(H(PSystem, Particles))); }
+void MpsPressure::predictionPressGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_prediction_press_gradient(H(PSystem, Particles))); }
+void MpsPressure::predictionWallPressGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_prediction_wall_press_gradient(H(PSystem, Particles))); }
 void MpsPressure::calcPressGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_press_gradient(H(PSystem, Particles))); }
 void MpsPressure::calcWallPressGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_press_gradient(H(PSystem, Particles))); }
 

@@ -35,6 +35,8 @@ STAGE_MAP = {
 }
 # stages whose call list depends on the wall type
 def stage_calls(stage, ps):
+    if stage == "predictionPressGradient":   # relax_fact < 1: src/main.cpp:270-276
+        return ["prediction_press_gradient"] + (["prediction_wall_press_gradient"] if ps.wallType == 1 else [])
     if stage == "meanPnd":   # pnd type 1: src/main.cpp:345-350
         return (["mean_wall_pnd"] if ps.wallType == 1 else []) + ["mean_pnd"]
     return STAGE_MAP[stage]
@@ -137,5 +139,6 @@ VARIANTS = {
     "gradcorr": _v3(grad_type=3, grad_corr=True), "rep0": _v3(rep_type=0), "rep1": _v3(rep_type=1), "rep3": _v3(rep_type=3),
     "w1": _v3(weight_type=1), "w2": _v3(weight_type=2), "w3": _v3(weight_type=3), "w4": _v3(weight_type=4),
     "pnd0": _v3(pnd_type=0), "pnd1": _v3(pnd_type=1), "fs0": _v3(fs_type=0), "noshift": _v3(shifting=0), "shift1": _v3(shifting=1), "2d_shift1": _v2(shifting=1),
+    "relax": _v3(relax=0.7), "relax_grad0": _v3(relax=0.5, grad_type=0), "2d_relax": _v2(relax=0.6),
     "2d_grad3": _v2(grad_type=3, grad_corr=False), "2d_w3": _v2(weight_type=3), "2d_fs1": _v2(fs_type=1), "2d_pnd0": _v2(pnd_type=0),
 }
