@@ -295,7 +295,50 @@ void oracle_wall_viscosity(const PmpsParams* P, PmpsHostArrays* A, const OBucket
 }
 
 /* ------------------------------------------------------------------------------------------------ collisions (PC) */
+/* dynamic particle collision (collision type 1), src/MpsParticleCollision.cpp:124-292: pairs closer than partDist; approaching pairs
+ * exchange momentum scaled by kappa, separating ones are pushed apart by a background pressure; positions move with the velocity jump */
+static void collisions_dpc(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	const double Wij5 = 0.5 * 0.5 * 0.5 * 0.5 * 3.0, invLo = 1.0 / P->partDist;
+	const double gravityMod = sqrt(P->gravityX * P->gravityX + P->gravityY * P->gravityY + P->gravityZ * P->gravityZ);
+	double* dv = (double*)calloc(3 * (size_t)A->numParticlesZero, sizeof(double));
+	PARFOR
+	for (int i = 0; i < A->numParticles; i++) {
+		if (A->particleType[i] != P->fluid) continue;
+		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i;
+		const double* vi = A->vel + 3 * (size_t)i; const double m_i = A->PTYPE[i] == 1 ? P->DNS_FL1 : P->DNS_FL2;
+		double dx = 0.0, dy = 0.0, dz = 0.0;
+		NEIGH_LOOP(P, A, B, xi, mi, {
+			if (d2 < P->partDist * P->partDist && (d2 < dm2 || P->wallType == 0) && j != i) {
+				const int jf = A->particleType[j] == P->fluid;
+				const double m_j = jf ? (A->PTYPE[j] == 1 ? P->DNS_FL1 : P->DNS_FL2) : P->densityWall;
+				const double dst = sqrt(d2);
+				double Wij = 0.0;
+				if (dst > P->epsilonZero) { const double w1 = 1.0 - dst * invLo; const double w2 = 4.0 * dst * invLo + 1.0; Wij = w1 * w1 * w1 * w1 * w2; }
+				const double chi = sqrt(Wij / Wij5);
+				const double kappa = dst < 0.5 * P->partDist ? 1.0 : chi;
+				const double* vj = A->vel + 3 * (size_t)j;
+				double f = (vi[0] - vj[0]) * rx + (vi[1] - vj[1]) * ry + (vi[2] - vj[2]) * rz;
+				if (f > 0.0) f *= kappa * 2.0 * m_j / (m_i + m_j) / d2;
+				else {
+					const double pmax = 2.0 / 3.0 * A->RHO[i] * gravityMod * 0.2, pmin = A->RHO[i] * gravityMod * P->partDist;
+					const double a = P->lambdaCollision * fabs(A->press[i] + A->press[j]), b = P->lambdaCollision * pmax;
+					const double lo_ = a < b ? a : b; const double ptil = lo_ > pmin ? lo_ : pmin;
+					const double pb = ptil * chi;
+					f = P->timeStep / m_i * chi * pb / d2;
+				}
+				if (jf) { dx -= rx * f; dy -= ry * f; dz -= rz * f; }
+				else { dx -= 2.0 * rx * f; dy -= 2.0 * ry * f; dz -= 2.0 * rz * f; }
+			}
+		});
+		dv[3 * (size_t)i] = dx; dv[3 * (size_t)i + 1] = dy; dv[3 * (size_t)i + 2] = dz;
+	}
+	for (int i = 0; i < A->numParticles; i++)
+		if (A->particleType[i] == P->fluid) for (int k = 0; k < 3; k++) { A->vel[3 * (size_t)i + k] += dv[3 * (size_t)i + k]; A->pos[3 * (size_t)i + k] += dv[3 * (size_t)i + k] * P->timeStep; }
+	free(dv);
+}
+
 void oracle_collisions(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	if (P->collisionType == 1) { collisions_dpc(P, A, B); return; }
 	double* dv = (double*)calloc(3 * (size_t)A->numParticlesZero, sizeof(double));
 	PARFOR
 	for (int i = 0; i < A->numParticles; i++) {

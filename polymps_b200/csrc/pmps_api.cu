@@ -65,6 +65,16 @@ __global__ void k_apply_collision(const __grid_constant__ DevView S, const __gri
 	S.vel[i] = v;
 }
 
+__global__ void k_apply_collision_dpc(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= S.n) return;
+	double4 p = S.pos[i];
+	if (pk_type(p) != K.p.fluid) return;
+	double4 v = S.vel[i];
+	dpc_apply(S, K, i, p, v);
+	S.vel[i] = v; S.pos[i] = p; track_disp(S, K, i, p);
+}
+
 // MpsParticleVelPos::correctionVelocityPosition, src/MpsParticleVelPos.cpp:53-97 (velMax: max over fluid of |v|)
 __global__ void k_correct(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -206,7 +216,7 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	if (params->fluidType == 1 && params->fractionMethod != 1 && params->fractionMethod != 2) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: fractionMethod %d", params->fractionMethod);
 	if (params->domainTypeBC != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: periodic domain boundaries are not on the device path yet (SURVEY 8f row 4)");
 	if (params->freeSurfType == 2) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: ARC free-surface detection is not on the device path yet (SURVEY 8f row 4)");
-	if (params->collisionType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: DPC collisions are not on the device path yet (SURVEY 8f row 4)");
+	if (params->collisionType != 0 && params->collisionType != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: collisionType %d", params->collisionType);
 	if (params->mpsType == 3) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: IMPLICIT_PND_DIVU is not on the device path yet (SURVEY 8f row 4)");
 	if (params->numBucketsX < 1 || params->numBucketsY < 1 || params->numBucketsZ < 1 || !(params->bucketSide > 0.0)) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: bucket geometry not set");
 	const long long nB = (long long)params->numBucketsX * params->numBucketsY * params->numBucketsZ;
@@ -304,7 +314,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	if (const char* e = getenv("PMPS_HIT_DELTA")) { const double v = atof(e); if (v > 0.0 && v < 0.2) K.hitDelta = v * lo; }
 	if (maxRe + 2.0 * K.hitDelta > rl - 1e-3 * lo) K.hitDelta = fmax(0.5 * (rl - 1e-3 * lo - maxRe), 0.0);   // never beyond the Verlet radius
 	{ const double r = (maxRe + 2.0 * K.hitDelta) * (1.0 + 1e-5); K.hitR2 = (float)(r * r); }
-	{ const double r = (sqrt(P.distCollisionLimit2) + 2.0 * K.hitDelta) * (1.0 + 1e-5) + 8.0 * 1.2e-7 * 4.0 * rl; K.closeR2 = (float)(r * r); }
+	{ const double r = ((P.collisionType == 1 ? P.partDist : sqrt(P.distCollisionLimit2)) + 2.0 * K.hitDelta) * (1.0 + 1e-5) + 8.0 * 1.2e-7 * 4.0 * rl; K.closeR2 = (float)(r * r); }
 	// |x_j - mirror_i| >= 2 dist(i, wall) - displacement - |x_j - x_i| > re whenever dist > re + displacement/2: margin = the full guard
 	{ const double far = maxRe * (1.0 + 1e-6) + (guard > 0 ? guard : 0.0) + 1e-6 * lo; K.mirrorFar2 = far * far; }
 	k_iota<<<cdiv(n0, 256), 256, 0, h->stream>>>(S.hostIdx, S.slotOfHost, n0);

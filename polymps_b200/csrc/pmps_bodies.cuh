@@ -155,6 +155,59 @@ struct BCollisionTail {
 		S.vel2[s.i] = v;
 	}
 };
+// dynamic particle collision (collision type 1), src/MpsParticleCollision.cpp:124-292
+struct BCollisionDPC {
+	typedef void close_pairs_tag;
+	struct Ctx { double vx, vy, vz, mi, Pi, rho, dx, dy, dz; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (s.type != K.p.fluid) return false;
+		const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z; c.Pi = S.press[s.i]; c.rho = S.RHO[s.i];
+		c.mi = s.ptype == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2; c.dx = c.dy = c.dz = 0.0; return true;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_P<POLY>(q, K.p.partDist * K.p.partDist)) return;
+		const bool jf = q.tj == K.p.fluid;
+		const double mj = jf ? (q.ptj == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2) : K.p.densityWall;
+		const double dst = sqrt(q.d2), invLo = 1.0 / K.p.partDist;
+		double Wij = 0.0;
+		if (dst > K.p.epsilonZero) { const double w1 = 1.0 - dst * invLo; const double w2 = 4.0 * dst * invLo + 1.0; Wij = w1 * w1 * w1 * w1 * w2; }
+		const double chi = sqrt(Wij / (0.5 * 0.5 * 0.5 * 0.5 * 3.0));
+		const double kappa = dst < 0.5 * K.p.partDist ? 1.0 : chi;
+		double f = (c.vx - S.vx[q.j]) * q.rx + (c.vy - S.vy[q.j]) * q.ry + (c.vz - S.vz[q.j]) * q.rz;
+		if (f > 0.0) f *= kappa * 2.0 * mj / (c.mi + mj) / q.d2;
+		else {
+			const double gmod = sqrt(K.p.gravityX * K.p.gravityX + K.p.gravityY * K.p.gravityY + K.p.gravityZ * K.p.gravityZ);
+			const double pmax = 2.0 / 3.0 * c.rho * gmod * 0.2, pmin = c.rho * gmod * K.p.partDist;
+			const double a = K.p.lambdaCollision * fabs(c.Pi + S.press[q.j]), b = K.p.lambdaCollision * pmax;
+			const double lo = a < b ? a : b; const double ptil = lo > pmin ? lo : pmin;
+			f = K.p.timeStep / c.mi * chi * (ptil * chi) / q.d2;
+		}
+		if (jf) { c.dx -= q.rx * f; c.dy -= q.ry * f; c.dz -= q.rz * f; }
+		else { c.dx -= 2.0 * q.rx * f; c.dy -= 2.0 * q.ry * f; c.dz -= 2.0 * q.rz * f; }
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.dx = gsum(c.dx, m); c.dy = gsum(c.dy, m); c.dz = gsum(c.dz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		S.dvelCollision.x[s.i] = c.dx; S.dvelCollision.y[s.i] = c.dy; S.dvelCollision.z[s.i] = c.dz;
+	}
+};
+// second loop (:262-266): vel += dvel, pos += dvel dt
+__device__ __forceinline__ void dpc_apply(const DevView& S, const KParams& K, int i, double4& p, double4& v) {
+	const double dx = S.dvelCollision.x[i], dy = S.dvelCollision.y[i], dz = S.dvelCollision.z[i];
+	v.x = __dadd_rn(v.x, dx); v.y = __dadd_rn(v.y, dy); v.z = __dadd_rn(v.z, dz);
+	p.x = __dadd_rn(p.x, __dmul_rn(dx, K.p.timeStep)); p.y = __dadd_rn(p.y, __dmul_rn(dy, K.p.timeStep)); p.z = __dadd_rn(p.z, __dmul_rn(dz, K.p.timeStep));
+}
+struct BCollisionDPCTail {
+	typedef void copy_vel_tag; typedef void copy_pos_tag; typedef void no_pair_tag;
+	struct Ctx {};
+	__device__ __forceinline__ static bool begin(Ctx&, const DevView&, const KParams& K, const Self& s) { return s.type == K.p.fluid; }
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx&, const Nb&, const KParams&, const Self&, const Pair&) {}
+	__device__ __forceinline__ static void reduce(Ctx& , unsigned m) {  }
+	__device__ __forceinline__ static void end(Ctx&, const DevView& S, const KParams& K, const Self& s) {
+		double4 v = S.vel[s.i], p = s.pi;
+		dpc_apply(S, K, s.i, p, v);
+		S.vel2[s.i] = v; S.pos2[s.i] = p; track_disp(S, K, s.i, p);
+	}
+};
 // fused head: the polygon-wall pass of particle i (closest point, mirror, wall weights; pmps_wall.cuh) rides in the
 // collision launch — it needs only x_i, and the collision predicate does not look at the mirror (it was reset to
 // "infinity" by the prediction, so d2 < dm2 holds trivially: the launch uses the POLY = false walker).

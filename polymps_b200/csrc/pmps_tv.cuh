@@ -42,6 +42,7 @@ template <class B> struct NbFields { static constexpr unsigned value = 0; };
 template <> struct NbFields<BViscosity> { static constexpr unsigned value = NF_VEL | NF_MEU; };
 template <> struct NbFields<BWallViscosity> { static constexpr unsigned value = NF_VEL | NF_MEU; };
 template <> struct NbFields<BCollision> { static constexpr unsigned value = NF_VEL; };
+template <> struct NbFields<BCollisionDPC> { static constexpr unsigned value = NF_VEL | NF_PRESS; };
 template <> struct NbFields<BPndDiffusive> { static constexpr unsigned value = NF_VEL | NF_PRESS | NF_PNDI | NF_RHO; };
 template <> struct NbFields<BWallPndDiffusive> { static constexpr unsigned value = NF_VEL | NF_PNDI; };
 template <> struct NbFields<BMeanPnd<0>> { static constexpr unsigned value = NF_PNDI; };

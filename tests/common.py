@@ -134,11 +134,24 @@ def _v2(**kw):
     return (lambda: cases.dam2d_particle(8, 10, tank_nx=18, tank_nz=16, name="var", **kw), lambda: cases.dam2d_particle(24, 30, name="var", **kw))
 
 
+def _jittered(build, amp=0.04, seed=7):
+    """Fluid particles moved off the lattice: the dynamic collision model is discontinuous at zero approach speed (a separating
+    pair is pushed apart by a finite background pressure, an approaching one is not, src/MpsParticleCollision.cpp:212-241), so on
+    a perfect lattice — neighbours side by side with relative velocities of rounding size — the branch is decided by noise."""
+    def f():
+        c = build(); rng = np.random.default_rng(seed); lo = c.options["numerical"]["particle_dist"]
+        fl = c.ptype == 0
+        c.pos[fl, :2] += rng.uniform(-amp * lo, amp * lo, size=(int(fl.sum()), 2))
+        return c
+    return f
+
+
 VARIANTS = {
     "slip": _v3(slip=1), "grad0": _v3(grad_type=0), "grad1": _v3(grad_type=1), "grad2": _v3(grad_type=2),
     "gradcorr": _v3(grad_type=3, grad_corr=True), "rep0": _v3(rep_type=0), "rep1": _v3(rep_type=1), "rep3": _v3(rep_type=3),
     "w1": _v3(weight_type=1), "w2": _v3(weight_type=2), "w3": _v3(weight_type=3), "w4": _v3(weight_type=4),
     "pnd0": _v3(pnd_type=0), "pnd1": _v3(pnd_type=1), "fs0": _v3(fs_type=0), "noshift": _v3(shifting=0), "shift1": _v3(shifting=1), "2d_shift1": _v2(shifting=1),
+    "dpc": _v3(collision=1), "2d_dpc": tuple(_jittered(b) for b in _v2(collision=1)),
     "relax": _v3(relax=0.7), "relax_grad0": _v3(relax=0.5, grad_type=0), "2d_relax": _v2(relax=0.6),
     "2d_grad3": _v2(grad_type=3, grad_corr=False), "2d_w3": _v2(weight_type=3), "2d_fs1": _v2(fs_type=1), "2d_pnd0": _v2(pnd_type=0),
 }
