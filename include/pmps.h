@@ -33,7 +33,7 @@ typedef struct PmpsParams {
 	/* options (enums as in include/MpsParticleSystem.h:20-124) */
 	int32_t dim;                    /* 2 or 3 ((int)PSystem->dim) */
 	int32_t wallType;               /* 0 particle walls, 1 polygon walls */
-	int32_t mpsType;                /* 0 E-MPS, 1 WC-MPS, 2 implicit PND, 3 implicit PND+divU */
+	int32_t mpsType;                /* 0 E-MPS, 1 WC-MPS, 2 implicit PND, 3 implicit PND + div(u) */
 	int32_t solverType;             /* 0 CG, 1 BiCGSTAB */
 	int32_t pndType;                /* 0 sum wij, 1 mean, 2 diffusive */
 	int32_t weightType;             /* 0..4 (src/MpsParticle.cpp:57-108) */
@@ -76,6 +76,7 @@ typedef struct PmpsParams {
 	double velMax;                  /* velMax carried in from the host (0 at start, src/MpsParticle.cpp:212) */
 	/* non-Newtonian rheology (fluidType 1), names as in include/MpsParticleSystem.h; src/MpsInputOutput.cpp:250-316 */
 	double KNM_VS1, KNM_VS2, DNS_SDT, PHI_1, PHI_2, cohes, MEU0, DG, I0, mm, Cd, VF_min, VF_max;
+	double relaxPND;                /* semi_implicit_mps.source_term.relax_pnd: the divergence part of the IMPLICIT_PND_DIVU source (src/MpsPressure.cpp:373) */
 	double timeCurrent;             /* time at pmps_create; the fused step advances its own copy by timeStep (src/main.cpp:463) */
 } PmpsParams;
 

@@ -465,7 +465,11 @@ void oracle_pnd_diffusive(const PmpsParams* P, PmpsHostArrays* A, const OBuckets
 	}
 }
 
-void oracle_wall_pnd_diffusive(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+static void wall_pnd_diffusive_impl(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, int divergence);
+void oracle_wall_pnd_diffusive(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) { wall_pnd_diffusive_impl(P, A, B, 0); }
+/* calcWallNoSlipVelDivergence / calcWallSlipVelDivergence, src/MpsPressure.cpp:554-788: the same sum, added to velDivergence */
+void oracle_wall_vel_divergence(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) { wall_pnd_diffusive_impl(P, A, B, 1); }
+static void wall_pnd_diffusive_impl(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, int divergence) {
 	PARFOR
 	for (int i = 0; i < A->numParticles; i++) {
 		const double ni = A->pndi[i];
@@ -492,7 +496,32 @@ void oracle_wall_pnd_diffusive(const PmpsParams* P, PmpsHostArrays* A, const OBu
 			if (P->slipCondition == 1) { ux = vi[0] - vm[0]; uy = vi[1] - vm[1]; uz = vi[2] - vm[2]; qx = ex; qy = ey; qz = ez; }   /* :580-583 */
 			div += ((double)P->dim / P->pndSmallZero) * (A->pndi[i] / ni) * (ux * qx + uy * qy + uz * qz) * wS / dd;
 		}
-		A->pndAuxVar1[i] += -A->pndi[i] * P->timeStep * div;
+		if (divergence) A->velDivergence[i] += div;
+		else A->pndAuxVar1[i] += -A->pndi[i] * P->timeStep * div;
+	}
+}
+
+void oracle_vel_divergence(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {   /* src/MpsPressure.cpp:479-551 */
+	PARFOR
+	for (int i = 0; i < A->numParticles; i++) {
+		A->velDivergence[i] = 0.0;
+		if (A->particleType[i] != P->fluid) continue;
+		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i; const double* vi = A->vel + 3 * (size_t)i;
+		const double ni = A->pndi[i]; double div = 0.0;
+		const double *c1 = A->correcMatrixRow1 + 3 * (size_t)i, *c2 = A->correcMatrixRow2 + 3 * (size_t)i, *c3 = A->correcMatrixRow3 + 3 * (size_t)i;
+		NEIGH_LOOP(P, A, B, xi, mi, {
+			if (PRED_P(P, P->reS2) && j != i) {
+				const double* vj = A->vel + 3 * (size_t)j;
+				const double ux = vj[0] - vi[0], uy = vj[1] - vi[1], uz = vj[2] - vi[2];
+				const double wS = wgt(sqrt(d2), P->reS, P->weightType);
+				if (!P->gradientCorrection) { if (ni > P->epsilonZero) div += ((double)P->dim / P->pndSmallZero) * (A->pndi[j] / ni) * (ux * rx + uy * ry + uz * rz) * wS / d2; }
+				else {
+					const double qx = (rx * c1[0] + ry * c1[1] + rz * c1[2]), qy = (rx * c2[0] + ry * c2[1] + rz * c2[2]), qz = (rx * c3[0] + ry * c3[1] + rz * c3[2]);
+					div += ((double)P->dim / P->pndSmallZero) * (ux * qx + uy * qy + uz * qz) * wS / d2;
+				}
+			}
+		});
+		A->velDivergence[i] = div;
 	}
 }
 
@@ -976,7 +1005,8 @@ int oracle_solve_ppe(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, 
 		const double rho = A->PTYPE[i] == 1 ? P->DNS_FL1 : P->DNS_FL2;
 		sum -= P->alphaCompressibility * rho / (P->timeStep * P->timeStep);
 		diag[i] = sum;
-		b[i] += -P->coeffPPESource * rho * (A->pndSmall[i] - P->pndSmallZero);
+		if (P->mpsType == 3) b[i] += -P->coeffPPESource * rho * (A->pndki[i] - P->pndSmallZero) + (1.0 - P->relaxPND) * rho * A->velDivergence[i] / P->timeStep;   /* src/MpsPressure.cpp:373 */
+		else b[i] += -P->coeffPPESource * rho * (A->pndSmall[i] - P->pndSmallZero);
 	}
 	/* column-compressed storage of A == row-compressed storage of A^T: bucket the off-diagonals by column j */
 	for (int k = 0; k < nnz; k++) cnt[tj[k] + 1]++;
@@ -1108,7 +1138,10 @@ void oracle_update_wall_dummy_vel(const PmpsParams* P, PmpsHostArrays* A, const 
 /* ------------------------------------------------------------------------------------------------ drivers */
 static void pressure_stage(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, int* it, double* err) {
 	if (P->mpsType == 0 || P->mpsType == 1) oracle_calc_press_eos(P, A);
-	else { const int k = oracle_solve_ppe(P, A, B, err); if (it) *it = k; }   /* mpsType 3 (PND+divU) is SURVEY §8f row 4 */
+	else {
+		if (P->mpsType == 3) { oracle_vel_divergence(P, A, B); if (P->wallType == 1) oracle_wall_vel_divergence(P, A, B); }   /* src/MpsPressure.cpp:44-56 */
+		const int k = oracle_solve_ppe(P, A, B, err); if (it) *it = k;
+	}
 }
 
 void oracle_init_step0(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMesh* meshes) {   /* src/main.cpp:121-180 */

@@ -48,6 +48,8 @@ void oracle_correction_matrix(const PmpsParams* P, PmpsHostArrays* A, const OBuc
 void oracle_pnd_neigh_npcd(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);     /* src/MpsPndNeigh.cpp:199-331 */
 void oracle_pnd_diffusive(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);      /* src/MpsPndNeigh.cpp:334-489 */
 void oracle_wall_pnd_diffusive(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B); /* src/MpsPndNeigh.cpp:492-744 */
+void oracle_vel_divergence(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);       /* src/MpsPressure.cpp:479-551 */
+void oracle_wall_vel_divergence(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);  /* src/MpsPressure.cpp:554-788 */
 void oracle_update_pnd(const PmpsParams* P, PmpsHostArrays* A);                            /* src/MpsPndNeigh.cpp:747-774 */
 void oracle_mean_pnd_wall_dummy_surface(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B); /* src/MpsPndNeigh.cpp:777-852 */
 void oracle_update_bc(const PmpsParams* P, PmpsHostArrays* A);                             /* src/MpsBoundaryCondition.cpp:66-399 */

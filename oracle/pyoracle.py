@@ -48,7 +48,7 @@ def _ip(a):
 class Oracle:
     """One simulation on the CPU oracle: params (ParticleSystem), HostState, buckets, meshes."""
 
-    STAGES_PAB = ["prediction_press_gradient", "calc_volume_fraction", "calc_viscosity", "collisions", "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive",
+    STAGES_PAB = ["vel_divergence", "wall_vel_divergence", "prediction_press_gradient", "calc_volume_fraction", "calc_viscosity", "collisions", "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive",
                   "wall_pnd_diffusive", "mean_pnd_wall_dummy_surface", "extrapolate_press", "press_gradient", "wall_viscosity",
                   "shifting", "wall_shifting", "update_wall_dummy_vel", "initial_pnd", "mean_wall_pnd", "mean_pnd",
                   "mean_neigh_fluid_pnd"]
@@ -139,6 +139,10 @@ class Oracle:
         if self.P.mpsType in (0, 1):
             self.calc_press_eos()
         else:
+            if self.P.mpsType == 3:   # IMPLICIT_PND_DIVU, src/MpsPressure.cpp:44-56
+                self.vel_divergence()
+                if self.P.wallType == 1:
+                    self.wall_vel_divergence()
             self.solve_ppe()
 
     def init_step0(self):

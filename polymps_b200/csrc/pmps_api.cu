@@ -217,7 +217,7 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	if (params->domainTypeBC != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: periodic domain boundaries are not on the device path yet (SURVEY 8f row 4)");
 	if (params->freeSurfType == 2) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: ARC free-surface detection is not on the device path yet (SURVEY 8f row 4)");
 	if (params->collisionType != 0 && params->collisionType != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: collisionType %d", params->collisionType);
-	if (params->mpsType == 3) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: IMPLICIT_PND_DIVU is not on the device path yet (SURVEY 8f row 4)");
+	if (params->mpsType < 0 || params->mpsType > 3) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: mpsType %d", params->mpsType);
 	if (params->numBucketsX < 1 || params->numBucketsY < 1 || params->numBucketsZ < 1 || !(params->bucketSide > 0.0)) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: bucket geometry not set");
 	const long long nB = (long long)params->numBucketsX * params->numBucketsY * params->numBucketsZ;
 	if (nB > 2000000000ll) return pmps_fail(nullptr, PMPS_E_OVERFLOW, "pmps_create: %lld buckets overflow int32", nB);

@@ -128,7 +128,8 @@ struct BPndDiffusive {
 };
 
 // MpsPndNeigh::calcWallNoSlipPndDiffusiveTerm / calcWallSlipPndDiffusiveTerm, src/MpsPndNeigh.cpp:492-744
-struct BWallPndDiffusive {
+// DIV = true: calcWallNoSlipVelDivergence / calcWallSlipVelDivergence (src/MpsPressure.cpp:554-788): the same sum, added to velDivergence
+template <bool DIV> struct BWallPndDiffusiveT {
 	typedef void wall_frame_tag;
 	struct Ctx { double ni, v[3], vm[3], div; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
@@ -156,7 +157,42 @@ struct BWallPndDiffusive {
 	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		const double ex = s.pi.x - s.mix, ey = s.pi.y - s.miy, ez = s.pi.z - s.miz; const double dd = sq3_exact(ex, ey, ez);
 		if (dd < K.p.reS2) c.div += term(c, K, s, c.v[0], c.v[1], c.v[2], ex, ey, ez, c.ni, dd);
-		S.pndAuxVar1[s.i] += -c.ni * K.p.timeStep * c.div;
+		if (DIV) S.velDivergence[s.i] += c.div;
+		else S.pndAuxVar1[s.i] += -c.ni * K.p.timeStep * c.div;
+	}
+};
+typedef BWallPndDiffusiveT<false> BWallPndDiffusive;
+typedef BWallPndDiffusiveT<true> BWallVelDivergence;
+
+// MpsPressure::calcVelDivergence, src/MpsPressure.cpp:479-551 (IMPLICIT_PND_DIVU): divergence of the velocity over P(reS), fluid particles
+struct BVelDivergence {
+	struct Ctx { double ni, vx, vy, vz, div; double m[9]; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (s.type != K.p.fluid) { if (s.lead) S.velDivergence[s.i] = 0.0; return false; }
+		c.ni = S.pndi[s.i];
+		const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z; c.div = 0.0;
+		if (K.p.gradientCorrection) {
+			c.m[0] = S.correcMatrixRow1.x[s.i]; c.m[1] = S.correcMatrixRow1.y[s.i]; c.m[2] = S.correcMatrixRow1.z[s.i];
+			c.m[3] = S.correcMatrixRow2.x[s.i]; c.m[4] = S.correcMatrixRow2.y[s.i]; c.m[5] = S.correcMatrixRow2.z[s.i];
+			c.m[6] = S.correcMatrixRow3.x[s.i]; c.m[7] = S.correcMatrixRow3.y[s.i]; c.m[8] = S.correcMatrixRow3.z[s.i];
+		}
+		return true;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_P<POLY>(q, K.p.reS2)) return;
+		const double ux = S.vx[q.j] - c.vx, uy = S.vy[q.j] - c.vy, uz = S.vz[q.j] - c.vz;
+		const double wS = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType) * (q.rinv * q.rinv);
+		if (!K.p.gradientCorrection) { if (c.ni > K.p.epsilonZero) c.div += S.pndi[q.j] * (ux * q.rx + uy * q.ry + uz * q.rz) * wS; }
+		else {
+			const double qx = q.rx * c.m[0] + q.ry * c.m[1] + q.rz * c.m[2], qy = q.rx * c.m[3] + q.ry * c.m[4] + q.rz * c.m[5], qz = q.rx * c.m[6] + q.ry * c.m[7] + q.rz * c.m[8];
+			c.div += (ux * qx + uy * qy + uz * qz) * wS;
+		}
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.div = gsum(c.div, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		double div = c.div * ((double)K.p.dim / K.p.pndSmallZero);
+		if (!K.p.gradientCorrection) div = c.ni > K.p.epsilonZero ? div / c.ni : 0.0;
+		S.velDivergence[s.i] = div;
 	}
 };
 

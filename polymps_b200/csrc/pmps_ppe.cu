@@ -74,7 +74,8 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ 
 		const double rho = pk_ptype(pi) == 1 ? K.p.DNS_FL1 : K.p.DNS_FL2;
 		sum -= K.p.alphaCompressibility * rho / (K.p.timeStep * K.p.timeStep);
 		M.diag[i] = sum;
-		b += -K.p.coeffPPESource * rho * (S.pndSmall[i] - K.p.pndSmallZero);
+		if (K.p.mpsType == 3) b += -K.p.coeffPPESource * rho * (S.pndki[i] - K.p.pndSmallZero) + (1.0 - K.p.relaxPND) * rho * S.velDivergence[i] / K.p.timeStep;   // src/MpsPressure.cpp:373
+		else b += -K.p.coeffPPESource * rho * (S.pndSmall[i] - K.p.pndSmallZero);
 	} else { M.diag[i] = 1.0; b = 0.0; }
 	S.sourceTerm[i] = b;
 }

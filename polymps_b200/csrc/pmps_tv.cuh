@@ -45,6 +45,8 @@ template <> struct NbFields<BCollision> { static constexpr unsigned value = NF_V
 template <> struct NbFields<BCollisionDPC> { static constexpr unsigned value = NF_VEL | NF_PRESS; };
 template <> struct NbFields<BPndDiffusive> { static constexpr unsigned value = NF_VEL | NF_PRESS | NF_PNDI | NF_RHO; };
 template <> struct NbFields<BWallPndDiffusive> { static constexpr unsigned value = NF_VEL | NF_PNDI; };
+template <> struct NbFields<BWallVelDivergence> { static constexpr unsigned value = NF_VEL | NF_PNDI; };
+template <> struct NbFields<BVelDivergence> { static constexpr unsigned value = NF_VEL | NF_PNDI; };
 template <> struct NbFields<BMeanPnd<0>> { static constexpr unsigned value = NF_PNDI; };
 template <> struct NbFields<BMeanPnd<1>> { static constexpr unsigned value = NF_PNDI; };
 template <> struct NbFields<BMeanWallPnd> { static constexpr unsigned value = NF_PNDI; };

@@ -79,7 +79,7 @@ PmpsParams params_of(MpsParticleSystem* S) {
 	C(coeffViscMultiphase) C(coeffPressGrad) C(coeffPressEMPS) C(coeffPressWCMPS) C(coeffShifting1) C(coeffShifting2)
 	C(coeffPPE) C(coeffPPESource) C(distCollisionLimit2) C(restitutionCollision) C(lambdaCollision) C(betaPnd)
 	C(betaNeigh) C(delta2) C(velMax)
-	C(KNM_VS1) C(KNM_VS2) C(DNS_SDT) C(PHI_1) C(PHI_2) C(cohes) C(MEU0) C(DG) C(I0) C(mm) C(Cd) C(VF_min) C(VF_max) C(timeCurrent)
+	C(KNM_VS1) C(KNM_VS2) C(DNS_SDT) C(PHI_1) C(PHI_2) C(cohes) C(MEU0) C(DG) C(I0) C(mm) C(Cd) C(VF_min) C(VF_max) C(relaxPND) C(timeCurrent)
 #undef C
 	p.fractionMethod = S->Fraction_method;
 	for (int k = 0; k < 3; k++) p.uniformVelWall[k] = S->uniformVelWall[k];

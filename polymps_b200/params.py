@@ -434,7 +434,7 @@ class PmpsParams(ctypes.Structure):
            "coeffPressGrad", "coeffPressEMPS", "coeffPressWCMPS", "coeffShifting1", "coeffShifting2", "coeffPPE",
            "coeffPPESource", "distCollisionLimit2", "restitutionCollision", "lambdaCollision", "betaPnd", "betaNeigh",
            "delta2", "velMax"]
-    _D3 = ["KNM_VS1", "KNM_VS2", "DNS_SDT", "PHI_1", "PHI_2", "cohes", "MEU0", "DG", "I0", "mm", "Cd", "VF_min", "VF_max", "timeCurrent"]
+    _D3 = ["KNM_VS1", "KNM_VS2", "DNS_SDT", "PHI_1", "PHI_2", "cohes", "MEU0", "DG", "I0", "mm", "Cd", "VF_min", "VF_max", "relaxPND", "timeCurrent"]
     _fields_ = ([(n, ctypes.c_int32) for n in _I] + [(n, ctypes.c_double) for n in _D]
                 + [("uniformVelWall", ctypes.c_double * 3)] + [(n, ctypes.c_double) for n in _D2 + _D3])
 

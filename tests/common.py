@@ -151,6 +151,8 @@ VARIANTS = {
     "gradcorr": _v3(grad_type=3, grad_corr=True), "rep0": _v3(rep_type=0), "rep1": _v3(rep_type=1), "rep3": _v3(rep_type=3),
     "w1": _v3(weight_type=1), "w2": _v3(weight_type=2), "w3": _v3(weight_type=3), "w4": _v3(weight_type=4),
     "pnd0": _v3(pnd_type=0), "pnd1": _v3(pnd_type=1), "fs0": _v3(fs_type=0), "noshift": _v3(shifting=0), "shift1": _v3(shifting=1), "2d_shift1": _v2(shifting=1),
+    "divu": _v3(incompressible=True, mps_type=3), "divu_slip": _v3(incompressible=True, mps_type=3, slip=1),
+    "2d_divu": _v2(incompressible=True, mps_type=3), "divu_nocorr": _v3(incompressible=True, mps_type=3, grad_corr=False, grad_type=3),
     "dpc": _v3(collision=1), "2d_dpc": tuple(_jittered(b) for b in _v2(collision=1)),
     "relax": _v3(relax=0.7), "relax_grad0": _v3(relax=0.5, grad_type=0), "2d_relax": _v2(relax=0.6),
     "2d_grad3": _v2(grad_type=3, grad_corr=False), "2d_w3": _v2(weight_type=3), "2d_fs1": _v2(fs_type=1), "2d_pnd0": _v2(pnd_type=0),

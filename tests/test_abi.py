@@ -27,8 +27,8 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_struct_layouts_match_header():
-    # sizes computed from the header: 30 int32 + (30 + 3 + 20 + 14) doubles; 2 int32 + 53 pointers
-    assert ctypes.sizeof(PmpsParams) == 30 * 4 + 67 * 8
+    # sizes computed from the header: 30 int32 + (30 + 3 + 20 + 15) doubles; 2 int32 + 53 pointers
+    assert ctypes.sizeof(PmpsParams) == 30 * 4 + 68 * 8
     assert ctypes.sizeof(PmpsHostArrays) == 8 + 8 * (7 + 1 + 18 + 14 + 13)
     assert ctypes.sizeof(PmpsScalars) == 56
 

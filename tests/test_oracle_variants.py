@@ -33,7 +33,8 @@ def test_oracle_matches_live_reference_on_option_variant(name):
             orc = _oracle_for(ps, st, meshes, prev)
             for call in stage_calls(stage, ps):
                 getattr(orc, call)()
-            bad = compare_states(st, cur, rtol=0.0, live_only=False)
+            ppe = stage == "calcPress" and ps.mpsType >= 2   # Eigen's dot products are SIMD-blocked: tolerance on the converged pressure
+            bad = compare_states(st, cur, rtol=1e-9 if ppe else 0.0, live_only=False)
             assert not bad, "%s step %d stage %s: %s" % (name, step, stage, bad)
             if stage == "correctionVelocityPosition":
                 assert orc.P.velMax == float(cur["scalars"][0])
