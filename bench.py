@@ -252,6 +252,16 @@ def main_gpu_slab(args, rank, world, local):
     e2e_steps = max(1, min(args.e2e_steps, args.steps))
 
     def roundtrip(first):
+        import time
+        tm = os.environ.get("PMPS_SLAB_TIMING") is not None and rank == 0
+        def tick(label, _t=[None]):
+            if not tm:
+                return
+            torch.cuda.synchronize(); now = time.perf_counter()
+            if _t[0] is not None:
+                print("[e2e] %-10s %.1f ms" % (label, 1e3 * (now - _t[0])), flush=True)
+            _t[0] = now
+        tick("start")
         with torch.cuda.stream(stream):
             if first:
                 T = se.backend.download_table(e2e_fields)
@@ -259,13 +269,18 @@ def main_gpu_slab(args, rank, world, local):
                     host[f].copy_(T[f], non_blocking=True)
                 eng.synchronize()
             T = {f: host[f].to(se.dev, non_blocking=True) for f in e2e_fields}
+            tick("h2d")
             se.backend.upload_table(T, se.dom.n_live, se.dom.n_own)
+        tick("upload")
         se.step(1)
+        tick("step")
         with torch.cuda.stream(stream):
             T = se.backend.download_table(e2e_fields)
+            tick("download")
             for f in e2e_fields:
                 host[f].copy_(T[f], non_blocking=True)
             eng.synchronize()
+        tick("d2h")
     roundtrip(True)
     barrier(); e0.record(stream)
     for _ in range(e2e_steps):

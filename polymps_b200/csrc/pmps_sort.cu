@@ -35,7 +35,17 @@ __global__ void k_cell_hist(const __grid_constant__ DevView S, const __grid_cons
 		cell = cell_index(K, ix, iy, iz);   // tile-major: the particles of a tile end up in consecutive slots
 	}
 	newCell[i] = cell;
-	arbRank[i] = atomicAdd(&cellCount[cell], 1);
+	// the ghost cell can hold millions of rows (the unused tail of a slab rank's table): one atomic per warp instead of one per row
+	const bool ghostRow = cell == S.nC;
+	const unsigned act = __activemask();
+	const unsigned gm = __ballot_sync(act, ghostRow);
+	if (ghostRow) {
+		const int lane = threadIdx.x & 31, leader = __ffs(gm) - 1;
+		int base = 0;
+		if (lane == leader) base = atomicAdd(&cellCount[cell], __popc(gm));
+		base = __shfl_sync(gm, base, leader);
+		arbRank[i] = base + __popc(gm & ((1u << lane) - 1u));
+	} else arbRank[i] = atomicAdd(&cellCount[cell], 1);
 }
 
 // ---- 2. exclusive scan of the histogram (3 kernels: per-block scan, scan of block sums, add) ------------------
@@ -98,6 +108,7 @@ __global__ void k_rank_fix(const __grid_constant__ DevView S, const int32_t* new
 	if (t >= S.n0) return;
 	const int2 me = tmp[t];
 	const int c = newCell[me.y]; const int s0 = cellStart[c], s1 = cellStart[c + 1];
+	if (c == S.nC) { perm[t] = me.y; return; }   // ghosts: no order to keep (and the count-the-smaller ranking is quadratic in the cell size)
 	int rank = 0;
 	for (int u = s0; u < s1; u++) rank += tmp[u].x < me.x;
 	perm[s0 + rank] = me.y;

@@ -29,6 +29,7 @@ same code over gloo with a host backend (tests/test_slab_host.py); `SlabEngine` 
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, List, Optional, Sequence
 
 import numpy as np
@@ -173,14 +174,28 @@ class SlabDomain:
         """Owners decide by x where each of their particles lives now.  The first call takes the rank's initial particles
         (all owned, any of them possibly outside the slab by less than one slab width) with their global ids."""
         b = self.b; dev = b.device; n0 = b.n0
+        timing = os.environ.get("PMPS_SLAB_TIMING") is not None
+        def tick(label, _t=[None]):
+            if not timing:
+                return
+            import time
+            if dev.type == "cuda":
+                torch.cuda.synchronize(dev)
+            now = time.perf_counter()
+            if _t[0] is not None and self.rank == 0:
+                print("[slab] repartition %-12s %.1f ms" % (label, 1e3 * (now - _t[0])), flush=True)
+            _t[0] = now
+        tick("start")
         if gid is not None:
             self.gid = gid.to(device=dev, dtype=torch.int64); self.n_own = int(n_own); self.n_live = int(n_own)
         T = b.download_table(self.fields)
+        tick("download")
         nO = self.n_own
         x = T["pos"][:nO, 0]
         false = torch.zeros(nO, dtype=torch.bool, device=dev)
         if self.grid is not None and self.world > 1:
             self._rebalance(x if "particleType" not in T else x[T["particleType"][:nO] != int(b.ghost_fill("particleType"))])
+            tick("rebalance")
         alive = T["particleType"][:nO] != int(b.ghost_fill("particleType")) if "particleType" in T else ~false   # removed by the out-of-domain test: dropped here
         goL = alive & (x < self.xlo) if self.left is not None else false
         goR = alive & (x >= self.xhi) if self.right is not None else false
@@ -203,7 +218,9 @@ class SlabDomain:
         self._exchange(cnt_out, cnt_in)
         cin = {s: [int(v) for v in cnt_in[s].cpu()] for s in ("L", "R")}
         inc = {s: torch.empty((cin[s][0] + cin[s][1], R), dtype=torch.float64, device=dev) for s in ("L", "R")}
+        tick("pack")
         self._exchange(out, inc)
+        tick("exchange")
         mig = {s: inc[s][:cin[s][0]] for s in ("L", "R")}; hal = {s: inc[s][cin[s][0]:] for s in ("L", "R")}
         n_stay = len(idx["stay"]); mL, mR = cin["L"][0], cin["R"][0]
         new_own = n_stay + mL + mR
@@ -239,7 +256,9 @@ class SlabDomain:
                          "R": i32(torch.cat([ar(n_stay + mL, mR), new_of_old[idx["nearR"]]]))}
         self.halo_first = {"L": new_own, "R": new_own + nHL}; self.halo_n = {"L": nHL, "R": nHR}
         self.n_own = new_own; self.n_live = n_live
+        tick("assemble")
         b.upload_table(newT, n_live, new_own)
+        tick("upload")
         self.stats["repartitions"] += 1; self.stats["migrants_out"] += len(idx["goL"]) + len(idx["goR"]); self.stats["halo"] = nHL + nHR
 
     def _rebalance(self, x_alive: torch.Tensor) -> None:
@@ -433,9 +452,18 @@ class SlabEngine:
                 if L.pmps_slab_wants_rebuild(h) == 1:
                     self.dom.repartition()
                 m = ctypes.c_uint(0)
+                timing = os.environ.get("PMPS_SLAB_TIMING") is not None and self.rank == 0
                 for ph in range(self.nph):
+                    if timing:
+                        import time
+                        torch.cuda.synchronize(self.dev); t0 = time.perf_counter()
                     self.eng._chk(L.pmps_step_phase(h, ph, ctypes.byref(m)))
+                    if timing:
+                        torch.cuda.synchronize(self.dev); t1 = time.perf_counter()
                     self.dom.refresh(int(m.value))
+                    if timing:
+                        torch.cuda.synchronize(self.dev); t2 = time.perf_counter()
+                        print("[slab] phase %d: kernels %.1f ms, refresh %.1f ms" % (ph, 1e3 * (t1 - t0), 1e3 * (t2 - t1)), flush=True)
                 self.eng._chk(L.pmps_slab_collect(h, self.scal.data_ptr()))
                 self.dom.all_max(self.scal)
                 self.eng._chk(L.pmps_slab_apply(h, self.scal.data_ptr()))
