@@ -127,6 +127,9 @@ int pmps_download(pmps_t* h, PmpsHostArrays* a);               /* scatter back t
 int pmps_get_scalars(pmps_t* h, PmpsScalars* out);
 int pmps_set_velmax(pmps_t* h, double velMax);
 int pmps_set_uniform_vel_wall(pmps_t* h, const double v[3]);
+/* one host-driven step: upload `in`, step once, download `out` (non-NULL arrays), the copies the step does not wait for
+ * overlapped with it on a second stream.  Same results as pmps_upload + pmps_step(h, 1) + pmps_download. */
+int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArrays* out);
 /* device-resident inputs (bench `value` leg, multi-GPU slabs): same layout as the host arrays, device pointers */
 int pmps_upload_device(pmps_t* h, const PmpsHostArrays* device_arrays);
 int pmps_download_device(pmps_t* h, PmpsHostArrays* device_arrays);   /* gather to host order into device arrays */

@@ -143,6 +143,8 @@ struct pmps_handle {
 	double lastShift = 0.0;              // largest shift of the last step's shifting passes
 	double* slabWork = nullptr; pmps_sum_fn slabSum = nullptr; pmps_refresh_fn slabRefresh = nullptr; void* slabUser = nullptr;   // pmps_slab_set_hooks
 	double meuMax = 0.0;                 // max MEU of the last rheology pass (CFLvisc)
+	cudaStream_t ioStream = nullptr; cudaEvent_t evIoUp = nullptr, evIoMid = nullptr; void* stage2 = nullptr;   // pmps_step_host: copies overlapped with the step
+	bool deferSync = false;              // download_impl: leave the stream running (the caller synchronises later)
 	bool slab = false;                   // slab mode: rebuilds and the step-end scalars are decided by the caller from GLOBAL maxima (pmps_slab.cu)
 	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
 	bool hitForce = false;               // positions were replaced from outside (upload): the next check rebuilds the hit list
@@ -186,6 +188,7 @@ int pmps_ensure_list(pmps_handle* h);
 int pmps_tv_prepare(pmps_handle* h);
 int pmps_tv_hits(pmps_handle* h);
 int pmps_ppe_solve(pmps_handle* h);
+int pmps_step_end_host(pmps_handle* h);   // step_end of the fused step + the time advance (pmps_stages.inc), for pmps_step_host
 int pmps_step_end_apply(pmps_handle* h, double disp2, double shift2);   // pmps_stages.inc: the host half of step_end
 int pmps_mesh_upload(pmps_handle* h, int mesh_id, int nV, const double* V, int nF, const int32_t* F, const double* N,
                      int nTable, const double* xP, const double* xN, const double* Z, const int32_t* nW);

@@ -172,6 +172,7 @@ static int download_impl(pmps_handle* h, PmpsHostArrays* a, bool deviceDst) {
 #define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_v3, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 24 * (size_t)n0); }
 	PMPS_V3_FIELDS(X)
 #undef X
+	if (h->deferSync) return PMPS_OK;   // pmps_step_host: this part rides on the copy stream while the step goes on
 	CUDA_TRY(h, cudaMemcpyAsync(h->h_flags, S.flags, sizeof(int32_t) * NFLAGS, cudaMemcpyDeviceToHost, h->stream));
 	CUDA_TRY(h, cudaStreamSynchronize(h->stream));
 	h->numParticles = h->h_flags[FLAG_LIVE];
@@ -181,3 +182,81 @@ static int download_impl(pmps_handle* h, PmpsHostArrays* a, bool deviceDst) {
 }
 extern "C" int pmps_download(pmps_t* h, PmpsHostArrays* a) { return download_impl(h, a, false); }
 extern "C" int pmps_download_device(pmps_t* h, PmpsHostArrays* a) { return download_impl(h, a, true); }
+
+// One host-driven time step: upload `in`, step, download `out` — with the copies that the step does not wait for riding on a second
+// stream.  What a step needs first (positions, velocities, mirror positions, types) goes ahead on the step's stream; press / pndi /
+// particleBC are first read by the PND pass (phase 2) and arrive on the copy stream while the viscosity / prediction / collision
+// passes run.  On the way back press / pndi / particleBC / mirrorParticlePos are final once the pressure is known (phase 5) and are
+// copied out while the gradient, correction and shifting passes run; positions, velocities and the rest follow at the end.
+// Same results as pmps_upload + pmps_step(1) + pmps_download (tests/test_gpu_parity.py::test_host_driven_loop_keeps_lists_and_results).
+extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArrays* out) {
+	if (!h || !in || !out) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	if (h->slab) return pmps_fail(h, PMPS_E_STATE, "pmps_step_host: slab handles are driven phase by phase");
+	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_step_host: upload the full particle state once with pmps_upload first");
+	if (!h->ioStream) {
+		if (cudaStreamCreateWithFlags(&h->ioStream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&h->evIoUp, cudaEventDisableTiming) != cudaSuccess ||
+		    cudaEventCreateWithFlags(&h->evIoMid, cudaEventDisableTiming) != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "pmps_step_host: stream / event creation failed");
+		void* q = nullptr;
+		if (cudaMalloc(&q, h->stageBytes) != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "pmps_step_host: second staging buffer (%zu bytes): %s", h->stageBytes, cudaGetErrorString(cudaGetLastError()));
+		h->allocs.push_back(q); h->stage2 = q;
+	}
+	PmpsHostArrays early = *in; early.press = nullptr; early.pndi = nullptr; early.particleBC = nullptr;
+	const int ood0 = h->h_flags ? h->h_flags[FLAG_OOD_TOTAL] : 0;
+	int rc = upload_impl(h, &early, false); if (rc) return rc;
+	const int n0 = h->numParticlesZero, T = 256, G = cdiv(n0, T);
+	char* s2 = (char*)h->stage2;
+	// late inputs: the copy engine brings them into the second staging buffer on the copy stream; the (tiny) scatter kernels run on the
+	// step's stream at the point of first use, so nothing has to squeeze in between the persistent walker kernels
+	const bool haveLate = in->press || in->pndi || in->particleBC;
+	if (haveLate) {
+		if (in->press) { pin_host(h, in->press, 8 * (size_t)n0); cudaMemcpyAsync(s2, in->press, 8 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
+		if (in->pndi) { pin_host(h, in->pndi, 8 * (size_t)n0); cudaMemcpyAsync(s2 + 8 * (size_t)n0, in->pndi, 8 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
+		if (in->particleBC) { pin_host(h, in->particleBC, 4 * (size_t)n0); cudaMemcpyAsync(s2 + 16 * (size_t)n0, in->particleBC, 4 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
+		cudaEventRecord(h->evIoUp, h->ioStream);
+	}
+	auto scatter_late = [&]() {
+		if (!haveLate) return;
+		cudaStreamWaitEvent(h->stream, h->evIoUp, 0);
+		DevView& S = h->V; const int32_t* soh = S.slotOfHost;
+		if (in->press) LAUNCH(h, "upload", k_up_f64, G, T, (const double*)s2, S.press, soh, n0);
+		if (in->pndi) LAUNCH(h, "upload", k_up_f64, G, T, (const double*)(s2 + 8 * (size_t)n0), S.pndi, soh, n0);
+		if (in->particleBC) LAUNCH(h, "upload", k_up_i32, G, T, (const int32_t*)(s2 + 16 * (size_t)n0), S.particleBC, soh, n0);
+	};
+	unsigned m = 0;
+	// the first two phases read these fields with the rheology, the prediction gradient or the dynamic collisions; and a step that
+	// re-sorts renumbers the slots the scatter writes into: then the scatter goes first
+	const PmpsParams& P = h->K.p;
+	const bool first = P.fluidType == 1 || P.relaxPress < 1.0 || P.collisionType == 1 || pmps_slab_wants_rebuild(h) == 1;
+	if (first) scatter_late();
+	for (int ph = 0; ph < 2; ph++) { rc = pmps_step_phase(h, ph, &m); if (rc) return rc; }
+	if (!first) scatter_late();
+	for (int ph = 2; ph < 6; ph++) { rc = pmps_step_phase(h, ph, &m); if (rc) return rc; }
+	// early outputs: gathered on the step's stream, copied out by the copy stream while phases 6-9 run
+	PmpsHostArrays mid, rest = *out; memset(&mid, 0, sizeof mid); mid.numParticles = out->numParticles; mid.numParticlesZero = out->numParticlesZero;
+	mid.press = out->press; mid.pndi = out->pndi; mid.particleBC = out->particleBC; mid.mirrorParticlePos = out->mirrorParticlePos;
+	const bool haveMid = mid.press || mid.pndi || mid.particleBC || mid.mirrorParticlePos;
+	if (haveMid) {
+		DevView& S = h->V; const int32_t* soh = S.slotOfHost;
+		double* gp = (double*)s2; double* gn = (double*)(s2 + 8 * (size_t)n0); int32_t* gb = (int32_t*)(s2 + 16 * (size_t)n0); double* gm = (double*)(s2 + 24 * (size_t)n0);
+		if (mid.press) LAUNCH(h, "download", k_dn_f64, G, T, gp, S.press, soh, n0);
+		if (mid.pndi) LAUNCH(h, "download", k_dn_f64, G, T, gn, S.pndi, soh, n0);
+		if (mid.particleBC) LAUNCH(h, "download", k_dn_i32, G, T, gb, S.particleBC, soh, n0);
+		if (mid.mirrorParticlePos) LAUNCH(h, "download", k_dn_v3, G, T, gm, S.mirrorParticlePos, soh, n0);
+		cudaEventRecord(h->evIoMid, h->stream); cudaStreamWaitEvent(h->ioStream, h->evIoMid, 0);
+		if (mid.press) { pin_host(h, mid.press, 8 * (size_t)n0); cudaMemcpyAsync(mid.press, gp, 8 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
+		if (mid.pndi) { pin_host(h, mid.pndi, 8 * (size_t)n0); cudaMemcpyAsync(mid.pndi, gn, 8 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
+		if (mid.particleBC) { pin_host(h, mid.particleBC, 4 * (size_t)n0); cudaMemcpyAsync(mid.particleBC, gb, 4 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
+		if (mid.mirrorParticlePos) { pin_host(h, mid.mirrorParticlePos, 24 * (size_t)n0); cudaMemcpyAsync(mid.mirrorParticlePos, gm, 24 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
+		rest.press = nullptr; rest.pndi = nullptr; rest.particleBC = nullptr; rest.mirrorParticlePos = nullptr;
+	}
+	for (int ph = 6; ph < pmps_step_phases(); ph++) { rc = pmps_step_phase(h, ph, &m); if (rc) return rc; }
+	rc = pmps_step_end_host(h); if (rc) return rc;
+	rc = download_impl(h, &rest, false); if (rc) return rc;   // synchronises the step's stream, reads the flags
+	if (cudaStreamSynchronize(h->ioStream) != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "pmps_step_host: copy stream: %s", cudaGetErrorString(cudaGetLastError()));
+	if (haveMid && h->h_flags[FLAG_OOD_TOTAL] != ood0) {   // a particle left the domain after the early copy: its rows changed, fetch them again
+		rc = download_impl(h, &mid, false); if (rc) return rc;
+	}
+	out->numParticles = h->numParticles;
+	return PMPS_OK;
+}

@@ -71,6 +71,7 @@ def load_library() -> ctypes.CDLL:
         getattr(L, "pmps_" + s).argtypes = [ctypes.c_void_p]
     L.pmps_step.argtypes = [ctypes.c_void_p, ctypes.c_int]
     L.pmps_upload.argtypes = [ctypes.c_void_p, ctypes.POINTER(PmpsHostArrays)]
+    L.pmps_step_host.argtypes = [ctypes.c_void_p, ctypes.POINTER(PmpsHostArrays), ctypes.POINTER(PmpsHostArrays)]
     L.pmps_upload_device.argtypes = [ctypes.c_void_p, ctypes.POINTER(PmpsHostArrays)]
     L.pmps_download.argtypes = [ctypes.c_void_p, ctypes.POINTER(PmpsHostArrays)]
     L.pmps_get_scalars.argtypes = [ctypes.c_void_p, ctypes.POINTER(PmpsScalars)]
@@ -164,6 +165,12 @@ class Engine:
     # ---- stepping
     def step(self, n: int = 1):
         self._chk(self.lib.pmps_step(self.h, int(n)))
+
+    def step_host(self, state, up_fields=None, down_fields=None):
+        """One host-driven step (pmps_step_host): upload `up_fields` of `state`, step, download `down_fields` into it, copies overlapped."""
+        a = state.c_struct(up_fields); b = state.c_struct(down_fields)
+        self._chk(self.lib.pmps_step_host(self.h, ctypes.byref(a), ctypes.byref(b)))
+        state.numParticles = b.numParticles
 
     def scalars(self, check: bool = True) -> PmpsScalars:
         s = PmpsScalars()

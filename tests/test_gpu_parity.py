@@ -264,6 +264,13 @@ def test_host_driven_loop_keeps_lists_and_results():
         del os.environ["PMPS_HARD_UPLOAD"]
     assert per_step < hard - 8, (per_step, hard)
     assert not compare_states(s2, sa, rtol=1e-9, skip=NOISY, scales=natural_scales(ps))
+    # the same loop through pmps_step_host (copies overlapped with the step on a second stream): bit-identical again
+    b3 = _engine(ps, meshes, st0.numParticlesZero); b3.upload(st0); b3.init_step0(); s3 = st0.copy(); b3.download(s3)
+    for _ in range(8):
+        b3.step_host(s3)
+    assert np.array_equal(sa.pos, s3.pos) and np.array_equal(sa.vel, s3.vel) and np.array_equal(sa.press, s3.press)
+    assert np.array_equal(sa.pndi, s3.pndi) and np.array_equal(sa.particleBC, s3.particleBC) and np.array_equal(sa.mirrorParticlePos, s3.mirrorParticlePos)
+    b3.close()
     # a particle turned into a ghost on the host: the upload notices the changed type word and the next step rebuilds
     sb.particleType[5] = ps.ghost
     b.upload(sb); b.step(1); b.download(sb)
