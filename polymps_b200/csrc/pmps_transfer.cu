@@ -198,7 +198,7 @@ extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArray
 		if (cudaStreamCreateWithFlags(&h->ioStream, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&h->evIoUp, cudaEventDisableTiming) != cudaSuccess ||
 		    cudaEventCreateWithFlags(&h->evIoMid, cudaEventDisableTiming) != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "pmps_step_host: stream / event creation failed");
 		void* q = nullptr;
-		if (cudaMalloc(&q, h->stageBytes) != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "pmps_step_host: second staging buffer (%zu bytes): %s", h->stageBytes, cudaGetErrorString(cudaGetLastError()));
+		if (cudaMalloc(&q, 80 * (size_t)h->numParticlesZero) != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "pmps_step_host: second staging buffer (%zu bytes): %s", h->stageBytes, cudaGetErrorString(cudaGetLastError()));
 		h->allocs.push_back(q); h->stage2 = q;
 	}
 	PmpsHostArrays early = *in; early.press = nullptr; early.pndi = nullptr; early.particleBC = nullptr;
@@ -250,11 +250,22 @@ extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArray
 		if (mid.mirrorParticlePos) { pin_host(h, mid.mirrorParticlePos, 24 * (size_t)n0); cudaMemcpyAsync(mid.mirrorParticlePos, gm, 24 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
 		rest.press = nullptr; rest.pndi = nullptr; rest.particleBC = nullptr; rest.mirrorParticlePos = nullptr;
 	}
-	for (int ph = 6; ph < pmps_step_phases(); ph++) { rc = pmps_step_phase(h, ph, &m); if (rc) return rc; }
+	rc = pmps_step_phase(h, 6, &m); if (rc) return rc;
+	// polygon walls: the velocities are final after the correction (phase 6; with particle walls the dummy velocities change in phase 9)
+	const bool velEarly = h->K.poly && rest.vel;
+	double* velOut = rest.vel;
+	if (velEarly) {
+		double* gv = (double*)(s2 + 48 * (size_t)n0);
+		LAUNCH(h, "download", k_dn_pack, G, T, gv, (int32_t*)nullptr, (int32_t*)nullptr, h->V.vel, h->V.slotOfHost, n0);
+		cudaEventRecord(h->evIoUp, h->stream); cudaStreamWaitEvent(h->ioStream, h->evIoUp, 0);
+		pin_host(h, velOut, 24 * (size_t)n0); cudaMemcpyAsync(velOut, gv, 24 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream);
+		rest.vel = nullptr; mid.vel = velOut;
+	}
+	for (int ph = 7; ph < pmps_step_phases(); ph++) { rc = pmps_step_phase(h, ph, &m); if (rc) return rc; }
 	rc = pmps_step_end_host(h); if (rc) return rc;
 	rc = download_impl(h, &rest, false); if (rc) return rc;   // synchronises the step's stream, reads the flags
 	if (cudaStreamSynchronize(h->ioStream) != cudaSuccess) return pmps_fail(h, PMPS_E_CUDA, "pmps_step_host: copy stream: %s", cudaGetErrorString(cudaGetLastError()));
-	if (haveMid && h->h_flags[FLAG_OOD_TOTAL] != ood0) {   // a particle left the domain after the early copy: its rows changed, fetch them again
+	if ((haveMid || velEarly) && h->h_flags[FLAG_OOD_TOTAL] != ood0) {   // a particle left the domain after the early copy: its rows changed, fetch them again
 		rc = download_impl(h, &mid, false); if (rc) return rc;
 	}
 	out->numParticles = h->numParticles;

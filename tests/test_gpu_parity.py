@@ -300,3 +300,20 @@ def test_option_variants_against_oracle(name):
         assert not bad, "%s step %d: %s" % (name, k, bad)
         assert abs(eng.scalars().velMax - orc.P.velMax) <= 1e-9 * max(orc.P.velMax, 1e-30)
     eng.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["w2", "i3"])
+def test_step_host_equals_resident_run(kind):
+    """pmps_step_host on particle walls (velocities final only after the dummy-velocity pass) and on the incompressible scheme
+    (pressure final after the Poisson solve): bit-identical to the device-resident run."""
+    case = _seeded_case(kind)
+    ps, meshes, st0 = _build(case)
+    a = _engine(ps, meshes, st0.numParticlesZero); a.upload(st0); a.init_step0(); a.step(5)
+    sa = st0.copy(); a.download(sa)
+    b = _engine(ps, meshes, st0.numParticlesZero); b.upload(st0); b.init_step0(); sb = st0.copy(); b.download(sb)
+    for _ in range(5):
+        b.step_host(sb)
+    for f in ("pos", "vel", "press", "pndi", "particleBC", "pressurePPE"):
+        assert np.array_equal(getattr(sa, f), getattr(sb, f)), f
+    a.close(); b.close()
