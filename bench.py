@@ -42,11 +42,31 @@ ALGO_BYTES = {
     "viscosity": 116, "collision": 104, "pnd_neigh_npcd": 160, "pnd_diffusive": 124, "press_gradient": 96, "wall.closest_point": 121,
     "predict": 172, "correct": 148, "update_bc": 48,
 }
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the round-1 `ncu --set full` captures at k = 171 (10.0 M particles),
-# profiles/r01_ncu_full_summaries.txt; used for roofline.traffic when the run has that size and --traffic is not given
-NCU_TRAFFIC_K171 = {"F3.pnd+diffusive": 5.613739e9 + 0.754892e9, "F1.viscosity+predict": 4.492037e9 + 1.947121e9,
-                    "F5.gradient": 3.306431e9 + 0.238906e9, "shift.concentration": 2.573800e9 + 0.082468e9}
+TRAFFIC_JSON = os.path.join(ROOT, "profiles", "r02_traffic.json")
 STEP_ALGO_BYTES = 1732   # sum over the fused groups G0..G7 + E1..E5 of the 3D WC polygon option set
+
+
+def build_id():
+    """sha256 over the kernel sources the library is built from: an ncu capture applies to a run only when both carry the same id."""
+    import hashlib
+    d = os.path.join(ROOT, "polymps_b200", "csrc"); h = hashlib.sha256()
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".inc", ".h")) or f == "Makefile":
+            h.update(f.encode()); h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def ncu_capture(kernel, n_particles):
+    """(traffic bytes per launch, fp64 pipe active %) of `kernel` from profiles/r02_traffic.json — an `ncu --set full` capture —
+    when it was taken on THIS build (same build_id) at this problem size; (None, None) otherwise: a citation is not a measurement."""
+    try:
+        d = json.load(open(TRAFFIC_JSON))
+    except Exception:
+        return None, None
+    if d.get("build_id") != build_id() or abs(d.get("particles", 0) - n_particles) > 0.02 * n_particles:
+        return None, None
+    e = d.get("kernels", {}).get(kernel)
+    return (e.get("dram_bytes"), e.get("fp64_active_pct")) if e else (None, None)
 
 
 def measured_peaks():
@@ -103,19 +123,23 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def block_case(k, jitter=0.0, inc=False):
+def block_case(k, jitter=0.0, inc=False, flow=True):
     from polymps_b200 import cases
-    return cases.dam3d_block(k, jitter=jitter, name="block%d" % k, incompressible=inc)
+    return cases.dam3d_block(k, flow=flow, jitter=jitter, name="block%d" % k, incompressible=inc)
+
+
+STATE_NOTE = {True: "MOVING initial state: vortex cells of ~40 lo, peak speed = expectMaxVelocity 2 sqrt(gH) = 0.086 lo per step (cases.flow_field), both arms",
+              False: "column at rest (hydrostatic start)"}
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm
-def run_reference_cpu(k, steps, warmup, threads):
+def run_reference_cpu(k, steps, warmup, threads, flow=True):
     """Times the reference's own CPU implementation on a bounded sample (block of 2k*k*k particles) of the workload.
     kind "reference": oracle/_ref/ref_driver = the unmodified reference sources driven through main.cpp's call order;
     kind "port": the C oracle when the reference binary is not present."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import refrun
-    case = block_case(k)
+    case = block_case(k, flow=flow)
     n = case.n
     if refrun.have_ref():
         from polymps_b200 import cases
@@ -146,7 +170,7 @@ def run_reference_cpu(k, steps, warmup, threads):
         t0 = time.time(); orc.step(steps); sec = time.time() - t0
         kind = "port"
     return {"value": n * steps / sec, "unit": UNIT, "cores": threads, "kind": kind,
-            "sample": "%d steps of a %dx%dx%d-particle dam-break block (%d particles), same option set" % (steps, 2 * k, k, k, n)}, sec
+            "sample": "%d steps (after %d warm-up) of a %dx%dx%d-particle dam-break block (%d particles), same option set, %s" % (steps, warmup, 2 * k, k, k, n, "moving initial state" if flow else "at rest")}, sec
 
 
 def main_reference(args):
@@ -154,11 +178,13 @@ def main_reference(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    cb, sec = run_reference_cpu(args.ref_k, args.steps, args.warmup, threads)
+    flow = args.state == "flow"
+    cb, sec = run_reference_cpu(args.ref_k, args.steps, args.warmup, threads, flow=flow)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": {"workload": "synthetic 3D WC dam-break block %dx%dx%d = %d particles per GPU, STL polygon tank (10 triangles), InputDamWC option set" % (2 * args.k, args.k, args.k, 2 * args.k ** 3),
-                                            "cpu_sample": "each step runs a %d-particle block of the same recipe (CPU throughput is size-insensitive, SURVEY 8d)" % (2 * args.ref_k ** 3)},
+                                            "state": STATE_NOTE[flow],
+                                            "cpu_sample": "each step runs a %d-particle block of the same recipe (CPU throughput is size-insensitive, SURVEY 8d; BASELINE.md section 3: k = 80)" % (2 * args.ref_k ** 3)},
             "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
@@ -184,10 +210,13 @@ def roofline_from_profile(prof, profile_steps, n_particles, ms_step, traffic):
     peak, peak_src, _ = measured_peaks()
     algo = ALGO_BYTES.get(top_name, 0) * n_particles
     achieved = algo / (top_avg_ms * 1e-3) / 1e9
-    if traffic is None and abs(n_particles - 10000422) < 800000:
-        traffic = NCU_TRAFFIC_K171.get(top_name)
+    cap_traffic, fp64 = ncu_capture(top_name, n_particles)
+    if traffic is None:
+        traffic = cap_traffic
     return {"bound": "hbm", "kernel": top_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": traffic, "peak_source": peak_src, "kernel_ms": top_avg_ms, "kernel_share_of_step": top[1] / profile_steps / max(step_prof_ms, 1e-9),
+            "traffic": traffic, "fp64_active": None if fp64 is None else fp64 / 100.0,
+            "traffic_source": ("profiles/r02_traffic.json (ncu --set full of this build, id %s)" % build_id()) if cap_traffic is not None else None,
+            "peak_source": peak_src, "kernel_ms": top_avg_ms, "kernel_share_of_step": top[1] / profile_steps / max(step_prof_ms, 1e-9),
             "algorithmic_bytes_per_particle": ALGO_BYTES.get(top_name, 0),
             "step": {"algorithmic_bytes_per_particle_step": STEP_ALGO_BYTES, "achieved_GBps": STEP_ALGO_BYTES * n_particles / (ms_step * 1e-3) / 1e9,
                      "frac": STEP_ALGO_BYTES * n_particles / (ms_step * 1e-3) / 1e9 / peak},
@@ -215,7 +244,8 @@ def main_gpu_slab(args, rank, world, local):
     cuts = choose_cuts(np.bincount(col, minlength=ps.numBucketsX) * (ny * nz), world)
     cuts_x = [ps.domainMinX + c * ps.bucketSide for c in cuts]
     mine = np.nonzero((xi >= cuts_x[rank]) & (xi < cuts_x[rank + 1]))[0]
-    loc = cases.dam3d_block_columns(kN, int(mine[0]), int(mine[-1]) + 1, lo=lo)
+    flow = args.state == "flow"
+    loc = cases.dam3d_block_columns(kN, int(mine[0]), int(mine[-1]) + 1, lo=lo, flow=flow)
     halo_est = int(2 * 3.6 * ny * nz)
     se = SlabEngine(ps, meshes, loc, cuts_x, rank, world, device=local, capacity=len(loc["ptype"]) + 6 * halo_est + 200000, cuts=cuts)
     del loc
@@ -226,14 +256,14 @@ def main_gpu_slab(args, rank, world, local):
         torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
 
     sampler = ClockSampler(local)
-    l0 = eng.launch_count(); st0 = dict(se.dom.stats)
+    l0 = eng.launch_count(); st0 = dict(se.dom.stats); c0 = eng.counters()
     barrier(); sampler.start()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     e0.record(stream); se.step(args.steps); e1.record(stream)
     eng.synchronize(); barrier()
     clocks = sampler.stop()
     ms_local = e0.elapsed_time(e1)
-    launches = eng.launch_count() - l0
+    launches = eng.launch_count() - l0; c1 = eng.counters()
     st1 = dict(se.dom.stats)
     n_own = se.n_own
     t = torch.tensor([ms_local], dtype=torch.float64, device="cuda"); cnt = torch.tensor([float(n_own)], dtype=torch.float64, device="cuda")
@@ -249,7 +279,7 @@ def main_gpu_slab(args, rank, world, local):
     # end to end with HOST buffers: every step sends the carried state of the rank's table from pinned host memory, steps, reads it back
     e2e_fields = [f for f in E2E_UP]
     host = {f: torch.empty((se.backend.n0, 3) if field_width(f) == 3 else (se.backend.n0,), dtype=field_dtype(f)).pin_memory() for f in e2e_fields}
-    e2e_steps = max(1, min(args.e2e_steps, args.steps))
+    e2e_steps = max(1, args.e2e_steps)
 
     def roundtrip(first):
         import time
@@ -293,13 +323,15 @@ def main_gpu_slab(args, rank, world, local):
     per_rank = [None] * world
     dist.all_gather_object(per_rank, {"owned": n_own, "halo": se.dom.n_live - n_own, "ms_per_step": ms_local / args.steps,
                                       "repartitions": st1["repartitions"] - st0["repartitions"], "migrants_out": st1["migrants_out"] - st0["migrants_out"],
+                                      "bucket_rebuilds": c1["bucket_rebuilds"] - c0["bucket_rebuilds"], "hit_refilters": c1["hit_refilters"] - c0["hit_refilters"],
                                       "halo_refresh_MB_per_step": (st1["refresh_bytes"] - st0["refresh_bytes"]) / args.steps / 1e6})
     inc = args.scheme == "inc"
     line = {"metric": METRIC if not inc else "particle-steps/sec (3D INC dam break: PPE assembly + Jacobi-CG)", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "synthetic 3D %s dam-break block %dx%dx%d = %d particles over %d GPUs (%.2fM per GPU), STL polygon tank (10 triangles), %s option set" % ("INC" if inc else "WC", nx, ny, nz, int(total), world, total / world / 1e6, "InputDamINC" if inc else "InputDamWC"),
-                       "cg_iterations_last_step": sc.solverIter if inc else None,
-                       "particles_total": int(total), "parallelism": "%d x-slabs cut on bucket columns, one rank per GPU; halo refresh after every phase + migration at rebuilds over NCCL send/recv; 3 scalars MAX-all-reduced per step" % world,
+                       "state": STATE_NOTE[flow], "cg_iterations_last_step": sc.solverIter if inc else None,
+                       "bucket_rebuilds": c1["bucket_rebuilds"] - c0["bucket_rebuilds"], "hit_refilters": c1["hit_refilters"] - c0["hit_refilters"],
+                       "particles_total": int(total), "build_id": build_id(), "parallelism": "%d x-slabs cut on bucket columns, one rank per GPU; halo refresh after every phase + migration at rebuilds over NCCL send/recv; 3 scalars MAX-all-reduced per step" % world,
                        "l2": "state per GPU (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (se.dom.n_live * 1500 / 1e9),
                        "ranks": per_rank, "max_displacement_over_lo": sc.maxDisplacement / ps.partDist},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline}
@@ -325,7 +357,8 @@ def main_gpu(args):
         return main_gpu_slab(args, rank, world, local)
     from polymps_b200.engine import make_engine
 
-    case = block_case(args.k, inc=args.scheme == "inc")
+    flow = args.state == "flow"
+    case = block_case(args.k, inc=args.scheme == "inc", flow=flow)
     ps, meshes, st, eng = make_engine(case, device=local)
     n = st.numParticles
     stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
@@ -340,60 +373,78 @@ def main_gpu(args):
         torch.cuda.synchronize()
 
     sampler = ClockSampler(local)
-    l0 = eng.launch_count()
+    l0 = eng.launch_count(); c0 = eng.counters()
     barrier(); sampler.start()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     e0.record(stream); eng.step(args.steps); e1.record(stream)
     eng.synchronize(); barrier()
     clocks = sampler.stop()
     ms = e0.elapsed_time(e1)
-    launches = eng.launch_count() - l0
+    launches = eng.launch_count() - l0; c1 = eng.counters()
     sc = eng.scalars()
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    cnt = torch.tensor([float(sc.numParticles)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    ms = float(t.item()); total_particles = float(cnt.item())
+    total_particles = float(sc.numParticles)
     value = total_particles * args.steps / (ms * 1e-3)
 
     # per-kernel device time (CUDA events around every launch on the step stream; separate pass: it serialises)
+    cp0 = eng.counters()
     eng.profile(True); eng.step(args.profile_steps); prof = eng.profile_get(); eng.profile(False)
+    cp1 = eng.counters()
     roofline = roofline_from_profile(prof, args.profile_steps, sc.numParticles, ms / args.steps, args.traffic)
+    roofline["profile_pass"] = {"steps": args.profile_steps, "bucket_rebuilds": cp1["bucket_rebuilds"] - cp0["bucket_rebuilds"], "hit_refilters": cp1["hit_refilters"] - cp0["hit_refilters"]}
 
     # end to end through the C ABI with HOST buffers: every step uploads the carried state, steps, and reads it back
-    e2e_steps = max(1, min(args.e2e_steps, args.steps))
-    eng.download(st)   # host copy of the current state (also pins the host arrays)
-    eng.step_host(st, E2E_UP, E2E_DOWN)   # warm: pinning + first touch
+    e2e_steps = max(1, args.e2e_steps)
+    eng.download(st)   # host copy of the current state
+    eng.register_host(st, sorted(set(E2E_UP + E2E_DOWN)))   # explicit opt-in: the library never pins caller memory by itself
+    eng.step_host(st, E2E_UP, E2E_DOWN)   # warm: first touch
+    ce0 = eng.counters()
     barrier()
     e0.record(stream)
     for _ in range(e2e_steps):
         eng.step_host(st, E2E_UP, E2E_DOWN)
     e1.record(stream); eng.synchronize(); barrier()
     ms_e = e0.elapsed_time(e1)
-    te = torch.tensor([ms_e], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    ce1 = eng.counters()
     sc2 = eng.scalars()
-    e2e = {"value": total_particles * e2e_steps / (float(te.item()) * 1e-3), "unit": UNIT, "steps": e2e_steps,
-           "h2d_bytes_per_step": field_bytes(st, E2E_UP) * world, "d2h_bytes_per_step": field_bytes(st, E2E_DOWN) * world,
-           "api": "pmps_step_host(in, out) per step: upload of the carried state, one step, download — the copies the step does not wait for ride on a second stream; host arrays pinned in place"}
+    e2e = {"value": total_particles * e2e_steps / (ms_e * 1e-3), "unit": UNIT, "steps": e2e_steps,
+           "h2d_bytes_per_step": field_bytes(st, E2E_UP), "d2h_bytes_per_step": field_bytes(st, E2E_DOWN),
+           "bucket_rebuilds": ce1["bucket_rebuilds"] - ce0["bucket_rebuilds"], "hit_refilters": ce1["hit_refilters"] - ce0["hit_refilters"],
+           "api": "pmps_step_host(in, out) per step: upload of the carried state, one step, download — the copies the step does not wait for ride on a second stream; host arrays registered once with pmps_register_host"}
+    eng.close()
+
+    # the same block AT REST (round 1's headline regime: no rebuild ever falls into the timed region), for comparison
+    at_rest = None
+    if flow and args.rest_steps > 0:
+        case.vel[:] = 0.0
+        ps_r, _, st_r, eng_r = make_engine(case, device=local)
+        stream_r = torch.cuda.ExternalStream(eng_r.stream, device=torch.device("cuda", local))
+        eng_r.init_step0(); eng_r.step(args.warmup); eng_r.synchronize(); r0 = eng_r.counters()
+        barrier(); e0.record(stream_r); eng_r.step(args.rest_steps); e1.record(stream_r); eng_r.synchronize(); barrier()
+        r1 = eng_r.counters(); ms_r = e0.elapsed_time(e1)
+        at_rest = {"value": float(eng_r.scalars().numParticles) * args.rest_steps / (ms_r * 1e-3), "ms_per_step": ms_r / args.rest_steps, "steps": args.rest_steps,
+                   "bucket_rebuilds": r1["bucket_rebuilds"] - r0["bucket_rebuilds"], "hit_refilters": r1["hit_refilters"] - r0["hit_refilters"]}
+        eng_r.close(); del st_r
 
     line = {"metric": METRIC if args.scheme == "wc" else "particle-steps/sec (3D INC dam break: PPE assembly + Jacobi-CG)", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "synthetic 3D %s dam-break block %dx%dx%d = %d particles per GPU, STL polygon tank (10 triangles), %s option set" % (args.scheme.upper(), 2 * args.k, args.k, args.k, n, "InputDamWC" if args.scheme == "wc" else "InputDamINC"),
+                       "state": STATE_NOTE[flow],
+                       "bucket_rebuilds": c1["bucket_rebuilds"] - c0["bucket_rebuilds"], "hit_refilters": c1["hit_refilters"] - c0["hit_refilters"],
+                       "at_rest_value": None if at_rest is None else at_rest["value"], "at_rest": at_rest,
                        "cg_iterations_last_step": sc2.solverIter if args.scheme == "inc" else None,
                        "particles_per_gpu": n, "parallelism": "1 GPU",
                        "l2": "state per GPU (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (n * 1500 / 1e9),
-                       "max_displacement_over_lo": sc2.maxDisplacement / ps.partDist, "max_bucket_count": sc2.maxBucketCount},
+                       "max_displacement_over_lo": sc2.maxDisplacement / ps.partDist, "max_bucket_count": sc2.maxBucketCount, "vel_max": sc2.velMax,
+                       "build_id": build_id()},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline}
     if rank == 0 and world == 1 and not args.no_cpu:
-        cb, _ = run_reference_cpu(args.cpu_k, args.cpu_steps, 1, os.cpu_count() or 1)
+        cb, _ = run_reference_cpu(args.cpu_k, args.cpu_steps, 2, os.cpu_count() or 1, flow=flow)
+        if args.cpu1_k > 0:   # the deterministic 1-thread figure next to the all-cores one
+            c1t, _ = run_reference_cpu(args.cpu1_k, 2, 1, 1, flow=flow)
+            cb["one_thread"] = {"value": c1t["value"], "sample": c1t["sample"]}
         line["cpu_baseline"] = cb
     if rank == 0:
         print(json.dumps(line), flush=True)
-    eng.close()
-    if world > 1:
-        dist.destroy_process_group()
 
 
 def main():
@@ -404,10 +455,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scheme", default="wc", choices=["wc", "inc"], help="wc = the BASELINE.json metric (default); inc = the incompressible configuration (#3), single GPU, reported under profiles/")
     ap.add_argument("--k", type=int, default=171, help="block edge: 2k x k x k particles per GPU (171 -> 10.0M)")
-    ap.add_argument("--ref-k", type=int, default=50, help="block edge of the CPU sample for --impl reference")
-    ap.add_argument("--cpu-k", type=int, default=40, help="block edge of the cpu_baseline sample")
-    ap.add_argument("--cpu-steps", type=int, default=3)
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--state", default="flow", choices=["flow", "rest"], help="flow (default): the moving initial state both arms start from; rest: the column at rest")
+    ap.add_argument("--rest-steps", type=int, default=20, help="timed steps of the at-rest comparison run (config.at_rest_value); 0 skips it")
+    ap.add_argument("--ref-k", type=int, default=80, help="block edge of the CPU sample for --impl reference (80 -> 1.02 M particles, BASELINE.md section 3)")
+    ap.add_argument("--cpu-k", type=int, default=80, help="block edge of the cpu_baseline sample")
+    ap.add_argument("--cpu-steps", type=int, default=10)
+    ap.add_argument("--cpu1-k", type=int, default=40, help="block edge of the 1-thread CPU figure (0 skips it)")
+    ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--profile-steps", type=int, default=2)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--traffic", type=float, default=None, help="dram bytes per launch of the top kernel from an ncu --set full capture (profiles/)")

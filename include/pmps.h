@@ -17,6 +17,7 @@
  */
 #ifndef PMPS_H_
 #define PMPS_H_
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -125,6 +126,14 @@ int pmps_set_mesh(pmps_t* h, int mesh_id, int nV, const double* V, int nF, const
 int pmps_upload(pmps_t* h, const PmpsHostArrays* a);           /* all non-NULL arrays, host (reference) order */
 int pmps_download(pmps_t* h, PmpsHostArrays* a);               /* scatter back to host order; non-NULL arrays only */
 int pmps_get_scalars(pmps_t* h, PmpsScalars* out);
+/* Optional: page-lock a host array the caller will pass to pmps_upload / pmps_download / pmps_step_host again and again, so the
+ * copies run as asynchronous DMA (about 2x the pageable rate).  The library never pins caller memory on its own.  CONTRACT: the
+ * range must stay allocated, at this address, until pmps_unregister_host(ptr) or pmps_destroy; freeing or reallocating a
+ * registered array first is undefined behaviour (the driver keeps a stale registration).  Arrays the caller already pinned
+ * (cudaHostAlloc / cudaHostRegister) are accepted and left alone.  The reference's MpsParticle arrays are malloc'd once and
+ * never freed (src/MpsInputOutput.cpp:667-750, empty destructors src/MpsParticle.cpp:20-22): the shim registers them. */
+int pmps_register_host(pmps_t* h, void* ptr, size_t bytes);
+int pmps_unregister_host(pmps_t* h, void* ptr);
 int pmps_set_velmax(pmps_t* h, double velMax);
 int pmps_set_uniform_vel_wall(pmps_t* h, const double v[3]);
 /* one host-driven step: upload `in`, step once, download `out` (non-NULL arrays), the copies the step does not wait for
@@ -213,6 +222,10 @@ int pmps_debug_neighbors(pmps_t* h, int i, int kind, int32_t* out, int cap);
 int pmps_profile_enable(pmps_t* h, int on);
 int pmps_profile_get(pmps_t* h, int* n, const char*** names, const float** ms_total, const int** launches);
 int pmps_launch_count(pmps_t* h, long long* launches); /* kernels launched by this handle so far */
+/* work counters of the temporal caches (bench.py reports their deltas over the timed region): out[0] bucket-order rebuilds (sort +
+ * Verlet list; the reference does src/MpsBucket.cpp:299-353 every step), out[1] hit-list refilters, out[2] fused steps, out[3] 1 if
+ * a step ever ended with a particle beyond the search slack (sticky until the next pmps_upload) */
+int pmps_get_counters(pmps_t* h, long long out[4]);
 void* pmps_stream(pmps_t* h);                    /* cudaStream_t the stages run on */
 int pmps_synchronize(pmps_t* h);                 /* wait for everything queued on the handle's stream */
 

@@ -123,12 +123,54 @@ def dam3d(nx: int, ny: int, nz: int, *, lo: float = 0.01, incompressible: bool =
                 meta={"tank": tank, "H": H, "c0": c0})
 
 
-def dam3d_block(k: int, **kw) -> Case:
-    """The benchmark block of SURVEY.md §8d: fluid column 2k x k x k (k=171 -> 10.0M, 292 -> 49.8M, 464 -> 199.8M)."""
-    return dam3d(2 * k, k, k, **kw)
+def flow_field(pos: np.ndarray, *, Lc: float, H: float, W: float, vmax: float, lo: float, cell: float = 40.0) -> np.ndarray:
+    """The MOVING initial state of the benchmark block (both arms start from it): counter-rotating vortex cells of about
+    `cell` particle spacings in the x-z plane, peak speed vmax (= expectMaxVelocity of the case, 2 sqrt(g H): at the block's
+    time step a particle then moves 0.086 lo per step, so the bucket order of the GPU path is rebuilt every 2-3 steps and the
+    reference's per-step re-bucketing does real work too).  Stream function psi = A sin(mx pi x/Lc) sin(mz pi z/H) g(y):
+    divergence-free, tangential at the tank floor, the left wall and the column's free faces; g(y) = 0.6 + 0.4 cos(2 pi my y/W)
+    makes it vary across the tank.  Deterministic, no RNG."""
+    mz = max(1, int(round(H / (cell * lo)))); mx = max(1, int(round(Lc / (cell * lo)))); my = max(1, int(round(W / (2.0 * cell * lo))))
+    kx = mx * math.pi / Lc; kz = mz * math.pi / H
+    A = vmax / max(kx, kz)
+    x, y, z = pos[:, 0], pos[:, 1], pos[:, 2]
+    g = 0.6 + 0.4 * np.cos(2.0 * math.pi * my * y / W)
+    v = np.zeros_like(pos)
+    v[:, 0] = A * kz * np.sin(kx * x) * np.cos(kz * z) * g
+    v[:, 2] = -A * kx * np.cos(kx * x) * np.sin(kz * z) * g
+    return v
 
 
-def dam3d_block_columns(k: int, i0: int, i1: int, *, lo: float = 0.01):
+def dam3d_block(k: int, flow: bool = False, **kw) -> Case:
+    """The benchmark block of SURVEY.md §8d: fluid column 2k x k x k (k=171 -> 10.0M, 292 -> 49.8M, 464 -> 199.8M).
+    flow=True: the moving initial state (flow_field) instead of the column at rest."""
+    c = dam3d(2 * k, k, k, **kw)
+    if flow:
+        lo = c.options["numerical"]["particle_dist"]
+        c.vel = flow_field(c.pos, Lc=2 * k * lo, H=k * lo, W=k * lo, vmax=c.options["numerical"]["wall_repulsive_force"]["maxVel"], lo=lo)
+        c.meta["flow"] = True
+    return c
+
+
+def dam3d_splash(nx: int, ny: int, nz: int, *, lo: float = 0.01, seed: int = 3, name: str | None = None, **kw) -> Case:
+    """Particles LEAVE the domain: a dam3d column under a low open top (tank barely higher than the column) whose whole top layer
+    flies upwards at staggered speeds, so that in every one of the three out-of-domain checks of the next few steps some particles
+    cross z = domainMax - bucketSide (src/MpsParticle.cpp:286-296).  The top layer ends the particle array (x fastest, then y,
+    then z), so the LAST live particle is among the leavers: the reference's serial swap-with-last loop copies a particle that is
+    itself outside over a hole and does not re-test it in the same call (src/MpsParticle.cpp:298-396) — the order-dependent detail
+    SURVEY H5 names."""
+    tank = ((1.61 / 0.6) * nx * lo, ny * lo, (nz + 1.5) * lo)
+    c = dam3d(nx, ny, nz, lo=lo, jitter=0.05, name=name or "splash", tank=tank, **kw)
+    dt = c.options["numerical"]["time_step"]
+    bucket = max(c.options["numerical"]["effective_radius"].values()) * lo * (1.0 + c.options["numerical"]["CFL_number"])
+    top = c.pos[:, 2] > (nz - 1) * lo
+    dist = (tank[2] + 3.0 * lo) - bucket - c.pos[:, 2]   # the reference pads the domain by 3 lo (src/MpsParticle.cpp:139-144)
+    rng = np.random.default_rng(seed)
+    c.vel[top, 2] = dist[top] / dt / rng.uniform(0.8, 3.2, size=int(top.sum()))
+    return c
+
+
+def dam3d_block_columns(k: int, i0: int, i1: int, *, lo: float = 0.01, flow: bool = False):
     """Lattice columns i0 <= i < i1 (along x) of the benchmark block dam3d_block(k), without building the whole block:
     (ptype, pos, vel, press, gid) with gid = the particle's index in dam3d_block(k)'s order (x fastest, then y, then z).
     A slab rank generates only its own part of a 50M / 200M-particle block this way (polymps_b200/slab.py)."""
@@ -138,7 +180,10 @@ def dam3d_block_columns(k: int, i0: int, i1: int, *, lo: float = 0.01):
     i = i.ravel(); j = j.ravel(); m = m.ravel()
     pos = np.stack([(i + 0.5) * lo, (j + 0.5) * lo, (m + 0.5) * lo], axis=1)
     n = len(pos)
-    return {"ptype": np.zeros(n, dtype=np.int32), "pos": np.ascontiguousarray(pos), "vel": np.zeros((n, 3)), "press": np.zeros(n),
+    vel = np.zeros((n, 3))
+    if flow:
+        vel = flow_field(pos, Lc=nx * lo, H=nz * lo, W=ny * lo, vmax=2.0 * math.sqrt(9.81 * nz * lo), lo=lo)
+    return {"ptype": np.zeros(n, dtype=np.int32), "pos": np.ascontiguousarray(pos), "vel": vel, "press": np.zeros(n),
             "gid": (m * ny + j) * nx + i}
 
 

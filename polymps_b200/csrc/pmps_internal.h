@@ -152,6 +152,8 @@ struct pmps_handle {
 	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;
 	long long launches = 0;
+	long long nRebuilds = 0, nStepsDone = 0;   // pmps_get_counters: bucket-order rebuilds (sort + Verlet list) and fused steps so far
+	double guardWorst = 0.0;             // sticky: largest displacement since a rebuild that exceeded the search slack (0: never); cleared by pmps_upload
 	int oodTotal = 0, maxCell = 0;
 	std::string err;
 	std::vector<std::pair<void*, size_t>> registered;   // host ranges pinned with cudaHostRegister

@@ -73,11 +73,29 @@ __global__ void k_dn_pack(double* xyz, int32_t* type, int32_t* ptype, const doub
 }
 __global__ void k_set_live(const __grid_constant__ DevView S, int live) { S.flags[FLAG_LIVE] = live; }
 
-static void pin_host(pmps_handle* h, const void* p, size_t bytes) {
-	if (!p || bytes < (1u << 16)) return;
-	for (auto& r : h->registered) if (r.first == p && r.second >= bytes) return;
-	if (cudaHostRegister(const_cast<void*>(p), bytes, cudaHostRegisterDefault) == cudaSuccess) h->registered.push_back({ const_cast<void*>(p), bytes });
-	else cudaGetLastError();   // not fatal (already pinned by the caller, or not registrable): the copy still works
+// Caller memory is never page-locked behind the caller's back: a transfer from pageable memory is correct (the driver stages it),
+// a caller that wants the asynchronous DMA path registers its arrays once (pmps_register_host) and owns their lifetime.
+extern "C" int pmps_register_host(pmps_t* h, void* p, size_t bytes) {
+	if (!h || !p || !bytes) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	for (auto& r : h->registered) if (r.first == p) {
+		if (r.second >= bytes) return PMPS_OK;
+		return pmps_fail(h, PMPS_E_ARG, "pmps_register_host: %p is registered with %zu bytes, asked for %zu: unregister it first", p, r.second, bytes);
+	}
+	const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterDefault);
+	if (e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return PMPS_OK; }   // pinned by the caller itself: nothing to own
+	if (e != cudaSuccess) { cudaGetLastError(); return pmps_fail(h, PMPS_E_CUDA, "pmps_register_host(%p, %zu): %s", p, bytes, cudaGetErrorString(e)); }
+	h->registered.push_back({ p, bytes });
+	return PMPS_OK;
+}
+extern "C" int pmps_unregister_host(pmps_t* h, void* p) {
+	if (!h || !p) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	for (size_t k = 0; k < h->registered.size(); k++) if (h->registered[k].first == p) {
+		cudaStreamSynchronize(h->stream); if (h->ioStream) cudaStreamSynchronize(h->ioStream);   // no copy may still be using the pages
+		cudaHostUnregister(p); h->registered.erase(h->registered.begin() + k); return PMPS_OK;
+	}
+	return PMPS_OK;   // not ours (never registered here, or pinned by the caller)
 }
 
 static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) {
@@ -91,7 +109,6 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 	auto src = [&](const void* p, size_t bytes, size_t off) -> const void* {
 		if (!p) return nullptr;
 		if (deviceSrc) return p;
-		pin_host(h, p, bytes);
 		cudaMemcpyAsync(st + off, p, bytes, cudaMemcpyHostToDevice, h->stream);
 		return st + off;
 	};
@@ -119,6 +136,7 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 	LAUNCH(h, "upload", k_set_live, 1, 1, S, a->numParticles);
 	CUDA_TRY(h, cudaGetLastError());
 	h->numParticles = a->numParticles; h->haveState = true;
+	if (a->pos) h->guardWorst = 0.0;   // a new state from the caller: the sticky guard flag of the old one goes
 	if (a->particleNearWall) h->tileWallValid = false;
 	if (a->pos && soft) {
 		// the bucket order and the candidate lists survive an upload that moves nobody beyond their guards (a host-driven loop
@@ -147,7 +165,7 @@ static int download_impl(pmps_handle* h, PmpsHostArrays* a, bool deviceDst) {
 	DevView& S = h->V; const int32_t* soh = S.slotOfHost;
 	// two staging halves so the gather of field k+1 can be queued behind the copy-out of field k
 	char* half[2] = { (char*)h->stage, (char*)h->stage + 32 * (size_t)n0 }; int hb = 0;
-	auto out = [&](void* dstHost, const void* stg, size_t bytes) { if (deviceDst) return; pin_host(h, dstHost, bytes); cudaMemcpyAsync(dstHost, stg, bytes, cudaMemcpyDeviceToHost, h->stream); };
+	auto out = [&](void* dstHost, const void* stg, size_t bytes) { if (deviceDst) return; cudaMemcpyAsync(dstHost, stg, bytes, cudaMemcpyDeviceToHost, h->stream); };
 	// device destinations (pmps_download_device): the gather kernels write straight into the caller's arrays
 #define STG(dst) (deviceDst ? (char*)(dst) : half[(hb ^= 1) ^ 1])
 	if (a->pos || a->particleType || a->PTYPE) {
@@ -210,9 +228,9 @@ extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArray
 	// step's stream at the point of first use, so nothing has to squeeze in between the persistent walker kernels
 	const bool haveLate = in->press || in->pndi || in->particleBC;
 	if (haveLate) {
-		if (in->press) { pin_host(h, in->press, 8 * (size_t)n0); cudaMemcpyAsync(s2, in->press, 8 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
-		if (in->pndi) { pin_host(h, in->pndi, 8 * (size_t)n0); cudaMemcpyAsync(s2 + 8 * (size_t)n0, in->pndi, 8 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
-		if (in->particleBC) { pin_host(h, in->particleBC, 4 * (size_t)n0); cudaMemcpyAsync(s2 + 16 * (size_t)n0, in->particleBC, 4 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
+		if (in->press) { cudaMemcpyAsync(s2, in->press, 8 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
+		if (in->pndi) { cudaMemcpyAsync(s2 + 8 * (size_t)n0, in->pndi, 8 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
+		if (in->particleBC) { cudaMemcpyAsync(s2 + 16 * (size_t)n0, in->particleBC, 4 * (size_t)n0, cudaMemcpyHostToDevice, h->ioStream); }
 		cudaEventRecord(h->evIoUp, h->ioStream);
 	}
 	auto scatter_late = [&]() {
@@ -244,10 +262,10 @@ extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArray
 		if (mid.particleBC) LAUNCH(h, "download", k_dn_i32, G, T, gb, S.particleBC, soh, n0);
 		if (mid.mirrorParticlePos) LAUNCH(h, "download", k_dn_v3, G, T, gm, S.mirrorParticlePos, soh, n0);
 		cudaEventRecord(h->evIoMid, h->stream); cudaStreamWaitEvent(h->ioStream, h->evIoMid, 0);
-		if (mid.press) { pin_host(h, mid.press, 8 * (size_t)n0); cudaMemcpyAsync(mid.press, gp, 8 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
-		if (mid.pndi) { pin_host(h, mid.pndi, 8 * (size_t)n0); cudaMemcpyAsync(mid.pndi, gn, 8 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
-		if (mid.particleBC) { pin_host(h, mid.particleBC, 4 * (size_t)n0); cudaMemcpyAsync(mid.particleBC, gb, 4 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
-		if (mid.mirrorParticlePos) { pin_host(h, mid.mirrorParticlePos, 24 * (size_t)n0); cudaMemcpyAsync(mid.mirrorParticlePos, gm, 24 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
+		if (mid.press) { cudaMemcpyAsync(mid.press, gp, 8 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
+		if (mid.pndi) { cudaMemcpyAsync(mid.pndi, gn, 8 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
+		if (mid.particleBC) { cudaMemcpyAsync(mid.particleBC, gb, 4 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
+		if (mid.mirrorParticlePos) { cudaMemcpyAsync(mid.mirrorParticlePos, gm, 24 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
 		rest.press = nullptr; rest.pndi = nullptr; rest.particleBC = nullptr; rest.mirrorParticlePos = nullptr;
 	}
 	rc = pmps_step_phase(h, 6, &m); if (rc) return rc;
@@ -257,8 +275,7 @@ extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArray
 	if (velEarly) {
 		double* gv = (double*)(s2 + 48 * (size_t)n0);
 		LAUNCH(h, "download", k_dn_pack, G, T, gv, (int32_t*)nullptr, (int32_t*)nullptr, h->V.vel, h->V.slotOfHost, n0);
-		cudaEventRecord(h->evIoUp, h->stream); cudaStreamWaitEvent(h->ioStream, h->evIoUp, 0);
-		pin_host(h, velOut, 24 * (size_t)n0); cudaMemcpyAsync(velOut, gv, 24 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream);
+		cudaEventRecord(h->evIoUp, h->stream); cudaStreamWaitEvent(h->ioStream, h->evIoUp, 0); cudaMemcpyAsync(velOut, gv, 24 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream);
 		rest.vel = nullptr; mid.vel = velOut;
 	}
 	for (int ph = 7; ph < pmps_step_phases(); ph++) { rc = pmps_step_phase(h, ph, &m); if (rc) return rc; }

@@ -83,6 +83,9 @@ def load_library() -> ctypes.CDLL:
     L.pmps_profile_get.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.POINTER(ctypes.c_char_p)),
                                    ctypes.POINTER(ctypes.POINTER(ctypes.c_float)), ctypes.POINTER(ctypes.POINTER(ctypes.c_int))]
     L.pmps_launch_count.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_longlong)]
+    L.pmps_get_counters.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_longlong)]
+    L.pmps_register_host.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]
+    L.pmps_unregister_host.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
     L.pmps_set_mesh.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_int,
                                 ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_double), ctypes.c_int,
                                 ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
@@ -112,6 +115,7 @@ class Engine:
         if rc != 0:
             raise PmpsError(rc, (self.lib.pmps_last_error(None) or b"").decode())
         self._keep = []
+        self._pinned = {}   # address -> the numpy array (kept alive while registered: the contract of pmps_register_host)
         self._n0_value = 0
         for k, m in enumerate(meshes):
             self.set_mesh(k, m)
@@ -124,8 +128,9 @@ class Engine:
 
     def close(self):
         if self.h:
-            self.lib.pmps_destroy(self.h)
+            self.lib.pmps_destroy(self.h)   # unregisters what register_host pinned
             self.h = ctypes.c_void_p()
+            self._pinned = {}
 
     def __del__(self):
         try:
@@ -158,6 +163,25 @@ class Engine:
         self._chk(self.lib.pmps_download(self.h, ctypes.byref(c)))
         state.numParticles = c.numParticles
         return state
+
+    def register_host(self, state: HostState, fields=None):
+        """Page-lock the named arrays of `state` for asynchronous copies (pmps_register_host).  The engine keeps a reference to
+        every registered array until close(), which is the lifetime the C contract asks for."""
+        from .state import ALL_FIELDS
+        for f in (fields or ALL_FIELDS):
+            a = getattr(state, f)
+            if a.nbytes < (1 << 16) or a.ctypes.data in self._pinned:
+                continue
+            self._chk(self.lib.pmps_register_host(self.h, ctypes.c_void_p(a.ctypes.data), a.nbytes))
+            self._pinned[a.ctypes.data] = a
+
+    def unregister_host(self, state: HostState, fields=None):
+        from .state import ALL_FIELDS
+        for f in (fields or ALL_FIELDS):
+            a = getattr(state, f)
+            if a.ctypes.data in self._pinned:
+                self._chk(self.lib.pmps_unregister_host(self.h, ctypes.c_void_p(a.ctypes.data)))
+                del self._pinned[a.ctypes.data]
 
     def upload_device(self, c: PmpsHostArrays):
         self._chk(self.lib.pmps_upload_device(self.h, ctypes.byref(c)))
@@ -217,6 +241,12 @@ class Engine:
         n = ctypes.c_int(); names = ctypes.POINTER(ctypes.c_char_p)(); ms = ctypes.POINTER(ctypes.c_float)(); ln = ctypes.POINTER(ctypes.c_int)()
         self._chk(self.lib.pmps_profile_get(self.h, ctypes.byref(n), ctypes.byref(names), ctypes.byref(ms), ctypes.byref(ln)))
         return [(names[k].decode(), float(ms[k]), int(ln[k])) for k in range(n.value)]
+
+    def counters(self) -> dict:
+        """Work counters of the temporal caches: bucket-order rebuilds, hit-list refilters, fused steps, guard violation flag."""
+        v = (ctypes.c_longlong * 4)()
+        self._chk(self.lib.pmps_get_counters(self.h, v))
+        return {"bucket_rebuilds": int(v[0]), "hit_refilters": int(v[1]), "steps": int(v[2]), "guard_violated": int(v[3])}
 
     def launch_count(self) -> int:
         v = ctypes.c_longlong()

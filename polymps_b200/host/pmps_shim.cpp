@@ -2,9 +2,12 @@
 // (called from the UNMODIFIED src/main.cpp:98-456) re-implemented as forwards to the C ABI (include/pmps.h).
 //
 // Built only where the reference tree is present (polymps_b200/host/Makefile): this file is compiled against the reference's
-// own headers and linked IN FRONT OF the unmodified reference objects with -Wl,--allow-multiple-definition, so the linker
-// takes these definitions for the hot-path methods and the reference's for everything else (input parsing, setParameters,
-// bucket geometry, STL reading, wall tables, VTU output).  Nothing of the reference is copied or edited.
+// own headers and linked with the unmodified reference objects, in whose copies every symbol defined HERE has been made weak
+// (objcopy --weaken-symbols), so each hot-path method has exactly one strong definition — this one — and the reference's code
+// serves everything else (input parsing, setParameters, bucket geometry, STL reading, wall tables, VTU output).  Nothing of the
+// reference is copied or edited.  EVERY engine method main.cpp:98-456 can reach is defined here: forwarded to the C ABI, or —
+// where the device path does not have the feature yet — a loud exit(10); tests/test_shim_link.py checks that no per-particle
+// method main.o references can fall through to the reference's CPU loop (which would run on stale host arrays).
 //
 // State policy: the particle arrays live on the device between calls.  The host arrays of MpsParticle are refreshed
 //   * before every output iteration (writeOutputFiles reads them, src/main.cpp:234-236): pmps_download of every field;
@@ -95,6 +98,15 @@ pmps_t* handle(MpsParticleSystem* S, MpsParticle* P) {
 	const int rc = pmps_create(&p, dev, &g_h);
 	if (rc < 0) { fprintf(stderr, "libpmps: pmps_create failed (%d): %s\n", rc, pmps_last_error(nullptr)); exit(10); }
 	const PmpsHostArrays a = host_arrays(P);
+	// the reference mallocs its particle arrays once and never frees them (src/MpsInputOutput.cpp:667-750): safe to page-lock for
+	// the lifetime of the handle (contract of pmps_register_host); failure to pin is not fatal, the copies then go the pageable way
+	{
+		const size_t n0 = (size_t)P->numParticlesZero;
+		void* v3[] = { P->pos, P->vel, P->acc, P->accStar, P->mirrorParticlePos, P->particleAtWallPos, P->polygonNormal };
+		void* f8[] = { P->press, P->pndi, P->pndSmall, P->concentration, P->RHO, P->MEU };
+		for (void* q : v3) if (q) pmps_register_host(g_h, q, 24 * n0);
+		for (void* q : f8) if (q) pmps_register_host(g_h, q, 8 * n0);
+	}
 	CALL(pmps_upload(g_h, &a));
 	return g_h;
 }
@@ -116,6 +128,10 @@ void pull_arrays() {    // before writeOutputFiles
 bool output_next(int inc) { return g_S->iterOutput > 0 && (g_S->numOfIterations + inc) % g_S->iterOutput == 0; }
 
 // row-major copies of an Eigen mesh (column-major) for pmps_set_mesh; the wall tables are private members, passed in by the caller
+void unsupported(const char* method, const char* where) {
+	fprintf(stderr, "libpmps: %s (%s) is not on the device path of this build; refusing to run the reference's CPU loop on stale host arrays\n", method, where);
+	exit(10);
+}
 void send_mesh(int me, const Eigen::MatrixXd& NV, const Eigen::MatrixXi& NF, const Eigen::MatrixXd& NN, const std::vector<double>& xP,
                const std::vector<double>& xN, const std::vector<double>& Z, const std::vector<int>& nNW) {
 	const int nV = (int)NV.rows(), nF = (int)NF.rows();
@@ -151,6 +167,10 @@ void MpsViscosity::calcViscosityInteractionVal(MpsParticleSystem *PSystem, MpsPa
 	CALL(pmps_set_time(H(PSystem, Particles), PSystem->timeCurrent));
 	CALL(pmps_calc_viscosity_interaction(H(PSystem, Particles)));
 }
+// polygon-wall variants of the rheology (src/MpsViscosity.cpp:703-1526; src/main.cpp:391-399): pmps_create refuses fluidType 1 with polygon
+// walls, so these are unreachable with a live handle — they are defined so that they can never resolve to the reference's loops
+void MpsViscosity::calcWallSlipViscosityInteractionVal(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { unsupported("MpsViscosity::calcWallSlipViscosityInteractionVal", "non-Newtonian rheology with polygon walls"); }
+void MpsViscosity::calcWallNoSlipViscosityInteractionVal(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { unsupported("MpsViscosity::calcWallNoSlipViscosityInteractionVal", "non-Newtonian rheology with polygon walls"); }
 void MpsViscosity::calcWallSlipViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_viscosity(H(PSystem, Particles))); }
 void MpsViscosity::calcWallNoSlipViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_viscosity(H(PSystem, Particles))); }
 
@@ -159,8 +179,10 @@ void MpsParticleVelPos::predictionVelocityPosition(MpsParticleSystem *PSystem, M
 void MpsParticleVelPos::correctionVelocityPosition(MpsParticleSystem *PSystem, MpsParticle *Particles) { CALL(pmps_correct(H(PSystem, Particles))); }
 void MpsParticleVelPos::updateVelocityParticlesWallDummy(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_update_wall_dummy_vel(H(PSystem, Particles))); }
 
-// ---- MpsParticleCollision (src/MpsParticleCollision.cpp:22-119) ------------------------------------------------------
+// ---- MpsParticleCollision (src/MpsParticleCollision.cpp:22-119, dynamic model :124-292) -------------------------------
+// pmps_collisions runs the model PmpsParams.collisionType names; main.cpp picks the method by the same flag (src/main.cpp:285-290)
 void MpsParticleCollision::checkParticleCollisions(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_collisions(H(PSystem, Particles))); }
+void MpsParticleCollision::checkDynamicParticleCollisions(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_collisions(H(PSystem, Particles))); }
 
 // ---- MpsPndNeigh (src/MpsPndNeigh.cpp:21-1049) ------------------------------------------------------------------------
 void MpsPndNeigh::setInitialPndNumberOfNeighNPCD(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_initial_pnd(H(PSystem, Particles))); }
@@ -195,7 +217,10 @@ void MpsPressure::predictionWallPressGradient(MpsParticleSystem *PSystem, MpsPar
 void MpsPressure::calcPressGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_press_gradient(H(PSystem, Particles))); }
 void MpsPressure::calcWallPressGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_press_gradient(H(PSystem, Particles))); }
 
-// ---- MpsShifting (src/MpsShifting.cpp:432-691) -------------------------------------------------------------------------------
+// ---- MpsShifting (src/MpsShifting.cpp:23-101 type 1, :432-691 type 2, :106-174 / :319-429 normals) ----------------------------
+void MpsShifting::calcShifting(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_shifting(H(PSystem, Particles))); }   // pmps_shifting runs the type PmpsParams.shiftingType names
+void MpsShifting::calcNormalParticles(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { unsupported("MpsShifting::calcNormalParticles", "ARC free-surface detection, src/main.cpp:351-357"); }
+void MpsShifting::calcWallNormalParticles(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { unsupported("MpsShifting::calcWallNormalParticles", "ARC free-surface detection, src/main.cpp:351-357"); }
 void MpsShifting::calcConcAndConcGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_shifting(H(PSystem, Particles))); }
 void MpsShifting::calcWallConcAndConcGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_shifting(H(PSystem, Particles))); }
 

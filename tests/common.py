@@ -17,7 +17,7 @@ from polymps_b200.mesh import PolygonMesh  # noqa: E402
 from polymps_b200.state import HostState, ALL_FIELDS, I32, U8  # noqa: E402
 from make_golden import load_golden  # noqa: E402
 
-GOLDEN = ["w3", "w3j", "i3", "w2", "i2", "n2", "b3", "e3"]
+GOLDEN = ["w3", "w3j", "i3", "w2", "i2", "n2", "b3", "e3", "o3"]
 
 # ref_driver stage name -> stage calls (oracle method names == engine method names)
 STAGE_MAP = {
@@ -146,7 +146,13 @@ def _jittered(build, amp=0.04, seed=7):
     return f
 
 
+def _splash(a, b):
+    from polymps_b200 import cases
+    return (lambda: cases.dam3d_splash(*a, name="var"), lambda: cases.dam3d_splash(*b, name="var"))
+
+
 VARIANTS = {
+    "ood": _splash((6, 5, 5), (14, 8, 10)),   # particles leave the domain (swap-with-last compaction, src/MpsParticle.cpp:286-396)
     "slip": _v3(slip=1), "grad0": _v3(grad_type=0), "grad1": _v3(grad_type=1), "grad2": _v3(grad_type=2),
     "gradcorr": _v3(grad_type=3, grad_corr=True), "rep0": _v3(rep_type=0), "rep1": _v3(rep_type=1), "rep3": _v3(rep_type=3),
     "w1": _v3(weight_type=1), "w2": _v3(weight_type=2), "w3": _v3(weight_type=3), "w4": _v3(weight_type=4),

@@ -102,8 +102,23 @@ def main():
             v = np.concatenate([g[f] for g in allgot]); w = getattr(st, f)
             w = w.reshape(-1, 3)[gid] if v.ndim == 2 else w[gid]
             if v.dtype.kind in "iu":
-                bad = int((v != w).sum())
-                print("  %-16s int mismatches %d" % (f, bad)); ok &= bad <= max(1, case.n // 2000)
+                # integer fields must be EXACT.  The only excuse is a threshold tie: the slabs sum a particle's neighbours in another
+                # order (1e-16 relative), so a comparison sitting on its threshold to rounding may fall either way — each such
+                # particle is printed with its margin, anything else fails.
+                idx = np.nonzero(v != w)[0]
+                print("  %-16s int mismatches %d" % (f, len(idx)))
+                for q in idx:
+                    g = int(gid[q]); why = None
+                    if f == "particleBC":
+                        m1 = abs(st.pndSmall[g] - ps.betaPnd) / ps.betaPnd; m2 = abs(st.npcdDeviation2[g] - ps.delta2) / ps.delta2
+                        m3 = abs(st.numNeigh[g] - ps.betaNeigh)
+                        if min(m1, m2) < 1e-9: why = "threshold tie: |pndSmall - beta n0|/beta n0 = %.1e, |npcd^2 - delta^2|/delta^2 = %.1e" % (m1, m2)
+                    elif f == "numNeigh":
+                        P3 = st.pos.reshape(-1, 3)[:s1.numParticles]; d = np.linalg.norm(P3 - P3[g], axis=1)
+                        near = np.abs(d - ps.reL) < 1e-9 * ps.reL
+                        if near.any(): why = "a neighbour sits on the cut-off: | |r| - reL | / reL = %.1e" % float(np.abs(d[near] - ps.reL).min() / ps.reL)
+                    print("    gid %d: slabs %d, single engine %d -- %s" % (g, int(v[q]), int(w[q]), why or "UNEXPLAINED"))
+                    ok &= why is not None
             else:
                 scale = max(float(np.abs(w).max()), 1e-300)
                 err = float(np.abs(v - w).max()) / scale
