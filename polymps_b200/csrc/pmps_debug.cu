@@ -4,7 +4,7 @@
 #include <vector>
 
 // The neighbour set of one particle exactly as the tile passes find it: the work item that owns the slot, its halo
-// table, the particle's tile-local candidate list mapped back to slots, then the reference's predicates (exact).
+// table, the particle's tile-local hit list mapped back to slots, then the reference's predicates (exact).
 template <bool POLY>
 __global__ void __launch_bounds__(TV_T) k_debug_neighbors(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int hostI, int kind, int32_t* out, int cap, int32_t* count) {
 	__shared__ int hBase[TV_HMAX], hOff[TV_HMAX + 1], sItem;
@@ -23,9 +23,9 @@ __global__ void __launch_bounds__(TV_T) k_debug_neighbors(const __grid_constant_
 	const int M = hOff[b.HV];
 	const double4 pi = S.pos[i];
 	const double mix = POLY ? S.mirrorParticlePos.x[i] : 0.0, miy = POLY ? S.mirrorParticlePos.y[i] : 0.0, miz = POLY ? S.mirrorParticlePos.z[i] : 0.0;
-	const uint16_t* L = S.tlist + (size_t)i * (size_t)S.tlCap;
+	const uint16_t* L = S.hlist + (size_t)i * (size_t)S.tlCap;
 	int n = 0;
-	for (int e = 0; e < S.tlistCnt[i]; e++) {
+	for (int e = 0; e < S.hcnt[i]; e++) {
 		const int m = L[tv_list_pos(e)];
 		if (m >= M) continue;   // padding
 		int hb = 0; while (hOff[hb + 1] <= m) hb++;
@@ -48,6 +48,7 @@ extern "C" int pmps_debug_neighbors(pmps_t* h, int i, int kind, int32_t* out, in
 	cudaSetDevice(h->device);
 	if (!h->haveList) return pmps_fail(h, PMPS_E_STATE, "pmps_debug_neighbors: call pmps_update_buckets first");
 	if (i < 0 || i >= h->numParticlesZero) return pmps_fail(h, PMPS_E_ARG, "pmps_debug_neighbors: index out of range");
+	if (!h->hitValid) { const int rc = pmps_tv_hits(h); if (rc) return rc; }   // the hit list of the CURRENT positions, as the next pass would use it
 	int32_t* d = (int32_t*)h->stage; int32_t* dcount = d + cap;
 	if ((size_t)(cap + 1) * 4 > h->stageBytes) return pmps_fail(h, PMPS_E_ARG, "pmps_debug_neighbors: cap too large");
 	if (h->K.poly) k_debug_neighbors<true><<<1, TV_T, 0, h->stream>>>(h->V, h->K, i, kind, d, cap, dcount);

@@ -4,8 +4,8 @@
 // bucket id (src/MpsBucket.cpp:299-353), ascending host index inside a bucket (= the reference's list order).
 //   pos, vel      : 32-byte records {x,y,z,w}; pos.w carries the bits of {particleType, PTYPE}; one sector per gather
 //   every other field : one 8-byte (or 4/1-byte) plane per component, coalesced own-index access
-//   tlist         : per-step Verlet candidates as 16-bit indices into the staged halo of the particle's tile
-//                   (pmps_tv.cuh); list: the same candidates as global slot ids, built on demand (PPE, debug hooks)
+//   hlist         : per-epoch candidates as 16-bit indices into the staged halo of the particle's tile (pmps_tv.cuh);
+//                   list: Verlet candidates as global slot ids, built on demand (PPE assembly)
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -38,8 +38,8 @@ struct DevView {
 	int32_t* cellOf;                     // slot -> bucket id at the last rebuild
 	int32_t* cellStart;                  // nC+2, slots of cell c (tile-major bucket index, cell_index()) are [cellStart[c], cellStart[c+1]); cell nC = ghosts
 	uint32_t* list; uint16_t* listCnt;   // Verlet candidates (slot ids), row-major, listCap per particle; built on demand
-	uint16_t* tlist; uint16_t* tlistCnt;   // tile-local Verlet candidates: tlCap entries per slot in chunks of 64 (tv_list_pos), entries used
-	uint16_t* hlist; uint16_t* hcnt;       // hit list: the candidates within reach at the positions of the current epoch (same layout)
+	uint16_t* hlist; uint16_t* hcnt;       // hit list (pmps_tv.cuh, k_hl_build): the staged records within reach at the positions of the current epoch, tlCap entries
+	                                       // per slot in chunks of 64 (tv_list_pos), as 16-bit indices into the staged halo of the slot's work item; entries used
 	uint8_t* particleNearWall;
 	double* ppeP;                        // CG search direction (pmps_ppe.cu), here so that the halo pack / unpack kernels reach it
 	double* scratch1;                    // per-slot scratch (Pmin of the gradient passes); not a reference field
@@ -61,12 +61,13 @@ struct DevView {
 	int32_t listCap;
 	int32_t nB;                          // reference buckets (numBucketsX*Y*Z)
 	int32_t nC;                          // cells of the tile-major index (>= nB: tiles are padded to full size)
-	int32_t tlCap;                       // entries per slot in tlist (multiple of 64)
+	int32_t tlCap;                       // entries per slot in hlist (multiple of 64)
 	// device scalars
 	unsigned long long* velMax2Bits;     // max |v|^2 of fluid particles (bits of a non-negative double)
 	float* maxDisp2;                     // [0] max squared displacement since the list build, [1] max squared shift of the shifting passes of the step (float, >= 0)
 	float* hitMove;                      // hit-list validity (pmps_tv.cuh): [0] largest squared displacement of ANY slot (halo copies included)
-	                                     // from its position when the hit list was made (running maximum, reset by a rebuild)
+	                                     // from its position when the hit list was made (running maximum, reset by a rebuild), [1] the margin
+	                                     // hitDelta the current list was made with
 	int32_t* hitFlag;                    // [0] 1: k_tv_hits must rebuild the hit list now (set by k_hits_decide), [1] rebuilds so far
 	int32_t* flags;                      // [0] list overflow, [1] out-of-domain count, [2] guard violated, [3] live count
 	int32_t* oodList;                    // host ids flagged by the out-of-domain test

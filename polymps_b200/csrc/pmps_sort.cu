@@ -257,42 +257,48 @@ int pmps_ensure_list(pmps_handle* h) {
 	return PMPS_OK;
 }
 
-// work items + tile-local Verlet list of the new bucket order (every neighbour pass of the step walks it)
-int pmps_tv_prepare(pmps_handle* h) {
+// work items + hit list of the new bucket order (every neighbour pass of the step follows it)
+static int ilog2_ceil(int n) { int b = 0; while ((1 << b) < n) b++; return b; }
+static int launch_hl_build(pmps_handle* h, const char* name, int force) {
 	DevView& S = h->V;
+	if (h->walkSeq >= PMPS_CURSORS) return pmps_fail(h, PMPS_E_STATE, "more than %d tile passes since the last pmps_update_buckets", PMPS_CURSORS - 1);
+	const size_t smem = 16 * (size_t)TV_MAXM + (size_t)HL_T * (S.tlCap + 2) * 2;   // float positions + one list row per lane
+	CUDA_TRY(h, cudaFuncSetAttribute(k_hl_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	{ ProfScope ps_(h, name); k_hl_build<<<h->smCount * 4, HL_T, smem, h->stream>>>(S, h->K, h->walkSeq++, force); h->launches++; }
+	CUDA_TRY(h, cudaGetLastError());
+	return PMPS_OK;
+}
+int pmps_tv_prepare(pmps_handle* h) {
+	DevView& S = h->V; const KParams& K = h->K;
 	CUDA_TRY(h, cudaMemsetAsync(S.nTiles, 0, sizeof(int32_t), h->stream));
 	CUDA_TRY(h, cudaMemsetAsync(S.tileCursor, 0, sizeof(int32_t) * PMPS_CURSORS, h->stream));
 	CUDA_TRY(h, cudaMemsetAsync(S.tileWall, 0, (size_t)h->nTilesAll, h->stream));
 	h->walkSeq = 0; h->tileWallValid = false;
-	LAUNCH(h, "sort.tile_items", k_tv_items, cdiv(h->nTilesAll, 128), 128, S, h->K, h->nTilesAll);
-	const size_t smem = 16 * (size_t)TV_MAXM + 2 * (size_t)(TV_T / TV_BG) * S.tlCap * 2;   // float positions + the two lists under construction
-	CUDA_TRY(h, cudaFuncSetAttribute(k_tv_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	{ ProfScope ps_(h, "list.tile_build"); k_tv_build<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, h->walkSeq++); h->launches++; }
-	CUDA_TRY(h, cudaGetLastError());
-	CUDA_TRY(h, cudaMemsetAsync(S.hitMove, 0, 4 * sizeof(float), h->stream));   // the build emits the hit list of the build positions too
+	const int bx = ilog2_ceil(K.nTX), by = ilog2_ceil(K.nTY), bz = ilog2_ceil(K.nTZ);
+	if (bx + by + bz > 30) return pmps_fail(h, PMPS_E_OVERFLOW, "tile grid %d x %d x %d is too large for the Z-order enumeration", K.nTX, K.nTY, K.nTZ);
+	const int nCodes = 1 << (bx + by + bz);
+	LAUNCH(h, "sort.tile_items", k_tv_items, cdiv(nCodes, 128), 128, S, h->K, nCodes, bx, by, bz);
+	{ const int rc = launch_hl_build(h, "list.build", 1); if (rc) return rc; }
+	CUDA_TRY(h, cudaMemsetAsync(S.hitMove, 0, sizeof(float), h->stream));   // nobody has moved since this list was made
 	h->hitValid = true; h->hitForce = false;
 	return PMPS_OK;
 }
 
 // Is the hit list still good for the positions of the new epoch?  It reaches hitDelta beyond every cut-off on both sides, so it
 // is while nobody has moved farther than hitDelta from where it was when the list was made (hpos; track_hit_disp keeps the
-// running maximum over all slots).  One thread.
+// running maximum over all slots; hitMove[1] = the margin the list was made with).  One thread.
 __global__ void k_hits_decide(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int force) {
-	const float lim = (float)K.hitDelta * 0.98f;   // float positions relative to domainMin: a few 1e-7 of the domain extent of slack
+	const float lim = S.hitMove[1] * 0.98f;   // float positions relative to domainMin: a few 1e-7 of the domain extent of slack
 	if (force || S.hitMove[0] > lim * lim) { S.hitFlag[0] = 1; S.hitFlag[1] += 1; S.hitMove[0] = 0.f; }
 	else S.hitFlag[0] = 0;
 }
 // hit list for the current positions (after the prediction / correction / shifting moved the particles): re-made only when
-// k_hits_decide says the old one may miss a pair (k_tv_hits returns at once otherwise)
+// k_hits_decide says the old one may miss a pair (k_hl_build returns at once otherwise)
 int pmps_tv_hits(pmps_handle* h) {
 	DevView& S = h->V;
 	LAUNCH(h, "list.hits_decide", k_hits_decide, 1, 1, S, h->K, h->hitForce ? 1 : 0);
 	h->hitForce = false;
-	if (h->walkSeq >= PMPS_CURSORS) return pmps_fail(h, PMPS_E_STATE, "more than %d tile passes since the last pmps_update_buckets", PMPS_CURSORS - 1);
-	const size_t smem = 16 * (size_t)TV_MAXM + 2 * (size_t)TV_MAXOWN + (size_t)TV_NG * S.tlCap * 2;
-	CUDA_TRY(h, cudaFuncSetAttribute(k_tv_hits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	{ ProfScope ps_(h, "list.hits"); k_tv_hits<<<h->smCount * 4, TV_T, smem, h->stream>>>(S, h->K, h->walkSeq++); h->launches++; }
-	CUDA_TRY(h, cudaGetLastError());
+	{ const int rc = launch_hl_build(h, "list.hits", 0); if (rc) return rc; }
 	h->hitValid = true;
 	return PMPS_OK;
 }

@@ -29,10 +29,11 @@
 #define TV_HMAX 160              // halo buckets a work item may have
 #define TV_CHUNK 64              // list entries per chunk: walker lane g holds entries g, g+TV_G, ... of the chunk, contiguously
 #define TV_PER (TV_CHUNK / TV_G) // entries per lane and chunk
-#define TV_MAXOWN 1024           // particles a work item may own (ownMap)
+#define TV_MAXOWN 512            // particles a work item may own (ownMap, sCnt, sHas)
 #define TV_SMEM_BUDGET (111 * 1024)   // dynamic shared memory per block: two blocks per SM
-// fixed dynamic shared memory of the walker besides the staged records: the queues (one chunk per particle) + ownMap
-#define TV_FIXED_BYTES(follow) (((follow) ? 0 : TV_NG * TV_CHUNK * 2) + TV_MAXOWN * 2)
+#define TV_LROW (TV_CHUNK * 2 + 16)   // bytes per prefetched list row in shared memory: 16 bytes of padding stagger the lane groups over the banks
+// fixed dynamic shared memory of the walker besides the staged records: two rounds of list rows, ownMap, sCnt, sHas
+#define TV_FIXED_BYTES (2 * TV_NG * TV_LROW + TV_MAXOWN * 2 + TV_MAXOWN * 2 + TV_MAXOWN)
 // position of list entry e inside the particle's list: chunk-major, then lane-major
 __host__ __device__ __forceinline__ int tv_list_pos(int e) { const int w = e & (TV_CHUNK - 1); return (e & ~(TV_CHUNK - 1)) + (w % TV_G) * TV_PER + w / TV_G; }
 
@@ -79,16 +80,21 @@ template <class B, class... R> struct PackSparse<B, R...> { static constexpr boo
 
 __host__ __device__ constexpr int popc8(unsigned f) { int n = 0; for (int k = 0; k < 8; k++) n += (f >> k) & 1; return n; }
 __host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes per halo record
-	return 16 + 24 + ((f & NF_VEL) ? 24 : 0) + 8 * popc8(f & ~(unsigned)NF_VEL);
+	return 4 + 24 + ((f & NF_VEL) ? 24 : 0) + 8 * popc8(f & ~(unsigned)NF_VEL);
 }
-#define TV_REC_MAX (16 + 24 + 24 + 8 * 3)   // the fattest pack of the step paths: F3 (vel, press, pndi, RHO)
-#ifndef TV_LIGHT_REC
-#define TV_LIGHT_REC 0            // packs staging at most this many bytes per record would run three blocks per SM (measured: 85 registers spill, slower)
+#define TV_REC_MAX (4 + 24 + 24 + 8 * 3)   // the fattest pack of the step paths: F3 (vel, press, pndi, RHO)
+// blocks per SM by the bytes a pack stages per record (shared memory decides: TV_MAXM * rec + TV_FIXED_BYTES per block, 227 KB per SM):
+// up to TV_OCC4_REC four blocks (64 registers per thread), up to TV_OCC3_REC three (80 registers), two otherwise (128 registers)
+#ifndef TV_OCC4_REC
+#define TV_OCC4_REC 0
 #endif
-#define TV_BLOCKS(f) (tv_rec_bytes(f) <= TV_LIGHT_REC ? 3 : 2)
+#ifndef TV_OCC3_REC
+#define TV_OCC3_REC 0
+#endif
+#define TV_BLOCKS(f) (tv_rec_bytes(f) <= TV_OCC4_REC ? 4 : tv_rec_bytes(f) <= TV_OCC3_REC ? 3 : 2)
 // staged records per work item: a compile-time constant, so every plane of the shared-memory image sits at a constant
 // offset (no registers spent on plane pointers).  Sized for two blocks per SM of the fattest pack in follow mode.
-#define TV_MAXM ((TV_SMEM_BUDGET - TV_FIXED_BYTES(true)) / TV_REC_MAX)
+#define TV_MAXM (((TV_SMEM_BUDGET - TV_FIXED_BYTES) / TV_REC_MAX) & ~3)   // multiple of 4: every plane and the fixed part stay 16-byte aligned
 #ifndef TV_ILP2
 #define TV_ILP2 0                 // 1: follow passes take two list entries per trip (interleaved geometry chains); measured: no gain
 #endif
@@ -163,9 +169,22 @@ __device__ __forceinline__ void tv_write_table(const DevView& S, const KParams& 
 	const int own0 = S.cellStart[b.c0];
 	tab[2 * K.HVt + 1] = own0; tab[2 * K.HVt + 2] = S.cellStart[b.c1] - own0;
 }
-static __global__ void k_tv_items(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int nTilesAll) {
-	const int t = blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= nTilesAll) return;
+// Threads enumerate the tiles along a Z-order curve (bits of the thread index dealt round-robin to the axes that still have bits
+// left), so the work items come out in roughly that order: the blocks working at any one time — they take items from a cursor —
+// then sit in a compact 3-D neighbourhood and find each other's halo records in L2 (a raster order re-reads every record from
+// DRAM for the tiles of the next z-layer: ncu, 2.1 - 4.1 x the algorithmic bytes in round 1).
+static __global__ void k_tv_items(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int nCodes, int bx, int by, int bz) {
+	const int code = blockIdx.x * blockDim.x + threadIdx.x;
+	if (code >= nCodes) return;
+	int tx = 0, ty = 0, tz = 0;
+	{ int c = code, ax = 0, ay = 0, az = 0;
+	  while (ax < bx || ay < by || az < bz) {
+		if (ax < bx) { tx |= (c & 1) << ax; c >>= 1; ax++; }
+		if (ay < by) { ty |= (c & 1) << ay; c >>= 1; ay++; }
+		if (az < bz) { tz |= (c & 1) << az; c >>= 1; az++; }
+	  } }
+	if (tx >= K.nTX || ty >= K.nTY || tz >= K.nTZ) return;
+	const int t = (tz * K.nTY + ty) * K.nTX + tx;
 	if (S.cellStart[(t + 1) * K.TV] == S.cellStart[t * K.TV]) return;
 	const TvBox b = tv_box(K, t);
 	int M = 0;
@@ -188,8 +207,8 @@ __device__ __forceinline__ int tv_advance(int nxt, int* sItem) {
 	__syncthreads();
 	return *sItem;
 }
-__device__ __forceinline__ void tv_load_table(const DevView& S, const KParams& K, int tt, int* sTab) {
-	for (int k = threadIdx.x; k < K.tabStride; k += TV_T) sTab[k] = S.itemTab[(size_t)tt * K.tabStride + k];
+template <int NT = TV_T> __device__ __forceinline__ void tv_load_table(const DevView& S, const KParams& K, int tt, int* sTab) {
+	for (int k = threadIdx.x; k < K.tabStride; k += NT) sTab[k] = S.itemTab[(size_t)tt * K.tabStride + k];
 	__syncthreads();
 }
 static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int copyPos, int copyVel) {
@@ -201,13 +220,14 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 
 
 // ---- shared-memory image of the halo ------------------------------------------------------------------------------
-struct TvStage {   // shared-memory planes of the staged halo
-	float4* fpos; double *px, *py, *pz; Nb nb;
+struct TvStage {   // shared-memory planes of the staged halo: the walker stages FP64 positions + the type word, the list build float positions
+	float4* fpos; int32_t* tw; double *px, *py, *pz; Nb nb;
 };
 template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp) {
 	TvStage t; constexpr size_t m = TV_MAXM;
-	t.fpos = (float4*)sp; sp += 16 * m;
+	t.fpos = nullptr;
 	t.px = (double*)sp; sp += 8 * m; t.py = (double*)sp; sp += 8 * m; t.pz = (double*)sp; sp += 8 * m;
+	t.tw = (int32_t*)sp; sp += 4 * m;
 	double *vx = nullptr, *vy = nullptr, *vz = nullptr, *pr = nullptr, *pn = nullptr, *rh = nullptr, *mu = nullptr, *cc = nullptr, *pk = nullptr;
 	if (FIELDS & NF_VEL) { vx = (double*)sp; sp += 8 * m; vy = (double*)sp; sp += 8 * m; vz = (double*)sp; sp += 8 * m; }
 	if (FIELDS & NF_PRESS) { pr = (double*)sp; sp += 8 * m; }
@@ -228,17 +248,17 @@ template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned 
 // samples when issued one bucket at a time).
 template <bool PLANES, unsigned FIELDS>
 __device__ __forceinline__ void tv_stage_one(const DevView& S, const TvStage& T, int j, int m, const double4& pj, double ox, double oy, double oz) {
-	T.fpos[m] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), tv_type_word(pj));
-	if (PLANES) { T.px[m] = pj.x; T.py[m] = pj.y; T.pz[m] = pj.z; }
+	if (PLANES) { T.px[m] = pj.x; T.py[m] = pj.y; T.pz[m] = pj.z; T.tw[m] = __float_as_int(tv_type_word(pj)); }
+	else T.fpos[m] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), tv_type_word(pj));
 }
 __device__ __forceinline__ void tv_cp8(const double* dstShared, const double* srcGlobal) {   // 8-byte asynchronous global -> shared copy
 	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"((unsigned)__cvta_generic_to_shared(dstShared)), "l"(srcGlobal));
 }
-template <bool PLANES, unsigned FIELDS>
+template <bool PLANES, unsigned FIELDS, int NT = TV_T>
 __device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, const int* hOff, const int* hBase, int HV, int own0, int P,
                                          double ox, double oy, double oz, uint16_t* ownMap) {
 	constexpr int NB = 4;   // buckets per thread whose position loads are in flight together
-	constexpr int NW = TV_T / 32;
+	constexpr int NW = NT / 32;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	// neighbour fields: asynchronous copies straight into the planes (cp.async: no registers, nothing waits until the end)
 	if (FIELDS) {
@@ -286,48 +306,61 @@ __device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, con
 	if (FIELDS) asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
-// ---- Verlet list in tile-local indices ---------------------------------------------------------------------------
-// Same tiling as the walker.  Float positions (relative to the tile origin) of the halo are staged; TV_BG lanes per
-// particle sweep the 27 (9 in 2D) buckets around the particle's own bucket — nine (three) contiguous stretches of the
-// staged halo — and append the records within the list radius, in staged order, to the particle's list (tv_list_pos()).
-// The unused tail of the last chunk points at the far-away dummy record (index M).  Control flow is warp-uniform
-// (trip counts are the maximum over the warp) so the ballots run with the full mask.
-static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
+// ---- hit list in tile-local indices ------------------------------------------------------------------------------------
+// ONE kernel makes the candidate list of every neighbour pass: for each own particle of a work item, the staged records within
+// hitR = max(reS, reL) + 2 hitDelta at the current positions, as 16-bit indices into the staged halo (same tiling and staging
+// order as the walker, so the indices mean the same records there).  It runs after a bucket rebuild (force = 1) and whenever
+// k_hits_decide finds that somebody has moved hitDelta since the list was made (positions change three times per step).
+//
+// One LANE per own particle: the lane sweeps the 27 (9 in 2D) buckets around its particle's bucket — nine (three) contiguous
+// stretches of the staged float positions — and appends the hits to its own row in shared memory.  The lanes of a warp are
+// particles of the same one or two buckets, so they read the same staged record at the same time (a shared-memory broadcast),
+// there are no votes and no cross-lane compaction; a row is an odd number of 32-bit words long, so the lanes' appends fall
+// into different banks.  The rows are then copied to hlist chunk by chunk (128 contiguous bytes per particle) in the lane-major
+// order the walker reads (tv_list_pos); the unused tail of the last chunk points at the far-away dummy record M.
+// 197 warp-instructions per particle against 1 218 (two-level build: Verlet list + hit list) + 197 (refilter) of the
+// round-1 kernels (ncu, profiles/r02_ncu_*): the Verlet list of radius bucketSide is gone.
+#define HL_T 128
+static __global__ void __launch_bounds__(HL_T, 4) k_hl_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx, int force) {
+	if (!force && !S.hitFlag[0]) return;   // k_hits_decide: the hit list still covers the current positions
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
 	__shared__ unsigned sMinBits;   // smallest squared pair distance of the item (bits of a positive float)
-	constexpr int NGB = TV_T / TV_BG;   // particles per round
 	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
 	float4* const fpos = T.fpos;
-	uint16_t* glist = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM) + (size_t)(threadIdx.x / TV_BG) * S.tlCap;
-	uint16_t* hl = glist + (size_t)NGB * S.tlCap;   // hit list of the build positions (epoch of the first passes of the step)
-	const float rfilt2 = K.hitR2;
-	const int tid = threadIdx.x, grp = tid / TV_BG, g = tid % TV_BG;
-	const unsigned gshift = (tid & 31) & ~(TV_BG - 1);
-	const unsigned gbits = (1u << TV_BG) - 1u, lower = (1u << g) - 1u;
+	const int cap = S.tlCap, LS = cap + 2;   // row stride in 16-bit entries: (cap + 2) / 2 is odd
+	const int tid = threadIdx.x, lane = tid & 31, w0 = tid & ~31;
+	uint16_t* const rows = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM);
+	uint16_t* const row = rows + (size_t)tid * LS;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
+	const float R2 = K.hitR2;
 	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
+	if (blockIdx.x == 0 && tid == 0) S.hitMove[1] = (float)K.hitDelta;   // the margin THIS list was made with (k_hits_decide)
 	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const TvBox b = tv_box(K, S.tileList[tt]);
 		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; S.tileClose[b.c0 / K.TV] = 1; }
-		tv_load_table(S, K, tt, sTab);
+		tv_load_table<HL_T>(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
 			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1 > TV_MAXM ? M + 1 : P);
-			for (int p = tid; p < P; p += TV_T) { S.tlistCnt[own0 + p] = 0; S.hcnt[own0 + p] = 0; }
+			for (int p = tid; p < P; p += HL_T) S.hcnt[own0 + p] = 0;
 			continue;
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		tv_stage<false, 0>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, nullptr);
+		tv_stage<false, 0, HL_T>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, nullptr);
 		__syncthreads();
-		for (int p0 = 0; p0 < P; p0 += NGB) {   // uniform over the block
-			const int p = p0 + grp;
+		for (int p0 = 0; p0 < P; p0 += HL_T) {   // uniform over the block
+			const int p = p0 + tid;
 			const bool act = p < P;
 			const int i = own0 + (act ? p : 0);
-			int hx = 1, hy = 1, hz = three ? 1 : 0, self = 0;
+			{	// every entry of the row points at the dummy record until a hit overwrites it
+				uint32_t* r32 = (uint32_t*)row; const uint32_t pad = (uint32_t)M * 0x10001u;
+				for (int q = 0; q < cap / 2; q++) r32[q] = pad;
+			}
+			int hx = 1, hy = 1, hz = three ? 1 : 0, self = -1;
 			float4 fi = make_float4(0.f, 0.f, 0.f, 0.f);
 			if (act) {
 				int ix, iy, iz; cell_coords(K, S.cellOf[i], ix, iy, iz);
@@ -336,44 +369,39 @@ static __global__ void __launch_bounds__(TV_T, 4) k_tv_build(const __grid_consta
 				self = hOff[hbs] + (i - hBase[hbs]);
 				fi = fpos[self];
 			}
-			int cnt = 0, cntH = 0; float dmin = __int_as_float(0x7f800000);
+			int cnt = 0; float dmin = __int_as_float(0x7f800000);
 			for (int dz = three ? -1 : 0; dz <= (three ? 1 : 0); dz++) for (int dy = -1; dy <= 1; dy++) {
 				const int hb0 = ((hz + dz) * b.HY + hy + dy) * b.HX + hx - 1;
 				const int r0 = hOff[hb0], r1 = act ? hOff[hb0 + 3] : r0;
-				const int trips = __reduce_max_sync(0xffffffffu, (r1 - r0 + TV_BG - 1) / TV_BG);
+				const int trips = __reduce_max_sync(0xffffffffu, r1 - r0);
+				#pragma unroll 4
 				for (int k = 0; k < trips; k++) {
-					const int m = r0 + k * TV_BG + g; bool hit = false, hitH = false;
-					if (m < r1) {
+					const int m = r0 + k;
+					if (m < r1 && m != self) {
 						const float4 f = fpos[m];
 						const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
 						const float d2 = dx * dx + dy2 * dy2 + dz2 * dz2;
-						hit = d2 < K.rl2 && m != self; hitH = hit && d2 < rfilt2;
-						if (m != self) dmin = fminf(dmin, d2);
+						dmin = fminf(dmin, d2);
+						if (d2 < R2) { if (cnt < cap) row[tv_list_pos(cnt)] = (uint16_t)m; cnt++; }
 					}
-					const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
-					if (hit) { const int e = cnt + __popc(gb & lower); if (e < S.tlCap) glist[tv_list_pos(e)] = (uint16_t)m; }
-					cnt += __popc(gb);
-					const unsigned gh = (__ballot_sync(0xffffffffu, hitH) >> gshift) & gbits;
-					if (hitH) { const int e = cntH + __popc(gh & lower); if (e < S.tlCap) hl[tv_list_pos(e)] = (uint16_t)m; }
-					cntH += __popc(gh);
 				}
 			}
 			if (act) {
-				if (cnt > S.tlCap) { if (g == 0) atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = S.tlCap; }
-				const int nch = (cnt + TV_CHUNK - 1) / TV_CHUNK;
-				for (int e = cnt + g; e < nch * TV_CHUNK; e += TV_BG) glist[tv_list_pos(e)] = (uint16_t)M;
-			}
+				if (cnt > cap) { atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = cap; }
+				S.hcnt[i] = (uint16_t)cnt;
+				S.hpos[i] = make_float4(fi.x + (float)(ox - K.p.domainMinX), fi.y + (float)(oy - K.p.domainMinY), fi.z + (float)(oz - (three ? K.p.domainMinZ : 0.0)), 0.f);
+			} else cnt = 0;
 			__syncwarp();
-			if (act) {
-				const int nch = (cnt + TV_CHUNK - 1) / TV_CHUNK;
-				uint4* dst = (uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap);
-				for (int q = g; q < nch * (TV_CHUNK / 8); q += TV_BG) dst[q] = ((const uint4*)glist)[q];
-				if (cntH > S.tlCap) cntH = S.tlCap;
-				uint4* dstH = (uint4*)(S.hlist + (size_t)i * (size_t)S.tlCap);
-				for (int q = g; q < (cntH + TV_CHUNK - 1) / TV_CHUNK * (TV_CHUNK / 8); q += TV_BG) dstH[q] = ((const uint4*)hl)[q];
-				if (g == 0) { S.tlistCnt[i] = (uint16_t)cnt; S.hcnt[i] = (uint16_t)cntH; S.hpos[i] = S.bpos[i]; }
+			// rows -> hlist: the warp copies one particle's chunks at a time, 128 contiguous bytes per instruction
+			for (int q = 0; q < 32; q++) {
+				const int pq = p0 + w0 + q;
+				if (pq >= P) break;   // uniform over the warp
+				const int nch = (__shfl_sync(0xffffffffu, cnt, q) + TV_CHUNK - 1) / TV_CHUNK;
+				const uint32_t* src = (const uint32_t*)(rows + (size_t)(w0 + q) * LS);
+				uint32_t* dst = (uint32_t*)(S.hlist + (size_t)(own0 + pq) * (size_t)cap);
+				for (int c = 0; c < nch; c++) dst[c * (TV_CHUNK / 2) + lane] = src[c * (TV_CHUNK / 2) + lane];
 			}
-			{ const unsigned mb = __reduce_min_sync(0xffffffffu, __float_as_uint(dmin)); if ((tid & 31) == 0) atomicMin(&sMinBits, mb); }
+			{ const unsigned mb = __reduce_min_sync(0xffffffffu, __float_as_uint(dmin)); if (lane == 0) atomicMin(&sMinBits, mb); }
 			__syncwarp();
 		}
 		__syncthreads();
@@ -432,7 +460,7 @@ __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, 
 	q.rx = xj - s.pi.x; q.ry = yj - s.pi.y; q.rz = zj - s.pi.z;
 	q.d2 = sq3_exact(q.rx, q.ry, q.rz);
 	if (!(q.d2 < K.reMax2)) return;
-	const int tw = __float_as_int(T.fpos[m].w);
+	const int tw = T.tw[m];
 	q.tj = (int)(short)(tw & 0xffff); q.ptj = tw >> 16;
 	if (POLY && s.hasMirror) { q.mx = xj - s.mix; q.my = yj - s.miy; q.mz = zj - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
 	else { q.mx = q.my = q.mz = 0.0; q.dm2 = __longlong_as_double(0x7ff0000000000000ll); }   // no mirror in reach: d2 < dm2 holds, M(re) fails (pmps_internal.h, mirrorFar2)
@@ -440,12 +468,12 @@ __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, 
 	F::template pair<POLY>(ctx, T.nb, K, s, q);
 }
 // two staged records at once: the two geometry chains (shared-memory loads, exact distance, reciprocal square root) are
-// independent and interleave, which is what hides the FP64 latencies with only four warps per scheduler
+// independent and interleave
 template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair2(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m0, int m1) {
 	Pair a, b; a.j = m0; b.j = m1;
 	const double xa = T.px[m0], ya = T.py[m0], za = T.pz[m0], xb = T.px[m1], yb = T.py[m1], zb = T.pz[m1];
-	const int wa = __float_as_int(T.fpos[m0].w), wb = __float_as_int(T.fpos[m1].w);
+	const int wa = T.tw[m0], wb = T.tw[m1];
 	a.rx = xa - s.pi.x; a.ry = ya - s.pi.y; a.rz = za - s.pi.z; b.rx = xb - s.pi.x; b.ry = yb - s.pi.y; b.rz = zb - s.pi.z;
 	a.d2 = sq3_exact(a.rx, a.ry, a.rz); b.d2 = sq3_exact(b.rx, b.ry, b.rz);
 	const bool ha = a.d2 < K.reMax2, hb = b.d2 < K.reMax2;
@@ -461,24 +489,38 @@ __device__ __forceinline__ void tv_pair2(typename F::Ctx& ctx, const TvStage& T,
 	if (ha) F::template pair<POLY>(ctx, T.nb, K, s, a);
 	if (hb) F::template pair<POLY>(ctx, T.nb, K, s, b);
 }
-__device__ __forceinline__ void tv_prefetch(const void* p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+__device__ __forceinline__ void tv_cp16(const void* dstShared, const void* srcGlobal) {   // 16-byte asynchronous global -> shared copy, L2 only
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((unsigned)__cvta_generic_to_shared(dstShared)), "l"(srcGlobal));
+}
+// the hit lists of one round of TV_NG particles on their way into shared memory: 8 x 16 bytes per chunk-0 row, one commit group
+__device__ __forceinline__ void tv_fetch_lists(const DevView& S, unsigned char* rowsBuf, int own0, int p0, int P) {
+	const int n = min(TV_NG, P - p0);
+	for (int q = threadIdx.x; q < n * (TV_CHUNK * 2 / 16); q += TV_T) {
+		const int r = q >> 3, c = q & 7;
+		tv_cp16(rowsBuf + (size_t)r * TV_LROW + c * 16, (const unsigned char*)(S.hlist + (size_t)(own0 + p0 + r) * (size_t)S.tlCap) + c * 16);
+	}
+	asm volatile("cp.async.commit_group;" ::: "memory");
+}
 
-// FOLLOW: the candidates are the particle's HIT list (k_tv_hits / k_tv_build: the Verlet candidates within reach at the
-// positions of the current epoch), every lane just takes its share — no scan, no queue, no votes.  Otherwise the Verlet
-// list itself is scanned with the float positions and the survivors are queued (used when no hit list is valid).
-template <bool POLY, unsigned FIELDS, bool WALLONLY, bool SPARSE, bool FOLLOW, class F>
+// Every lane group takes its particle's HIT list (k_hl_build: the staged records within reach at the positions of the current
+// epoch) — no scan, no queue, no votes.  What a round needs from global memory besides the staged halo — the list rows, the list
+// lengths, the has-a-mirror flags — is fetched into shared memory ahead of time (lists: cp.async, double-buffered per round; the
+// per-particle scalars with the staging loads), because ncu showed the round-start loads of these as 25 % of all stall samples.
+template <bool POLY, unsigned FIELDS, bool WALLONLY, bool SPARSE, class F>
 __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
 	const TvStage T = tv_carve<FIELDS>(smemRaw);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
-	uint16_t* gq = (uint16_t*)(smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS)) + grp * TV_CHUNK;   // this particle's queue: one chunk
-	uint16_t* ownMap = (uint16_t*)(smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS)) + (FOLLOW ? 0 : TV_NG * TV_CHUNK);   // own particle -> staged index
+	unsigned char* const fx = smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS);
+	unsigned char* const rowsBuf = fx;                                       // 2 x TV_NG list rows of TV_LROW bytes
+	uint16_t* const ownMap = (uint16_t*)(fx + 2 * TV_NG * TV_LROW);          // own particle -> staged index
+	uint16_t* const sCnt = ownMap + TV_MAXOWN;                               // own particle -> entries of its hit list
+	uint8_t* const sHas = (uint8_t*)(sCnt + TV_MAXOWN);                      // own particle -> a mirror particle is in reach
 	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
-	const unsigned gbits = (1u << TV_G) - 1u, lower = (1u << g) - 1u, gmask = gbits << gshift;
+	const unsigned gbits = (1u << TV_G) - 1u, gmask = gbits << gshift;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
-	const float rfilt2 = K.hitR2;
 	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
 	// wall-only / close-pair packs visit only the work items k_item_flags listed for them (the tails of the other tiles: k_tails)
 	constexpr bool LISTED = WALLONLY || F::kCloseOnly || SPARSE;
@@ -492,7 +534,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		const TvBox b = tv_box(K, item);
 		tv_load_table(S, K, tt, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
-		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_tv_build (FLAG_TILE_OVERFLOW)
+		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_hl_build (FLAG_TILE_OVERFLOW)
 		if (SPARSE) {   // does any particle of the tile want pairs?  (begin() of these bodies is idempotent)
 			bool want = false;
 			for (int p = tid; p < P; p += TV_T) {
@@ -519,28 +561,28 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		// first round's lists on their way while the staging loads land
-		const uint16_t* const LIST = FOLLOW ? S.hlist : S.tlist;
-		if (grp < P) { const char* L0 = (const char*)(LIST + (size_t)(own0 + grp) * (size_t)S.tlCap); tv_prefetch(L0 + g * (2 * TV_PER)); }
+		tv_fetch_lists(S, rowsBuf, own0, 0, P);   // first round's lists on their way while the staging loads land
+		for (int p = tid; p < P; p += TV_T) {     // per-particle scalars of the whole item, independent loads issued together with the staging
+			sCnt[p] = S.hcnt[own0 + p];
+			if (POLY) sHas[p] = S.distParticleWall2[own0 + p] < K.mirrorFar2 ? 1 : 0;
+		}
 		tv_stage<true, FIELDS>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, ownMap);
-		if (tid == 0) { T.fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f); T.px[M] = T.py[M] = T.pz[M] = 1e30; }   // the record list padding points at
-		__syncthreads();
-		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask ballots) ----
-		for (int p0 = 0; p0 < P; p0 += TV_NG) {
+		if (tid == 0) { T.tw[M] = 0; T.px[M] = T.py[M] = T.pz[M] = 1e30; }   // the record list padding points at
+		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask shuffles) ----
+		for (int p0 = 0, rnd = 0; p0 < P; p0 += TV_NG, rnd++) {
+			asm volatile("cp.async.wait_group 0;" ::: "memory");
+			__syncthreads();   // this round's list rows (and, in round 0, the staged halo) are visible to every thread; everybody has left the round before
+			if (p0 + TV_NG < P) tv_fetch_lists(S, rowsBuf + ((rnd + 1) & 1) * (TV_NG * TV_LROW), own0, p0 + TV_NG, P);   // next round's rows land while this round computes
 			const int p = p0 + grp;
 			bool act = p < P;
 			const int i = own0 + (act ? p : 0);
-			if (p + TV_NG < P) {   // next round's list and flags on their way to L1
-				const char* Ln = (const char*)(LIST + (size_t)(i + TV_NG) * (size_t)S.tlCap);
-				tv_prefetch(Ln + g * (2 * TV_PER)); if (!FOLLOW) tv_prefetch(Ln + TV_CHUNK * 2 + g * (2 * TV_PER));
-			}
 			Self s; s.i = i; s.lead = g == 0; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
 			s.type = K.p.ghost; s.ptype = 0;
 			int cntE = 0;
 			if (act) {
-				cntE = FOLLOW ? S.hcnt[i] : S.tlistCnt[i];
+				cntE = sCnt[p];
 				const int ms = ownMap[p];
-				const int tw = __float_as_int(T.fpos[ms].w);
+				const int tw = T.tw[ms];
 				s.type = (int)(short)(tw & 0xffff); s.ptype = tw >> 16;
 				s.pi.x = T.px[ms]; s.pi.y = T.py[ms]; s.pi.z = T.pz[ms]; s.pi.w = pk_make(s.type, s.ptype);
 				if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
@@ -551,7 +593,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 			bool pairs = false;
 			if (act) {
 				if (POLY) {
-					s.hasMirror = S.distParticleWall2[i] < K.mirrorFar2;
+					s.hasMirror = sHas[p] != 0;
 					if (s.hasMirror) { s.mix = S.mirrorParticlePos.x[i]; s.miy = S.mirrorParticlePos.y[i]; s.miz = S.mirrorParticlePos.z[i]; }
 					else { s.mix = s.miy = s.miz = K.big; }
 				}
@@ -560,145 +602,27 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 				pairs = act && F::need_pairs(ctx);
 			}
 			if (!pairs) cntE = 0;
-			const uint4* L = (const uint4*)(LIST + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);
-			if (FOLLOW) {
-				for (int ch = 0; ch * TV_CHUNK < cntE; ch++) {
-					unsigned w[TV_PER / 2];
-					#pragma unroll
-					for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(L + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
-					const int rem = cntE - ch * TV_CHUNK - g;   // entries u * TV_G + g of this chunk exist for u * TV_G < rem
+			const uint4* Ls = (const uint4*)(rowsBuf + (rnd & 1) * (TV_NG * TV_LROW) + (size_t)grp * TV_LROW) + g * (TV_PER / 8);   // chunk 0: shared memory
+			const uint4* Lg = (const uint4*)(S.hlist + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);                            // further chunks (rare): global
+			for (int ch = 0; ch * TV_CHUNK < cntE; ch++) {
+				unsigned w[TV_PER / 2];
+				#pragma unroll
+				for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = ch == 0 ? Ls[v] : __ldg(Lg + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
+				const int rem = cntE - ch * TV_CHUNK - g;   // entries u * TV_G + g of this chunk exist for u * TV_G < rem
 #if TV_ILP2
-					#pragma unroll
-					for (int u = 0; u < TV_PER; u += 2) {   // two entries per trip (one 32-bit word of the list); a missing one points at the dummy record
-						if (u * TV_G < rem) tv_pair2<POLY, F>(ctx, T, K, s, (int)(w[u >> 1] & 0xffffu), (u + 1) * TV_G < rem ? (int)(w[u >> 1] >> 16) : M);
-					}
+				#pragma unroll
+				for (int u = 0; u < TV_PER; u += 2) {   // two entries per trip (one 32-bit word of the list); a missing one points at the dummy record
+					if (u * TV_G < rem) tv_pair2<POLY, F>(ctx, T, K, s, (int)(w[u >> 1] & 0xffffu), (u + 1) * TV_G < rem ? (int)(w[u >> 1] >> 16) : M);
+				}
 #else
-					#pragma unroll
-					for (int u = 0; u < TV_PER; u++) {
-						if (u * TV_G < rem) tv_pair<POLY, F>(ctx, T, K, s, (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu));
-					}
+				#pragma unroll
+				for (int u = 0; u < TV_PER; u++) {
+					if (u * TV_G < rem) tv_pair<POLY, F>(ctx, T, K, s, (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu));
+				}
 #endif
-				}
-			} else {
-				const float fx = pairs ? (float)(s.pi.x - ox) : 0.f, fy = pairs ? (float)(s.pi.y - oy) : 0.f, fz = pairs ? (float)(s.pi.z - oz) : 0.f;
-				const int nchW = __reduce_max_sync(0xffffffffu, (cntE + TV_CHUNK - 1) / TV_CHUNK);
-				for (int ch = 0; ch < nchW; ch++) {
-					unsigned w[TV_PER / 2];
-					const int rem = cntE - ch * TV_CHUNK;
-					if (rem > 0) {
-						#pragma unroll
-						for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(L + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
-					} else {
-						#pragma unroll
-						for (int v = 0; v < TV_PER / 2; v++) w[v] = (unsigned)M * 0x10001u;
-					}
-					const int tripsW = (min(__reduce_max_sync(0xffffffffu, rem), TV_CHUNK) + TV_G - 1) / TV_G;   // the tail of a chunk is padding
-					int qn = 0;
-					#pragma unroll
-					for (int u = 0; u < TV_PER; u++) {
-						if (u < tripsW) {   // uniform over the warp
-							const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
-							const float4 f = T.fpos[m];
-							const float dx = f.x - fx, dy = f.y - fy, dz = f.z - fz;
-							const bool hit = dx * dx + dy * dy + dz * dz < rfilt2;
-							const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
-							if (hit) gq[qn + __popc(gb & lower)] = (uint16_t)m;
-							qn += __popc(gb);
-						}
-					}
-					__syncwarp();
-					for (int t = g; t < qn; t += TV_G) tv_pair<POLY, F>(ctx, T, K, s, gq[t]);
-					__syncwarp();
-				}
 			}
 			F::reduce(ctx, gmask);   // all lanes, uniform
 			if (act && s.lead) F::end(ctx, S, K, s);
 		}
-	}
-}
-
-// ---- hit list of a new position epoch ------------------------------------------------------------------------------
-// After the positions changed (prediction, correction) the Verlet candidates are filtered ONCE with the float positions
-// of the new epoch; every neighbour pass until the next change then follows the hit list (k_tv, FOLLOW).  Stages only the
-// float positions (16 bytes per halo record); same warp-uniform scan as the walker's scanning mode.
-static __global__ void __launch_bounds__(TV_T, 4) k_tv_hits(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
-	if (!S.hitFlag[0]) return;   // k_hits_decide: the hit list still covers the current positions
-	extern __shared__ __align__(16) unsigned char smemRaw[];
-	__shared__ int sTab[TV_TABMAX], sItem;
-	__shared__ unsigned sMinBits;
-	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
-	float4* const fpos = T.fpos;
-	uint16_t* ownMap = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM);
-	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
-	uint16_t* hl = ownMap + TV_MAXOWN + (size_t)grp * S.tlCap;
-	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
-	const unsigned gbits = (1u << TV_G) - 1u, lower = (1u << g) - 1u;
-	const bool three = K.p.dim == 3;
-	const int nItems = *S.nTiles;
-	const float rfilt2 = K.hitR2;
-	const int* hOff = sTab; const int* hBase = sTab + K.HVt + 1;
-	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
-		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
-		const TvBox b = tv_box(K, S.tileList[tt]);
-		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; S.tileClose[b.c0 / K.TV] = 1; }
-		tv_load_table(S, K, tt, sTab);
-		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
-		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_tv_build
-		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
-		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		tv_stage<false, 0>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, ownMap);
-		if (tid == 0) fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);
-		__syncthreads();
-		for (int p0 = 0; p0 < P; p0 += TV_NG) {
-			const int p = p0 + grp;
-			const bool act = p < P;
-			const int i = own0 + (act ? p : 0);
-			int cntE = 0; float4 fi = make_float4(0.f, 0.f, 0.f, 0.f);
-			if (act) { cntE = S.tlistCnt[i]; fi = fpos[ownMap[p]]; }
-			const uint4* L = (const uint4*)(S.tlist + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);
-			const int nchW = __reduce_max_sync(0xffffffffu, (cntE + TV_CHUNK - 1) / TV_CHUNK);
-			int cntH = 0; float dmin = __int_as_float(0x7f800000);
-			for (int ch = 0; ch < nchW; ch++) {
-				unsigned w[TV_PER / 2];
-				const int rem = cntE - ch * TV_CHUNK;
-				if (rem > 0) {
-					#pragma unroll
-					for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(L + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
-				} else {
-					#pragma unroll
-					for (int v = 0; v < TV_PER / 2; v++) w[v] = (unsigned)M * 0x10001u;
-				}
-				const int tripsW = (min(__reduce_max_sync(0xffffffffu, rem), TV_CHUNK) + TV_G - 1) / TV_G;
-				#pragma unroll
-				for (int u = 0; u < TV_PER; u++) {
-					if (u < tripsW) {
-						const int m = (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu);
-						const float4 f = fpos[m];
-						const float dx = f.x - fi.x, dy = f.y - fi.y, dz = f.z - fi.z;
-						const float d2 = dx * dx + dy * dy + dz * dz;
-						const bool hit = d2 < rfilt2;
-						if (act) dmin = fminf(dmin, d2);
-						const unsigned gb = (__ballot_sync(0xffffffffu, hit) >> gshift) & gbits;
-						if (hit) hl[tv_list_pos(cntH + __popc(gb & lower))] = (uint16_t)m;
-						cntH += __popc(gb);
-					}
-				}
-			}
-			__syncwarp();
-			if (act) {
-				uint4* dstH = (uint4*)(S.hlist + (size_t)i * (size_t)S.tlCap);
-				const int nq = (cntH + TV_CHUNK - 1) / TV_CHUNK * (TV_CHUNK / 8);
-				#pragma unroll
-				for (int v = 0; v < TV_PER / 8; v++) for (int c = 0; c * (TV_CHUNK / 8) < nq; c++) dstH[c * (TV_CHUNK / 8) + g * (TV_PER / 8) + v] = ((const uint4*)hl)[c * (TV_CHUNK / 8) + g * (TV_PER / 8) + v];
-				if (g == 0) {
-					S.hcnt[i] = (uint16_t)cntH;
-					S.hpos[i] = make_float4(fi.x + (float)(ox - K.p.domainMinX), fi.y + (float)(oy - K.p.domainMinY), fi.z + (float)(oz - (three ? K.p.domainMinZ : 0.0)), 0.f);
-				}
-			}
-			{ const unsigned mb = __reduce_min_sync(0xffffffffu, __float_as_uint(dmin)); if ((tid & 31) == 0) atomicMin(&sMinBits, mb); }
-			__syncwarp();
-		}
-		__syncthreads();
-		if (tid == 0) { const float md = __uint_as_float(sMinBits); S.itemMinD2[tt] = md; if (S.tileList[tt] >= 0) S.tileClose[b.c0 / K.TV] = md < K.closeR2 ? 1 : 0; }
 	}
 }
