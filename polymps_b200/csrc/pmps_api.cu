@@ -252,6 +252,16 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	return PMPS_OK;
 }
 
+// margin of the hit lists made from now on: a list reaches hitDelta beyond every cut-off on both sides and stays valid until somebody
+// may have moved hitDelta since it was made (k_hits_decide); a larger margin means fewer re-makes and more rejected candidates per
+// pass, (re + 2 delta)^3.  The close-pair radius of the collision skip moves with it.
+void pmps_set_hit_delta(pmps_handle* h, double delta) {
+	KParams& K = h->K; const PmpsParams& P = K.p;
+	const double maxRe = fmax(P.reL, P.reS), rl = P.bucketSide;
+	K.hitDelta = delta;
+	{ const double r = (maxRe + 2.0 * K.hitDelta) * (1.0 + 1e-5); K.hitR2 = (float)(r * r); }
+	{ const double r = ((P.collisionType == 1 ? P.partDist : sqrt(P.distCollisionLimit2)) + 2.0 * K.hitDelta) * (1.0 + 1e-5) + 8.0 * 1.2e-7 * 4.0 * rl; K.closeR2 = (float)(r * r); }
+}
 static int ensure_capacity(pmps_handle* h, int n0) {
 	if (h->numParticlesZero == n0) return PMPS_OK;
 	if (h->numParticlesZero != 0) return pmps_fail(h, PMPS_E_ARG, "numParticlesZero changed from %d to %d; create a new handle", h->numParticlesZero, n0);
@@ -278,7 +288,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 		const size_t nc = K.p.fluidType == 1 ? (size_t)(K.rheoKx + 1) * (K.rheoKy + 1) : 1;
 		rc |= dalloc(h, &S.rheoBL, nc); rc |= dalloc(h, &S.rheoWL, nc); rc |= dalloc(h, &S.rheoIdx, nc); rc |= dalloc(h, &S.meuMaxBits, 1);
 	}
-	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 2); rc |= dalloc(h, &S.hitMove, 4); rc |= dalloc(h, &S.hitFlag, 2); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
+	rc |= dalloc(h, &S.velMax2Bits, 2); rc |= dalloc(h, &S.maxDisp2, 4); rc |= dalloc(h, &S.hitMove, 4); rc |= dalloc(h, &S.hitFlag, 2); rc |= dalloc(h, &S.flags, NFLAGS); rc |= dalloc(h, &S.oodList, PMPS_OOD_CAP);
 	// Verlet list: radius = bucketSide (the reference's own search slack, src/MpsBucket.cpp:23); capacity from the
 	// lattice count with head room (PMPS_LIST_CAP overrides)
 	const double rl = P.bucketSide, lo = P.partDist;
@@ -309,11 +319,9 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	K.guard2 = (float)(guard > 0 ? guard * guard : 0.0);
 	// reach of the hit lists beyond the cut-offs: a hit list stays valid until somebody may have moved hitDelta since it was made
 	// (k_hits_decide); a larger reach means fewer rebuilds and more rejected candidates per pass, (re + 2 delta)^3
-	K.hitDelta = 0.06 * lo;
-	if (const char* e = getenv("PMPS_HIT_DELTA")) { const double v = atof(e); if (v > 0.0 && v < 0.2) K.hitDelta = v * lo; }
-	if (maxRe + 2.0 * K.hitDelta > rl - 1e-3 * lo) K.hitDelta = fmax(0.5 * (rl - 1e-3 * lo - maxRe), 0.0);   // never beyond the Verlet radius
-	{ const double r = (maxRe + 2.0 * K.hitDelta) * (1.0 + 1e-5); K.hitR2 = (float)(r * r); }
-	{ const double r = ((P.collisionType == 1 ? P.partDist : sqrt(P.distCollisionLimit2)) + 2.0 * K.hitDelta) * (1.0 + 1e-5) + 8.0 * 1.2e-7 * 4.0 * rl; K.closeR2 = (float)(r * r); }
+	h->hitDeltaFixed = -1.0;
+	if (const char* e = getenv("PMPS_HIT_DELTA")) { const double v = atof(e); if (v > 0.0 && v < 0.2) h->hitDeltaFixed = v * lo; }
+	pmps_set_hit_delta(h, h->hitDeltaFixed > 0.0 ? h->hitDeltaFixed : 0.06 * lo);
 	// |x_j - mirror_i| >= 2 dist(i, wall) - displacement - |x_j - x_i| > re whenever dist > re + displacement/2: margin = the full guard
 	{ const double far = maxRe * (1.0 + 1e-6) + (guard > 0 ? guard : 0.0) + 1e-6 * lo; K.mirrorFar2 = far * far; }
 	k_iota<<<cdiv(n0, 256), 256, 0, h->stream>>>(S.hostIdx, S.slotOfHost, n0);

@@ -64,7 +64,8 @@ struct DevView {
 	int32_t tlCap;                       // entries per slot in hlist (multiple of 64)
 	// device scalars
 	unsigned long long* velMax2Bits;     // max |v|^2 of fluid particles (bits of a non-negative double)
-	float* maxDisp2;                     // [0] max squared displacement since the list build, [1] max squared shift of the shifting passes of the step (float, >= 0)
+	float* maxDisp2;                     // [0] max squared displacement since the list build, [1] max squared shift of the shifting passes of the step (float, >= 0),
+	                                     // [2] copy of [0] taken at the end of the last step (one GPU: mid_step_check derives the size of a step's small moves from it)
 	float* hitMove;                      // hit-list validity (pmps_tv.cuh): [0] largest squared displacement of ANY slot (halo copies included)
 	                                     // from its position when the hit list was made (running maximum, reset by a rebuild), [1] the margin
 	                                     // hitDelta the current list was made with
@@ -142,6 +143,7 @@ struct pmps_handle {
 	int nTilesAll = 0, smCount = 148, walkSeq = 0; bool tileWallValid = false;
 	double dispNow = 0.0, dispInc = 0.0, dispIncPrev = 0.0; int stepsSinceBuild = 0; bool needRebuild = true;   // displacement since the list build (step_begin's rebuild decision)
 	double lastShift = 0.0;              // largest shift of the last step's shifting passes
+	double dispMid = 0.0, tailMove = 0.0, hitDeltaFixed = -1.0;   // one GPU: displacement right after the last mid-step check; largest move of a step's phases after it; PMPS_HIT_DELTA
 	double* slabWork = nullptr; pmps_sum_fn slabSum = nullptr; pmps_refresh_fn slabRefresh = nullptr; void* slabUser = nullptr;   // pmps_slab_set_hooks
 	double meuMax = 0.0;                 // max MEU of the last rheology pass (CFLvisc)
 	cudaStream_t ioStream = nullptr; cudaEvent_t evIoUp = nullptr, evIoMid = nullptr; void* stage2 = nullptr;   // pmps_step_host: copies overlapped with the step
@@ -190,6 +192,7 @@ int pmps_sort_and_list(pmps_handle* h);
 int pmps_ensure_list(pmps_handle* h);
 int pmps_tv_prepare(pmps_handle* h);
 int pmps_tv_hits(pmps_handle* h);
+void pmps_set_hit_delta(pmps_handle* h, double delta);
 int pmps_ppe_solve(pmps_handle* h);
 int pmps_step_end_host(pmps_handle* h);   // step_end of the fused step + the time advance (pmps_stages.inc), for pmps_step_host
 int pmps_step_end_apply(pmps_handle* h, double disp2, double shift2);   // pmps_stages.inc: the host half of step_end

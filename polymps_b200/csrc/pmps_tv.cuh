@@ -85,11 +85,13 @@ __host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes p
 #define TV_REC_MAX (4 + 24 + 24 + 8 * 3)   // the fattest pack of the step paths: F3 (vel, press, pndi, RHO)
 // blocks per SM by the bytes a pack stages per record (shared memory decides: TV_MAXM * rec + TV_FIXED_BYTES per block, 227 KB per SM):
 // up to TV_OCC4_REC four blocks (64 registers per thread), up to TV_OCC3_REC three (80 registers), two otherwise (128 registers)
+// (measured on the B200, 10 M particles: four / three blocks against two everywhere -28 % on the concentration pass, -14 % on the
+// concentration gradient, -12 % on the pressure gradient, profiles/r02_variants.txt)
 #ifndef TV_OCC4_REC
-#define TV_OCC4_REC 0
+#define TV_OCC4_REC 28
 #endif
 #ifndef TV_OCC3_REC
-#define TV_OCC3_REC 0
+#define TV_OCC3_REC 44
 #endif
 #define TV_BLOCKS(f) (tv_rec_bytes(f) <= TV_OCC4_REC ? 4 : tv_rec_bytes(f) <= TV_OCC3_REC ? 3 : 2)
 // staged records per work item: a compile-time constant, so every plane of the shared-memory image sits at a constant
@@ -321,17 +323,18 @@ __device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, con
 // 197 warp-instructions per particle against 1 218 (two-level build: Verlet list + hit list) + 197 (refilter) of the
 // round-1 kernels (ncu, profiles/r02_ncu_*): the Verlet list of radius bucketSide is gone.
 #define HL_T 128
-static __global__ void __launch_bounds__(HL_T, 4) k_hl_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx, int force) {
+#define HL_ROW (TV_CHUNK + 2)   // 16-bit entries per shared-memory row: the first chunk of a list ((HL_ROW / 2) is odd: lanes fall into different banks)
+static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx, int force) {
 	if (!force && !S.hitFlag[0]) return;   // k_hits_decide: the hit list still covers the current positions
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
 	__shared__ unsigned sMinBits;   // smallest squared pair distance of the item (bits of a positive float)
 	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
 	float4* const fpos = T.fpos;
-	const int cap = S.tlCap, LS = cap + 2;   // row stride in 16-bit entries: (cap + 2) / 2 is odd
+	const int cap = S.tlCap;
 	const int tid = threadIdx.x, lane = tid & 31, w0 = tid & ~31;
 	uint16_t* const rows = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM);
-	uint16_t* const row = rows + (size_t)tid * LS;
+	uint16_t* const row = rows + (size_t)tid * HL_ROW;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
 	const float R2 = K.hitR2;
@@ -351,6 +354,7 @@ static __global__ void __launch_bounds__(HL_T, 4) k_hl_build(const __grid_consta
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
 		tv_stage<false, 0, HL_T>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, nullptr);
+		if (tid == 0) fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the far-away dummy record: what a lane reads beyond the end of its stretch
 		__syncthreads();
 		for (int p0 = 0; p0 < P; p0 += HL_T) {   // uniform over the block
 			const int p = p0 + tid;
@@ -358,7 +362,8 @@ static __global__ void __launch_bounds__(HL_T, 4) k_hl_build(const __grid_consta
 			const int i = own0 + (act ? p : 0);
 			{	// every entry of the row points at the dummy record until a hit overwrites it
 				uint32_t* r32 = (uint32_t*)row; const uint32_t pad = (uint32_t)M * 0x10001u;
-				for (int q = 0; q < cap / 2; q++) r32[q] = pad;
+				#pragma unroll
+				for (int q = 0; q < TV_CHUNK / 2; q++) r32[q] = pad;
 			}
 			int hx = 1, hy = 1, hz = three ? 1 : 0, self = -1;
 			float4 fi = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -369,22 +374,43 @@ static __global__ void __launch_bounds__(HL_T, 4) k_hl_build(const __grid_consta
 				self = hOff[hbs] + (i - hBase[hbs]);
 				fi = fpos[self];
 			}
+			// the sweep: hits are appended to the row in the order found (the copy-out below applies the lane-major order of the
+			// walker); only the first chunk lives in shared memory — a longer list (rare: 64 hits need 1.4 x the lattice density)
+			// gets its further entries from a second sweep that writes straight to global memory
 			int cnt = 0; float dmin = __int_as_float(0x7f800000);
+			const unsigned rowS = (unsigned)__cvta_generic_to_shared(row);
 			for (int dz = three ? -1 : 0; dz <= (three ? 1 : 0); dz++) for (int dy = -1; dy <= 1; dy++) {
 				const int hb0 = ((hz + dz) * b.HY + hy + dy) * b.HX + hx - 1;
 				const int r0 = hOff[hb0], r1 = act ? hOff[hb0 + 3] : r0;
 				const int trips = __reduce_max_sync(0xffffffffu, r1 - r0);
-				#pragma unroll 4
-				for (int k = 0; k < trips; k++) {
-					const int m = r0 + k;
-					if (m < r1 && m != self) {
-						const float4 f = fpos[m];
-						const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
-						const float d2 = dx * dx + dy2 * dy2 + dz2 * dz2;
-						dmin = fminf(dmin, d2);
-						if (d2 < R2) { if (cnt < cap) row[tv_list_pos(cnt)] = (uint16_t)m; cnt++; }
+				for (int k = 0; k < trips; k += 4) {
+					// four candidates at a time: the loads first (independent), then the four tests, then the appends
+					int m[4]; float4 f[4]; float d2[4];
+					#pragma unroll
+					for (int u = 0; u < 4; u++) { const int mm = r0 + k + u; m[u] = (mm < r1 && mm != self) ? mm : M; f[u] = fpos[m[u]]; }
+					#pragma unroll
+					for (int u = 0; u < 4; u++) { const float dx = f[u].x - fi.x, dy2 = f[u].y - fi.y, dz2 = f[u].z - fi.z; d2[u] = dx * dx + dy2 * dy2 + dz2 * dz2; }
+					dmin = fminf(fminf(dmin, fminf(d2[0], d2[1])), fminf(d2[2], d2[3]));
+					#pragma unroll
+					for (int u = 0; u < 4; u++) {   // (the row address is kept in a register by hand: under the 80-register cap ptxas re-derives it from %tid for every store)
+						const bool hit = d2[u] < R2;
+						if (hit && cnt < TV_CHUNK) asm volatile("st.shared.u16 [%0], %1;" :: "r"(rowS + 2u * (unsigned)cnt), "h"((unsigned short)m[u]) : "memory");
+						cnt += hit ? 1 : 0;
 					}
 				}
+			}
+			if (cnt > TV_CHUNK) {   // second sweep (divergent, rare): entries 64, 65, ... in the walker's order, then the padding of the last chunk
+				uint16_t* const grow = S.hlist + (size_t)i * (size_t)cap;
+				int c2 = 0;
+				for (int dz = three ? -1 : 0; dz <= (three ? 1 : 0); dz++) for (int dy = -1; dy <= 1; dy++) {
+					const int hb0 = ((hz + dz) * b.HY + hy + dy) * b.HX + hx - 1;
+					for (int mm = hOff[hb0]; mm < hOff[hb0 + 3]; mm++) {
+						if (mm == self) continue;
+						const float4 f = fpos[mm]; const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
+						if (dx * dx + dy2 * dy2 + dz2 * dz2 < R2) { if (c2 >= TV_CHUNK && c2 < cap) grow[tv_list_pos(c2)] = (uint16_t)mm; c2++; }
+					}
+				}
+				for (int e = min(cnt, cap); (e & (TV_CHUNK - 1)) != 0; e++) grow[tv_list_pos(e)] = (uint16_t)M;
 			}
 			if (act) {
 				if (cnt > cap) { atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = cap; }
@@ -392,14 +418,16 @@ static __global__ void __launch_bounds__(HL_T, 4) k_hl_build(const __grid_consta
 				S.hpos[i] = make_float4(fi.x + (float)(ox - K.p.domainMinX), fi.y + (float)(oy - K.p.domainMinY), fi.z + (float)(oz - (three ? K.p.domainMinZ : 0.0)), 0.f);
 			} else cnt = 0;
 			__syncwarp();
-			// rows -> hlist: the warp copies one particle's chunks at a time, 128 contiguous bytes per instruction
+			// first chunks: rows -> hlist in the lane-major order (entry e of the list sits at tv_list_pos(e)): destination word `lane`
+			// holds positions 2 lane and 2 lane + 1 = entries e0 and e0 + TV_G; one particle's 128 contiguous bytes per instruction
+			const int e0 = ((2 * lane) % TV_PER) * TV_G + (2 * lane) / TV_PER;
 			for (int q = 0; q < 32; q++) {
 				const int pq = p0 + w0 + q;
 				if (pq >= P) break;   // uniform over the warp
-				const int nch = (__shfl_sync(0xffffffffu, cnt, q) + TV_CHUNK - 1) / TV_CHUNK;
-				const uint32_t* src = (const uint32_t*)(rows + (size_t)(w0 + q) * LS);
+				if (__shfl_sync(0xffffffffu, cnt, q) == 0) continue;   // uniform
+				const uint16_t* src = rows + (size_t)(w0 + q) * HL_ROW;
 				uint32_t* dst = (uint32_t*)(S.hlist + (size_t)(own0 + pq) * (size_t)cap);
-				for (int c = 0; c < nch; c++) dst[c * (TV_CHUNK / 2) + lane] = src[c * (TV_CHUNK / 2) + lane];
+				dst[lane] = (uint32_t)src[e0] | ((uint32_t)src[e0 + TV_G] << 16);
 			}
 			{ const unsigned mb = __reduce_min_sync(0xffffffffu, __float_as_uint(dmin)); if (lane == 0) atomicMin(&sMinBits, mb); }
 			__syncwarp();
