@@ -153,20 +153,22 @@ def dam3d_block(k: int, flow: bool = False, **kw) -> Case:
 
 
 def dam3d_splash(nx: int, ny: int, nz: int, *, lo: float = 0.01, seed: int = 3, name: str | None = None, **kw) -> Case:
-    """Particles LEAVE the domain: a dam3d column under a low open top (tank barely higher than the column) whose whole top layer
-    flies upwards at staggered speeds, so that in every one of the three out-of-domain checks of the next few steps some particles
-    cross z = domainMax - bucketSide (src/MpsParticle.cpp:286-296).  The top layer ends the particle array (x fastest, then y,
-    then z), so the LAST live particle is among the leavers: the reference's serial swap-with-last loop copies a particle that is
-    itself outside over a hole and does not re-test it in the same call (src/MpsParticle.cpp:298-396) — the order-dependent detail
+    """Particles LEAVE the domain: a dam3d column whose whole top layer rises at staggered speeds of 0.09-0.18 lo per step (inside
+    the search slack (bucketSide - re)/2 = 0.21 lo a step may move, so the reference's own stale-bucket search stays complete)
+    under a domain top set 0.55 lo above that layer, so that in the out-of-domain checks of steps 3-7 some particles cross
+    z = domainMax - bucketSide (src/MpsParticle.cpp:286-296).  The top layer ends the particle array (x fastest, then y, then z),
+    so the LAST live particle is among the leavers: the reference's serial swap-with-last loop copies a particle that is itself
+    outside over a hole and does not re-test it in the same call (src/MpsParticle.cpp:298-396) — the order-dependent detail
     SURVEY H5 names."""
     tank = ((1.61 / 0.6) * nx * lo, ny * lo, (nz + 1.5) * lo)
     c = dam3d(nx, ny, nz, lo=lo, jitter=0.05, name=name or "splash", tank=tank, **kw)
     dt = c.options["numerical"]["time_step"]
     bucket = max(c.options["numerical"]["effective_radius"].values()) * lo * (1.0 + c.options["numerical"]["CFL_number"])
+    # the reference pads the domain by 3 lo (src/MpsParticle.cpp:139-144): limit = domain max + 3 lo - bucketSide
+    c.options["domain"]["max"]["z"] = float((nz - 0.5 + 0.55) * lo - 3.0 * lo + bucket)
     top = c.pos[:, 2] > (nz - 1) * lo
-    dist = (tank[2] + 3.0 * lo) - bucket - c.pos[:, 2]   # the reference pads the domain by 3 lo (src/MpsParticle.cpp:139-144)
     rng = np.random.default_rng(seed)
-    c.vel[top, 2] = dist[top] / dt / rng.uniform(0.8, 3.2, size=int(top.sum()))
+    c.vel[top, 2] = rng.uniform(0.09, 0.18, size=int(top.sum())) * lo / dt
     return c
 
 

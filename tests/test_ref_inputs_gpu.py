@@ -76,6 +76,17 @@ def _oracle(case, root, jacobi):
 
 
 PRINT = 2.1e-6   # one unit of the 6th printed decimal (+ rounding)
+# .vtu array name (src/MpsInputOutput.cpp:1338-1570) -> state field
+VTU_FIELD = {"Position": "pos", "Velocity": "vel", "pressure": "press", "BC": "particleBC", "pnd": "pndi", "pndSmall": "pndSmall", "nNeigh": "numNeigh",
+             "npcdDeviation": "npcdDeviation", "polygonNormal": "polygonNormal", "concentration": "concentration", "GradCi": "gradConcentration",
+             "RHO": "RHO", "MEU": "MEU", "PTYPE": "PTYPE", "ParticleType": "particleType", "nearMeshType": "nearMeshType",
+             "ConcVol": "Cv", "MEUy": "MEU_Y", "II": "II", "p_smooth": "p_smooth", "Inertia": "Inertia", "Normal_Stress": "p_rheo_new", "VF": "VF"}
+INT_FIELDS = ("BC", "nNeigh", "PTYPE", "ParticleType", "nearMeshType")
+
+
+def _field(st, k, n):
+    x = getattr(st, VTU_FIELD[k]); w = x.size // st.numParticlesZero
+    return np.asarray(x[:n * w], dtype=np.float64)
 
 
 @pytest.mark.gpu
@@ -98,29 +109,33 @@ def test_reference_documents_verbatim_through_both_binaries(name, capsys):
         gs, ps = _oracle(case, root, jacobi=False)
         if gs is not None:   # (single-mesh cases) the oracle's Gauss-Seidel mode IS the stock binary, to the printed decimals
             n = gs.numParticles
-            assert np.abs(a["Position"] - gs.pos[:3 * n]).max() <= PRINT and np.abs(a["pressure"] - gs.press[:n]).max() <= PRINT + 1e-6 * np.abs(a["pressure"]).max()
+            for k in a:   # every array of the file (values are printed as float32, 6 decimals)
+                if k in VTU_FIELD and hasattr(gs, VTU_FIELD[k]):
+                    w = _field(gs, k, n); err = float(np.abs(a[k] - w).max())
+                    assert err <= (0.0 if k in INT_FIELDS else PRINT + 1e-6 * float(np.abs(w).max())), (name, "stock binary vs Gauss-Seidel oracle", k, err)
         if shifting and gs is not None:
             jc, _ = _oracle(case, root, jacobi=True)
-            # (a) tight: drop-in == Jacobi oracle to the printed decimals
-            assert np.abs(b["Position"] - jc.pos[:3 * n]).max() <= PRINT, float(np.abs(b["Position"] - jc.pos[:3 * n]).max())
-            assert np.abs(b["Velocity"] - jc.vel[:3 * n]).max() <= PRINT + 1e-7 * np.abs(jc.vel).max()
-            assert np.abs(b["pressure"] - jc.press[:n]).max() <= PRINT + 1e-6 * np.abs(jc.press).max()
-            assert np.array_equal(b["BC"], jc.particleBC[:n].astype(np.float64))
-            # (b) against the stock binary: the measured Gauss-Seidel / Jacobi difference of this very case, x 1.5
-            tol["Position"] = PRINT + 1.5 * np.abs(gs.pos - jc.pos).max()
-            tol["Velocity"] = PRINT + 1.5 * np.abs(gs.vel - jc.vel).max()
-            tol["pressure"] = PRINT + 1.5 * np.abs(gs.press - jc.press).max()
-            tol["pnd"] = PRINT + 1.5 * np.abs(gs.pndi - jc.pndi).max()
+            # (a) tight: drop-in == Jacobi oracle to the printed decimals, every field the file holds
+            for k in a:
+                if k in INT_FIELDS:
+                    assert np.array_equal(b[k], _field(jc, k, n).astype(np.float64)), k
+                elif k in VTU_FIELD and hasattr(jc, VTU_FIELD[k]):
+                    w = _field(jc, k, n); err = float(np.abs(b[k] - w).max())
+                    assert err <= PRINT + 1e-6 * float(np.abs(w).max()), (name, "drop-in vs Jacobi oracle", k, err)
+            # (b) against the stock binary: the measured Gauss-Seidel / Jacobi difference of this very case and field, x 1.5
+            for k in a:
+                if k in VTU_FIELD and k not in INT_FIELDS and hasattr(jc, VTU_FIELD[k]):
+                    tol[k] = PRINT + 1.5 * float(np.abs(_field(gs, k, n) - _field(jc, k, n)).max())
             with capsys.disabled():
                 print("\n%s: Gauss-Seidel vs Jacobi shifting after %d steps: pos %.2e lo, vel %.2e, press %.2e" % (name, STEPS, (tol["Position"] - PRINT) / 1.5 / ps.partDist, (tol["Velocity"] - PRINT) / 1.5, (tol["pressure"] - PRINT) / 1.5))
-        elif shifting:   # three-mesh / rheology cases without an oracle run here: stock binary only, loose bound of a few shifts
+        elif shifting:   # three-mesh cases without an oracle run here: stock binary only, loose bound of a few shifts on the positions
             lo = DOCS[name]["numerical"]["particle_dist"]
-            tol.update(Position=0.05 * lo, Velocity=None, pressure=None, pnd=None)
+            tol = {k: None for k in a}; tol["Position"] = 0.05 * lo
         for k in a:
             if k in ("connectivity", "offsets", "types") or tol.get(k, PRINT) is None:
                 continue
-            if k == "BC":
-                assert (a[k] != b[k]).mean() <= (0.02 if shifting else 0.0), (k, float((a[k] != b[k]).mean()))
+            if k in INT_FIELDS:   # free-surface flags / neighbour counts flip where the two sweeps leave a particle on either side of a threshold
+                assert (a[k] != b[k]).mean() <= (0.05 if shifting else 0.0), (k, float((a[k] != b[k]).mean()))
                 continue
             err = float(np.abs(a[k] - b[k]).max())
             assert err <= tol.get(k, PRINT) + 1e-8 * float(np.abs(a[k]).max()), (name, k, err, tol.get(k, PRINT))
