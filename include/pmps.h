@@ -218,6 +218,15 @@ int pmps_debug_buckets(pmps_t* h, int32_t* bucketOfParticle, int32_t* bucketStar
 /* neighbour set of host-order particle i under predicate kind: 0 = P(reL), 1 = P(reS), 2 = M(reS), 3 = M(reL),
  * 4 = collision; returns count, fills out[0..cap) with host-order ids in traversal order. */
 int pmps_debug_neighbors(pmps_t* h, int i, int kind, int32_t* out, int cap);
+/* Stale bucket lists after an out-of-domain swap.  checkParticleOutDomain copies the last live particle over the one that left
+ * (src/MpsParticle.cpp:298-396) but the reference re-threads its bucket lists only at the next step start (src/main.cpp:256): for the
+ * rest of the step the moved particle is found by a neighbour loop only from the buckets around the one the particle that left was
+ * listed in.  A single-GPU handle replays that (default on) so that results equal the reference's; off = every particle is found
+ * from where it is (what a slab rank does, whose table order means nothing across ranks). */
+int pmps_set_stale_list_replay(pmps_t* h, int on);
+/* tests: declare array elements (host indices) as listed in the given reference buckets (iz*nXY + iy*nX + ix) until the next
+ * pmps_update_buckets / step start, as if an out-of-domain swap of this step had moved them there */
+int pmps_debug_set_stale(pmps_t* h, int n, const int32_t* hostIdx, const int32_t* bucket);
 /* per-kernel device time of the last pmps_step (CUDA events on the step stream), name list is static */
 int pmps_profile_enable(pmps_t* h, int on);
 int pmps_profile_get(pmps_t* h, int* n, const char*** names, const float** ms_total, const int** launches);

@@ -184,7 +184,7 @@ template <class T> static int dalloc(pmps_handle* h, T** p, size_t count) {
 
 static int alloc_view(pmps_handle* h, DevView& V, int n0, bool primary) {
 	int rc = 0;
-	rc |= dalloc(h, &V.pos, n0); rc |= dalloc(h, &V.vel, n0); rc |= dalloc(h, &V.hostIdx, n0); rc |= dalloc(h, &V.particleNearWall, n0);
+	rc |= dalloc(h, &V.pos, n0); rc |= dalloc(h, &V.vel, n0); rc |= dalloc(h, &V.hostIdx, n0); rc |= dalloc(h, &V.particleNearWall, n0); rc |= dalloc(h, &V.stepCell, n0);
 #define X(n) rc |= dalloc(h, &V.n, n0);
 	PMPS_I32_FIELDS(X)
 	PMPS_F64_FIELDS(X)
@@ -243,7 +243,7 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	if (const char* e = getenv("PMPS_TILE")) { int a = 0, b = 0, c = 0; if (sscanf(e, "%d,%d,%d", &a, &b, &c) == 3 && a > 0 && b > 0 && c > 0 && (a + 2) * (b + 2) * (c + 2) <= TV_HMAX) { K.TX = a; K.TY = b; K.TZ = params->dim == 3 ? c : 1; } }
 	K.TV = K.TX * K.TY * K.TZ;
 	K.HVt = (K.TX + 2) * (K.TY + 2) * (params->dim == 3 ? K.TZ + 2 : 1); if (K.HVt < 27) K.HVt = 27;
-	K.tabStride = (2 * K.HVt + 3 + 3) & ~3;
+	K.tabStride = (2 * K.HVt + 6 + 3) & ~3;   // hOff[HVt + 1], hBase[HVt], own0, P, box origin (3), rounded up to a multiple of 4
 	K.nTX = (params->numBucketsX + K.TX - 1) / K.TX; K.nTY = (params->numBucketsY + K.TY - 1) / K.TY; K.nTZ = (params->numBucketsZ + K.TZ - 1) / K.TZ;
 	const long long nC = (long long)K.nTX * K.nTY * K.nTZ * K.TV;
 	if (nC > 2000000000ll) { delete h; return pmps_fail(nullptr, PMPS_E_OVERFLOW, "pmps_create: %lld cells overflow int32", nC); }
@@ -270,7 +270,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	DevView& S = h->V; KParams& K = h->K; const PmpsParams& P = K.p;
 	int rc = 0;
 	rc |= alloc_view(h, S, n0, true); rc |= alloc_view(h, h->A, n0, false);
-	rc |= dalloc(h, &S.scratch1, n0); rc |= dalloc(h, &S.bpos, n0); rc |= dalloc(h, &S.hpos, n0); rc |= dalloc(h, &S.slotOfHost, n0); rc |= dalloc(h, &S.cellOf, n0);
+	rc |= dalloc(h, &S.scratch1, n0); rc |= dalloc(h, &S.bpos, n0); rc |= dalloc(h, &S.hpos, n0); rc |= dalloc(h, &S.slotOfHost, n0); rc |= dalloc(h, &S.cellOf, n0); rc |= dalloc(h, &S.hid, 1 + 2 * PMPS_HID_CAP);
 	rc |= dalloc(h, &S.cellStart, (size_t)S.nC + 2); rc |= dalloc(h, &h->cellCount, (size_t)S.nC + 2);
 	rc |= dalloc(h, &h->perm, n0); rc |= dalloc(h, &h->arbRank, n0); rc |= dalloc(h, &h->newCell, n0);
 	rc |= dalloc(h, &h->tmpHost, 2 * (size_t)n0);

@@ -65,6 +65,7 @@ struct BPredictTail {
 		S.accStar.x[i] = ax; S.accStar.y[i] = ay; S.accStar.z[i] = az;
 		if (s.type == K.p.fluid) {
 			double4 p = s.pi, v = S.vel[i];
+			S.stepCell[i] = ref_bucket_insert(K, s.pi);   // where the reference's lists of this step hold the particle (pmps_domain.cu)
 			integrate_predict(p, v, ax, ay, az, K.p.timeStep);
 			S.pos2[i] = p; S.vel2[i] = v;
 			track_disp(S, K, i, p);

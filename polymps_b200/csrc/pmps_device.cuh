@@ -21,21 +21,42 @@ __device__ __forceinline__ double dot3_exact(double ax, double ay, double az, do
 __device__ __forceinline__ int bucket_coord(double x, double mn, double inv, double eps) {   // src/MpsBucket.cpp:420-425
 	return (int)__dadd_rn(__dmul_rn(__dsub_rn(x, mn), inv), eps);
 }
+// the bucket updateParticlesID threads a particle on (src/MpsBucket.cpp:310-313 in 2D — with epsilonZero —, :333-336 in 3D — without)
+__device__ __forceinline__ int ref_bucket_insert(const KParams& K, const double4& p) {
+	const PmpsParams& P = K.p;
+	if (P.dim == 2) return bucket_coord(p.y, P.domainMinY, P.invBucketSide, P.epsilonZero) * P.numBucketsX + bucket_coord(p.x, P.domainMinX, P.invBucketSide, P.epsilonZero);
+	const int ix = (int)__dmul_rn(__dsub_rn(p.x, P.domainMinX), P.invBucketSide), iy = (int)__dmul_rn(__dsub_rn(p.y, P.domainMinY), P.invBucketSide),
+	          iz = (int)__dmul_rn(__dsub_rn(p.z, P.domainMinZ), P.invBucketSide);
+	return (iz * P.numBucketsY + iy) * P.numBucketsX + ix;
+}
 __device__ __forceinline__ double madd_exact(double a, double b, double c) { return __dadd_rn(c, __dmul_rn(a, b)); }   // c + a*b, two roundings
 
-// ---- fast 1-ulp reciprocals (MUFU seed + two Newton steps; no special-case handling: arguments are finite, > 0) ----
+// ---- fast 1-ulp reciprocals (MUFU seed, relative error <= 2^-20, + ONE third-order step; no special-case handling: arguments
+// are finite, > 0).  With e = 1 - x y0^2 the exact correction is y0 (1 - e)^-1/2 = y0 (1 + e/2 + 3 e^2/8 + O(e^3)): the O(e^3) left
+// over is < 1e-18, i.e. the result carries only the rounding of its last two operations (checked against a 64-bit-mantissa
+// evaluation over the whole seed-error range: 1.4e-16).  5 FP64 operations instead of the 7 of two Newton steps.
 __device__ __forceinline__ double fast_rsqrt(double x) {
 	double y; asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+#ifdef PMPS_NEWTON2
 	const double h = 0.5 * x;
 	double e = fma(-h * y, y, 0.5); y = fma(y, e, y);
 	e = fma(-h * y, y, 0.5); y = fma(y, e, y);
 	return y;
+#else
+	const double e = fma(-(x * y), y, 1.0);
+	return fma(y, fma(0.375, e, 0.5) * e, y);
+#endif
 }
-__device__ __forceinline__ double fast_rcp(double x) {
+__device__ __forceinline__ double fast_rcp(double x) {   // e = 1 - x y0: 1/x = y0 (1 + e + e^2 + O(e^3))
 	double y; asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+#ifdef PMPS_NEWTON2
 	double e = fma(-x, y, 1.0); y = fma(y, e, y);
 	e = fma(-x, y, 1.0); y = fma(y, e, y);
 	return y;
+#else
+	const double e = fma(-x, y, 1.0);
+	return fma(y, fma(e, e, e), y);
+#endif
 }
 
 __device__ __forceinline__ int pk_type(const double4& p) { return (int)(uint32_t)(__double_as_longlong(p.w) & 0xffffffffll); }
@@ -89,6 +110,28 @@ __device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, i
 __device__ __forceinline__ void track_shift(const DevView& S, int i, double dx, double dy, double dz) {   // size of a shifting move (hit-list validity)
 	if (!owned_slot(S, i)) return;
 	const float a = (float)dx, b = (float)dy, c = (float)dz; atomic_max_f(S.maxDisp2 + 1, (a * a + b * b + c * c) * 1.0001f);
+}
+
+// ---- stale bucket lists after an out-of-domain swap ------------------------------------------------------------------
+// checkParticleOutDomain copies the LAST live particle over the one that left (src/MpsParticle.cpp:298-396) but the bucket
+// lists are only re-threaded at the next step start (src/main.cpp:256): until then array element i — now the moved particle —
+// is still listed in the bucket of the particle that left, so a neighbour loop finds it only from there.  hid_visible(): does the
+// 27-bucket search of a particle at pi (bucketCoordinates, src/MpsBucket.cpp:420-425: epsilonZero on every axis) reach `cell`?
+__device__ __forceinline__ bool hid_visible(const KParams& K, int cell, const double4& pi) {
+	const PmpsParams& P = K.p;
+	const int nX = P.numBucketsX, nXY = nX * P.numBucketsY;
+	const int cz = cell / nXY, cy = (cell - cz * nXY) / nX, cx = cell - cz * nXY - cy * nX;
+	const int bx = bucket_coord(pi.x, P.domainMinX, P.invBucketSide, P.epsilonZero), by = bucket_coord(pi.y, P.domainMinY, P.invBucketSide, P.epsilonZero);
+	if (abs(bx - cx) > 1 || abs(by - cy) > 1) return false;
+	if (P.dim == 2) return cz == 0;   // minZ = maxZ = 0 (src/MpsViscosity.cpp:35)
+	return abs(bucket_coord(pi.z, P.domainMinZ, P.invBucketSide, P.epsilonZero) - cz) <= 1;
+}
+// the bucket the array element of slot `slot` is listed in when the reference's lists are stale for it, else -1
+__device__ __forceinline__ int hid_cell_of_slot(const DevView& S, int slot) {
+	const int nh = S.hid[0]; if (nh == 0) return -1;
+	const int label = S.hostIdx[slot];
+	for (int e = 0; e < nh; e++) if (S.hid[1 + e] == label) return S.hid[1 + PMPS_HID_CAP + e];
+	return -1;
 }
 
 // ---- lane groups --------------------------------------------------------------------------------------------------

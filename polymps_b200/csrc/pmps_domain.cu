@@ -23,7 +23,7 @@ __global__ void k_ood_flag(const __grid_constant__ DevView S, const __grid_const
 	if (k < PMPS_OOD_CAP) S.oodList[k] = S.hostIdx[i];
 }
 
-__global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
+__global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int staleReplay) {
 	int cnt = S.flags[FLAG_OOD_COUNT];
 	if (cnt == 0) return;
 	S.flags[FLAG_OOD_COUNT] = 0;
@@ -31,6 +31,10 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 	int32_t* L = S.oodList;
 	for (int a = 1; a < cnt; a++) { const int v = L[a]; int b = a; while (b > 0 && L[b - 1] > v) { L[b] = L[b - 1]; b--; } L[b] = v; }
 	int live = S.flags[FLAG_LIVE];
+	// stale-list visibility (pmps_device.cuh, hid_visible): array element hi keeps its place in the reference's bucket lists — the
+	// bucket the particle that left was threaded on at the step start — while its content becomes the moved particle
+	int32_t* const H = S.hid; int nh = H[0];
+	auto hid_find = [&](int label) { for (int q = 0; q < nh; q++) if (H[1 + q] == label) return q; return -1; };
 	for (int e = 0; e < cnt; e++) {
 		const int hi = L[e];
 		if (!(hi < live)) continue;
@@ -53,7 +57,13 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 		// it is (slot sl keeps searching around its own position with its own candidate list); the host LABELS are swapped:
 		// slot sl now answers to host index hi, slot si — which receives a copy of sl's fields, as array element hl keeps
 		// them in the reference — becomes the ghost hl.
+		const int cellOfHole = S.stepCell[si];
+		{ const int q = hid_find(hl); if (q >= 0) H[1 + q] = -1; }   // the last element becomes a ghost: whatever it was, it is listed nowhere that matters
 		if (sl != si) {
+			if (staleReplay && hid_find(hi) < 0) {   // (a hole filled twice in one step keeps the bucket of its first occupant: the lists have not changed)
+				if (nh < PMPS_HID_CAP) { H[1 + nh] = hi; H[1 + PMPS_HID_CAP + nh] = cellOfHole; nh++; }
+				else atomicOr(&S.flags[FLAG_GUARD], 8);
+			}
 			S.pos[si] = S.pos[sl]; S.vel[si] = S.vel[sl]; S.particleNearWall[si] = S.particleNearWall[sl];
 #define X(n) S.n[si] = S.n[sl];
 			PMPS_I32_FIELDS(X)
@@ -77,7 +87,7 @@ __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_consta
 		S.press[sg] = 0.0;
 		live--; S.flags[FLAG_OOD_TOTAL] += 1;
 	}
-	S.flags[FLAG_LIVE] = live;
+	S.flags[FLAG_LIVE] = live; H[0] = nh;
 	S.hitMove[0] = 1e30f;   // a slot changed its content: the hit lists are rebuilt at the next check
 }
 
@@ -85,7 +95,21 @@ extern "C" int pmps_check_out_domain(pmps_t* h) {
 	if (!h) return PMPS_E_ARG;
 	if (!h->haveList) return pmps_fail(h, PMPS_E_STATE, "pmps_check_out_domain: call pmps_update_buckets first");
 	LAUNCH(h, "domain.flag", k_ood_flag, cdiv(h->V.n, 256), 256, h->V, h->K);
-	LAUNCH(h, "domain.fix", k_ood_fix, 1, 1, h->V, h->K);
+	LAUNCH(h, "domain.fix", k_ood_fix, 1, 1, h->V, h->K, h->staleReplay ? 1 : 0);
 	CUDA_TRY(h, cudaGetLastError());
+	return PMPS_OK;
+}
+
+extern "C" int pmps_set_stale_list_replay(pmps_t* h, int on) { if (!h) return PMPS_E_ARG; h->staleReplay = on != 0; return PMPS_OK; }
+extern "C" int pmps_debug_set_stale(pmps_t* h, int n, const int32_t* hostIdx, const int32_t* bucket) {
+	if (!h || n < 0 || n > PMPS_HID_CAP || (n > 0 && (!hostIdx || !bucket))) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_debug_set_stale: nothing uploaded");
+	CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+	CUDA_TRY(h, cudaMemcpy(h->V.hid, &n, sizeof(int32_t), cudaMemcpyHostToDevice));
+	if (n > 0) {
+		CUDA_TRY(h, cudaMemcpy(h->V.hid + 1, hostIdx, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice));
+		CUDA_TRY(h, cudaMemcpy(h->V.hid + 1 + PMPS_HID_CAP, bucket, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice));
+	}
 	return PMPS_OK;
 }

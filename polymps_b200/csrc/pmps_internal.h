@@ -36,6 +36,10 @@ struct DevView {
 	int32_t* hostIdx;                    // slot -> host (reference) index
 	int32_t* slotOfHost;                 // host index -> slot
 	int32_t* cellOf;                     // slot -> bucket id at the last rebuild
+	int32_t* stepCell;                   // slot -> the reference bucket (iz*nXY + iy*nX + ix) the particle was threaded on at the START of the current step
+	                                     // (updateParticlesID, src/MpsBucket.cpp:299-353); read when a particle leaves the domain (pmps_domain.cu)
+	int32_t* hid;                        // particles the reference's stale bucket lists hide for the rest of a step after an out-of-domain swap:
+	                                     // [0] entries, [1 .. CAP] host label (-1: dead), [1 + CAP .. 2 CAP] the bucket its array element sits in (hid_visible())
 	int32_t* cellStart;                  // nC+2, slots of cell c (tile-major bucket index, cell_index()) are [cellStart[c], cellStart[c+1]); cell nC = ghosts
 	uint32_t* list; uint16_t* listCnt;   // Verlet candidates (slot ids), row-major, listCap per particle; built on demand
 	uint16_t* hlist; uint16_t* hcnt;       // hit list (pmps_tv.cuh, k_hl_build): the staged records within reach at the positions of the current epoch, tlCap entries
@@ -91,6 +95,7 @@ struct DevView {
 
 enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, FLAG_UPLOAD_TYPES = 7, NFLAGS = 8 };
 #define PMPS_OOD_CAP 65536
+#define PMPS_HID_CAP 1024    // particles moved into a hole by the out-of-domain swap within one step
 #define PMPS_CURSORS 64   // work-stealing cursors per step (one per tile-walker launch)
 
 // Kernel-side parameters: the ABI params plus derived constants
@@ -151,6 +156,7 @@ struct pmps_handle {
 	bool slab = false;                   // slab mode: rebuilds and the step-end scalars are decided by the caller from GLOBAL maxima (pmps_slab.cu)
 	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
 	bool hitForce = false;               // positions were replaced from outside (upload): the next check rebuilds the hit list
+	bool staleReplay = true;             // replay the reference's stale bucket lists after an out-of-domain swap (pmps_set_stale_list_replay)
 	bool hitValid = false;               // hlist matches the current positions (set by the list build / k_tv_hits, cleared when positions change)
 	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;

@@ -40,15 +40,20 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ 
 	const uint32_t* L = S.list + (size_t)i * (size_t)S.listCap; uint32_t* C = M.col + base; double* V = M.val + base;
 	const int cnt = S.listCnt[i];
 	double sum = 0.0, b = 0.0; int nz = 0;
+	// particles moved into a hole by an out-of-domain swap of this step are found only through the bucket their array element is still
+	// listed in (hid_visible, pmps_device.cuh): iFindsJ gates row i's own terms, jFindsI the transposed entry
+	const int nHid = S.hid[0]; const int myHid = nHid > 0 ? hid_cell_of_slot(S, i) : -1;
 	for (int k = 0; k < cnt; k++) {
 		const int j = (int)L[k];
 		const double4 pj = S.pos[j];
+		bool iFindsJ = true, jFindsI = true;
+		if (nHid > 0) { const int hc = hid_cell_of_slot(S, j); iFindsJ = hc < 0 || hid_visible(K, hc, pi); jFindsI = myHid < 0 || hid_visible(K, myHid, pj); }
 		const double rx = pj.x - pi.x, ry = pj.y - pi.y, rz = pj.z - pi.z; const double d2 = sq3_exact(rx, ry, rz);
 		if (!(d2 < K.p.reL2)) continue;
 		const double wL = wgt(sqrt(d2), K.p.reL, K.p.weightType); const double a = wL * K.p.coeffPPE;
 		const int tj = pk_type(pj);
 		// row i (src/MpsPressure.cpp:213-229)
-		bool mine = rowActive;
+		bool mine = rowActive && iFindsJ;
 		if (POLY && mine) { const double mx = pj.x - mix, my = pj.y - miy, mz = pj.z - miz; mine = d2 < sq3_exact(mx, my, mz); }
 		if (mine) {
 			if (tj == K.p.dummyWall) b -= K.p.coeffPPE * (S.RHO[j] * (rx * K.p.gravityX + ry * K.p.gravityY + rz * K.p.gravityZ) * wL);
@@ -61,7 +66,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ 
 		// column i of row j: A_ji exists if row j is active, i is a real neighbour of j, i is not a dummy and BC[i] == inner
 		else if (colOK) {
 			const int bcj = S.particleBC[j];
-			bool theirs = !(bcj == K.p.other || bcj == K.p.surface);
+			bool theirs = !(bcj == K.p.other || bcj == K.p.surface) && jFindsI;
 			if (POLY && theirs) {
 				const double ex = pi.x - S.mirrorParticlePos.x[j], ey = pi.y - S.mirrorParticlePos.y[j], ez = pi.z - S.mirrorParticlePos.z[j];
 				theirs = d2 < sq3_exact(ex, ey, ez);

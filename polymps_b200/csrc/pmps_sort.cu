@@ -139,7 +139,7 @@ __global__ void k_permute_packs(const int32_t* __restrict__ perm, const __grid_c
 	const int o = perm[s];
 	const double4 p = S.pos[o];
 	A.pos[s] = p; A.vel[s] = S.vel[o];
-	A.particleNearWall[s] = S.particleNearWall[o];
+	A.particleNearWall[s] = S.particleNearWall[o]; A.stepCell[s] = S.stepCell[o];
 	const int h = S.hostIdx[o];
 	A.hostIdx[s] = h; S.slotOfHost[h] = s;
 	S.cellOf[s] = newCell[o];   // cellOf / bpos are not double-buffered: written at the new slot, read via perm only above
@@ -207,7 +207,7 @@ int pmps_sort_and_list(pmps_handle* h) {
 	LAUNCH(h, "sort.rank_fix", k_rank_fix, cdiv(n0, T), T, S, h->newCell, S.cellStart, tmp, h->perm);
 	// gather: packs first (needs the old hostIdx), then the planes in groups
 	LAUNCH(h, "sort.permute_packs", k_permute_packs, cdiv(n0, T), T, h->perm, S, A, K, h->newCell);
-	swp(S.pos, A.pos); swp(S.vel, A.vel); swp(S.particleNearWall, A.particleNearWall); swp(S.hostIdx, A.hostIdx);
+	swp(S.pos, A.pos); swp(S.vel, A.vel); swp(S.particleNearWall, A.particleNearWall); swp(S.hostIdx, A.hostIdx); swp(S.stepCell, A.stepCell);
 	S.pos2 = A.pos; S.vel2 = A.vel;
 	{
 		std::vector<std::pair<double**, double**>> planes;

@@ -157,7 +157,7 @@ __device__ __forceinline__ float tv_type_word(const double4& p) { return __int_a
 // One thread per tile: a tile whose halo fits the staging area is one item; otherwise each of its non-empty buckets is.
 // Every item gets its halo table precomputed (K.tabStride ints: hOff[0..HVt], hBase[0..HVt), own0, P — HVt = halo
 // buckets of a whole tile) so the passes read it with one coalesced load instead of chasing cellStart.
-#define TV_TABMAX (2 * TV_HMAX + 4)
+#define TV_TABMAX (2 * TV_HMAX + 8)
 __device__ __forceinline__ void tv_write_table(const DevView& S, const KParams& K, const TvBox& b, int slot) {
 	int* tab = S.itemTab + (size_t)slot * K.tabStride;
 	int run = 0;
@@ -170,6 +170,16 @@ __device__ __forceinline__ void tv_write_table(const DevView& S, const KParams& 
 	tab[b.HV] = run;
 	const int own0 = S.cellStart[b.c0];
 	tab[2 * K.HVt + 1] = own0; tab[2 * K.HVt + 2] = S.cellStart[b.c1] - own0;
+	tab[2 * K.HVt + 3] = b.ox; tab[2 * K.HVt + 4] = b.oy; tab[2 * K.HVt + 5] = b.oz;   // (the passes read the box from here: no divisions per item)
+}
+// the box of a work item from its table in shared memory
+__device__ __forceinline__ TvBox tv_box_tab(const KParams& K, int item, const int* tab) {
+	TvBox b; const bool three = K.p.dim == 3, whole = item >= 0;
+	b.ox = tab[2 * K.HVt + 3]; b.oy = tab[2 * K.HVt + 4]; b.oz = tab[2 * K.HVt + 5];
+	const int ex = whole ? K.TX : 1, ey = whole ? K.TY : 1, ez = whole ? K.TZ : 1;
+	b.c0 = whole ? item * K.TV : ~item; b.c1 = whole ? b.c0 + K.TV : b.c0 + 1;
+	b.HX = ex + 2; b.HY = ey + 2; b.HZ = three ? ez + 2 : 1; b.HV = b.HX * b.HY * b.HZ;
+	return b;
 }
 // Threads enumerate the tiles along a Z-order curve (bits of the thread index dealt round-robin to the axes that still have bits
 // left), so the work items come out in roughly that order: the blocks working at any one time — they take items from a cursor —
@@ -222,8 +232,10 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 
 
 // ---- shared-memory image of the halo ------------------------------------------------------------------------------
+#define TV_HIDMAX 32   // staged records of one work item the reference's stale bucket lists may hide (pmps_device.cuh, hid_visible)
 struct TvStage {   // shared-memory planes of the staged halo: the walker stages FP64 positions + the type word, the list build float positions
 	float4* fpos; int32_t* tw; double *px, *py, *pz; Nb nb;
+	const int* hidN; const int* hidM; const int* hidCell; const unsigned* hidMask;   // hidden records of the item: staged index, bucket their array element is listed in (bit 31 of tw marks them); per lane group: which of them its particle cannot see
 };
 template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp) {
 	TvStage t; constexpr size_t m = TV_MAXM;
@@ -342,9 +354,10 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 	if (blockIdx.x == 0 && tid == 0) S.hitMove[1] = (float)K.hitDelta;   // the margin THIS list was made with (k_hits_decide)
 	for (int tt = tv_first_item(S, cursorIdx, &sItem), nxt = 0; tt < nItems; tt = tv_advance(nxt, &sItem)) {
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
-		const TvBox b = tv_box(K, S.tileList[tt]);
-		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; S.tileClose[b.c0 / K.TV] = 1; }
+		const int item = S.tileList[tt];
 		tv_load_table<HL_T>(S, K, tt, sTab);
+		const TvBox b = tv_box_tab(K, item, sTab);
+		if (tid == 0) { sMinBits = 0x7f800000u; S.itemMinD2[tt] = 0.f; S.tileClose[item >= 0 ? item : (~item) / K.TV] = 1; }
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) {   // a single bucket whose 27-bucket neighbourhood does not fit: reported by pmps_get_scalars
 			if (tid == 0) atomicMax(&S.flags[FLAG_TILE_OVERFLOW], M + 1 > TV_MAXM ? M + 1 : P);
@@ -433,7 +446,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 			__syncwarp();
 		}
 		__syncthreads();
-		if (tid == 0) { const float md = __uint_as_float(sMinBits); S.itemMinD2[tt] = md; if (S.tileList[tt] >= 0) S.tileClose[b.c0 / K.TV] = md < K.closeR2 ? 1 : 0; }
+		if (tid == 0) { const float md = __uint_as_float(sMinBits); S.itemMinD2[tt] = md; if (item >= 0) S.tileClose[item] = md < K.closeR2 ? 1 : 0; }
 	}
 }
 
@@ -480,6 +493,42 @@ static __global__ void __launch_bounds__(256) k_tails(const __grid_constant__ De
 }
 
 // ---- the walker ---------------------------------------------------------------------------------------------------
+// a staged record marked hidden (bit 31 of its type word): may particle s see it?  hidMask (per lane group, made at the start of the
+// round by tv_hid_mask) has bit k set when the reference's search of s does NOT reach the bucket entry k of the item's table is listed in
+__device__ __forceinline__ bool tv_hid_visible(const TvStage& T, int m) {
+	const unsigned mk = T.hidMask[threadIdx.x / TV_G];
+	const int n = min(*T.hidN, TV_HIDMAX);
+	for (int k = 0; k < n; k++) if (T.hidM[k] == m) return ((mk >> k) & 1u) == 0u;
+	return true;
+}
+__device__ __forceinline__ void tv_hid_mask(const TvStage& T, const KParams& K, const Self& s, unsigned* hidMask) {
+	const int n = min(*T.hidN, TV_HIDMAX);
+	unsigned mk = 0u;
+	for (int k = 0; k < n; k++) if (!hid_visible(K, T.hidCell[k], s.pi)) mk |= 1u << k;
+	if (s.lead) hidMask[threadIdx.x / TV_G] = mk;
+	__syncwarp();
+}
+// marks the staged records of the item that are hidden entries (S.hid): one thread per entry; the caller's next barrier publishes the marks
+__device__ __forceinline__ void tv_mark_hidden(const DevView& S, const KParams& K, const TvBox& b, const TvStage& T, const int* hOff, const int* hBase, int nh,
+                                               int* hidN, int* hidM, int* hidCell) {
+	if (threadIdx.x == 0) *hidN = 0;
+	__syncthreads();   // the staging stores have landed, the counter is reset
+	const bool three = K.p.dim == 3;
+	for (int e = threadIdx.x; e < nh; e += blockDim.x) {
+		const int label = S.hid[1 + e];
+		if (label < 0) continue;
+		const int slot = S.slotOfHost[label], c = S.cellOf[slot];
+		if (c >= S.nC) continue;
+		int ix, iy, iz; cell_coords(K, c, ix, iy, iz);
+		const int hx = ix - b.ox + 1, hy = iy - b.oy + 1, hz = three ? iz - b.oz + 1 : 0;
+		if (hx < 0 || hx >= b.HX || hy < 0 || hy >= b.HY || hz < 0 || hz >= b.HZ) continue;
+		const int hb = (hz * b.HY + hy) * b.HX + hx, r = slot - hBase[hb];
+		if (r < 0 || r >= hOff[hb + 1] - hOff[hb]) continue;
+		const int k = atomicAdd(hidN, 1);
+		if (k < TV_HIDMAX) { hidM[k] = hOff[hb] + r; hidCell[k] = S.hid[1 + PMPS_HID_CAP + e]; T.tw[hOff[hb] + r] |= (int32_t)0x80000000; }
+		else atomicOr(&S.flags[FLAG_GUARD], 8);
+	}
+}
 // exact pair geometry of staged record m for particle s, then the bodies
 template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m) {
@@ -488,7 +537,8 @@ __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, 
 	q.rx = xj - s.pi.x; q.ry = yj - s.pi.y; q.rz = zj - s.pi.z;
 	q.d2 = sq3_exact(q.rx, q.ry, q.rz);
 	if (!(q.d2 < K.reMax2)) return;
-	const int tw = T.tw[m];
+	int tw = T.tw[m];
+	if (tw < 0) { if (!tv_hid_visible(T, m)) return; tw &= 0x7fffffff; }   // rare: a particle moved into a hole by the out-of-domain swap of this step
 	q.tj = (int)(short)(tw & 0xffff); q.ptj = tw >> 16;
 	if (POLY && s.hasMirror) { q.mx = xj - s.mix; q.my = yj - s.miy; q.mz = zj - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
 	else { q.mx = q.my = q.mz = 0.0; q.dm2 = __longlong_as_double(0x7ff0000000000000ll); }   // no mirror in reach: d2 < dm2 holds, M(re) fails (pmps_internal.h, mirrorFar2)
@@ -501,11 +551,12 @@ template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair2(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m0, int m1) {
 	Pair a, b; a.j = m0; b.j = m1;
 	const double xa = T.px[m0], ya = T.py[m0], za = T.pz[m0], xb = T.px[m1], yb = T.py[m1], zb = T.pz[m1];
-	const int wa = T.tw[m0], wb = T.tw[m1];
+	int wa = T.tw[m0], wb = T.tw[m1];
 	a.rx = xa - s.pi.x; a.ry = ya - s.pi.y; a.rz = za - s.pi.z; b.rx = xb - s.pi.x; b.ry = yb - s.pi.y; b.rz = zb - s.pi.z;
 	a.d2 = sq3_exact(a.rx, a.ry, a.rz); b.d2 = sq3_exact(b.rx, b.ry, b.rz);
-	const bool ha = a.d2 < K.reMax2, hb = b.d2 < K.reMax2;
+	bool ha = a.d2 < K.reMax2, hb = b.d2 < K.reMax2;
 	if (!(ha || hb)) return;
+	if ((wa | wb) < 0) { if (wa < 0 && !tv_hid_visible(T, m0)) ha = false; if (wb < 0 && !tv_hid_visible(T, m1)) hb = false; wa &= 0x7fffffff; wb &= 0x7fffffff; }
 	a.tj = (int)(short)(wa & 0xffff); a.ptj = wa >> 16; b.tj = (int)(short)(wb & 0xffff); b.ptj = wb >> 16;
 	if (POLY && s.hasMirror) {
 		a.mx = xa - s.mix; a.my = ya - s.miy; a.mz = za - s.miz; a.dm2 = sq3_exact(a.mx, a.my, a.mz);
@@ -538,7 +589,8 @@ template <bool POLY, unsigned FIELDS, bool WALLONLY, bool SPARSE, class F>
 __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
-	const TvStage T = tv_carve<FIELDS>(smemRaw);
+	__shared__ int sHidN, sHidM[TV_HIDMAX], sHidCell[TV_HIDMAX]; __shared__ unsigned sHidMask[TV_NG];
+	TvStage T = tv_carve<FIELDS>(smemRaw); T.hidN = &sHidN; T.hidM = sHidM; T.hidCell = sHidCell; T.hidMask = sHidMask;
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
 	unsigned char* const fx = smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS);
 	unsigned char* const rowsBuf = fx;                                       // 2 x TV_NG list rows of TV_LROW bytes
@@ -559,8 +611,8 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		if (tid == 0) nxt = atomicAdd(&S.tileCursor[cursorIdx], 1);
 		const int tt = LISTED ? visit[it] : it;
 		const int item = S.tileList[tt];
-		const TvBox b = tv_box(K, item);
 		tv_load_table(S, K, tt, sTab);
+		const TvBox b = tv_box_tab(K, item, sTab);
 		const int M = hOff[b.HV], own0 = sTab[2 * K.HVt + 1], P = sTab[2 * K.HVt + 2];
 		if (M + 1 > TV_MAXM || P > TV_MAXOWN) continue;   // reported by k_hl_build (FLAG_TILE_OVERFLOW)
 		if (SPARSE) {   // does any particle of the tile want pairs?  (begin() of these bodies is idempotent)
@@ -596,6 +648,8 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		}
 		tv_stage<true, FIELDS>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, ownMap);
 		if (tid == 0) { T.tw[M] = 0; T.px[M] = T.py[M] = T.pz[M] = 1e30; }   // the record list padding points at
+		const int nHid = S.hid[0];   // uniform; 0 unless a particle left the domain in this step
+		if (nHid > 0) tv_mark_hidden(S, K, b, T, hOff, hBase, nHid, &sHidN, sHidM, sHidCell);
 		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask shuffles) ----
 		for (int p0 = 0, rnd = 0; p0 < P; p0 += TV_NG, rnd++) {
 			asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -610,13 +664,14 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 			if (act) {
 				cntE = sCnt[p];
 				const int ms = ownMap[p];
-				const int tw = T.tw[ms];
+				const int tw = T.tw[ms] & 0x7fffffff;
 				s.type = (int)(short)(tw & 0xffff); s.ptype = tw >> 16;
 				s.pi.x = T.px[ms]; s.pi.y = T.py[ms]; s.pi.z = T.pz[ms]; s.pi.w = pk_make(s.type, s.ptype);
 				if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
 				if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
 				act = s.type != K.p.ghost;
 			}
+			if (nHid > 0) tv_hid_mask(T, K, s, sHidMask);   // (uniform)
 			typename F::Ctx ctx = {};   // idle lanes still take part in the (full-mask) reductions
 			bool pairs = false;
 			if (act) {

@@ -86,6 +86,9 @@ def load_library() -> ctypes.CDLL:
     L.pmps_get_counters.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_longlong)]
     L.pmps_register_host.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]
     L.pmps_unregister_host.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    if os.environ.get("PMPS_LIB") is None or hasattr(L, "pmps_set_stale_list_replay"):   # (an older experimental build named by PMPS_LIB may lack them)
+        L.pmps_set_stale_list_replay.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.pmps_debug_set_stale.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
     L.pmps_set_mesh.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_int,
                                 ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_double), ctypes.c_int,
                                 ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
@@ -217,7 +220,15 @@ class Engine:
     def stream(self) -> int:
         return int(self.lib.pmps_stream(self.h) or 0)
 
+    def set_stale_list_replay(self, on: bool):
+        self._chk(self.lib.pmps_set_stale_list_replay(self.h, 1 if on else 0))
+
     # ---- parity hooks
+    def set_stale(self, host_idx, bucket):
+        """Tests: array elements `host_idx` are listed in reference buckets `bucket` until the next step start (pmps_debug_set_stale)."""
+        a = np.ascontiguousarray(host_idx, dtype=np.int32); b = np.ascontiguousarray(bucket, dtype=np.int32)
+        self._chk(self.lib.pmps_debug_set_stale(self.h, len(a), _ip(a), _ip(b)))
+
     def neighbors(self, i: int, kind: int, cap: int = 1024) -> np.ndarray:
         out = np.zeros(cap, dtype=np.int32)
         n = self._chk(self.lib.pmps_debug_neighbors(self.h, int(i), int(kind), _ip(out), cap))

@@ -118,20 +118,22 @@ def test_flowing_block_1m_against_oracle(capsys):
 
 
 def test_guard_violation_is_loud():
-    """a particle that jumps farther than the search slack within one list lifetime (here: a 1.5 lo kick in one step, the
-    predictor saw a column at rest) must not pass silently — pmps_step fails with PMPS_E_STATE, the flag is sticky (a rebuild does
-    not clear it) and an upload of a state clears it."""
+    """particles that jump farther than the search slack within one list lifetime must not pass silently.  A fused step
+    re-makes its bucket order right after the prediction when the displacement reached there asks for it, so a velocity kick alone is
+    handled (no pass runs beyond the slack); what can still violate it are the moves AFTER that check.  Here one interior particle's
+    number density is doubled, the equation of state turns that into a pressure spike and the correction throws its neighbours
+    about one particle distance: pmps_step fails with PMPS_E_STATE, the flag is sticky (a rebuild does not clear it) and an upload of
+    a state clears it."""
     from polymps_b200.engine import PmpsError
     case = cases.dam3d(16, 8, 12, jitter=0.03, name="kick")
     ps, meshes, st0 = _build(case)
     eng = _engine(ps, meshes, st0.numParticlesZero); eng.upload(st0); eng.init_step0(); eng.step(3)
     st = st0.copy(); eng.download(st)
-    # a soft upload (same positions) keeps the lists; the kicked velocity moves one interior particle 1.5 lo in the next step
     i = int(np.argmin(np.abs(st.vec("pos")[:st.numParticles] - st.vec("pos")[:st.numParticles].mean(axis=0)).sum(axis=1)))
-    st.vel[3 * i + 0] = 1.5 * ps.partDist / ps.timeStep
-    eng.upload(st, ["vel"])
+    st.pndi[i] *= 2.0
+    eng.upload(st, ["pndi"])   # no positions: the lists stay
     with pytest.raises(PmpsError) as ei:
-        eng.step(1)
+        eng.step(2)
     assert "search slack" in str(ei.value)
     assert eng.counters()["guard_violated"] == 1
     with pytest.raises(PmpsError):
@@ -139,3 +141,26 @@ def test_guard_violation_is_loud():
     eng.upload(st0); eng.init_step0(); eng.step(2)   # a fresh state clears it
     assert eng.counters()["guard_violated"] == 0
     eng.close()
+
+
+def test_velocity_kick_is_absorbed_by_the_mid_step_rebuild():
+    """A particle kicked 1.5 lo in one prediction: the displacement read back right after the prediction triggers the rebuild at the
+    predicted positions, so every later pass of the step searches a complete neighbourhood — no violation, and the result equals a
+    run that re-sorts at every step start as well as in the middle (PMPS_RESORT_EVERY=1 semantics are the reference's cadence)."""
+    case = cases.dam3d(16, 8, 12, jitter=0.03, name="kick2")
+    ps, meshes, st0 = _build(case)
+    outs = []
+    for hard in (False, True):
+        eng = _engine(ps, meshes, st0.numParticlesZero); eng.upload(st0); eng.init_step0(); eng.step(3)
+        st = st0.copy(); eng.download(st)
+        i = int(np.argmin(np.abs(st.vec("pos")[:st.numParticles] - st.vec("pos")[:st.numParticles].mean(axis=0)).sum(axis=1)))
+        st.vel[3 * i + 0] = 1.5 * ps.partDist / ps.timeStep
+        if hard:
+            eng.upload(st)               # full upload: forces a re-sort at the step start
+        else:
+            eng.upload(st, ["vel"])      # the lists of the earlier steps stay
+        eng.step(1)
+        assert eng.counters()["guard_violated"] == 0
+        out = st0.copy(); eng.download(out); outs.append(out); eng.close()
+    bad = compare_states(outs[0], outs[1], rtol=1e-9, skip=NOISY, scales=natural_scales(ps))
+    assert not bad, bad
