@@ -234,7 +234,9 @@ def main_gpu_slab(args, rank, world, local):
     from polymps_b200.params import ParticleSystem
     from polymps_b200.slab import SlabEngine, choose_cuts, TABLE_FIELDS, field_width, field_dtype
 
-    kN = int(round(args.k * world ** (1.0 / 3.0)))
+    # weak scaling (default): N x the single-GPU particle count; --total-k fixes the WHOLE block instead (strong scaling: the named
+    # sizes of BASELINE.json configs[4], k = 292 -> 49.8 M, 464 -> 199.8 M particles over the N ranks)
+    kN = args.total_k if args.total_k > 0 else int(round(args.k * world ** (1.0 / 3.0)))
     case = cases.dam3d_block_options(kN, incompressible=args.scheme == "inc")
     ps = ParticleSystem.from_json(case.options).set_parameters(); ps.allocate_buckets(None)
     meshes = [PolygonMesh.from_triangles(case.tris).init_wall_tables(int(ps.dim), ps.weightType, ps.partDist, ps.reL, ps.reS)]
@@ -327,7 +329,7 @@ def main_gpu_slab(args, rank, world, local):
                                       "halo_refresh_MB_per_step": (st1["refresh_bytes"] - st0["refresh_bytes"]) / args.steps / 1e6})
     inc = args.scheme == "inc"
     line = {"metric": METRIC if not inc else "particle-steps/sec (3D INC dam break: PPE assembly + Jacobi-CG)", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if args.total_k > 0 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "synthetic 3D %s dam-break block %dx%dx%d = %d particles over %d GPUs (%.2fM per GPU), STL polygon tank (10 triangles), %s option set" % ("INC" if inc else "WC", nx, ny, nz, int(total), world, total / world / 1e6, "InputDamINC" if inc else "InputDamWC"),
                        "state": STATE_NOTE[flow], "cg_iterations_last_step": sc.solverIter if inc else None,
                        "bucket_rebuilds": c1["bucket_rebuilds"] - c0["bucket_rebuilds"], "hit_refilters": c1["hit_refilters"] - c0["hit_refilters"],
@@ -455,6 +457,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scheme", default="wc", choices=["wc", "inc"], help="wc = the BASELINE.json metric (default); inc = the incompressible configuration (#3), single GPU, reported under profiles/")
     ap.add_argument("--k", type=int, default=171, help="block edge: 2k x k x k particles per GPU (171 -> 10.0M)")
+    ap.add_argument("--total-k", type=int, default=0, help="N > 1: block edge of the WHOLE block (strong scaling at a named size: 292 -> 49.8M, 464 -> 199.8M particles); 0 = weak scaling from --k")
     ap.add_argument("--state", default="flow", choices=["flow", "rest"], help="flow (default): the moving initial state both arms start from; rest: the column at rest")
     ap.add_argument("--rest-steps", type=int, default=20, help="timed steps of the at-rest comparison run (config.at_rest_value); 0 skips it")
     ap.add_argument("--ref-k", type=int, default=80, help="block edge of the CPU sample for --impl reference (80 -> 1.02 M particles, BASELINE.md section 3)")

@@ -31,7 +31,6 @@ __global__ void __launch_bounds__(TV_T) k_debug_neighbors(const __grid_constant_
 		int hb = 0; while (hOff[hb + 1] <= m) hb++;
 		const int j = hBase[hb] + (m - hOff[hb]);
 		const double4 pj = S.pos[j];
-		{ const int hc = hid_cell_of_slot(S, j); if (hc >= 0 && !hid_visible(K, hc, pi)) continue; }   // the reference's stale bucket lists hide j from i
 		Pair q; q.j = j; q.tj = pk_type(pj); q.ptj = pk_ptype(pj);
 		q.rx = pj.x - pi.x; q.ry = pj.y - pi.y; q.rz = pj.z - pi.z; q.d2 = sq3_exact(q.rx, q.ry, q.rz);
 		q.mx = pj.x - mix; q.my = pj.y - miy; q.mz = pj.z - miz; q.dm2 = POLY ? sq3_exact(q.mx, q.my, q.mz) : 0.0;

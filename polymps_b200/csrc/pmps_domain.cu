@@ -111,5 +111,6 @@ extern "C" int pmps_debug_set_stale(pmps_t* h, int n, const int32_t* hostIdx, co
 		CUDA_TRY(h, cudaMemcpy(h->V.hid + 1, hostIdx, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice));
 		CUDA_TRY(h, cudaMemcpy(h->V.hid + 1 + PMPS_HID_CAP, bucket, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice));
 	}
+	h->hitValid = false;   // the next pass has the hit list re-made with these entries (k_hits_decide)
 	return PMPS_OK;
 }

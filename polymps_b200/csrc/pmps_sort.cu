@@ -289,7 +289,9 @@ int pmps_tv_prepare(pmps_handle* h) {
 // running maximum over all slots; hitMove[1] = the margin the list was made with).  One thread.
 __global__ void k_hits_decide(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int force) {
 	const float lim = S.hitMove[1] * 0.98f;   // float positions relative to domainMin: a few 1e-7 of the domain extent of slack
-	if (force || S.hitMove[0] > lim * lim) { S.hitFlag[0] = 1; S.hitFlag[1] += 1; S.hitMove[0] = 0.f; }
+	// (hidden entries — a particle left the domain in this step: which particle finds them depends on the bucket its CURRENT position is
+	// in, so the list is re-made at every position epoch until the step ends; pmps_device.cuh, hid_visible)
+	if (force || S.hid[0] > 0 || S.hitMove[0] > lim * lim) { S.hitFlag[0] = 1; S.hitFlag[1] += 1; S.hitMove[0] = 0.f; }
 	else S.hitFlag[0] = 0;
 }
 // hit list for the current positions (after the prediction / correction / shifting moved the particles): re-made only when

@@ -30,7 +30,8 @@
 #define TV_CHUNK 64              // list entries per chunk: walker lane g holds entries g, g+TV_G, ... of the chunk, contiguously
 #define TV_PER (TV_CHUNK / TV_G) // entries per lane and chunk
 #define TV_MAXOWN 512            // particles a work item may own (ownMap, sCnt, sHas)
-#define TV_SMEM_BUDGET (111 * 1024)   // dynamic shared memory per block: two blocks per SM
+#define TV_SMEM_BUDGET (111 * 1024)   // dynamic shared memory per block: two blocks per SM with their static part (< 2 KB) and the 1 KB the driver reserves per block
+                                      // (228 KB per SM; walk() in pmps_stages.inc checks the resident blocks of every pass against TV_BLOCKS)
 #define TV_LROW (TV_CHUNK * 2 + 16)   // bytes per prefetched list row in shared memory: 16 bytes of padding stagger the lane groups over the banks
 // fixed dynamic shared memory of the walker besides the staged records: two rounds of list rows, ownMap, sCnt, sHas
 #define TV_FIXED_BYTES (2 * TV_NG * TV_LROW + TV_MAXOWN * 2 + TV_MAXOWN * 2 + TV_MAXOWN)
@@ -232,11 +233,15 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 
 
 // ---- shared-memory image of the halo ------------------------------------------------------------------------------
-#define TV_HIDMAX 32   // staged records of one work item the reference's stale bucket lists may hide (pmps_device.cuh, hid_visible)
+#define TV_HIDMAX 16   // staged records of one work item the reference's stale bucket lists may hide (pmps_device.cuh, hid_visible)
 struct TvStage {   // shared-memory planes of the staged halo: the walker stages FP64 positions + the type word, the list build float positions
 	float4* fpos; int32_t* tw; double *px, *py, *pz; Nb nb;
-	const int* hidN; const int* hidM; const int* hidCell; const unsigned* hidMask;   // hidden records of the item: staged index, bucket their array element is listed in (bit 31 of tw marks them); per lane group: which of them its particle cannot see
 };
+// Hidden records of a work item (rare: only in a step in which a particle left the domain; pmps_device.cuh, hid_visible): staged
+// index and the bucket the record's array element is listed in.  Only the hit-list build looks at them (k_hl_build): a particle whose
+// search does not reach that bucket does not get the record into its list, and the list is re-made at every position epoch while
+// hidden entries exist (k_hits_decide) — the walkers carry no test.
+struct TvHid { int n; int m[TV_HIDMAX]; int cell[TV_HIDMAX]; };
 template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp) {
 	TvStage t; constexpr size_t m = TV_MAXM;
 	t.fpos = nullptr;
@@ -341,6 +346,8 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
 	__shared__ unsigned sMinBits;   // smallest squared pair distance of the item (bits of a positive float)
+	__shared__ TvHid sHid;          // hidden records of the item (only in a step in which a particle left the domain)
+	const int nHidAll = S.hid[0];   // uniform over the grid
 	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
 	float4* const fpos = T.fpos;
 	const int cap = S.tlCap;
@@ -368,7 +375,26 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
 		tv_stage<false, 0, HL_T>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, nullptr);
 		if (tid == 0) fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the far-away dummy record: what a lane reads beyond the end of its stretch
+		if (nHidAll > 0) {   // which staged records of this item are hidden entries (S.hid)?  One thread per entry.
+			if (tid == 0) sHid.n = 0;
+			__syncthreads();
+			for (int e = tid; e < nHidAll; e += HL_T) {
+				const int label = S.hid[1 + e];
+				if (label < 0) continue;
+				const int slot = S.slotOfHost[label], c = S.cellOf[slot];
+				if (c >= S.nC) continue;
+				int ix, iy, iz; cell_coords(K, c, ix, iy, iz);
+				const int gx = ix - b.ox + 1, gy = iy - b.oy + 1, gz = three ? iz - b.oz + 1 : 0;
+				if (gx < 0 || gx >= b.HX || gy < 0 || gy >= b.HY || gz < 0 || gz >= b.HZ) continue;
+				const int hb = (gz * b.HY + gy) * b.HX + gx, r = slot - hBase[hb];
+				if (r < 0 || r >= hOff[hb + 1] - hOff[hb]) continue;
+				const int k = atomicAdd(&sHid.n, 1);
+				if (k < TV_HIDMAX) { sHid.m[k] = hOff[hb] + r; sHid.cell[k] = S.hid[1 + PMPS_HID_CAP + e]; }
+				else atomicOr(&S.flags[FLAG_GUARD], 8);
+			}
+		}
 		__syncthreads();
+		const int nHid = nHidAll > 0 ? min(sHid.n, TV_HIDMAX) : 0;   // uniform over the block
 		for (int p0 = 0; p0 < P; p0 += HL_T) {   // uniform over the block
 			const int p = p0 + tid;
 			const bool act = p < P;
@@ -404,6 +430,12 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 					#pragma unroll
 					for (int u = 0; u < 4; u++) { const float dx = f[u].x - fi.x, dy2 = f[u].y - fi.y, dz2 = f[u].z - fi.z; d2[u] = dx * dx + dy2 * dy2 + dz2 * dz2; }
 					dmin = fminf(fminf(dmin, fminf(d2[0], d2[1])), fminf(d2[2], d2[3]));
+					if (nHid > 0) {   // (uniform, rare) a hidden record is a hit only for a particle whose search reaches the bucket it is listed in
+						#pragma unroll
+						for (int u = 0; u < 4; u++) if (d2[u] < R2) {
+							for (int q = 0; q < nHid; q++) if (sHid.m[q] == m[u] && !hid_visible(K, sHid.cell[q], S.pos[i])) d2[u] = 3e38f;
+						}
+					}
 					#pragma unroll
 					for (int u = 0; u < 4; u++) {   // (the row address is kept in a register by hand: under the 80-register cap ptxas re-derives it from %tid for every store)
 						const bool hit = d2[u] < R2;
@@ -420,7 +452,9 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 					for (int mm = hOff[hb0]; mm < hOff[hb0 + 3]; mm++) {
 						if (mm == self) continue;
 						const float4 f = fpos[mm]; const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
-						if (dx * dx + dy2 * dy2 + dz2 * dz2 < R2) { if (c2 >= TV_CHUNK && c2 < cap) grow[tv_list_pos(c2)] = (uint16_t)mm; c2++; }
+						bool hit = dx * dx + dy2 * dy2 + dz2 * dz2 < R2;
+						if (hit && nHid > 0) for (int q = 0; q < nHid; q++) if (sHid.m[q] == mm && !hid_visible(K, sHid.cell[q], S.pos[i])) hit = false;
+						if (hit) { if (c2 >= TV_CHUNK && c2 < cap) grow[tv_list_pos(c2)] = (uint16_t)mm; c2++; }
 					}
 				}
 				for (int e = min(cnt, cap); (e & (TV_CHUNK - 1)) != 0; e++) grow[tv_list_pos(e)] = (uint16_t)M;
@@ -493,42 +527,6 @@ static __global__ void __launch_bounds__(256) k_tails(const __grid_constant__ De
 }
 
 // ---- the walker ---------------------------------------------------------------------------------------------------
-// a staged record marked hidden (bit 31 of its type word): may particle s see it?  hidMask (per lane group, made at the start of the
-// round by tv_hid_mask) has bit k set when the reference's search of s does NOT reach the bucket entry k of the item's table is listed in
-__device__ __forceinline__ bool tv_hid_visible(const TvStage& T, int m) {
-	const unsigned mk = T.hidMask[threadIdx.x / TV_G];
-	const int n = min(*T.hidN, TV_HIDMAX);
-	for (int k = 0; k < n; k++) if (T.hidM[k] == m) return ((mk >> k) & 1u) == 0u;
-	return true;
-}
-__device__ __forceinline__ void tv_hid_mask(const TvStage& T, const KParams& K, const Self& s, unsigned* hidMask) {
-	const int n = min(*T.hidN, TV_HIDMAX);
-	unsigned mk = 0u;
-	for (int k = 0; k < n; k++) if (!hid_visible(K, T.hidCell[k], s.pi)) mk |= 1u << k;
-	if (s.lead) hidMask[threadIdx.x / TV_G] = mk;
-	__syncwarp();
-}
-// marks the staged records of the item that are hidden entries (S.hid): one thread per entry; the caller's next barrier publishes the marks
-__device__ __forceinline__ void tv_mark_hidden(const DevView& S, const KParams& K, const TvBox& b, const TvStage& T, const int* hOff, const int* hBase, int nh,
-                                               int* hidN, int* hidM, int* hidCell) {
-	if (threadIdx.x == 0) *hidN = 0;
-	__syncthreads();   // the staging stores have landed, the counter is reset
-	const bool three = K.p.dim == 3;
-	for (int e = threadIdx.x; e < nh; e += blockDim.x) {
-		const int label = S.hid[1 + e];
-		if (label < 0) continue;
-		const int slot = S.slotOfHost[label], c = S.cellOf[slot];
-		if (c >= S.nC) continue;
-		int ix, iy, iz; cell_coords(K, c, ix, iy, iz);
-		const int hx = ix - b.ox + 1, hy = iy - b.oy + 1, hz = three ? iz - b.oz + 1 : 0;
-		if (hx < 0 || hx >= b.HX || hy < 0 || hy >= b.HY || hz < 0 || hz >= b.HZ) continue;
-		const int hb = (hz * b.HY + hy) * b.HX + hx, r = slot - hBase[hb];
-		if (r < 0 || r >= hOff[hb + 1] - hOff[hb]) continue;
-		const int k = atomicAdd(hidN, 1);
-		if (k < TV_HIDMAX) { hidM[k] = hOff[hb] + r; hidCell[k] = S.hid[1 + PMPS_HID_CAP + e]; T.tw[hOff[hb] + r] |= (int32_t)0x80000000; }
-		else atomicOr(&S.flags[FLAG_GUARD], 8);
-	}
-}
 // exact pair geometry of staged record m for particle s, then the bodies
 template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m) {
@@ -537,8 +535,7 @@ __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, 
 	q.rx = xj - s.pi.x; q.ry = yj - s.pi.y; q.rz = zj - s.pi.z;
 	q.d2 = sq3_exact(q.rx, q.ry, q.rz);
 	if (!(q.d2 < K.reMax2)) return;
-	int tw = T.tw[m];
-	if (tw < 0) { if (!tv_hid_visible(T, m)) return; tw &= 0x7fffffff; }   // rare: a particle moved into a hole by the out-of-domain swap of this step
+	const int tw = T.tw[m];
 	q.tj = (int)(short)(tw & 0xffff); q.ptj = tw >> 16;
 	if (POLY && s.hasMirror) { q.mx = xj - s.mix; q.my = yj - s.miy; q.mz = zj - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
 	else { q.mx = q.my = q.mz = 0.0; q.dm2 = __longlong_as_double(0x7ff0000000000000ll); }   // no mirror in reach: d2 < dm2 holds, M(re) fails (pmps_internal.h, mirrorFar2)
@@ -551,12 +548,11 @@ template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair2(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m0, int m1) {
 	Pair a, b; a.j = m0; b.j = m1;
 	const double xa = T.px[m0], ya = T.py[m0], za = T.pz[m0], xb = T.px[m1], yb = T.py[m1], zb = T.pz[m1];
-	int wa = T.tw[m0], wb = T.tw[m1];
+	const int wa = T.tw[m0], wb = T.tw[m1];
 	a.rx = xa - s.pi.x; a.ry = ya - s.pi.y; a.rz = za - s.pi.z; b.rx = xb - s.pi.x; b.ry = yb - s.pi.y; b.rz = zb - s.pi.z;
 	a.d2 = sq3_exact(a.rx, a.ry, a.rz); b.d2 = sq3_exact(b.rx, b.ry, b.rz);
-	bool ha = a.d2 < K.reMax2, hb = b.d2 < K.reMax2;
+	const bool ha = a.d2 < K.reMax2, hb = b.d2 < K.reMax2;
 	if (!(ha || hb)) return;
-	if ((wa | wb) < 0) { if (wa < 0 && !tv_hid_visible(T, m0)) ha = false; if (wb < 0 && !tv_hid_visible(T, m1)) hb = false; wa &= 0x7fffffff; wb &= 0x7fffffff; }
 	a.tj = (int)(short)(wa & 0xffff); a.ptj = wa >> 16; b.tj = (int)(short)(wb & 0xffff); b.ptj = wb >> 16;
 	if (POLY && s.hasMirror) {
 		a.mx = xa - s.mix; a.my = ya - s.miy; a.mz = za - s.miz; a.dm2 = sq3_exact(a.mx, a.my, a.mz);
@@ -589,8 +585,7 @@ template <bool POLY, unsigned FIELDS, bool WALLONLY, bool SPARSE, class F>
 __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
-	__shared__ int sHidN, sHidM[TV_HIDMAX], sHidCell[TV_HIDMAX]; __shared__ unsigned sHidMask[TV_NG];
-	TvStage T = tv_carve<FIELDS>(smemRaw); T.hidN = &sHidN; T.hidM = sHidM; T.hidCell = sHidCell; T.hidMask = sHidMask;
+	const TvStage T = tv_carve<FIELDS>(smemRaw);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
 	unsigned char* const fx = smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS);
 	unsigned char* const rowsBuf = fx;                                       // 2 x TV_NG list rows of TV_LROW bytes
@@ -648,8 +643,6 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		}
 		tv_stage<true, FIELDS>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, ownMap);
 		if (tid == 0) { T.tw[M] = 0; T.px[M] = T.py[M] = T.pz[M] = 1e30; }   // the record list padding points at
-		const int nHid = S.hid[0];   // uniform; 0 unless a particle left the domain in this step
-		if (nHid > 0) tv_mark_hidden(S, K, b, T, hOff, hBase, nHid, &sHidN, sHidM, sHidCell);
 		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask shuffles) ----
 		for (int p0 = 0, rnd = 0; p0 < P; p0 += TV_NG, rnd++) {
 			asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -664,14 +657,13 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 			if (act) {
 				cntE = sCnt[p];
 				const int ms = ownMap[p];
-				const int tw = T.tw[ms] & 0x7fffffff;
+				const int tw = T.tw[ms];
 				s.type = (int)(short)(tw & 0xffff); s.ptype = tw >> 16;
 				s.pi.x = T.px[ms]; s.pi.y = T.py[ms]; s.pi.z = T.pz[ms]; s.pi.w = pk_make(s.type, s.ptype);
 				if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
 				if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
 				act = s.type != K.p.ghost;
 			}
-			if (nHid > 0) tv_hid_mask(T, K, s, sHidMask);   // (uniform)
 			typename F::Ctx ctx = {};   // idle lanes still take part in the (full-mask) reductions
 			bool pairs = false;
 			if (act) {

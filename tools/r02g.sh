@@ -1,4 +1,3 @@
-python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "o3 or chained" > gpurun_out/r02g_fix.log 2>&1; echo "fix rc=$?"; tail -5 gpurun_out/r02g_fix.log
 for v in base cur; do
   L=$PWD/polymps_b200/libpmps.so; [ $v = base ] && L=$PWD/polymps_b200/libpmps_base.so
   PMPS_LIB=$L python bench.py --steps 20 --warmup 5 --no-cpu --rest-steps 10 --e2e-steps 2 > gpurun_out/r02g_bench_$v.json 2> gpurun_out/r02g_bench_$v.err; echo "bench $v rc=$?"
