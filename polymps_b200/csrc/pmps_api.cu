@@ -3,6 +3,8 @@
 // bodies (pmps_bodies.cuh).  There is no CPU fallback anywhere: without a CUDA device pmps_create fails.
 #include "pmps_bodies.cuh"
 #include "pmps_tv.cuh"
+#include "pmps_optset.h"
+#include "pmps_walk_packs.h"
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -236,6 +238,7 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	K.velMax = params->velMax;
 	K.poly = params->wallType == 1;
 	K.reMax2 = fmax(params->reS2, params->reL2); K.invReS = 1.0 / params->reS; K.invReL = 1.0 / params->reL;
+	h->optset = getenv("PMPS_GENERIC_KERNELS") ? PMPS_OPT_GENERIC : pmps_optset_of(*params);   // walker kernels with this option set's enums as constants (pmps_optset.h)
 	memset(&h->V, 0, sizeof(DevView)); memset(&h->A, 0, sizeof(DevView));
 	h->V.nB = (int)nB;
 	// tiles of the tile-Verlet walker (pmps_tv.cuh): 2x2x2 buckets in 3D (halo 4x4x4), 4x4 in 2D (halo 6x6)
@@ -356,6 +359,20 @@ extern "C" int pmps_set_mesh(pmps_t* h, int mesh_id, int nV, const double* V, in
 	cudaSetDevice(h->device);
 	cudaStreamSynchronize(h->stream);
 	return pmps_mesh_upload(h, mesh_id, nV, V, nF, F, faceNormals, nTable, xDataPND, xDataNeigh, Zij, nNeighWall);
+}
+
+// ---- walker dispatch: option set x pack group -> the translation unit that holds the kernels (pmps_walk_inst.inc) ---------------
+#define PMPS_WALK_DECL(set) int pmps_walk_##set##_g0(int, pmps_handle*, const char*, int); int pmps_walk_##set##_g1(int, pmps_handle*, const char*, int); \
+	int pmps_walk_##set##_g2(int, pmps_handle*, const char*, int); int pmps_walk_##set##_g3(int, pmps_handle*, const char*, int);
+PMPS_WALK_DECL(generic) PMPS_WALK_DECL(wc3d) PMPS_WALK_DECL(inc3d)
+int pmps_walk_dispatch(int optset, int packId, int group, pmps_handle* h, const char* name, int polyOverride) {
+	typedef int (*fn)(int, pmps_handle*, const char*, int);
+	static const fn table[PMPS_OPT_SETS][PMPS_WALK_GROUPS] = {
+		{ pmps_walk_generic_g0, pmps_walk_generic_g1, pmps_walk_generic_g2, pmps_walk_generic_g3 },
+		{ pmps_walk_wc3d_g0, pmps_walk_wc3d_g1, pmps_walk_wc3d_g2, pmps_walk_wc3d_g3 },
+		{ pmps_walk_inc3d_g0, pmps_walk_inc3d_g1, pmps_walk_inc3d_g2, pmps_walk_inc3d_g3 } };
+	if (optset < 0 || optset >= PMPS_OPT_SETS || group < 0 || group >= PMPS_WALK_GROUPS) return pmps_fail(h, PMPS_E_ARG, "%s: option set %d / group %d", name, optset, group);
+	return table[optset][group](packId, h, name, polyOverride);
 }
 
 #include "pmps_stages.inc"

@@ -99,8 +99,10 @@ enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLA
 #define PMPS_CURSORS 64   // work-stealing cursors per step (one per tile-walker launch)
 
 // Kernel-side parameters: the ABI params plus derived constants
-struct KParams {
-	PmpsParams p;
+// (a template on the type of `p`: the walker kernels are also compiled with option sets whose enums are compile-time constants,
+// pmps_optset.h — same layout, the constants hide the run-time members)
+template <class PT> struct KParamsT {
+	PT p;
 	double big;          // 10e8*partDist, the reference's "infinity" (src/MpsParticleVelPos.cpp:37)
 	double vol;          // partDist^dim
 	double velMax;       // velMax of the previous correction (src/MpsPressure.cpp:1585)
@@ -119,6 +121,7 @@ struct KParams {
 	double mirrorFar2;   // a particle farther than this from every wall (distParticleWall2) cannot fail d2 < dm2 nor pass M(re): its mirror is skipped
 	double invReS, invReL;
 };
+typedef KParamsT<PmpsParams> KParams;
 
 #define MAX_TRI_CONST 64
 struct DevMesh {       // one polygon mesh on the device + libigl-order AABB hierarchy in heap order
@@ -156,6 +159,7 @@ struct pmps_handle {
 	bool slab = false;                   // slab mode: rebuilds and the step-end scalars are decided by the caller from GLOBAL maxima (pmps_slab.cu)
 	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
 	bool hitForce = false;               // positions were replaced from outside (upload): the next check rebuilds the hit list
+	int optset = 0;                      // option set of the walker kernels this handle runs (pmps_optset.h), chosen by pmps_create
 	bool staleReplay = true;             // replay the reference's stale bucket lists after an out-of-domain swap (pmps_set_stale_list_replay)
 	bool hitValid = false;               // hlist matches the current positions (set by the list build / k_tv_hits, cleared when positions change)
 	size_t listAllocated = 0;

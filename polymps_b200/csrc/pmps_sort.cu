@@ -8,6 +8,7 @@
 // order so every later kernel reads its neighbours from nearby addresses.  Finally ONE pass over the 27 (9 in 2D)
 // surrounding buckets builds a candidate list with radius bucketSide = reL(1+CFL) in float; the ~10 neighbour passes
 // of the step walk that list (≈67 candidates) instead of re-walking 27 buckets (≈430 candidates) each.
+#define PMPS_TV_LISTBUILD   // this translation unit launches k_tv_items / k_hl_build
 #include "pmps_tv.cuh"
 #include <cstdio>
 

@@ -186,6 +186,7 @@ __device__ __forceinline__ TvBox tv_box_tab(const KParams& K, int item, const in
 // left), so the work items come out in roughly that order: the blocks working at any one time — they take items from a cursor —
 // then sit in a compact 3-D neighbourhood and find each other's halo records in L2 (a raster order re-reads every record from
 // DRAM for the tiles of the next z-layer: ncu, 2.1 - 4.1 x the algorithmic bytes in round 1).
+#ifdef PMPS_TV_LISTBUILD
 static __global__ void k_tv_items(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int nCodes, int bx, int by, int bz) {
 	const int code = blockIdx.x * blockDim.x + threadIdx.x;
 	if (code >= nCodes) return;
@@ -207,6 +208,7 @@ static __global__ void k_tv_items(const __grid_constant__ DevView S, const __gri
 		const int slot = atomicAdd(S.nTiles, 1); S.tileList[slot] = ~c; tv_write_table(S, K, tv_box(K, ~c), slot);
 	}
 }
+#endif
 // item scheduling shared by the tile kernels: a work-stealing cursor whose NEXT value is requested at the start of an
 // item, so the atomic's latency is hidden behind the item's work
 __device__ __forceinline__ int tv_first_item(const DevView& S, int cursorIdx, int* sItem) {
@@ -242,6 +244,7 @@ struct TvStage {   // shared-memory planes of the staged halo: the walker stages
 // search does not reach that bucket does not get the record into its list, and the list is re-made at every position epoch while
 // hidden entries exist (k_hits_decide) — the walkers carry no test.
 struct TvHid { int n; int m[TV_HIDMAX]; int cell[TV_HIDMAX]; };
+template <bool B> struct TvBool { static constexpr bool value = B; };
 template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp) {
 	TvStage t; constexpr size_t m = TV_MAXM;
 	t.fpos = nullptr;
@@ -341,6 +344,7 @@ __device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, con
 // round-1 kernels (ncu, profiles/r02_ncu_*): the Verlet list of radius bucketSide is gone.
 #define HL_T 128
 #define HL_ROW (TV_CHUNK + 2)   // 16-bit entries per shared-memory row: the first chunk of a list ((HL_ROW / 2) is odd: lanes fall into different banks)
+#ifdef PMPS_TV_LISTBUILD   // (compiled only where it is launched: pmps_sort.cu)
 static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx, int force) {
 	if (!force && !S.hitFlag[0]) return;   // k_hits_decide: the hit list still covers the current positions
 	extern __shared__ __align__(16) unsigned char smemRaw[];
@@ -395,6 +399,9 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 		}
 		__syncthreads();
 		const int nHid = nHidAll > 0 ? min(sHid.n, TV_HIDMAX) : 0;   // uniform over the block
+		// (the particle loop exists twice: with the hidden-record test — only in a step in which a particle left the domain — and without)
+		auto sweep = [&](auto hidTag) {
+		constexpr bool HID = decltype(hidTag)::value;
 		for (int p0 = 0; p0 < P; p0 += HL_T) {   // uniform over the block
 			const int p = p0 + tid;
 			const bool act = p < P;
@@ -430,7 +437,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 					#pragma unroll
 					for (int u = 0; u < 4; u++) { const float dx = f[u].x - fi.x, dy2 = f[u].y - fi.y, dz2 = f[u].z - fi.z; d2[u] = dx * dx + dy2 * dy2 + dz2 * dz2; }
 					dmin = fminf(fminf(dmin, fminf(d2[0], d2[1])), fminf(d2[2], d2[3]));
-					if (nHid > 0) {   // (uniform, rare) a hidden record is a hit only for a particle whose search reaches the bucket it is listed in
+					if (HID) {   // (rare) a hidden record is a hit only for a particle whose search reaches the bucket it is listed in
 						#pragma unroll
 						for (int u = 0; u < 4; u++) if (d2[u] < R2) {
 							for (int q = 0; q < nHid; q++) if (sHid.m[q] == m[u] && !hid_visible(K, sHid.cell[q], S.pos[i])) d2[u] = 3e38f;
@@ -453,7 +460,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 						if (mm == self) continue;
 						const float4 f = fpos[mm]; const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
 						bool hit = dx * dx + dy2 * dy2 + dz2 * dz2 < R2;
-						if (hit && nHid > 0) for (int q = 0; q < nHid; q++) if (sHid.m[q] == mm && !hid_visible(K, sHid.cell[q], S.pos[i])) hit = false;
+						if (HID && hit) for (int q = 0; q < nHid; q++) if (sHid.m[q] == mm && !hid_visible(K, sHid.cell[q], S.pos[i])) hit = false;
 						if (hit) { if (c2 >= TV_CHUNK && c2 < cap) grow[tv_list_pos(c2)] = (uint16_t)mm; c2++; }
 					}
 				}
@@ -479,10 +486,13 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 			{ const unsigned mb = __reduce_min_sync(0xffffffffu, __float_as_uint(dmin)); if (lane == 0) atomicMin(&sMinBits, mb); }
 			__syncwarp();
 		}
+		};
+		if (nHid > 0) sweep(TvBool<true>()); else sweep(TvBool<false>());
 		__syncthreads();
 		if (tid == 0) { const float md = __uint_as_float(sMinBits); S.itemMinD2[tt] = md; if (item >= 0) S.tileClose[item] = md < K.closeR2 ? 1 : 0; }
 	}
 }
+#endif   // PMPS_TV_LISTBUILD
 
 // ---- passes that act on few tiles ----------------------------------------------------------------------------------
 // Wall-only packs touch the tiles with a particle near a polygon wall, close-pair packs (collisions) the tiles that held a

@@ -1,11 +1,10 @@
-python -m pytest tests/test_gpu_parity.py tests/test_slab_gpu.py tests/test_flow_gpu.py -m gpu -q -x -k "o3 or chained or ood or splash or guard or kick" > gpurun_out/r02j_fix.log 2>&1; echo "fix rc=$?"; tail -3 gpurun_out/r02j_fix.log
-for v in base cur; do
+for v in base cur fix; do
   L=$PWD/polymps_b200/libpmps_$v.so; [ $v = cur ] && L=$PWD/polymps_b200/libpmps.so
   PMPS_LIB=$L python bench.py --state rest --steps 10 --warmup 5 --no-cpu --rest-steps 0 --e2e-steps 1 --profile-steps 2 > gpurun_out/r02j_$v.json 2> gpurun_out/r02j_$v.err; echo "bench $v rc=$?"
 done
 python - <<'PY'
 import json
-for v in ["base","cur"]:
+for v in ["base","cur","fix"]:
     try:
         d=json.load(open("gpurun_out/r02j_%s.json"%v))
         k=d["roofline"]["kernels_ms_per_step"]
