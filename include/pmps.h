@@ -200,8 +200,14 @@ int pmps_halo_pack(pmps_t* h, unsigned fields, const int32_t* d_hostIndex, int n
 int pmps_halo_unpack(pmps_t* h, unsigned fields, int firstHostIndex, int n, const double* d_in);    /* onto host indices [first, first+n) */
 int pmps_step_phases(void);                      /* number of phases of the fused step */
 int pmps_step_phase(pmps_t* h, int phase, unsigned* haloFieldsAfter);   /* one phase of the loop body of src/main.cpp:256-460 */
-int pmps_slab_collect(pmps_t* h, double* d_out3);        /* device: {max displacement^2 since rebuild, max shift^2, velMax^2} of this rank */
-int pmps_slab_apply(pmps_t* h, const double* d_in3);     /* the same three after the MAX all-reduce: ends the step */
+int pmps_slab_collect(pmps_t* h, double* d_out4);        /* device, FOUR doubles: {max displacement^2 since rebuild, max shift^2, velMax^2, displacement^2 the step before ended with} of this rank */
+int pmps_slab_apply(pmps_t* h, const double* d_in3);     /* the first three after the MAX all-reduce: ends the step */
+/* Rebuild decision of a slab step, taken where a single GPU takes it: right after the prediction (phase 0 and its halo refresh), from
+ * the four scalars of pmps_slab_collect MAX-all-reduced over the ranks — so every rank answers alike.  1: re-partition now (migrants,
+ * new halo copies, pmps_upload_device of the new table), then pmps_slab_mid_rebuild (bucket order + hit lists at the predicted
+ * positions), then go on with phase 1.  A driver that never calls it gets the step-start predictor of pmps_slab_wants_rebuild. */
+int pmps_slab_mid_check(pmps_t* h, const double* d_in4);
+int pmps_slab_mid_rebuild(pmps_t* h);
 int pmps_slab_wants_rebuild(pmps_t* h);
 /* Incompressible scheme on slabs: the conjugate-gradient solve (src/MpsPressure.cpp:424-445; Eigen ConjugateGradient.h:27-91) sums
  * its dot products over OWNED rows and calls back into the host at the two points where ranks must talk: `sum(user, n)` must

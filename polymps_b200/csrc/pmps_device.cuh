@@ -92,16 +92,18 @@ __device__ __forceinline__ void atomic_max_f(float* addr, float v) {   // v >= 0
 }
 // slab decomposition: is slot i a particle this rank owns (not a halo copy)?  Always true on a single GPU.
 __device__ __forceinline__ bool owned_slot(const DevView& S, int i) { return S.nOwn == 0x7fffffff || S.hostIdx[i] < S.nOwn; }
-// displacement of slot i at its new position p: from the hit-list positions (every slot: a halo copy's garbage move counts until the
-// refresh replaces it, pmps_slab.cu) and from the bucket-build positions (owned particles; their owner decides about rebuilds)
+// displacement of slot i at its new position p: from the hit-list positions (owned slots when they move; halo copies when the owner's
+// position arrives, pmps_slab.cu) and from the bucket-build positions (owned particles; their owner decides about rebuilds)
 __device__ __forceinline__ void track_hit_disp(const DevView& S, const KParams& K, int i, const double4& p) {
 	const float4 b = S.hpos[i];
 	const float dx = (float)(p.x - K.p.domainMinX) - b.x, dy = (float)(p.y - K.p.domainMinY) - b.y, dz = (float)(p.z - K.p.domainMinZ) - b.z;
 	atomic_max_f(S.hitMove, dx * dx + dy * dy + dz * dz);
 }
 __device__ __forceinline__ void track_disp(const DevView& S, const KParams& K, int i, const double4& p) {
-	track_hit_disp(S, K, i, p);
+	// a halo copy's own integration is garbage (it lacks half its neighbours) and is replaced by the owner's position before any pass
+	// reads it (every phase that moves particles ends with a position refresh): only the TRUE position counts, at the unpack
 	if (!owned_slot(S, i)) return;
+	track_hit_disp(S, K, i, p);
 	const float4 b = S.bpos[i];
 	const float dx = (float)(p.x - K.p.domainMinX) - b.x, dy = (float)(p.y - K.p.domainMinY) - b.y, dz = (float)(p.z - K.p.domainMinZ) - b.z;
 	atomic_max_f(S.maxDisp2, dx * dx + dy * dy + dz * dz);

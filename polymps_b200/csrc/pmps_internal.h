@@ -156,6 +156,7 @@ struct pmps_handle {
 	double meuMax = 0.0;                 // max MEU of the last rheology pass (CFLvisc)
 	cudaStream_t ioStream = nullptr; cudaEvent_t evIoUp = nullptr, evIoMid = nullptr; void* stage2 = nullptr;   // pmps_step_host: copies overlapped with the step
 	bool deferSync = false;              // download_impl: leave the stream running (the caller synchronises later)
+	bool slabMidChecks = false;          // slab mode: the driver takes the rebuild decision after the prediction (pmps_slab_mid_check)
 	bool slab = false;                   // slab mode: rebuilds and the step-end scalars are decided by the caller from GLOBAL maxima (pmps_slab.cu)
 	bool shiftListOk = false;            // the shifting passes of this step followed a complete hit list
 	bool hitForce = false;               // positions were replaced from outside (upload): the next check rebuilds the hit list

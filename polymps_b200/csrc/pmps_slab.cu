@@ -91,15 +91,18 @@ extern "C" int pmps_halo_unpack(pmps_t* h, unsigned fields, int firstHostIndex, 
 	return PMPS_OK;
 }
 
-// step-end scalars: {max squared displacement since the list build, max squared shift of this step, velMax^2}, as doubles in
+// step scalars: {max squared displacement since the list build, max squared shift of this step, velMax^2, the displacement the step
+// before ended with}, FOUR doubles in
 // DEVICE memory so that the caller can all-reduce (MAX) them in place over the ranks before pmps_slab_apply reads them
 __global__ void k_slab_collect(const __grid_constant__ DevView S, double* out) {
 	out[0] = (double)S.maxDisp2[0]; out[1] = (double)S.maxDisp2[1]; out[2] = __longlong_as_double((long long)S.velMax2Bits[1]);
+	out[3] = (double)S.maxDisp2[2];   // the displacement the step before ended with (pmps_slab_mid_check)
 }
 __global__ void k_slab_set_velmax(const __grid_constant__ DevView S, const double* in) {
 	const unsigned long long b = (unsigned long long)__double_as_longlong(in[2]); S.velMax2Bits[0] = b; S.velMax2Bits[1] = b;
 }
-extern "C" int pmps_slab_collect(pmps_t* h, double* d_out3) {
+extern "C" int pmps_slab_collect(pmps_t* h, double* d_out4) {
+	double* const d_out3 = d_out4;
 	if (!h || !d_out3) return PMPS_E_ARG;
 	cudaSetDevice(h->device);
 	LAUNCH(h, "slab.collect", k_slab_collect, 1, 1, h->V, d_out3);

@@ -31,10 +31,11 @@
 #define TV_PER (TV_CHUNK / TV_G) // entries per lane and chunk
 #define TV_MAXOWN 512            // particles a work item may own (ownMap, sCnt, sHas)
 #define TV_SMEM_BUDGET (111 * 1024)   // dynamic shared memory per block: two blocks per SM with their static part (< 2 KB) and the 1 KB the driver reserves per block
-                                      // (228 KB per SM; walk() in pmps_stages.inc checks the resident blocks of every pass against TV_BLOCKS)
+                                      // (228 KB per SM; walk() in pmps_walk.cuh checks the resident blocks of every pass against TV_BLOCKS)
 #define TV_LROW (TV_CHUNK * 2 + 16)   // bytes per prefetched list row in shared memory: 16 bytes of padding stagger the lane groups over the banks
-// fixed dynamic shared memory of the walker besides the staged records: two rounds of list rows, ownMap, sCnt, sHas
-#define TV_FIXED_BYTES (2 * TV_NG * TV_LROW + TV_MAXOWN * 2 + TV_MAXOWN * 2 + TV_MAXOWN)
+// fixed dynamic shared memory of the walker besides the staged records: one round of list rows (each warp fetches the rows of its
+// own lane groups, so a round needs no block barrier and one buffer is enough), ownMap, sCnt, sHas
+#define TV_FIXED_BYTES (TV_NG * TV_LROW + TV_MAXOWN * 2 + TV_MAXOWN * 2 + TV_MAXOWN)
 // position of list entry e inside the particle's list: chunk-major, then lane-major
 __host__ __device__ __forceinline__ int tv_list_pos(int e) { const int w = e & (TV_CHUNK - 1); return (e & ~(TV_CHUNK - 1)) + (w % TV_G) * TV_PER + w / TV_G; }
 
@@ -80,19 +81,19 @@ template <class... B> struct PackSparse { static constexpr bool value = true; };
 template <class B, class... R> struct PackSparse<B, R...> { static constexpr bool value = (Sparse<B>::value || NoPairs<B>::value) && PackSparse<R...>::value; };
 
 __host__ __device__ constexpr int popc8(unsigned f) { int n = 0; for (int k = 0; k < 8; k++) n += (f >> k) & 1; return n; }
-__host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes per halo record
-	return 4 + 24 + ((f & NF_VEL) ? 24 : 0) + 8 * popc8(f & ~(unsigned)NF_VEL);
+__host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes per halo record: {x, y} and {z, type word} as two 16-byte planes, then the fields
+	return 32 + ((f & NF_VEL) ? 24 : 0) + 8 * popc8(f & ~(unsigned)NF_VEL);
 }
-#define TV_REC_MAX (4 + 24 + 24 + 8 * 3)   // the fattest pack of the step paths: F3 (vel, press, pndi, RHO)
-// blocks per SM by the bytes a pack stages per record (shared memory decides: TV_MAXM * rec + TV_FIXED_BYTES per block, 227 KB per SM):
+#define TV_REC_MAX (32 + 24 + 8 * 3)   // the fattest pack of the step paths: F3 (vel, press, pndi, RHO)
+// blocks per SM by the bytes a pack stages per record (shared memory decides: TV_MAXM * rec + TV_FIXED_BYTES per block, 228 KB per SM):
 // up to TV_OCC4_REC four blocks (64 registers per thread), up to TV_OCC3_REC three (80 registers), two otherwise (128 registers)
 // (measured on the B200, 10 M particles: four / three blocks against two everywhere -28 % on the concentration pass, -14 % on the
-// concentration gradient, -12 % on the pressure gradient, profiles/r02_variants.txt)
+// concentration gradient, -12 % on the pressure gradient)
 #ifndef TV_OCC4_REC
-#define TV_OCC4_REC 28
+#define TV_OCC4_REC 32
 #endif
 #ifndef TV_OCC3_REC
-#define TV_OCC3_REC 44
+#define TV_OCC3_REC 48
 #endif
 #define TV_BLOCKS(f) (tv_rec_bytes(f) <= TV_OCC4_REC ? 4 : tv_rec_bytes(f) <= TV_OCC3_REC ? 3 : 2)
 // staged records per work item: a compile-time constant, so every plane of the shared-memory image sits at a constant
@@ -236,8 +237,9 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 
 // ---- shared-memory image of the halo ------------------------------------------------------------------------------
 #define TV_HIDMAX 16   // staged records of one work item the reference's stale bucket lists may hide (pmps_device.cuh, hid_visible)
-struct TvStage {   // shared-memory planes of the staged halo: the walker stages FP64 positions + the type word, the list build float positions
-	float4* fpos; int32_t* tw; double *px, *py, *pz; Nb nb;
+struct TvStage {   // shared-memory planes of the staged halo: the walker stages {x, y} / {z, type word} pairs of doubles (two 16-byte planes: a candidate
+	// is two 128-bit loads, and 8 consecutive records cover all 32 banks), the list build float positions
+	float4* fpos; double2 *pxy, *pzw; Nb nb;
 };
 // Hidden records of a work item (rare: only in a step in which a particle left the domain; pmps_device.cuh, hid_visible): staged
 // index and the bucket the record's array element is listed in.  Only the hit-list build looks at them (k_hl_build): a particle whose
@@ -248,8 +250,7 @@ template <bool B> struct TvBool { static constexpr bool value = B; };
 template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned char* sp) {
 	TvStage t; constexpr size_t m = TV_MAXM;
 	t.fpos = nullptr;
-	t.px = (double*)sp; sp += 8 * m; t.py = (double*)sp; sp += 8 * m; t.pz = (double*)sp; sp += 8 * m;
-	t.tw = (int32_t*)sp; sp += 4 * m;
+	t.pxy = (double2*)sp; sp += 16 * m; t.pzw = (double2*)sp; sp += 16 * m;
 	double *vx = nullptr, *vy = nullptr, *vz = nullptr, *pr = nullptr, *pn = nullptr, *rh = nullptr, *mu = nullptr, *cc = nullptr, *pk = nullptr;
 	if (FIELDS & NF_VEL) { vx = (double*)sp; sp += 8 * m; vy = (double*)sp; sp += 8 * m; vz = (double*)sp; sp += 8 * m; }
 	if (FIELDS & NF_PRESS) { pr = (double*)sp; sp += 8 * m; }
@@ -264,68 +265,63 @@ template <unsigned FIELDS> __device__ __forceinline__ TvStage tv_carve(unsigned 
 
 
 // ---- staging the halo ------------------------------------------------------------------------------------------------
-// One warp per halo bucket.  Neighbour fields are copied with cp.async (global -> shared, no registers, no waiting until
-// the end); positions go through registers four buckets at a time, every load of a batch issued before the first store,
-// so a tile pays a few memory round trips instead of one per bucket (ncu: the staging loads were 20-30 % of all stall
-// samples when issued one bucket at a time).
-template <bool PLANES, unsigned FIELDS>
-__device__ __forceinline__ void tv_stage_one(const DevView& S, const TvStage& T, int j, int m, const double4& pj, double ox, double oy, double oz) {
-	if (PLANES) { T.px[m] = pj.x; T.py[m] = pj.y; T.pz[m] = pj.z; T.tw[m] = __float_as_int(tv_type_word(pj)); }
-	else T.fpos[m] = make_float4((float)(pj.x - ox), (float)(pj.y - oy), (float)(pj.z - oz), tv_type_word(pj));
-}
+// One warp per halo bucket, one lane per record.  Everything the WALKER stages travels with cp.async (global -> shared, no registers,
+// nothing waits until the end): the 32-byte position record as two 16-byte copies into the {x, y} and {z, w} planes, the neighbour
+// fields as 8-byte copies into theirs.  (ncu, round 1/2: with the positions going through registers the staging loads and the
+// stores waiting for them were a quarter of all stall samples of a light pass.)  The list build stages float positions relative to
+// the tile origin and does go through registers, four buckets in flight per thread.
 __device__ __forceinline__ void tv_cp8(const double* dstShared, const double* srcGlobal) {   // 8-byte asynchronous global -> shared copy
 	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"((unsigned)__cvta_generic_to_shared(dstShared)), "l"(srcGlobal));
 }
-template <bool PLANES, unsigned FIELDS, int NT = TV_T>
-__device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, const int* hOff, const int* hBase, int HV, int own0, int P,
-                                         double ox, double oy, double oz, uint16_t* ownMap) {
+__device__ __forceinline__ void tv_cp16(const void* dstShared, const void* srcGlobal) {   // 16-byte asynchronous global -> shared copy, L2 only
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((unsigned)__cvta_generic_to_shared(dstShared)), "l"(srcGlobal));
+}
+template <unsigned FIELDS, int NT = TV_T>
+__device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, const int* hOff, const int* hBase, int HV, int own0, int P, uint16_t* ownMap) {
+	constexpr int NW = NT / 32;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	for (int hb = warp; hb < HV; hb += NW) {
+		const int off = hOff[hb], n = hOff[hb + 1] - off, s0 = hBase[hb];
+		for (int r = lane; r < n; r += 32) {
+			const int j = s0 + r, m = off + r;
+			const double2* pj = (const double2*)(S.pos + j);
+			tv_cp16(T.pxy + m, pj); tv_cp16(T.pzw + m, pj + 1);
+			if (j >= own0 && j < own0 + P) ownMap[j - own0] = (uint16_t)m;
+			if (FIELDS & NF_VEL) { const double* v = (const double*)(S.vel + j); tv_cp8(T.nb.vx + m, v); tv_cp8(T.nb.vy + m, v + 1); tv_cp8(T.nb.vz + m, v + 2); }
+			if (FIELDS & NF_PRESS) tv_cp8(T.nb.press + m, S.press + j);
+			if (FIELDS & NF_PNDI) tv_cp8(T.nb.pndi + m, S.pndi + j);
+			if (FIELDS & NF_RHO) tv_cp8(T.nb.RHO + m, S.RHO + j);
+			if (FIELDS & NF_MEU) tv_cp8(T.nb.MEU + m, S.MEU + j);
+			if (FIELDS & NF_CONC) tv_cp8(T.nb.concentration + m, S.concentration + j);
+			if (FIELDS & NF_PNDKI) tv_cp8(T.nb.pndki + m, S.pndki + j);
+		}
+	}
+	asm volatile("cp.async.wait_all;" ::: "memory");
+}
+// float positions (+ type word) of the halo for the list build
+template <int NT>
+__device__ __forceinline__ void tv_stage_float(const DevView& S, float4* fpos, const int* hOff, const int* hBase, int HV, double ox, double oy, double oz) {
 	constexpr int NB = 4;   // buckets per thread whose position loads are in flight together
 	constexpr int NW = NT / 32;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	// neighbour fields: asynchronous copies straight into the planes (cp.async: no registers, nothing waits until the end)
-	if (FIELDS) {
-		for (int hb = warp; hb < HV; hb += NW) {
-			const int off = hOff[hb], n = hOff[hb + 1] - off, s0 = hBase[hb];
-			for (int r = lane; r < n; r += 32) {
-				const int j = s0 + r, m = off + r;
-				if (FIELDS & NF_VEL) { const double* v = (const double*)(S.vel + j); tv_cp8(T.nb.vx + m, v); tv_cp8(T.nb.vy + m, v + 1); tv_cp8(T.nb.vz + m, v + 2); }
-				if (FIELDS & NF_PRESS) tv_cp8(T.nb.press + m, S.press + j);
-				if (FIELDS & NF_PNDI) tv_cp8(T.nb.pndi + m, S.pndi + j);
-				if (FIELDS & NF_RHO) tv_cp8(T.nb.RHO + m, S.RHO + j);
-				if (FIELDS & NF_MEU) tv_cp8(T.nb.MEU + m, S.MEU + j);
-				if (FIELDS & NF_CONC) tv_cp8(T.nb.concentration + m, S.concentration + j);
-				if (FIELDS & NF_PNDKI) tv_cp8(T.nb.pndki + m, S.pndki + j);
-			}
-		}
-	}
-	// positions go through registers (float copy relative to the tile origin, type word, planes)
 	for (int hb0 = warp; hb0 < HV; hb0 += NW * NB) {
-		double4 p[NB]; int j[NB], m[NB]; bool ok[NB];
+		double4 p[NB]; int m[NB]; bool ok[NB];
 		#pragma unroll
 		for (int b = 0; b < NB; b++) {
 			const int hb = hb0 + b * NW;
-			ok[b] = false; j[b] = 0; m[b] = 0;
-			if (hb < HV) { const int off = hOff[hb]; ok[b] = lane < hOff[hb + 1] - off; j[b] = hBase[hb] + lane; m[b] = off + lane; }
-			if (ok[b]) p[b] = ld256(S.pos + j[b]);
+			ok[b] = false; m[b] = 0;
+			if (hb < HV) { const int off = hOff[hb]; ok[b] = lane < hOff[hb + 1] - off; m[b] = off + lane; if (ok[b]) p[b] = ld256(S.pos + hBase[hb] + lane); }
 		}
 		#pragma unroll
-		for (int b = 0; b < NB; b++) {
-			if (!ok[b]) continue;
-			tv_stage_one<PLANES, FIELDS>(S, T, j[b], m[b], p[b], ox, oy, oz);
-			if (ownMap && j[b] >= own0 && j[b] < own0 + P) ownMap[j[b] - own0] = (uint16_t)m[b];
-		}
+		for (int b = 0; b < NB; b++) if (ok[b]) fpos[m[b]] = make_float4((float)(p[b].x - ox), (float)(p[b].y - oy), (float)(p[b].z - oz), tv_type_word(p[b]));
 		#pragma unroll
 		for (int b = 0; b < NB; b++) {   // buckets with more than 32 particles (far above the lattice density)
 			const int hb = hb0 + b * NW;
 			if (hb >= HV) continue;
 			const int off = hOff[hb], n = hOff[hb + 1] - off, s0 = hBase[hb];
-			for (int r = lane + 32; r < n; r += 32) {
-				tv_stage_one<PLANES, FIELDS>(S, T, s0 + r, off + r, ld256(S.pos + s0 + r), ox, oy, oz);
-				if (ownMap && s0 + r >= own0 && s0 + r < own0 + P) ownMap[s0 + r - own0] = (uint16_t)(off + r);
-			}
+			for (int r = lane + 32; r < n; r += 32) { const double4 q = ld256(S.pos + s0 + r); fpos[off + r] = make_float4((float)(q.x - ox), (float)(q.y - oy), (float)(q.z - oz), tv_type_word(q)); }
 		}
 	}
-	if (FIELDS) asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 // ---- hit list in tile-local indices ------------------------------------------------------------------------------------
@@ -352,8 +348,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 	__shared__ unsigned sMinBits;   // smallest squared pair distance of the item (bits of a positive float)
 	__shared__ TvHid sHid;          // hidden records of the item (only in a step in which a particle left the domain)
 	const int nHidAll = S.hid[0];   // uniform over the grid
-	TvStage T; T.fpos = (float4*)smemRaw; T.px = T.py = T.pz = nullptr;
-	float4* const fpos = T.fpos;
+	float4* const fpos = (float4*)smemRaw;
 	const int cap = S.tlCap;
 	const int tid = threadIdx.x, lane = tid & 31, w0 = tid & ~31;
 	uint16_t* const rows = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM);
@@ -377,7 +372,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		tv_stage<false, 0, HL_T>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, nullptr);
+		tv_stage_float<HL_T>(S, fpos, hOff, hBase, b.HV, ox, oy, oz);
 		if (tid == 0) fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the far-away dummy record: what a lane reads beyond the end of its stretch
 		if (nHidAll > 0) {   // which staged records of this item are hidden entries (S.hid)?  One thread per entry.
 			if (tid == 0) sHid.n = 0;
@@ -541,12 +536,12 @@ static __global__ void __launch_bounds__(256) k_tails(const __grid_constant__ De
 template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m) {
 	Pair q; q.j = m;
-	const double xj = T.px[m], yj = T.py[m], zj = T.pz[m];
+	const double2 xy = T.pxy[m], zw = T.pzw[m];
+	const double xj = xy.x, yj = xy.y, zj = zw.x;
 	q.rx = xj - s.pi.x; q.ry = yj - s.pi.y; q.rz = zj - s.pi.z;
 	q.d2 = sq3_exact(q.rx, q.ry, q.rz);
 	if (!(q.d2 < K.reMax2)) return;
-	const int tw = T.tw[m];
-	q.tj = (int)(short)(tw & 0xffff); q.ptj = tw >> 16;
+	q.tj = __double2loint(zw.y); q.ptj = __double2hiint(zw.y);   // the type word of the position record (pk_make)
 	if (POLY && s.hasMirror) { q.mx = xj - s.mix; q.my = yj - s.miy; q.mz = zj - s.miz; q.dm2 = sq3_exact(q.mx, q.my, q.mz); }
 	else { q.mx = q.my = q.mz = 0.0; q.dm2 = __longlong_as_double(0x7ff0000000000000ll); }   // no mirror in reach: d2 < dm2 holds, M(re) fails (pmps_internal.h, mirrorFar2)
 	q.rinv = fast_rsqrt(q.d2);
@@ -557,13 +552,13 @@ __device__ __forceinline__ void tv_pair(typename F::Ctx& ctx, const TvStage& T, 
 template <bool POLY, class F>
 __device__ __forceinline__ void tv_pair2(typename F::Ctx& ctx, const TvStage& T, const KParams& K, const Self& s, int m0, int m1) {
 	Pair a, b; a.j = m0; b.j = m1;
-	const double xa = T.px[m0], ya = T.py[m0], za = T.pz[m0], xb = T.px[m1], yb = T.py[m1], zb = T.pz[m1];
-	const int wa = T.tw[m0], wb = T.tw[m1];
+	const double2 xya = T.pxy[m0], zwa = T.pzw[m0], xyb = T.pxy[m1], zwb = T.pzw[m1];
+	const double xa = xya.x, ya = xya.y, za = zwa.x, xb = xyb.x, yb = xyb.y, zb = zwb.x;
 	a.rx = xa - s.pi.x; a.ry = ya - s.pi.y; a.rz = za - s.pi.z; b.rx = xb - s.pi.x; b.ry = yb - s.pi.y; b.rz = zb - s.pi.z;
 	a.d2 = sq3_exact(a.rx, a.ry, a.rz); b.d2 = sq3_exact(b.rx, b.ry, b.rz);
 	const bool ha = a.d2 < K.reMax2, hb = b.d2 < K.reMax2;
 	if (!(ha || hb)) return;
-	a.tj = (int)(short)(wa & 0xffff); a.ptj = wa >> 16; b.tj = (int)(short)(wb & 0xffff); b.ptj = wb >> 16;
+	a.tj = __double2loint(zwa.y); a.ptj = __double2hiint(zwa.y); b.tj = __double2loint(zwb.y); b.ptj = __double2hiint(zwb.y);
 	if (POLY && s.hasMirror) {
 		a.mx = xa - s.mix; a.my = ya - s.miy; a.mz = za - s.miz; a.dm2 = sq3_exact(a.mx, a.my, a.mz);
 		b.mx = xb - s.mix; b.my = yb - s.miy; b.mz = zb - s.miz; b.dm2 = sq3_exact(b.mx, b.my, b.mz);
@@ -574,23 +569,25 @@ __device__ __forceinline__ void tv_pair2(typename F::Ctx& ctx, const TvStage& T,
 	if (ha) F::template pair<POLY>(ctx, T.nb, K, s, a);
 	if (hb) F::template pair<POLY>(ctx, T.nb, K, s, b);
 }
-__device__ __forceinline__ void tv_cp16(const void* dstShared, const void* srcGlobal) {   // 16-byte asynchronous global -> shared copy, L2 only
-	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((unsigned)__cvta_generic_to_shared(dstShared)), "l"(srcGlobal));
-}
-// the hit lists of one round of TV_NG particles on their way into shared memory: 8 x 16 bytes per chunk-0 row, one commit group
-__device__ __forceinline__ void tv_fetch_lists(const DevView& S, unsigned char* rowsBuf, int own0, int p0, int P) {
-	const int n = min(TV_NG, P - p0);
-	for (int q = threadIdx.x; q < n * (TV_CHUNK * 2 / 16); q += TV_T) {
-		const int r = q >> 3, c = q & 7;
-		tv_cp16(rowsBuf + (size_t)r * TV_LROW + c * 16, (const unsigned char*)(S.hlist + (size_t)(own0 + p0 + r) * (size_t)S.tlCap) + c * 16);
+// The first chunk (64 entries, 128 bytes) of the hit lists of one round on its way into shared memory.  Every WARP fetches the rows
+// of its own lane groups (8 rows x 8 pieces of 16 bytes, two per lane) and is the only one to read them: a round needs no block
+// barrier, and because a lane group takes its row into registers at the start of the round, the next round's rows can land in the
+// same buffer while the round computes.  One commit group.
+__device__ __forceinline__ void tv_fetch_rows(const DevView& S, unsigned char* rowsBuf, int own0, int p0, int P) {
+	const int lane = threadIdx.x & 31, g0 = (threadIdx.x >> 5) * (32 / TV_G);
+	#pragma unroll
+	for (int q = lane; q < (32 / TV_G) * (TV_CHUNK * 2 / 16); q += 32) {
+		const int r = q >> 3, c = q & 7, p = p0 + g0 + r;
+		if (p < P) tv_cp16(rowsBuf + (size_t)(g0 + r) * TV_LROW + c * 16, (const unsigned char*)(S.hlist + (size_t)(own0 + p) * (size_t)S.tlCap) + c * 16);
 	}
 	asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
 // Every lane group takes its particle's HIT list (k_hl_build: the staged records within reach at the positions of the current
 // epoch) — no scan, no queue, no votes.  What a round needs from global memory besides the staged halo — the list rows, the list
-// lengths, the has-a-mirror flags — is fetched into shared memory ahead of time (lists: cp.async, double-buffered per round; the
+// lengths, the has-a-mirror flags — is fetched into shared memory ahead of time (lists: cp.async, one round ahead, per warp; the
 // per-particle scalars with the staging loads), because ncu showed the round-start loads of these as 25 % of all stall samples.
+// Block barriers per work item: table loaded, halo staged, item done (twice) — none inside the rounds.
 template <bool POLY, unsigned FIELDS, bool WALLONLY, bool SPARSE, class F>
 __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
@@ -598,8 +595,8 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 	const TvStage T = tv_carve<FIELDS>(smemRaw);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
 	unsigned char* const fx = smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS);
-	unsigned char* const rowsBuf = fx;                                       // 2 x TV_NG list rows of TV_LROW bytes
-	uint16_t* const ownMap = (uint16_t*)(fx + 2 * TV_NG * TV_LROW);          // own particle -> staged index
+	unsigned char* const rowsBuf = fx;                                       // TV_NG list rows of TV_LROW bytes
+	uint16_t* const ownMap = (uint16_t*)(fx + TV_NG * TV_LROW);          // own particle -> staged index
 	uint16_t* const sCnt = ownMap + TV_MAXOWN;                               // own particle -> entries of its hit list
 	uint8_t* const sHas = (uint8_t*)(sCnt + TV_MAXOWN);                      // own particle -> a mirror particle is in reach
 	const unsigned gshift = (tid & 31) & ~(TV_G - 1);
@@ -646,18 +643,24 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		tv_fetch_lists(S, rowsBuf, own0, 0, P);   // first round's lists on their way while the staging loads land
+		tv_fetch_rows(S, rowsBuf, own0, 0, P);   // first round's lists on their way while the staging loads land
 		for (int p = tid; p < P; p += TV_T) {     // per-particle scalars of the whole item, independent loads issued together with the staging
 			sCnt[p] = S.hcnt[own0 + p];
 			if (POLY) sHas[p] = S.distParticleWall2[own0 + p] < K.mirrorFar2 ? 1 : 0;
 		}
-		tv_stage<true, FIELDS>(S, T, hOff, hBase, b.HV, own0, P, ox, oy, oz, ownMap);
-		if (tid == 0) { T.tw[M] = 0; T.px[M] = T.py[M] = T.pz[M] = 1e30; }   // the record list padding points at
+		tv_stage<FIELDS>(S, T, hOff, hBase, b.HV, own0, P, ownMap);
+		if (tid == 0) { T.pxy[M] = make_double2(1e30, 1e30); T.pzw[M] = make_double2(1e30, 0.0); }   // the record list padding points at
+		__syncthreads();   // the staged halo, ownMap and the per-particle scalars are visible to every thread
+		const uint4* const Ls = (const uint4*)(rowsBuf + (size_t)grp * TV_LROW) + g * (TV_PER / 8);   // this lane's part of its group's row
 		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask shuffles) ----
-		for (int p0 = 0, rnd = 0; p0 < P; p0 += TV_NG, rnd++) {
+		for (int p0 = 0; p0 < P; p0 += TV_NG) {
 			asm volatile("cp.async.wait_group 0;" ::: "memory");
-			__syncthreads();   // this round's list rows (and, in round 0, the staged halo) are visible to every thread; everybody has left the round before
-			if (p0 + TV_NG < P) tv_fetch_lists(S, rowsBuf + ((rnd + 1) & 1) * (TV_NG * TV_LROW), own0, p0 + TV_NG, P);   // next round's rows land while this round computes
+			__syncwarp();   // this warp's rows of the round have landed
+			unsigned w[TV_PER / 2];   // chunk 0 of the list: this lane's entries, into registers
+			#pragma unroll
+			for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = Ls[v]; w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
+			__syncwarp();
+			if (p0 + TV_NG < P) tv_fetch_rows(S, rowsBuf, own0, p0 + TV_NG, P);   // next round's rows land while this round computes
 			const int p = p0 + grp;
 			bool act = p < P;
 			const int i = own0 + (act ? p : 0);
@@ -667,9 +670,9 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 			if (act) {
 				cntE = sCnt[p];
 				const int ms = ownMap[p];
-				const int tw = T.tw[ms];
-				s.type = (int)(short)(tw & 0xffff); s.ptype = tw >> 16;
-				s.pi.x = T.px[ms]; s.pi.y = T.py[ms]; s.pi.z = T.pz[ms]; s.pi.w = pk_make(s.type, s.ptype);
+				const double2 xy = T.pxy[ms], zw = T.pzw[ms];
+				s.pi.x = xy.x; s.pi.y = xy.y; s.pi.z = zw.x; s.pi.w = zw.y;
+				s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
 				if (F::kCopyPos && s.lead) S.pos2[i] = s.pi;
 				if (F::kCopyVel && s.lead) S.vel2[i] = S.vel[i];
 				act = s.type != K.p.ghost;
@@ -687,12 +690,12 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 				pairs = act && F::need_pairs(ctx);
 			}
 			if (!pairs) cntE = 0;
-			const uint4* Ls = (const uint4*)(rowsBuf + (rnd & 1) * (TV_NG * TV_LROW) + (size_t)grp * TV_LROW) + g * (TV_PER / 8);   // chunk 0: shared memory
-			const uint4* Lg = (const uint4*)(S.hlist + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);                            // further chunks (rare): global
+			const uint4* Lg = (const uint4*)(S.hlist + (size_t)i * (size_t)S.tlCap) + g * (TV_PER / 8);   // further chunks (rare): global
 			for (int ch = 0; ch * TV_CHUNK < cntE; ch++) {
-				unsigned w[TV_PER / 2];
-				#pragma unroll
-				for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = ch == 0 ? Ls[v] : __ldg(Lg + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
+				if (ch > 0) {
+					#pragma unroll
+					for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(Lg + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
+				}
 				const int rem = cntE - ch * TV_CHUNK - g;   // entries u * TV_G + g of this chunk exist for u * TV_G < rem
 #if TV_ILP2
 				#pragma unroll

@@ -342,6 +342,8 @@ class EngineBackend(TableBackend):
         L.pmps_slab_collect.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.pmps_slab_apply.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.pmps_slab_wants_rebuild.argtypes = [ctypes.c_void_p]
+        L.pmps_slab_mid_check.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.pmps_slab_mid_rebuild.argtypes = [ctypes.c_void_p]
         L.pmps_slab_set_hooks.argtypes = [ctypes.c_void_p, ctypes.c_void_p, SUM_FN, REFRESH_FN, ctypes.c_void_p]
         ps = eng.ps
         self._ghost_pos = [ps.domainMaxX - ps.partDist, ps.domainMaxY - ps.partDist, 0.0 if int(ps.dim) == 2 else ps.domainMaxZ - ps.partDist]
@@ -399,8 +401,9 @@ class SlabEngine:
         self.backend = EngineBackend(self.eng, n0, self.dev)
         grid = (ps.domainMinX, ps.bucketSide, ps.numBucketsX, list(cuts)) if cuts is not None else None
         self.dom = SlabDomain(self.backend, rank, world, cuts_x[rank], cuts_x[rank + 1], ps.bucketSide * (1.0 + 1e-9), group=group, grid=grid)
-        self.scal = torch.zeros(3, dtype=torch.float64, device=self.dev)
+        self.scal = torch.zeros(4, dtype=torch.float64, device=self.dev)
         self.nph = int(self.eng.lib.pmps_step_phases())
+        self.midstep = os.environ.get("PMPS_SLAB_STEPSTART") is None   # rebuild decision after the prediction (default) or at the step start (round 1)
         # the Poisson solve of the incompressible scheme calls back for its all-reduces and the halo refresh of the search direction
         self.work = torch.zeros(8, dtype=torch.float64, device=self.dev)
         def _sum(user, n):
@@ -464,6 +467,13 @@ class SlabEngine:
                     if timing:
                         torch.cuda.synchronize(self.dev); t2 = time.perf_counter()
                         print("[slab] phase %d: kernels %.1f ms, refresh %.1f ms" % (ph, 1e3 * (t1 - t0), 1e3 * (t2 - t1)), flush=True)
+                    if ph == 0 and self.midstep:
+                        # the rebuild decision, where a single GPU takes it: after the prediction, from the maxima over all ranks
+                        self.eng._chk(L.pmps_slab_collect(h, self.scal.data_ptr()))
+                        self.dom.all_max(self.scal)
+                        if self.eng._chk(L.pmps_slab_mid_check(h, self.scal.data_ptr())) == 1:
+                            self.dom.repartition()
+                            self.eng._chk(L.pmps_slab_mid_rebuild(h))
                 self.eng._chk(L.pmps_slab_collect(h, self.scal.data_ptr()))
                 self.dom.all_max(self.scal)
                 self.eng._chk(L.pmps_slab_apply(h, self.scal.data_ptr()))

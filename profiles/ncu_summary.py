@@ -78,9 +78,13 @@ def lines(rep, pat, top, ncupat):
             curb = {"name": r[1], "rows": []}; blocks.append(curb); continue
         if curb is not None:
             curb["rows"].append(r)
+    def weight(b):   # several launches of the kernel may be in the report (some return at once): take the one that did the most work
+        try:
+            ie_ = b["rows"][0].index("Instructions Executed"); return sum(int(r[ie_]) for r in b["rows"][1:])
+        except Exception:
+            return 0
+    blocks = sorted([b for b in blocks if ncupat in b["name"]], key=weight, reverse=True)[:1]
     for b in blocks:
-        if ncupat not in b["name"]:
-            continue
         hdr, data = b["rows"][0], b["rows"][1:]
         ie, isamp = hdr.index("Instructions Executed"), hdr.index("Warp Stall Sampling (All Samples)")
         if len(data) != len(seq):
