@@ -100,6 +100,7 @@ __global__ void k_slab_collect(const __grid_constant__ DevView S, double* out) {
 }
 __global__ void k_slab_set_velmax(const __grid_constant__ DevView S, const double* in) {
 	const unsigned long long b = (unsigned long long)__double_as_longlong(in[2]); S.velMax2Bits[0] = b; S.velMax2Bits[1] = b;
+	S.maxDisp2[2] = S.maxDisp2[0];   // the displacement this step ends with: the next mid-step check derives the size of a step's small moves from it
 }
 extern "C" int pmps_slab_collect(pmps_t* h, double* d_out4) {
 	double* const d_out3 = d_out4;

@@ -299,6 +299,11 @@ __global__ void k_hits_decide(const __grid_constant__ DevView S, const __grid_co
 // k_hits_decide says the old one may miss a pair (k_hl_build returns at once otherwise)
 int pmps_tv_hits(pmps_handle* h) {
 	DevView& S = h->V;
+	if (getenv("PMPS_DEBUG")) {   // what the decision below will see
+		float hm[2] = { 0.f, 0.f }; int32_t hc = 0;
+		cudaMemcpyAsync(hm, S.hitMove, sizeof hm, cudaMemcpyDeviceToHost, h->stream); cudaMemcpyAsync(&hc, S.hid, sizeof hc, cudaMemcpyDeviceToHost, h->stream); cudaStreamSynchronize(h->stream);
+		fprintf(stderr, "[pmps] hit-list check (walk %d): moved %.4g lo since the list was made, margin %.4g lo, forced %d, hidden entries %d\n", h->walkSeq, sqrt((double)hm[0]) / h->K.p.partDist, (double)hm[1] / h->K.p.partDist, h->hitForce ? 1 : 0, hc);
+	}
 	LAUNCH(h, "list.hits_decide", k_hits_decide, 1, 1, S, h->K, h->hitForce ? 1 : 0);
 	h->hitForce = false;
 	{ const int rc = launch_hl_build(h, "list.hits", 0); if (rc) return rc; }
