@@ -302,7 +302,7 @@ def main_gpu_slab(args, rank, world, local):
                 eng.synchronize()
             T = {f: host[f].to(se.dev, non_blocking=True) for f in e2e_fields}
             tick("h2d")
-            se.backend.upload_table(T, se.dom.n_live, se.dom.n_own)
+            se.backend.upload_table(T, se.dom.n_live, se.dom.n_own, same_rows=True)   # the rows the engine handed out: no re-partition, no re-sort unless somebody moved too far
         tick("upload")
         se.step(1)
         tick("step")
@@ -321,7 +321,7 @@ def main_gpu_slab(args, rank, world, local):
     te = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda"); dist.all_reduce(te, op=dist.ReduceOp.MAX)
     nb = torch.tensor([float(sum(host[f].numel() * host[f].element_size() for f in e2e_fields))], dtype=torch.float64, device="cuda"); dist.all_reduce(nb)
     e2e = {"value": total * e2e_steps / (float(te.item()) * 1e-3), "unit": UNIT, "steps": e2e_steps, "h2d_bytes_per_step": int(nb.item()), "d2h_bytes_per_step": int(nb.item()),
-           "api": "per rank and step: pinned host table -> pmps_upload_device, the phased step with halo refreshes (re-partition included: new positions force the bucket rebuild), pmps_download_device -> pinned host"}
+           "api": "per rank and step: pinned host table -> pmps_upload_values_device (same rows: partition, bucket order and lists survive, the displacement trackers decide), the phased step with halo refreshes and mid-step re-partitions, pmps_download_device -> pinned host"}
     per_rank = [None] * world
     dist.all_gather_object(per_rank, {"owned": n_own, "halo": se.dom.n_live - n_own, "ms_per_step": ms_local / args.steps,
                                       "repartitions": st1["repartitions"] - st0["repartitions"], "migrants_out": st1["migrants_out"] - st0["migrants_out"],

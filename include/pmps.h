@@ -141,6 +141,14 @@ int pmps_set_uniform_vel_wall(pmps_t* h, const double v[3]);
 int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArrays* out);
 /* device-resident inputs (bench `value` leg, multi-GPU slabs): same layout as the host arrays, device pointers */
 int pmps_upload_device(pmps_t* h, const PmpsHostArrays* device_arrays);
+/* The same rows with new values — a host-driven loop that hands back the particle table it received (a slab rank between two
+ * re-partitions): bucket order, hit lists and the partition survive, the displacement trackers decide about rebuilds as inside a step. */
+int pmps_upload_values_device(pmps_t* h, const PmpsHostArrays* device_arrays);
+/* Row sets: gather / scatter the particles with host indices d_rows[0..n) from / into compact device arrays of n entries (the non-NULL
+ * members of the struct).  The upload makes a NEW particle table of the handle (a slab re-partition that rewrites only the rows that
+ * changed hands or places): bucket order and lists are re-made before the next pass; numParticles = the new live count. */
+int pmps_download_rows_device(pmps_t* h, PmpsHostArrays* device_arrays, int n, const int32_t* d_rows);
+int pmps_upload_rows_device(pmps_t* h, const PmpsHostArrays* device_arrays, int n, const int32_t* d_rows, int numParticles);
 int pmps_download_device(pmps_t* h, PmpsHostArrays* device_arrays);   /* gather to host order into device arrays */
 
 /* ---- stage calls: one per reference method, in mainLoopOfSimulation order (src/main.cpp:256-456) ----------- */

@@ -5,31 +5,33 @@
 #include "pmps_device.cuh"
 #include <cstring>
 
-__global__ void k_up_f64(const double* __restrict__ src, double* dst, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	dst[slotOfHost[hI]] = src[hI];
+// `rows` (optional): the n entries of the host-side arrays are the particles with these host indices (a compact row set); without it
+// entry t is host index t
+__global__ void k_up_f64(const double* __restrict__ src, double* dst, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	dst[slotOfHost[rows ? rows[t] : t]] = src[t];
 }
-__global__ void k_up_i32(const int32_t* __restrict__ src, int32_t* dst, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	dst[slotOfHost[hI]] = src[hI];
+__global__ void k_up_i32(const int32_t* __restrict__ src, int32_t* dst, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	dst[slotOfHost[rows ? rows[t] : t]] = src[t];
 }
-__global__ void k_up_u8(const uint8_t* __restrict__ src, uint8_t* dst, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	dst[slotOfHost[hI]] = src[hI];
+__global__ void k_up_u8(const uint8_t* __restrict__ src, uint8_t* dst, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	dst[slotOfHost[rows ? rows[t] : t]] = src[t];
 }
-__global__ void k_up_v3(const double* __restrict__ src, V3 dst, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	const int s = slotOfHost[hI];
-	dst.x[s] = src[3 * (size_t)hI]; dst.y[s] = src[3 * (size_t)hI + 1]; dst.z[s] = src[3 * (size_t)hI + 2];
+__global__ void k_up_v3(const double* __restrict__ src, V3 dst, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	const int s = slotOfHost[rows ? rows[t] : t];
+	dst.x[s] = src[3 * (size_t)t]; dst.y[s] = src[3 * (size_t)t + 1]; dst.z[s] = src[3 * (size_t)t + 2];
 }
 // pos/vel records: xyz from an interleaved array, pos.w from particleType / PTYPE (any of the sources may be NULL)
 __global__ void k_up_pack(const double* __restrict__ xyz, const int32_t* __restrict__ type, const int32_t* __restrict__ ptype,
-                          double4* dst, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	const int s = slotOfHost[hI];
+                          double4* dst, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	const int s = slotOfHost[rows ? rows[t] : t];
 	double4 r = dst[s];
-	if (xyz) { r.x = xyz[3 * (size_t)hI]; r.y = xyz[3 * (size_t)hI + 1]; r.z = xyz[3 * (size_t)hI + 2]; }
-	if (type || ptype) r.w = pk_make(type ? type[hI] : pk_type(r), ptype ? ptype[hI] : pk_ptype(r));
+	if (xyz) { r.x = xyz[3 * (size_t)t]; r.y = xyz[3 * (size_t)t + 1]; r.z = xyz[3 * (size_t)t + 2]; }
+	if (type || ptype) r.w = pk_make(type ? type[t] : pk_type(r), ptype ? ptype[t] : pk_ptype(r));
 	dst[s] = r;
 }
 
@@ -44,32 +46,35 @@ __global__ void k_up_pos_soft(const double* __restrict__ xyz, const int32_t* __r
 	if (type || ptype) r.w = pk_make(type ? type[hI] : pk_type(r), ptype ? ptype[hI] : pk_ptype(r));
 	if (__double_as_longlong(r.w) != __double_as_longlong(old.w)) S.flags[FLAG_UPLOAD_TYPES] = 1;
 	S.pos[s] = r;
-	if (pk_type(r) != K.p.ghost) track_disp(S, K, s, r);
+	if (pk_type(r) != K.p.ghost) {
+		if (owned_slot(S, s)) track_disp(S, K, s, r);
+		else track_hit_disp(S, K, s, r);   // a halo copy (slab rank): its position as the caller has it — does the hit list still cover it?
+	}
 }
 
-__global__ void k_dn_f64(double* dst, const double* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	dst[hI] = src[slotOfHost[hI]];
+__global__ void k_dn_f64(double* dst, const double* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	dst[t] = src[slotOfHost[rows ? rows[t] : t]];
 }
-__global__ void k_dn_i32(int32_t* dst, const int32_t* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	dst[hI] = src[slotOfHost[hI]];
+__global__ void k_dn_i32(int32_t* dst, const int32_t* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	dst[t] = src[slotOfHost[rows ? rows[t] : t]];
 }
-__global__ void k_dn_u8(uint8_t* dst, const uint8_t* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	dst[hI] = src[slotOfHost[hI]];
+__global__ void k_dn_u8(uint8_t* dst, const uint8_t* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	dst[t] = src[slotOfHost[rows ? rows[t] : t]];
 }
-__global__ void k_dn_v3(double* dst, V3 src, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	const int s = slotOfHost[hI];
-	dst[3 * (size_t)hI] = src.x[s]; dst[3 * (size_t)hI + 1] = src.y[s]; dst[3 * (size_t)hI + 2] = src.z[s];
+__global__ void k_dn_v3(double* dst, V3 src, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	const int s = slotOfHost[rows ? rows[t] : t];
+	dst[3 * (size_t)t] = src.x[s]; dst[3 * (size_t)t + 1] = src.y[s]; dst[3 * (size_t)t + 2] = src.z[s];
 }
-__global__ void k_dn_pack(double* xyz, int32_t* type, int32_t* ptype, const double4* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n0) {
-	const int hI = blockIdx.x * blockDim.x + threadIdx.x; if (hI >= n0) return;
-	const double4 r = src[slotOfHost[hI]];
-	if (xyz) { xyz[3 * (size_t)hI] = r.x; xyz[3 * (size_t)hI + 1] = r.y; xyz[3 * (size_t)hI + 2] = r.z; }
-	if (type) type[hI] = pk_type(r);
-	if (ptype) ptype[hI] = pk_ptype(r);
+__global__ void k_dn_pack(double* xyz, int32_t* type, int32_t* ptype, const double4* __restrict__ src, const int32_t* __restrict__ slotOfHost, int n, const int32_t* __restrict__ rows) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x; if (t >= n) return;
+	const double4 r = src[slotOfHost[rows ? rows[t] : t]];
+	if (xyz) { xyz[3 * (size_t)t] = r.x; xyz[3 * (size_t)t + 1] = r.y; xyz[3 * (size_t)t + 2] = r.z; }
+	if (type) type[t] = pk_type(r);
+	if (ptype) ptype[t] = pk_ptype(r);
 }
 __global__ void k_set_live(const __grid_constant__ DevView S, int live) { S.flags[FLAG_LIVE] = live; }
 
@@ -98,7 +103,7 @@ extern "C" int pmps_unregister_host(pmps_t* h, void* p) {
 	return PMPS_OK;   // not ours (never registered here, or pinned by the caller)
 }
 
-static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) {
+static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc, bool sameRows = false) {
 	if (!h || !a) return PMPS_E_ARG;
 	cudaSetDevice(h->device);
 	{ const int rc = pmps_ensure_capacity(h, a->numParticlesZero); if (rc) return rc; }   // first upload fixes the capacity
@@ -117,20 +122,21 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 		const double* x = (const double*)src(a->pos, 24 * (size_t)n0, 0);
 		const int32_t* t = (const int32_t*)src(a->particleType, 4 * (size_t)n0, 24 * (size_t)n0);
 		const int32_t* pt = (const int32_t*)src(a->PTYPE, 4 * (size_t)n0, 28 * (size_t)n0);
-		soft = a->pos && h->haveList && !h->slab && a->numParticles == h->numParticles && !getenv("PMPS_HARD_UPLOAD");
+		// (a slab rank's table changes its rows at a re-partition: only the caller knows when it hands back the SAME rows, pmps_upload_values_device)
+		soft = a->pos && h->haveList && (!h->slab || sameRows) && a->numParticles == h->numParticles && !getenv("PMPS_HARD_UPLOAD");
 		if (soft) { cudaMemsetAsync(&S.flags[FLAG_UPLOAD_TYPES], 0, sizeof(int32_t), h->stream); LAUNCH(h, "upload", k_up_pos_soft, G, T, x, t, pt, S, h->K, n0); }
-		else LAUNCH(h, "upload", k_up_pack, G, T, x, t, pt, S.pos, soh, n0);
+		else LAUNCH(h, "upload", k_up_pack, G, T, x, t, pt, S.pos, soh, n0, (const int32_t*)nullptr);
 	}
-	if (a->vel) { const double* x = (const double*)src(a->vel, 24 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_pack, G, T, x, (const int32_t*)nullptr, (const int32_t*)nullptr, S.vel, soh, n0); }
-	if (a->particleNearWall) { const uint8_t* x = (const uint8_t*)src(a->particleNearWall, (size_t)n0, 0); LAUNCH(h, "upload", k_up_u8, G, T, x, S.particleNearWall, soh, n0); }
-#define X(n) if (a->n) { const int32_t* x = (const int32_t*)src(a->n, 4 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_i32, G, T, x, S.n, soh, n0); }
+	if (a->vel) { const double* x = (const double*)src(a->vel, 24 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_pack, G, T, x, (const int32_t*)nullptr, (const int32_t*)nullptr, S.vel, soh, n0, (const int32_t*)nullptr); }
+	if (a->particleNearWall) { const uint8_t* x = (const uint8_t*)src(a->particleNearWall, (size_t)n0, 0); LAUNCH(h, "upload", k_up_u8, G, T, x, S.particleNearWall, soh, n0, (const int32_t*)nullptr); }
+#define X(n) if (a->n) { const int32_t* x = (const int32_t*)src(a->n, 4 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_i32, G, T, x, S.n, soh, n0, (const int32_t*)nullptr); }
 	PMPS_I32_FIELDS(X)
 #undef X
-#define X(n) if (a->n) { const double* x = (const double*)src(a->n, 8 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_f64, G, T, x, S.n, soh, n0); }
+#define X(n) if (a->n) { const double* x = (const double*)src(a->n, 8 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_f64, G, T, x, S.n, soh, n0, (const int32_t*)nullptr); }
 	PMPS_F64_FIELDS(X)
 	if (h->K.p.fluidType == 1) { PMPS_RHEO_FIELDS(X) }
 #undef X
-#define X(n) if (a->n) { const double* x = (const double*)src(a->n, 24 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_v3, G, T, x, S.n, soh, n0); }
+#define X(n) if (a->n) { const double* x = (const double*)src(a->n, 24 * (size_t)n0, 0); LAUNCH(h, "upload", k_up_v3, G, T, x, S.n, soh, n0, (const int32_t*)nullptr); }
 	PMPS_V3_FIELDS(X)
 #undef X
 	LAUNCH(h, "upload", k_set_live, 1, 1, S, a->numParticles);
@@ -155,6 +161,7 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc) 
 
 extern "C" int pmps_upload(pmps_t* h, const PmpsHostArrays* a) { return upload_impl(h, a, false); }
 extern "C" int pmps_upload_device(pmps_t* h, const PmpsHostArrays* a) { return upload_impl(h, a, true); }
+extern "C" int pmps_upload_values_device(pmps_t* h, const PmpsHostArrays* a) { return upload_impl(h, a, true, true); }
 
 static int download_impl(pmps_handle* h, PmpsHostArrays* a, bool deviceDst) {
 	if (!h || !a) return PMPS_E_ARG;
@@ -173,21 +180,21 @@ static int download_impl(pmps_handle* h, PmpsHostArrays* a, bool deviceDst) {
 		double* x = a->pos ? (double*)b : nullptr; int32_t* t = a->particleType ? (int32_t*)(b + 24 * (size_t)n0) : nullptr;
 		int32_t* pt = a->PTYPE ? (int32_t*)(b + 28 * (size_t)n0) : nullptr;
 		if (deviceDst) { x = a->pos; t = a->particleType; pt = a->PTYPE; }
-		LAUNCH(h, "download", k_dn_pack, G, T, x, t, pt, S.pos, soh, n0);
+		LAUNCH(h, "download", k_dn_pack, G, T, x, t, pt, S.pos, soh, n0, (const int32_t*)nullptr);
 		if (x) out(a->pos, x, 24 * (size_t)n0);
 		if (t) out(a->particleType, t, 4 * (size_t)n0);
 		if (pt) out(a->PTYPE, pt, 4 * (size_t)n0);
 	}
-	if (a->vel) { char* b = STG(a->vel); LAUNCH(h, "download", k_dn_pack, G, T, (double*)b, (int32_t*)nullptr, (int32_t*)nullptr, S.vel, soh, n0); out(a->vel, b, 24 * (size_t)n0); }
-	if (a->particleNearWall) { char* b = STG(a->particleNearWall); LAUNCH(h, "download", k_dn_u8, G, T, (uint8_t*)b, S.particleNearWall, soh, n0); out(a->particleNearWall, b, (size_t)n0); }
-#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_i32, G, T, (int32_t*)b, S.n, soh, n0); out(a->n, b, 4 * (size_t)n0); }
+	if (a->vel) { char* b = STG(a->vel); LAUNCH(h, "download", k_dn_pack, G, T, (double*)b, (int32_t*)nullptr, (int32_t*)nullptr, S.vel, soh, n0, (const int32_t*)nullptr); out(a->vel, b, 24 * (size_t)n0); }
+	if (a->particleNearWall) { char* b = STG(a->particleNearWall); LAUNCH(h, "download", k_dn_u8, G, T, (uint8_t*)b, S.particleNearWall, soh, n0, (const int32_t*)nullptr); out(a->particleNearWall, b, (size_t)n0); }
+#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_i32, G, T, (int32_t*)b, S.n, soh, n0, (const int32_t*)nullptr); out(a->n, b, 4 * (size_t)n0); }
 	PMPS_I32_FIELDS(X)
 #undef X
-#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_f64, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 8 * (size_t)n0); }
+#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_f64, G, T, (double*)b, S.n, soh, n0, (const int32_t*)nullptr); out(a->n, b, 8 * (size_t)n0); }
 	PMPS_F64_FIELDS(X)
 	if (h->K.p.fluidType == 1) { PMPS_RHEO_FIELDS(X) }
 #undef X
-#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_v3, G, T, (double*)b, S.n, soh, n0); out(a->n, b, 24 * (size_t)n0); }
+#define X(n) if (a->n) { char* b = STG(a->n); LAUNCH(h, "download", k_dn_v3, G, T, (double*)b, S.n, soh, n0, (const int32_t*)nullptr); out(a->n, b, 24 * (size_t)n0); }
 	PMPS_V3_FIELDS(X)
 #undef X
 	if (h->deferSync) return PMPS_OK;   // pmps_step_host: this part rides on the copy stream while the step goes on
@@ -198,6 +205,60 @@ static int download_impl(pmps_handle* h, PmpsHostArrays* a, bool deviceDst) {
 	return PMPS_OK;
 #undef STG
 }
+// ---- row sets (slab re-partition: only the rows that change hands or places travel; polymps_b200/slab.py) --------------------------
+// Gathers / scatters the particles with host indices d_rows[0..n) from / into COMPACT device arrays of n entries each (the arrays of
+// `a` that are not NULL).  The upload turns the handle's particle table into a new one: bucket order and lists are re-made before
+// the next pass, numParticles becomes the new live count.
+extern "C" int pmps_download_rows_device(pmps_t* h, PmpsHostArrays* a, int n, const int32_t* d_rows) {
+	if (!h || !a || n < 0 || (n > 0 && !d_rows)) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_download_rows_device: nothing uploaded");
+	if (n == 0) return PMPS_OK;
+	const int T = 256, G = cdiv(n, T); DevView& S = h->V; const int32_t* soh = S.slotOfHost;
+	if (a->pos || a->particleType || a->PTYPE) LAUNCH(h, "download", k_dn_pack, G, T, a->pos, a->particleType, a->PTYPE, S.pos, soh, n, d_rows);
+	if (a->vel) LAUNCH(h, "download", k_dn_pack, G, T, a->vel, (int32_t*)nullptr, (int32_t*)nullptr, S.vel, soh, n, d_rows);
+	if (a->particleNearWall) LAUNCH(h, "download", k_dn_u8, G, T, a->particleNearWall, S.particleNearWall, soh, n, d_rows);
+#define X(f) if (a->f) LAUNCH(h, "download", k_dn_i32, G, T, a->f, S.f, soh, n, d_rows);
+	PMPS_I32_FIELDS(X)
+#undef X
+#define X(f) if (a->f) LAUNCH(h, "download", k_dn_f64, G, T, a->f, S.f, soh, n, d_rows);
+	PMPS_F64_FIELDS(X)
+	if (h->K.p.fluidType == 1) { PMPS_RHEO_FIELDS(X) }
+#undef X
+#define X(f) if (a->f) LAUNCH(h, "download", k_dn_v3, G, T, a->f, S.f, soh, n, d_rows);
+	PMPS_V3_FIELDS(X)
+#undef X
+	CUDA_TRY(h, cudaGetLastError());
+	return PMPS_OK;
+}
+extern "C" int pmps_upload_rows_device(pmps_t* h, const PmpsHostArrays* a, int n, const int32_t* d_rows, int numParticles) {
+	if (!h || !a || n < 0 || (n > 0 && !d_rows)) return PMPS_E_ARG;
+	cudaSetDevice(h->device);
+	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_upload_rows_device: upload a full particle table first");
+	if (numParticles < 0 || numParticles > h->numParticlesZero) return pmps_fail(h, PMPS_E_ARG, "pmps_upload_rows_device: bad numParticles");
+	const int T = 256, G = cdiv(n > 0 ? n : 1, T); DevView& S = h->V; const int32_t* soh = S.slotOfHost;
+	if (n > 0) {
+		if (a->pos || a->particleType || a->PTYPE) LAUNCH(h, "upload", k_up_pack, G, T, (const double*)a->pos, (const int32_t*)a->particleType, (const int32_t*)a->PTYPE, S.pos, soh, n, d_rows);
+		if (a->vel) LAUNCH(h, "upload", k_up_pack, G, T, (const double*)a->vel, (const int32_t*)nullptr, (const int32_t*)nullptr, S.vel, soh, n, d_rows);
+		if (a->particleNearWall) LAUNCH(h, "upload", k_up_u8, G, T, (const uint8_t*)a->particleNearWall, S.particleNearWall, soh, n, d_rows);
+#define X(f) if (a->f) LAUNCH(h, "upload", k_up_i32, G, T, (const int32_t*)a->f, S.f, soh, n, d_rows);
+		PMPS_I32_FIELDS(X)
+#undef X
+#define X(f) if (a->f) LAUNCH(h, "upload", k_up_f64, G, T, (const double*)a->f, S.f, soh, n, d_rows);
+		PMPS_F64_FIELDS(X)
+		if (h->K.p.fluidType == 1) { PMPS_RHEO_FIELDS(X) }
+#undef X
+#define X(f) if (a->f) LAUNCH(h, "upload", k_up_v3, G, T, (const double*)a->f, S.f, soh, n, d_rows);
+		PMPS_V3_FIELDS(X)
+#undef X
+	}
+	LAUNCH(h, "upload", k_set_live, 1, 1, S, numParticles);
+	CUDA_TRY(h, cudaGetLastError());
+	h->numParticles = numParticles; h->guardWorst = 0.0; h->tileWallValid = false;
+	h->hitValid = false; h->hitForce = true; h->needRebuild = true;
+	return PMPS_OK;
+}
+
 extern "C" int pmps_download(pmps_t* h, PmpsHostArrays* a) { return download_impl(h, a, false); }
 extern "C" int pmps_download_device(pmps_t* h, PmpsHostArrays* a) { return download_impl(h, a, true); }
 
@@ -237,9 +298,9 @@ extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArray
 		if (!haveLate) return;
 		cudaStreamWaitEvent(h->stream, h->evIoUp, 0);
 		DevView& S = h->V; const int32_t* soh = S.slotOfHost;
-		if (in->press) LAUNCH(h, "upload", k_up_f64, G, T, (const double*)s2, S.press, soh, n0);
-		if (in->pndi) LAUNCH(h, "upload", k_up_f64, G, T, (const double*)(s2 + 8 * (size_t)n0), S.pndi, soh, n0);
-		if (in->particleBC) LAUNCH(h, "upload", k_up_i32, G, T, (const int32_t*)(s2 + 16 * (size_t)n0), S.particleBC, soh, n0);
+		if (in->press) LAUNCH(h, "upload", k_up_f64, G, T, (const double*)s2, S.press, soh, n0, (const int32_t*)nullptr);
+		if (in->pndi) LAUNCH(h, "upload", k_up_f64, G, T, (const double*)(s2 + 8 * (size_t)n0), S.pndi, soh, n0, (const int32_t*)nullptr);
+		if (in->particleBC) LAUNCH(h, "upload", k_up_i32, G, T, (const int32_t*)(s2 + 16 * (size_t)n0), S.particleBC, soh, n0, (const int32_t*)nullptr);
 	};
 	unsigned m = 0;
 	// the first two phases read these fields with the rheology, the prediction gradient or the dynamic collisions; and a step that
@@ -257,10 +318,10 @@ extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArray
 	if (haveMid) {
 		DevView& S = h->V; const int32_t* soh = S.slotOfHost;
 		double* gp = (double*)s2; double* gn = (double*)(s2 + 8 * (size_t)n0); int32_t* gb = (int32_t*)(s2 + 16 * (size_t)n0); double* gm = (double*)(s2 + 24 * (size_t)n0);
-		if (mid.press) LAUNCH(h, "download", k_dn_f64, G, T, gp, S.press, soh, n0);
-		if (mid.pndi) LAUNCH(h, "download", k_dn_f64, G, T, gn, S.pndi, soh, n0);
-		if (mid.particleBC) LAUNCH(h, "download", k_dn_i32, G, T, gb, S.particleBC, soh, n0);
-		if (mid.mirrorParticlePos) LAUNCH(h, "download", k_dn_v3, G, T, gm, S.mirrorParticlePos, soh, n0);
+		if (mid.press) LAUNCH(h, "download", k_dn_f64, G, T, gp, S.press, soh, n0, (const int32_t*)nullptr);
+		if (mid.pndi) LAUNCH(h, "download", k_dn_f64, G, T, gn, S.pndi, soh, n0, (const int32_t*)nullptr);
+		if (mid.particleBC) LAUNCH(h, "download", k_dn_i32, G, T, gb, S.particleBC, soh, n0, (const int32_t*)nullptr);
+		if (mid.mirrorParticlePos) LAUNCH(h, "download", k_dn_v3, G, T, gm, S.mirrorParticlePos, soh, n0, (const int32_t*)nullptr);
 		cudaEventRecord(h->evIoMid, h->stream); cudaStreamWaitEvent(h->ioStream, h->evIoMid, 0);
 		if (mid.press) { cudaMemcpyAsync(mid.press, gp, 8 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
 		if (mid.pndi) { cudaMemcpyAsync(mid.pndi, gn, 8 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream); }
@@ -274,7 +335,7 @@ extern "C" int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArray
 	double* velOut = rest.vel;
 	if (velEarly) {
 		double* gv = (double*)(s2 + 48 * (size_t)n0);
-		LAUNCH(h, "download", k_dn_pack, G, T, gv, (int32_t*)nullptr, (int32_t*)nullptr, h->V.vel, h->V.slotOfHost, n0);
+		LAUNCH(h, "download", k_dn_pack, G, T, gv, (int32_t*)nullptr, (int32_t*)nullptr, h->V.vel, h->V.slotOfHost, n0, (const int32_t*)nullptr);
 		cudaEventRecord(h->evIoUp, h->stream); cudaStreamWaitEvent(h->ioStream, h->evIoUp, 0); cudaMemcpyAsync(velOut, gv, 24 * (size_t)n0, cudaMemcpyDeviceToHost, h->ioStream);
 		rest.vel = nullptr; mid.vel = velOut;
 	}
