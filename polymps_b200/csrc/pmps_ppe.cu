@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_init_p(const __grid_constant__ De
 // t = A^T p ; partial sums of p.t
 __global__ void __launch_bounds__(PPE_T) k_ppe_spmv(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks) {
 	__shared__ double sh[PPE_T / 32];
+	if (M.scal[14] != 0.0) return;   // (one-GPU batches: converged earlier in the batch)
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	double v = 0.0;
 	if (i < S.n) { const double t = ell_row_dot(S, M, i, M.p); M.t[i] = t; if (owned_slot(S, i)) v = M.p[i] * t; }
@@ -142,6 +143,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_spmv(const __grid_constant__ DevV
 // x += alpha p ; r -= alpha t ; partial sums of |r|^2 and r.(M^-1 r)
 __global__ void __launch_bounds__(PPE_T) k_ppe_update_xr(const __grid_constant__ DevView S, const __grid_constant__ PpeView M, int nBlocks) {
 	__shared__ double sh[PPE_T / 32];
+	if (M.scal[14] != 0.0) return;
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	const double alpha = M.scal[5];
 	double r2 = 0.0, rz = 0.0;
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_update_xr(const __grid_constant__
 // p = M^-1 r + beta p
 __global__ void __launch_bounds__(PPE_T) k_ppe_update_p(const __grid_constant__ DevView S, const __grid_constant__ PpeView M) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= S.n) return;
+	if (i >= S.n || M.scal[14] != 0.0) return;
 	const double beta = M.scal[6]; const double d = M.diag[i];
 	M.p[i] = (d != 0.0 ? 1.0 / d : 1.0) * M.r[i] + beta * M.p[i];
 }
@@ -180,6 +182,26 @@ __global__ void k_ppe_recur(const __grid_constant__ PpeView M, int mode, const d
 	else { s[1] = sa; s[3] = s[2]; s[2] = sb; s[6] = sb / s[3]; }
 	hostMirror[0] = s[0]; hostMirror[1] = s[1]; hostMirror[2] = s[7];
 }
+// ---- one GPU: second stage of the dot products + the scalar recurrence of Eigen's CG (ConjugateGradient.h:50-89) in ONE block of 1024
+// threads, and the convergence test on the device: once the residual is below the threshold (scal[14] = 1) the remaining launches of
+// a batch return at once, so the host reads the state back once per batch of iterations instead of synchronising in every one.
+// 5 launches per iteration instead of 7, no per-iteration host round trip.  scal[15] counts the iterations.
+#define RR_T 1024
+__global__ void __launch_bounds__(RR_T) k_cg_reduce_recur(const __grid_constant__ PpeView M, int nBlocks, int mode) {
+	__shared__ double sh[RR_T / 32];
+	if (M.scal[14] != 0.0) return;
+	double a = 0.0, b = 0.0;
+	for (int k = threadIdx.x; k < nBlocks; k += RR_T) { a += M.partial[k]; if (mode == 3) b += M.partial[nBlocks + k]; }
+	const double sa = block_sum<RR_T>(a, sh); const double sb = block_sum<RR_T>(b, sh);
+	if (threadIdx.x != 0) return;
+	double* s = M.scal;
+	if (mode == 2) { s[4] = sa; s[5] = s[2] / sa; }   // alpha = absNew / p.Ap (:73)
+	else {
+		s[1] = sa; s[3] = s[2]; s[2] = sb; s[6] = sb / s[3];   // |r|^2 ; absOld ; absNew ; beta (:77-86)
+		if (sa < s[7] || !(sa == sa)) s[14] = 1.0; else s[15] += 1.0;   // :78 "if(residualNorm2 < threshold) break" comes before "i++"
+	}
+}
+
 // press = max(pressurePPE, 0)  (setZeroOnNegativePressure acts on press only, src/MpsPressure.cpp:471-476)
 __global__ void k_ppe_finish(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int zeroX) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -348,7 +370,26 @@ int pmps_ppe_solve(pmps_handle* h) {
 			LAUNCH(h, "ppe.init_p", k_ppe_init_p, nBlocks, PPE_T, S, M, nBlocks);
 			REDUCE(1, 1);
 			const long long maxIt = 2ll * h->numParticles;
-			while (iters < maxIt) {
+			if (!slab && !getenv("PMPS_CG_HOST_LOOP")) {
+				// one GPU: reductions fused into the producing kernels, convergence tested on the device, one read-back per batch
+				CUDA_TRY(h, cudaMemsetAsync(M.scal + 14, 0, 2 * sizeof(double), h->stream));   // done flag, iteration count
+				const int batch = 6;
+				while (true) {
+					for (int k = 0; k < batch; k++) {
+						LAUNCH(h, "ppe.spmv", k_ppe_spmv, nBlocks, PPE_T, S, M, nBlocks);
+						LAUNCH(h, "ppe.reduce", k_cg_reduce_recur, 1, RR_T, M, nBlocks, 2);
+						LAUNCH(h, "ppe.update_xr", k_ppe_update_xr, nBlocks, PPE_T, S, M, nBlocks);
+						LAUNCH(h, "ppe.reduce", k_cg_reduce_recur, 1, RR_T, M, nBlocks, 3);
+						LAUNCH(h, "ppe.update_p", k_ppe_update_p, nBlocks, PPE_T, S, M);
+					}
+					CUDA_TRY(h, cudaMemcpyAsync(hm, M.scal + 1, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+					CUDA_TRY(h, cudaMemcpyAsync(hm + 1, M.scal + 14, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+					CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+					res2 = hm[0]; iters = (int)hm[2];
+					if (hm[1] != 0.0 || iters >= maxIt) break;
+				}
+			}
+			else while (iters < maxIt) {
 				if (slab) h->slabRefresh(h->slabUser, PMPS_HF_PPE_P);   // the halo copies' p before the matrix-vector product
 				LAUNCH(h, "ppe.spmv", k_ppe_spmv, nBlocks, PPE_T, S, M, nBlocks);
 				REDUCE(2, 1);
