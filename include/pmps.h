@@ -225,6 +225,16 @@ typedef void (*pmps_sum_fn)(void* user, int n);
 typedef void (*pmps_refresh_fn)(void* user, unsigned fields);
 int pmps_slab_set_hooks(pmps_t* h, double* d_workspace8, pmps_sum_fn sum, pmps_refresh_fn refresh, void* user);                  /* 1: re-partition (migrate + new halo) and re-upload before the next step */
 
+/* ---- integrated observables on the device (north_star: surge-front position and pressure-probe history of a dam break) -----------
+ * The reference samples on the host: its pressure sensors average the pressure of the particles inside a window
+ * (src/MpsInputOutput.cpp:1937-2229) and every output step writes all arrays (:861-1875).  These two calls reduce on the device —
+ * one pass over the position records, two-stage reductions in a fixed order — so a run records its history without a particle
+ * array leaving the GPU.  On a slab rank they cover the OWNED particles; the caller combines the ranks (MIN / MAX / SUM).
+ * pmps_observe_extent: bounding box and count of the particles of one type (surge front = mx[0] of the fluid);
+ * pmps_observe_box: count, pressure sum and pressure maximum of the particles of one type inside [lo, hi] (probe = sum / count). */
+int pmps_observe_extent(pmps_t* h, int particleType, double mn[3], double mx[3], long long* count);
+int pmps_observe_box(pmps_t* h, int particleType, const double lo[3], const double hi[3], long long* count, double* pressSum, double* pressMax);
+
 /* ---- debug / parity hooks (tests only) ---------------------------------------------------------------------- */
 /* bucket id of every host-order particle as the reference computes it at rebuild time, and the members of every
  * bucket in list order (= ascending host index): flattened CSR. members may be NULL to query sizes. */

@@ -89,6 +89,9 @@ def load_library() -> ctypes.CDLL:
     if os.environ.get("PMPS_LIB") is None or hasattr(L, "pmps_set_stale_list_replay"):   # (an older experimental build named by PMPS_LIB may lack them)
         L.pmps_set_stale_list_replay.argtypes = [ctypes.c_void_p, ctypes.c_int]
         L.pmps_debug_set_stale.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]
+    if os.environ.get("PMPS_LIB") is None or hasattr(L, "pmps_observe_extent"):
+        L.pmps_observe_extent.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong)]
+        L.pmps_observe_box.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
     L.pmps_set_mesh.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_int,
                                 ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_double), ctypes.c_int,
                                 ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
@@ -222,6 +225,20 @@ class Engine:
 
     def set_stale_list_replay(self, on: bool):
         self._chk(self.lib.pmps_set_stale_list_replay(self.h, 1 if on else 0))
+
+    # ---- integrated observables, reduced on the device (pmps_observe_*)
+    def observe_extent(self, particle_type: int):
+        """(min xyz, max xyz, count) of the particles of one type; surge front of a dam break = max x of the fluid."""
+        mn = (ctypes.c_double * 3)(); mx = (ctypes.c_double * 3)(); n = ctypes.c_longlong()
+        self._chk(self.lib.pmps_observe_extent(self.h, int(particle_type), mn, mx, ctypes.byref(n)))
+        return np.array(mn[:]), np.array(mx[:]), int(n.value)
+
+    def observe_box(self, particle_type: int, lo, hi):
+        """(count, pressure sum, pressure max) of the particles of one type inside the box [lo, hi]; probe pressure = sum / count."""
+        a = (ctypes.c_double * 3)(*[float(v) for v in lo]); b = (ctypes.c_double * 3)(*[float(v) for v in hi])
+        n = ctypes.c_longlong(); s = ctypes.c_double(); m = ctypes.c_double()
+        self._chk(self.lib.pmps_observe_box(self.h, int(particle_type), a, b, ctypes.byref(n), ctypes.byref(s), ctypes.byref(m)))
+        return int(n.value), float(s.value), float(m.value)
 
     # ---- parity hooks
     def set_stale(self, host_idx, bucket):

@@ -119,8 +119,22 @@ void pull_scalars() {   // what displayInfo and the host loop read
 	g_P->numParticles = s.numParticles; g_S->velMax = s.velMax; g_S->CFLcurrent = s.CFLcurrent;
 	if (g_S->fluidType == viscType::NON_NEWTONIAN) g_S->CFLvisc = s.CFLvisc;
 }
-void pull_arrays() {    // before writeOutputFiles
-	PmpsHostArrays a = host_arrays(g_P);
+// Before writeOutputFiles: only what the reference's writers read comes back from the device — the union over the output flags
+// (private members of MpsInputOutput, not visible from here) of the arrays writeVtuAscii / writeVtuBinary / writeVtuAsciiFreeSurface
+// touch (src/MpsInputOutput.cpp:861-1875): positions, velocities, pressure, boundary flags, both number densities, neighbour count,
+// NPCD deviation, polygon normal, concentration and its gradient, particle / mesh types, and the rheology fields of a non-Newtonian
+// run: 168 of the 585 bytes per particle the full state has.  PMPS_SHIM_PULL_ALL=1 brings everything back (debugging).
+void pull_arrays() {
+	PmpsHostArrays all = host_arrays(g_P), a;
+	if (getenv("PMPS_SHIM_PULL_ALL")) a = all;
+	else {
+		memset(&a, 0, sizeof a); a.numParticles = all.numParticles; a.numParticlesZero = all.numParticlesZero;
+#define F(n) a.n = all.n;
+		F(pos) F(vel) F(press) F(particleBC) F(pndi) F(pndSmall) F(numNeigh) F(npcdDeviation) F(polygonNormal) F(concentration) F(gradConcentration)
+		F(particleType) F(nearMeshType) F(PTYPE)
+		if (g_S->fluidType == viscType::NON_NEWTONIAN) { F(RHO) F(Cv) F(MEU) F(MEU_Y) F(II) F(p_smooth) F(Inertia) F(p_rheo_new) F(VF) }
+#undef F
+	}
 	CALL(pmps_download(g_h, &a));
 	g_P->numParticles = a.numParticles;
 }

@@ -277,6 +277,12 @@ def test_integrated_observables_over_a_run():
         orc.step(25); eng.step(25); eng.download(got, ["pos", "press", "particleType"])
         fg, pg, ng = _observables(got, ps, px, pz); fw, pw, nw = _observables(want, ps, px, pz)
         hist.append((fg, fw, pg, pw))
+        # the same two observables reduced on the device (pmps_observe_*): no array download needed for a history
+        mn, mx, nf = eng.observe_extent(ps.fluid)
+        big = 1e9
+        nb, psum, pmax = eng.observe_box(ps.fluid, [px - 2.0 * ps.partDist, -big, pz - 2.0 * ps.partDist], [px + 2.0 * ps.partDist, big, pz + 2.0 * ps.partDist])
+        assert mx[0] == fg and nf == int((got.particleType[:got.numParticles] == ps.fluid).sum())
+        assert nb == ng and abs(psum / nb - pg) <= 1e-12 * max(abs(pg), pscale)
         assert ng == nw and ng > 0
         assert abs(fg - fw) <= 1e-9 * abs(fw), "step %d: surge front %r vs %r" % (25 * (k + 1), fg, fw)
         assert abs(pg - pw) <= 1e-6 * pscale, "step %d: probe pressure %r vs %r (scale %g)" % (25 * (k + 1), pg, pw, pscale)
