@@ -335,7 +335,7 @@ def main_gpu_slab(args, rank, world, local):
                        "bucket_rebuilds": c1["bucket_rebuilds"] - c0["bucket_rebuilds"], "hit_refilters": c1["hit_refilters"] - c0["hit_refilters"],
                        "particles_total": int(total), "build_id": build_id(), "parallelism": "%d x-slabs cut on bucket columns, one rank per GPU; halo refresh after every phase + migration at rebuilds over NCCL send/recv; 3 scalars MAX-all-reduced per step" % world,
                        "l2": "state per GPU (%.1f GB) is far larger than the 126 MB L2; no flush needed" % (se.dom.n_live * 1500 / 1e9),
-                       "ranks": per_rank, "max_displacement_over_lo": sc.maxDisplacement / ps.partDist},
+                       "host_binding": args.cpu_binding, "ranks": per_rank, "max_displacement_over_lo": sc.maxDisplacement / ps.partDist},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline}
     if rank == 0:
         print(json.dumps(line), flush=True)
@@ -346,10 +346,31 @@ def main_gpu_slab(args, rank, world, local):
     dist.destroy_process_group()
 
 
+def bind_to_gpu_numa_node(local):
+    """Pins this process to the CPU cores NVML names as local to its GPU, BEFORE any pinned host buffer is allocated: the pages of the
+    end-to-end leg's host tables then sit on the NUMA node whose PCIe root the GPU hangs off (first touch), instead of wherever the
+    launcher happened to start the rank.  Returns a short description for the JSON line (None when NVML has nothing to say)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return "%d cores local to GPU %d (NVML)" % (len(cpus), local)
+    except Exception:
+        pass
+    return None
+
+
 def main_gpu(args):
     import torch
     import torch.distributed as dist
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    args.cpu_binding = bind_to_gpu_numa_node(local) if world > 1 else None   # (one GPU: the CPU baseline leg wants all cores)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if not torch.cuda.is_available():

@@ -302,7 +302,7 @@ static int ensure_capacity(pmps_handle* h, int n0) {
 	S.listCap = cap;   // the global-slot list itself is allocated on first use (pmps_ensure_list)
 	// tile-local list: whole chunks of 64 entries; staging capacity from the shared-memory budget of the fattest pass
 	S.tlCap = ((cap + TV_CHUNK - 1) / TV_CHUNK) * TV_CHUNK; if (S.tlCap > 255 * TV_CHUNK) S.tlCap = 255 * TV_CHUNK;
-	rc |= dalloc(h, &S.hlist, (size_t)n0 * (size_t)S.tlCap); rc |= dalloc(h, &S.hcnt, n0);
+	rc |= dalloc(h, &S.hlist, (size_t)n0 * (size_t)S.tlCap); rc |= dalloc(h, &S.hcnt, n0); rc |= dalloc(h, &S.clist, (size_t)n0 * PMPS_CLOSE_CAP); rc |= dalloc(h, &S.ccnt, n0);
 	K.tvMaxM = TV_MAXM;   // follow passes; a scanning pass of the fattest pack gets one block per SM
 	if (K.tvMaxM > 65534) K.tvMaxM = 65534;
 	if (const char* e = getenv("PMPS_TILE_MAXM")) { const int v = atoi(e); if (v > 0 && v < K.tvMaxM) K.tvMaxM = v; }   // tests: force the split path

@@ -42,6 +42,8 @@ struct DevView {
 	                                     // [0] entries, [1 .. CAP] host label (-1: dead), [1 + CAP .. 2 CAP] the bucket its array element sits in (hid_visible())
 	int32_t* cellStart;                  // nC+2, slots of cell c (tile-major bucket index, cell_index()) are [cellStart[c], cellStart[c+1]); cell nC = ghosts
 	uint32_t* list; uint16_t* listCnt;   // Verlet candidates (slot ids), row-major, listCap per particle; built on demand
+	uint32_t* clist; uint8_t* ccnt;      // close-pair list of every fluid slot (k_hl_build): GLOBAL slots of the neighbours within closeR when the hit list was
+	                                       // made, PMPS_CLOSE_CAP per slot; ccnt 255 = more than that (the collision kernel then searches the buckets itself)
 	uint16_t* hlist; uint16_t* hcnt;       // hit list (pmps_tv.cuh, k_hl_build): the staged records within reach at the positions of the current epoch, tlCap entries
 	                                       // per slot in chunks of 64 (tv_list_pos), as 16-bit indices into the staged halo of the slot's work item; entries used
 	uint8_t* particleNearWall;
@@ -96,6 +98,7 @@ struct DevView {
 enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, FLAG_UPLOAD_TYPES = 7, NFLAGS = 8 };
 #define PMPS_OOD_CAP 65536
 #define PMPS_HID_CAP 1024    // particles moved into a hole by the out-of-domain swap within one step
+#define PMPS_CLOSE_CAP 16 // close-pair list entries per slot (collision pass)
 #define PMPS_CURSORS 64   // work-stealing cursors per step (one per tile-walker launch)
 
 // Kernel-side parameters: the ABI params plus derived constants
@@ -203,6 +206,7 @@ int pmps_sort_and_list(pmps_handle* h);
 int pmps_ensure_list(pmps_handle* h);
 int pmps_tv_prepare(pmps_handle* h);
 int pmps_tv_hits(pmps_handle* h);
+int pmps_collide_lists(pmps_handle* h);   // pmps_collide.cu: the PC collision model from the close-pair lists (dvel + vel2 = vel + dvel)
 void pmps_set_hit_delta(pmps_handle* h, double delta);
 int pmps_ppe_solve(pmps_handle* h);
 int pmps_step_end_host(pmps_handle* h);   // step_end of the fused step + the time advance (pmps_stages.inc), for pmps_step_host

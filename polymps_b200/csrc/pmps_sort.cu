@@ -263,7 +263,7 @@ static int ilog2_ceil(int n) { int b = 0; while ((1 << b) < n) b++; return b; }
 static int launch_hl_build(pmps_handle* h, const char* name, int force) {
 	DevView& S = h->V;
 	if (h->walkSeq >= PMPS_CURSORS) return pmps_fail(h, PMPS_E_STATE, "more than %d tile passes since the last pmps_update_buckets", PMPS_CURSORS - 1);
-	const size_t smem = 16 * (size_t)(TV_MAXM + 4) + (size_t)HL_T * HL_ROW * 2;   // float positions (+ the dummy record) + the first chunk of one list row per lane
+	const size_t smem = 16 * (size_t)(TV_MAXM + 4) + (size_t)HL_T * HL_ROW * 2 + 4 * (size_t)(TV_MAXM + 4);   // float positions (+ the dummy record) + the first chunk of one list row per lane + staged index -> slot
 	CUDA_TRY(h, cudaFuncSetAttribute(k_hl_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 	{ ProfScope ps_(h, name); k_hl_build<<<h->smCount * 5, HL_T, smem, h->stream>>>(S, h->K, h->walkSeq++, force); h->launches++; }
 	CUDA_TRY(h, cudaGetLastError());

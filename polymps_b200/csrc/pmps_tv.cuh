@@ -300,7 +300,7 @@ __device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, con
 }
 // float positions (+ type word) of the halo for the list build
 template <int NT>
-__device__ __forceinline__ void tv_stage_float(const DevView& S, float4* fpos, const int* hOff, const int* hBase, int HV, double ox, double oy, double oz) {
+__device__ __forceinline__ void tv_stage_float(const DevView& S, float4* fpos, int32_t* slotOf, const int* hOff, const int* hBase, int HV, double ox, double oy, double oz) {
 	constexpr int NB = 4;   // buckets per thread whose position loads are in flight together
 	constexpr int NW = NT / 32;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -313,13 +313,13 @@ __device__ __forceinline__ void tv_stage_float(const DevView& S, float4* fpos, c
 			if (hb < HV) { const int off = hOff[hb]; ok[b] = lane < hOff[hb + 1] - off; m[b] = off + lane; if (ok[b]) p[b] = ld256(S.pos + hBase[hb] + lane); }
 		}
 		#pragma unroll
-		for (int b = 0; b < NB; b++) if (ok[b]) fpos[m[b]] = make_float4((float)(p[b].x - ox), (float)(p[b].y - oy), (float)(p[b].z - oz), tv_type_word(p[b]));
+		for (int b = 0; b < NB; b++) if (ok[b]) { fpos[m[b]] = make_float4((float)(p[b].x - ox), (float)(p[b].y - oy), (float)(p[b].z - oz), tv_type_word(p[b])); slotOf[m[b]] = hBase[hb0 + b * NW] + lane; }
 		#pragma unroll
 		for (int b = 0; b < NB; b++) {   // buckets with more than 32 particles (far above the lattice density)
 			const int hb = hb0 + b * NW;
 			if (hb >= HV) continue;
 			const int off = hOff[hb], n = hOff[hb + 1] - off, s0 = hBase[hb];
-			for (int r = lane + 32; r < n; r += 32) { const double4 q = ld256(S.pos + s0 + r); fpos[off + r] = make_float4((float)(q.x - ox), (float)(q.y - oy), (float)(q.z - oz), tv_type_word(q)); }
+			for (int r = lane + 32; r < n; r += 32) { const double4 q = ld256(S.pos + s0 + r); fpos[off + r] = make_float4((float)(q.x - ox), (float)(q.y - oy), (float)(q.z - oz), tv_type_word(q)); slotOf[off + r] = s0 + r; }
 		}
 	}
 }
@@ -351,8 +351,10 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 	float4* const fpos = (float4*)smemRaw;
 	const int cap = S.tlCap;
 	const int tid = threadIdx.x, lane = tid & 31, w0 = tid & ~31;
-	uint16_t* const rows = (uint16_t*)(smemRaw + 16 * (size_t)TV_MAXM);
+	uint16_t* const rows = (uint16_t*)(smemRaw + 16 * (size_t)(TV_MAXM + 4));
 	uint16_t* const row = rows + (size_t)tid * HL_ROW;
+	int32_t* const slotOf = (int32_t*)(smemRaw + 16 * (size_t)(TV_MAXM + 4) + (size_t)HL_T * HL_ROW * 2);   // staged index -> global slot (close-pair lists)
+	const float C2 = K.closeR2;
 	const bool three = K.p.dim == 3;
 	const int nItems = *S.nTiles;
 	const float R2 = K.hitR2;
@@ -372,7 +374,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		tv_stage_float<HL_T>(S, fpos, hOff, hBase, b.HV, ox, oy, oz);
+		tv_stage_float<HL_T>(S, fpos, slotOf, hOff, hBase, b.HV, ox, oy, oz);
 		if (tid == 0) fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the far-away dummy record: what a lane reads beyond the end of its stretch
 		if (nHidAll > 0) {   // which staged records of this item are hidden entries (S.hid)?  One thread per entry.
 			if (tid == 0) sHid.n = 0;
@@ -446,6 +448,16 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 					}
 				}
 			}
+			// close pairs (the collision pass needs nothing else, pmps_collide.cu): the first-chunk hits within closeR, as GLOBAL slots
+			int nClose = 0;
+			if (act && (int)(short)(__float_as_int(fi.w) & 0xffff) == K.p.fluid) {
+				const int ne = min(cnt, TV_CHUNK);
+				for (int e = 0; e < ne; e++) {
+					const int mm = row[e]; const float4 f = fpos[mm];
+					const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
+					if (dx * dx + dy2 * dy2 + dz2 * dz2 < C2) { if (nClose < PMPS_CLOSE_CAP) S.clist[(size_t)i * PMPS_CLOSE_CAP + nClose] = (uint32_t)slotOf[mm]; nClose++; }
+				}
+			}
 			if (cnt > TV_CHUNK) {   // second sweep (divergent, rare): entries 64, 65, ... in the walker's order, then the padding of the last chunk
 				uint16_t* const grow = S.hlist + (size_t)i * (size_t)cap;
 				int c2 = 0;
@@ -456,14 +468,18 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 						const float4 f = fpos[mm]; const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
 						bool hit = dx * dx + dy2 * dy2 + dz2 * dz2 < R2;
 						if (HID && hit) for (int q = 0; q < nHid; q++) if (sHid.m[q] == mm && !hid_visible(K, sHid.cell[q], S.pos[i])) hit = false;
-						if (hit) { if (c2 >= TV_CHUNK && c2 < cap) grow[tv_list_pos(c2)] = (uint16_t)mm; c2++; }
+						if (hit) {
+							if (c2 >= TV_CHUNK && c2 < cap) grow[tv_list_pos(c2)] = (uint16_t)mm;
+							if (c2 >= TV_CHUNK && dx * dx + dy2 * dy2 + dz2 * dz2 < C2) { if (nClose < PMPS_CLOSE_CAP) S.clist[(size_t)i * PMPS_CLOSE_CAP + nClose] = (uint32_t)slotOf[mm]; nClose++; }
+							c2++;
+						}
 					}
 				}
 				for (int e = min(cnt, cap); (e & (TV_CHUNK - 1)) != 0; e++) grow[tv_list_pos(e)] = (uint16_t)M;
 			}
 			if (act) {
 				if (cnt > cap) { atomicMax(&S.flags[FLAG_OVERFLOW], cnt); cnt = cap; }
-				S.hcnt[i] = (uint16_t)cnt;
+				S.hcnt[i] = (uint16_t)cnt; S.ccnt[i] = (uint8_t)(nClose > PMPS_CLOSE_CAP ? 255 : nClose);
 				S.hpos[i] = make_float4(fi.x + (float)(ox - K.p.domainMinX), fi.y + (float)(oy - K.p.domainMinY), fi.z + (float)(oz - (three ? K.p.domainMinZ : 0.0)), 0.f);
 			} else cnt = 0;
 			__syncwarp();
@@ -570,17 +586,48 @@ __device__ __forceinline__ void tv_pair2(typename F::Ctx& ctx, const TvStage& T,
 	if (hb) F::template pair<POLY>(ctx, T.nb, K, s, b);
 }
 // The first chunk (64 entries, 128 bytes) of the hit lists of one round on its way into shared memory.  Every WARP fetches the rows
-// of its own lane groups (8 rows x 8 pieces of 16 bytes, two per lane) and is the only one to read them: a round needs no block
-// barrier, and because a lane group takes its row into registers at the start of the round, the next round's rows can land in the
-// same buffer while the round computes.  One commit group.
-__device__ __forceinline__ void tv_fetch_rows(const DevView& S, unsigned char* rowsBuf, int own0, int p0, int P) {
+// of its own lane groups and is the only one to read them: a round needs no block barrier, and because a lane group takes its row
+// into registers at the start of the round, the next round's rows can land in the same buffer while the round computes.
+// A row is 128 contiguous, 128-byte aligned bytes of global memory: ONE bulk copy of the TMA unit per row (cp.async.bulk, SASS
+// UBLKCP), completing on the warp's mbarrier — 8 instructions per warp and round instead of 64 16-byte cp.async.  (The staged
+// halo cannot travel that way: a bucket's stretch of an 8-byte plane starts at an arbitrary slot, i.e. is 8-byte aligned, and the
+// 32-byte position records would land as an array of structures whose 128-bit reads conflict two ways on the banks; they go as
+// 16-byte / 8-byte cp.async, tv_stage.)
+#ifndef TV_ROWS_TMA
+#define TV_ROWS_TMA 0   // measured on the B200 (10 M particles, A/B on one box): every walker pass 4-6 % SLOWER with the bulk copies + mbarrier wait than
+                      // with the 16-byte cp.async it replaces (F3 5.71 -> 6.07 ms, F1 4.59 -> 4.79, F5 2.82 -> 2.96): kept as an option, off
+#endif
+__device__ __forceinline__ void tv_bar_init(uint64_t* bar) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void tv_bar_wait(uint64_t* bar, unsigned phase) {
+	asm volatile("{\n\t.reg .pred P1;\n\tTV_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t@P1 bra TV_DONE;\n\tbra TV_WAIT;\n\tTV_DONE:\n\t}"
+	             :: "r"((unsigned)__cvta_generic_to_shared(bar)), "r"(phase) : "memory");
+}
+// returns true when the warp has rows on their way (it must then wait for them at the start of the round that uses them)
+__device__ __forceinline__ bool tv_fetch_rows(const DevView& S, unsigned char* rowsBuf, uint64_t* bar, int own0, int p0, int P) {
 	const int lane = threadIdx.x & 31, g0 = (threadIdx.x >> 5) * (32 / TV_G);
+#if TV_ROWS_TMA
+	const int nrows = min(32 / TV_G, P - (p0 + g0));   // rows of this warp in the round (uniform over the warp)
+	if (nrows <= 0) return false;
+	const unsigned barS = (unsigned)__cvta_generic_to_shared(bar);
+	if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(barS), "r"((unsigned)(nrows * TV_CHUNK * 2)) : "memory");
+	__syncwarp();
+	if (lane < nrows) {
+		const unsigned dst = (unsigned)__cvta_generic_to_shared(rowsBuf + (size_t)(g0 + lane) * TV_LROW);
+		const void* src = S.hlist + (size_t)(own0 + p0 + g0 + lane) * (size_t)S.tlCap;
+		asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" :: "r"(dst), "l"(src), "r"((unsigned)(TV_CHUNK * 2)), "r"(barS) : "memory");
+	}
+	return true;
+#else
 	#pragma unroll
 	for (int q = lane; q < (32 / TV_G) * (TV_CHUNK * 2 / 16); q += 32) {
 		const int r = q >> 3, c = q & 7, p = p0 + g0 + r;
 		if (p < P) tv_cp16(rowsBuf + (size_t)(g0 + r) * TV_LROW + c * 16, (const unsigned char*)(S.hlist + (size_t)(own0 + p) * (size_t)S.tlCap) + c * 16);
 	}
 	asm volatile("cp.async.commit_group;" ::: "memory");
+	return true;
+#endif
 }
 
 // Every lane group takes its particle's HIT list (k_hl_build: the staged records within reach at the positions of the current
@@ -592,8 +639,16 @@ template <bool POLY, unsigned FIELDS, bool WALLONLY, bool SPARSE, class F>
 __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx) {
 	extern __shared__ __align__(16) unsigned char smemRaw[];
 	__shared__ int sTab[TV_TABMAX], sItem;
+	__shared__ __align__(8) uint64_t sRowBar[TV_T / 32];   // one mbarrier per warp: its list rows have landed
 	const TvStage T = tv_carve<FIELDS>(smemRaw);
 	const int tid = threadIdx.x, grp = tid / TV_G, g = tid % TV_G;
+	uint64_t* const rowBar = sRowBar + (tid >> 5);
+	unsigned rowPhase = 0u;   // parity of the warp's next completed row fetch (uniform over the warp)
+#if TV_ROWS_TMA
+	if ((tid & 31) == 0) tv_bar_init(rowBar);
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	__syncthreads();
+#endif
 	unsigned char* const fx = smemRaw + (size_t)TV_MAXM * tv_rec_bytes(FIELDS);
 	unsigned char* const rowsBuf = fx;                                       // TV_NG list rows of TV_LROW bytes
 	uint16_t* const ownMap = (uint16_t*)(fx + TV_NG * TV_LROW);          // own particle -> staged index
@@ -643,7 +698,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		tv_fetch_rows(S, rowsBuf, own0, 0, P);   // first round's lists on their way while the staging loads land
+		bool rowsComing = tv_fetch_rows(S, rowsBuf, rowBar, own0, 0, P);   // first round's lists on their way while the staging loads land
 		for (int p = tid; p < P; p += TV_T) {     // per-particle scalars of the whole item, independent loads issued together with the staging
 			sCnt[p] = S.hcnt[own0 + p];
 			if (POLY) sHas[p] = S.distParticleWall2[own0 + p] < K.mirrorFar2 ? 1 : 0;
@@ -654,13 +709,17 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 		const uint4* const Ls = (const uint4*)(rowsBuf + (size_t)grp * TV_LROW) + g * (TV_PER / 8);   // this lane's part of its group's row
 		// ---- rounds of TV_NG particles; control flow stays uniform over a warp (full-mask shuffles) ----
 		for (int p0 = 0; p0 < P; p0 += TV_NG) {
+#if TV_ROWS_TMA
+			if (rowsComing) { tv_bar_wait(rowBar, rowPhase); rowPhase ^= 1u; }   // this warp's rows of the round have landed
+#else
 			asm volatile("cp.async.wait_group 0;" ::: "memory");
-			__syncwarp();   // this warp's rows of the round have landed
+			__syncwarp();
+#endif
 			unsigned w[TV_PER / 2];   // chunk 0 of the list: this lane's entries, into registers
 			#pragma unroll
 			for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = Ls[v]; w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
-			__syncwarp();
-			if (p0 + TV_NG < P) tv_fetch_rows(S, rowsBuf, own0, p0 + TV_NG, P);   // next round's rows land while this round computes
+			{ unsigned t_ = w[TV_PER / 2 - 1] ^ w[0]; t_ = __shfl_xor_sync(0xffffffffu, t_, 1); asm volatile("" :: "r"(t_)); }   // every lane HAS its words before the buffer is reused
+			rowsComing = p0 + TV_NG < P ? tv_fetch_rows(S, rowsBuf, rowBar, own0, p0 + TV_NG, P) : false;   // next round's rows land while this round computes
 			const int p = p0 + grp;
 			bool act = p < P;
 			const int i = own0 + (act ? p : 0);

@@ -16,13 +16,3 @@ for tag in ["weak","50M","200M"]:
     d=load("gpurun_out/r02_%s_n$N.json"%tag)
     if d: print(tag, "N=$N ms/step %.2f value %.4g e2e %.4g rebuilds %s refilters %s"%(d["ms_per_step"], d["value"], d["e2e"]["value"], d["config"]["bucket_rebuilds"], d["config"]["hit_refilters"]), [ (r["owned"], r["halo"], r["repartitions"], r["migrants_out"]) for r in d["config"]["ranks"]])
 PY
-PMPS_SLAB_TIMING=1 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $P bench.py --gpus $N --steps 4 --warmup 5 --e2e-steps 1 --profile-steps 1 > gpurun_out/r02_timing_n$N.log 2>&1
-grep "\[slab\] repartition" gpurun_out/r02_timing_n$N.log | tail -7
-python - <<'PY'
-import re,collections
-t=collections.defaultdict(float); n=0
-for l in open("gpurun_out/r02_timing_n$N.log"):
-    m=re.match(r"\[slab\] phase (\d+): kernels ([\d.]+) ms, refresh ([\d.]+) ms", l)
-    if m: t["k"]+=float(m.group(2)); t["r"]+=float(m.group(3)); n+= (m.group(1)=="9")
-print("per step (synchronised): kernels %.1f ms, refreshes %.1f ms over %d steps"%(t["k"]/max(n,1), t["r"]/max(n,1), n))
-PY
