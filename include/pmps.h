@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define PMPS_ABI_VERSION 2
+#define PMPS_ABI_VERSION 3
 
 enum { PMPS_OK = 0, PMPS_E_ARG = -1, PMPS_E_CUDA = -2, PMPS_E_STATE = -3, PMPS_E_UNSUPPORTED = -4, PMPS_E_OVERFLOW = -5 };
 
@@ -41,7 +41,7 @@ typedef struct PmpsParams {
 	int32_t gradientType;           /* 0..3 (src/MpsPressure.cpp:1288-1300) */
 	int32_t gradientCorrection;     /* bool */
 	int32_t slipCondition;          /* 0 no-slip, 1 free-slip */
-	int32_t freeSurfType;           /* 0 PND+neigh, 1 PND+NPCD, 2 ARC */
+	int32_t freeSurfType;           /* 0 PND+neigh, 1 PND+NPCD, 2 PND+ARC (particle normals + arc test, src/MpsBoundaryCondition.cpp:205-390) */
 	int32_t collisionType;          /* 0 PC, 1 DPC */
 	int32_t shiftingType;           /* 0 off, 1 DW*Uij, 2 grad C */
 	int32_t repulsiveForceType;     /* 0 Harada 1 Mitsume 2 Lennard-Jones 3 Monaghan-Kajtar */
@@ -79,6 +79,8 @@ typedef struct PmpsParams {
 	double KNM_VS1, KNM_VS2, DNS_SDT, PHI_1, PHI_2, cohes, MEU0, DG, I0, mm, Cd, VF_min, VF_max;
 	double relaxPND;                /* semi_implicit_mps.source_term.relax_pnd: the divergence part of the IMPLICIT_PND_DIVU source (src/MpsPressure.cpp:373) */
 	double timeCurrent;             /* time at pmps_create; the fused step advances its own copy by timeStep (src/main.cpp:463) */
+	/* ARC free-surface detection (freeSurfType 2), src/MpsParticle.cpp:219-222 */
+	double thetaArc, hThreshold2, dstThreshold2, normThreshold2;
 } PmpsParams;
 
 /* Pointers into the host's MpsParticle arrays (include/MpsParticle.h:139-241); NULL = not transferred. */
@@ -93,6 +95,7 @@ typedef struct PmpsHostArrays {
 	double *pos, *vel, *acc, *accStar, *npcdDeviation, *gradConcentration;
 	double *correcMatrixRow1, *correcMatrixRow2, *correcMatrixRow3;
 	double *particleAtWallPos, *mirrorParticlePos, *polygonNormal, *forceWall, *dvelCollision;
+	double *normal;                 /* particle normal of the ARC free-surface detection (src/MpsShifting.cpp:106-174,319-429) */
 	/* non-Newtonian fields (allocated by the reference only when fluidType == 1, src/MpsInputOutput.cpp:729-744) */
 	double *Cv, *II, *MEU_Y, *Inertia, *p_rheo_new, *p_smooth, *VF, *S11, *S12, *S13, *S22, *S23, *S33;
 } PmpsHostArrays;
@@ -172,6 +175,8 @@ int pmps_wall_pnd_diffusive(pmps_t* h);          /* MpsPndNeigh::calcWall{Slip,N
 int pmps_update_pnd(pmps_t* h);                  /* MpsPndNeigh::updatePnd                  src/MpsPndNeigh.cpp:747-774 */
 int pmps_mean_pnd_wall_dummy_surface(pmps_t* h); /* MpsPndNeigh::meanPndParticlesWallDummySurface  src/MpsPndNeigh.cpp:777-852 */
 int pmps_update_bc(pmps_t* h);                   /* MpsBoundaryCondition::updateParticleBC  src/MpsBoundaryCondition.cpp:66-399 */
+int pmps_calc_normals(pmps_t* h);                   /* MpsShifting::calcNormalParticles, src/MpsShifting.cpp:106-174 (ARC free surface, src/main.cpp:351-357) */
+int pmps_calc_wall_normals(pmps_t* h);              /* MpsShifting::calcWallNormalParticles, src/MpsShifting.cpp:319-429 */
 int pmps_calc_press(pmps_t* h);                  /* MpsPressure::calcPress (EOS or PPE+Krylov)  src/MpsPressure.cpp:31-57 */
 int pmps_extrapolate_press(pmps_t* h);           /* MpsPressure::extrapolatePressParticlesWallDummy  src/MpsPressure.cpp:792-846 */
 int pmps_press_gradient(pmps_t* h);              /* MpsPressure::calcPressGradient          src/MpsPressure.cpp:1217-1338 */

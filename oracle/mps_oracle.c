@@ -197,12 +197,87 @@ void oracle_update_pnd(const PmpsParams* P, PmpsHostArrays* A) {
 	for (int i = 0; i < A->numParticles; i++) { A->pndi[i] = A->pndAuxVar1[i]; A->pndAuxVar1[i] = 0.0; }
 }
 
-void oracle_update_bc(const PmpsParams* P, PmpsHostArrays* A) {   /* PND_NEIGH and PND_NPCD; ARC is SURVEY §8f row 4 */
+/* MpsShifting::calcNormalParticles, src/MpsShifting.cpp:106-174: normal_i = -(1/n0S) sum_j r_ij w_S / |r_ij| over P(reS) */
+void oracle_calc_normals(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	PARFOR
+	for (int i = 0; i < A->numParticles; i++) {
+		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i;
+		double dx = 0.0, dy = 0.0, dz = 0.0;
+		NEIGH_LOOP(P, A, B, xi, mi, {
+			if (PRED_P(P, P->reS2) && j != i) {
+				const double dst = sqrt(d2); const double w = wgt(dst, P->reS, P->weightType);
+				dx += rx * w / dst; dy += ry * w / dst; dz += rz * w / dst;
+			}
+		});
+		A->normal[3 * (size_t)i] = -dx / P->pndSmallZero; A->normal[3 * (size_t)i + 1] = -dy / P->pndSmallZero; A->normal[3 * (size_t)i + 2] = -dz / P->pndSmallZero;
+	}
+}
+/* MpsShifting::calcWallNormalParticles, src/MpsShifting.cpp:319-429: the mirror neighbourhood's part, reflected back */
+void oracle_calc_wall_normals(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	PARFOR
+	for (int i = 0; i < A->numParticles; i++) {
+		if (!(A->particleType[i] == P->fluid && A->particleNearWall[i])) continue;
+		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i;
+		double n[3], R[9]; wall_normal(xi, mi, P->epsilonZero, 0, n); reflection(n, R);
+		double dx = 0.0, dy = 0.0, dz = 0.0;
+		NEIGH_LOOP(P, A, B, xi, mi, {
+			if (PRED_M(P->reS2) && j != i) {
+				const double dst = sqrt(dm2); const double w = wgt(dst, P->reS, P->weightType);
+				dx += mx * w / dst; dy += my * w / dst; dz += mz * w / dst;
+			}
+		});
+		const double ex = xi[0] - mi[0], ey = xi[1] - mi[1], ez = xi[2] - mi[2]; const double dd = ex * ex + ey * ey + ez * ez;
+		if (dd < P->reS2) { const double dst = sqrt(dd); const double w = wgt(dst, P->reS, P->weightType); dx += ex * w / dst; dy += ey * w / dst; dz += ez * w / dst; }
+		const double rx_ = MATVEC(R, dx, dy, dz, 0), ry_ = MATVEC(R, dx, dy, dz, 1), rz_ = MATVEC(R, dx, dy, dz, 2);
+		A->normal[3 * (size_t)i] += -rx_ / P->pndSmallZero; A->normal[3 * (size_t)i + 1] += -ry_ / P->pndSmallZero; A->normal[3 * (size_t)i + 2] += -rz_ / P->pndSmallZero;
+	}
+}
+
+/* MpsBoundaryCondition::updateParticleBC, src/MpsBoundaryCondition.cpp:66-399 (PND_NEIGH, PND_NPCD, PND_ARC) */
+void oracle_update_bc(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	PARFOR
 	for (int i = 0; i < A->numParticles; i++) {
 		if (A->particleType[i] == P->dummyWall) { A->particleBC[i] = P->other; continue; }
 		int bc = A->pndSmall[i] < P->betaPnd ? P->surface : P->inner;
 		if (P->freeSurfType == 0) bc = (A->pndSmall[i] < P->betaPnd && A->numNeigh[i] < P->betaNeigh) ? P->surface : P->inner;
 		else if (P->freeSurfType == 1) { if (bc == P->surface && A->numNeigh[i] > 4 && A->npcdDeviation2[i] < P->delta2) bc = P->inner; }
+		else if (P->freeSurfType == 2) {   /* :205-390 */
+			double nx = A->normal[3 * (size_t)i], ny = A->normal[3 * (size_t)i + 1], nz = A->normal[3 * (size_t)i + 2];
+			const double norm2 = nx * nx + ny * ny + nz * nz;
+			if (A->pndi[i] >= P->betaPnd && A->numNeigh[i] >= P->betaNeigh && norm2 <= P->normThreshold2) bc = P->inner;
+			else {
+				const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i;
+				if (norm2 > P->epsilonZero) { const double nm = sqrt(norm2); nx /= nm; ny /= nm; nz /= nm; } else { nx = ny = nz = 0.0; }
+				double nw[3]; nw[0] = 0.5 * (xi[0] - mi[0]); nw[1] = 0.5 * (xi[1] - mi[1]); nw[2] = 0.5 * (xi[2] - mi[2]);
+				const double nw2 = nw[0] * nw[0] + nw[1] * nw[1] + nw[2] * nw[2];
+				if (nw2 > P->epsilonZero) { const double m_ = sqrt(nw2); nw[0] /= m_; nw[1] /= m_; nw[2] /= m_; } else { nw[0] = nw[1] = nw[2] = 0.0; }
+				double R[9]; reflection(nw, R);
+				double qx = MATVEC(R, nx, ny, nz, 0), qy = MATVEC(R, nx, ny, nz, 1), qz = MATVEC(R, nx, ny, nz, 2);   /* normal of the mirror particle */
+				const double q2 = qx * qx + qy * qy + qz * qz;
+				if (q2 > P->epsilonZero) { const double qm = sqrt(q2); qx /= qm; qy /= qm; qz /= qm; } else { qx = qy = qz = 0.0; }
+				const double lo = P->partDist;
+				const double tx = xi[0] + lo * nx, ty = xi[1] + lo * ny, tz = xi[2] + lo * nz;          /* point one particle distance along the normal */
+				const double ux = mi[0] + lo * qx, uy = mi[1] + lo * qy, uz = mi[2] + lo * qz;          /* the same from the mirror particle */
+				int found = 0;
+				NEIGH_LOOP(P, A, B, xi, mi, {
+					if (!found) {   /* the reference leaves both loops at the first hit (goto endloop) */
+						const double* xj = A->pos + 3 * (size_t)j;
+						if (PRED_P(P, P->reS2) && j != i) {
+							const double ax = xj[0] - tx, ay = xj[1] - ty, az = xj[2] - tz; const double dn2 = ax * ax + ay * ay + az * az;
+							const double rn = rx * nx + ry * ny + rz * nz; const double ang = acos(rn / sqrt(d2));
+							if ((d2 >= P->dstThreshold2 && dn2 < P->hThreshold2) || (d2 < P->dstThreshold2 && ang < P->thetaArc)) { bc = P->inner; found = 1; }
+							else bc = P->surface;
+						}
+						if (!found && P->wallType == 1 && PRED_M(P->reS2) && j != i) {
+							const double ax = xj[0] - ux, ay = xj[1] - uy, az = xj[2] - uz; const double dn2 = ax * ax + ay * ay + az * az;
+							const double rn = mx * qx + my * qy + mz * qz; const double ang = acos(rn / sqrt(dm2));
+							if ((dm2 >= P->dstThreshold2 && dn2 < P->hThreshold2) || (dm2 < P->dstThreshold2 && ang < P->thetaArc)) { bc = P->inner; found = 1; }
+							else bc = P->surface;
+						}
+					}
+				});
+			}
+		}
 		A->particleBC[i] = bc;
 	}
 }
@@ -1152,7 +1227,8 @@ void oracle_init_step0(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMes
 	if (P->wallType == 1) oracle_mean_wall_pnd(P, A, B);
 	oracle_mean_pnd(P, A, B);
 	oracle_mean_neigh_fluid_pnd(P, A, B);
-	oracle_update_bc(P, A);
+	if (P->freeSurfType == 2) { oracle_calc_normals(P, A, B); if (P->wallType == 1) oracle_calc_wall_normals(P, A, B); }   /* src/main.cpp:170-176 */
+	oracle_update_bc(P, A, B);
 	pressure_stage(P, A, B, NULL, NULL);
 }
 
@@ -1305,7 +1381,8 @@ void oracle_step(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMesh* mes
 		if (poly) oracle_mean_wall_pnd(P, A, B);
 		oracle_mean_pnd(P, A, B);
 	}
-	oracle_update_bc(P, A);
+	if (P->freeSurfType == 2) { oracle_calc_normals(P, A, B); if (poly) oracle_calc_wall_normals(P, A, B); }   /* src/main.cpp:351-357 */
+	oracle_update_bc(P, A, B);
 	pressure_stage(P, A, B, solverIter, solverErr);
 	if (!poly) oracle_extrapolate_press(P, A, B);
 	if (P->gradientCorrection) oracle_correction_matrix(P, A, B);

@@ -52,7 +52,9 @@ void oracle_vel_divergence(const PmpsParams* P, PmpsHostArrays* A, const OBucket
 void oracle_wall_vel_divergence(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);  /* src/MpsPressure.cpp:554-788 */
 void oracle_update_pnd(const PmpsParams* P, PmpsHostArrays* A);                            /* src/MpsPndNeigh.cpp:747-774 */
 void oracle_mean_pnd_wall_dummy_surface(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B); /* src/MpsPndNeigh.cpp:777-852 */
-void oracle_update_bc(const PmpsParams* P, PmpsHostArrays* A);                             /* src/MpsBoundaryCondition.cpp:66-399 */
+void oracle_update_bc(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);          /* src/MpsBoundaryCondition.cpp:66-399 */
+void oracle_calc_normals(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);       /* src/MpsShifting.cpp:106-174 */
+void oracle_calc_wall_normals(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);  /* src/MpsShifting.cpp:319-429 */
 void oracle_calc_press_eos(const PmpsParams* P, PmpsHostArrays* A);                        /* src/MpsPressure.cpp:62-163 */
 int  oracle_solve_ppe(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B, double* err); /* src/MpsPressure.cpp:169-286,424-476 */
 void oracle_extrapolate_press(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);  /* src/MpsPressure.cpp:792-846 */

@@ -140,6 +140,7 @@ static void dump_state(const Sim& s, const std::string& path) {
 	D.d("correcMatrixRow3", p->correcMatrixRow3, 3 * n);
 	D.d("particleAtWallPos", p->particleAtWallPos, 3 * n); D.d("mirrorParticlePos", p->mirrorParticlePos, 3 * n);
 	D.d("polygonNormal", p->polygonNormal, 3 * n); D.d("forceWall", p->forceWall, 3 * n);
+	if (s.ps->freeSurfType == calcBCType::PND_ARC) D.d("normal", p->normal, 3 * n);   // (only then: the committed goldens keep their layout)
 	if (s.ps->mpsType == calcPressType::IMPLICIT_PND || s.ps->mpsType == calcPressType::IMPLICIT_PND_DIVU) {
 		D.d("pressurePPE", p->pressurePPE.data(), n); D.d("sourceTerm", p->sourceTerm.data(), n);
 		double it[2] = { (double)s.pr->getSolverIter(), s.pr->getSolverError() }; D.d("solver", it, 2);

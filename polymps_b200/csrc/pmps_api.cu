@@ -217,7 +217,7 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	if (params->fluidType == 1 && params->wallType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: the non-Newtonian rheology is on the device path for particle walls only (the polygon-wall variants, src/MpsViscosity.cpp:703-1526, are not: SURVEY 8f row 1)");
 	if (params->fluidType == 1 && params->fractionMethod != 1 && params->fractionMethod != 2) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: fractionMethod %d", params->fractionMethod);
 	if (params->domainTypeBC != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: periodic domain boundaries are not on the device path yet (SURVEY 8f row 4)");
-	if (params->freeSurfType == 2) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: ARC free-surface detection is not on the device path yet (SURVEY 8f row 4)");
+	if (params->freeSurfType < 0 || params->freeSurfType > 2) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: freeSurfType %d", params->freeSurfType);
 	if (params->collisionType != 0 && params->collisionType != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: collisionType %d", params->collisionType);
 	if (params->mpsType < 0 || params->mpsType > 3) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: mpsType %d", params->mpsType);
 	if (params->numBucketsX < 1 || params->numBucketsY < 1 || params->numBucketsZ < 1 || !(params->bucketSide > 0.0)) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: bucket geometry not set");

@@ -299,4 +299,85 @@ struct BShiftVel {
 		S.vel2[s.i] = v;
 	}
 };
+// ------------------------------------------------------------------------------------------------ ARC free-surface detection
+// MpsShifting::calcNormalParticles, src/MpsShifting.cpp:106-174: normal_i = -(1/n0S) sum_j r_ij w_S / |r_ij| over P(reS), every particle
+struct BNormal {
+	struct Ctx { double dx, dy, dz; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) { c.dx = c.dy = c.dz = 0.0; return true; }
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_P<POLY>(q, K.p.reS2)) return;
+		const double f = wgt_r(q.rinv, q.d2, K.p.reS, K.invReS, K.p.weightType) * q.rinv;
+		c.dx += q.rx * f; c.dy += q.ry * f; c.dz += q.rz * f;
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.dx = gsum(c.dx, m); c.dy = gsum(c.dy, m); c.dz = gsum(c.dz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		S.normal.x[s.i] = -c.dx / K.p.pndSmallZero; S.normal.y[s.i] = -c.dy / K.p.pndSmallZero; S.normal.z[s.i] = -c.dz / K.p.pndSmallZero;
+	}
+};
+// MpsShifting::calcWallNormalParticles, src/MpsShifting.cpp:319-429: the mirror neighbourhood's part (+ the particle itself), reflected back
+struct BWallNormal {
+	typedef void wall_frame_tag;
+	struct Ctx { double dx, dy, dz; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (!s.nearWallFluid) return false;
+		c.dx = c.dy = c.dz = 0.0; return true;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (!pred_M(q, K.p.reS2)) return;
+		const double ri = fast_rsqrt(q.dm2); const double f = wgt_r(ri, q.dm2, K.p.reS, K.invReS, K.p.weightType) * ri;
+		c.dx += q.mx * f; c.dy += q.my * f; c.dz += q.mz * f;
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.dx = gsum(c.dx, m); c.dy = gsum(c.dy, m); c.dz = gsum(c.dz, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		const double ex = s.pi.x - s.mix, ey = s.pi.y - s.miy, ez = s.pi.z - s.miz; const double dd = sq3_exact(ex, ey, ez);
+		if (dd < K.p.reS2) { const double dst = sqrt(dd); const double f = wgt(dst, K.p.reS, K.p.weightType) / dst; c.dx += ex * f; c.dy += ey * f; c.dz += ez * f; }
+		WallFrame f; wall_frame_of(f, s, K.p.epsilonZero, false);
+		S.normal.x[s.i] += -MATVEC(f.R, c.dx, c.dy, c.dz, 0) / K.p.pndSmallZero;
+		S.normal.y[s.i] += -MATVEC(f.R, c.dx, c.dy, c.dz, 1) / K.p.pndSmallZero;
+		S.normal.z[s.i] += -MATVEC(f.R, c.dx, c.dy, c.dz, 2) / K.p.pndSmallZero;
+	}
+};
+// MpsBoundaryCondition::updateParticleBC with PND_ARC, src/MpsBoundaryCondition.cpp:66-88,205-390.  A particle that is not inner by
+// its density, neighbour count and normal length is INNER when some neighbour lies in the arc in front of it (within 1.33 lo of the
+// point one particle distance along the normal, or — closer than sqrt(2) 1.33 lo — inside the cone of half-angle thetaArc around the
+// normal; the same test from the mirror particle for a particle near a polygon wall), SURFACE when it has neighbours but none there,
+// and keeps the density-based flag when it has none.  The reference leaves its loops at the first hit: an OR, independent of order.
+struct BArcBC {
+	struct Ctx { double nx, ny, nz, qx, qy, qz; int bc0, found, seen; };
+	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		if (s.type == K.p.dummyWall) { if (s.lead) S.particleBC[s.i] = K.p.other; return false; }
+		c.bc0 = S.pndSmall[s.i] < K.p.betaPnd ? K.p.surface : K.p.inner; c.found = 0; c.seen = 0;
+		double nx = S.normal.x[s.i], ny = S.normal.y[s.i], nz = S.normal.z[s.i];
+		const double n2 = nx * nx + ny * ny + nz * nz;
+		if (S.pndi[s.i] >= K.p.betaPnd && S.numNeigh[s.i] >= K.p.betaNeigh && n2 <= K.p.normThreshold2) { if (s.lead) S.particleBC[s.i] = K.p.inner; return false; }
+		if (n2 > K.p.epsilonZero) { const double nm = sqrt(n2); nx /= nm; ny /= nm; nz /= nm; } else { nx = ny = nz = 0.0; }
+		c.nx = nx; c.ny = ny; c.nz = nz;
+		// normal of the mirror particle: the reflection about the wall plane through the closest point (R = I - 2 n_w n_w^T)
+		double wx = 0.5 * (s.pi.x - s.mix), wy = 0.5 * (s.pi.y - s.miy), wz = 0.5 * (s.pi.z - s.miz);
+		const double w2 = wx * wx + wy * wy + wz * wz;
+		if (w2 > K.p.epsilonZero) { const double wm = sqrt(w2); wx /= wm; wy /= wm; wz /= wm; } else { wx = wy = wz = 0.0; }
+		const double dn = wx * nx + wy * ny + wz * nz;
+		double qx = nx - 2.0 * wx * dn, qy = ny - 2.0 * wy * dn, qz = nz - 2.0 * wz * dn;
+		const double q2 = qx * qx + qy * qy + qz * qz;
+		if (q2 > K.p.epsilonZero) { const double qm = sqrt(q2); qx /= qm; qy /= qm; qz /= qm; } else { qx = qy = qz = 0.0; }
+		c.qx = qx; c.qy = qy; c.qz = qz;
+		return true;
+	}
+	__device__ __forceinline__ static bool in_arc(const KParams& K, double rx, double ry, double rz, double d2, double nx, double ny, double nz) {
+		if (d2 >= K.p.dstThreshold2) {   // |x_j - (x_i + lo n)|^2 < hThreshold2
+			const double ax = rx - K.p.partDist * nx, ay = ry - K.p.partDist * ny, az = rz - K.p.partDist * nz;
+			return ax * ax + ay * ay + az * az < K.p.hThreshold2;
+		}
+		return acos((rx * nx + ry * ny + rz * nz) / sqrt(d2)) < K.p.thetaArc;
+	}
+	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
+		if (pred_P<POLY>(q, K.p.reS2)) { c.seen = 1; if (in_arc(K, q.rx, q.ry, q.rz, q.d2, c.nx, c.ny, c.nz)) c.found = 1; }
+		if (POLY && pred_M(q, K.p.reS2)) { c.seen = 1; if (in_arc(K, q.mx, q.my, q.mz, q.dm2, c.qx, c.qy, c.qz)) c.found = 1; }
+	}
+	__device__ __forceinline__ static void reduce(Ctx& c, unsigned m) { c.found = gsum(c.found, m); c.seen = gsum(c.seen, m); }
+	__device__ __forceinline__ static void end(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
+		S.particleBC[s.i] = c.found ? K.p.inner : c.seen ? K.p.surface : c.bc0;
+	}
+};
+
 #include "pmps_rheo.cuh"

@@ -23,7 +23,7 @@
 #define PMPS_RHEO_FIELDS(X) X(Cv) X(II) X(MEU_Y) X(Inertia) X(p_rheo_new) X(p_smooth) X(VF) X(S11) X(S12) X(S13) X(S22) X(S23) X(S33)
 #define PMPS_V3_FIELDS(X) X(acc) X(accStar) X(npcdDeviation) X(gradConcentration) X(correcMatrixRow1) \
 	X(correcMatrixRow2) X(correcMatrixRow3) X(particleAtWallPos) X(mirrorParticlePos) X(polygonNormal) X(forceWall) \
-	X(dvelCollision)
+	X(dvelCollision) X(normal)
 
 struct V3 { double* x; double* y; double* z; };
 

@@ -99,6 +99,9 @@ __host__ __device__ constexpr int tv_rec_bytes(unsigned f) {   // staged bytes p
 // staged records per work item: a compile-time constant, so every plane of the shared-memory image sits at a constant
 // offset (no registers spent on plane pointers).  Sized for two blocks per SM of the fattest pack in follow mode.
 #define TV_MAXM (((TV_SMEM_BUDGET - TV_FIXED_BYTES) / TV_REC_MAX) & ~3)   // multiple of 4: every plane and the fixed part stay 16-byte aligned
+#ifndef TV_ILP2_FAT
+#define TV_ILP2_FAT 0             // 1: two list entries per trip in the passes that run two blocks per SM (their registers allow it)
+#endif
 #ifndef TV_ILP2
 #define TV_ILP2 0                 // 1: follow passes take two list entries per trip (interleaved geometry chains); measured: no gain
 #endif
@@ -756,17 +759,17 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 					for (int v = 0; v < TV_PER / 8; v++) { const uint4 e = __ldg(Lg + ch * (TV_CHUNK / 8) + v); w[4 * v] = e.x; w[4 * v + 1] = e.y; w[4 * v + 2] = e.z; w[4 * v + 3] = e.w; }
 				}
 				const int rem = cntE - ch * TV_CHUNK - g;   // entries u * TV_G + g of this chunk exist for u * TV_G < rem
-#if TV_ILP2
-				#pragma unroll
-				for (int u = 0; u < TV_PER; u += 2) {   // two entries per trip (one 32-bit word of the list); a missing one points at the dummy record
-					if (u * TV_G < rem) tv_pair2<POLY, F>(ctx, T, K, s, (int)(w[u >> 1] & 0xffffu), (u + 1) * TV_G < rem ? (int)(w[u >> 1] >> 16) : M);
+				if (TV_ILP2 || (TV_ILP2_FAT && TV_BLOCKS(FIELDS) == 2)) {
+					#pragma unroll
+					for (int u = 0; u < TV_PER; u += 2) {   // two entries per trip (one 32-bit word of the list); a missing one points at the dummy record
+						if (u * TV_G < rem) tv_pair2<POLY, F>(ctx, T, K, s, (int)(w[u >> 1] & 0xffffu), (u + 1) * TV_G < rem ? (int)(w[u >> 1] >> 16) : M);
+					}
+				} else {
+					#pragma unroll
+					for (int u = 0; u < TV_PER; u++) {
+						if (u * TV_G < rem) tv_pair<POLY, F>(ctx, T, K, s, (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu));
+					}
 				}
-#else
-				#pragma unroll
-				for (int u = 0; u < TV_PER; u++) {
-					if (u * TV_G < rem) tv_pair<POLY, F>(ctx, T, K, s, (int)((w[u >> 1] >> ((u & 1) * 16)) & 0xffffu));
-				}
-#endif
 			}
 			F::reduce(ctx, gmask);   // all lanes, uniform
 			if (act && s.lead) F::end(ctx, S, K, s);

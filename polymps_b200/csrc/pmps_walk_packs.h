@@ -10,5 +10,6 @@
 	X(18, 2, BPressGradient) X(19, 2, BPressGradient, BCorrectTail) X(20, 2, BPredPressGradient) X(21, 2, BPredWallPressGradient) X(22, 2, BWallPressGradient) \
 	X(23, 2, BWallPressGradient, BWallViscosity, BCorrectTail) X(24, 2, BWallViscosity) X(25, 2, BPressMin) X(26, 2, BMeanNeighFluidPnd) \
 	X(27, 3, BCorrectionMatrix) X(28, 3, BCorrectionMatrix, BPressMin) X(29, 3, BExtrapolatePress) X(30, 3, BConcentration) X(31, 3, BGradConcentration) X(32, 3, BWallGradConcentration) \
-	X(33, 3, BWallDummyVel) X(34, 3, BVolumeFraction) X(35, 3, BStrainRate)
+	X(33, 3, BWallDummyVel) X(34, 3, BVolumeFraction) X(35, 3, BStrainRate) \
+	X(36, 0, BNormal) X(37, 1, BWallNormal) X(38, 2, BArcBC)
 #define PMPS_WALK_GROUPS 4

@@ -20,7 +20,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PMPS_LIB", os.path.join(HERE, "libpmps.so"))   # PMPS_LIB: an experimental build of the same library (A/B timing)
 
 STAGES = ["update_buckets", "calc_volume_fraction", "calc_viscosity_interaction", "calc_viscosity", "add_gravity", "predict", "check_out_domain", "collisions", "wall_closest_point",
-          "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive", "wall_pnd_diffusive", "update_pnd",
+          "wall_npcd", "correction_matrix", "calc_normals", "calc_wall_normals", "pnd_neigh_npcd", "pnd_diffusive", "wall_pnd_diffusive", "update_pnd",
           "mean_pnd_wall_dummy_surface", "update_bc", "calc_press", "extrapolate_press", "press_gradient",
           "wall_press_gradient", "prediction_press_gradient", "prediction_wall_press_gradient", "wall_viscosity", "correct", "shifting", "wall_shifting", "update_wall_dummy_vel",
           "initial_pnd", "mean_wall_pnd", "mean_pnd", "mean_neigh_fluid_pnd", "init_step0", "synchronize"]
@@ -34,7 +34,7 @@ REFERENCE_NAMES = {
     "correctionMatrix": "correction_matrix", "calcPndnNeighNPCD": "pnd_neigh_npcd", "calcPndDiffusiveTerm": "pnd_diffusive",
     "calcWallNoSlipPndDiffusiveTerm": "wall_pnd_diffusive", "calcWallSlipPndDiffusiveTerm": "wall_pnd_diffusive",
     "updatePnd": "update_pnd", "meanPndParticlesWallDummySurface": "mean_pnd_wall_dummy_surface",
-    "updateParticleBC": "update_bc", "calcPress": "calc_press", "extrapolatePressParticlesWallDummy": "extrapolate_press",
+    "updateParticleBC": "update_bc", "calcNormalParticles": "calc_normals", "calcWallNormalParticles": "calc_wall_normals", "calcPress": "calc_press", "extrapolatePressParticlesWallDummy": "extrapolate_press",
     "predictionPressGradient": "prediction_press_gradient", "predictionWallPressGradient": "prediction_wall_press_gradient",
     "calcPressGradient": "press_gradient", "calcWallPressGradient": "wall_press_gradient",
     "calcWallNoSlipViscosity": "wall_viscosity", "calcWallSlipViscosity": "wall_viscosity",

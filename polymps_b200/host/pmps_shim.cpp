@@ -53,7 +53,7 @@ PmpsHostArrays host_arrays(MpsParticle* P) {
 	F(press) F(pndi) F(pndki) F(pndski) F(pndSmall) F(npcdDeviation2) F(concentration) F(velDivergence) F(diffusiveTerm)
 	F(pndWallContribution) F(distParticleWall2) F(deviationDotPolygonNormal) F(RHO) F(MEU) F(pndAuxVar1) F(pndAuxVar2)
 	F(pos) F(vel) F(acc) F(accStar) F(npcdDeviation) F(gradConcentration) F(correcMatrixRow1) F(correcMatrixRow2) F(correcMatrixRow3)
-	F(particleAtWallPos) F(mirrorParticlePos) F(polygonNormal) F(forceWall) F(dvelCollision)
+	F(particleAtWallPos) F(mirrorParticlePos) F(polygonNormal) F(forceWall) F(dvelCollision) F(normal)
 #undef F
 	if (g_S && g_S->fluidType == viscType::NON_NEWTONIAN) {   // allocated only then (src/MpsInputOutput.cpp:729-744)
 #define F(n) a.n = P->n;
@@ -83,6 +83,7 @@ PmpsParams params_of(MpsParticleSystem* S) {
 	C(coeffPPE) C(coeffPPESource) C(distCollisionLimit2) C(restitutionCollision) C(lambdaCollision) C(betaPnd)
 	C(betaNeigh) C(delta2) C(velMax)
 	C(KNM_VS1) C(KNM_VS2) C(DNS_SDT) C(PHI_1) C(PHI_2) C(cohes) C(MEU0) C(DG) C(I0) C(mm) C(Cd) C(VF_min) C(VF_max) C(relaxPND) C(timeCurrent)
+	C(thetaArc) C(hThreshold2) C(dstThreshold2) C(normThreshold2)
 #undef C
 	p.fractionMethod = S->Fraction_method;
 	for (int k = 0; k < 3; k++) p.uniformVelWall[k] = S->uniformVelWall[k];
@@ -233,8 +234,8 @@ void MpsPressure::calcWallPressGradient(MpsParticleSystem *PSystem, MpsParticle 
 
 // ---- MpsShifting (src/MpsShifting.cpp:23-101 type 1, :432-691 type 2, :106-174 / :319-429 normals) ----------------------------
 void MpsShifting::calcShifting(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_shifting(H(PSystem, Particles))); }   // pmps_shifting runs the type PmpsParams.shiftingType names
-void MpsShifting::calcNormalParticles(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { unsupported("MpsShifting::calcNormalParticles", "ARC free-surface detection, src/main.cpp:351-357"); }
-void MpsShifting::calcWallNormalParticles(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { unsupported("MpsShifting::calcWallNormalParticles", "ARC free-surface detection, src/main.cpp:351-357"); }
+void MpsShifting::calcNormalParticles(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_calc_normals(handle())); }
+void MpsShifting::calcWallNormalParticles(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_calc_wall_normals(handle())); }
 void MpsShifting::calcConcAndConcGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_shifting(H(PSystem, Particles))); }
 void MpsShifting::calcWallConcAndConcGradient(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_shifting(H(PSystem, Particles))); }
 

@@ -159,6 +159,10 @@ class ParticleSystem:
     betaPnd: float = 0.0
     betaNeigh: float = 0.0
     delta2: float = 0.0
+    thetaArc: float = 0.0
+    hThreshold2: float = 0.0
+    dstThreshold2: float = 0.0
+    normThreshold2: float = 0.0
     velMax: float = 0.0
     CFLcurrent: float = 0.0
     timeCurrent: float = 0.0
@@ -370,6 +374,11 @@ class ParticleSystem:
         self.betaPnd = self.pndThreshold * n0S
         self.betaNeigh = self.neighThreshold * nN
         self.delta2 = self.npcdThreshold * self.npcdThreshold * lo * lo
+        # ARC free-surface detection (src/MpsParticle.cpp:219-222)
+        self.thetaArc = self.thetaThreshold / 180.0 * 3.14159265
+        self.hThreshold2 = 1.33 * 1.33 * lo * lo
+        self.dstThreshold2 = 2.0 * self.hThreshold2
+        self.normThreshold2 = self.normThreshold * self.normThreshold
         self._parameters_set = True
         return self
 
@@ -434,7 +443,8 @@ class PmpsParams(ctypes.Structure):
            "coeffPressGrad", "coeffPressEMPS", "coeffPressWCMPS", "coeffShifting1", "coeffShifting2", "coeffPPE",
            "coeffPPESource", "distCollisionLimit2", "restitutionCollision", "lambdaCollision", "betaPnd", "betaNeigh",
            "delta2", "velMax"]
-    _D3 = ["KNM_VS1", "KNM_VS2", "DNS_SDT", "PHI_1", "PHI_2", "cohes", "MEU0", "DG", "I0", "mm", "Cd", "VF_min", "VF_max", "relaxPND", "timeCurrent"]
+    _D3 = ["KNM_VS1", "KNM_VS2", "DNS_SDT", "PHI_1", "PHI_2", "cohes", "MEU0", "DG", "I0", "mm", "Cd", "VF_min", "VF_max", "relaxPND", "timeCurrent",
+           "thetaArc", "hThreshold2", "dstThreshold2", "normThreshold2"]
     _fields_ = ([(n, ctypes.c_int32) for n in _I] + [(n, ctypes.c_double) for n in _D]
                 + [("uniformVelWall", ctypes.c_double * 3)] + [(n, ctypes.c_double) for n in _D2 + _D3])
 
@@ -443,7 +453,7 @@ def to_c_params(ps: ParticleSystem, shifting_jacobi: bool = True) -> PmpsParams:
     c = PmpsParams()
     for n in PmpsParams._I:
         if n == "abi_version":
-            c.abi_version = 2
+            c.abi_version = 3
         elif n == "shiftingJacobi":
             c.shiftingJacobi = 1 if shifting_jacobi else 0
         elif n == "_pad0":

@@ -16,7 +16,7 @@ F64 = ["press", "pndi", "pndki", "pndski", "pndSmall", "npcdDeviation2", "concen
        "pndWallContribution", "distParticleWall2", "deviationDotPolygonNormal", "RHO", "MEU", "pndAuxVar1", "pndAuxVar2",
        "pressurePPE", "sourceTerm"]
 VEC = ["pos", "vel", "acc", "accStar", "npcdDeviation", "gradConcentration", "correcMatrixRow1", "correcMatrixRow2",
-       "correcMatrixRow3", "particleAtWallPos", "mirrorParticlePos", "polygonNormal", "forceWall", "dvelCollision"]
+       "correcMatrixRow3", "particleAtWallPos", "mirrorParticlePos", "polygonNormal", "forceWall", "dvelCollision", "normal"]
 # non-Newtonian fields (src/MpsInputOutput.cpp:729-744); transferred only by handles created with fluidType 1
 RHEO = ["Cv", "II", "MEU_Y", "Inertia", "p_rheo_new", "p_smooth", "VF", "S11", "S12", "S13", "S22", "S23", "S33"]
 ALL_FIELDS = I32 + U8 + F64 + VEC + RHEO

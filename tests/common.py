@@ -39,6 +39,8 @@ def stage_calls(stage, ps):
         return ["prediction_press_gradient"] + (["prediction_wall_press_gradient"] if ps.wallType == 1 else [])
     if stage == "meanPnd":   # pnd type 1: src/main.cpp:345-350
         return (["mean_wall_pnd"] if ps.wallType == 1 else []) + ["mean_pnd"]
+    if stage == "normals":   # ARC free-surface detection: src/main.cpp:351-357
+        return ["calc_normals"] + (["calc_wall_normals"] if ps.wallType == 1 else [])
     return STAGE_MAP[stage]
 
 
@@ -161,5 +163,6 @@ VARIANTS = {
     "2d_divu": _v2(incompressible=True, mps_type=3), "divu_nocorr": _v3(incompressible=True, mps_type=3, grad_corr=False, grad_type=3),
     "dpc": _v3(collision=1), "2d_dpc": tuple(_jittered(b) for b in _v2(collision=1)),
     "relax": _v3(relax=0.7), "relax_grad0": _v3(relax=0.5, grad_type=0), "2d_relax": _v2(relax=0.6),
+    "arc": _v3(fs_type=2), "2d_arc": _v2(fs_type=2), "arc_pnd0": _v3(fs_type=2, pnd_type=0),   # ARC free-surface detection + particle normals
     "2d_grad3": _v2(grad_type=3, grad_corr=False), "2d_w3": _v2(weight_type=3), "2d_fs1": _v2(fs_type=1), "2d_pnd0": _v2(pnd_type=0),
 }

@@ -35,12 +35,14 @@ def _run(binary, root, name, threads=1):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kind", ["wc3d", "inc3d", "wc2d", "nn2d", "slosh3d"])
+@pytest.mark.parametrize("kind", ["wc3d", "inc3d", "wc2d", "nn2d", "slosh3d", "arc3d"])
 def test_unmodified_main_with_shim_matches_stock_reference(kind):
     if not (os.path.isfile(REF_BIN) and os.path.isfile(GPU_BIN)):
         pytest.skip("drop-in binaries not built (they need the reference tree at build time)")
     if kind == "wc3d":
         case = cases.dam3d(14, 7, 10, jitter=0.05, name="dropin", shifting=0)
+    elif kind == "arc3d":   # ARC free-surface detection (free_surface_threshold.type 2): particle normals + arc test on the device
+        case = cases.dam3d(14, 7, 10, jitter=0.05, name="dropin", shifting=0, fs_type=2)
     elif kind == "inc3d":
         case = cases.dam3d(12, 6, 8, jitter=0.03, incompressible=True, name="dropin")
     elif kind == "slosh3d":   # BASELINE configs[3]: three meshes, the tank is the forced mesh the host rotates every step
