@@ -143,6 +143,11 @@ int pmps_set_uniform_vel_wall(pmps_t* h, const double v[3]);
  * overlapped with it on a second stream.  Same results as pmps_upload + pmps_step(h, 1) + pmps_download. */
 int pmps_step_host(pmps_t* h, const PmpsHostArrays* in, PmpsHostArrays* out);
 /* device-resident inputs (bench `value` leg, multi-GPU slabs): same layout as the host arrays, device pointers */
+/* The reference's particle file straight into the device layout (replaces MpsInputOutput::readMpsParticleFile,
+ * src/MpsInputOutput.cpp:645-857, for a fresh handle): "0", N, N rows "type x y z vx vy vz press pressAverage".  Parsed in chunks by a few
+ * host threads; the other live fields get the reference's initial values.  The state is as after pmps_upload of the arrays the
+ * reference's reader builds; no host array of N entries is ever allocated. */
+int pmps_load_grid(pmps_t* h, const char* path, int* numParticles);
 int pmps_upload_device(pmps_t* h, const PmpsHostArrays* device_arrays);
 /* The same rows with new values — a host-driven loop that hands back the particle table it received (a slab rank between two
  * re-partitions): bucket order, hit lists and the partition survive, the displacement trackers decide about rebuilds as inside a step. */

@@ -92,6 +92,8 @@ def load_library() -> ctypes.CDLL:
     if os.environ.get("PMPS_LIB") is None or hasattr(L, "pmps_observe_extent"):
         L.pmps_observe_extent.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong)]
         L.pmps_observe_box.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+    if os.environ.get("PMPS_LIB") is None or hasattr(L, "pmps_load_grid"):
+        L.pmps_load_grid.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int)]
     L.pmps_set_mesh.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_int,
                                 ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_double), ctypes.c_int,
                                 ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double),
@@ -163,6 +165,13 @@ class Engine:
         c = state.c_struct(fields)
         self._n0_value = state.numParticlesZero
         self._chk(self.lib.pmps_upload(self.h, ctypes.byref(c)))
+
+    def load_grid(self, path: str) -> int:
+        """The reference's .grid particle file straight into the device layout (pmps_load_grid); returns the particle count."""
+        n = ctypes.c_int()
+        self._chk(self.lib.pmps_load_grid(self.h, os.fsencode(path), ctypes.byref(n)))
+        self._n0_value = int(n.value)
+        return int(n.value)
 
     def download(self, state: HostState, fields=None):
         c = state.c_struct(fields)
