@@ -34,7 +34,7 @@ ALGO_BYTES = {
     # fused groups of the whole-step path (names = LAUNCH names in polymps_b200/csrc/pmps_stages.inc)
     "F1.viscosity+predict": 288, "F2.wall+collision": 225, "F2.collision": 104, "F3.pnd+diffusive+wall": 217, "F3.pnd+diffusive": 217,
     "F3.pnd+wall": 160, "mean_pnd_surface": 72, "E4.bc+eos": 48, "F5.gradient+wall+correct": 313, "F5.gradient+correct": 313,
-    "shift.concentration": 64, "shift.gradient": 113, "shift.wall_gradient": 0, "list.build": 308,
+    "shift.concentration": 64, "shift.gradient": 113, "shift.wall_gradient": 0, "sort.permute8": 308,   # G0: the gather of every plane into the new bucket order
     "F5.gradient": 165, "W5.wall+correct": 148,
     # incompressible scheme (--scheme inc; SURVEY.md 8d "Same, INC"): ELL row of A^T 40 x 12 B + count/diag + x, y
     "ppe.spmv": 500, "ppe.assemble": 580, "ppe.update_xr": 56, "ppe.update_p": 32, "ppe.residual0": 516,
@@ -486,7 +486,7 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=10)
     ap.add_argument("--cpu1-k", type=int, default=40, help="block edge of the 1-thread CPU figure (0 skips it)")
     ap.add_argument("--e2e-steps", type=int, default=10)
-    ap.add_argument("--profile-steps", type=int, default=2)
+    ap.add_argument("--profile-steps", type=int, default=6, help="steps of the per-kernel timing pass (serialised by its events; long enough to see the rebuild / refilter mix of the timed region)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--traffic", type=float, default=None, help="dram bytes per launch of the top kernel from an ncu --set full capture (profiles/)")
     args = ap.parse_args()

@@ -12,8 +12,13 @@ import sys
 rows = [r for r in csv.reader(open(sys.argv[1])) if len(r) > 14 and r[0].isdigit()]
 tot = collections.OrderedDict()
 for r in rows:
-    name = re.sub(r"\(.*", "", r[4])
-    name = re.sub(r"<.*", "<...>", name) if len(name) > 90 else name
+    full = r[4]
+    m = re.search(r"k_tv<.*?Fused<(.*?)>>\(", full)
+    if m:   # a walker pass: name it by its bodies
+        name = "k_tv<" + re.sub(r"pmps_set_\w+::", "", m.group(1)) + ">"
+    else:
+        name = re.sub(r"\(.*", "", full); name = re.sub(r"pmps_set_\w+::", "", name)
+        name = re.sub(r"<.*", "<...>", name) if len(name) > 90 else name
     t = tot.setdefault(name, [0, 0.0]); t[0] += 1; t[1] += float(r[14].replace(",", ""))
 total = sum(v[1] for v in tot.values())
 print("# %d launches, %.3f ms total (whole command incl. upload, 0-th step, warm-up, profile pass, e2e pass)" % (len(rows), total / 1e6))
