@@ -244,6 +244,14 @@ int pmps_slab_set_hooks(pmps_t* h, double* d_workspace8, pmps_sum_fn sum, pmps_r
  * pmps_observe_box: count, pressure sum and pressure maximum of the particles of one type inside [lo, hi] (probe = sum / count). */
 int pmps_observe_extent(pmps_t* h, int particleType, double mn[3], double mx[3], long long* count);
 int pmps_observe_box(pmps_t* h, int particleType, const double lo[3], const double hi[3], long long* count, double* pressSum, double* pressMax);
+/* pmps_observe_extent_static: same arguments and results as pmps_observe_extent.  No counterpart in the reference; added
+ * for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  The call allocates nothing: the per-block partial records of the reduction live in a file-scope device array of
+ * 1024 records (80 KiB, held by every GPU that loads the library until exit) instead of the handle's staging area.  One record per
+ * block, four blocks per SM: a device that needs more than 1024 records (> 256 SMs) is refused with PMPS_E_ARG and a message in
+ * pmps_last_error.  Every call on one GPU shares the array (the previous call's contents are overwritten before they are read,
+ * nothing has to be cleared), so calls that overlap on the same GPU — other handles, other streams — race: serialise them. */
+int pmps_observe_extent_static(pmps_t* h, int particleType, double mn[3], double mx[3], long long* count);
 
 /* ---- debug / parity hooks (tests only) ---------------------------------------------------------------------- */
 /* bucket id of every host-order particle as the reference computes it at rebuild time, and the members of every

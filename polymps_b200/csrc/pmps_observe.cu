@@ -6,6 +6,7 @@
 // Two-stage reductions in a fixed order: the sums are reproducible run to run.
 #include "pmps_device.cuh"
 #include <cfloat>
+#include <mutex>
 
 #define OBS_T 256
 struct ObsPartial { double mn[3], mx[3], psum, pmax; long long n, nbox; };
@@ -81,5 +82,57 @@ extern "C" int pmps_observe_box(pmps_t* h, int particleType, const double lo[3],
 	if (count) *count = r.nbox;
 	if (pressSum) *pressSum = r.psum;
 	if (pressMax) *pressMax = r.nbox ? r.pmax : 0.0;
+	return PMPS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// pmps_observe_extent_static: the extent reduction with its per-block partial records in a file-scope device array instead of
+// the handle's cudaMalloc'ed staging area.  No counterpart in the reference; added for
+// callers that may not allocate (graph capture, tight serving loops).  The call makes no cudaMalloc / cudaFree and uses no
+// allocating library routine.  Limits and rules:
+//   * the array holds PMPS_OBS_STATIC_MAX partial records (1024 x 80 bytes = 80 KiB); every GPU that loads the library keeps it
+//     until exit.  One record per block, four blocks per SM: a device that would need more records is refused with PMPS_E_ARG;
+//   * every call on a device shares the one array.  Stage 1 overwrites each record it later reads, so nothing has to start at
+//     zero and the previous call's contents are harmless, but two calls that overlap on the same GPU (different handles or
+//     streams) race on it: serialise them;
+//   * in host code the array's name is only a stand-in; its device address is looked up once per device, with that device
+//     current, through cudaGetSymbolAddress and handed to the kernels.
+#define PMPS_OBS_STATIC_MAX 1024
+#define PMPS_OBS_MAX_DEVICES 64
+static __device__ __align__(256) ObsPartial g_obsScratch[PMPS_OBS_STATIC_MAX];
+static ObsPartial* g_obsScratchAddr[PMPS_OBS_MAX_DEVICES];   // per device ordinal; written once under the lock below
+static std::mutex g_obsScratchLock;
+
+static int obs_static_scratch(pmps_handle* h, ObsPartial** out) {   // h->device is current
+	if (h->device < 0 || h->device >= PMPS_OBS_MAX_DEVICES) return pmps_fail(h, PMPS_E_ARG, "pmps_observe_extent_static: device ordinal %d beyond %d", h->device, PMPS_OBS_MAX_DEVICES - 1);
+	std::lock_guard<std::mutex> g(g_obsScratchLock);
+	if (!g_obsScratchAddr[h->device]) {
+		ObsPartial* p = nullptr;
+		CUDA_TRY(h, cudaGetSymbolAddress((void**)&p, g_obsScratch));
+		if (!p) return pmps_fail(h, PMPS_E_CUDA, "pmps_observe_extent_static: cudaGetSymbolAddress returned no address");
+		g_obsScratchAddr[h->device] = p;
+	}
+	*out = g_obsScratchAddr[h->device];
+	return PMPS_OK;
+}
+
+extern "C" int pmps_observe_extent_static(pmps_t* h, int particleType, double mn[3], double mx[3], long long* count) {
+	if (!h || !mn || !mx) return PMPS_E_ARG;
+	CUDA_TRY(h, cudaSetDevice(h->device));
+	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_observe_extent_static: no particle state uploaded");
+	const int grid = h->smCount * 4;   // same partition as pmps_observe_extent
+	if (grid > PMPS_OBS_STATIC_MAX)
+		return pmps_fail(h, PMPS_E_ARG, "pmps_observe_extent_static: %d partial records needed (4 per SM, %d SMs), the static scratch holds %d", grid, h->smCount, PMPS_OBS_STATIC_MAX);
+	ObsPartial* parts = nullptr;
+	const int rc = obs_static_scratch(h, &parts); if (rc) return rc;
+	k_observe<<<grid, OBS_T, 0, h->stream>>>(h->V, particleType, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0, parts);
+	k_observe_final<<<1, OBS_T, 0, h->stream>>>(parts, grid);
+	h->launches += 2;
+	CUDA_TRY(h, cudaGetLastError());
+	ObsPartial r;
+	CUDA_TRY(h, cudaMemcpyAsync(&r, parts, sizeof(ObsPartial), cudaMemcpyDeviceToHost, h->stream));
+	CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+	for (int k = 0; k < 3; k++) { mn[k] = r.mn[k]; mx[k] = r.mx[k]; }
+	if (count) *count = r.n;
 	return PMPS_OK;
 }
