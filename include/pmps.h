@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define PMPS_ABI_VERSION 3
+#define PMPS_ABI_VERSION 4
 
 enum { PMPS_OK = 0, PMPS_E_ARG = -1, PMPS_E_CUDA = -2, PMPS_E_STATE = -3, PMPS_E_UNSUPPORTED = -4, PMPS_E_OVERFLOW = -5 };
 
@@ -46,14 +46,14 @@ typedef struct PmpsParams {
 	int32_t shiftingType;           /* 0 off, 1 DW*Uij, 2 grad C */
 	int32_t repulsiveForceType;     /* 0 Harada 1 Mitsume 2 Lennard-Jones 3 Monaghan-Kajtar */
 	int32_t fluidType;              /* 0 Newtonian, 1 non-Newtonian (two-phase granular rheology; particle walls only so far) */
-	int32_t domainTypeBC;           /* 0 none (1 = periodic: PMPS_E_UNSUPPORTED) */
+	int32_t domainTypeBC;           /* 0 none, 1 periodic in ONE direction (periodicAxis; src/MpsBucket.cpp:142-289, src/MpsParticle.cpp:238-269) */
 	int32_t ghost, fluid, wall, dummyWall;      /* particle type ids */
 	int32_t surface, inner, other;              /* particleBC ids */
 	int32_t numBucketsX, numBucketsY, numBucketsZ;
 	int32_t numOfMeshs;
 	int32_t shiftingJacobi;         /* 1: shifting reads a position snapshot (default, parallel-safe);
 	                                   the reference's 1-thread behaviour is a Gauss-Seidel sweep in index order */
-	int32_t _pad0;
+	int32_t periodicAxis;           /* domainTypeBC 1: 0 x, 1 y, 2 z (the reference's domain limits accept exactly one periodic direction) */
 	int32_t fractionMethod;         /* PSystem->Fraction_method: 1 neighbour count, 2 weighted (src/MpsViscosity.cpp:106,145) */
 	/* geometry */
 	double domainMinX, domainMinY, domainMinZ, domainMaxX, domainMaxY, domainMaxZ;   /* AFTER the +-3 lo extension */
@@ -81,6 +81,10 @@ typedef struct PmpsParams {
 	double timeCurrent;             /* time at pmps_create; the fused step advances its own copy by timeStep (src/main.cpp:463) */
 	/* ARC free-surface detection (freeSurfType 2), src/MpsParticle.cpp:219-222 */
 	double thetaArc, hThreshold2, dstThreshold2, normThreshold2;
+	/* periodic domain (domainTypeBC 1), along periodicAxis: PSystem->periodicLength[axis], physDomMin / physDomMax of that axis
+	 * (src/MpsBucket.cpp:150-156).  The first and the last bucket layer of the axis alias the last and the first inner layer, shifted
+	 * by -/+ periodicLength (copyDataBetweenBuckets :356-417, getPeriodicLengths src/MpsParticle.cpp:48-54) */
+	double periodicLength, physDomMin, physDomMax;
 } PmpsParams;
 
 /* Pointers into the host's MpsParticle arrays (include/MpsParticle.h:139-241); NULL = not transferred. */

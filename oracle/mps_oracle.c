@@ -39,6 +39,19 @@ static inline void bucket_of(const PmpsParams* P, const double* x, int* bx, int*
 
 /* The one neighbour walk every stage shares (canonical instance src/MpsViscosity.cpp:33-78).
  * Inside BODY: j, rx,ry,rz,d2 (r_ij = x_j - x_i), mx,my,mz,dm2 (x_j - mirror_i).  j == i is NOT filtered here. */
+/* Periodic domain (domainTypeBC 1): the first / last bucket layer of the periodic axis carries the list of the last / first inner
+ * layer (oracle_update_buckets) and its members are seen moved by -/+ periodicLength: r = (x_j + pl) - x_i, two roundings
+ * (getPeriodicLengths + sqrDistBetweenParticles, src/MpsParticle.cpp:35-54). */
+static inline double periodic_shift(const PmpsParams* P, int jb) {
+	/* bucketPeriodicBC is looked up by the LINEAR bucket index (setBucketBC, src/MpsBoundaryCondition.cpp:20-60): a particle that has
+	 * just crossed a periodic face sits in a border layer until the next out-of-domain check, its loop coordinate -1 / n along the axis
+	 * then runs into the neighbouring row of the bucket array, and the shift is that of the bucket actually read */
+	const int nX = P->numBucketsX, nXY = nX * P->numBucketsY;
+	const int jz = jb / nXY, jy = (jb - jz * nXY) / nX, jx = jb - jz * nXY - jy * nX;
+	const int c = P->periodicAxis == 0 ? jx : P->periodicAxis == 1 ? jy : jz;
+	const int n = P->periodicAxis == 0 ? P->numBucketsX : P->periodicAxis == 1 ? P->numBucketsY : P->numBucketsZ;
+	return c == 0 ? -P->periodicLength : c == n - 1 ? P->periodicLength : 0.0;
+}
 #define NEIGH_LOOP(P, A, B, xi, mi, ...)                                                                       \
 	do {                                                                                                       \
 		int bx_, by_, bz_; bucket_of(P, xi, &bx_, &by_, &bz_);                                                 \
@@ -46,8 +59,12 @@ static inline void bucket_of(const PmpsParams* P, const double* x, int* bx, int*
 		const int z0_ = (P)->dim == 3 ? bz_ - 1 : 0, z1_ = (P)->dim == 3 ? bz_ + 1 : 0;                        \
 		for (int jz_ = z0_; jz_ <= z1_; jz_++) for (int jy_ = by_ - 1; jy_ <= by_ + 1; jy_++)                  \
 		for (int jx_ = bx_ - 1; jx_ <= bx_ + 1; jx_++) {                                                       \
-			for (int j = (B)->first[jz_ * nXY_ + jy_ * nX_ + jx_]; j != -1; j = (B)->next[j]) {                 \
-				const double* xj_ = (A)->pos + 3 * (size_t)j;                                                  \
+			const int jb_ = jz_ * nXY_ + jy_ * nX_ + jx_;                                                       \
+			const double pl_ = (P)->domainTypeBC == 1 ? periodic_shift(P, jb_) : 0.0;                           \
+			for (int j = (B)->first[jb_]; j != -1; j = (B)->next[j]) {                                          \
+				const double* xr_ = (A)->pos + 3 * (size_t)j; double xs_[3];                                   \
+				const double* xj_ = xr_;                                                                       \
+				if ((P)->domainTypeBC == 1) { xs_[0] = xr_[0]; xs_[1] = xr_[1]; xs_[2] = xr_[2]; xs_[(P)->periodicAxis] = xr_[(P)->periodicAxis] + pl_; xj_ = xs_; } \
 				const double rx = xj_[0] - (xi)[0], ry = xj_[1] - (xi)[1], rz = xj_[2] - (xi)[2];              \
 				const double d2 = rx * rx + ry * ry + rz * rz;                                                 \
 				const double mx = xj_[0] - (mi)[0], my = xj_[1] - (mi)[1], mz = xj_[2] - (mi)[2];              \
@@ -102,6 +119,15 @@ void oracle_update_buckets(const PmpsParams* P, PmpsHostArrays* A, OBuckets* B) 
 		const int tail = B->last[ib];
 		B->last[ib] = i;
 		if (tail == -1) B->first[ib] = i; else B->next[tail] = i;
+	}
+	if (P->domainTypeBC == 1) {   /* copyDataBetweenBuckets, src/MpsBucket.cpp:356-417: the border layers alias the opposite inner layers */
+		const int nX = P->numBucketsX, nY = P->numBucketsY, nZ = P->numBucketsZ, a = P->periodicAxis;
+		const int nA = a == 0 ? nX : a == 1 ? nY : nZ, stride = a == 0 ? 1 : a == 1 ? nX : nXY;
+		for (int iz = 0; iz < nZ; iz++) for (int iy = 0; iy < nY; iy++) for (int ix = 0; ix < nX; ix++) {
+			const int c = a == 0 ? ix : a == 1 ? iy : iz, ib = iz * nXY + iy * nX + ix;
+			if (c == 0) { B->first[ib] = B->first[ib + stride * (nA - 2)]; B->last[ib] = B->last[ib + stride * (nA - 2)]; }
+			if (c == nA - 1) { B->first[ib] = B->first[ib - stride * (nA - 2)]; B->last[ib] = B->last[ib - stride * (nA - 2)]; }
+		}
 	}
 }
 
@@ -158,6 +184,13 @@ int oracle_check_out_domain(const PmpsParams* P, PmpsHostArrays* A) {
 	const double lo[3] = { P->domainMinX + P->bucketSide, P->domainMinY + P->bucketSide, P->domainMinZ + P->bucketSide };
 	const double hi[3] = { P->domainMaxX - P->bucketSide, P->domainMaxY - P->bucketSide, P->domainMaxZ - P->bucketSide };
 	int live = A->numParticles, removed = 0;
+	if (P->domainTypeBC == 1) {   /* periodic: every particle beyond a face of the physical domain re-enters through the opposite one (src/MpsParticle.cpp:236-269) */
+		for (int i = 0; i < A->numParticles; i++) {
+			double* x = A->pos + 3 * (size_t)i + P->periodicAxis;
+			if (*x > P->physDomMax) *x -= P->periodicLength;
+			if (*x < P->physDomMin) *x += P->periodicLength;
+		}
+	}
 #define MV1(arr) do { if (A->arr) A->arr[i] = A->arr[last]; } while (0)
 #define MV3(arr) do { if (A->arr) for (int k = 0; k < 3; k++) A->arr[3 * (size_t)i + k] = A->arr[3 * (size_t)last + k]; } while (0)
 	for (int i = 0; i < A->numParticles; i++) {   /* the loop bound shrinks as particles are removed (:286,:392) */

@@ -235,6 +235,81 @@ def dam2d_particle(nx: int, nz: int, *, lo: float = 0.005, tank_nx: int | None =
                 ptype=ptype, pos=pos, vel=np.zeros((n, 3)), press=np.zeros(n), tris=None, meta={"H": H, "c0": c0})
 
 
+def channel2d_periodic(nx: int, nz: int, *, lo: float = 0.005, hump: int = 0, drift: float = 1.0, window: float = 0.45,
+                       incompressible: bool = False, name: str | None = None, **overrides) -> Case:
+    """2D open channel, PERIODIC in x, particle walls (the boundary block of input/dam1610_BC.json: type 1, one direction): a floor
+    of one wall + two dummy layers over nx columns, nz layers of fluid on top (+ `hump` more layers over the middle third, so the
+    free surface is not flat), every fluid particle drifting with `drift` * expectMaxVelocity along -x.  The domain limits come from
+    the json (limit 1; setParameters widens them by 3 lo each side first, src/MpsParticle.cpp:139-144) with the window shifted by
+    `window` lo against the lattice: the first fluid column then starts 0.05 lo inside the left face of the physical domain and is
+    wrapped to the right one by the first prediction (src/MpsParticle.cpp:238-269)."""
+    P, T = [], []
+    for jy in range(-3, nz + hump):
+        for ix in range(nx):
+            if jy < 0:
+                P.append(((ix + 0.5) * lo, (jy + 0.5) * lo, 0.0)); T.append(2 if jy == -1 else 3)
+            elif jy < nz or nx // 3 <= ix < 2 * nx // 3:
+                P.append(((ix + 0.5) * lo, (jy + 0.5) * lo, 0.0)); T.append(0)
+    pos = np.array(P); ptype = np.array(T, dtype=np.int32)
+    H = (nz + hump) * lo
+    c0 = 15.0 * math.sqrt(H / 0.3)
+    dt = 0.375 * lo / c0
+    vmax = 2.0 * math.sqrt(9.81 * H)
+    x0, x1 = 0.5 * lo, (nx - 0.5) * lo
+    kw = dict(dim=2, lo=lo, dt=dt, wall_type=0, c0=c0, re_small=2.1, re_large=3.1, gravity=(0.0, -9.81, 0.0),
+              grad_type=0, grad_corr=True, fs_type=0, fs_pnd=0.97, max_vel=vmax,
+              dom_min=(x0 + (3.0 + window) * lo, -0.5 * lo, 0.0), dom_max=(x1 - (3.0 - window) * lo, (2 * (nz + hump) - 2.5) * lo, 0.0))
+    if incompressible:
+        kw.update(mps_type=2, shifting=0, pnd_type=0, dt=dt * 2.0)
+    else:
+        kw.update(mps_type=1, shifting=2, pnd_type=2)
+    kw.update(overrides)
+    opts = base_options(**kw)
+    opts["domain"]["boundary"] = {"type": 1, "limit": 1, "direction": {"x": True, "y": False, "z": False}}
+    n = len(pos)
+    vel = np.zeros((n, 3)); vel[ptype == 0, 0] = -drift * vmax
+    return Case(name=name or "channel2d_periodic_%dx%d" % (nx, nz), options=opts, ptype=ptype, pos=pos, vel=vel, press=np.zeros(n),
+                tris=None, meta={"H": H, "c0": c0})
+
+
+def channel3d_periodic(nx: int, ny: int, nz: int, *, lo: float = 0.01, drift: float = 1.0, window: float = 0.45, jitter: float = 0.0,
+                       seed: int = 11, incompressible: bool = False, name: str | None = None, **overrides) -> Case:
+    """3D open channel along y, PERIODIC in y, polygon walls: floor z = 0 and side walls x = 0, x = 2 nx lo (triangles reaching far
+    beyond both periodic faces), a fluid block of nx * ny * nz particles against the x = 0 wall that fills the whole periodic length
+    ny lo and drifts with `drift` * expectMaxVelocity along -y while it collapses sideways.  Limits from the json as in
+    channel2d_periodic (limit 1, window shifted by `window` lo against the lattice)."""
+    Lx, Lz, far = 2.0 * nx * lo, 2.0 * nz * lo, 50.0 * ny * lo
+    i, j, m = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    order = np.lexsort((i.ravel(), j.ravel(), m.ravel()))
+    pos = np.stack([(i.ravel()[order] + 0.5) * lo, (j.ravel()[order] + 0.5) * lo, (m.ravel()[order] + 0.5) * lo], axis=1)
+    if jitter > 0.0:
+        rng = np.random.default_rng(seed); pos = pos + rng.uniform(-jitter * lo, jitter * lo, size=pos.shape)
+    tris = np.array([
+        [[Lx, far, 0], [0, -far, 0], [0, far, 0]], [[0, -far, 0], [Lx, far, 0], [Lx, -far, 0]],          # floor
+        [[0, far, Lz], [0, -far, 0], [0, -far, Lz]], [[0, -far, 0], [0, far, Lz], [0, far, 0]],          # x = 0
+        [[Lx, far, 0], [Lx, -far, Lz], [Lx, -far, 0]], [[Lx, -far, Lz], [Lx, far, 0], [Lx, far, Lz]],    # x = Lx
+    ], dtype=np.float64)
+    H = nz * lo
+    c0 = 15.0 * math.sqrt(H / 0.3)
+    dt = 0.375 * lo / c0
+    vmax = 2.0 * math.sqrt(9.81 * H)
+    y0, y1 = 0.5 * lo, (ny - 0.5) * lo
+    kw = dict(dim=3, lo=lo, dt=dt, wall_type=1, c0=c0, max_vel=vmax,
+              dom_min=(0.0, y0 + (3.0 + window) * lo, 0.0), dom_max=(Lx, y1 - (3.0 - window) * lo, Lz))
+    if incompressible:
+        kw.update(mps_type=2, grad_type=0, grad_corr=True, shifting=0, pnd_type=0, dt=dt * 2.0)
+    else:
+        kw.update(mps_type=1, grad_type=3, grad_corr=False, shifting=2, pnd_type=2)
+    kw.update(overrides)
+    opts = base_options(**kw)
+    opts["domain"]["boundary"] = {"type": 1, "limit": 1, "direction": {"x": False, "y": True, "z": False}}
+    n = len(pos)
+    vel = np.zeros((n, 3)); vel[:, 1] = -drift * vmax
+    return Case(name=name or "channel3d_periodic_%dx%dx%d" % (nx, ny, nz), options=opts, ptype=np.zeros(n, dtype=np.int32),
+                pos=np.ascontiguousarray(pos), vel=vel, press=np.zeros(n), tris=tris.astype(np.float32).astype(np.float64),
+                meta={"H": H, "c0": c0})
+
+
 def slosh3d(nx: int, ny: int, nz: int, *, lo: float = 0.0093, name: str | None = None, jitter: float = 0.0, **overrides) -> Case:
     """Sloshing tank with MOVING polygon walls (option set of input/sloshing_3D_bulian_lo0p00930.json, BASELINE configs[3]):
     three meshes as in the reference input — rigid and deformable are single far-away triangles, the tank is the FORCED mesh

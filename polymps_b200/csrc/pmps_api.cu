@@ -216,7 +216,17 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	if (params->fluidType != 0 && params->fluidType != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: fluidType %d", params->fluidType);
 	if (params->fluidType == 1 && params->wallType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: the non-Newtonian rheology is on the device path for particle walls only (the polygon-wall variants, src/MpsViscosity.cpp:703-1526, are not: SURVEY 8f row 1)");
 	if (params->fluidType == 1 && params->fractionMethod != 1 && params->fractionMethod != 2) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: fractionMethod %d", params->fractionMethod);
-	if (params->domainTypeBC != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: periodic domain boundaries are not on the device path yet (SURVEY 8f row 4)");
+	if (params->domainTypeBC != 0 && params->domainTypeBC != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: domainTypeBC %d", params->domainTypeBC);
+	if (params->domainTypeBC == 1) {   // periodic in one direction (src/MpsBucket.cpp:142-289)
+		const int a = params->periodicAxis;
+		if (a < 0 || a > 2 || (a == 2 && params->dim == 2)) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: periodicAxis %d in a %dD case", a, params->dim);
+		const int nA = a == 0 ? params->numBucketsX : a == 1 ? params->numBucketsY : params->numBucketsZ;
+		if (!(params->periodicLength > 0.0) || !(params->physDomMax > params->physDomMin)) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: periodic domain without periodicLength / physDomMin / physDomMax");
+		// the two border layers alias inner layers: a tile must not meet a bucket and its alias at once
+		if (nA < 8) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: %d bucket layers along the periodic axis; the device path needs at least 8 (6 inner layers)", nA);
+		if (params->freeSurfType == 2) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: ARC free-surface detection in a periodic domain (the reference's arc test mixes moved and unmoved neighbour positions, src/MpsBoundaryCondition.cpp:205-390)");
+		if (params->fluidType == 1) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: non-Newtonian rheology in a periodic domain is not on the device path");
+	}
 	if (params->freeSurfType < 0 || params->freeSurfType > 2) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: freeSurfType %d", params->freeSurfType);
 	if (params->collisionType != 0 && params->collisionType != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: collisionType %d", params->collisionType);
 	if (params->mpsType < 0 || params->mpsType > 3) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: mpsType %d", params->mpsType);

@@ -10,8 +10,9 @@
 // vel in this launch).  The predicate ignores the mirror particle (it was reset to "infinity" by the prediction, src/main.cpp:286-290).
 #include "pmps_device.cuh"
 
-template <bool FALLBACK> __device__ __forceinline__ void collide_pair(const DevView& S, const KParams& K, const double4& pi, const double4& vi, double mi, int j, double& dx, double& dy, double& dz) {
-	const double4 pj = ld256(S.pos + j);
+template <bool FALLBACK, bool PER> __device__ __forceinline__ void collide_pair(const DevView& S, const KParams& K, int i, const double4& pi, const double4& vi, double mi, int j, double& dx, double& dy, double& dz) {
+	double4 pj = ld256(S.pos + j);
+	if (PER) per_move(K, pj, per_pair_shift(S, K, i, j));   // periodic domain: the partner across the face, as i sees it
 	const double rx = pj.x - pi.x, ry = pj.y - pi.y, rz = pj.z - pi.z; const double d2 = sq3_exact(rx, ry, rz);
 	if (!(d2 < K.p.distCollisionLimit2)) return;
 	const int tj = pk_type(pj);
@@ -26,6 +27,7 @@ template <bool FALLBACK> __device__ __forceinline__ void collide_pair(const DevV
 		else { dx -= 2.0 * rx * f; dy -= 2.0 * ry * f; dz -= 2.0 * rz * f; }
 	}
 }
+template <bool PER>   // PER: periodic domain
 __global__ void __launch_bounds__(256) k_collide(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= S.n0) return;
@@ -39,7 +41,7 @@ __global__ void __launch_bounds__(256) k_collide(const __grid_constant__ DevView
 	const int cnt = S.ccnt[i];
 	if (cnt != 255) {
 		const uint32_t* L = S.clist + (size_t)i * PMPS_CLOSE_CAP;
-		for (int k = 0; k < cnt; k++) collide_pair<false>(S, K, pi, vi, mi, (int)L[k], dx, dy, dz);
+		for (int k = 0; k < cnt; k++) collide_pair<false, PER>(S, K, i, pi, vi, mi, (int)L[k], dx, dy, dz);
 	} else {
 		// more close partners than a list row holds (a badly compressed spot): the 27 (9) buckets around the particle's own, as at the
 		// last rebuild — complete while nobody has moved beyond the search slack
@@ -49,8 +51,9 @@ __global__ void __launch_bounds__(256) k_collide(const __grid_constant__ DevView
 			const bool three = K.p.dim == 3;
 			for (int jz = three ? cz - 1 : 0; jz <= (three ? cz + 1 : 0); jz++) for (int jy = cy - 1; jy <= cy + 1; jy++) for (int jx = cx - 1; jx <= cx + 1; jx++) {
 				if (jx < 0 || jx >= K.p.numBucketsX || jy < 0 || jy >= K.p.numBucketsY || jz < 0 || jz >= K.p.numBucketsZ) continue;
-				const int cj = cell_index(K, jx, jy, jz);
-				for (int j = S.cellStart[cj]; j < S.cellStart[cj + 1]; j++) if (j != i) collide_pair<true>(S, K, pi, vi, mi, j, dx, dy, dz);
+				int ax = jx, ay = jy, az = jz; if (PER) per_alias(K, ax, ay, az);
+				const int cj = cell_index(K, ax, ay, az);
+				for (int j = S.cellStart[cj]; j < S.cellStart[cj + 1]; j++) if (j != i) collide_pair<true, PER>(S, K, i, pi, vi, mi, j, dx, dy, dz);
 			}
 		}
 	}
@@ -62,7 +65,8 @@ __global__ void __launch_bounds__(256) k_collide(const __grid_constant__ DevView
 // both loops of checkParticleCollisions in one launch; the caller swaps the velocity buffers
 int pmps_collide_lists(pmps_handle* h) {
 	if (!h->hitValid) { const int rc = pmps_tv_hits(h); if (rc) return rc; }   // the close-pair lists live and die with the hit list
-	LAUNCH(h, "F2.collision", k_collide, cdiv(h->V.n0, 256), 256, h->V, h->K);
+	if (h->K.p.domainTypeBC == 1) LAUNCH(h, "F2.collision", k_collide<true>, cdiv(h->V.n0, 256), 256, h->V, h->K);
+	else LAUNCH(h, "F2.collision", k_collide<false>, cdiv(h->V.n0, 256), 256, h->V, h->K);
 	CUDA_TRY(h, cudaGetLastError());
 	return PMPS_OK;
 }

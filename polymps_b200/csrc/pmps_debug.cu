@@ -30,7 +30,8 @@ __global__ void __launch_bounds__(TV_T) k_debug_neighbors(const __grid_constant_
 		if (m >= M) continue;   // padding
 		int hb = 0; while (hOff[hb + 1] <= m) hb++;
 		const int j = hBase[hb] + (m - hOff[hb]);
-		const double4 pj = S.pos[j];
+		double4 pj = S.pos[j];
+		if (K.p.domainTypeBC == 1) per_move(K, pj, tv_halo_shift(K, b, hb));   // periodic domain: the records of an aliased border layer
 		Pair q; q.j = j; q.tj = pk_type(pj); q.ptj = pk_ptype(pj);
 		q.rx = pj.x - pi.x; q.ry = pj.y - pi.y; q.rz = pj.z - pi.z; q.d2 = sq3_exact(q.rx, q.ry, q.rz);
 		q.mx = pj.x - mix; q.my = pj.y - miy; q.mz = pj.z - miz; q.dm2 = POLY ? sq3_exact(q.mx, q.my, q.mz) : 0.0;

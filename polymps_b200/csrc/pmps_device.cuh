@@ -114,13 +114,44 @@ __device__ __forceinline__ void track_shift(const DevView& S, int i, double dx, 
 	const float a = (float)dx, b = (float)dy, c = (float)dz; atomic_max_f(S.maxDisp2 + 1, (a * a + b * b + c * c) * 1.0001f);
 }
 
+// ---- periodic domain (domainTypeBC 1, one direction) -------------------------------------------------------------------
+// MpsBucket::copyDataBetweenBuckets gives the first / last bucket layer of the periodic axis the particle list of the last / first
+// INNER layer (src/MpsBucket.cpp:356-417); a neighbour loop that reaches such a layer sees its members moved by
+// bucketPeriodicBC * periodicLength = -/+ L (getPeriodicLengths, src/MpsParticle.cpp:48-54) and forms r = (x_j + pl) - x_i (:35-45).
+__device__ __forceinline__ int per_layers(const KParams& K) { return K.p.periodicAxis == 0 ? K.p.numBucketsX : K.p.periodicAxis == 1 ? K.p.numBucketsY : K.p.numBucketsZ; }
+// bucket coordinates of a border layer -> the inner layer whose particles it holds
+__device__ __forceinline__ void per_alias(const KParams& K, int& ix, int& iy, int& iz) {
+	int& c = K.p.periodicAxis == 0 ? ix : K.p.periodicAxis == 1 ? iy : iz;
+	const int n = per_layers(K);
+	if (c == 0) c = n - 2; else if (c == n - 1) c = 1;
+}
+// what the members of the layer with coordinate c (along the periodic axis) are moved by
+__device__ __forceinline__ double per_shift_of_coord(const KParams& K, int c) { return c == 0 ? -K.p.periodicLength : c == per_layers(K) - 1 ? K.p.periodicLength : 0.0; }
+__device__ __forceinline__ void per_move(const KParams& K, double4& p, double sh) {   // x_j + pl, rounded as the reference rounds it
+	if (K.p.periodicAxis == 0) p.x = __dadd_rn(p.x, sh); else if (K.p.periodicAxis == 1) p.y = __dadd_rn(p.y, sh); else p.z = __dadd_rn(p.z, sh);
+}
+__host__ __device__ __forceinline__ void cell_coords(const KParams& K, int c, int& ix, int& iy, int& iz);
+// for the consumers that hold GLOBAL slots (PPE assembly, close-pair lists, debug hooks): the move of partner j as particle i sees it,
+// from the layers the two were sorted into — partners within reach are either in neighbouring layers or on opposite ends of the axis
+__device__ __forceinline__ double per_pair_shift(const DevView& S, const KParams& K, int i, int j) {
+	int ci[3], cj[3];
+	cell_coords(K, S.cellOf[i], ci[0], ci[1], ci[2]); cell_coords(K, S.cellOf[j], cj[0], cj[1], cj[2]);
+	const int d = cj[K.p.periodicAxis] - ci[K.p.periodicAxis], half = per_layers(K) / 2;
+	return d > half ? -K.p.periodicLength : d < -half ? K.p.periodicLength : 0.0;
+}
+
 // ---- stale bucket lists after an out-of-domain swap ------------------------------------------------------------------
 // checkParticleOutDomain copies the LAST live particle over the one that left (src/MpsParticle.cpp:298-396) but the bucket
 // lists are only re-threaded at the next step start (src/main.cpp:256): until then array element i — now the moved particle —
 // is still listed in the bucket of the particle that left, so a neighbour loop finds it only from there.  hid_visible(): does the
 // 27-bucket search of a particle at pi (bucketCoordinates, src/MpsBucket.cpp:420-425: epsilonZero on every axis) reach `cell`?
+// A particle the periodic wrap moved to the other end of the domain stays threaded on the bucket it started the step in, now a
+// domain length away from where it is: no search that reaches that bucket finds it within any radius.  Its entry carries
+// PMPS_HID_NOWHERE instead of a bucket (pmps_domain.cu, k_ood_flag).
+#define PMPS_HID_NOWHERE (-2)
 __device__ __forceinline__ bool hid_visible(const KParams& K, int cell, const double4& pi) {
 	const PmpsParams& P = K.p;
+	if (cell < 0) return false;
 	const int nX = P.numBucketsX, nXY = nX * P.numBucketsY;
 	const int cz = cell / nXY, cy = (cell - cz * nXY) / nX, cx = cell - cz * nXY - cy * nX;
 	const int bx = bucket_coord(pi.x, P.domainMinX, P.invBucketSide, P.epsilonZero), by = bucket_coord(pi.y, P.domainMinY, P.invBucketSide, P.epsilonZero);
@@ -128,7 +159,7 @@ __device__ __forceinline__ bool hid_visible(const KParams& K, int cell, const do
 	if (P.dim == 2) return cz == 0;   // minZ = maxZ = 0 (src/MpsViscosity.cpp:35)
 	return abs(bucket_coord(pi.z, P.domainMinZ, P.invBucketSide, P.epsilonZero) - cz) <= 1;
 }
-// the bucket the array element of slot `slot` is listed in when the reference's lists are stale for it, else -1
+// the bucket the array element of slot `slot` is listed in when the reference's lists are stale for it (or PMPS_HID_NOWHERE), else -1
 __device__ __forceinline__ int hid_cell_of_slot(const DevView& S, int slot) {
 	const int nh = S.hid[0]; if (nh == 0) return -1;
 	const int label = S.hostIdx[slot];

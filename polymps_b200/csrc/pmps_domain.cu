@@ -1,4 +1,4 @@
-// pmps_domain.cu — MpsParticle::checkParticleOutDomain (reference src/MpsParticle.cpp:234-402, non-periodic branch).
+// pmps_domain.cu — MpsParticle::checkParticleOutDomain (reference src/MpsParticle.cpp:234-402), the periodic wrap included.
 //
 // The reference removes a fluid particle that left [domainMin+bucketSide, domainMax-bucketSide] by copying the LAST
 // live particle over it and turning the last array element into a ghost; the loop is serial and order dependent.  On the
@@ -14,16 +14,45 @@ __device__ __forceinline__ bool out_of_domain(const KParams& K, const double4& p
 	return p.x > hx || p.x < lx || p.y > hy || p.y < ly || (P.dim == 3 && (p.z > hz || p.z < lz));
 }
 
+// Periodic domain: a particle beyond a face of the physical domain re-enters through the opposite one (src/MpsParticle.cpp:236-269, every
+// particle, before the out-of-domain test).  The reference's bucket lists still hold it where it started the step — a domain length
+// away from where it now is — so until the lists are re-threaded at the next step start nobody finds it, while its own search runs
+// around its new position: the wrapped particle gets a hidden-everywhere entry (pmps_device.cuh, PMPS_HID_NOWHERE; a particle wrapped
+// back within the same step loses it again) and the host re-sorts the buckets before the next pass (pmps_check_out_domain).
+// Entries are appended behind the committed ones (hid[0]); k_ood_fix commits them.
+__device__ __forceinline__ void periodic_wrap(const DevView& S, const KParams& K, int i, double4& p) {
+	double& x = K.p.periodicAxis == 0 ? p.x : K.p.periodicAxis == 1 ? p.y : p.z;
+	const double x0 = x;
+	if (x > K.p.physDomMax) x = __dsub_rn(x, K.p.periodicLength);
+	if (x < K.p.physDomMin) x = __dadd_rn(x, K.p.periodicLength);
+	if (x == x0) return;
+	S.pos[i] = p;
+	const int label = S.hostIdx[i], nh0 = S.hid[0];
+	for (int q = 0; q < nh0; q++) if (S.hid[1 + q] == label && S.hid[1 + PMPS_HID_CAP + q] == PMPS_HID_NOWHERE) { S.hid[1 + q] = -1; atomicAdd(&S.flags[FLAG_WRAP_LAST], 1); return; }
+	const int k = atomicAdd(&S.flags[FLAG_WRAPPED], 1);
+	if (nh0 + k < PMPS_HID_CAP) { S.hid[1 + nh0 + k] = label; S.hid[1 + PMPS_HID_CAP + nh0 + k] = PMPS_HID_NOWHERE; }
+}
+
 __global__ void k_ood_flag(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= S.n) return;
-	const double4 p = S.pos[i];
+	double4 p = S.pos[i];
+	if (K.p.domainTypeBC == 1 && pk_type(p) != K.p.ghost && owned_slot(S, i)) periodic_wrap(S, K, i, p);
 	if (pk_type(p) != K.p.fluid || !out_of_domain(K, p) || !owned_slot(S, i)) return;
 	const int k = atomicAdd(&S.flags[FLAG_OOD_COUNT], 1);
 	if (k < PMPS_OOD_CAP) S.oodList[k] = S.hostIdx[i];
 }
 
 __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int staleReplay) {
+	if (K.p.domainTypeBC == 1) {   // commit the entries of the particles this check wrapped; FLAG_WRAP_LAST = particles moved (host: re-sort)
+		const int w = S.flags[FLAG_WRAPPED];
+		if (w > 0) {
+			int nh = S.hid[0] + w;
+			if (nh > PMPS_HID_CAP) { atomicOr(&S.flags[FLAG_GUARD], 8); nh = PMPS_HID_CAP; }
+			S.hid[0] = nh; S.flags[FLAG_WRAPPED] = 0; S.flags[FLAG_WRAP_LAST] += w;
+		}
+		if (S.flags[FLAG_WRAP_LAST] > 0) S.hitMove[0] = 1e30f;
+	}
 	int cnt = S.flags[FLAG_OOD_COUNT];
 	if (cnt == 0) return;
 	S.flags[FLAG_OOD_COUNT] = 0;
@@ -97,6 +126,18 @@ extern "C" int pmps_check_out_domain(pmps_t* h) {
 	LAUNCH(h, "domain.flag", k_ood_flag, cdiv(h->V.n, 256), 256, h->V, h->K);
 	LAUNCH(h, "domain.fix", k_ood_fix, 1, 1, h->V, h->K, h->staleReplay ? 1 : 0);
 	CUDA_TRY(h, cudaGetLastError());
+	if (h->K.p.domainTypeBC == 1) {
+		// periodic domain: a wrapped particle now sits a domain length away from the bucket it is sorted into; the tiles see a particle
+		// through its bucket, so the bucket order is re-made at once (one read-back per check; no particle wrapped = nothing to do)
+		int32_t w = 0;
+		CUDA_TRY(h, cudaMemcpyAsync(&w, h->V.flags + FLAG_WRAP_LAST, sizeof w, cudaMemcpyDeviceToHost, h->stream));
+		CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+		if (w > 0) {
+			CUDA_TRY(h, cudaMemsetAsync(h->V.flags + FLAG_WRAP_LAST, 0, sizeof(int32_t), h->stream));
+			h->nWrapped += w;
+			const int rc = pmps_rebuild_now(h); if (rc) return rc;
+		}
+	}
 	return PMPS_OK;
 }
 

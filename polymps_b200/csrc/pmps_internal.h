@@ -95,9 +95,9 @@ struct DevView {
 	unsigned long long* rheoBL; unsigned long long* rheoWL; int32_t* rheoIdx; unsigned long long* meuMaxBits;
 };
 
-enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, FLAG_UPLOAD_TYPES = 7, NFLAGS = 8 };
+enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, FLAG_UPLOAD_TYPES = 7, FLAG_WRAPPED = 8, FLAG_WRAP_LAST = 9, NFLAGS = 10 };
 #define PMPS_OOD_CAP 65536
-#define PMPS_HID_CAP 1024    // particles moved into a hole by the out-of-domain swap within one step
+#define PMPS_HID_CAP 8192    // particles moved into a hole by the out-of-domain swap, or to the other end of a periodic domain, within one step
 #define PMPS_CLOSE_CAP 16 // close-pair list entries per slot (collision pass)
 #define PMPS_CURSORS 64   // work-stealing cursors per step (one per tile-walker launch)
 
@@ -169,6 +169,7 @@ struct pmps_handle {
 	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;
 	long long launches = 0;
+	long long nWrapped = 0;   // particles moved through a periodic face so far
 	long long nRebuilds = 0, nStepsDone = 0;   // pmps_get_counters: bucket-order rebuilds (sort + Verlet list) and fused steps so far
 	double guardWorst = 0.0;             // sticky: largest displacement since a rebuild that exceeded the search slack (0: never); cleared by pmps_upload
 	int oodTotal = 0, maxCell = 0;
@@ -203,6 +204,7 @@ struct ProfScope {
 // implemented in the .cu files
 int pmps_ensure_capacity(pmps_handle* h, int n0);
 int pmps_sort_and_list(pmps_handle* h);
+int pmps_rebuild_now(pmps_handle* h);   // bucket order + work items + hit list of the current positions, in the middle of a step
 int pmps_ensure_list(pmps_handle* h);
 int pmps_tv_prepare(pmps_handle* h);
 int pmps_tv_hits(pmps_handle* h);

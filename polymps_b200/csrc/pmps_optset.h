@@ -14,11 +14,11 @@
 // X(field, value): InputDamWC / dam1610 WC option set in 3D (weight re/r - 1, gradient type 3 without correction, no-slip, diffusive PND,
 // PC collisions, Lennard-Jones wall repulsion) with the reference's default particle / boundary ids
 #define PMPS_OPTSET_WC3D(X) X(int32_t, weightType, 0) X(int32_t, gradientCorrection, 0) X(int32_t, gradientType, 3) X(int32_t, dim, 3) X(int32_t, slipCondition, 0) \
-	X(int32_t, pndType, 2) X(int32_t, collisionType, 0) X(int32_t, repulsiveForceType, 2) X(int32_t, mpsType, 1) X(int32_t, fluidType, 0) \
+	X(int32_t, pndType, 2) X(int32_t, collisionType, 0) X(int32_t, repulsiveForceType, 2) X(int32_t, mpsType, 1) X(int32_t, fluidType, 0) X(int32_t, domainTypeBC, 0) \
 	X(int32_t, ghost, -1) X(int32_t, fluid, 0) X(int32_t, wall, 2) X(int32_t, dummyWall, 3) X(int32_t, surface, 1) X(int32_t, inner, 0) X(int32_t, other, -1)
 // InputDamINC option set in 3D (gradient type 0 with the correction matrix, PND by sum, implicit pressure)
 #define PMPS_OPTSET_INC3D(X) X(int32_t, weightType, 0) X(int32_t, gradientCorrection, 1) X(int32_t, gradientType, 0) X(int32_t, dim, 3) X(int32_t, slipCondition, 0) \
-	X(int32_t, pndType, 0) X(int32_t, collisionType, 0) X(int32_t, repulsiveForceType, 2) X(int32_t, mpsType, 2) X(int32_t, fluidType, 0) \
+	X(int32_t, pndType, 0) X(int32_t, collisionType, 0) X(int32_t, repulsiveForceType, 2) X(int32_t, mpsType, 2) X(int32_t, fluidType, 0) X(int32_t, domainTypeBC, 0) \
 	X(int32_t, ghost, -1) X(int32_t, fluid, 0) X(int32_t, wall, 2) X(int32_t, dummyWall, 3) X(int32_t, surface, 1) X(int32_t, inner, 0) X(int32_t, other, -1)
 
 enum { PMPS_OPT_GENERIC = 0, PMPS_OPT_WC3D = 1, PMPS_OPT_INC3D = 2, PMPS_OPT_SETS = 3 };

@@ -45,9 +45,11 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ 
 	const int nHid = S.hid[0]; const int myHid = nHid > 0 ? hid_cell_of_slot(S, i) : -1;
 	for (int k = 0; k < cnt; k++) {
 		const int j = (int)L[k];
-		const double4 pj = S.pos[j];
+		double4 pj = S.pos[j];
 		bool iFindsJ = true, jFindsI = true;
-		if (nHid > 0) { const int hc = hid_cell_of_slot(S, j); iFindsJ = hc < 0 || hid_visible(K, hc, pi); jFindsI = myHid < 0 || hid_visible(K, myHid, pj); }
+		if (nHid > 0) { const int hc = hid_cell_of_slot(S, j); iFindsJ = hc == -1 || hid_visible(K, hc, pi); jFindsI = myHid == -1 || hid_visible(K, myHid, pj); }
+		const double pl = K.p.domainTypeBC == 1 ? per_pair_shift(S, K, i, j) : 0.0;   // periodic domain: j as i sees it
+		if (K.p.domainTypeBC == 1) per_move(K, pj, pl);
 		const double rx = pj.x - pi.x, ry = pj.y - pi.y, rz = pj.z - pi.z; const double d2 = sq3_exact(rx, ry, rz);
 		if (!(d2 < K.p.reL2)) continue;
 		const double wL = wgt(sqrt(d2), K.p.reL, K.p.weightType); const double a = wL * K.p.coeffPPE;
@@ -68,7 +70,8 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ 
 			const int bcj = S.particleBC[j];
 			bool theirs = !(bcj == K.p.other || bcj == K.p.surface) && jFindsI;
 			if (POLY && theirs) {
-				const double ex = pi.x - S.mirrorParticlePos.x[j], ey = pi.y - S.mirrorParticlePos.y[j], ez = pi.z - S.mirrorParticlePos.z[j];
+				double4 pim = pi; if (K.p.domainTypeBC == 1) per_move(K, pim, -pl);   // i as j sees it
+				const double ex = pim.x - S.mirrorParticlePos.x[j], ey = pim.y - S.mirrorParticlePos.y[j], ez = pim.z - S.mirrorParticlePos.z[j];
 				theirs = d2 < sq3_exact(ex, ey, ez);
 			}
 			if (theirs) { C[(size_t)nz * 32] = (uint32_t)j; V[(size_t)nz * 32] = a; nz++; }

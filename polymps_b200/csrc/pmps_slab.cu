@@ -57,6 +57,7 @@ extern "C" int pmps_slab_begin(pmps_t* h, int nOwned) {
 	if (!h) return PMPS_E_ARG;
 	if (!h->haveState) return pmps_fail(h, PMPS_E_STATE, "pmps_slab_begin: upload the particle table first");
 	if (h->K.p.fluidType == 1) return pmps_fail(h, PMPS_E_UNSUPPORTED, "pmps_slab_begin: the non-Newtonian rheology (column maps, Cv / MEU / RHO halo fields) is single-GPU so far");
+	if (h->K.p.domainTypeBC == 1) return pmps_fail(h, PMPS_E_UNSUPPORTED, "pmps_slab_begin: periodic domains are single-GPU so far (the slab driver has no wrap-around halo)");
 	if (nOwned < 0 || nOwned > h->numParticles) return pmps_fail(h, PMPS_E_ARG, "pmps_slab_begin: %d owned of %d particles", nOwned, h->numParticles);
 	const PmpsParams& P = h->K.p;
 	if ((P.mpsType == 2 || P.mpsType == 3) && !h->slabSum) return pmps_fail(h, PMPS_E_STATE, "pmps_slab_begin: the incompressible scheme needs pmps_slab_set_hooks first (all-reduce / halo refresh inside the Poisson solve)");

@@ -166,12 +166,18 @@ __global__ void __launch_bounds__(128) k_build_list(const __grid_constant__ DevV
 	const int y0 = max(cy - 1, 0), y1 = min(cy + 1, nY - 1), x0 = max(cx - 1, 0), x1 = min(cx + 1, nX - 1);
 	const unsigned below = (1u << lane) - 1u;
 	for (int jz = z0; jz <= z1; jz++) for (int jy = y0; jy <= y1; jy++) for (int jx = x0; jx <= x1; jx++) {
-		const int cj = cell_index(K, jx, jy, jz);
+		int ax = jx, ay = jy, az = jz; float sx = 0.f, sy = 0.f, sz = 0.f;
+		if (K.p.domainTypeBC == 1) {   // periodic domain: a border layer holds the opposite inner layer, moved by -/+ periodicLength
+			const float sh = (float)per_shift_of_coord(K, K.p.periodicAxis == 0 ? jx : K.p.periodicAxis == 1 ? jy : jz);
+			per_alias(K, ax, ay, az);
+			if (K.p.periodicAxis == 0) sx = sh; else if (K.p.periodicAxis == 1) sy = sh; else sz = sh;
+		}
+		const int cj = cell_index(K, ax, ay, az);
 		const int s0 = S.cellStart[cj], s1 = S.cellStart[cj + 1];
 		for (int base = s0; base < s1; base += 32) {
 			const int j = base + lane; bool hit = false;
 			if (j < s1) {
-				const float4 bj = S.bpos[j];
+				float4 bj = S.bpos[j]; bj.x += sx; bj.y += sy; bj.z += sz;
 				const float dx = bj.x - bi.x, dy = bj.y - bi.y, dz = bj.z - bi.z;
 				hit = dx * dx + dy * dy + dz * dz < K.rl2 && j != i;
 			}
@@ -264,8 +270,13 @@ static int launch_hl_build(pmps_handle* h, const char* name, int force) {
 	DevView& S = h->V;
 	if (h->walkSeq >= PMPS_CURSORS) return pmps_fail(h, PMPS_E_STATE, "more than %d tile passes since the last pmps_update_buckets", PMPS_CURSORS - 1);
 	const size_t smem = 16 * (size_t)(TV_MAXM + 4) + (size_t)HL_T * HL_ROW * 2 + 4 * (size_t)(TV_MAXM + 4);   // float positions (+ the dummy record) + the first chunk of one list row per lane + staged index -> slot
-	CUDA_TRY(h, cudaFuncSetAttribute(k_hl_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	{ ProfScope ps_(h, name); k_hl_build<<<h->smCount * 5, HL_T, smem, h->stream>>>(S, h->K, h->walkSeq++, force); h->launches++; }
+	if (h->K.p.domainTypeBC == 1) {
+		CUDA_TRY(h, cudaFuncSetAttribute(k_hl_build<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		ProfScope ps_(h, name); k_hl_build<true><<<h->smCount * 5, HL_T, smem, h->stream>>>(S, h->K, h->walkSeq++, force); h->launches++;
+	} else {
+		CUDA_TRY(h, cudaFuncSetAttribute(k_hl_build<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		ProfScope ps_(h, name); k_hl_build<false><<<h->smCount * 5, HL_T, smem, h->stream>>>(S, h->K, h->walkSeq++, force); h->launches++;
+	}
 	CUDA_TRY(h, cudaGetLastError());
 	return PMPS_OK;
 }

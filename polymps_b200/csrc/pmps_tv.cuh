@@ -127,9 +127,16 @@ __device__ __forceinline__ TvBox tv_box(const KParams& K, int item) {
 // cell of halo bucket hb of the box, or -1 outside the bucket grid
 __device__ __forceinline__ int tv_halo_cell(const KParams& K, const TvBox& b, int hb) {
 	const int hz = hb / (b.HX * b.HY), hy = (hb - hz * b.HX * b.HY) / b.HX, hx = hb - (hz * b.HY + hy) * b.HX;
-	const int ix = b.ox - 1 + hx, iy = b.oy - 1 + hy, iz = K.p.dim == 3 ? b.oz - 1 + hz : 0;
+	int ix = b.ox - 1 + hx, iy = b.oy - 1 + hy, iz = K.p.dim == 3 ? b.oz - 1 + hz : 0;
 	if (ix < 0 || ix >= K.p.numBucketsX || iy < 0 || iy >= K.p.numBucketsY || iz < 0 || iz >= K.p.numBucketsZ) return -1;
+	if (K.p.domainTypeBC == 1) per_alias(K, ix, iy, iz);   // periodic: a border layer holds the particles of the opposite inner layer
 	return cell_index(K, ix, iy, iz);
+}
+// periodic domain: what the records of halo bucket hb are moved by along the periodic axis (pmps_device.cuh, per_shift_of_coord)
+__device__ __forceinline__ double tv_halo_shift(const KParams& K, const TvBox& b, int hb) {
+	const int hz = hb / (b.HX * b.HY), hy = (hb - hz * b.HX * b.HY) / b.HX, hx = hb - (hz * b.HY + hy) * b.HX;
+	const int a = K.p.periodicAxis;
+	return per_shift_of_coord(K, a == 0 ? b.ox - 1 + hx : a == 1 ? b.oy - 1 + hy : b.oz - 1 + hz);
 }
 // halo table in shared memory: hBase[hb] first slot, hOff[hb] first staged index (hOff[HV] = staged records)
 __device__ __forceinline__ void tv_halo_table(const DevView& S, const KParams& K, const TvBox& b, int* hBase, int* hOff) {
@@ -239,7 +246,8 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 
 
 // ---- shared-memory image of the halo ------------------------------------------------------------------------------
-#define TV_HIDMAX 16   // staged records of one work item the reference's stale bucket lists may hide (pmps_device.cuh, hid_visible)
+#define TV_W_HIDDEN 0x40000000   // bit of the float type word (list build only): the record is found by nobody (a particle the periodic wrap moved in this step)
+#define TV_HIDMAX 32   // staged records of one work item the reference's stale bucket lists may hide (pmps_device.cuh, hid_visible)
 struct TvStage {   // shared-memory planes of the staged halo: the walker stages {x, y} / {z, type word} pairs of doubles (two 16-byte planes: a candidate
 	// is two 128-bit loads, and 8 consecutive records cover all 32 banks), the list build float positions
 	float4* fpos; double2 *pxy, *pzw; Nb nb;
@@ -301,9 +309,26 @@ __device__ __forceinline__ void tv_stage(const DevView& S, const TvStage& T, con
 	}
 	asm volatile("cp.async.wait_all;" ::: "memory");
 }
+// Periodic domain: the records of the aliased border layers are seen moved by -/+ periodicLength, x_j + pl with its own rounding as
+// in the reference (src/MpsParticle.cpp:35-45).  Every thread moves the records it copied itself (same warp -> bucket, lane -> record
+// mapping as tv_stage, whose cp.async.wait_all made them visible to it); the block barrier after the staging publishes them.
+template <int NT = TV_T>
+__device__ __forceinline__ void tv_stage_periodic(const KParams& K, const TvBox& b, const TvStage& T, const int* hOff) {
+	constexpr int NW = NT / 32;
+	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, a = K.p.periodicAxis;
+	for (int hb = warp; hb < b.HV; hb += NW) {
+		const double sh = tv_halo_shift(K, b, hb);
+		if (sh == 0.0) continue;
+		const int off = hOff[hb], n = hOff[hb + 1] - off;
+		for (int r = lane; r < n; r += 32) {
+			const int m = off + r;
+			if (a == 0) T.pxy[m].x = __dadd_rn(T.pxy[m].x, sh); else if (a == 1) T.pxy[m].y = __dadd_rn(T.pxy[m].y, sh); else T.pzw[m].x = __dadd_rn(T.pzw[m].x, sh);
+		}
+	}
+}
 // float positions (+ type word) of the halo for the list build
-template <int NT>
-__device__ __forceinline__ void tv_stage_float(const DevView& S, float4* fpos, int32_t* slotOf, const int* hOff, const int* hBase, int HV, double ox, double oy, double oz) {
+template <int NT, bool PER>
+__device__ __forceinline__ void tv_stage_float(const DevView& S, const KParams& K, const TvBox& bx, float4* fpos, int32_t* slotOf, const int* hOff, const int* hBase, int HV, double ox, double oy, double oz) {
 	constexpr int NB = 4;   // buckets per thread whose position loads are in flight together
 	constexpr int NW = NT / 32;
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -314,6 +339,7 @@ __device__ __forceinline__ void tv_stage_float(const DevView& S, float4* fpos, i
 			const int hb = hb0 + b * NW;
 			ok[b] = false; m[b] = 0;
 			if (hb < HV) { const int off = hOff[hb]; ok[b] = lane < hOff[hb + 1] - off; m[b] = off + lane; if (ok[b]) p[b] = ld256(S.pos + hBase[hb] + lane); }
+			if (PER && hb < HV && ok[b]) per_move(K, p[b], tv_halo_shift(K, bx, hb));
 		}
 		#pragma unroll
 		for (int b = 0; b < NB; b++) if (ok[b]) { fpos[m[b]] = make_float4((float)(p[b].x - ox), (float)(p[b].y - oy), (float)(p[b].z - oz), tv_type_word(p[b])); slotOf[m[b]] = hBase[hb0 + b * NW] + lane; }
@@ -322,7 +348,8 @@ __device__ __forceinline__ void tv_stage_float(const DevView& S, float4* fpos, i
 			const int hb = hb0 + b * NW;
 			if (hb >= HV) continue;
 			const int off = hOff[hb], n = hOff[hb + 1] - off, s0 = hBase[hb];
-			for (int r = lane + 32; r < n; r += 32) { const double4 q = ld256(S.pos + s0 + r); fpos[off + r] = make_float4((float)(q.x - ox), (float)(q.y - oy), (float)(q.z - oz), tv_type_word(q)); slotOf[off + r] = s0 + r; }
+			const double sh = PER ? tv_halo_shift(K, bx, hb) : 0.0;
+			for (int r = lane + 32; r < n; r += 32) { double4 q = ld256(S.pos + s0 + r); if (PER) per_move(K, q, sh); fpos[off + r] = make_float4((float)(q.x - ox), (float)(q.y - oy), (float)(q.z - oz), tv_type_word(q)); slotOf[off + r] = s0 + r; }
 		}
 	}
 }
@@ -344,6 +371,7 @@ __device__ __forceinline__ void tv_stage_float(const DevView& S, float4* fpos, i
 #define HL_T 128
 #define HL_ROW (TV_CHUNK + 2)   // 16-bit entries per shared-memory row: the first chunk of a list ((HL_ROW / 2) is odd: lanes fall into different banks)
 #ifdef PMPS_TV_LISTBUILD   // (compiled only where it is launched: pmps_sort.cu)
+template <bool PER>   // PER: periodic domain (aliased border layers, their records moved by -/+ periodicLength)
 static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int cursorIdx, int force) {
 	if (!force && !S.hitFlag[0]) return;   // k_hits_decide: the hit list still covers the current positions
 	extern __shared__ __align__(16) unsigned char smemRaw[];
@@ -377,7 +405,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 		}
 		const double ox = K.p.domainMinX + (double)(b.ox - 1) * K.p.bucketSide, oy = K.p.domainMinY + (double)(b.oy - 1) * K.p.bucketSide,
 		             oz = three ? K.p.domainMinZ + (double)(b.oz - 1) * K.p.bucketSide : 0.0;
-		tv_stage_float<HL_T>(S, fpos, slotOf, hOff, hBase, b.HV, ox, oy, oz);
+		tv_stage_float<HL_T, PER>(S, K, b, fpos, slotOf, hOff, hBase, b.HV, ox, oy, oz);
 		if (tid == 0) fpos[M] = make_float4(1e18f, 1e18f, 1e18f, 0.f);   // the far-away dummy record: what a lane reads beyond the end of its stretch
 		if (nHidAll > 0) {   // which staged records of this item are hidden entries (S.hid)?  One thread per entry.
 			if (tid == 0) sHid.n = 0;
@@ -387,14 +415,25 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 				if (label < 0) continue;
 				const int slot = S.slotOfHost[label], c = S.cellOf[slot];
 				if (c >= S.nC) continue;
-				int ix, iy, iz; cell_coords(K, c, ix, iy, iz);
-				const int gx = ix - b.ox + 1, gy = iy - b.oy + 1, gz = three ? iz - b.oz + 1 : 0;
-				if (gx < 0 || gx >= b.HX || gy < 0 || gy >= b.HY || gz < 0 || gz >= b.HZ) continue;
-				const int hb = (gz * b.HY + gy) * b.HX + gx, r = slot - hBase[hb];
-				if (r < 0 || r >= hOff[hb + 1] - hOff[hb]) continue;
-				const int k = atomicAdd(&sHid.n, 1);
-				if (k < TV_HIDMAX) { sHid.m[k] = hOff[hb] + r; sHid.cell[k] = S.hid[1 + PMPS_HID_CAP + e]; }
-				else atomicOr(&S.flags[FLAG_GUARD], 8);
+				int cc[3]; cell_coords(K, c, cc[0], cc[1], cc[2]);
+				// (periodic domain: the record is staged where its bucket is and where the border layer that aliases its bucket is)
+				const int nAx = K.p.periodicAxis == 0 ? K.p.numBucketsX : K.p.periodicAxis == 1 ? K.p.numBucketsY : K.p.numBucketsZ;
+				const int alias = !PER ? -1 : cc[K.p.periodicAxis] == nAx - 2 ? 0 : cc[K.p.periodicAxis] == 1 ? nAx - 1 : -1;
+				for (int v = 0; v < (alias >= 0 ? 2 : 1); v++) {
+					if (v == 1) cc[K.p.periodicAxis] = alias;
+					const int gx = cc[0] - b.ox + 1, gy = cc[1] - b.oy + 1, gz = three ? cc[2] - b.oz + 1 : 0;
+					if (gx < 0 || gx >= b.HX || gy < 0 || gy >= b.HY || gz < 0 || gz >= b.HZ) continue;
+					const int hb = (gz * b.HY + gy) * b.HX + gx, r = slot - hBase[hb];
+					if (r < 0 || r >= hOff[hb + 1] - hOff[hb]) continue;
+					const int listed = S.hid[1 + PMPS_HID_CAP + e];
+					if (PER && listed == PMPS_HID_NOWHERE) {   // a particle the periodic wrap moved (a whole layer of them may sit in one item): found by nobody,
+						fpos[hOff[hb] + r].w = __int_as_float(__float_as_int(fpos[hOff[hb] + r].w) | TV_W_HIDDEN);   // marked in its own record
+						continue;
+					}
+					const int k = atomicAdd(&sHid.n, 1);
+					if (k < TV_HIDMAX) { sHid.m[k] = hOff[hb] + r; sHid.cell[k] = listed; }
+					else atomicOr(&S.flags[FLAG_GUARD], 8);
+				}
 			}
 		}
 		__syncthreads();
@@ -445,7 +484,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 					}
 					#pragma unroll
 					for (int u = 0; u < 4; u++) {   // (the row address is kept in a register by hand: under the 80-register cap ptxas re-derives it from %tid for every store)
-						const bool hit = d2[u] < R2;
+						const bool hit = d2[u] < R2 && !(PER && (__float_as_int(f[u].w) & TV_W_HIDDEN));
 						if (hit && cnt < TV_CHUNK) asm volatile("st.shared.u16 [%0], %1;" :: "r"(rowS + 2u * (unsigned)cnt), "h"((unsigned short)m[u]) : "memory");
 						cnt += hit ? 1 : 0;
 					}
@@ -469,7 +508,7 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 					for (int mm = hOff[hb0]; mm < hOff[hb0 + 3]; mm++) {
 						if (mm == self) continue;
 						const float4 f = fpos[mm]; const float dx = f.x - fi.x, dy2 = f.y - fi.y, dz2 = f.z - fi.z;
-						bool hit = dx * dx + dy2 * dy2 + dz2 * dz2 < R2;
+						bool hit = dx * dx + dy2 * dy2 + dz2 * dz2 < R2 && !(PER && (__float_as_int(f.w) & TV_W_HIDDEN));
 						if (HID && hit) for (int q = 0; q < nHid; q++) if (sHid.m[q] == mm && !hid_visible(K, sHid.cell[q], S.pos[i])) hit = false;
 						if (hit) {
 							if (c2 >= TV_CHUNK && c2 < cap) grow[tv_list_pos(c2)] = (uint16_t)mm;
@@ -707,6 +746,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 			if (POLY) sHas[p] = S.distParticleWall2[own0 + p] < K.mirrorFar2 ? 1 : 0;
 		}
 		tv_stage<FIELDS>(S, T, hOff, hBase, b.HV, own0, P, ownMap);
+		if (K.p.domainTypeBC == 1) tv_stage_periodic(K, b, T, hOff);
 		if (tid == 0) { T.pxy[M] = make_double2(1e30, 1e30); T.pzw[M] = make_double2(1e30, 0.0); }   // the record list padding points at
 		__syncthreads();   // the staged halo, ownMap and the per-particle scalars are visible to every thread
 		const uint4* const Ls = (const uint4*)(rowsBuf + (size_t)grp * TV_LROW) + g * (TV_PER / 8);   // this lane's part of its group's row

@@ -87,6 +87,12 @@ PmpsParams params_of(MpsParticleSystem* S) {
 #undef C
 	p.fractionMethod = S->Fraction_method;
 	for (int k = 0; k < 3; k++) p.uniformVelWall[k] = S->uniformVelWall[k];
+	if (S->domainTypeBC == 1) {   // periodic domain: the one direction calcDomainLimits handled (src/MpsBucket.cpp:142-289)
+		const int a = S->periodicDirectionX ? 0 : S->periodicDirectionY ? 1 : 2;
+		p.periodicAxis = a; p.periodicLength = S->periodicLength[a];
+		p.physDomMin = a == 0 ? S->physDomMinX : a == 1 ? S->physDomMinY : S->physDomMinZ;
+		p.physDomMax = a == 0 ? S->physDomMaxX : a == 1 ? S->physDomMaxY : S->physDomMaxZ;
+	}
 	return p;
 }
 

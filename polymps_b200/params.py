@@ -395,9 +395,10 @@ class ParticleSystem:
         if int(self.dim) == 2:
             self.numBucketsZ = 1
         self.periodicLength = [0.0, 0.0, 0.0]
+        self.periodicAxis = 0; self.periodicLen = 0.0; self.physDomMin = 0.0; self.physDomMax = 0.0
         if self.domainTypeBC == 1:
-            raise NotImplementedError("periodic domain BC is out of scope this round (SURVEY §8f row 4)")
-        if self.wallType == 0:
+            self._periodic_limits(pos)
+        elif self.wallType == 0:
             if self.limitTypeBC == 0:
                 if pos is None:
                     raise ValueError("particle walls: initial positions are needed for the domain limits")
@@ -427,13 +428,61 @@ class ParticleSystem:
         self.numBucketsXYZ = self.numBucketsXY * self.numBucketsZ
         return self
 
+    def _periodic_limits(self, pos):
+        """calcDomainLimits, periodic branch (src/MpsBucket.cpp:142-289): ONE periodic direction.  Along it the physical domain is
+        the particle extent (or the json limits) widened by half a particle distance each side, bucketSide is shrunk so that a whole
+        number of buckets covers the periodic length, and one more bucket layer is added on each side — the layers that alias the
+        opposite inner layers (copyDataBetweenBuckets, :356-417).  The other directions get one bucket of margin."""
+        dirs = [self.periodicDirectionX, self.periodicDirectionY, self.periodicDirectionZ]
+        if sum(1 for d in dirs if d) != 1:
+            raise ValueError("periodic domain: exactly one of direction.x / .y / .z must be true (the reference's limits handle one)")
+        a = dirs.index(True)
+        if a == 2 and int(self.dim) == 2:
+            raise ValueError("periodic domain: direction z in a 2D case")
+        json_lim = [[self.domainMinX, self.domainMaxX], [self.domainMinY, self.domainMaxY], [self.domainMinZ, self.domainMaxZ]]
+        if self.limitTypeBC == 0:
+            if pos is None:
+                raise ValueError("periodic domain with limit 0: initial positions are needed for the domain limits")
+            lim = [[float(pos[:, k].min()), float(pos[:, k].max())] for k in range(3)]
+            testdim = sum(1 for k in range(3) if lim[k][0] != lim[k][1])
+            if testdim != self.dim:
+                raise ValueError("Dimensions in json [%d] and grid file [%d] do not match!" % (int(self.dim), testdim))
+        else:
+            lim = [list(v) for v in json_lim]
+        nb = [self.numBucketsX, self.numBucketsY, self.numBucketsZ]
+        L = lim[a][1] - lim[a][0] + self.partDist
+        lim[a][0] -= self.partDist * 0.5
+        lim[a][1] += self.partDist * 0.5
+        phys = (lim[a][0], lim[a][1])
+        nb[a] = int((lim[a][1] - lim[a][0]) / self.bucketSide)
+        self.bucketSide = L / int(L / self.bucketSide)
+        lim[a][0] -= self.bucketSide
+        lim[a][1] += self.bucketSide
+        nb[a] += 2
+        others = [k for k in range(3) if k != a and (k < 2 or int(self.dim) == 3 or a == 2)]
+        for k in others:
+            if self.wallType == 0:
+                lim[k][0] -= self.bucketSide
+                lim[k][1] += self.bucketSide
+            else:
+                lim[k] = [json_lim[k][0] - self.bucketSide, json_lim[k][1] + self.bucketSide]
+            nb[k] = int((lim[k][1] - lim[k][0]) / self.bucketSide + 1)
+            lim[k][1] = lim[k][0] + nb[k] * self.bucketSide
+        self.periodicLength = [0.0, 0.0, 0.0]; self.periodicLength[a] = L
+        self.periodicAxis = a; self.periodicLen = L; self.physDomMin, self.physDomMax = phys
+        self.numBucketsX, self.numBucketsY, self.numBucketsZ = nb
+        self.domainMinX, self.domainMaxX = lim[0]
+        self.domainMinY, self.domainMaxY = lim[1]
+        self.domainMinZ, self.domainMaxZ = lim[2]
+        self.invBucketSide = 1.0 / self.bucketSide
+
 
 # ---------------------------------------------------------------------- ctypes mirror of PmpsParams (include/pmps.h)
 class PmpsParams(ctypes.Structure):
     _I = ["abi_version", "dim", "wallType", "mpsType", "solverType", "pndType", "weightType", "gradientType",
           "gradientCorrection", "slipCondition", "freeSurfType", "collisionType", "shiftingType", "repulsiveForceType",
           "fluidType", "domainTypeBC", "ghost", "fluid", "wall", "dummyWall", "surface", "inner", "other",
-          "numBucketsX", "numBucketsY", "numBucketsZ", "numOfMeshs", "shiftingJacobi", "_pad0", "fractionMethod"]
+          "numBucketsX", "numBucketsY", "numBucketsZ", "numOfMeshs", "shiftingJacobi", "periodicAxis", "fractionMethod"]
     _D = ["domainMinX", "domainMinY", "domainMinZ", "domainMaxX", "domainMaxY", "domainMaxZ", "bucketSide", "invBucketSide",
           "partDist", "timeStep", "epsilonZero", "reS", "reL", "reS2", "reL2", "gravityX", "gravityY", "gravityZ",
           "densityWall", "DNS_FL1", "DNS_FL2", "soundSpeed", "gamma", "relaxPress", "alphaCompressibility",
@@ -445,23 +494,25 @@ class PmpsParams(ctypes.Structure):
            "delta2", "velMax"]
     _D3 = ["KNM_VS1", "KNM_VS2", "DNS_SDT", "PHI_1", "PHI_2", "cohes", "MEU0", "DG", "I0", "mm", "Cd", "VF_min", "VF_max", "relaxPND", "timeCurrent",
            "thetaArc", "hThreshold2", "dstThreshold2", "normThreshold2"]
+    _D4 = ["periodicLength", "physDomMin", "physDomMax"]   # of the periodic axis (ParticleSystem.periodicLen / physDomMin / physDomMax)
     _fields_ = ([(n, ctypes.c_int32) for n in _I] + [(n, ctypes.c_double) for n in _D]
-                + [("uniformVelWall", ctypes.c_double * 3)] + [(n, ctypes.c_double) for n in _D2 + _D3])
+                + [("uniformVelWall", ctypes.c_double * 3)] + [(n, ctypes.c_double) for n in _D2 + _D3 + _D4])
 
 
 def to_c_params(ps: ParticleSystem, shifting_jacobi: bool = True) -> PmpsParams:
     c = PmpsParams()
     for n in PmpsParams._I:
         if n == "abi_version":
-            c.abi_version = 3
+            c.abi_version = 4
         elif n == "shiftingJacobi":
             c.shiftingJacobi = 1 if shifting_jacobi else 0
-        elif n == "_pad0":
-            c._pad0 = 0
+        elif n == "periodicAxis":
+            c.periodicAxis = int(getattr(ps, "periodicAxis", 0))
         else:
             setattr(c, n, int(getattr(ps, n)))
     for n in PmpsParams._D + PmpsParams._D2 + PmpsParams._D3:
         setattr(c, n, float(getattr(ps, n)))
     for k in range(3):
         c.uniformVelWall[k] = float(ps.uniformVelWall[k])
+    c.periodicLength = float(getattr(ps, "periodicLen", 0.0)); c.physDomMin = float(getattr(ps, "physDomMin", 0.0)); c.physDomMax = float(getattr(ps, "physDomMax", 0.0))
     return c

@@ -153,7 +153,24 @@ def _splash(a, b):
     return (lambda: cases.dam3d_splash(*a, name="var"), lambda: cases.dam3d_splash(*b, name="var"))
 
 
+def _per2(**kw):
+    from polymps_b200 import cases
+    return (lambda: cases.channel2d_periodic(24, 6, hump=3, name="var", **kw), lambda: cases.channel2d_periodic(64, 14, hump=6, name="var", **kw))
+
+
+def _per3(**kw):
+    from polymps_b200 import cases
+    return (lambda: cases.channel3d_periodic(5, 22, 5, jitter=0.05, name="var", **kw), lambda: cases.channel3d_periodic(8, 30, 8, jitter=0.04, name="var", **kw))
+
+
 VARIANTS = {
+    # periodic domain (one direction): alias bucket layers + shifted pair geometry + the wrap at every out-of-domain check
+    # (src/MpsBucket.cpp:142-289,356-417, src/MpsParticle.cpp:35-54,236-269); the drifting channel wraps particles from the first step on
+    "2d_per": _per2(), "2d_per_right": _per2(drift=-1.0, window=-0.45), "2d_per_inc": _per2(incompressible=True), "2d_per_dpc": _per2(collision=1),
+    # (the larger block also for the live reference run: in its first step a near-wall particle crosses the face during the shifting and
+    # takes the wall-shifting pass from INSIDE the aliased border layer — its search then runs over the end of a bucket row)
+    "3d_per_edge": (lambda: __import__("polymps_b200.cases", fromlist=["x"]).channel3d_periodic(8, 30, 8, jitter=0.04, name="var"),) * 2,
+    "3d_per": _per3(), "3d_per_right": _per3(drift=-1.0, window=-0.45), "3d_per_inc": _per3(incompressible=True),
     "ood": _splash((6, 5, 5), (14, 8, 10)),   # particles leave the domain (swap-with-last compaction, src/MpsParticle.cpp:286-396)
     "slip": _v3(slip=1), "grad0": _v3(grad_type=0), "grad1": _v3(grad_type=1), "grad2": _v3(grad_type=2),
     "gradcorr": _v3(grad_type=3, grad_corr=True), "rep0": _v3(rep_type=0), "rep1": _v3(rep_type=1), "rep3": _v3(rep_type=3),

@@ -40,3 +40,26 @@ def test_oracle_matches_live_reference_on_option_variant(name):
                 assert orc.P.velMax == float(cur["scalars"][0])
             n += 1
     assert n >= 20
+
+
+@pytest.mark.parametrize("name", sorted(n for n in VARIANTS if "per" in n))
+def test_periodic_domain_limits_equal_the_references_and_particles_wrap(name):
+    """polymps_b200/params.py, periodic branch of calcDomainLimits (src/MpsBucket.cpp:142-289) against the live reference's own
+    parameter block; and the variant does what it is for: particles re-enter through the opposite face in the dumped steps."""
+    if not refrun.have_ref():
+        pytest.skip("oracle/_ref/ref_driver not built (needs /root/reference)")
+    case = VARIANTS[name][0]()
+    order, dumps, params = reference_dumps(case, (1, 2))
+    ps = ParticleSystem.from_json(case.options).set_parameters(); ps.allocate_buckets(case.pos)
+    for k in ("numBucketsX", "numBucketsY", "numBucketsZ", "bucketSide", "invBucketSide", "domainMinX", "domainMaxX", "domainMinY", "domainMaxY", "domainMinZ", "domainMaxZ"):
+        assert float(params[k]) == float(getattr(ps, k)), (k, params[k], getattr(ps, k))
+    ax = "XYZ"[ps.periodicAxis]
+    assert float(params["physDomMin" + ax]) == ps.physDomMin and float(params["physDomMax" + ax]) == ps.physDomMax
+    assert [float(v) for v in params["periodicLength"]] == [float(v) for v in ps.periodicLength] and ps.periodicLen == ps.periodicLength[ps.periodicAxis]
+    wrapped = 0
+    for step in dumped_steps(order):
+        for stage, prev_name, cur_name in stage_sequence(order, step):
+            if stage.startswith("checkParticleOutDomain"):
+                a = np.asarray(dumps[prev_name]["pos"]).reshape(-1, 3)[:, ps.periodicAxis]; b = np.asarray(dumps[cur_name]["pos"]).reshape(-1, 3)[:, ps.periodicAxis]
+                wrapped += int((np.abs(a - b) > 0.5 * ps.periodicLen).sum())
+    assert wrapped >= 3, wrapped
