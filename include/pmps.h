@@ -248,6 +248,15 @@ int pmps_slab_set_hooks(pmps_t* h, double* d_workspace8, pmps_sum_fn sum, pmps_r
  * pmps_observe_box: count, pressure sum and pressure maximum of the particles of one type inside [lo, hi] (probe = sum / count). */
 int pmps_observe_extent(pmps_t* h, int particleType, double mn[3], double mx[3], long long* count);
 int pmps_observe_box(pmps_t* h, int particleType, const double lo[3], const double hi[3], long long* count, double* pressSum, double* pressMax);
+/* pmps_write_vtu: the particle file of an output step, written straight from the device state — the same bytes MpsInputOutput::
+ * writeVtuAscii (flags without PMPS_VTU_FREE_SURFACE_ONLY, src/MpsInputOutput.cpp:1313-1580) or writeVtuAsciiFreeSurface (with it,
+ * :1582-1875: free-surface and wall particles only) puts out for the same state.  flags = the reference's output switches
+ * (flags.output_VTU of the input file, src/MpsInputOutput.cpp:150-170).  Only the arrays the file holds come back from the device;
+ * the text is formatted by all host cores (PMPS_VTU_THREADS overrides the count).  The binary variants of the reference
+ * ("ONLY ASCII WORKING", its own input files say) are not provided. */
+enum { PMPS_VTU_PND = 1, PMPS_VTU_NEIGH = 2, PMPS_VTU_DEVIATION = 4, PMPS_VTU_CONCENTRATION = 8, PMPS_VTU_NONNEWTONIAN = 16,
+       PMPS_VTU_AUXILIAR = 32, PMPS_VTU_FREE_SURFACE_ONLY = 64 };
+int pmps_write_vtu(pmps_t* h, const char* filename, unsigned flags);
 /* pmps_observe_extent_static: same arguments and results as pmps_observe_extent.  No counterpart in the reference; added
  * for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
  * cudaMalloc).  The call allocates nothing: the per-block partial records of the reduction live in a file-scope device array of
@@ -258,6 +267,8 @@ int pmps_observe_box(pmps_t* h, int particleType, const double lo[3], const doub
 int pmps_observe_extent_static(pmps_t* h, int particleType, double mn[3], double mx[3], long long* count);
 
 /* ---- debug / parity hooks (tests only) ---------------------------------------------------------------------- */
+/* "%f " of every value with the formatter pmps_write_vtu uses (host code, no device needed); returns the length written */
+int pmps_debug_format_f6(const double* v, int n, char* out, size_t cap);
 /* bucket id of every host-order particle as the reference computes it at rebuild time, and the members of every
  * bucket in list order (= ascending host index): flattened CSR. members may be NULL to query sizes. */
 int pmps_debug_buckets(pmps_t* h, int32_t* bucketOfParticle, int32_t* bucketStart /* nB+1 */, int32_t* members /* N */);

@@ -92,6 +92,9 @@ def load_library() -> ctypes.CDLL:
     if os.environ.get("PMPS_LIB") is None or hasattr(L, "pmps_observe_extent"):
         L.pmps_observe_extent.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong)]
         L.pmps_observe_box.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]
+    if os.environ.get("PMPS_LIB") is None or hasattr(L, "pmps_write_vtu"):
+        L.pmps_write_vtu.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint]
+        L.pmps_debug_format_f6.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t]
     if os.environ.get("PMPS_LIB") is None or hasattr(L, "pmps_load_grid"):
         L.pmps_load_grid.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_int)]
     L.pmps_set_mesh.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_double), ctypes.c_int,
@@ -248,6 +251,23 @@ class Engine:
         n = ctypes.c_longlong(); s = ctypes.c_double(); m = ctypes.c_double()
         self._chk(self.lib.pmps_observe_box(self.h, int(particle_type), a, b, ctypes.byref(n), ctypes.byref(s), ctypes.byref(m)))
         return int(n.value), float(s.value), float(m.value)
+
+    # ---- output (pmps_write_vtu): the reference's ASCII .vtu file from the device state
+    VTU_PND, VTU_NEIGH, VTU_DEVIATION, VTU_CONCENTRATION, VTU_NONNEWTONIAN, VTU_AUXILIAR, VTU_FREE_SURFACE_ONLY = 1, 2, 4, 8, 16, 32, 64
+
+    def write_vtu(self, path: str, flags: int = 1):
+        """MpsInputOutput::writeVtuAscii / writeVtuAsciiFreeSurface (src/MpsInputOutput.cpp:1313-1875) for the state on the device."""
+        self._chk(self.lib.pmps_write_vtu(self.h, os.fsencode(path), int(flags)))
+
+    @staticmethod
+    def vtu_flags(options: dict) -> int:
+        """flags.output_VTU of an input document -> pmps_write_vtu flags (src/MpsInputOutput.cpp:150-170)."""
+        o = options["flags"]["output_VTU"]
+        f = 0
+        for key, bit in (("pnd", 1), ("neigh", 2), ("deviation", 4), ("concentration", 8), ("non_newtonian", 16), ("auxiliar", 32), ("freeSurfWall", 64)):
+            if o.get(key, False):
+                f |= bit
+        return f
 
     # ---- parity hooks
     def set_stale(self, host_idx, bucket):

@@ -30,6 +30,7 @@
 #include "MpsParticleVelPos.h"
 #include "MpsBoundaryCondition.h"
 #include "PolygonMesh.h"
+#include "MpsInputOutput.h"
 #include "pmps.h"
 
 namespace {
@@ -258,4 +259,22 @@ void PolygonMesh::closestPointPNDBoundaryAABB(double reS2, double reL2, int nP, 
 void PolygonMesh::updateParticlesNearPolygonMesh(double reS2, double reL2, int nP, int wijType, int *Typ, int fld, const double *riw2,
 	double *niw, int *numNeighw, std::vector<int>& meshParticlesNeighbors, bool *Nw) {
 	CALL(pmps_wall_closest_point(handle()));
+}
+
+// ---- output ------------------------------------------------------------------------------------------------------------------
+// MpsInputOutput::writeOutputFiles (src/MpsInputOutput.cpp:861-885) picks one of four writers by flags.output_VTU.  The two ASCII ones
+// (the only ones the reference's input files call working) are replaced by pmps_write_vtu: same bytes, from the device state, formatted
+// by all host cores instead of one fprintf per number.  The binary variants, and PMPS_VTU_HOST=1, run the reference's own writers on the
+// host arrays (refreshed by pull_arrays before every output iteration).
+void MpsInputOutput::writeOutputFiles(MpsParticleSystem *PSystem, MpsParticle *Particles) {
+	if (vtuType == 0 && g_h && !getenv("PMPS_VTU_HOST")) {
+		char name[1024]; snprintf(name, sizeof name, "%s/output%05d.vtu", vtuOutputFoldername.c_str(), PSystem->fileNumber);
+		const unsigned f = (outputPnd ? PMPS_VTU_PND : 0) | (outputNeigh ? PMPS_VTU_NEIGH : 0) | (outputDeviation ? PMPS_VTU_DEVIATION : 0) |
+		                   (outputConcentration ? PMPS_VTU_CONCENTRATION : 0) | (outputNonNewtonian ? PMPS_VTU_NONNEWTONIAN : 0) |
+		                   (outputAuxiliar ? PMPS_VTU_AUXILIAR : 0) | (freeSurfWall ? PMPS_VTU_FREE_SURFACE_ONLY : 0);
+		CALL(pmps_write_vtu(g_h, name, f));
+		return;
+	}
+	if (vtuType == 0) { if (freeSurfWall) writeVtuAsciiFreeSurface(PSystem, Particles); else writeVtuAscii(PSystem, Particles); }
+	else { if (freeSurfWall) writeVtuBinaryFreeSurface(PSystem, Particles); else writeVtuBinary(PSystem, Particles); }
 }
