@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define PMPS_ABI_VERSION 4
+#define PMPS_ABI_VERSION 5
 
 enum { PMPS_OK = 0, PMPS_E_ARG = -1, PMPS_E_CUDA = -2, PMPS_E_STATE = -3, PMPS_E_UNSUPPORTED = -4, PMPS_E_OVERFLOW = -5 };
 
@@ -45,7 +45,7 @@ typedef struct PmpsParams {
 	int32_t collisionType;          /* 0 PC, 1 DPC */
 	int32_t shiftingType;           /* 0 off, 1 DW*Uij, 2 grad C */
 	int32_t repulsiveForceType;     /* 0 Harada 1 Mitsume 2 Lennard-Jones 3 Monaghan-Kajtar */
-	int32_t fluidType;              /* 0 Newtonian, 1 non-Newtonian (two-phase granular rheology; particle walls only so far) */
+	int32_t fluidType;              /* 0 Newtonian, 1 non-Newtonian (two-phase granular rheology; with polygon walls in 3D only, as the reference's wall variants are) */
 	int32_t domainTypeBC;           /* 0 none, 1 periodic in ONE direction (periodicAxis; src/MpsBucket.cpp:142-289, src/MpsParticle.cpp:238-269) */
 	int32_t ghost, fluid, wall, dummyWall;      /* particle type ids */
 	int32_t surface, inner, other;              /* particleBC ids */
@@ -85,6 +85,7 @@ typedef struct PmpsParams {
 	 * (src/MpsBucket.cpp:150-156).  The first and the last bucket layer of the axis alias the last and the first inner layer, shifted
 	 * by -/+ periodicLength (copyDataBetweenBuckets :356-417, getPeriodicLengths src/MpsParticle.cpp:48-54) */
 	double periodicLength, physDomMin, physDomMax;
+	double powerLawN;               /* PSystem->N, physical.rheological.power_law_index: read only by the polygon-wall variants of the rheology (src/MpsViscosity.cpp:1090,1505) */
 } PmpsParams;
 
 /* Pointers into the host's MpsParticle arrays (include/MpsParticle.h:139-241); NULL = not transferred. */
@@ -167,6 +168,8 @@ int pmps_download_device(pmps_t* h, PmpsHostArrays* device_arrays);   /* gather 
 int pmps_update_buckets(pmps_t* h);              /* MpsBucket::updateParticlesID            src/MpsBucket.cpp:299-353 */
 int pmps_calc_volume_fraction(pmps_t* h);        /* MpsViscosity::calcVolumeFraction        src/MpsViscosity.cpp:104-190 (fluidType 1) */
 int pmps_calc_viscosity_interaction(pmps_t* h);  /* MpsViscosity::calcViscosityInteractionVal src/MpsViscosity.cpp:194-700 (fluidType 1) */
+int pmps_calc_wall_viscosity_interaction(pmps_t* h);  /* MpsViscosity::calcWallSlipViscosityInteractionVal / calcWallNoSlipViscosityInteractionVal src/MpsViscosity.cpp:703-1526
+                                                       * (fluidType 1, polygon walls, by slipCondition; called after the one above at src/main.cpp:391-399 only) */
 int pmps_set_time(pmps_t* h, double timeCurrent);/* PSystem->timeCurrent as the rheology reads it (3D branch, src/MpsViscosity.cpp:529) */
 int pmps_calc_viscosity(pmps_t* h);              /* MpsViscosity::calcViscosity             src/MpsViscosity.cpp:20-100 */
 int pmps_add_gravity(pmps_t* h);                 /* MpsParticle::addGravity                 src/MpsParticle.cpp:111-130 */

@@ -1392,6 +1392,114 @@ double oracle_calc_viscosity_interaction(const PmpsParams* P, PmpsHostArrays* A,
 	return P->timeStep * mi_max / ((P->DNS_SDT * P->VF_max + (1.0 - P->VF_max) * P->DNS_FL1) * P->partDist * P->partDist);
 }
 
+/* calcWallSlipViscosityInteractionVal / calcWallNoSlipViscosityInteractionVal, src/MpsViscosity.cpp:703-1111 / :1112-1526 (polygon walls, 3D):
+ * for the fluid particles near a wall the velocity gradient over the MIRROR neighbourhood M(reS) is added to the strain-rate invariant
+ * and the smoothed pressure, and their viscosity is evaluated again — with the older regularised form of the model these two functions
+ * still carry (exponential yield term, power-law index N).  The bed / water level maps are rebuilt from the same state as in
+ * calcViscosityInteractionVal, which always runs right before (src/main.cpp:387-399). */
+void oracle_calc_wall_viscosity_interaction(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B) {
+	const int slip = P->slipCondition == 1;
+	const double gravityMod = sqrt(P->gravityX * P->gravityX + P->gravityY * P->gravityY + P->gravityZ * P->gravityZ);
+	const double Xmin = P->domainMinX, Xmax = P->domainMaxX, Ymin = P->domainMinY;
+	double Ymax = Ymin, Zmin = 0.0;
+	if (P->dim == 3) { Ymax = P->domainMaxY; Zmin = P->domainMinZ; }
+	const double aaL0 = 2.0 * P->partDist;
+	const int kx_max = (int)((Xmax - Xmin) / aaL0) + 1, ky_max = (int)((Ymax - Ymin) / aaL0) + 1;
+	const int stride = ky_max + 1; const size_t cells = (size_t)(kx_max + 1) * stride;
+	double* BL = (double*)malloc(sizeof(double) * cells); double* WL = (double*)malloc(sizeof(double) * cells);
+	for (size_t c = 0; c < cells; c++) { BL[c] = Zmin; WL[c] = Zmin; }
+	for (int i = 0; i < A->numParticles; i++) {   /* :1165-1176 */
+		if (A->particleType[i] != P->fluid) continue;
+		const double* x = A->pos + 3 * (size_t)i;
+		const size_t c = (size_t)((int)((x[0] - Xmin) / aaL0) + 1) * stride + ((int)((x[1] - Ymin) / aaL0) + 1);
+		if (x[2] > BL[c] && A->Cv[i] > 0.5) BL[c] = x[2];
+		if (x[2] > WL[c] && A->PTYPE[i] == 1) WL[c] = x[2];
+	}
+	PARFOR
+	for (int i = 0; i < A->numParticles; i++) {   /* :1179-1345 */
+		if (!(A->particleType[i] == P->fluid && A->particleNearWall[i])) continue;
+		double sum1 = 0.0, sum2 = 0.0, sum3 = 0.0, sum4 = 0.0, sum5 = 0.0, sum6 = 0.0, sum7 = 0.0, sum8 = 0.0, sum9 = 0.0, sum10 = 0.0;
+		const double* xi = A->pos + 3 * (size_t)i; const double* mi = A->mirrorParticlePos + 3 * (size_t)i; const double* vi = A->vel + 3 * (size_t)i;
+		double n[3], R[9]; wall_normal(xi, mi, P->epsilonZero, 1, n); reflection(n, R);
+		double vm[3];
+		if (slip) { for (int k = 0; k < 3; k++) vm[k] = MATVEC(R, vi[0], vi[1], vi[2], k); }   /* v_i' = R v_i, :800-803 */
+		else {   /* v_i' = -(v_i - 2 (v_wall - (n.v_wall) n)), :1214-1240 */
+			double vw[3] = { 0.0, 0.0, 0.0 };
+			if (A->nearMeshType[i] == 2) { vw[0] = P->uniformVelWall[0]; vw[1] = P->uniformVelWall[1]; vw[2] = P->uniformVelWall[2]; }
+			const double dotnv = n[0] * vw[0] + n[1] * vw[1] + n[2] * vw[2];
+			double vt[3]; for (int k = 0; k < 3; k++) vt[k] = vi[k] - 2.0 * (vw[k] - dotnv * n[k]);
+			vm[0] = (-1.0 * vt[0] + 0.0 * vt[1] + 0.0 * vt[2]); vm[1] = (0.0 * vt[0] + -1.0 * vt[1] + 0.0 * vt[2]); vm[2] = (0.0 * vt[0] + 0.0 * vt[1] + -1.0 * vt[2]);
+		}
+		NEIGH_LOOP(P, A, B, xi, mi, {
+			if (PRED_M(P->reS2)) {
+				if (j != i) {
+					const double dst = sqrt(dm2); const double wS = wgt(dst, P->reS, P->weightType);
+					const double ux = A->vel[3 * (size_t)j] - vm[0], uy = A->vel[3 * (size_t)j + 1] - vm[1], uz = A->vel[3 * (size_t)j + 2] - vm[2];
+					sum1 += ux * mx * wS / dm2; sum2 += ux * my * wS / dm2; sum3 += ux * mz * wS / dm2;
+					sum4 += uy * mx * wS / dm2; sum5 += uy * my * wS / dm2; sum6 += uy * mz * wS / dm2;
+					sum7 += uz * mx * wS / dm2; sum8 += uz * my * wS / dm2; sum9 += uz * mz * wS / dm2;
+					sum10 += A->press[j] * wS;
+				}
+			}
+		});
+		double Uxx, Uxy, Uxz, Uyx, Uyy, Uyz, Uzx, Uzy, Uzz; const double cg = P->coeffPressGrad;
+		if (slip) {   /* R (grad u) R, :868-890 */
+			const double aUxx = -cg * (R[0] * sum1 + R[1] * sum4 + R[2] * sum7), aUxy = -cg * (R[0] * sum2 + R[1] * sum5 + R[2] * sum8), aUxz = -cg * (R[0] * sum3 + R[1] * sum6 + R[2] * sum9);
+			const double aUyx = -cg * (R[3] * sum1 + R[4] * sum4 + R[5] * sum7), aUyy = -cg * (R[3] * sum2 + R[4] * sum5 + R[5] * sum8), aUyz = -cg * (R[3] * sum3 + R[4] * sum6 + R[5] * sum9);
+			const double aUzx = -cg * (R[6] * sum1 + R[7] * sum4 + R[8] * sum7), aUzy = -cg * (R[6] * sum2 + R[7] * sum5 + R[8] * sum8), aUzz = -cg * (R[6] * sum3 + R[7] * sum6 + R[8] * sum9);
+			Uxx = aUxx * R[0] + aUxy * R[3] + aUxz * R[6]; Uxy = aUxx * R[1] + aUxy * R[4] + aUxz * R[7]; Uxz = aUxx * R[2] + aUxy * R[5] + aUxz * R[8];
+			Uyx = aUyx * R[0] + aUyy * R[3] + aUyz * R[6]; Uyy = aUyx * R[1] + aUyy * R[4] + aUyz * R[7]; Uyz = aUyx * R[2] + aUyy * R[5] + aUyz * R[8];
+			Uzx = aUzx * R[0] + aUzy * R[3] + aUzz * R[6]; Uzy = aUzx * R[1] + aUzy * R[4] + aUzz * R[7]; Uzz = aUzx * R[2] + aUzy * R[5] + aUzz * R[8];
+		} else {      /* -(grad u) R, :1289-1300 */
+			Uxx = cg * (sum1 * R[0] + sum2 * R[3] + sum3 * R[6]); Uxy = cg * (sum1 * R[1] + sum2 * R[4] + sum3 * R[7]); Uxz = cg * (sum1 * R[2] + sum2 * R[5] + sum3 * R[8]);
+			Uyx = cg * (sum4 * R[0] + sum5 * R[3] + sum6 * R[6]); Uyy = cg * (sum4 * R[1] + sum5 * R[4] + sum6 * R[7]); Uyz = cg * (sum4 * R[2] + sum5 * R[5] + sum6 * R[8]);
+			Uzx = cg * (sum7 * R[0] + sum8 * R[3] + sum9 * R[6]); Uzy = cg * (sum7 * R[1] + sum8 * R[4] + sum9 * R[7]); Uzz = cg * (sum7 * R[2] + sum8 * R[5] + sum9 * R[8]);
+		}
+		A->p_smooth[i] += sum10 / P->pndGradientZero;
+		if (A->p_smooth[i] < P->epsilonZero) A->p_smooth[i] = 0.0;
+		A->S11[i] = 0.5 * (Uxx + Uxx); A->S12[i] = 0.5 * (Uxy + Uyx); A->S13[i] = 0.5 * (Uxz + Uzx);
+		A->S22[i] = 0.5 * (Uyy + Uyy); A->S23[i] = 0.5 * (Uyz + Uzy); A->S33[i] = 0.5 * (Uzz + Uzz);
+		A->II[i] += 0.5 * (A->S11[i] * A->S11[i] + 2.0 * A->S12[i] * A->S12[i] + 2.0 * A->S13[i] * A->S13[i] + A->S22[i] * A->S22[i] + 2.0 * A->S23[i] * A->S23[i] + A->S33[i] * A->S33[i]);
+		if (A->II[i] < P->epsilonZero || A->II[i] * 0 != 0) A->II[i] = 0.0;
+	}
+	for (int i = 0; i < A->numParticles; i++) {   /* :1360-1515 */
+		if (!(A->particleType[i] == P->fluid && A->particleNearWall[i])) continue;
+		const double* x = A->pos + 3 * (size_t)i; const double* v = A->vel + 3 * (size_t)i;
+		const double vel2i = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+		if (A->PTYPE[i] == 1) A->MEU[i] = P->KNM_VS1 * P->DNS_FL1;
+		else if (A->PTYPE[i] == 2) {
+			double phi = (A->Cv[i] - 0.25) * P->PHI_1 / (1.0 - 0.25), phi2 = (A->Cv[i] - 0.25) * P->PHI_2 / (1.0 - 0.25);
+			if (A->Cv[i] <= 0.25) { phi = P->epsilonZero; phi2 = P->epsilonZero; }
+			const size_t c = (size_t)((int)((x[0] - Xmin) / aaL0) + 1) * stride + ((int)((x[1] - Ymin) / aaL0) + 1);
+			double normal_stress = (BL[c] - x[2] + P->partDist * 0.5) * (P->DNS_FL2 - P->DNS_FL1) * gravityMod - vel2i * (P->DNS_FL2 - P->DNS_FL1) * 0.5;
+			if (A->p_smooth[i] < (WL[c] - x[2]) * P->DNS_FL1 * gravityMod) A->p_smooth[i] = (WL[c] - x[2]) * P->DNS_FL1 * gravityMod;
+			if (P->timeCurrent <= 1.0) normal_stress = (1.0 - P->timeCurrent) * (A->p_smooth[i] - (WL[c] - x[2]) * P->DNS_FL1 * gravityMod) + P->timeCurrent * normal_stress;
+			if (normal_stress < 1.0 || A->Cv[i] < 0.5) normal_stress = 1.0;
+			A->p_rheo_new[i] = normal_stress;
+			A->Inertia[i] = sqrt(A->II[i]) * P->DG / sqrt(normal_stress / (P->DNS_FL1 * P->Cd));
+			A->VF[i] = P->VF_max - (P->VF_max - P->VF_min) * A->Inertia[i];
+			if (A->VF[i] < P->VF_min) A->VF[i] = P->VF_min;
+			A->RHO[i] = P->DNS_SDT * A->VF[i] + (1.0 - A->VF[i]) * P->DNS_FL1;
+			phi = phi * A->VF[i] / P->VF_max;
+			double yield_stress = P->cohes * cos(phi) + normal_stress * sin(phi);
+			if (yield_stress < (slip ? P->epsilonZero : 0.0)) yield_stress = 0.0;   /* :1083 against :1497 */
+			double visc_max = (yield_stress * P->mm * 0.5 + P->MEU0);
+			if (A->II[i] > P->epsilonZero) A->MEU_Y[i] = yield_stress * (1.0 - exp(-P->mm * sqrt(A->II[i]))) * 0.5 / sqrt(A->II[i]);
+			else A->MEU_Y[i] = visc_max;
+			double meu_0 = 0.5 * (tan(phi2) - tan(phi)) * normal_stress * P->DG / (P->I0 * sqrt(normal_stress / (P->DNS_FL1 * P->Cd)) + sqrt(A->II[i]) * P->DG);
+			if (A->II[i] <= P->epsilonZero || (meu_0 * 0) != 0) meu_0 = P->MEU0;
+			visc_max = (yield_stress * P->mm * 0.5 + meu_0);
+			A->MEU[i] = A->MEU_Y[i] + P->MEU0 * pow(4.0 * A->II[i], (P->powerLawN - 1.0) * 0.5);
+			if (A->II[i] == 0 || A->MEU[i] > visc_max) A->MEU[i] = visc_max;
+		}
+		if (A->PTYPE[i] >= 2) {
+			if (A->Cv[i] > 0.5) A->RHO[i] = P->DNS_FL2;
+			else A->RHO[i] = A->Cv[i] * P->DNS_FL2 + (1.0 - A->Cv[i]) * P->DNS_FL1;
+		}
+	}
+	free(BL); free(WL);
+}
+
 void oracle_step(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMesh* meshes, int* solverIter, double* solverErr) {
 	const int poly = P->wallType == 1;   /* order: src/main.cpp:256-456 */
 	oracle_update_buckets(P, A, B);
@@ -1421,7 +1529,7 @@ void oracle_step(PmpsParams* P, PmpsHostArrays* A, OBuckets* B, const OMesh* mes
 	if (P->gradientCorrection) oracle_correction_matrix(P, A, B);
 	oracle_press_gradient(P, A, B);
 	if (poly) oracle_wall_press_gradient(P, A, B, P->velMax);
-	if (P->fluidType == 1) { oracle_calc_volume_fraction(P, A, B); oracle_calc_viscosity_interaction(P, A, B); }   /* src/main.cpp:387-390 (particle walls) */
+	if (P->fluidType == 1) { oracle_calc_volume_fraction(P, A, B); oracle_calc_viscosity_interaction(P, A, B); if (poly) oracle_calc_wall_viscosity_interaction(P, A, B); }   /* src/main.cpp:387-399 */
 	if (poly) oracle_wall_viscosity(P, A, B);
 	P->velMax = oracle_correct(P, A);
 	oracle_check_out_domain(P, A);

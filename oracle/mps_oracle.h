@@ -38,6 +38,7 @@ void oracle_update_buckets(const PmpsParams* P, PmpsHostArrays* A, OBuckets* B);
 void oracle_calc_viscosity(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);     /* src/MpsViscosity.cpp:20-100 */
 void oracle_calc_volume_fraction(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B);   /* src/MpsViscosity.cpp:104-190 */
 double oracle_calc_viscosity_interaction(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B); /* src/MpsViscosity.cpp:194-700, returns CFLvisc */
+void oracle_calc_wall_viscosity_interaction(const PmpsParams* P, PmpsHostArrays* A, const OBuckets* B); /* src/MpsViscosity.cpp:703-1526 (by slipCondition) */
 void oracle_add_gravity(const PmpsParams* P, PmpsHostArrays* A);                           /* src/MpsParticle.cpp:111-130 */
 void oracle_predict(const PmpsParams* P, PmpsHostArrays* A);                               /* src/MpsParticleVelPos.cpp:20-50 */
 int  oracle_check_out_domain(const PmpsParams* P, PmpsHostArrays* A);                      /* src/MpsParticle.cpp:234-402 */

@@ -51,7 +51,7 @@ class Oracle:
     STAGES_PAB = ["vel_divergence", "wall_vel_divergence", "prediction_press_gradient", "calc_volume_fraction", "calc_viscosity", "collisions", "wall_npcd", "correction_matrix", "pnd_neigh_npcd", "pnd_diffusive",
                   "wall_pnd_diffusive", "mean_pnd_wall_dummy_surface", "extrapolate_press", "press_gradient", "wall_viscosity",
                   "shifting", "wall_shifting", "update_wall_dummy_vel", "initial_pnd", "mean_wall_pnd", "mean_pnd",
-                  "mean_neigh_fluid_pnd", "update_bc", "calc_normals", "calc_wall_normals"]
+                  "mean_neigh_fluid_pnd", "update_bc", "calc_normals", "calc_wall_normals", "calc_wall_viscosity_interaction"]
     STAGES_PA = ["add_gravity", "predict", "update_pnd", "calc_press_eos"]
 
     def __init__(self, ps, state: HostState, meshes=(), shifting_jacobi=True, threads=1):

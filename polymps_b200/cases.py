@@ -362,6 +362,35 @@ def dam2d_erosion(nx: int, nz: int, bed: int, *, lo: float = 0.0025, tank_nx: in
                 vel=np.zeros((n, 3)), press=np.zeros(n), tris=None, meta={"H": H})
 
 
+def dam3d_erosion(nx: int, ny: int, nz: int, bed: int, *, lo: float = 0.005, tank_nx: int | None = None, jitter: float = 0.0, seed: int = 20261105,
+                  name: str | None = None, **overrides) -> Case:
+    """3D erosional dam break in a POLYGON tank (option set of input/damErosion3D_WC.json: polygon walls, WC-MPS, non-Newtonian
+    two-phase rheology — the configuration whose near-wall particles go through calcWall{Slip,NoSlip}ViscosityInteractionVal,
+    src/MpsViscosity.cpp:703-1526).  A sediment bed of `bed` layers (grid id 1 = fluid of phase 2) covers the tank floor, a water column
+    of nx x ny x nz particles stands on its left end; the tank is ny particles wide."""
+    tank_nx = tank_nx or int(round(nx * 2.5))
+    rng = np.random.default_rng(seed)
+    P, T = [], []
+    for m in range(bed + nz):
+        for j in range(ny):
+            for i in range(tank_nx):
+                t = 1 if m < bed else (0 if i < nx else None)
+                if t is None:
+                    continue
+                x = np.array([(i + 0.5) * lo, (j + 0.5) * lo, (m + 0.5) * lo])
+                if jitter > 0.0:
+                    x = x + rng.uniform(-jitter * lo, jitter * lo, size=3)
+                P.append(x); T.append(t)
+    pos = np.array(P); ptype = np.array(T, dtype=np.int32)
+    tank = (tank_nx * lo, ny * lo, 2.0 * (bed + nz) * lo)
+    kw = dict(dim=3, lo=lo, dt=0.02 * lo, wall_type=1, mps_type=1, c0=20.0, grad_type=3, grad_corr=False, fs_type=1, max_vel=4.0, shifting=2, pnd_type=2,
+              fluid_type=1, rheo=FRACCAROLLO_RHEO, dom_min=(0.0, 0.0, 0.0), dom_max=tank)
+    kw.update(overrides)
+    n = len(pos)
+    return Case(name=name or "dam3d_erosion_%dx%dx%d_%d" % (nx, ny, nz, bed), options=base_options(**kw), ptype=ptype, pos=np.ascontiguousarray(pos),
+                vel=np.zeros((n, 3)), press=np.zeros(n), tris=box_triangles(*tank).astype(np.float32).astype(np.float64), meta={"H": nz * lo})
+
+
 # ---------------------------------------------------------------------------------------------- files
 def write_grid(path: str, ptype, pos, vel, press) -> None:
     """.grid: '0', N, then 'id x y z vx vy vz p pav' rows (reference README.md:65-74).  %.17g round-trips doubles."""

@@ -214,7 +214,8 @@ extern "C" int pmps_create(const PmpsParams* params, int device, pmps_t** out) {
 	if (params->abi_version != PMPS_ABI_VERSION) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: ABI version %d, library is %d", params->abi_version, PMPS_ABI_VERSION);
 	if (params->dim != 2 && params->dim != 3) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: dim must be 2 or 3");
 	if (params->fluidType != 0 && params->fluidType != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: fluidType %d", params->fluidType);
-	if (params->fluidType == 1 && params->wallType != 0) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: the non-Newtonian rheology is on the device path for particle walls only (the polygon-wall variants, src/MpsViscosity.cpp:703-1526, are not: SURVEY 8f row 1)");
+	if (params->fluidType == 1 && params->wallType != 0 && params->dim != 3) return pmps_fail(nullptr, PMPS_E_UNSUPPORTED, "pmps_create: the polygon-wall variants of the non-Newtonian rheology (src/MpsViscosity.cpp:703-1526) exist in 3D only — the reference's code reads the bed level along z");
+	if (params->fluidType == 1 && params->wallType != 0 && params->slipCondition != 0 && params->slipCondition != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: slipCondition %d", params->slipCondition);
 	if (params->fluidType == 1 && params->fractionMethod != 1 && params->fractionMethod != 2) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: fractionMethod %d", params->fractionMethod);
 	if (params->domainTypeBC != 0 && params->domainTypeBC != 1) return pmps_fail(nullptr, PMPS_E_ARG, "pmps_create: domainTypeBC %d", params->domainTypeBC);
 	if (params->domainTypeBC == 1) {   // periodic in one direction (src/MpsBucket.cpp:142-289)

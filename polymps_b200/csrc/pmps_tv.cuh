@@ -65,6 +65,7 @@ template <> struct NbFields<BExtrapolatePress> { static constexpr unsigned value
 template <> struct NbFields<BWallDummyVel> { static constexpr unsigned value = NF_VEL; };
 template <> struct NbFields<BShiftVel> { static constexpr unsigned value = NF_VEL; };
 template <> struct NbFields<BStrainRate> { static constexpr unsigned value = NF_VEL | NF_PRESS; };
+template <> struct NbFields<BWallStrainRate> { static constexpr unsigned value = NF_VEL | NF_PRESS; };
 template <class... B> struct PackFields { static constexpr unsigned value = 0; };
 template <class B, class... R> struct PackFields<B, R...> { static constexpr unsigned value = NbFields<B>::value | PackFields<R...>::value; };
 // bodies that act only on particles near a polygon wall: their launches skip tiles without any (tileWall)

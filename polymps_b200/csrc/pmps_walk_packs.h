@@ -11,5 +11,5 @@
 	X(23, 2, BWallPressGradient, BWallViscosity, BCorrectTail) X(24, 2, BWallViscosity) X(25, 2, BPressMin) X(26, 2, BMeanNeighFluidPnd) \
 	X(27, 3, BCorrectionMatrix) X(28, 3, BCorrectionMatrix, BPressMin) X(29, 3, BExtrapolatePress) X(30, 3, BConcentration) X(31, 3, BGradConcentration) X(32, 3, BWallGradConcentration) \
 	X(33, 3, BWallDummyVel) X(34, 3, BVolumeFraction) X(35, 3, BStrainRate) \
-	X(36, 0, BNormal) X(37, 1, BWallNormal) X(38, 2, BArcBC)
+	X(36, 0, BNormal) X(37, 1, BWallNormal) X(38, 2, BArcBC) X(39, 3, BWallStrainRate)
 #define PMPS_WALK_GROUPS 4

@@ -19,7 +19,7 @@ from .state import HostState, PmpsHostArrays, PmpsScalars
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PMPS_LIB", os.path.join(HERE, "libpmps.so"))   # PMPS_LIB: an experimental build of the same library (A/B timing)
 
-STAGES = ["update_buckets", "calc_volume_fraction", "calc_viscosity_interaction", "calc_viscosity", "add_gravity", "predict", "check_out_domain", "collisions", "wall_closest_point",
+STAGES = ["update_buckets", "calc_volume_fraction", "calc_viscosity_interaction", "calc_wall_viscosity_interaction", "calc_viscosity", "add_gravity", "predict", "check_out_domain", "collisions", "wall_closest_point",
           "wall_npcd", "correction_matrix", "calc_normals", "calc_wall_normals", "pnd_neigh_npcd", "pnd_diffusive", "wall_pnd_diffusive", "update_pnd",
           "mean_pnd_wall_dummy_surface", "update_bc", "calc_press", "extrapolate_press", "press_gradient",
           "wall_press_gradient", "prediction_press_gradient", "prediction_wall_press_gradient", "wall_viscosity", "correct", "shifting", "wall_shifting", "update_wall_dummy_vel",
@@ -28,7 +28,8 @@ STAGES = ["update_buckets", "calc_volume_fraction", "calc_viscosity_interaction"
 # reference method name -> stage call (src/main.cpp:256-456)
 REFERENCE_NAMES = {
     "updateParticlesID": "update_buckets", "calcVolumeFraction": "calc_volume_fraction",
-    "calcViscosityInteractionVal": "calc_viscosity_interaction", "calcViscosity": "calc_viscosity", "addGravity": "add_gravity",
+    "calcViscosityInteractionVal": "calc_viscosity_interaction", "calcWallSlipViscosityInteractionVal": "calc_wall_viscosity_interaction",
+    "calcWallNoSlipViscosityInteractionVal": "calc_wall_viscosity_interaction", "calcViscosity": "calc_viscosity", "addGravity": "add_gravity",
     "predictionVelocityPosition": "predict", "checkParticleOutDomain": "check_out_domain",
     "checkParticleCollisions": "collisions", "closestPointPNDBoundaryAABB": "wall_closest_point", "calcWallNPCD": "wall_npcd",
     "correctionMatrix": "correction_matrix", "calcPndnNeighNPCD": "pnd_neigh_npcd", "calcPndDiffusiveTerm": "pnd_diffusive",

@@ -86,7 +86,7 @@ PmpsParams params_of(MpsParticleSystem* S) {
 	C(KNM_VS1) C(KNM_VS2) C(DNS_SDT) C(PHI_1) C(PHI_2) C(cohes) C(MEU0) C(DG) C(I0) C(mm) C(Cd) C(VF_min) C(VF_max) C(relaxPND) C(timeCurrent)
 	C(thetaArc) C(hThreshold2) C(dstThreshold2) C(normThreshold2)
 #undef C
-	p.fractionMethod = S->Fraction_method;
+	p.fractionMethod = S->Fraction_method; p.powerLawN = S->N;
 	for (int k = 0; k < 3; k++) p.uniformVelWall[k] = S->uniformVelWall[k];
 	if (S->domainTypeBC == 1) {   // periodic domain: the one direction calcDomainLimits handled (src/MpsBucket.cpp:142-289)
 		const int a = S->periodicDirectionX ? 0 : S->periodicDirectionY ? 1 : 2;
@@ -182,17 +182,19 @@ void MpsParticle::checkParticleOutDomain(MpsParticleSystem *PSystem) {
 
 // ---- MpsViscosity (src/MpsViscosity.cpp:20-100, 1527-1910) -----------------------------------------------------------
 void MpsViscosity::calcViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_calc_viscosity(H(PSystem, Particles))); }
-// non-Newtonian rheology, particle walls (src/MpsViscosity.cpp:104-190, :194-700); the polygon-wall variants stay on the host side of the
-// boundary and are refused by pmps_create (fluidType 1 with wallType 1)
+// non-Newtonian rheology (src/MpsViscosity.cpp:104-190, :194-700)
 void MpsViscosity::calcVolumeFraction(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_calc_volume_fraction(H(PSystem, Particles))); }
 void MpsViscosity::calcViscosityInteractionVal(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) {
 	CALL(pmps_set_time(H(PSystem, Particles), PSystem->timeCurrent));
 	CALL(pmps_calc_viscosity_interaction(H(PSystem, Particles)));
 }
-// polygon-wall variants of the rheology (src/MpsViscosity.cpp:703-1526; src/main.cpp:391-399): pmps_create refuses fluidType 1 with polygon
-// walls, so these are unreachable with a live handle — they are defined so that they can never resolve to the reference's loops
-void MpsViscosity::calcWallSlipViscosityInteractionVal(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { unsupported("MpsViscosity::calcWallSlipViscosityInteractionVal", "non-Newtonian rheology with polygon walls"); }
-void MpsViscosity::calcWallNoSlipViscosityInteractionVal(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { unsupported("MpsViscosity::calcWallNoSlipViscosityInteractionVal", "non-Newtonian rheology with polygon walls"); }
+// polygon-wall variants of the rheology (src/MpsViscosity.cpp:703-1526; src/main.cpp:391-399): one stage call, the slip condition is in the parameters
+void MpsViscosity::calcWallSlipViscosityInteractionVal(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) {
+	CALL(pmps_set_time(H(PSystem, Particles), PSystem->timeCurrent)); CALL(pmps_calc_wall_viscosity_interaction(H(PSystem, Particles)));
+}
+void MpsViscosity::calcWallNoSlipViscosityInteractionVal(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) {
+	CALL(pmps_set_time(H(PSystem, Particles), PSystem->timeCurrent)); CALL(pmps_calc_wall_viscosity_interaction(H(PSystem, Particles)));
+}
 void MpsViscosity::calcWallSlipViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_viscosity(H(PSystem, Particles))); }
 void MpsViscosity::calcWallNoSlipViscosity(MpsParticleSystem *PSystem, MpsParticle *Particles, MpsBucket *Buckets) { CALL(pmps_wall_viscosity(H(PSystem, Particles))); }
 

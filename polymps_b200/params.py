@@ -66,6 +66,7 @@ class ParticleSystem:
     KNM_VS2: float = 0.000001
     DNS_SDT: float = 1540.0
     MEU0: float = 0.03
+    N: float = 1.2                # power_law_index (src/MpsInputOutput.cpp:272)
     PHI_1: float = 0.541
     PHI_2: float = 0.6
     cohes: float = 0.0
@@ -232,6 +233,7 @@ class ParticleSystem:
         ps.DNS_FL2 = float(g(rh, "fluid_density_phase_2", 1540.0))
         ps.DNS_SDT = float(g(rh, "sediment_density", 1540.0))
         ps.MEU0 = float(g(rh, "consistency_index", 0.03))
+        ps.N = float(g(rh, "power_law_index", 1.2))
         phi = rh.get("phi", {})
         ps.PHI_1 = float(g(phi, "lower", 0.541)); ps.PHI_2 = float(g(phi, "second", 0.6))
         ps.cohes = float(g(rh, "cohes_coeff", 0.0))
@@ -494,7 +496,7 @@ class PmpsParams(ctypes.Structure):
            "delta2", "velMax"]
     _D3 = ["KNM_VS1", "KNM_VS2", "DNS_SDT", "PHI_1", "PHI_2", "cohes", "MEU0", "DG", "I0", "mm", "Cd", "VF_min", "VF_max", "relaxPND", "timeCurrent",
            "thetaArc", "hThreshold2", "dstThreshold2", "normThreshold2"]
-    _D4 = ["periodicLength", "physDomMin", "physDomMax"]   # of the periodic axis (ParticleSystem.periodicLen / physDomMin / physDomMax)
+    _D4 = ["periodicLength", "physDomMin", "physDomMax", "powerLawN"]   # of the periodic axis (ParticleSystem.periodicLen / physDomMin / physDomMax)
     _fields_ = ([(n, ctypes.c_int32) for n in _I] + [(n, ctypes.c_double) for n in _D]
                 + [("uniformVelWall", ctypes.c_double * 3)] + [(n, ctypes.c_double) for n in _D2 + _D3 + _D4])
 
@@ -503,7 +505,7 @@ def to_c_params(ps: ParticleSystem, shifting_jacobi: bool = True) -> PmpsParams:
     c = PmpsParams()
     for n in PmpsParams._I:
         if n == "abi_version":
-            c.abi_version = 4
+            c.abi_version = 5
         elif n == "shiftingJacobi":
             c.shiftingJacobi = 1 if shifting_jacobi else 0
         elif n == "periodicAxis":
@@ -514,5 +516,5 @@ def to_c_params(ps: ParticleSystem, shifting_jacobi: bool = True) -> PmpsParams:
         setattr(c, n, float(getattr(ps, n)))
     for k in range(3):
         c.uniformVelWall[k] = float(ps.uniformVelWall[k])
-    c.periodicLength = float(getattr(ps, "periodicLen", 0.0)); c.physDomMin = float(getattr(ps, "physDomMin", 0.0)); c.physDomMax = float(getattr(ps, "physDomMax", 0.0))
+    c.periodicLength = float(getattr(ps, "periodicLen", 0.0)); c.physDomMin = float(getattr(ps, "physDomMin", 0.0)); c.physDomMax = float(getattr(ps, "physDomMax", 0.0)); c.powerLawN = float(ps.N)
     return c

@@ -39,6 +39,8 @@ def stage_calls(stage, ps):
         return ["prediction_press_gradient"] + (["prediction_wall_press_gradient"] if ps.wallType == 1 else [])
     if stage == "meanPnd":   # pnd type 1: src/main.cpp:345-350
         return (["mean_wall_pnd"] if ps.wallType == 1 else []) + ["mean_pnd"]
+    if stage in ("nonNewtonian1", "nonNewtonian2"):   # src/main.cpp:259-262, :387-399 (the polygon-wall variants only at the second site)
+        return ["calc_volume_fraction", "calc_viscosity_interaction"] + (["calc_wall_viscosity_interaction"] if stage == "nonNewtonian2" and ps.wallType == 1 else [])
     if stage == "normals":   # ARC free-surface detection: src/main.cpp:351-357
         return ["calc_normals"] + (["calc_wall_normals"] if ps.wallType == 1 else [])
     return STAGE_MAP[stage]
@@ -169,6 +171,11 @@ VARIANTS = {
     "2d_per": _per2(), "2d_per_right": _per2(drift=-1.0, window=-0.45), "2d_per_inc": _per2(incompressible=True), "2d_per_dpc": _per2(collision=1),
     # (the larger block also for the live reference run: in its first step a near-wall particle crosses the face during the shifting and
     # takes the wall-shifting pass from INSIDE the aliased border layer — its search then runs over the end of a bucket row)
+    # non-Newtonian rheology with polygon walls (option set of input/damErosion3D_WC.json): the wall variants of the viscosity model, src/MpsViscosity.cpp:703-1526
+    "nn3d_poly": (lambda: __import__("polymps_b200.cases", fromlist=["x"]).dam3d_erosion(5, 4, 5, 3, jitter=0.03, name="var"),
+                  lambda: __import__("polymps_b200.cases", fromlist=["x"]).dam3d_erosion(10, 6, 10, 4, jitter=0.03, name="var")),
+    "nn3d_poly_slip": (lambda: __import__("polymps_b200.cases", fromlist=["x"]).dam3d_erosion(5, 4, 5, 3, jitter=0.03, name="var", slip=1),
+                       lambda: __import__("polymps_b200.cases", fromlist=["x"]).dam3d_erosion(10, 6, 10, 4, jitter=0.03, name="var", slip=1)),
     "3d_per_edge": (lambda: __import__("polymps_b200.cases", fromlist=["x"]).channel3d_periodic(8, 30, 8, jitter=0.04, name="var"),) * 2,
     "3d_per": _per3(), "3d_per_right": _per3(drift=-1.0, window=-0.45), "3d_per_inc": _per3(incompressible=True),
     "ood": _splash((6, 5, 5), (14, 8, 10)),   # particles leave the domain (swap-with-last compaction, src/MpsParticle.cpp:286-396)

@@ -23,12 +23,12 @@ def test_library_exports_every_declared_symbol():
     assert len(syms) >= 45
     missing = [s for s in syms if not hasattr(lib, s)]
     assert not missing, missing
-    assert lib.pmps_abi_version() == 4
+    assert lib.pmps_abi_version() == 5
 
 
 def test_struct_layouts_match_header():
     # sizes computed from the header: 30 int32 + (30 + 3 + 20 + 15) doubles; 2 int32 + 53 pointers
-    assert ctypes.sizeof(PmpsParams) == 30 * 4 + 75 * 8
+    assert ctypes.sizeof(PmpsParams) == 30 * 4 + 76 * 8
     assert ctypes.sizeof(PmpsHostArrays) == 8 + 8 * (7 + 1 + 18 + 15 + 13)
     assert ctypes.sizeof(PmpsScalars) == 56
 

@@ -35,7 +35,7 @@ def _run(binary, root, name, threads=1):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kind", ["wc3d", "inc3d", "wc2d", "nn2d", "slosh3d", "arc3d", "per2d", "per3d"])
+@pytest.mark.parametrize("kind", ["wc3d", "inc3d", "wc2d", "nn2d", "slosh3d", "arc3d", "per2d", "per3d", "nn3d"])
 def test_unmodified_main_with_shim_matches_stock_reference(kind):
     if not (os.path.isfile(REF_BIN) and os.path.isfile(GPU_BIN)):
         pytest.skip("drop-in binaries not built (they need the reference tree at build time)")
@@ -47,6 +47,9 @@ def test_unmodified_main_with_shim_matches_stock_reference(kind):
         case = cases.channel2d_periodic(64, 14, hump=6, name="dropin", shifting=0)
     elif kind == "per3d":   # periodic in y, polygon walls
         case = cases.channel3d_periodic(8, 30, 8, jitter=0.04, name="dropin", shifting=0)
+    elif kind == "nn3d":   # option set of input/damErosion3D_WC.json: non-Newtonian rheology with POLYGON walls (the wall variants of the viscosity model)
+        case = cases.dam3d_erosion(10, 6, 10, 4, jitter=0.03, name="dropin", shifting=0)
+        case.options["flags"]["output_VTU"].update(non_newtonian=True, auxiliar=True)
     elif kind == "inc3d":
         case = cases.dam3d(12, 6, 8, jitter=0.03, incompressible=True, name="dropin")
     elif kind == "slosh3d":   # BASELINE configs[3]: three meshes, the tank is the forced mesh the host rotates every step

@@ -13,6 +13,7 @@ def _oracle_for(ps, st, meshes, prev, jacobi=False):
     orc = pyoracle.Oracle(ps, st, meshes, shifting_jacobi=jacobi)
     orc.first[:] = prev["firstParticleInBucket"]; orc.last[:] = prev["lastParticleInBucket"]; orc.next[:] = prev["nextParticleInSameBucket"]
     orc.P.velMax = float(prev["scalars"][0])
+    orc.P.timeCurrent = float(prev["scalars"][2])   # (the 3D rheology blends its normal stress over the first second, src/MpsViscosity.cpp:523)
     return orc
 
 
