@@ -9,7 +9,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_INPUT = "/root/reference/input"
 NAMES = ["InputDamWC", "InputDamINC", "dam1610_h300_lo0p0050_WC", "dam1610_h300_lo0p0050_INC", "2D_dam_fraccarollo_lo02p50e-03_WC",
-         "sloshing_3D_bulian_lo0p00930"]
+         "sloshing_3D_bulian_lo0p00930", "dam1610_BC", "damErosion3D_WC"]
 
 
 def strip_comments(t):

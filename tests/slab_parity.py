@@ -40,6 +40,8 @@ def main():
     ap.add_argument("--rtol", type=float, default=1e-9)
     ap.add_argument("--splash", type=float, default=0.0, help="upward velocity of the top two particle layers under a low domain lid: they leave the domain (out-of-domain removal on slabs)")
     ap.add_argument("--inc", action="store_true", help="incompressible scheme: PPE assembly + CG sharded over the slabs")
+    ap.add_argument("--pnd1", action="store_true", help="pnd type 1 (mean PND over the neighbours): one more halo refresh inside the phase")
+    ap.add_argument("--arc", action="store_true", help="ARC free-surface detection (free_surface_threshold.type 2): particle normals + arc test on slab ranks")
     a = ap.parse_args()
     rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); local = 0 if a.one_gpu else int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -50,7 +52,7 @@ def main():
     tank = None
     if a.splash > 0.0:   # open-top tank barely higher than the column: what flies up leaves [domainMin + bucketSide, domainMax - bucketSide]
         tank = ((1.61 / 0.6) * a.nx * 0.01, a.ny * 0.01, (a.nz + 1.5) * 0.01)
-    case = cases.dam3d(a.nx, a.ny, a.nz, jitter=0.05, name="slabparity", incompressible=a.inc, tank=tank)
+    case = cases.dam3d(a.nx, a.ny, a.nz, jitter=0.05, name="slabparity", incompressible=a.inc, tank=tank, **({"fs_type": 2} if a.arc else {}), **({"pnd_type": 1} if a.pnd1 else {}))
     case.vel[:, 0] = a.drift
     if a.splash > 0.0:
         # A patch of the two top layers, away from the END of the particle array (x fastest, then y, then z: the array ends with the

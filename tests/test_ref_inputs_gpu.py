@@ -1,6 +1,6 @@
 """The reference's OWN input documents (BASELINE.json configurations) through both binaries.
 
-tests/golden/ref_inputs.json holds the six documents as parsed from /root/reference/input/*.json (generator:
+tests/golden/ref_inputs.json holds the eight documents as parsed from /root/reference/input/*.json (generator:
 tests/golden/make_ref_inputs.py).  Each is used VERBATIM — every option, lo, dt, c0, domain, relax_pnd as the file has it; only
 `pathNames` point at a grid / STL synthesized here at the file's own particle distance (the shipped grids are stripped LFS blobs)
 and final_time / iter_output are shortened — by the stock reference binary (1 thread) and by the drop-in (unmodified main.cpp +
@@ -35,7 +35,11 @@ STEPS = 12
 
 def build_case(name):
     doc = json.loads(json.dumps(DOCS[name])); lo = doc["numerical"]["particle_dist"]
-    if name.startswith("InputDam"):
+    if name == "dam1610_BC":          # periodic in x, limits from the border particles (boundary.limit 0): the drifting channel reaches the face within the run
+        c = cases.channel2d_periodic(64, 14, hump=6, lo=lo, name="vb")
+    elif name == "damErosion3D_WC":   # non-Newtonian rheology with polygon walls
+        c = cases.dam3d_erosion(10, 6, 10, 4, lo=lo, jitter=0.03, name="vb")
+    elif name.startswith("InputDam"):
         c = cases.dam3d(12, 6, 8, lo=lo, jitter=0.04, name="vb")
     elif name.startswith("dam1610"):
         c = cases.dam2d_particle(20, 24, lo=lo, name="vb")
