@@ -556,7 +556,12 @@ class SlabEngine:
             self._stage("initial_pnd", m)
             if poly:
                 self._stage("mean_wall_pnd", m)
-            self._stage("mean_pnd", m); self._stage("mean_neigh_fluid_pnd", m); self._stage("update_bc", HF_BC); self._stage("calc_press", m | HF_PPE_X)
+            self._stage("mean_pnd", m); self._stage("mean_neigh_fluid_pnd", m)
+            if self.ps.freeSurfType == 2:   # ARC free-surface detection: the particle normals first (src/main.cpp:170-176); they read positions only
+                self._stage("calc_normals")
+                if poly:
+                    self._stage("calc_wall_normals")
+            self._stage("update_bc", HF_BC); self._stage("calc_press", m | HF_PPE_X)
 
     def step(self, n: int = 1):
         L = self.eng.lib; h = self.eng.h
