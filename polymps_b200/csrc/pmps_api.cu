@@ -186,7 +186,7 @@ template <class T> static int dalloc(pmps_handle* h, T** p, size_t count) {
 
 static int alloc_view(pmps_handle* h, DevView& V, int n0, bool primary) {
 	int rc = 0;
-	rc |= dalloc(h, &V.pos, n0); rc |= dalloc(h, &V.vel, n0); rc |= dalloc(h, &V.hostIdx, n0); rc |= dalloc(h, &V.particleNearWall, n0); rc |= dalloc(h, &V.stepCell, n0);
+	rc |= dalloc(h, &V.pos, n0); rc |= dalloc(h, &V.vel, n0); rc |= dalloc(h, &V.hostIdx, n0); rc |= dalloc(h, &V.particleNearWall, n0); rc |= dalloc(h, &V.stepCell, n0); rc |= dalloc(h, &V.wrapHid, h->K.p.domainTypeBC == 1 ? n0 : 1);
 #define X(n) rc |= dalloc(h, &V.n, n0);
 	PMPS_I32_FIELDS(X)
 	PMPS_F64_FIELDS(X)

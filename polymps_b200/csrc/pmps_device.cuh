@@ -145,10 +145,6 @@ __device__ __forceinline__ double per_pair_shift(const DevView& S, const KParams
 // lists are only re-threaded at the next step start (src/main.cpp:256): until then array element i — now the moved particle —
 // is still listed in the bucket of the particle that left, so a neighbour loop finds it only from there.  hid_visible(): does the
 // 27-bucket search of a particle at pi (bucketCoordinates, src/MpsBucket.cpp:420-425: epsilonZero on every axis) reach `cell`?
-// A particle the periodic wrap moved to the other end of the domain stays threaded on the bucket it started the step in, now a
-// domain length away from where it is: no search that reaches that bucket finds it within any radius.  Its entry carries
-// PMPS_HID_NOWHERE instead of a bucket (pmps_domain.cu, k_ood_flag).
-#define PMPS_HID_NOWHERE (-2)
 __device__ __forceinline__ bool hid_visible(const KParams& K, int cell, const double4& pi) {
 	const PmpsParams& P = K.p;
 	if (cell < 0) return false;
@@ -159,7 +155,7 @@ __device__ __forceinline__ bool hid_visible(const KParams& K, int cell, const do
 	if (P.dim == 2) return cz == 0;   // minZ = maxZ = 0 (src/MpsViscosity.cpp:35)
 	return abs(bucket_coord(pi.z, P.domainMinZ, P.invBucketSide, P.epsilonZero) - cz) <= 1;
 }
-// the bucket the array element of slot `slot` is listed in when the reference's lists are stale for it (or PMPS_HID_NOWHERE), else -1
+// the bucket the array element of slot `slot` is listed in when the reference's lists are stale for it, else -1
 __device__ __forceinline__ int hid_cell_of_slot(const DevView& S, int slot) {
 	const int nh = S.hid[0]; if (nh == 0) return -1;
 	const int label = S.hostIdx[slot];

@@ -17,9 +17,8 @@ __device__ __forceinline__ bool out_of_domain(const KParams& K, const double4& p
 // Periodic domain: a particle beyond a face of the physical domain re-enters through the opposite one (src/MpsParticle.cpp:236-269, every
 // particle, before the out-of-domain test).  The reference's bucket lists still hold it where it started the step — a domain length
 // away from where it now is — so until the lists are re-threaded at the next step start nobody finds it, while its own search runs
-// around its new position: the wrapped particle gets a hidden-everywhere entry (pmps_device.cuh, PMPS_HID_NOWHERE; a particle wrapped
-// back within the same step loses it again) and the host re-sorts the buckets before the next pass (pmps_check_out_domain).
-// Entries are appended behind the committed ones (hid[0]); k_ood_fix commits them.
+// around its new position: the slot gets its hidden flag (DevView::wrapHid, carried through the bucket sort; a particle wrapped back
+// within the same step loses it again) and the host re-sorts the buckets before the next pass (pmps_check_out_domain).
 __device__ __forceinline__ void periodic_wrap(const DevView& S, const KParams& K, int i, double4& p) {
 	double& x = K.p.periodicAxis == 0 ? p.x : K.p.periodicAxis == 1 ? p.y : p.z;
 	const double x0 = x;
@@ -27,10 +26,8 @@ __device__ __forceinline__ void periodic_wrap(const DevView& S, const KParams& K
 	if (x < K.p.physDomMin) x = __dadd_rn(x, K.p.periodicLength);
 	if (x == x0) return;
 	S.pos[i] = p;
-	const int label = S.hostIdx[i], nh0 = S.hid[0];
-	for (int q = 0; q < nh0; q++) if (S.hid[1 + q] == label && S.hid[1 + PMPS_HID_CAP + q] == PMPS_HID_NOWHERE) { S.hid[1 + q] = -1; atomicAdd(&S.flags[FLAG_WRAP_LAST], 1); return; }
-	const int k = atomicAdd(&S.flags[FLAG_WRAPPED], 1);
-	if (nh0 + k < PMPS_HID_CAP) { S.hid[1 + nh0 + k] = label; S.hid[1 + PMPS_HID_CAP + nh0 + k] = PMPS_HID_NOWHERE; }
+	S.wrapHid[i] ^= 1;
+	atomicAdd(&S.flags[FLAG_WRAPPED], 1);
 }
 
 __global__ void k_ood_flag(const __grid_constant__ DevView S, const __grid_constant__ KParams K) {
@@ -44,14 +41,9 @@ __global__ void k_ood_flag(const __grid_constant__ DevView S, const __grid_const
 }
 
 __global__ void k_ood_fix(const __grid_constant__ DevView S, const __grid_constant__ KParams K, int staleReplay) {
-	if (K.p.domainTypeBC == 1) {   // commit the entries of the particles this check wrapped; FLAG_WRAP_LAST = particles moved (host: re-sort)
+	if (K.p.domainTypeBC == 1) {   // FLAG_WRAP_LAST = particles this check moved through a face (host: re-sort), FLAG_WRAP_STEP = since the step start
 		const int w = S.flags[FLAG_WRAPPED];
-		if (w > 0) {
-			int nh = S.hid[0] + w;
-			if (nh > PMPS_HID_CAP) { atomicOr(&S.flags[FLAG_GUARD], 8); nh = PMPS_HID_CAP; }
-			S.hid[0] = nh; S.flags[FLAG_WRAPPED] = 0; S.flags[FLAG_WRAP_LAST] += w;
-		}
-		if (S.flags[FLAG_WRAP_LAST] > 0) S.hitMove[0] = 1e30f;
+		if (w > 0) { S.flags[FLAG_WRAPPED] = 0; S.flags[FLAG_WRAP_LAST] += w; S.flags[FLAG_WRAP_STEP] += w; S.hitMove[0] = 1e30f; }
 	}
 	int cnt = S.flags[FLAG_OOD_COUNT];
 	if (cnt == 0) return;

@@ -47,6 +47,7 @@ struct DevView {
 	uint16_t* hlist; uint16_t* hcnt;       // hit list (pmps_tv.cuh, k_hl_build): the staged records within reach at the positions of the current epoch, tlCap entries
 	                                       // per slot in chunks of 64 (tv_list_pos), as 16-bit indices into the staged halo of the slot's work item; entries used
 	uint8_t* particleNearWall;
+	uint8_t* wrapHid;                    // periodic domain: 1 = moved through a periodic face since the step start (found by nobody until the lists are re-threaded); n0 bytes, 1 byte when not periodic
 	double* ppeP;                        // CG search direction (pmps_ppe.cu), here so that the halo pack / unpack kernels reach it
 	double* scratch1;                    // per-slot scratch (Pmin of the gradient passes); not a reference field
 #define X(n) int32_t* n;
@@ -95,7 +96,7 @@ struct DevView {
 	unsigned long long* rheoBL; unsigned long long* rheoWL; int32_t* rheoIdx; unsigned long long* meuMaxBits;
 };
 
-enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, FLAG_UPLOAD_TYPES = 7, FLAG_WRAPPED = 8, FLAG_WRAP_LAST = 9, NFLAGS = 10 };
+enum { FLAG_OVERFLOW = 0, FLAG_OOD_COUNT = 1, FLAG_GUARD = 2, FLAG_LIVE = 3, FLAG_MAXCELL = 4, FLAG_OOD_TOTAL = 5, FLAG_TILE_OVERFLOW = 6, FLAG_UPLOAD_TYPES = 7, FLAG_WRAPPED = 8, FLAG_WRAP_LAST = 9, FLAG_WRAP_STEP = 10, NFLAGS = 11 };
 #define PMPS_OOD_CAP 65536
 #define PMPS_HID_CAP 8192    // particles moved into a hole by the out-of-domain swap, or to the other end of a periodic domain, within one step
 #define PMPS_CLOSE_CAP 16 // close-pair list entries per slot (collision pass)
@@ -169,7 +170,7 @@ struct pmps_handle {
 	size_t listAllocated = 0;
 	int solverIter = 0; double solverError = 0.0, velMax = 0.0;
 	long long launches = 0;
-	long long nWrapped = 0;   // particles moved through a periodic face so far
+	long long nWrapped = 0, nWrappedCleared = 0;   // particles moved through a periodic face so far; the count at the last clearing of their hidden flags
 	long long nRebuilds = 0, nStepsDone = 0;   // pmps_get_counters: bucket-order rebuilds (sort + Verlet list) and fused steps so far
 	double guardWorst = 0.0;             // sticky: largest displacement since a rebuild that exceeded the search slack (0: never); cleared by pmps_upload
 	int oodTotal = 0, maxCell = 0;

@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(PPE_T) k_ppe_assemble(const __grid_constant__ 
 		double4 pj = S.pos[j];
 		bool iFindsJ = true, jFindsI = true;
 		if (nHid > 0) { const int hc = hid_cell_of_slot(S, j); iFindsJ = hc == -1 || hid_visible(K, hc, pi); jFindsI = myHid == -1 || hid_visible(K, myHid, pj); }
+		if (K.p.domainTypeBC == 1) { if (S.wrapHid[j]) iFindsJ = false; if (S.wrapHid[i]) jFindsI = false; }   // wrapped in this step: found by nobody (pmps_domain.cu)
 		const double pl = K.p.domainTypeBC == 1 ? per_pair_shift(S, K, i, j) : 0.0;   // periodic domain: j as i sees it
 		if (K.p.domainTypeBC == 1) per_move(K, pj, pl);
 		const double rx = pj.x - pi.x, ry = pj.y - pi.y, rz = pj.z - pi.z; const double d2 = sq3_exact(rx, ry, rz);

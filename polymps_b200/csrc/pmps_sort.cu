@@ -141,6 +141,7 @@ __global__ void k_permute_packs(const int32_t* __restrict__ perm, const __grid_c
 	const double4 p = S.pos[o];
 	A.pos[s] = p; A.vel[s] = S.vel[o];
 	A.particleNearWall[s] = S.particleNearWall[o]; A.stepCell[s] = S.stepCell[o];
+	if (K.p.domainTypeBC == 1) A.wrapHid[s] = S.wrapHid[o];
 	const int h = S.hostIdx[o];
 	A.hostIdx[s] = h; S.slotOfHost[h] = s;
 	S.cellOf[s] = newCell[o];   // cellOf / bpos are not double-buffered: written at the new slot, read via perm only above
@@ -214,7 +215,7 @@ int pmps_sort_and_list(pmps_handle* h) {
 	LAUNCH(h, "sort.rank_fix", k_rank_fix, cdiv(n0, T), T, S, h->newCell, S.cellStart, tmp, h->perm);
 	// gather: packs first (needs the old hostIdx), then the planes in groups
 	LAUNCH(h, "sort.permute_packs", k_permute_packs, cdiv(n0, T), T, h->perm, S, A, K, h->newCell);
-	swp(S.pos, A.pos); swp(S.vel, A.vel); swp(S.particleNearWall, A.particleNearWall); swp(S.hostIdx, A.hostIdx); swp(S.stepCell, A.stepCell);
+	swp(S.pos, A.pos); swp(S.vel, A.vel); swp(S.particleNearWall, A.particleNearWall); swp(S.hostIdx, A.hostIdx); swp(S.stepCell, A.stepCell); swp(S.wrapHid, A.wrapHid);
 	S.pos2 = A.pos; S.vel2 = A.vel;
 	{
 		std::vector<std::pair<double**, double**>> planes;
@@ -303,7 +304,7 @@ __global__ void k_hits_decide(const __grid_constant__ DevView S, const __grid_co
 	const float lim = S.hitMove[1] * 0.98f;   // float positions relative to domainMin: a few 1e-7 of the domain extent of slack
 	// (hidden entries — a particle left the domain in this step: which particle finds them depends on the bucket its CURRENT position is
 	// in, so the list is re-made at every position epoch until the step ends; pmps_device.cuh, hid_visible)
-	if (force || S.hid[0] > 0 || S.hitMove[0] > lim * lim) { S.hitFlag[0] = 1; S.hitFlag[1] += 1; S.hitMove[0] = 0.f; }
+	if (force || S.hid[0] > 0 || S.flags[FLAG_WRAP_STEP] > 0 || S.hitMove[0] > lim * lim) { S.hitFlag[0] = 1; S.hitFlag[1] += 1; S.hitMove[0] = 0.f; }
 	else S.hitFlag[0] = 0;
 }
 // hit list for the current positions (after the prediction / correction / shifting moved the particles): re-made only when

@@ -156,6 +156,10 @@ static int upload_impl(pmps_handle* h, const PmpsHostArrays* a, bool deviceSrc, 
 		else h->dispNow = fmax(h->dispNow, sqrt((double)md));
 	}
 	if (a->pos && !soft) { h->hitValid = false; h->hitForce = true; h->needRebuild = true; }   // new positions: the next fused step re-sorts and rebuilds the lists
+	if (a->pos && !soft && h->K.p.domainTypeBC == 1) {   // a new state: nobody is hidden by a periodic wrap of the old one
+		CUDA_TRY(h, cudaMemsetAsync(S.wrapHid, 0, (size_t)S.n0, h->stream)); CUDA_TRY(h, cudaMemsetAsync(S.flags + FLAG_WRAP_STEP, 0, sizeof(int32_t), h->stream));
+		h->nWrappedCleared = h->nWrapped;
+	}
 	return PMPS_OK;
 }
 

@@ -247,7 +247,7 @@ static __global__ void k_copy_ghost_tail(const __grid_constant__ DevView S, int 
 
 
 // ---- shared-memory image of the halo ------------------------------------------------------------------------------
-#define TV_W_HIDDEN 0x40000000   // bit of the float type word (list build only): the record is found by nobody (a particle the periodic wrap moved in this step)
+#define TV_W_HIDDEN 0x40000000   // bit of the float type word (list build only): the record is found by nobody (a particle the periodic wrap moved in this step, DevView::wrapHid)
 #define TV_HIDMAX 32   // staged records of one work item the reference's stale bucket lists may hide (pmps_device.cuh, hid_visible)
 struct TvStage {   // shared-memory planes of the staged halo: the walker stages {x, y} / {z, type word} pairs of doubles (two 16-byte planes: a candidate
 	// is two 128-bit loads, and 8 consecutive records cover all 32 banks), the list build float positions
@@ -343,14 +343,23 @@ __device__ __forceinline__ void tv_stage_float(const DevView& S, const KParams& 
 			if (PER && hb < HV && ok[b]) per_move(K, p[b], tv_halo_shift(K, bx, hb));
 		}
 		#pragma unroll
-		for (int b = 0; b < NB; b++) if (ok[b]) { fpos[m[b]] = make_float4((float)(p[b].x - ox), (float)(p[b].y - oy), (float)(p[b].z - oz), tv_type_word(p[b])); slotOf[m[b]] = hBase[hb0 + b * NW] + lane; }
+		for (int b = 0; b < NB; b++) if (ok[b]) {
+			const int slot = hBase[hb0 + b * NW] + lane;
+			float w = tv_type_word(p[b]);
+			if (PER && S.wrapHid[slot]) w = __int_as_float(__float_as_int(w) | TV_W_HIDDEN);   // a particle the periodic wrap moved in this step: found by nobody
+			fpos[m[b]] = make_float4((float)(p[b].x - ox), (float)(p[b].y - oy), (float)(p[b].z - oz), w); slotOf[m[b]] = slot;
+		}
 		#pragma unroll
 		for (int b = 0; b < NB; b++) {   // buckets with more than 32 particles (far above the lattice density)
 			const int hb = hb0 + b * NW;
 			if (hb >= HV) continue;
 			const int off = hOff[hb], n = hOff[hb + 1] - off, s0 = hBase[hb];
 			const double sh = PER ? tv_halo_shift(K, bx, hb) : 0.0;
-			for (int r = lane + 32; r < n; r += 32) { double4 q = ld256(S.pos + s0 + r); if (PER) per_move(K, q, sh); fpos[off + r] = make_float4((float)(q.x - ox), (float)(q.y - oy), (float)(q.z - oz), tv_type_word(q)); slotOf[off + r] = s0 + r; }
+			for (int r = lane + 32; r < n; r += 32) {
+				double4 q = ld256(S.pos + s0 + r); if (PER) per_move(K, q, sh);
+				float w = tv_type_word(q); if (PER && S.wrapHid[s0 + r]) w = __int_as_float(__float_as_int(w) | TV_W_HIDDEN);
+				fpos[off + r] = make_float4((float)(q.x - ox), (float)(q.y - oy), (float)(q.z - oz), w); slotOf[off + r] = s0 + r;
+			}
 		}
 	}
 }
@@ -426,13 +435,8 @@ static __global__ void __launch_bounds__(HL_T, 5) k_hl_build(const __grid_consta
 					if (gx < 0 || gx >= b.HX || gy < 0 || gy >= b.HY || gz < 0 || gz >= b.HZ) continue;
 					const int hb = (gz * b.HY + gy) * b.HX + gx, r = slot - hBase[hb];
 					if (r < 0 || r >= hOff[hb + 1] - hOff[hb]) continue;
-					const int listed = S.hid[1 + PMPS_HID_CAP + e];
-					if (PER && listed == PMPS_HID_NOWHERE) {   // a particle the periodic wrap moved (a whole layer of them may sit in one item): found by nobody,
-						fpos[hOff[hb] + r].w = __int_as_float(__float_as_int(fpos[hOff[hb] + r].w) | TV_W_HIDDEN);   // marked in its own record
-						continue;
-					}
 					const int k = atomicAdd(&sHid.n, 1);
-					if (k < TV_HIDMAX) { sHid.m[k] = hOff[hb] + r; sHid.cell[k] = listed; }
+					if (k < TV_HIDMAX) { sHid.m[k] = hOff[hb] + r; sHid.cell[k] = S.hid[1 + PMPS_HID_CAP + e]; }
 					else atomicOr(&S.flags[FLAG_GUARD], 8);
 				}
 			}
