@@ -12,7 +12,9 @@
 struct BViscosity {
 	struct Ctx { double vx, vy, vz, mu, invRho, sx, sy, sz; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
-		const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z; c.mu = S.MEU[s.i]; c.invRho = 1.0 / S.RHO[s.i];
+		if (TV_OWN_STAGED && s.nb) { c.vx = s.nb->vx[s.ms]; c.vy = s.nb->vy[s.ms]; c.vz = s.nb->vz[s.ms]; }
+		else { const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z; }
+		c.mu = OWN(MEU, S.MEU[s.i]); c.invRho = 1.0 / S.RHO[s.i];
 		c.sx = c.sy = c.sz = 0.0; return true;
 	}
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {

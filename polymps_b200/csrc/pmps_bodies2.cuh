@@ -87,10 +87,12 @@ struct BInitialPnd {
 struct BPndDiffusive {
 	struct Ctx { double ni, invNi, vx, vy, vz, Pi, rho, kDi, Di, div; double c1[3], c2[3], c3[3]; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
-		c.ni = S.pndi[s.i];
+		c.ni = OWN(pndi, S.pndi[s.i]);
 		if (c.ni < K.p.epsilonZero) return false;
 		c.invNi = 1.0 / c.ni;
-		const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z; c.Pi = S.press[s.i]; c.rho = S.RHO[s.i];
+		if (TV_OWN_STAGED && s.nb) { c.vx = s.nb->vx[s.ms]; c.vy = s.nb->vy[s.ms]; c.vz = s.nb->vz[s.ms]; }
+		else { const double4 v = S.vel[s.i]; c.vx = v.x; c.vy = v.y; c.vz = v.z; }
+		c.Pi = OWN(press, S.press[s.i]); c.rho = OWN(RHO, S.RHO[s.i]);
 		c.kDi = K.p.timeStep / c.rho * K.p.coeffViscMultiphase;
 		if (K.p.gradientCorrection) {
 			c.c1[0] = S.correcMatrixRow1.x[s.i]; c.c1[1] = S.correcMatrixRow1.y[s.i]; c.c1[2] = S.correcMatrixRow1.z[s.i];

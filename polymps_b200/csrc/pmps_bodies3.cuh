@@ -32,7 +32,7 @@ struct BPressMin {
 template <bool PRED> struct BPressGradientT {
 	struct Ctx { double Pi, ni, invNi, Pmin, sx, sy, sz; double c1[3], c2[3], c3[3]; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
-		c.Pi = S.press[s.i]; c.ni = S.pndi[s.i]; c.invNi = c.ni > K.p.epsilonZero ? 1.0 / c.ni : 0.0;
+		c.Pi = OWN(press, S.press[s.i]); c.ni = OWN(pndi, S.pndi[s.i]); c.invNi = c.ni > K.p.epsilonZero ? 1.0 / c.ni : 0.0;
 		c.Pmin = (K.p.gradientType == 0 || K.p.gradientType == 2) ? S.scratch1[s.i] : c.Pi;
 		if (!PRED && K.p.gradientCorrection) {
 			c.c1[0] = S.correcMatrixRow1.x[s.i]; c.c1[1] = S.correcMatrixRow1.y[s.i]; c.c1[2] = S.correcMatrixRow1.z[s.i];
@@ -168,7 +168,7 @@ struct BGradConcentration {
 	struct Ctx { double ci, gx, gy, gz; };
 	__device__ __forceinline__ static bool begin(Ctx& c, const DevView& S, const KParams& K, const Self& s) {
 		if (s.type != K.p.fluid) return false;
-		c.ci = S.concentration[s.i]; c.gx = c.gy = c.gz = 0.0; return true;
+		c.ci = OWN(concentration, S.concentration[s.i]); c.gx = c.gy = c.gz = 0.0; return true;
 	}
 	template <bool POLY> __device__ __forceinline__ static void pair(Ctx& c, const Nb& S, const KParams& K, const Self& s, const Pair& q) {
 		if (!pred_P<POLY>(q, K.p.reS2)) return;

@@ -194,7 +194,9 @@ __device__ __forceinline__ double4 ld256(const double4* p) {
 }
 
 // ---- per-particle prologue shared by the fused bodies --------------------------------------------------------------
+struct Nb;
 struct Self {
+	const Nb* nb; int ms;       // tile walker: the staged neighbour fields and the particle's OWN staged index (nullptr outside the walker), see OWN()
 	int i; bool lead; double4 pi; int type, ptype; bool hasMirror;   // hasMirror: the polygon-wall pass gave i a mirror particle   // lead: first lane of the particle's group (does the side effects)
 	double mix, miy, miz;       // mirror position of i
 	// wall frame of a near-wall fluid particle: unit normal n = (x_i - mirror_i)/|.|, reflection R = I - 2 n n^T,
@@ -248,6 +250,13 @@ struct Pair {
 struct Nb {
 	const double *vx, *vy, *vz, *press, *pndi, *RHO, *MEU, *concentration, *pndki;
 };
+// A particle's own value of a field its pack stages for the neighbours (NbFields): from the staged copy in shared memory instead of a
+// global load at the start of the round — the staged halo holds the particle itself, and nothing writes these arrays before the pass
+// ends.  (ncu: the round-start loads of begin() were the largest part of the long-scoreboard stalls of the fat passes.)
+#ifndef TV_OWN_STAGED
+#define TV_OWN_STAGED 1
+#endif
+#define OWN(plane, globalValue) ((TV_OWN_STAGED && s.nb) ? s.nb->plane[s.ms] : (globalValue))
 
 // predicates: P(re) real neighbour, M(re) mirror neighbourhood
 template <bool POLY> __device__ __forceinline__ bool pred_P(const Pair& q, double re2) { return q.d2 < re2 && (!POLY || q.d2 < q.dm2); }

@@ -571,7 +571,7 @@ static __global__ void __launch_bounds__(256) k_sparse_mark(const __grid_constan
 	if (i >= S.n) return;
 	const int c = S.cellOf[i];
 	if (c >= S.nC) return;
-	Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+	Self s; s.nb = nullptr; s.ms = 0; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
 	s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
 	if (s.type == K.p.ghost) return;
 	typename F::Ctx ctx = {};
@@ -585,7 +585,7 @@ static __global__ void __launch_bounds__(256) k_tails(const __grid_constant__ De
 	if (c >= S.nC) return;   // parked ghost slots: k_copy_ghost_tail
 	const int tile = c / K.TV;
 	if ((KIND == 0 ? S.tileWall[tile] : KIND == 1 ? S.tileClose[tile] : S.tileSparse[tile]) != 0) return;   // k_tv does this tile
-	Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+	Self s; s.nb = nullptr; s.ms = 0; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
 	s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
 	if (F::kCopyPos) S.pos2[i] = s.pi;
 	if (F::kCopyVel) S.vel2[i] = S.vel[i];
@@ -723,7 +723,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 			bool want = false;
 			for (int p = tid; p < P; p += TV_T) {
 				const int i = own0 + p;
-				Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+				Self s; s.nb = nullptr; s.ms = 0; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
 				s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
 				if (s.type == K.p.ghost) continue;
 				typename F::Ctx ctx = {};
@@ -732,7 +732,7 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 			if (!__syncthreads_or(want)) {
 				for (int p = tid; p < P; p += TV_T) {   // nobody: the tails still run, one lane per particle
 					const int i = own0 + p;
-					Self s; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+					Self s; s.nb = nullptr; s.ms = 0; s.i = i; s.lead = true; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
 					s.pi = ld256(S.pos + i); s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
 					if (F::kCopyPos) S.pos2[i] = s.pi;
 					if (F::kCopyVel) S.vel2[i] = S.vel[i];
@@ -771,12 +771,12 @@ __global__ void __launch_bounds__(TV_T, TV_BLOCKS(FIELDS)) k_tv(const __grid_con
 			const int p = p0 + grp;
 			bool act = p < P;
 			const int i = own0 + (act ? p : 0);
-			Self s; s.i = i; s.lead = g == 0; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
+			Self s; s.nb = &T.nb; s.ms = M; s.i = i; s.lead = g == 0; s.nearWallFluid = false; s.hasMirror = false; s.mix = s.miy = s.miz = 0.0;
 			s.type = K.p.ghost; s.ptype = 0;
 			int cntE = 0;
 			if (act) {
 				cntE = sCnt[p];
-				const int ms = ownMap[p];
+				const int ms = ownMap[p]; s.ms = ms;
 				const double2 xy = T.pxy[ms], zw = T.pzw[ms];
 				s.pi.x = xy.x; s.pi.y = xy.y; s.pi.z = zw.x; s.pi.w = zw.y;
 				s.type = pk_type(s.pi); s.ptype = pk_ptype(s.pi);
