@@ -119,11 +119,21 @@ def test_flowing_block_1m_against_oracle(capsys):
 
 def test_guard_violation_is_loud():
     """particles that jump farther than the search slack within one list lifetime must not pass silently.  A fused step
-    re-makes its bucket order right after the prediction when the displacement reached there asks for it, so a velocity kick alone is
-    handled (no pass runs beyond the slack); what can still violate it are the moves AFTER that check.  Here one interior particle's
-    number density is doubled, the equation of state turns that into a pressure spike and the correction throws its neighbours
-    about one particle distance: pmps_step fails with PMPS_E_STATE, the flag is sticky (a rebuild does not clear it) and an upload of
-    a state clears it."""
+    re-makes its bucket order right after the prediction and again right after the correction when the displacement reached there asks
+    for it, so a velocity kick or a pressure spike alone is handled (next test); what can still violate the slack are the moves after
+    the second check.  To see the guard itself the second check is switched off (PMPS_NO_POST_CHECK): one interior particle's number
+    density is doubled, the equation of state turns that into a pressure spike and the correction throws its neighbours about one
+    particle distance: pmps_step fails with PMPS_E_STATE, the flag is sticky (a rebuild does not clear it) and an upload of a state
+    clears it."""
+    from polymps_b200.engine import PmpsError
+    os.environ["PMPS_NO_POST_CHECK"] = "1"
+    try:
+        _guard_violation_body()
+    finally:
+        del os.environ["PMPS_NO_POST_CHECK"]
+
+
+def _guard_violation_body():
     from polymps_b200.engine import PmpsError
     case = cases.dam3d(16, 8, 12, jitter=0.03, name="kick")
     ps, meshes, st0 = _build(case)
@@ -140,6 +150,30 @@ def test_guard_violation_is_loud():
         eng.step(1)                      # sticky
     eng.upload(st0); eng.init_step0(); eng.step(2)   # a fresh state clears it
     assert eng.counters()["guard_violated"] == 0
+    eng.close()
+
+
+def test_pressure_spike_is_absorbed_by_the_post_correction_rebuild():
+    """The same spike with the second check on (the default): the displacement read back right after the correction re-makes the bucket
+    order before the shifting passes, nothing runs beyond the slack, and the two steps equal the oracle's from the same state."""
+    import pyoracle
+    case = cases.dam3d(16, 8, 12, jitter=0.03, name="kick3")
+    ps, meshes, st0 = _build(case)
+    eng = _engine(ps, meshes, st0.numParticlesZero); eng.upload(st0); eng.init_step0(); eng.step(3)
+    st = st0.copy(); eng.download(st)
+    i = int(np.argmin(np.abs(st.vec("pos")[:st.numParticles] - st.vec("pos")[:st.numParticles].mean(axis=0)).sum(axis=1)))
+    st.pndi[i] *= 2.0
+    want = st.copy(); orc = pyoracle.Oracle(ps, want, meshes, shifting_jacobi=True); orc.P.velMax = eng.scalars().velMax
+    eng.upload(st, ["pndi"])   # no positions: the lists stay
+    c0 = eng.counters()
+    eng.step(2); orc.step(2)
+    c1 = eng.counters()
+    assert c1["guard_violated"] == 0 and c1["bucket_rebuilds"] - c0["bucket_rebuilds"] >= 2
+    got = st0.copy(); eng.download(got)
+    moved = np.abs(got.vec("pos")[:got.numParticles] - st.vec("pos")[:st.numParticles]).max() / ps.partDist
+    assert moved > 0.3, moved   # the spike did throw particles farther than the slack
+    bad = compare_states(got, want, rtol=1e-8, skip=NOISY, scales=natural_scales(ps))
+    assert not bad, bad
     eng.close()
 
 

@@ -17,3 +17,4 @@ d=json.load(open("gpurun_out/r04_bench_n1.json"))
 print("N=1 ms/step %.2f value %.4g rest %.2f e2e %.4g cpu %s"%(d["ms_per_step"], d["value"], d["config"]["at_rest"]["ms_per_step"], d["e2e"]["value"], d.get("cpu_baseline",{}).get("value")))
 PY
 python tools/vtu_timing.py 171 > gpurun_out/r04_vtu_timing.json 2> gpurun_out/r04_vtu_timing.err; echo "vtu rc=$?"; cat gpurun_out/r04_vtu_timing.json
+python tools/long_run.py 171 400 > gpurun_out/r04_long_run.json 2> gpurun_out/r04_long_run.err; echo "long run rc=$?"; python -c "import json; d=json.load(open('gpurun_out/r04_long_run.json')); print({k:d[k] for k in d if k!='history'}, d['history'][::5])"
