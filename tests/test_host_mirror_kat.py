@@ -50,3 +50,32 @@ def test_wall_tables_and_normals_equal_the_references(name):
     np.testing.assert_allclose(np.asarray(m.xDataNeigh), np.asarray(d["mesh0_xDataNeigh"]), rtol=1e-15, atol=0)
     np.testing.assert_allclose(np.asarray(m.Zij), np.asarray(d["mesh0_Zij"]), rtol=1e-13, atol=1e-13)
     assert np.array_equal(np.asarray(m.nNeighWall, dtype=np.int64), np.asarray(d["mesh0_nNeighWall"], dtype=np.int64))
+
+
+def test_periodic_limits_reject_what_the_reference_cannot_do():
+    """polymps_b200/params.py::_periodic_limits: exactly one periodic direction (the reference's calcDomainLimits handles one,
+    src/MpsBucket.cpp:142-289), not z in 2D, positions needed when the limits come from the border particles."""
+    from polymps_b200 import cases
+    from polymps_b200.params import ParticleSystem
+    case = cases.channel2d_periodic(24, 6, hump=3)
+    ok = ParticleSystem.from_json(case.options).set_parameters(); ok.allocate_buckets(case.pos)
+    assert ok.domainTypeBC == 1 and ok.periodicAxis == 0 and abs(ok.periodicLen - 24 * ok.partDist) < 1e-12
+    assert ok.numBucketsX == int(round(ok.periodicLen / ok.bucketSide)) + 2 and abs(ok.physDomMax - ok.physDomMin - ok.periodicLen) < 1e-12
+    for direction in ({"x": True, "y": True, "z": False}, {"x": False, "y": False, "z": False}, {"x": False, "y": False, "z": True}):
+        opts = __import__("json").loads(__import__("json").dumps(case.options)); opts["domain"]["boundary"]["direction"] = direction
+        ps = ParticleSystem.from_json(opts).set_parameters()
+        with pytest.raises(ValueError):
+            ps.allocate_buckets(case.pos)
+    opts = __import__("json").loads(__import__("json").dumps(case.options)); opts["domain"]["boundary"]["limit"] = 0
+    ps = ParticleSystem.from_json(opts).set_parameters()
+    with pytest.raises(ValueError):
+        ps.allocate_buckets(None)
+
+
+def test_vtu_flags_follow_the_input_document():
+    from polymps_b200 import cases
+    from polymps_b200.engine import Engine
+    case = cases.dam3d(4, 4, 4)
+    assert Engine.vtu_flags(case.options) == Engine.VTU_PND   # base_options: pnd on, everything else off
+    case.options["flags"]["output_VTU"].update(neigh=True, auxiliar=True, freeSurfWall=True)
+    assert Engine.vtu_flags(case.options) == Engine.VTU_PND | Engine.VTU_NEIGH | Engine.VTU_AUXILIAR | Engine.VTU_FREE_SURFACE_ONLY
