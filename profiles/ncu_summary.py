@@ -47,9 +47,15 @@ def raw(rep):
 
 def lines(rep, pat, top, ncupat):
     tmp = tempfile.mkdtemp()
-    subprocess.run(["cuobjdump", "-xelf", "all", (sys.argv[sys.argv.index("--lib") + 1] if "--lib" in sys.argv else os.path.join(ROOT, "polymps_b200", "libpmps.so"))], cwd=tmp, capture_output=True)
+    # the walker translation units all come from pmps_walk_g.cu: extracted from the library their cubins overwrite one another, so the
+    # object files of the build (one directory each) are taken where they exist
+    objs = sorted(glob.glob(os.path.join(ROOT, "polymps_b200", "csrc", "_build", "*.o"))) if "--lib" not in sys.argv else []
+    srcs = objs or [sys.argv[sys.argv.index("--lib") + 1] if "--lib" in sys.argv else os.path.join(ROOT, "polymps_b200", "libpmps.so")]
+    for k, src in enumerate(srcs):
+        d = os.path.join(tmp, "e%03d" % k); os.makedirs(d)
+        subprocess.run(["cuobjdump", "-xelf", "all", src], cwd=d, capture_output=True)
     seq = None
-    for cub in glob.glob(os.path.join(tmp, "*.cubin")):
+    for cub in glob.glob(os.path.join(tmp, "*", "*.cubin")):
         txt = subprocess.run(["nvdisasm", "-g", "-c", cub], capture_output=True, text=True).stdout
         cur, name, acc = None, None, {}
         for ln in txt.splitlines():
