@@ -33,6 +33,14 @@ __global__ void k_cell_hist(const __grid_constant__ DevView S, const __grid_cons
 			atomicOr(&S.flags[FLAG_GUARD], 2);   // a live particle outside the bucket grid: the reference would corrupt memory here
 			ix = min(max(ix, 0), P.numBucketsX - 1); iy = min(max(iy, 0), P.numBucketsY - 1); iz = min(max(iz, 0), P.numBucketsZ - 1);
 		}
+		if (P.domainTypeBC == 1) {
+			// periodic domain: a particle handed over beyond a periodic face (an initial state; the next out-of-domain check wraps it) lies in a
+			// border layer, which holds no particles of its own here — it aliases the opposite inner layer (tv_halo_cell).  It is sorted into the
+			// inner layer next to it: its search then covers the border layer's alias and that layer, i.e. everything within reach.
+			int& ca = P.periodicAxis == 0 ? ix : P.periodicAxis == 1 ? iy : iz;
+			const int na = P.periodicAxis == 0 ? P.numBucketsX : P.periodicAxis == 1 ? P.numBucketsY : P.numBucketsZ;
+			ca = min(max(ca, 1), na - 2);
+		}
 		cell = cell_index(K, ix, iy, iz);   // tile-major: the particles of a tile end up in consecutive slots
 	}
 	newCell[i] = cell;

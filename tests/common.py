@@ -177,6 +177,9 @@ VARIANTS = {
     "nn3d_poly_slip": (lambda: __import__("polymps_b200.cases", fromlist=["x"]).dam3d_erosion(5, 4, 5, 3, jitter=0.03, name="var", slip=1),
                        lambda: __import__("polymps_b200.cases", fromlist=["x"]).dam3d_erosion(10, 6, 10, 4, jitter=0.03, name="var", slip=1)),
     "3d_per_edge": (lambda: __import__("polymps_b200.cases", fromlist=["x"]).channel3d_periodic(8, 30, 8, jitter=0.04, name="var"),) * 2,
+    # the alias layers under more of the kernel family: velocity shifting, mean PND, correction matrix + gradient type 0, free slip, DPC, E-MPS
+    "2d_per_shift1": _per2(shifting=1), "2d_per_pnd1": _per2(pnd_type=1), "3d_per_gradcorr": _per3(grad_type=0, grad_corr=True, pnd_type=0),
+    "3d_per_slip": _per3(slip=1), "3d_per_dpc": tuple(_jittered(b) for b in _per3(collision=1)), "3d_per_emps": _per3(mps_type=0),
     "3d_per": _per3(), "3d_per_right": _per3(drift=-1.0, window=-0.45), "3d_per_inc": _per3(incompressible=True),
     "ood": _splash((6, 5, 5), (14, 8, 10)),   # particles leave the domain (swap-with-last compaction, src/MpsParticle.cpp:286-396)
     "slip": _v3(slip=1), "grad0": _v3(grad_type=0), "grad1": _v3(grad_type=1), "grad2": _v3(grad_type=2),
