@@ -165,7 +165,7 @@ int pmps_upload_rows_device(pmps_t* h, const PmpsHostArrays* device_arrays, int 
 int pmps_download_device(pmps_t* h, PmpsHostArrays* device_arrays);   /* gather to host order into device arrays */
 
 /* ---- stage calls: one per reference method, in mainLoopOfSimulation order (src/main.cpp:256-456) ----------- */
-int pmps_update_buckets(pmps_t* h);              /* MpsBucket::updateParticlesID            src/MpsBucket.cpp:299-353 */
+int pmps_update_buckets(pmps_t* h);              /* MpsBucket::updateParticlesID            src/MpsBucket.cpp:299-353 (+ copyDataBetweenBuckets :356-417 for a periodic domain) */
 int pmps_calc_volume_fraction(pmps_t* h);        /* MpsViscosity::calcVolumeFraction        src/MpsViscosity.cpp:104-190 (fluidType 1) */
 int pmps_calc_viscosity_interaction(pmps_t* h);  /* MpsViscosity::calcViscosityInteractionVal src/MpsViscosity.cpp:194-700 (fluidType 1) */
 int pmps_calc_wall_viscosity_interaction(pmps_t* h);  /* MpsViscosity::calcWallSlipViscosityInteractionVal / calcWallNoSlipViscosityInteractionVal src/MpsViscosity.cpp:703-1526
@@ -176,7 +176,8 @@ int pmps_add_gravity(pmps_t* h);                 /* MpsParticle::addGravity     
 int pmps_prediction_press_gradient(pmps_t* h);      /* MpsPressure::predictionPressGradient     src/MpsPressure.cpp:932-1028 (relax_fact < 1) */
 int pmps_prediction_wall_press_gradient(pmps_t* h); /* MpsPressure::predictionWallPressGradient src/MpsPressure.cpp:1031-1214 */
 int pmps_predict(pmps_t* h);                     /* MpsParticleVelPos::predictionVelocityPosition  src/MpsParticleVelPos.cpp:20-50 */
-int pmps_check_out_domain(pmps_t* h);            /* MpsParticle::checkParticleOutDomain     src/MpsParticle.cpp:234-402 */
+int pmps_check_out_domain(pmps_t* h);            /* MpsParticle::checkParticleOutDomain     src/MpsParticle.cpp:234-402; periodic domain: the wrap (:236-269) first,
+                                                  * and when it moved anybody (one 4-byte read-back) the bucket order is re-made before the call returns */
 int pmps_collisions(pmps_t* h);                  /* MpsParticleCollision::checkParticleCollisions / ...Dynamic...  src/MpsParticleCollision.cpp:22-292 */
 int pmps_wall_closest_point(pmps_t* h);          /* PolygonMesh::closestPointPNDBoundaryAABB (all meshes) + updateParticlesNearPolygonMesh  src/PolygonMesh.cpp:585-795 */
 int pmps_wall_npcd(pmps_t* h);                   /* MpsPndNeigh::calcWallNPCD               src/MpsPndNeigh.cpp:105-195 */
