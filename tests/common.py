@@ -18,6 +18,10 @@ from polymps_b200.state import HostState, ALL_FIELDS, I32, U8  # noqa: E402
 from make_golden import load_golden  # noqa: E402
 
 GOLDEN = ["w3", "w3j", "i3", "w2", "i2", "n2", "b3", "e3", "o3"]
+# reference dumps that pin the ORACLE only (tests/test_oracle_golden.py): periodic domains (2D, 3D, and the search from inside an aliased border
+# layer) and the non-Newtonian rheology with polygon walls.  The device path is checked against the oracle on the same option sets
+# (tests/test_periodic_gpu.py, tests/test_wall_rheology_gpu.py): a stage replay from a dump would need the reference's stale bucket lists.
+GOLDEN_ORACLE = ["p2", "p3", "pe", "q3"]
 
 # ref_driver stage name -> stage calls (oracle method names == engine method names)
 STAGE_MAP = {

@@ -46,6 +46,15 @@ def golden_cases():
         # particles leave the domain in the out-of-domain checks of steps 3-7 (dumped: 4 and 5), the last live particle among them
         # (serial swap-with-last compaction, src/MpsParticle.cpp:286-396)
         "o3": (cases.dam3d_splash(7, 5, 6, name="o3"), (4, 5)),
+        # ---- oracle-only fixtures (tests/test_oracle_golden.py, GOLDEN_ORACLE in tests/common.py): features of round 2 pinned where the
+        # reference tree is absent.  Periodic domain, 2D particle walls and 3D polygon walls: particles wrap in the first dumped step;
+        "p2": (cases.channel2d_periodic(24, 6, hump=3, name="p2"), (1, 2)),
+        "p3": (cases.channel3d_periodic(5, 22, 5, jitter=0.05, name="p3"), (1, 2)),
+        # the larger periodic block: in step 1 a near-wall particle crosses the face during the shifting and takes the wall-shifting pass from
+        # inside the aliased border layer (the shift is that of the bucket actually read, oracle periodic_shift);
+        "pe": (cases.channel3d_periodic(8, 30, 8, jitter=0.04, name="pe"), (1,)),
+        # non-Newtonian rheology with polygon walls (option set of input/damErosion3D_WC.json): the wall variants of the viscosity model
+        "q3": (cases.dam3d_erosion(5, 4, 5, 3, jitter=0.03, name="q3"), (1, 2)),
     }
 
 

@@ -5,14 +5,14 @@ the reference's own: every golden fixture carries the parameter block `ref_drive
 import numpy as np
 import pytest
 
-from common import GOLDEN, golden
+from common import GOLDEN, GOLDEN_ORACLE, golden
 
 
 def _close(a, b, rel=1e-14):
     return a == b or abs(a - b) <= rel * max(abs(a), abs(b))
 
 
-@pytest.mark.parametrize("name", GOLDEN)
+@pytest.mark.parametrize("name", GOLDEN + GOLDEN_ORACLE)
 def test_parameter_block_equals_the_references(name):
     order, dumps, meta, ps, meshes = golden(name)
     ref = meta["params"]

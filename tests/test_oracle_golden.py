@@ -5,7 +5,7 @@ mode).  Only the PPE solve is compared with a tolerance: Eigen's dot products ar
 import numpy as np
 import pytest
 
-from common import GOLDEN, STAGE_MAP, golden, stage_sequence, dumped_steps, state_from, compare_states
+from common import GOLDEN_ORACLE, stage_calls, GOLDEN, STAGE_MAP, golden, stage_sequence, dumped_steps, state_from, compare_states
 import pyoracle
 
 
@@ -39,6 +39,35 @@ def test_oracle_stage_by_stage_bit_identical(name):
             assert not bad, "%s step %d stage %s: %s" % (name, step, stage, bad)
             n_checked += 1
     assert n_checked >= 20
+
+
+@pytest.mark.parametrize("name", GOLDEN_ORACLE)
+def test_oracle_round2_features_bit_identical_to_committed_reference_dumps(name):
+    """Periodic domains and the polygon-wall rheology against reference dumps that travel with the repository (the live-reference runs of
+    tests/test_oracle_variants.py need /root/reference at build time): every stage of the dumped steps, bit for bit."""
+    order, dumps, meta, ps, meshes = golden(name)
+    n_checked = 0; wrapped = 0
+    for step in dumped_steps(order):
+        for stage, prev_name, cur_name in stage_sequence(order, step):
+            prev, cur = dumps[prev_name], dumps[cur_name]
+            st = state_from(prev)
+            orc = _oracle_for(ps, st, meshes, prev)
+            for call in stage_calls(stage, ps):
+                getattr(orc, call)()
+            bad = compare_states(st, cur, rtol=0.0, live_only=False)
+            assert not bad, "%s step %d stage %s: %s" % (name, step, stage, bad)
+            if stage == "updateParticlesID":   # the aliased border layers included (copyDataBetweenBuckets)
+                for a, b in (("firstParticleInBucket", orc.first), ("lastParticleInBucket", orc.last), ("nextParticleInSameBucket", orc.next)):
+                    assert np.array_equal(cur[a], b), a
+            if ps.domainTypeBC == 1 and stage.startswith("checkParticleOutDomain"):
+                a = np.asarray(prev["pos"]).reshape(-1, 3)[:, ps.periodicAxis]; b = np.asarray(cur["pos"]).reshape(-1, 3)[:, ps.periodicAxis]
+                wrapped += int((np.abs(a - b) > 0.5 * ps.periodicLen).sum())
+            n_checked += 1
+    assert n_checked >= 15
+    if ps.domainTypeBC == 1:
+        assert wrapped >= 3, wrapped
+    else:
+        assert ps.fluidType == 1 and ps.wallType == 1
 
 
 @pytest.mark.parametrize("name", GOLDEN)
